@@ -1,0 +1,526 @@
+// layers.cu — PReLU, BatchNorm, softmax-over-branches, MiniBatchStdDev, BCE, separable resampling.
+// All HBM-bound; see DESIGN.md for the per-kernel algorithmic bytes.
+#include "common.cuh"
+
+namespace ganb200 {
+
+// ------------------------------------------------------------------ PReLU family on [N,C,HW], a_n in {1, C}
+// MODE 0: y = x>0 ? x : a*x          (g unused)
+// MODE 1: y = g * (x>0 ? 1 : a)
+template <int MODE>
+__global__ void __launch_bounds__(256) prelu_kernel(const float* __restrict__ g, const float* __restrict__ x,
+                                                    const float* __restrict__ a, float* __restrict__ y,
+                                                    int64_t rows, int C, int HW, int a_n) {
+  if (HW >= 64) {
+    bool vec = ((HW & 3) == 0) && aligned16(x) && aligned16(y) && (MODE == 0 || aligned16(g));
+    for (int64_t row = blockIdx.x; row < rows; row += gridDim.x) {
+      float slope = a[a_n == 1 ? 0 : (int)(row % C)];
+      const float* xr = x + row * HW;
+      const float* gr = MODE == 1 ? g + row * HW : nullptr;
+      float* yr = y + row * HW;
+      if (vec) {
+        for (int i = threadIdx.x; i < (HW >> 2); i += blockDim.x) {
+          float4 v = reinterpret_cast<const float4*>(xr)[i], r;
+          if (MODE == 0) {
+            r.x = v.x > 0.f ? v.x : slope * v.x; r.y = v.y > 0.f ? v.y : slope * v.y;
+            r.z = v.z > 0.f ? v.z : slope * v.z; r.w = v.w > 0.f ? v.w : slope * v.w;
+          } else {
+            float4 q = reinterpret_cast<const float4*>(gr)[i];
+            r.x = v.x > 0.f ? q.x : slope * q.x; r.y = v.y > 0.f ? q.y : slope * q.y;
+            r.z = v.z > 0.f ? q.z : slope * q.z; r.w = v.w > 0.f ? q.w : slope * q.w;
+          }
+          reinterpret_cast<float4*>(yr)[i] = r;
+        }
+      } else {
+        for (int i = threadIdx.x; i < HW; i += blockDim.x) {
+          float v = xr[i];
+          float src = MODE == 0 ? v : gr[i];
+          yr[i] = v > 0.f ? src : slope * src;
+        }
+      }
+    }
+  } else {
+    int64_t total = rows * HW;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+      float slope = a[a_n == 1 ? 0 : (int)((i / HW) % C)];
+      float v = x[i];
+      float src = MODE == 0 ? v : g[i];
+      y[i] = v > 0.f ? src : slope * src;
+    }
+  }
+}
+
+// out[c or 0] += sum over (n,hw) of  MODE 0: gy*min(x,0)   MODE 1: u*v*[x<=0]
+// grid (groups, nsplit): groups = a_n==1 ? 1 : C
+template <int MODE>
+__global__ void __launch_bounds__(256) prelu_reduce_kernel(const float* __restrict__ u, const float* __restrict__ v,
+                                                           const float* __restrict__ x, float* __restrict__ out,
+                                                           int N, int C, int HW, int a_n) {
+  float acc = 0.f;
+  int split = blockIdx.y, nsplit = gridDim.y;
+  if (a_n == 1) {
+    int64_t len = (int64_t)N * C * HW;
+    int64_t chunk = (len + nsplit - 1) / nsplit;
+    int64_t lo = split * chunk, hi = lo + chunk < len ? lo + chunk : len;
+    for (int64_t i = lo + threadIdx.x; i < hi; i += blockDim.x) {
+      float xv = x[i];
+      if (!(xv > 0.f)) acc += MODE == 0 ? u[i] * xv : u[i] * v[i];
+    }
+  } else {
+    int c = blockIdx.x;
+    for (int n = split; n < N; n += nsplit) {
+      int64_t base = ((int64_t)n * C + c) * HW;
+      for (int i = threadIdx.x; i < HW; i += blockDim.x) {
+        float xv = x[base + i];
+        if (!(xv > 0.f)) acc += MODE == 0 ? u[base + i] * xv : u[base + i] * v[base + i];
+      }
+    }
+  }
+  float t = block_sum<256>(acc);
+  if (threadIdx.x == 0) atomicAdd(out + (a_n == 1 ? 0 : blockIdx.x), t);
+}
+
+}  // namespace ganb200
+using namespace ganb200;
+
+static int rows_grid(int64_t rows, int HW) {
+  if (HW >= 64) return (int)(rows < (int64_t)kNumSMs * 16 ? rows : (int64_t)kNumSMs * 16);
+  return ew_grid(rows * HW, 256, 4);
+}
+
+static void prelu_reduce_dims(int N, int C, int HW, int a_n, dim3* grid) {
+  int groups = a_n == 1 ? 1 : C;
+  int64_t per_group = (int64_t)N * C * HW / groups;
+  int max_split = a_n == 1 ? (int)((per_group + 2047) / 2048) : N;
+  int want = (kNumSMs * 4 + groups - 1) / groups;
+  int nsplit = want < max_split ? want : max_split;
+  if (nsplit < 1) nsplit = 1;
+  *grid = dim3(groups, nsplit);
+}
+
+extern "C" int ganb200_prelu_fwd(const float* x, const float* a, float* y, int N, int C, int HW, int a_n, void* stream) {
+  GB_REQUIRE(a_n == 1 || a_n == C, GANB200_BAD_SHAPE, "prelu: a_n must be 1 or C");
+  int64_t rows = (int64_t)N * C;
+  if (rows * HW == 0) return 0;
+  prelu_kernel<0><<<rows_grid(rows, HW), 256, 0, (cudaStream_t)stream>>>(nullptr, x, a, y, rows, C, HW, a_n);
+  GB_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int ganb200_maskscale(const float* g, const float* x, const float* a, float* y, int N, int C, int HW, int a_n,
+                                 void* stream) {
+  GB_REQUIRE(a_n == 1 || a_n == C, GANB200_BAD_SHAPE, "maskscale: a_n must be 1 or C");
+  int64_t rows = (int64_t)N * C;
+  if (rows * HW == 0) return 0;
+  prelu_kernel<1><<<rows_grid(rows, HW), 256, 0, (cudaStream_t)stream>>>(g, x, a, y, rows, C, HW, a_n);
+  GB_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int ganb200_prelu_bwd(const float* gy, const float* x, const float* a, float* gx, float* ga, int N, int C,
+                                 int HW, int a_n, void* stream) {
+  GB_REQUIRE(a_n == 1 || a_n == C, GANB200_BAD_SHAPE, "prelu_bwd: a_n must be 1 or C");
+  cudaStream_t s = (cudaStream_t)stream;
+  int64_t rows = (int64_t)N * C;
+  if (rows * HW == 0) return 0;
+  if (gx) {
+    prelu_kernel<1><<<rows_grid(rows, HW), 256, 0, s>>>(gy, x, a, gx, rows, C, HW, a_n);
+    GB_CHECK_LAUNCH();
+  }
+  if (ga) {
+    dim3 grid;
+    prelu_reduce_dims(N, C, HW, a_n, &grid);
+    GB_CHECK_CUDA(cudaMemsetAsync(ga, 0, sizeof(float) * a_n, s));
+    prelu_reduce_kernel<0><<<grid, 256, 0, s>>>(gy, nullptr, x, ga, N, C, HW, a_n);
+    GB_CHECK_LAUNCH();
+  }
+  return 0;
+}
+
+extern "C" int ganb200_masked_dot(const float* u, const float* v, const float* x, float* out, int N, int C, int HW,
+                                  int a_n, void* stream) {
+  GB_REQUIRE(a_n == 1 || a_n == C, GANB200_BAD_SHAPE, "masked_dot: a_n must be 1 or C");
+  cudaStream_t s = (cudaStream_t)stream;
+  dim3 grid;
+  prelu_reduce_dims(N, C, HW, a_n, &grid);
+  GB_CHECK_CUDA(cudaMemsetAsync(out, 0, sizeof(float) * a_n, s));
+  prelu_reduce_kernel<1><<<grid, 256, 0, s>>>(u, v, x, out, N, C, HW, a_n);
+  GB_CHECK_LAUNCH();
+  return 0;
+}
+
+// ------------------------------------------------------------------ BatchNorm (training mode)
+namespace ganb200 {
+
+// PASS 0: out_a[c] += sum x * inv_count                     (mean)
+// PASS 1: out_a[c] += sum (x-mean[c])^2 * inv_count          (biased variance)
+// PASS 2: out_a[c] += sum gy ; out_b[c] += sum gy*(x-mean)*invstd
+template <int PASS>
+__global__ void __launch_bounds__(256) bn_reduce_kernel(const float* __restrict__ x, const float* __restrict__ gy,
+                                                        const float* __restrict__ mean, const float* __restrict__ invstd,
+                                                        float* __restrict__ out_a, float* __restrict__ out_b,
+                                                        int N, int C, int HW, float inv_count) {
+  int c = blockIdx.x, split = blockIdx.y, nsplit = gridDim.y;
+  float m = PASS >= 1 ? mean[c] : 0.f;
+  float is = PASS == 2 ? invstd[c] : 0.f;
+  float a = 0.f, b = 0.f;
+  if (HW >= 32) {
+    for (int n = split; n < N; n += nsplit) {
+      int64_t base = ((int64_t)n * C + c) * HW;
+      for (int i = threadIdx.x; i < HW; i += blockDim.x) {
+        float xv = x[base + i];
+        if (PASS == 0) a += xv;
+        else if (PASS == 1) { float d = xv - m; a += d * d; }
+        else { float g = gy[base + i]; a += g; b += g * (xv - m) * is; }
+      }
+    }
+  } else {
+    // small HW: threads over (n, hw) pairs
+    int64_t total = (int64_t)N * HW;
+    for (int64_t j = (int64_t)split * blockDim.x + threadIdx.x; j < total; j += (int64_t)nsplit * blockDim.x) {
+      int n = (int)(j / HW), i = (int)(j % HW);
+      int64_t idx = ((int64_t)n * C + c) * HW + i;
+      float xv = x[idx];
+      if (PASS == 0) a += xv;
+      else if (PASS == 1) { float d = xv - m; a += d * d; }
+      else { float g = gy[idx]; a += g; b += g * (xv - m) * is; }
+    }
+  }
+  float ta = block_sum<256>(a);
+  if (PASS == 2) {
+    float tb = block_sum<256>(b);
+    if (threadIdx.x == 0) { atomicAdd(out_a + c, ta); atomicAdd(out_b + c, tb); }
+  } else {
+    if (threadIdx.x == 0) atomicAdd(out_a + c, ta * inv_count);
+  }
+}
+
+// MODE 0 (forward): y = (x-mean)*invstd*gamma + beta ; row n==0 also writes invstd + running stats
+// MODE 1 (backward): gx = gamma*invstd*(gy - sgy/cnt - xhat*sgx/cnt) ; row n==0 writes ggamma/gbeta
+template <int MODE>
+__global__ void __launch_bounds__(256) bn_apply_kernel(const float* __restrict__ x, const float* __restrict__ gy,
+                                                       const float* __restrict__ mean, const float* __restrict__ var_or_invstd,
+                                                       const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                       const float* __restrict__ sgy, const float* __restrict__ sgx,
+                                                       float* __restrict__ y, float* __restrict__ o0, float* __restrict__ o1,
+                                                       float* __restrict__ o2, int N, int C, int HW, float eps,
+                                                       float momentum, float count) {
+  int64_t rows = (int64_t)N * C;
+  int64_t total = rows * HW;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    int64_t row = i / HW;
+    int c = (int)(row % C);
+    float m = mean[c];
+    float gm = gamma ? gamma[c] : 1.f;
+    if (MODE == 0) {
+      float is = 1.f / sqrtf(var_or_invstd[c] + eps);
+      float bt = beta ? beta[c] : 0.f;
+      y[i] = (x[i] - m) * is * gm + bt;
+      if (row < C && (i % HW) == 0) {  // n == 0, first element of the row
+        float var = var_or_invstd[c];
+        if (o0) o0[c] = is;
+        if (o1) o1[c] = (1.f - momentum) * o1[c] + momentum * m;
+        if (o2) o2[c] = (1.f - momentum) * o2[c] + momentum * (count > 1.f ? var * count / (count - 1.f) : var);
+      }
+    } else {
+      float is = var_or_invstd[c];
+      float xhat = (x[i] - m) * is;
+      float a = sgy[c] / count, b = sgx[c] / count;
+      y[i] = gm * is * (gy[i] - a - xhat * b);
+      if (row < C && (i % HW) == 0) {
+        if (o0) o0[c] = sgx[c];
+        if (o1) o1[c] = sgy[c];
+      }
+    }
+  }
+}
+
+}  // namespace ganb200
+
+static dim3 bn_reduce_grid(int N, int C, int HW) {
+  int want = (kNumSMs * 4 + C - 1) / C;
+  int max_split = HW >= 32 ? N : (int)(((int64_t)N * HW + 255) / 256);
+  int nsplit = want < max_split ? want : max_split;
+  if (nsplit < 1) nsplit = 1;
+  return dim3(C, nsplit);
+}
+
+extern "C" int ganb200_bn_stats(const float* x, float* mean, float* var_biased, int N, int C, int HW, void* stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  GB_REQUIRE(N > 0 && C > 0 && HW > 0, GANB200_BAD_SHAPE, "bn_stats: empty");
+  float inv = 1.f / ((float)N * (float)HW);
+  dim3 grid = bn_reduce_grid(N, C, HW);
+  GB_CHECK_CUDA(cudaMemsetAsync(mean, 0, sizeof(float) * C, s));
+  GB_CHECK_CUDA(cudaMemsetAsync(var_biased, 0, sizeof(float) * C, s));
+  bn_reduce_kernel<0><<<grid, 256, 0, s>>>(x, nullptr, nullptr, nullptr, mean, nullptr, N, C, HW, inv);
+  bn_reduce_kernel<1><<<grid, 256, 0, s>>>(x, nullptr, mean, nullptr, var_biased, nullptr, N, C, HW, inv);
+  GB_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int ganb200_bn_apply(const float* x, const float* mean, const float* var_biased, const float* gamma,
+                                const float* beta, float* y, float* save_invstd, float* running_mean,
+                                float* running_var, int N, int C, int HW, float eps, float momentum,
+                                int64_t count_total, void* stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  int64_t total = (int64_t)N * C * HW;
+  bn_apply_kernel<0><<<ew_grid(total, 256, 4), 256, 0, s>>>(x, nullptr, mean, var_biased, gamma, beta, nullptr, nullptr, y,
+                                                           save_invstd, running_mean, running_var, N, C, HW, eps,
+                                                           momentum, (float)count_total);
+  GB_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int ganb200_bn_bwd_reduce(const float* gy, const float* x, const float* mean, const float* invstd,
+                                     float* sum_gy, float* sum_gy_xhat, int N, int C, int HW, void* stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  GB_CHECK_CUDA(cudaMemsetAsync(sum_gy, 0, sizeof(float) * C, s));
+  GB_CHECK_CUDA(cudaMemsetAsync(sum_gy_xhat, 0, sizeof(float) * C, s));
+  bn_reduce_kernel<2><<<bn_reduce_grid(N, C, HW), 256, 0, s>>>(x, gy, mean, invstd, sum_gy, sum_gy_xhat, N, C, HW, 1.f);
+  GB_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int ganb200_bn_bwd_apply(const float* gy, const float* x, const float* mean, const float* invstd,
+                                    const float* gamma, const float* sum_gy, const float* sum_gy_xhat, float* gx,
+                                    float* ggamma, float* gbeta, int N, int C, int HW, int64_t count_total,
+                                    void* stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  int64_t total = (int64_t)N * C * HW;
+  bn_apply_kernel<1><<<ew_grid(total, 256, 4), 256, 0, s>>>(x, gy, mean, invstd, gamma, nullptr, sum_gy, sum_gy_xhat, gx,
+                                                           ggamma, gbeta, nullptr, N, C, HW, 0.f, 0.f,
+                                                           (float)count_total);
+  GB_CHECK_LAUNCH();
+  return 0;
+}
+
+// ------------------------------------------------------------------ softmax over M of [B,M,C]
+namespace ganb200 {
+
+__global__ void __launch_bounds__(256) softmax_m_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, int B,
+                                                            int M, int C) {
+  int64_t total = (int64_t)B * C;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    int b = (int)(i / C), c = (int)(i % C);
+    const float* xp = x + (int64_t)b * M * C + c;
+    float* yp = y + (int64_t)b * M * C + c;
+    float mx = -INFINITY;
+    for (int m = 0; m < M; ++m) mx = fmaxf(mx, xp[(int64_t)m * C]);
+    float sum = 0.f;
+    for (int m = 0; m < M; ++m) sum += expf(xp[(int64_t)m * C] - mx);
+    float inv = 1.f / sum;
+    for (int m = 0; m < M; ++m) yp[(int64_t)m * C] = expf(xp[(int64_t)m * C] - mx) * inv;
+  }
+}
+
+__global__ void __launch_bounds__(256) softmax_m_bwd_kernel(const float* __restrict__ gy, const float* __restrict__ y,
+                                                            float* __restrict__ gx, int B, int M, int C) {
+  int64_t total = (int64_t)B * C;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    int b = (int)(i / C), c = (int)(i % C);
+    int64_t base = (int64_t)b * M * C + c;
+    float dot = 0.f;
+    for (int m = 0; m < M; ++m) dot += gy[base + (int64_t)m * C] * y[base + (int64_t)m * C];
+    for (int m = 0; m < M; ++m) {
+      int64_t k = base + (int64_t)m * C;
+      gx[k] = y[k] * (gy[k] - dot);
+    }
+  }
+}
+
+// ------------------------------------------------------------------ MiniBatchStdDev scalar, x as [G,L], G <= 16
+// MODE 0 fwd: out[0] += sum_j sigma_j / L
+// MODE 1 bwd: gx[q,j] = g * (x_qj - mu_j) / ((G-1) L sigma_j)
+// MODE 2 bwd_bwd: out[0] += sum ggx_qj (x_qj-mu_j)/((G-1) L sigma_j);
+//                 gx[r,j] = g/((G-1)L) * ((ggx_rj - mean_q ggx_qj)/sigma_j - (x_rj-mu_j)/((G-1) sigma_j^3) * sum_q ggx_qj (x_qj-mu_j))
+template <int MODE>
+__global__ void __launch_bounds__(256) mbstd_kernel(const float* __restrict__ g, const float* __restrict__ x,
+                                                    const float* __restrict__ ggx, float* __restrict__ out,
+                                                    float* __restrict__ gx, int G, int64_t L, float eps) {
+  float acc = 0.f;
+  float gv = MODE >= 1 ? g[0] : 0.f;
+  float invL = 1.f / (float)L, invG1 = 1.f / (float)(G - 1);
+  for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < L; j += (int64_t)gridDim.x * blockDim.x) {
+    float xv[16];
+    float mu = 0.f;
+    for (int q = 0; q < G; ++q) { xv[q] = x[(int64_t)q * L + j]; mu += xv[q]; }
+    mu /= (float)G;
+    float ss = 0.f;
+    for (int q = 0; q < G; ++q) { xv[q] -= mu; ss += xv[q] * xv[q]; }
+    float sigma = sqrtf(ss * invG1 + eps);
+    if (MODE == 0) {
+      acc += sigma * invL;
+    } else if (MODE == 1) {
+      float k = gv * invG1 * invL / sigma;
+      for (int q = 0; q < G; ++q) gx[(int64_t)q * L + j] = k * xv[q];
+    } else {
+      float gg[16];
+      float gmean = 0.f, dot = 0.f;
+      for (int q = 0; q < G; ++q) { gg[q] = ggx[(int64_t)q * L + j]; gmean += gg[q]; dot += gg[q] * xv[q]; }
+      gmean /= (float)G;
+      acc += dot * invG1 * invL / sigma;
+      float k = gv * invG1 * invL;
+      float c3 = dot * invG1 / (sigma * sigma * sigma);
+      for (int q = 0; q < G; ++q) gx[(int64_t)q * L + j] = k * ((gg[q] - gmean) / sigma - xv[q] * c3);
+    }
+  }
+  if (MODE != 1) {
+    float t = block_sum<256>(acc);
+    if (threadIdx.x == 0) atomicAdd(out, t);
+  }
+}
+
+// ------------------------------------------------------------------ BCE (mean), torch semantics
+__global__ void __launch_bounds__(256) bce_fwd_kernel(const float* __restrict__ p, const float* __restrict__ t,
+                                                      float* __restrict__ out, int* __restrict__ flag, int64_t n) {
+  float acc = 0.f;
+  bool bad = false;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    float pv = p[i], tv = t[i];
+    if (!(pv >= 0.f && pv <= 1.f)) bad = true;
+    float lp = fmaxf(logf(pv), -100.f), lq = fmaxf(logf(1.f - pv), -100.f);
+    acc += -(tv * lp + (1.f - tv) * lq);
+  }
+  if (bad && flag) atomicExch(flag, 1);
+  float s = block_sum<256>(acc);
+  if (threadIdx.x == 0) atomicAdd(out, s / (float)n);
+}
+
+__global__ void __launch_bounds__(256) bce_bwd_kernel(const float* __restrict__ g, const float* __restrict__ p,
+                                                      const float* __restrict__ t, float* __restrict__ gp, int64_t n) {
+  float gv = g[0] / (float)n;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    float pv = p[i];
+    gp[i] = gv * (pv - t[i]) / fmaxf((1.f - pv) * pv, 1e-12f);
+  }
+}
+
+// ------------------------------------------------------------------ separable resampling with tap tables
+__global__ void __launch_bounds__(256) resample2d_kernel(const float* __restrict__ x, float* __restrict__ y, int64_t NC,
+                                                         int Hi, int Wi, int Ho, int Wo, const int* __restrict__ ih,
+                                                         const float* __restrict__ wh, int Th,
+                                                         const int* __restrict__ iw, const float* __restrict__ ww, int Tw) {
+  int64_t total = NC * Ho * Wo;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    int wo = (int)(i % Wo);
+    int ho = (int)((i / Wo) % Ho);
+    int64_t nc = i / ((int64_t)Wo * Ho);
+    const float* xp = x + nc * Hi * Wi;
+    float acc = 0.f;
+    for (int a = 0; a < Th; ++a) {
+      float wa = wh[ho * Th + a];
+      if (wa == 0.f) continue;
+      const float* xr = xp + (int64_t)ih[ho * Th + a] * Wi;
+      float racc = 0.f;
+      for (int b = 0; b < Tw; ++b) racc = fmaf(ww[wo * Tw + b], xr[iw[wo * Tw + b]], racc);
+      acc = fmaf(wa, racc, acc);
+    }
+    y[i] = acc;
+  }
+}
+
+__global__ void __launch_bounds__(256) mixup_kernel(const float* __restrict__ t, const float* __restrict__ f, float lam,
+                                                    float* __restrict__ out, int64_t n) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    out[i] = lam * t[i] + (1.f - lam) * f[i];
+}
+
+// units/mixup.py:26  label:(B,1) f64 broadcast against (B,3,H,W): needs W==1 or B==W; label index = h (row!) when B==H.. 
+// torch broadcasting aligns trailing dims: label (B,1) -> (1,1,B,1): dim -2 (H) indexes label, dim -1 broadcast.
+__global__ void __launch_bounds__(256) mixup_wgan_kernel(const double* __restrict__ label, const float* __restrict__ t,
+                                                         const float* __restrict__ f, double* __restrict__ out, int B,
+                                                         int H, int W, int64_t n) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    int h = (int)((i / W) % H);
+    double l = label[B == 1 ? 0 : h];
+    out[i] = l * (double)t[i] + (1.0 - l) * (double)f[i];
+  }
+}
+
+__global__ void __launch_bounds__(256) clamp_kernel(float* __restrict__ x, int64_t n, float lo, float hi) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    x[i] = fminf(fmaxf(x[i], lo), hi);
+}
+
+}  // namespace ganb200
+
+extern "C" int ganb200_softmax_m_fwd(const float* x, float* y, int B, int M, int C, void* stream) {
+  softmax_m_fwd_kernel<<<ew_grid((int64_t)B * C, 256, 1), 256, 0, (cudaStream_t)stream>>>(x, y, B, M, C);
+  GB_CHECK_LAUNCH();
+  return 0;
+}
+extern "C" int ganb200_softmax_m_bwd(const float* gy, const float* y, float* gx, int B, int M, int C, void* stream) {
+  softmax_m_bwd_kernel<<<ew_grid((int64_t)B * C, 256, 1), 256, 0, (cudaStream_t)stream>>>(gy, y, gx, B, M, C);
+  GB_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int ganb200_mbstd_fwd(const float* x, float* out, int G, int64_t L, float eps, void* stream) {
+  GB_REQUIRE(G >= 2 && G <= 16 && L > 0, GANB200_BAD_SHAPE, "mbstd: need 2<=G<=16");
+  cudaStream_t s = (cudaStream_t)stream;
+  GB_CHECK_CUDA(cudaMemsetAsync(out, 0, sizeof(float), s));
+  mbstd_kernel<0><<<ew_grid(L, 256, 1), 256, 0, s>>>(nullptr, x, nullptr, out, nullptr, G, L, eps);
+  GB_CHECK_LAUNCH();
+  return 0;
+}
+extern "C" int ganb200_mbstd_bwd(const float* g, const float* x, float* gx, int G, int64_t L, float eps, void* stream) {
+  GB_REQUIRE(G >= 2 && G <= 16 && L > 0, GANB200_BAD_SHAPE, "mbstd: need 2<=G<=16");
+  mbstd_kernel<1><<<ew_grid(L, 256, 1), 256, 0, (cudaStream_t)stream>>>(g, x, nullptr, nullptr, gx, G, L, eps);
+  GB_CHECK_LAUNCH();
+  return 0;
+}
+extern "C" int ganb200_mbstd_bwd_bwd(const float* g, const float* x, const float* ggx, float* out_gg, float* out_gx,
+                                     int G, int64_t L, float eps, void* stream) {
+  GB_REQUIRE(G >= 2 && G <= 16 && L > 0, GANB200_BAD_SHAPE, "mbstd: need 2<=G<=16");
+  cudaStream_t s = (cudaStream_t)stream;
+  GB_CHECK_CUDA(cudaMemsetAsync(out_gg, 0, sizeof(float), s));
+  mbstd_kernel<2><<<ew_grid(L, 256, 1), 256, 0, s>>>(g, x, ggx, out_gg, out_gx, G, L, eps);
+  GB_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int ganb200_bce_fwd(const float* p, const float* t, float* out, int* range_flag, int64_t n, void* stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  GB_REQUIRE(n > 0, GANB200_BAD_SHAPE, "bce: empty");
+  GB_CHECK_CUDA(cudaMemsetAsync(out, 0, sizeof(float), s));
+  if (range_flag) GB_CHECK_CUDA(cudaMemsetAsync(range_flag, 0, sizeof(int), s));
+  bce_fwd_kernel<<<ew_grid(n, 256, 4), 256, 0, s>>>(p, t, out, range_flag, n);
+  GB_CHECK_LAUNCH();
+  return 0;
+}
+extern "C" int ganb200_bce_bwd(const float* g, const float* p, const float* t, float* gp, int64_t n, void* stream) {
+  bce_bwd_kernel<<<ew_grid(n, 256, 4), 256, 0, (cudaStream_t)stream>>>(g, p, t, gp, n);
+  GB_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int ganb200_resample2d(const float* x, float* y, int NC, int Hi, int Wi, int Ho, int Wo, const int* ih,
+                                  const float* wh, int Th, const int* iw, const float* ww, int Tw, void* stream) {
+  int64_t total = (int64_t)NC * Ho * Wo;
+  if (total == 0) return 0;
+  GB_REQUIRE(Th > 0 && Tw > 0, GANB200_BAD_SHAPE, "resample2d: empty tap table");
+  resample2d_kernel<<<ew_grid(total, 256, 2), 256, 0, (cudaStream_t)stream>>>(x, y, NC, Hi, Wi, Ho, Wo, ih, wh, Th, iw, ww, Tw);
+  GB_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int ganb200_mixup(const float* t, const float* f, float lam, float* out, int64_t n, void* stream) {
+  if (n <= 0) return 0;
+  mixup_kernel<<<ew_grid(n, 256, 4), 256, 0, (cudaStream_t)stream>>>(t, f, lam, out, n);
+  GB_CHECK_LAUNCH();
+  return 0;
+}
+extern "C" int ganb200_mixup_wgan_f64(const double* label, const float* t, const float* f, double* out, int B, int C,
+                                      int H, int W, void* stream) {
+  GB_REQUIRE(B == 1 || B == H, GANB200_BAD_SHAPE, "mixup_wgan: (B,1) label only broadcasts against (B,C,H,W) when B==1 or B==H");
+  int64_t n = (int64_t)B * C * H * W;
+  mixup_wgan_kernel<<<ew_grid(n, 256, 4), 256, 0, (cudaStream_t)stream>>>(label, t, f, out, B, H, W, n);
+  GB_CHECK_LAUNCH();
+  return 0;
+}
+extern "C" int ganb200_clamp_(float* x, int64_t n, float lo, float hi, void* stream) {
+  if (n <= 0) return 0;
+  clamp_kernel<<<ew_grid(n, 256, 4), 256, 0, (cudaStream_t)stream>>>(x, n, lo, hi);
+  GB_CHECK_LAUNCH();
+  return 0;
+}

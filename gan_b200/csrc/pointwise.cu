@@ -1,0 +1,296 @@
+// pointwise.cu — HBM-bound elementwise / broadcast / reduction kernels (fp32, 128-bit accesses when aligned).
+// Roofline: HBM.  Algorithmic bytes = 4 B per element read + 4 B per element written, each tensor once.
+#include "common.cuh"
+
+namespace ganb200 {
+
+thread_local char g_last_error[512] = {0};
+
+// ------------------------------------------------------------------ unary
+__device__ __forceinline__ float u_apply(int op, float x, float p0, float p1) {
+  switch (op) {
+    case GANB200_U_SIGMOID: return 1.f / (1.f + expf(-x));
+    case GANB200_U_TANH: return tanhf(x);
+    case GANB200_U_SQUARE: return x * x;
+    case GANB200_U_AFFINE: return fmaf(p0, x, p1);
+    case GANB200_U_RSQRT_EPS: return 1.f / sqrtf(x + p0);
+    case GANB200_U_SQRT: return sqrtf(x);
+    case GANB200_U_LEAKY: return x > 0.f ? x : p0 * x;
+    case GANB200_U_RECIP: return 1.f / x;
+    case GANB200_U_LEAKY_MASK: return x > 0.f ? 1.f : p0;
+    case GANB200_U_COPY: return x;
+    case GANB200_U_POW: return powf(x, p0);
+  }
+  return x;
+}
+
+template <int OP>
+__global__ void __launch_bounds__(256) ew_unary_kernel(const float* __restrict__ x, float* __restrict__ y, int64_t n,
+                                                       float p0, float p1, bool vec) {
+  int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  if (vec) {
+    int64_t n4 = n >> 2;
+    const float4* x4 = reinterpret_cast<const float4*>(x);
+    float4* y4 = reinterpret_cast<float4*>(y);
+    for (int64_t i = tid; i < n4; i += stride) {
+      float4 a = x4[i];
+      a.x = u_apply(OP, a.x, p0, p1); a.y = u_apply(OP, a.y, p0, p1);
+      a.z = u_apply(OP, a.z, p0, p1); a.w = u_apply(OP, a.w, p0, p1);
+      y4[i] = a;
+    }
+    for (int64_t i = (n4 << 2) + tid; i < n; i += stride) y[i] = u_apply(OP, x[i], p0, p1);
+  } else {
+    for (int64_t i = tid; i < n; i += stride) y[i] = u_apply(OP, x[i], p0, p1);
+  }
+}
+
+// ------------------------------------------------------------------ binary
+__device__ __forceinline__ float b_apply(int op, float a, float b, float p0) {
+  switch (op) {
+    case GANB200_B_ADD: return a + b;
+    case GANB200_B_SUB: return a - b;
+    case GANB200_B_MUL: return a * b;
+    case GANB200_B_DIV: return a / b;
+    case GANB200_B_SIGMOID_BWD: return a * b * (1.f - b);
+    case GANB200_B_TANH_BWD: return a * (1.f - b * b);
+    case GANB200_B_LEAKY_BWD: return b > 0.f ? a : a * p0;
+  }
+  return a;
+}
+
+template <int OP>
+__global__ void __launch_bounds__(256) ew_binary_kernel(const float* __restrict__ a, const float* __restrict__ b,
+                                                        float* __restrict__ y, int64_t n, float p0, bool vec) {
+  int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  if (vec) {
+    int64_t n4 = n >> 2;
+    const float4* a4 = reinterpret_cast<const float4*>(a);
+    const float4* b4 = reinterpret_cast<const float4*>(b);
+    float4* y4 = reinterpret_cast<float4*>(y);
+    for (int64_t i = tid; i < n4; i += stride) {
+      float4 u = a4[i], v = b4[i], r;
+      r.x = b_apply(OP, u.x, v.x, p0); r.y = b_apply(OP, u.y, v.y, p0);
+      r.z = b_apply(OP, u.z, v.z, p0); r.w = b_apply(OP, u.w, v.w, p0);
+      y4[i] = r;
+    }
+    for (int64_t i = (n4 << 2) + tid; i < n; i += stride) y[i] = b_apply(OP, a[i], b[i], p0);
+  } else {
+    for (int64_t i = tid; i < n; i += stride) y[i] = b_apply(OP, a[i], b[i], p0);
+  }
+}
+
+// ------------------------------------------------------------------ broadcast ops on [N,C,HW]
+__device__ __forceinline__ float v_load(const float* __restrict__ v, int vmode, int n, int c, int C) {
+  switch (vmode) {
+    case GANB200_V_NC: return v[(int64_t)n * C + c];
+    case GANB200_V_C: return v[c];
+    case GANB200_V_N: return v[n];
+    default: return v[0];
+  }
+}
+
+// one block row per (n,c): grid-stride over rows, threads stride over HW.  z == nullptr -> plain op.
+// mode: 0 add, 1 mul, 2 fma (x + v*z)
+template <int MODE>
+__global__ void __launch_bounds__(256) ew_bcast_kernel(const float* __restrict__ x, const float* __restrict__ v,
+                                                       const float* __restrict__ z, float* __restrict__ y,
+                                                       int N, int C, int HW, int vmode) {
+  int64_t rows = (int64_t)N * C;
+  if (HW >= 64) {
+    bool vec = ((HW & 3) == 0) && aligned16(x) && aligned16(y) && (MODE != 2 || aligned16(z));
+    for (int64_t row = blockIdx.x; row < rows; row += gridDim.x) {
+      int n = (int)(row / C), c = (int)(row % C);
+      float s = v_load(v, vmode, n, c, C);
+      const float* xr = x + row * HW;
+      float* yr = y + row * HW;
+      const float* zr = (MODE == 2) ? z + row * HW : nullptr;
+      if (vec) {
+        int hw4 = HW >> 2;
+        for (int i = threadIdx.x; i < hw4; i += blockDim.x) {
+          float4 a = reinterpret_cast<const float4*>(xr)[i], r;
+          if (MODE == 0) { r.x = a.x + s; r.y = a.y + s; r.z = a.z + s; r.w = a.w + s; }
+          else if (MODE == 1) { r.x = a.x * s; r.y = a.y * s; r.z = a.z * s; r.w = a.w * s; }
+          else {
+            float4 q = reinterpret_cast<const float4*>(zr)[i];
+            r.x = fmaf(s, q.x, a.x); r.y = fmaf(s, q.y, a.y); r.z = fmaf(s, q.z, a.z); r.w = fmaf(s, q.w, a.w);
+          }
+          reinterpret_cast<float4*>(yr)[i] = r;
+        }
+      } else {
+        for (int i = threadIdx.x; i < HW; i += blockDim.x) {
+          float a = xr[i];
+          yr[i] = MODE == 0 ? a + s : (MODE == 1 ? a * s : fmaf(s, zr[i], a));
+        }
+      }
+    }
+  } else {
+    // small HW (BatchNorm1d-like, SE vectors): flat mapping
+    int64_t total = rows * HW;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+      int64_t row = i / HW;
+      int n = (int)(row / C), c = (int)(row % C);
+      float s = v_load(v, vmode, n, c, C);
+      float a = x[i];
+      y[i] = MODE == 0 ? a + s : (MODE == 1 ? a * s : fmaf(s, z[i], a));
+    }
+  }
+}
+
+// ------------------------------------------------------------------ reductions of x*(y or 1) over [N,C,HW]
+// rmode 0: one warp per (n,c) row.
+__global__ void __launch_bounds__(256) reduce_rows_kernel(const float* __restrict__ x, const float* __restrict__ y,
+                                                          float* __restrict__ out, int64_t rows, int HW, float scale) {
+  int warps_per_block = blockDim.x >> 5;
+  int lane = threadIdx.x & 31;
+  for (int64_t row = (int64_t)blockIdx.x * warps_per_block + (threadIdx.x >> 5); row < rows;
+       row += (int64_t)gridDim.x * warps_per_block) {
+    const float* xr = x + row * HW;
+    const float* yr = y ? y + row * HW : nullptr;
+    float acc = 0.f;
+    if (((HW & 3) == 0) && aligned16(x) && (!y || aligned16(y))) {
+      int hw4 = HW >> 2;
+      for (int i = lane; i < hw4; i += 32) {
+        float4 a = reinterpret_cast<const float4*>(xr)[i];
+        if (yr) {
+          float4 b = reinterpret_cast<const float4*>(yr)[i];
+          acc += a.x * b.x + a.y * b.y + a.z * b.z + a.w * b.w;
+        } else acc += a.x + a.y + a.z + a.w;
+      }
+    } else {
+      for (int i = lane; i < HW; i += 32) acc += yr ? xr[i] * yr[i] : xr[i];
+    }
+    acc = warp_sum(acc);
+    if (lane == 0) out[row] = acc * scale;
+  }
+}
+
+// rmode 1 ([C] over n,hw) / rmode 2 ([N] over c,hw) / rmode 3 (all): grid (groups, splits); atomics into zeroed out.
+// element (g, j): rmode1: g=c, j over (n,hw): idx = (n*C + c)*HW + hw ;  rmode2: g=n, contiguous C*HW ; rmode3: g=0 all.
+__global__ void __launch_bounds__(256) reduce_groups_kernel(const float* __restrict__ x, const float* __restrict__ y,
+                                                            float* __restrict__ out, int N, int C, int HW, int rmode,
+                                                            float scale) {
+  int g = blockIdx.x;
+  int split = blockIdx.y, nsplit = gridDim.y;
+  float acc = 0.f;
+  if (rmode == 1) {
+    // iterate over n in [split::nsplit], hw by threads
+    for (int n = split; n < N; n += nsplit) {
+      const float* xr = x + ((int64_t)n * C + g) * HW;
+      const float* yr = y ? y + ((int64_t)n * C + g) * HW : nullptr;
+      for (int i = threadIdx.x; i < HW; i += blockDim.x) acc += yr ? xr[i] * yr[i] : xr[i];
+    }
+  } else {
+    int64_t len = rmode == 2 ? (int64_t)C * HW : (int64_t)N * C * HW;
+    const float* xr = x + (rmode == 2 ? (int64_t)g * len : 0);
+    const float* yr = y ? y + (rmode == 2 ? (int64_t)g * len : 0) : nullptr;
+    int64_t chunk = (len + nsplit - 1) / nsplit;
+    int64_t lo = (int64_t)split * chunk, hi = lo + chunk < len ? lo + chunk : len;
+    for (int64_t i = lo + threadIdx.x; i < hi; i += blockDim.x) acc += yr ? xr[i] * yr[i] : xr[i];
+  }
+  float t = block_sum<256>(acc);
+  if (threadIdx.x == 0) atomicAdd(out + g, t * scale);
+}
+
+}  // namespace ganb200
+
+using namespace ganb200;
+
+extern "C" int ganb200_abi_version(void) { return 1; }
+extern "C" const char* ganb200_last_error(void) { return g_last_error; }
+
+extern "C" int ganb200_device_check(int device) {
+  cudaDeviceProp prop;
+  GB_CHECK_CUDA(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10) return fail(GANB200_UNSUPPORTED_ARCH, "device is sm_%lld%s, libganb200 needs sm_100", "", prop.major * 10 + prop.minor);
+  return 0;
+}
+
+#define UNARY_CASE(OP) \
+  case OP: ew_unary_kernel<OP><<<grid, 256, 0, s>>>(x, y, n, p0, p1, vec); break;
+
+extern "C" int ganb200_ew_unary(int op, const float* x, float* y, int64_t n, float p0, float p1, void* stream) {
+  if (n <= 0) return 0;
+  cudaStream_t s = (cudaStream_t)stream;
+  bool vec = (((uintptr_t)x | (uintptr_t)y) & 15) == 0;
+  int grid = ew_grid(n, 256, 8);
+  switch (op) {
+    UNARY_CASE(GANB200_U_SIGMOID) UNARY_CASE(GANB200_U_TANH) UNARY_CASE(GANB200_U_SQUARE)
+    UNARY_CASE(GANB200_U_AFFINE) UNARY_CASE(GANB200_U_RSQRT_EPS) UNARY_CASE(GANB200_U_SQRT)
+    UNARY_CASE(GANB200_U_LEAKY) UNARY_CASE(GANB200_U_RECIP) UNARY_CASE(GANB200_U_LEAKY_MASK)
+    UNARY_CASE(GANB200_U_COPY) UNARY_CASE(GANB200_U_POW)
+    default: return fail(GANB200_BAD_ARG, "ew_unary: unknown op%s %lld", "", op);
+  }
+  GB_CHECK_LAUNCH();
+  return 0;
+}
+
+#define BINARY_CASE(OP) \
+  case OP: ew_binary_kernel<OP><<<grid, 256, 0, s>>>(a, b, y, n, p0, vec); break;
+
+extern "C" int ganb200_ew_binary(int op, const float* a, const float* b, float* y, int64_t n, float p0, void* stream) {
+  if (n <= 0) return 0;
+  cudaStream_t s = (cudaStream_t)stream;
+  bool vec = (((uintptr_t)a | (uintptr_t)b | (uintptr_t)y) & 15) == 0;
+  int grid = ew_grid(n, 256, 8);
+  switch (op) {
+    BINARY_CASE(GANB200_B_ADD) BINARY_CASE(GANB200_B_SUB) BINARY_CASE(GANB200_B_MUL) BINARY_CASE(GANB200_B_DIV)
+    BINARY_CASE(GANB200_B_SIGMOID_BWD) BINARY_CASE(GANB200_B_TANH_BWD) BINARY_CASE(GANB200_B_LEAKY_BWD)
+    default: return fail(GANB200_BAD_ARG, "ew_binary: unknown op%s %lld", "", op);
+  }
+  GB_CHECK_LAUNCH();
+  return 0;
+}
+
+static int bcast_grid(int N, int C, int HW) {
+  int64_t rows = (int64_t)N * C;
+  if (HW >= 64) return (int)(rows < (int64_t)kNumSMs * 16 ? rows : (int64_t)kNumSMs * 16);
+  return ew_grid(rows * HW, 256, 4);
+}
+
+extern "C" int ganb200_ew_bcast(int op, const float* x, const float* v, float* y, int N, int C, int HW, int vmode,
+                                void* stream) {
+  if ((int64_t)N * C * HW <= 0) return 0;
+  cudaStream_t s = (cudaStream_t)stream;
+  int grid = bcast_grid(N, C, HW);
+  if (op == GANB200_B_ADD) ew_bcast_kernel<0><<<grid, 256, 0, s>>>(x, v, nullptr, y, N, C, HW, vmode);
+  else if (op == GANB200_B_MUL) ew_bcast_kernel<1><<<grid, 256, 0, s>>>(x, v, nullptr, y, N, C, HW, vmode);
+  else return fail(GANB200_BAD_ARG, "ew_bcast: op must be ADD or MUL%s", "");
+  GB_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int ganb200_ew_fma_bcast(const float* x, const float* v, const float* z, float* y, int N, int C, int HW,
+                                    int vmode, void* stream) {
+  if ((int64_t)N * C * HW <= 0) return 0;
+  cudaStream_t s = (cudaStream_t)stream;
+  ew_bcast_kernel<2><<<bcast_grid(N, C, HW), 256, 0, s>>>(x, v, z, y, N, C, HW, vmode);
+  GB_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int ganb200_reduce(const float* x, const float* y, float* out, int N, int C, int HW, int rmode, float scale,
+                              void* stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  GB_REQUIRE(N > 0 && C > 0 && HW > 0, GANB200_BAD_SHAPE, "reduce: empty shape");
+  if (rmode == 0) {
+    int64_t rows = (int64_t)N * C;
+    int grid = (int)((rows + 7) / 8);
+    if (grid > kNumSMs * 16) grid = kNumSMs * 16;
+    reduce_rows_kernel<<<grid, 256, 0, s>>>(x, y, out, rows, HW, scale);
+  } else if (rmode >= 1 && rmode <= 3) {
+    int groups = rmode == 1 ? C : (rmode == 2 ? N : 1);
+    int64_t per_group = (int64_t)N * C * HW / groups;
+    int max_split = rmode == 1 ? N : (int)((per_group + 2047) / 2048);
+    int want = (kNumSMs * 4 + groups - 1) / groups;
+    int nsplit = want < max_split ? want : max_split;
+    if (nsplit < 1) nsplit = 1;
+    GB_CHECK_CUDA(cudaMemsetAsync(out, 0, sizeof(float) * groups, s));
+    reduce_groups_kernel<<<dim3(groups, nsplit), 256, 0, s>>>(x, y, out, N, C, HW, rmode, scale);
+  } else {
+    return fail(GANB200_BAD_ARG, "reduce: bad rmode%s %lld", "", rmode);
+  }
+  GB_CHECK_LAUNCH();
+  return 0;
+}

@@ -1,0 +1,354 @@
+"""Tensor-level wrappers over the C-ABI (torch is used for device memory and the current stream only).
+
+`backend()` returns the object whose methods launch kernels.  The product backend is `CudaBackend`
+(libganb200.so); it refuses CPU tensors.  tests/ may install a different backend with `set_backend`
+(the CPU restatement in oracle/kernels_ref.py) to check the autograd formulas without a GPU — the
+product itself never imports oracle/.
+"""
+import ctypes
+import os
+
+import torch
+
+from . import _lib
+from ._lib import ConvDesc
+
+# enums from include/ganb200.h
+U_SIGMOID, U_TANH, U_SQUARE, U_AFFINE, U_RSQRT_EPS, U_SQRT, U_LEAKY, U_RECIP, U_LEAKY_MASK, U_COPY, U_POW = range(11)
+B_ADD, B_SUB, B_MUL, B_DIV, B_SIGMOID_BWD, B_TANH_BWD, B_LEAKY_BWD = range(7)
+V_NC, V_C, V_N, V_SCALAR = range(4)
+R_HW, R_NHW, R_CHW, R_ALL = range(4)
+FPROP, DGRAD, WGRAD = range(3)
+
+# engine: 0 auto (tcgen05 when eligible), 1 fp32 CUDA cores, 2 force tcgen05
+_ENGINE = {"auto": 0, "fp32": 1, "simt": 1, "bf16": 0, "tc": 2}
+
+
+def default_engine():
+    return _ENGINE[os.environ.get("GANB200_PRECISION", "auto")]
+
+
+LAUNCH_COUNT = [0]  # number of libganb200 kernel-launching calls (bench.py reports it as gpu_launches)
+
+
+def _nchw(t):
+    """logical [N, C, HW] of a >=1-D tensor."""
+    if t.dim() == 1:
+        return 1, t.shape[0], 1
+    n, c = t.shape[0], t.shape[1]
+    hw = 1
+    for s in t.shape[2:]:
+        hw *= s
+    return n, c, hw
+
+
+def out_hw(h, w, r, s, stride, pad):
+    return (h + 2 * pad - r) // stride + 1, (w + 2 * pad - s) // stride + 1
+
+
+class CudaBackend:
+    name = "cuda"
+
+    def __init__(self):
+        self.lib = _lib.load()
+        self._checked = set()
+        self._ws = {}
+
+    # -- plumbing -------------------------------------------------------------------------------
+    def _prep(self, *tensors):
+        dev = None
+        for t in tensors:
+            if t is None:
+                continue
+            if not t.is_cuda:
+                raise _lib.GanB200Error("gan_b200 kernels need CUDA tensors (there is no CPU fallback)")
+            if t.dtype != torch.float32 and t.dtype not in (torch.int32, torch.float64):
+                raise _lib.GanB200Error(f"gan_b200 kernels are float32, got {t.dtype}")
+            if not t.is_contiguous():
+                raise _lib.GanB200Error("gan_b200 kernels need contiguous tensors")
+            dev = t.device
+        idx = dev.index if dev.index is not None else torch.cuda.current_device()
+        if idx not in self._checked:
+            _lib.check(self.lib.ganb200_device_check(idx))
+            self._checked.add(idx)
+        LAUNCH_COUNT[0] += 1
+        return ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+
+    @staticmethod
+    def _p(t):
+        return ctypes.c_void_p(t.data_ptr()) if t is not None else None
+
+    def _workspace(self, nbytes, device):
+        if nbytes == 0:
+            return None
+        # a fresh tensor from the caching allocator: stream-ordered reuse is handled by torch
+        return torch.empty(nbytes, dtype=torch.uint8, device=device)
+
+    # -- convolution family ---------------------------------------------------------------------
+    def _desc(self, N, C, H, W, K, R, S, stride, pad, pad_mode, alpha, engine):
+        P, Q = out_hw(H, W, R, S, stride, pad)
+        return ConvDesc(N, C, H, W, K, R, S, stride, pad, pad_mode, P, Q, float(alpha),
+                        default_engine() if engine is None else engine)
+
+    def conv_fprop(self, x, w, bias, stride, pad, pad_mode, alpha, iscale=None, oscale=None, engine=None):
+        N, C, H, W = x.shape
+        K, C2, R, S = w.shape
+        assert C == C2, (x.shape, w.shape)
+        d = self._desc(N, C, H, W, K, R, S, stride, pad, pad_mode, alpha, engine)
+        st = self._prep(x, w, bias, iscale, oscale)
+        y = torch.empty((N, K, d.P, d.Q), dtype=torch.float32, device=x.device)
+        nb = self.lib.ganb200_conv2d_workspace_bytes(ctypes.byref(d), FPROP)
+        ws = self._workspace(nb, x.device)
+        _lib.check(self.lib.ganb200_conv2d_fprop(ctypes.byref(d), self._p(x), self._p(w), self._p(bias),
+                                                 self._p(iscale), self._p(oscale), self._p(y), self._p(ws), nb, st))
+        return y
+
+    def conv_dgrad(self, dy, w, in_hw, stride, pad, pad_mode, alpha, iscale=None, oscale=None, engine=None):
+        N, K, P, Q = dy.shape
+        K2, C, R, S = w.shape
+        assert K == K2, (dy.shape, w.shape)
+        H, W = in_hw
+        d = self._desc(N, C, H, W, K, R, S, stride, pad, pad_mode, alpha, engine)
+        assert (d.P, d.Q) == (P, Q), ((d.P, d.Q), (P, Q))
+        st = self._prep(dy, w, iscale, oscale)
+        dx = torch.empty((N, C, H, W), dtype=torch.float32, device=dy.device)
+        nb = self.lib.ganb200_conv2d_workspace_bytes(ctypes.byref(d), DGRAD)
+        ws = self._workspace(nb, dy.device)
+        _lib.check(self.lib.ganb200_conv2d_dgrad(ctypes.byref(d), self._p(dy), self._p(w), self._p(iscale),
+                                                 self._p(oscale), self._p(dx), self._p(ws), nb, st))
+        return dx
+
+    def conv_wgrad(self, x, dy, rs, stride, pad, pad_mode, alpha, iscale=None, oscale=None, engine=None):
+        N, C, H, W = x.shape
+        N2, K, P, Q = dy.shape
+        R, S = rs
+        d = self._desc(N, C, H, W, K, R, S, stride, pad, pad_mode, alpha, engine)
+        assert N == N2 and (d.P, d.Q) == (P, Q), (x.shape, dy.shape)
+        st = self._prep(x, dy, iscale, oscale)
+        dw = torch.empty((K, C, R, S), dtype=torch.float32, device=x.device)
+        nb = self.lib.ganb200_conv2d_workspace_bytes(ctypes.byref(d), WGRAD)
+        ws = self._workspace(nb, x.device)
+        _lib.check(self.lib.ganb200_conv2d_wgrad(ctypes.byref(d), self._p(x), self._p(dy), self._p(iscale),
+                                                 self._p(oscale), self._p(dw), self._p(ws), nb, st))
+        return dw
+
+    # -- resampling -----------------------------------------------------------------------------
+    def resample2d(self, x, op_h, op_w):
+        *lead, Hi, Wi = x.shape
+        assert Hi == op_h.n_in and Wi == op_w.n_in, (x.shape, op_h.name, op_w.name)
+        st = self._prep(x)
+        nc = 1
+        for s in lead:
+            nc *= s
+        y = torch.empty((*lead, op_h.n_out, op_w.n_out), dtype=torch.float32, device=x.device)
+        ih, wh, th = op_h.taps(x.device)
+        iw, ww, tw = op_w.taps(x.device)
+        _lib.check(self.lib.ganb200_resample2d(self._p(x), self._p(y), nc, Hi, Wi, op_h.n_out, op_w.n_out,
+                                               self._p(ih), self._p(wh), th, self._p(iw), self._p(ww), tw, st))
+        return y
+
+    # -- pointwise ------------------------------------------------------------------------------
+    def ew_unary(self, op, x, p0=0.0, p1=0.0):
+        st = self._prep(x)
+        y = torch.empty_like(x)
+        _lib.check(self.lib.ganb200_ew_unary(op, self._p(x), self._p(y), x.numel(), p0, p1, st))
+        return y
+
+    def ew_binary(self, op, a, b, p0=0.0):
+        assert a.shape == b.shape, (a.shape, b.shape)
+        st = self._prep(a, b)
+        y = torch.empty_like(a)
+        _lib.check(self.lib.ganb200_ew_binary(op, self._p(a), self._p(b), self._p(y), a.numel(), p0, st))
+        return y
+
+    def ew_bcast(self, op, x, v, vmode):
+        N, C, HW = _nchw(x)
+        st = self._prep(x, v)
+        y = torch.empty_like(x)
+        _lib.check(self.lib.ganb200_ew_bcast(op, self._p(x), self._p(v), self._p(y), N, C, HW, vmode, st))
+        return y
+
+    def ew_fma_bcast(self, x, v, z, vmode):
+        N, C, HW = _nchw(x)
+        st = self._prep(x, v, z)
+        y = torch.empty_like(x)
+        _lib.check(self.lib.ganb200_ew_fma_bcast(self._p(x), self._p(v), self._p(z), self._p(y), N, C, HW, vmode, st))
+        return y
+
+    def reduce(self, x, y, rmode, scale=1.0):
+        N, C, HW = _nchw(x)
+        st = self._prep(x, y)
+        shape = {R_HW: (N, C), R_NHW: (C,), R_CHW: (N,), R_ALL: (1,)}[rmode]
+        out = torch.empty(shape, dtype=torch.float32, device=x.device)
+        _lib.check(self.lib.ganb200_reduce(self._p(x), self._p(y), self._p(out), N, C, HW, rmode, scale, st))
+        return out
+
+    # -- PReLU ----------------------------------------------------------------------------------
+    def prelu_fwd(self, x, a):
+        N, C, HW = _nchw(x)
+        st = self._prep(x, a)
+        y = torch.empty_like(x)
+        _lib.check(self.lib.ganb200_prelu_fwd(self._p(x), self._p(a), self._p(y), N, C, HW, a.numel(), st))
+        return y
+
+    def maskscale(self, g, x, a):
+        N, C, HW = _nchw(x)
+        st = self._prep(g, x, a)
+        y = torch.empty_like(x)
+        _lib.check(self.lib.ganb200_maskscale(self._p(g), self._p(x), self._p(a), self._p(y), N, C, HW, a.numel(), st))
+        return y
+
+    def prelu_bwd(self, gy, x, a, need_gx=True, need_ga=True):
+        N, C, HW = _nchw(x)
+        st = self._prep(gy, x, a)
+        gx = torch.empty_like(x) if need_gx else None
+        ga = torch.empty_like(a) if need_ga else None
+        _lib.check(self.lib.ganb200_prelu_bwd(self._p(gy), self._p(x), self._p(a), self._p(gx), self._p(ga), N, C, HW,
+                                              a.numel(), st))
+        return gx, ga
+
+    def masked_dot(self, u, v, x, a_n):
+        N, C, HW = _nchw(x)
+        st = self._prep(u, v, x)
+        out = torch.empty((a_n,), dtype=torch.float32, device=x.device)
+        _lib.check(self.lib.ganb200_masked_dot(self._p(u), self._p(v), self._p(x), self._p(out), N, C, HW, a_n, st))
+        return out
+
+    # -- BatchNorm ------------------------------------------------------------------------------
+    def bn_stats(self, x):
+        N, C, HW = _nchw(x)
+        st = self._prep(x)
+        mean = torch.empty((C,), dtype=torch.float32, device=x.device)
+        var = torch.empty((C,), dtype=torch.float32, device=x.device)
+        _lib.check(self.lib.ganb200_bn_stats(self._p(x), self._p(mean), self._p(var), N, C, HW, st))
+        return mean, var
+
+    def bn_apply(self, x, mean, var, gamma, beta, running_mean, running_var, eps, momentum, count_total):
+        N, C, HW = _nchw(x)
+        st = self._prep(x, mean, var, gamma, beta, running_mean, running_var)
+        y = torch.empty_like(x)
+        invstd = torch.empty((C,), dtype=torch.float32, device=x.device)
+        _lib.check(self.lib.ganb200_bn_apply(self._p(x), self._p(mean), self._p(var), self._p(gamma), self._p(beta),
+                                             self._p(y), self._p(invstd), self._p(running_mean),
+                                             self._p(running_var), N, C, HW, eps, momentum, count_total, st))
+        return y, invstd
+
+    def bn_bwd_reduce(self, gy, x, mean, invstd):
+        N, C, HW = _nchw(x)
+        st = self._prep(gy, x, mean, invstd)
+        s1 = torch.empty((C,), dtype=torch.float32, device=x.device)
+        s2 = torch.empty((C,), dtype=torch.float32, device=x.device)
+        _lib.check(self.lib.ganb200_bn_bwd_reduce(self._p(gy), self._p(x), self._p(mean), self._p(invstd),
+                                                  self._p(s1), self._p(s2), N, C, HW, st))
+        return s1, s2
+
+    def bn_bwd_apply(self, gy, x, mean, invstd, gamma, sum_gy, sum_gy_xhat, count_total):
+        N, C, HW = _nchw(x)
+        st = self._prep(gy, x, mean, invstd, gamma, sum_gy, sum_gy_xhat)
+        gx = torch.empty_like(x)
+        gg = torch.empty((C,), dtype=torch.float32, device=x.device)
+        gb = torch.empty((C,), dtype=torch.float32, device=x.device)
+        _lib.check(self.lib.ganb200_bn_bwd_apply(self._p(gy), self._p(x), self._p(mean), self._p(invstd),
+                                                 self._p(gamma), self._p(sum_gy), self._p(sum_gy_xhat), self._p(gx),
+                                                 self._p(gg), self._p(gb), N, C, HW, count_total, st))
+        return gx, gg, gb
+
+    # -- softmax over branches, minibatch stddev, BCE ---------------------------------------------
+    def softmax_m_fwd(self, x):
+        B, M, C = x.shape
+        st = self._prep(x)
+        y = torch.empty_like(x)
+        _lib.check(self.lib.ganb200_softmax_m_fwd(self._p(x), self._p(y), B, M, C, st))
+        return y
+
+    def softmax_m_bwd(self, gy, y):
+        B, M, C = y.shape
+        st = self._prep(gy, y)
+        gx = torch.empty_like(y)
+        _lib.check(self.lib.ganb200_softmax_m_bwd(self._p(gy), self._p(y), self._p(gx), B, M, C, st))
+        return gx
+
+    def mbstd_fwd(self, x, G, eps):
+        st = self._prep(x)
+        out = torch.empty((1,), dtype=torch.float32, device=x.device)
+        _lib.check(self.lib.ganb200_mbstd_fwd(self._p(x), self._p(out), G, x.numel() // G, eps, st))
+        return out
+
+    def mbstd_bwd(self, g, x, G, eps):
+        st = self._prep(g, x)
+        gx = torch.empty_like(x)
+        _lib.check(self.lib.ganb200_mbstd_bwd(self._p(g), self._p(x), self._p(gx), G, x.numel() // G, eps, st))
+        return gx
+
+    def mbstd_bwd_bwd(self, g, x, ggx, G, eps):
+        st = self._prep(g, x, ggx)
+        out_gg = torch.empty((1,), dtype=torch.float32, device=x.device)
+        out_gx = torch.empty_like(x)
+        _lib.check(self.lib.ganb200_mbstd_bwd_bwd(self._p(g), self._p(x), self._p(ggx), self._p(out_gg),
+                                                  self._p(out_gx), G, x.numel() // G, eps, st))
+        return out_gg, out_gx
+
+    def bce_fwd(self, p, t):
+        st = self._prep(p, t)
+        out = torch.empty((1,), dtype=torch.float32, device=p.device)
+        flag = torch.empty((1,), dtype=torch.int32, device=p.device)
+        _lib.check(self.lib.ganb200_bce_fwd(self._p(p), self._p(t), self._p(out), self._p(flag), p.numel(), st))
+        return out, flag
+
+    def bce_bwd(self, g, p, t):
+        st = self._prep(g, p, t)
+        gp = torch.empty_like(p)
+        _lib.check(self.lib.ganb200_bce_bwd(self._p(g), self._p(p), self._p(t), self._p(gp), p.numel(), st))
+        return gp
+
+    # -- optimiser / misc -------------------------------------------------------------------------
+    def adam_blocks(self, tab, block_tab, n_blocks, chunk, lr, b1, b2, eps, wd, decoupled, step, grad_scale):
+        st = self._prep(tab, block_tab) if False else ctypes.c_void_p(
+            torch.cuda.current_stream(tab.device).cuda_stream)
+        LAUNCH_COUNT[0] += 1
+        _lib.check(self.lib.ganb200_multi_tensor_adam_blocks(self._p(tab), self._p(block_tab), n_blocks, chunk, lr,
+                                                             b1, b2, eps, wd, int(decoupled), step, grad_scale, st))
+
+    def mixup(self, t, f, lam):
+        st = self._prep(t, f)
+        out = torch.empty_like(t)
+        _lib.check(self.lib.ganb200_mixup(self._p(t), self._p(f), float(lam), self._p(out), t.numel(), st))
+        return out
+
+    def mixup_wgan_f64(self, label, t, f):
+        B, C, H, W = t.shape
+        st = self._prep(label, t, f)
+        out = torch.empty(t.shape, dtype=torch.float64, device=t.device)
+        _lib.check(self.lib.ganb200_mixup_wgan_f64(self._p(label), self._p(t), self._p(f), self._p(out), B, C, H, W, st))
+        return out
+
+    def clamp_(self, x, lo, hi):
+        st = self._prep(x)
+        _lib.check(self.lib.ganb200_clamp_(self._p(x), x.numel(), lo, hi, st))
+        return x
+
+    def spectral_power_iter(self, w2d, u, v, n_iter, eps):
+        rows, cols = w2d.shape
+        st = self._prep(w2d, u, v)
+        sigma = torch.empty((1,), dtype=torch.float32, device=w2d.device)
+        _lib.check(self.lib.ganb200_spectral_power_iter(self._p(w2d), self._p(u), self._p(v), self._p(sigma), rows,
+                                                        cols, n_iter, eps, st))
+        return sigma
+
+
+_backend = None
+
+
+def backend():
+    global _backend
+    if _backend is None:
+        _backend = CudaBackend()
+    return _backend
+
+
+def set_backend(b):
+    """tests only: install another kernel backend (returns the previous one)."""
+    global _backend
+    prev = _backend
+    _backend = b
+    return prev

@@ -1,0 +1,682 @@
+"""Autograd formulas over the libganb200 kernels.
+
+Every op is a torch.autograd.Function whose forward launches kernels through gan_b200.kernels and whose
+backward is written with other Functions of this file, so that `torch.autograd.grad(..., create_graph=True)`
+(compute_grad2, train/ganR2.py:30-39 in the reference) records a graph made of our kernels only: the
+R1/R2/WGAN-GP double backward through D runs on explicit dgrad-of-dgrad / wgrad-of-dgrad / mask-scale /
+gate-product kernels, not on ATen's generic double-backward graph.
+
+Ops only needed by the generator (BatchNorm, softmax over branches, modulated conv, noise) are
+once-differentiable: the reference never differentiates G twice.
+"""
+from collections import namedtuple
+
+import torch
+from torch.autograd import Function
+from torch.autograd.function import once_differentiable
+
+from . import kernels as KN
+from . import resample as RS
+
+ConvCfg = namedtuple("ConvCfg", "stride pad pad_mode alpha engine")
+
+
+def K():
+    return KN.backend()
+
+
+def _c(t):
+    return t if (t is None or t.is_contiguous()) else t.contiguous()
+
+
+_RMODE_OF_VMODE = {KN.V_NC: KN.R_HW, KN.V_C: KN.R_NHW, KN.V_N: KN.R_CHW, KN.V_SCALAR: KN.R_ALL}
+_VMODE_OF_RMODE = {v: k for k, v in _RMODE_OF_VMODE.items()}
+
+
+# =====================================================================================================
+# convolution family: closed under differentiation
+# =====================================================================================================
+class Conv2dFn(Function):
+    @staticmethod
+    def forward(ctx, x, w, bias, cfg):
+        x, w, bias = _c(x), _c(w), _c(bias)
+        ctx.save_for_backward(x, w)
+        ctx.cfg = cfg
+        ctx.has_bias = bias is not None
+        return K().conv_fprop(x, w, bias, cfg.stride, cfg.pad, cfg.pad_mode, cfg.alpha, engine=cfg.engine)
+
+    @staticmethod
+    def backward(ctx, gy):
+        x, w = ctx.saved_tensors
+        cfg = ctx.cfg
+        gy = _c(gy)
+        gx = ConvDgradFn.apply(gy, w, cfg, tuple(x.shape[2:])) if ctx.needs_input_grad[0] else None
+        gw = ConvWgradFn.apply(x, gy, cfg, tuple(w.shape[2:])) if ctx.needs_input_grad[1] else None
+        gb = ReduceFn.apply(gy, None, KN.R_NHW, 1.0) if (ctx.has_bias and ctx.needs_input_grad[2]) else None
+        return gx, gw, gb, None
+
+
+class ConvDgradFn(Function):
+    """dx of a conv given dy; also the forward of ConvTranspose2d."""
+
+    @staticmethod
+    def forward(ctx, dy, w, cfg, in_hw):
+        dy, w = _c(dy), _c(w)
+        ctx.save_for_backward(dy, w)
+        ctx.cfg = cfg
+        return K().conv_dgrad(dy, w, in_hw, cfg.stride, cfg.pad, cfg.pad_mode, cfg.alpha, engine=cfg.engine)
+
+    @staticmethod
+    def backward(ctx, g):
+        dy, w = ctx.saved_tensors
+        cfg = ctx.cfg
+        g = _c(g)
+        g_dy = Conv2dFn.apply(g, w, None, cfg) if ctx.needs_input_grad[0] else None
+        g_w = ConvWgradFn.apply(g, dy, cfg, tuple(w.shape[2:])) if ctx.needs_input_grad[1] else None
+        return g_dy, g_w, None, None
+
+
+class ConvWgradFn(Function):
+    @staticmethod
+    def forward(ctx, x, dy, cfg, rs):
+        x, dy = _c(x), _c(dy)
+        ctx.save_for_backward(x, dy)
+        ctx.cfg = cfg
+        return K().conv_wgrad(x, dy, rs, cfg.stride, cfg.pad, cfg.pad_mode, cfg.alpha, engine=cfg.engine)
+
+    @staticmethod
+    def backward(ctx, gw):
+        x, dy = ctx.saved_tensors
+        cfg = ctx.cfg
+        gw = _c(gw)
+        g_x = ConvDgradFn.apply(dy, gw, cfg, tuple(x.shape[2:])) if ctx.needs_input_grad[0] else None
+        g_dy = Conv2dFn.apply(x, gw, None, cfg) if ctx.needs_input_grad[1] else None
+        return g_x, g_dy, None, None
+
+
+def conv2d(x, w, bias=None, stride=1, pad=0, pad_mode=0, alpha=1.0, engine=None):
+    return Conv2dFn.apply(x, w, bias, ConvCfg(stride, pad, pad_mode, float(alpha), engine))
+
+
+def linear(x, w, bias=None, alpha=1.0, engine=None):
+    """x:(B,in) w:(out,in) — a 1x1 conv on a 1x1 map."""
+    B = x.shape[0]
+    y = Conv2dFn.apply(x.reshape(B, -1, 1, 1), w.reshape(w.shape[0], w.shape[1], 1, 1), bias,
+                       ConvCfg(1, 0, 0, float(alpha), engine))
+    return y.reshape(B, w.shape[0])
+
+
+def conv_transpose2d(x, wt, bias=None, stride=1, pad=0, engine=None):
+    """nn.ConvTranspose2d semantics, wt:(Cin,Cout,R,S) = the KCRS weight of the conv whose dgrad this is."""
+    R, S = wt.shape[2:]
+    Ho = (x.shape[2] - 1) * stride - 2 * pad + R
+    Wo = (x.shape[3] - 1) * stride - 2 * pad + S
+    y = ConvDgradFn.apply(x, wt, ConvCfg(stride, pad, 0, 1.0, engine), (Ho, Wo))
+    if bias is not None:
+        y = AddBcFn.apply(y, bias, KN.V_C)
+    return y
+
+
+# =====================================================================================================
+# reductions / broadcasts
+# =====================================================================================================
+class ReduceFn(Function):
+    """sum of x*(y or 1) over HW / N,HW / C,HW / all (see ganb200_reduce)."""
+
+    @staticmethod
+    def forward(ctx, x, y, rmode, scale):
+        x, y = _c(x), _c(y)
+        ctx.save_for_backward(x, y)
+        ctx.rmode, ctx.scale = rmode, scale
+        return K().reduce(x, y, rmode, scale)
+
+    @staticmethod
+    def backward(ctx, g):
+        x, y = ctx.saved_tensors
+        vmode = _VMODE_OF_RMODE[ctx.rmode]
+        g = _c(g)
+        if ctx.scale != 1.0:
+            g = affine(g, ctx.scale, 0.0)
+        if y is None:
+            gx = AddBcFn.apply(torch.zeros_like(x), g, vmode) if ctx.needs_input_grad[0] else None
+            return gx, None, None, None
+        gx = MulBcFn.apply(y, g, vmode) if ctx.needs_input_grad[0] else None
+        gy = MulBcFn.apply(x, g, vmode) if ctx.needs_input_grad[1] else None
+        return gx, gy, None, None
+
+
+class MulBcFn(Function):
+    """y = x * v, v broadcast over the logical [N,C,HW] view of x."""
+
+    @staticmethod
+    def forward(ctx, x, v, vmode):
+        x, v = _c(x), _c(v)
+        ctx.save_for_backward(x, v)
+        ctx.vmode = vmode
+        return K().ew_bcast(KN.B_MUL, x, v, vmode)
+
+    @staticmethod
+    def backward(ctx, g):
+        x, v = ctx.saved_tensors
+        g = _c(g)
+        gx = MulBcFn.apply(g, v, ctx.vmode) if ctx.needs_input_grad[0] else None
+        gv = None
+        if ctx.needs_input_grad[1]:
+            gv = ReduceFn.apply(g, x, _RMODE_OF_VMODE[ctx.vmode], 1.0).reshape(v.shape)
+        return gx, gv, None
+
+
+class AddBcFn(Function):
+    @staticmethod
+    def forward(ctx, x, v, vmode):
+        x, v = _c(x), _c(v)
+        ctx.vmode = vmode
+        ctx.vshape = v.shape
+        return K().ew_bcast(KN.B_ADD, x, v, vmode)
+
+    @staticmethod
+    def backward(ctx, g):
+        gv = None
+        if ctx.needs_input_grad[1]:
+            gv = ReduceFn.apply(_c(g), None, _RMODE_OF_VMODE[ctx.vmode], 1.0).reshape(ctx.vshape)
+        return g, gv, None
+
+
+class FmaBcFn(Function):
+    """y = x + v*z (noise injection, generators/generator_13_5.py:265): z is a constant."""
+
+    @staticmethod
+    def forward(ctx, x, v, z, vmode):
+        x, v, z = _c(x), _c(v), _c(z)
+        ctx.save_for_backward(z)
+        ctx.vmode, ctx.vshape = vmode, v.shape
+        return K().ew_fma_bcast(x, v, z, vmode)
+
+    @staticmethod
+    def backward(ctx, g):
+        (z,) = ctx.saved_tensors
+        gv = None
+        if ctx.needs_input_grad[1]:
+            gv = ReduceFn.apply(_c(g), z, _RMODE_OF_VMODE[ctx.vmode], 1.0).reshape(ctx.vshape)
+        return g, gv, None, None
+
+
+# =====================================================================================================
+# elementwise
+# =====================================================================================================
+class AddFn(Function):
+    @staticmethod
+    def forward(ctx, a, b):
+        return K().ew_binary(KN.B_ADD, _c(a), _c(b))
+
+    @staticmethod
+    def backward(ctx, g):
+        return g, g
+
+
+class SubFn(Function):
+    @staticmethod
+    def forward(ctx, a, b):
+        return K().ew_binary(KN.B_SUB, _c(a), _c(b))
+
+    @staticmethod
+    def backward(ctx, g):
+        return g, (affine(g, -1.0, 0.0) if ctx.needs_input_grad[1] else None)
+
+
+class MulFn(Function):
+    @staticmethod
+    def forward(ctx, a, b):
+        a, b = _c(a), _c(b)
+        ctx.save_for_backward(a, b)
+        return K().ew_binary(KN.B_MUL, a, b)
+
+    @staticmethod
+    def backward(ctx, g):
+        a, b = ctx.saved_tensors
+        g = _c(g)
+        return (MulFn.apply(g, b) if ctx.needs_input_grad[0] else None,
+                MulFn.apply(g, a) if ctx.needs_input_grad[1] else None)
+
+
+class BinaryFn(Function):
+    """a (op) b for DIV and the activation-backward forms (see ganb200_ew_binary)."""
+
+    @staticmethod
+    def forward(ctx, a, b, op, p0):
+        a, b = _c(a), _c(b)
+        ctx.op, ctx.p0 = op, p0
+        out = K().ew_binary(op, a, b, p0)
+        ctx.save_for_backward(a, b, out)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        a, b, out = ctx.saved_tensors
+        op, p0 = ctx.op, ctx.p0
+        g = _c(g)
+        ga = gb = None
+        if op == KN.B_DIV:
+            if ctx.needs_input_grad[0]:
+                ga = BinaryFn.apply(g, b, KN.B_DIV, 0.0)
+            if ctx.needs_input_grad[1]:
+                gb = affine(MulFn.apply(BinaryFn.apply(g, b, KN.B_DIV, 0.0), out), -1.0, 0.0)
+        elif op == KN.B_SIGMOID_BWD:  # out = a*b*(1-b)
+            if ctx.needs_input_grad[0]:
+                ga = BinaryFn.apply(g, b, op, 0.0)
+            if ctx.needs_input_grad[1]:
+                gb = MulFn.apply(MulFn.apply(g, a), affine(b, -2.0, 1.0))
+        elif op == KN.B_TANH_BWD:  # out = a*(1-b^2)
+            if ctx.needs_input_grad[0]:
+                ga = BinaryFn.apply(g, b, op, 0.0)
+            if ctx.needs_input_grad[1]:
+                gb = MulFn.apply(MulFn.apply(g, a), affine(b, -2.0, 0.0))
+        elif op == KN.B_LEAKY_BWD:  # out = a * slope(b)
+            if ctx.needs_input_grad[0]:
+                ga = BinaryFn.apply(g, b, op, p0)
+        else:
+            raise NotImplementedError(op)
+        return ga, gb, None, None
+
+
+class UnaryFn(Function):
+    @staticmethod
+    def forward(ctx, x, op, p0, p1):
+        x = _c(x)
+        y = K().ew_unary(op, x, p0, p1)
+        ctx.op, ctx.p0, ctx.p1 = op, p0, p1
+        ctx.save_for_backward(x, y)
+        return y
+
+    @staticmethod
+    def backward(ctx, g):
+        x, y = ctx.saved_tensors
+        op, p0 = ctx.op, ctx.p0
+        g = _c(g)
+        if op == KN.U_SIGMOID:
+            gx = BinaryFn.apply(g, y, KN.B_SIGMOID_BWD, 0.0)
+        elif op == KN.U_TANH:
+            gx = BinaryFn.apply(g, y, KN.B_TANH_BWD, 0.0)
+        elif op == KN.U_SQUARE:
+            gx = MulFn.apply(g, affine(x, 2.0, 0.0))
+        elif op == KN.U_AFFINE:
+            gx = affine(g, p0, 0.0)
+        elif op == KN.U_COPY:
+            gx = g
+        elif op == KN.U_SQRT:
+            gx = affine(BinaryFn.apply(g, y, KN.B_DIV, 0.0), 0.5, 0.0)
+        elif op == KN.U_RSQRT_EPS:
+            gx = MulFn.apply(g, affine(MulFn.apply(MulFn.apply(y, y), y), -0.5, 0.0))
+        elif op == KN.U_LEAKY:
+            gx = BinaryFn.apply(g, x, KN.B_LEAKY_BWD, p0)
+        elif op == KN.U_RECIP:
+            gx = affine(MulFn.apply(g, MulFn.apply(y, y)), -1.0, 0.0)
+        elif op == KN.U_POW:
+            gx = MulFn.apply(g, affine(UnaryFn.apply(x, KN.U_POW, p0 - 1.0, 0.0), p0, 0.0))
+        else:
+            raise NotImplementedError(op)
+        return gx, None, None, None
+
+
+def affine(x, p0, p1):
+    return UnaryFn.apply(x, KN.U_AFFINE, float(p0), float(p1))
+
+
+def add(a, b):
+    return AddFn.apply(a, b)
+
+
+def sub(a, b):
+    return SubFn.apply(a, b)
+
+
+def mul(a, b):
+    return MulFn.apply(a, b)
+
+
+def sigmoid(x):
+    return UnaryFn.apply(x, KN.U_SIGMOID, 0.0, 0.0)
+
+
+def tanh(x):
+    return UnaryFn.apply(x, KN.U_TANH, 0.0, 0.0)
+
+
+def leaky_relu(x, slope):
+    return UnaryFn.apply(x, KN.U_LEAKY, float(slope), 0.0)
+
+
+def square(x):
+    return UnaryFn.apply(x, KN.U_SQUARE, 0.0, 0.0)
+
+
+def sqrt(x):
+    return UnaryFn.apply(x, KN.U_SQRT, 0.0, 0.0)
+
+
+def rsqrt_eps(x, eps):
+    return UnaryFn.apply(x, KN.U_RSQRT_EPS, float(eps), 0.0)
+
+
+def mul_bc(x, v, vmode=KN.V_NC):
+    """x:(N,C,...) times v:(N,C) [V_NC], (C,) [V_C], (N,) [V_N] or (1,) [V_SCALAR]."""
+    return MulBcFn.apply(x, v, vmode)
+
+
+def add_bc(x, v, vmode=KN.V_C):
+    return AddBcFn.apply(x, v, vmode)
+
+
+def noise_add(x, scale_c, z):
+    return FmaBcFn.apply(x, scale_c, z, KN.V_C)
+
+
+def global_avg_pool(x):
+    """AdaptiveAvgPool2d(1) + view(b,c): (N,C,H,W) -> (N,C)."""
+    hw = x.shape[2] * x.shape[3]
+    return ReduceFn.apply(x, None, KN.R_HW, 1.0 / hw)
+
+
+def mean(x):
+    """torch.mean over all elements -> 0-dim."""
+    return ReduceFn.apply(x, None, KN.R_ALL, 1.0 / x.numel()).reshape(())
+
+
+def sum_all(x):
+    return ReduceFn.apply(x, None, KN.R_ALL, 1.0).reshape(())
+
+
+def sumsq_per_sample(g):
+    """grad.pow(2).view(B,-1).sum(1) of compute_grad2 (train/ganR2.py:36-38)."""
+    return ReduceFn.apply(g, g, KN.R_CHW, 1.0)
+
+
+# =====================================================================================================
+# PReLU
+# =====================================================================================================
+class PReluFn(Function):
+    @staticmethod
+    def forward(ctx, x, a):
+        x, a = _c(x), _c(a)
+        ctx.save_for_backward(x, a)
+        return K().prelu_fwd(x, a)
+
+    @staticmethod
+    def backward(ctx, gy):
+        x, a = ctx.saved_tensors
+        gy = _c(gy)
+        if not torch.is_grad_enabled():  # plain first-order backward: one fused pass
+            gx, ga = K().prelu_bwd(gy, x, a, ctx.needs_input_grad[0], ctx.needs_input_grad[1])
+            return gx, ga
+        gx = MaskScaleFn.apply(gy, x, a) if ctx.needs_input_grad[0] else None
+        ga = None
+        if ctx.needs_input_grad[1]:
+            _, ga = K().prelu_bwd(gy.detach(), x, a, False, True)  # d(ga) is third order: never needed
+        return gx, ga
+
+
+class MaskScaleFn(Function):
+    """g * (x>0 ? 1 : a): the PReLU input-gradient; linear in g, piecewise constant in x."""
+
+    @staticmethod
+    def forward(ctx, g, x, a):
+        g, x, a = _c(g), _c(x), _c(a)
+        ctx.save_for_backward(g, x, a)
+        return K().maskscale(g, x, a)
+
+    @staticmethod
+    def backward(ctx, G):
+        g, x, a = ctx.saved_tensors
+        G = _c(G)
+        gg = MaskScaleFn.apply(G, x, a) if ctx.needs_input_grad[0] else None
+        ga = K().masked_dot(G.detach(), g.detach(), x, a.numel()).reshape(a.shape) if ctx.needs_input_grad[2] else None
+        return gg, None, ga
+
+
+def prelu(x, a):
+    return PReluFn.apply(x, a)
+
+
+# =====================================================================================================
+# separable resampling (Smooth / bicubic / adaptive average pool / pads): linear, adjoint = transposed op
+# =====================================================================================================
+class Resample2dFn(Function):
+    @staticmethod
+    def forward(ctx, x, op_h, op_w):
+        ctx.op_h, ctx.op_w = op_h, op_w
+        return K().resample2d(_c(x), op_h, op_w)
+
+    @staticmethod
+    def backward(ctx, g):
+        return Resample2dFn.apply(_c(g), ctx.op_h.T, ctx.op_w.T), None, None
+
+
+def smooth(x):
+    return Resample2dFn.apply(x, RS.smooth3(x.shape[-2]), RS.smooth3(x.shape[-1]))
+
+
+def smooth_bicubic_down2(x):
+    return Resample2dFn.apply(x, RS.smooth_then_bicubic_down2(x.shape[-2]), RS.smooth_then_bicubic_down2(x.shape[-1]))
+
+
+def bicubic_up2_smooth(x):
+    return Resample2dFn.apply(x, RS.bicubic_up2_then_smooth(x.shape[-2]), RS.bicubic_up2_then_smooth(x.shape[-1]))
+
+
+def bicubic_resize(x, out_h, out_w, scale=None):
+    return Resample2dFn.apply(x, RS.bicubic(x.shape[-2], out_h, scale), RS.bicubic(x.shape[-1], out_w, scale))
+
+
+def adaptive_avg_pool(x, out):
+    return Resample2dFn.apply(x, RS.adaptive_avg(x.shape[-2], out), RS.adaptive_avg(x.shape[-1], out))
+
+
+# =====================================================================================================
+# MiniBatchStdDev (discriminators/discriminator_9_4.py:42-54)
+# =====================================================================================================
+class MbStdFn(Function):
+    @staticmethod
+    def forward(ctx, x, G, eps):
+        x = _c(x)
+        ctx.save_for_backward(x)
+        ctx.G, ctx.eps = G, eps
+        return K().mbstd_fwd(x, G, eps)
+
+    @staticmethod
+    def backward(ctx, g):
+        (x,) = ctx.saved_tensors
+        return MbStdBwdFn.apply(_c(g), x, ctx.G, ctx.eps), None, None
+
+
+class MbStdBwdFn(Function):
+    @staticmethod
+    def forward(ctx, g, x, G, eps):
+        g, x = _c(g), _c(x)
+        ctx.save_for_backward(g, x)
+        ctx.G, ctx.eps = G, eps
+        return K().mbstd_bwd(g, x, G, eps)
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, ggx):
+        g, x = ctx.saved_tensors
+        out_gg, out_gx = K().mbstd_bwd_bwd(g, x, _c(ggx), ctx.G, ctx.eps)
+        return out_gg, out_gx, None, None
+
+
+def minibatch_stddev(x, group_size=4, eps=1e-8):
+    """returns cat([x, std.expand(b,1,h,w)], 1)"""
+    b, _, h, w = x.shape
+    s = MbStdFn.apply(x, group_size, eps)
+    plane = AddBcFn.apply(torch.zeros((b, 1, h, w), dtype=x.dtype, device=x.device), s, KN.V_SCALAR)
+    return torch.cat([x, plane], dim=1)
+
+
+# =====================================================================================================
+# losses
+# =====================================================================================================
+class BceFn(Function):
+    """torch.nn.BCELoss (mean).  Raises like the reference when an input is outside [0,1]."""
+    check_range = True
+
+    @staticmethod
+    def forward(ctx, p, t):
+        p, t = _c(p), _c(t)
+        out, flag = K().bce_fwd(p, t)
+        do_check = BceFn.check_range
+        if do_check and p.is_cuda and torch.cuda.is_current_stream_capturing():
+            do_check = False  # a D2H read cannot be captured; the eager warm-up iterations have checked
+        if do_check and int(flag.item()) != 0:
+            raise RuntimeError("all elements of input should be between 0 and 1")
+        ctx.save_for_backward(p, t)
+        return out.reshape(())
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, g):
+        p, t = ctx.saved_tensors
+        return K().bce_bwd(_c(g).reshape(1), p, t), None
+
+
+def bce_loss(p, t):
+    return BceFn.apply(p, t)
+
+
+# =====================================================================================================
+# generator-only ops (once differentiable)
+# =====================================================================================================
+_sync_bn_hooks = {"stats": None, "grads": None}  # installed by gan_b200.dist for data-parallel sync-BN
+
+
+class BatchNormTrainFn(Function):
+    """nn.BatchNorm1d/2d in training mode: batch statistics + running-stat update (momentum)."""
+
+    @staticmethod
+    def forward(ctx, x, gamma, beta, running_mean, running_var, eps, momentum):
+        x = _c(x)
+        N, C, HW = KN._nchw(x)
+        count = N * HW
+        mean, var = K().bn_stats(x)
+        if _sync_bn_hooks["stats"] is not None:
+            mean, var, count = _sync_bn_hooks["stats"](mean, var, count)
+        y, invstd = K().bn_apply(x, mean, var, gamma, beta, running_mean, running_var, eps, momentum, count)
+        ctx.save_for_backward(x, mean, invstd, gamma)
+        ctx.count = count
+        ctx.mark_non_differentiable(*[t for t in (running_mean, running_var) if t is not None])
+        return y
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, gy):
+        x, mean, invstd, gamma = ctx.saved_tensors
+        gy = _c(gy)
+        s1, s2 = K().bn_bwd_reduce(gy, x, mean, invstd)
+        if _sync_bn_hooks["grads"] is not None:
+            s1, s2 = _sync_bn_hooks["grads"](s1, s2)
+        gx, gg, gb = K().bn_bwd_apply(gy, x, mean, invstd, gamma, s1, s2, ctx.count)
+        return gx, (gg if gamma is not None else None), (gb if ctx.needs_input_grad[2] else None), None, None, None, None
+
+
+def batch_norm_train(x, gamma, beta, running_mean, running_var, eps, momentum):
+    return BatchNormTrainFn.apply(x, gamma, beta, running_mean, running_var, eps, momentum)
+
+
+def batch_norm_eval(x, gamma, beta, running_mean, running_var, eps):
+    scale = rsqrt_eps(running_var, eps)
+    if gamma is not None:
+        scale = mul(scale, gamma)
+    shift = affine(mul(running_mean, scale), -1.0, 0.0)
+    if beta is not None:
+        shift = add(shift, beta)
+    return add_bc(mul_bc(x, scale, KN.V_C), shift, KN.V_C)
+
+
+class SoftmaxMFn(Function):
+    """nn.Softmax(dim=1) on (B,M,C) attention vectors (generators/generator_13_5.py:87)."""
+
+    @staticmethod
+    def forward(ctx, x):
+        y = K().softmax_m_fwd(_c(x))
+        ctx.save_for_backward(y)
+        return y
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, gy):
+        (y,) = ctx.saved_tensors
+        return K().softmax_m_bwd(_c(gy), y)
+
+
+def softmax_m(x):
+    return SoftmaxMFn.apply(x)
+
+
+class ModConvFn(Function):
+    """Conv2dWeightModulate (generators/generator_13_5.py:234-248) in shared-weight form:
+
+        y[b,o] = sinv[b,o] * alpha * sum_{i,t} w[o,i,t] * s[b,i] * xpad[b,i,.+t]
+        sinv[b,o] = rsqrt( alpha^2 * sum_i s[b,i]^2 * sum_t w[o,i,t]^2 + eps )
+
+    algebraically identical to materialising per-sample weights and running conv2d(groups=b), but the weight
+    is shared across the batch (one implicit GEMM with M = B*H*W) and nothing of size B*Cout*Cin*k*k exists.
+    """
+
+    @staticmethod
+    def forward(ctx, x, w, s, pad, alpha, demodulate, eps, engine):
+        x, w, s = _c(x), _c(w), _c(s)
+        k = K()
+        Kout, C = w.shape[:2]
+        sinv = None
+        if demodulate:
+            wsq = k.reduce(w.reshape(Kout, C, -1), w.reshape(Kout, C, -1), KN.R_HW, 1.0)            # (K,C)
+            s2 = k.ew_unary(KN.U_SQUARE, s)                                                        # (B,C)
+            d = k.conv_fprop(s2.reshape(*s2.shape, 1, 1), wsq.reshape(Kout, C, 1, 1), None, 1, 0, 0, alpha * alpha,
+                             engine=1)                                                             # (B,K,1,1)
+            sinv = k.ew_unary(KN.U_RSQRT_EPS, d.reshape(d.shape[0], Kout), eps)
+            ctx.aux = (wsq, s2)
+        y = k.conv_fprop(x, w, None, 1, pad, 1, alpha, iscale=s, oscale=sinv, engine=engine)
+        ctx.save_for_backward(x, w, s, sinv, y)
+        ctx.cfg = (pad, alpha, demodulate, engine)
+        return y
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, gy):
+        x, w, s, sinv, y = ctx.saved_tensors
+        pad, alpha, demodulate, engine = ctx.cfg
+        k = K()
+        gy = _c(gy)
+        Kout, C = w.shape[:2]
+        rs = tuple(w.shape[2:])
+        need_x, need_w, need_s = ctx.needs_input_grad[:3]
+        gx = gw = gs = None
+        dxs = None
+        if need_x or need_s:
+            dxs = k.conv_dgrad(gy, w, tuple(x.shape[2:]), 1, pad, 1, alpha, iscale=None, oscale=sinv, engine=engine)
+            if need_x:
+                gx = k.ew_bcast(KN.B_MUL, dxs, s, KN.V_NC)
+            if need_s:
+                gs = k.reduce(dxs, x, KN.R_HW, 1.0)
+        if need_w:
+            gw = k.conv_wgrad(x, gy, rs, 1, pad, 1, alpha, iscale=s, oscale=sinv, engine=engine)
+        if demodulate and (need_w or need_s):
+            wsq, s2 = ctx.aux
+            # dL/dsinv = sum_hw gy*y0 = sum_hw gy*y / sinv ;  sinv = (d+eps)^-1/2 -> dL/dd = -0.5*sinv^3 * dL/dsinv
+            gsinv_times_sinv = k.reduce(gy, y, KN.R_HW, 1.0)                                        # (B,K)
+            dd = k.ew_binary(KN.B_MUL, gsinv_times_sinv, k.ew_unary(KN.U_SQUARE, sinv))             # * sinv^2
+            dd = k.ew_unary(KN.U_AFFINE, dd, -0.5, 0.0)
+            dd4 = dd.reshape(dd.shape[0], Kout, 1, 1)
+            if need_s:
+                ds2 = k.conv_dgrad(dd4, wsq.reshape(Kout, C, 1, 1), (1, 1), 1, 0, 0, alpha * alpha, engine=1)
+                ds2 = ds2.reshape(s.shape)
+                t = k.ew_binary(KN.B_MUL, ds2, s)
+                gs = k.ew_binary(KN.B_ADD, gs, k.ew_unary(KN.U_AFFINE, t, 2.0, 0.0))
+            if need_w:
+                dwsq = k.conv_wgrad(s2.reshape(*s2.shape, 1, 1), dd4, (1, 1), 1, 0, 0, alpha * alpha, engine=1)
+                v = k.ew_unary(KN.U_AFFINE, dwsq.reshape(Kout, C), 2.0, 0.0)
+                gw = k.ew_fma_bcast(gw.reshape(Kout, C, -1), v, w.reshape(Kout, C, -1), KN.V_NC).reshape(w.shape)
+        return gx, gw, gs, None, None, None, None, None
+
+
+def modulated_conv2d(x, w, s, pad, alpha, demodulate=True, eps=1e-8, engine=None):
+    return ModConvFn.apply(x, w, s, pad, float(alpha), demodulate, float(eps), engine)

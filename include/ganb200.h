@@ -1,0 +1,200 @@
+/*
+ * ganb200.h — C-ABI of libganb200.so: the B200 (sm_100a) kernels under the GAN training step.
+ *
+ * The reference (xxxxx23124/-GAN-) has no FFI of its own: every FLOP of its hot path is an ATen call
+ * made from Python.  The entry points below are what a binding for that path binds
+ * instead of ATen; each one cites the reference call site(s) it replaces (file:line under
+ * /root/reference).  INTEGRATION.md shows the ctypes stub a maintainer adds on the reference side.
+ *
+ * Conventions
+ *  - extern "C", plain pointers and sizes.  No torch types.  All tensors are DEVICE pointers to
+ *    contiguous float32 unless stated; layouts are the reference's (NCHW activations, KCRS weights).
+ *  - `stream` is a cudaStream_t passed as void*.  Nothing here synchronises the stream or allocates
+ *    device memory, so every call is CUDA-graph capturable.  Scratch comes from the caller (`ws`).
+ *  - Return value: 0 = ok, negative = ganb200_status.  ganb200_last_error() gives a thread-local text.
+ *  - Ownership: the library borrows pointers for the duration of the enqueue only.
+ *  - There is no CPU path: the library refuses to run on a device that is not sm_100.
+ */
+#ifndef GANB200_H
+#define GANB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+  GANB200_OK = 0,
+  GANB200_BAD_SHAPE = -1,
+  GANB200_BAD_ALIGN = -2,
+  GANB200_UNSUPPORTED_ARCH = -3,
+  GANB200_CUDA_ERROR = -4,
+  GANB200_WORKSPACE_TOO_SMALL = -5,
+  GANB200_BAD_ARG = -6
+} ganb200_status;
+
+int ganb200_abi_version(void);
+const char* ganb200_last_error(void);
+/* 0 when `device` is a compute-capability 10.x GPU, GANB200_UNSUPPORTED_ARCH otherwise. */
+int ganb200_device_check(int device);
+
+/* ------------------------------------------------------------------------------------------------
+ * Convolution family.  Replaces nn.functional.conv2d + nn.ReplicationPad2d / zero padding and
+ * nn.ConvTranspose2d / nn.functional.linear and all their autograd backward formulas:
+ *   EqualizedConv2d.forward      discriminators/discriminator_9_4.py:38-40, generators/generator_13_5.py:36-38
+ *   Conv2dWeightModulate.forward generators/generator_13_5.py:234-248 (shared-weight form)
+ *   EqualizedLinear.forward      discriminator_9_4.py:26-27, generator_13_5.py:25-26   (H=W=R=S=1)
+ *   nn.ConvTranspose2d           generator_13_5.py:156,594  (= dgrad of a strided conv)
+ *
+ *   fprop: y[n,k,p,q]  = oscale[n,k] * alpha * sum_{c,r,s} w[k,c,r,s] * iscale[n,c] * xpad[n,c,p*stride+r,q*stride+s] + bias[k]
+ *   dgrad: dx[n,c,h,w] = iscale[n,c] * fold( alpha * sum_{k,r,s} w[k,c,r,s] * oscale[n,k] * dy[n,k,p,q] )
+ *   wgrad: dw[k,c,r,s] = alpha * sum_{n,p,q} oscale[n,k]*dy[n,k,p,q] * iscale[n,c]*xpad[n,c,p*stride+r,q*stride+s]
+ * xpad = x padded by `pad` on each side with zeros (pad_mode 0) or edge replication (pad_mode 1);
+ * fold = adjoint of that padding.  iscale/oscale/bias may be NULL.
+ * P = (H + 2*pad - R)/stride + 1, Q likewise.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct {
+  int N, C, H, W;   /* input  (x / dx)            */
+  int K, R, S;      /* filter (w / dw): K,C,R,S   */
+  int stride, pad;
+  int pad_mode;     /* 0 zeros, 1 replicate       */
+  int P, Q;         /* output (y / dy) spatial    */
+  float alpha;
+  int engine;       /* 0 auto, 1 fp32 CUDA-core implicit GEMM, 2 bf16 tcgen05/TMEM implicit GEMM */
+} ganb200_conv_desc;
+
+enum { GANB200_CONV_FPROP = 0, GANB200_CONV_DGRAD = 1, GANB200_CONV_WGRAD = 2 };
+
+size_t ganb200_conv2d_workspace_bytes(const ganb200_conv_desc* d, int op);
+/* 1 if the tcgen05 engine can run this (desc, op); engine 0 picks it when this returns 1. */
+int ganb200_conv2d_tc_eligible(const ganb200_conv_desc* d, int op);
+int ganb200_conv2d_fprop(const ganb200_conv_desc* d, const float* x, const float* w, const float* bias,
+                         const float* iscale, const float* oscale, float* y,
+                         void* ws, size_t ws_bytes, void* stream);
+int ganb200_conv2d_dgrad(const ganb200_conv_desc* d, const float* dy, const float* w,
+                         const float* iscale, const float* oscale, float* dx,
+                         void* ws, size_t ws_bytes, void* stream);
+int ganb200_conv2d_wgrad(const ganb200_conv_desc* d, const float* x, const float* dy,
+                         const float* iscale, const float* oscale, float* dw,
+                         void* ws, size_t ws_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Separable linear resampling with per-output tap tables:
+ *   y[nc,ho,wo] = sum_{a<Th} sum_{b<Tw} wh[ho,a]*ww[wo,b] * x[nc, ih[ho,a], iw[wo,b]]
+ * One kernel for Smooth (discriminator_9_4.py:56-72, generator_13_5.py:134-150), bicubic x2 / x0.5
+ * (generator_13_5.py:160, discriminator_9_4.py:81), AdaptiveAvgPool2d(5) (discriminator_9_4.py:86),
+ * ReplicationPad2d, their compositions and all their adjoints (the host builds the tables).
+ * ---------------------------------------------------------------------------------------------- */
+int ganb200_resample2d(const float* x, float* y, int NC, int Hi, int Wi, int Ho, int Wo,
+                       const int* ih, const float* wh, int Th,
+                       const int* iw, const float* ww, int Tw, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Pointwise ops.  Replaces the aten elementwise calls of the model files and loops
+ * (sigmoid: discriminator_9_4.py:109; gate product :160; residual add :161; noise add
+ * generator_13_5.py:265; tanh generator_1.py; LeakyReLU generator_1.py / discriminator_1.py ...).
+ * ---------------------------------------------------------------------------------------------- */
+enum {
+  GANB200_U_SIGMOID = 0, GANB200_U_TANH = 1, GANB200_U_SQUARE = 2, GANB200_U_AFFINE = 3, /* p0*x+p1 */
+  GANB200_U_RSQRT_EPS = 4 /* rsqrt(x+p0) */, GANB200_U_SQRT = 5, GANB200_U_LEAKY = 6 /* slope p0 */,
+  GANB200_U_RECIP = 7, GANB200_U_LEAKY_MASK = 8 /* x>0 ? 1 : p0 */, GANB200_U_COPY = 9,
+  GANB200_U_POW = 10 /* x^p0 */
+};
+enum {
+  GANB200_B_ADD = 0, GANB200_B_SUB = 1, GANB200_B_MUL = 2, GANB200_B_DIV = 3,
+  GANB200_B_SIGMOID_BWD = 4 /* a*b*(1-b) */, GANB200_B_TANH_BWD = 5 /* a*(1-b*b) */,
+  GANB200_B_LEAKY_BWD = 6 /* a * (b>0 ? 1 : p0) */
+};
+/* v-broadcast modes for a logical [N,C,HW] tensor */
+enum { GANB200_V_NC = 0 /* v[n*C+c] */, GANB200_V_C = 1 /* v[c] */, GANB200_V_N = 2 /* v[n] */, GANB200_V_SCALAR = 3 };
+
+int ganb200_ew_unary(int op, const float* x, float* y, int64_t n, float p0, float p1, void* stream);
+int ganb200_ew_binary(int op, const float* a, const float* b, float* y, int64_t n, float p0, void* stream);
+/* y = x + v (op ADD) or x * v (op MUL) with v broadcast per vmode */
+int ganb200_ew_bcast(int op, const float* x, const float* v, float* y, int N, int C, int HW, int vmode, void* stream);
+/* y = x + v*z, v broadcast per vmode (noise injection generator_13_5.py:265) */
+int ganb200_ew_fma_bcast(const float* x, const float* v, const float* z, float* y, int N, int C, int HW, int vmode, void* stream);
+
+/* out = sum x*(y or 1) over: rmode 0: HW -> [N,C];  1: N,HW -> [C];  2: C,HW -> [N];  3: all -> [1].
+ * Replaces the bias/scale gradient reductions, AdaptiveAvgPool2d(1) (scaled by the caller), compute_grad2's
+ * pow(2).view(B,-1).sum(1) (train/ganR2.py:36-38), torch.mean (train/wgangpR2.py:21). */
+int ganb200_reduce(const float* x, const float* y, float* out, int N, int C, int HW, int rmode, float scale, void* stream);
+
+/* PReLU (nn.PReLU(C) discriminator_9_4.py:91,136; nn.PReLU() scalar generator_3_progan.py): a_n = C or 1.
+ *   prelu_fwd : y = x>0 ? x : a*x
+ *   maskscale : y = g * (x>0 ? 1 : a)         (PReLU input-gradient; linear in g, so also its own double-backward)
+ *   prelu_bwd : gx = maskscale(gy,x,a), ga[c] = sum gy*min(x,0)   (ga overwritten)
+ *   masked_dot: out[c] = sum u*v*[x<=0]        (d/da of maskscale, needed by the R1/R2/GP double backward) */
+int ganb200_prelu_fwd(const float* x, const float* a, float* y, int N, int C, int HW, int a_n, void* stream);
+int ganb200_maskscale(const float* g, const float* x, const float* a, float* y, int N, int C, int HW, int a_n, void* stream);
+int ganb200_prelu_bwd(const float* gy, const float* x, const float* a, float* gx, float* ga, int N, int C, int HW, int a_n, void* stream);
+int ganb200_masked_dot(const float* u, const float* v, const float* x, float* out, int N, int C, int HW, int a_n, void* stream);
+
+/* BatchNorm, training mode (nn.BatchNorm2d / nn.BatchNorm1d in generator_13_5.py:49,56,157,...):
+ * batch statistics (biased variance, eps inside sqrt), affine, running stats with `momentum`
+ * (running_var gets the unbiased variance), x viewed as [N,C,HW] (HW=1 for BatchNorm1d).
+ * If sum_ws != NULL the kernel only produces per-channel (sum, sumsq-about-mean) partials for a
+ * cross-rank reduction (data-parallel sync-BN) — see bn_stats / bn_apply. */
+int ganb200_bn_stats(const float* x, float* mean, float* var_biased, int N, int C, int HW, void* stream);
+int ganb200_bn_apply(const float* x, const float* mean, const float* var_biased, const float* gamma, const float* beta,
+                     float* y, float* save_invstd, float* running_mean, float* running_var,
+                     int N, int C, int HW, float eps, float momentum, int64_t count_total, void* stream);
+/* gx, ggamma, gbeta from (gy, x, mean, invstd, gamma).  If reduce_ws != NULL (2*C floats, holding
+ * already-reduced sum(gy) and sum(gy*xhat)) the reduction phase is skipped (sync-BN). */
+int ganb200_bn_bwd_reduce(const float* gy, const float* x, const float* mean, const float* invstd,
+                          float* sum_gy, float* sum_gy_xhat, int N, int C, int HW, void* stream);
+int ganb200_bn_bwd_apply(const float* gy, const float* x, const float* mean, const float* invstd, const float* gamma,
+                         const float* sum_gy, const float* sum_gy_xhat, float* gx, float* ggamma, float* gbeta,
+                         int N, int C, int HW, int64_t count_total, void* stream);
+
+/* softmax over dim=1 of a [B,M,C] tensor (nn.Softmax(dim=1), generator_13_5.py:72,87) */
+int ganb200_softmax_m_fwd(const float* x, float* y, int B, int M, int C, void* stream);
+int ganb200_softmax_m_bwd(const float* gy, const float* y, float* gx, int B, int M, int C, void* stream);
+
+/* MiniBatchStdDev scalar (discriminator_9_4.py:42-54): x viewed as [G, L]; s = mean_j sqrt(var_unbiased_j + eps).
+ *   fwd    : out[0] = s
+ *   bwd    : gx = g[0] * ds/dx
+ *   bwd_bwd: given ggx: out_gg[0] = <ggx, ds/dx>,  out_gx = g[0] * (d2s/dx2 . ggx) */
+int ganb200_mbstd_fwd(const float* x, float* out, int G, int64_t L, float eps, void* stream);
+int ganb200_mbstd_bwd(const float* g, const float* x, float* gx, int G, int64_t L, float eps, void* stream);
+int ganb200_mbstd_bwd_bwd(const float* g, const float* x, const float* ggx, float* out_gg, float* out_gx,
+                          int G, int64_t L, float eps, void* stream);
+
+/* BCELoss, mean reduction, log clamped at -100 (torch.nn.BCELoss, train/gan.py:21, ganR2.py:17).
+ * range_flag[0] is set to 1 if any p is outside [0,1] (the caller raises, as the reference does). */
+int ganb200_bce_fwd(const float* p, const float* t, float* out, int* range_flag, int64_t n, void* stream);
+int ganb200_bce_bwd(const float* g, const float* p, const float* t, float* gp, int64_t n, void* stream);
+
+/* Fused multi-tensor Adam / AdamW (torch.optim.Adam train/trainunits.py:18-19; AdamW train/wgangp.py:17-18).
+ * Table entries are device pointers; `tab` is a DEVICE array.
+ * grad_scale multiplies every gradient first (1/world_size for data-parallel averaging). */
+typedef struct {
+  float* p; const float* g; float* m; float* v; int64_t n;
+} ganb200_adam_entry;
+/* block_tab: DEVICE array of n_blocks (tensor index, chunk index) int32 pairs; each CTA updates elements
+ * [chunk_idx*chunk, min(n, (chunk_idx+1)*chunk)) of its tensor.  step is the 1-based Adam step count. */
+int ganb200_multi_tensor_adam_blocks(const ganb200_adam_entry* tab, const int32_t* block_tab, int n_blocks,
+                                     int64_t chunk, float lr, float beta1, float beta2, float eps,
+                                     float weight_decay, int decoupled, int64_t step, float grad_scale,
+                                     void* stream);
+
+/* units/mixup.py:9-17 and :19-27 (with its (B,1)x(B,3,64,64) float64 broadcast) */
+int ganb200_mixup(const float* t, const float* f, float lam, float* out, int64_t n, void* stream);
+int ganb200_mixup_wgan_f64(const double* label, const float* t, const float* f, double* out,
+                           int B, int C, int H, int W, void* stream);
+
+/* Clamp all elements to [lo,hi] in place (train/wgan.py:47-48 weight clipping). */
+int ganb200_clamp_(float* x, int64_t n, float lo, float hi, void* stream);
+
+/* Spectral norm power iteration (torch.nn.utils.parametrizations.spectral_norm, used by
+ * discriminators/discriminator_7_wgangpsn.py:14): W viewed as [rows, cols];
+ * one iteration: v = normalize(W^T u), u = normalize(W v) (eps 1e-12), in place; sigma = u . (W v). */
+int ganb200_spectral_power_iter(const float* W, float* u, float* v, float* sigma, int rows, int cols,
+                                int n_iter, float eps, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GANB200_H */

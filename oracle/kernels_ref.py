@@ -1,0 +1,257 @@
+"""TEST INFRASTRUCTURE — CPU restatement of every libganb200 kernel, in plain torch ops.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline may import this file.  It is the checker
+for the CUDA kernels (same method names and argument meaning as gan_b200.kernels.CudaBackend) and it lets
+the autograd formulas in gan_b200/ops.py be grad-checked in float64 without a GPU.  Each method states the
+math of the kernel it mirrors (include/ganb200.h) using stock ATen on the CPU; nothing here is shipped.
+"""
+import torch
+import torch.nn.functional as F
+
+U_SIGMOID, U_TANH, U_SQUARE, U_AFFINE, U_RSQRT_EPS, U_SQRT, U_LEAKY, U_RECIP, U_LEAKY_MASK, U_COPY, U_POW = range(11)
+B_ADD, B_SUB, B_MUL, B_DIV, B_SIGMOID_BWD, B_TANH_BWD, B_LEAKY_BWD = range(7)
+V_NC, V_C, V_N, V_SCALAR = range(4)
+R_HW, R_NHW, R_CHW, R_ALL = range(4)
+
+
+def _v(x, v, vmode):
+    n, c = (x.shape[0], x.shape[1]) if x.dim() > 1 else (1, x.shape[0])
+    tail = (1,) * (x.dim() - 2)
+    if vmode == V_NC:
+        return v.reshape(n, c, *tail)
+    if vmode == V_C:
+        return v.reshape(1, c, *tail) if x.dim() > 1 else v
+    if vmode == V_N:
+        return v.reshape(n, 1, *tail)
+    return v.reshape(())
+
+
+def _pad(x, pad, pad_mode):
+    if pad == 0:
+        return x
+    return F.pad(x, (pad,) * 4, mode="replicate" if pad_mode == 1 else "constant")
+
+
+class RefBackend:
+    name = "ref"
+
+    # ---- convolution family (include/ganb200.h: fprop / dgrad / wgrad) ---------------------------------
+    def conv_fprop(self, x, w, bias, stride, pad, pad_mode, alpha, iscale=None, oscale=None, engine=None):
+        with torch.no_grad():
+            if iscale is not None:
+                x = x * iscale[:, :, None, None]
+            y = F.conv2d(_pad(x, pad, pad_mode), w, None, stride) * alpha
+            if oscale is not None:
+                y = y * oscale[:, :, None, None]
+            if bias is not None:
+                y = y + bias[None, :, None, None]
+            return y
+
+    def conv_dgrad(self, dy, w, in_hw, stride, pad, pad_mode, alpha, iscale=None, oscale=None, engine=None):
+        N, K = dy.shape[:2]
+        C = w.shape[1]
+        with torch.enable_grad():
+            x = torch.zeros((N, C, *in_hw), dtype=dy.dtype, requires_grad=True)
+            y = F.conv2d(_pad(x, pad, pad_mode), w.detach(), None, stride)
+            g = dy.detach() if oscale is None else dy.detach() * oscale.detach()[:, :, None, None]
+            (dx,) = torch.autograd.grad(y, x, g)
+        dx = dx * alpha
+        if iscale is not None:
+            dx = dx * iscale[:, :, None, None]
+        return dx.detach()
+
+    def conv_wgrad(self, x, dy, rs, stride, pad, pad_mode, alpha, iscale=None, oscale=None, engine=None):
+        K, C = dy.shape[1], x.shape[1]
+        with torch.enable_grad():
+            w = torch.zeros((K, C, *rs), dtype=x.dtype, requires_grad=True)
+            xs = x.detach() if iscale is None else x.detach() * iscale.detach()[:, :, None, None]
+            y = F.conv2d(_pad(xs, pad, pad_mode), w, None, stride)
+            g = dy.detach() if oscale is None else dy.detach() * oscale.detach()[:, :, None, None]
+            (dw,) = torch.autograd.grad(y, w, g)
+        return (dw * alpha).detach()
+
+    # ---- separable resampling: y = Mh x Mw^T on the last two axes -------------------------------------
+    def resample2d(self, x, op_h, op_w):
+        mh = op_h.dense(x.device, x.dtype)
+        mw = op_w.dense(x.device, x.dtype)
+        return torch.einsum("oh,...hw,pw->...op", mh, x, mw).contiguous()
+
+    # ---- pointwise -----------------------------------------------------------------------------------
+    def ew_unary(self, op, x, p0=0.0, p1=0.0):
+        if op == U_SIGMOID: return torch.sigmoid(x)
+        if op == U_TANH: return torch.tanh(x)
+        if op == U_SQUARE: return x * x
+        if op == U_AFFINE: return p0 * x + p1
+        if op == U_RSQRT_EPS: return torch.rsqrt(x + p0)
+        if op == U_SQRT: return torch.sqrt(x)
+        if op == U_LEAKY: return torch.where(x > 0, x, p0 * x)
+        if op == U_RECIP: return 1.0 / x
+        if op == U_LEAKY_MASK: return torch.where(x > 0, torch.ones_like(x), torch.full_like(x, p0))
+        if op == U_COPY: return x.clone()
+        if op == U_POW: return torch.pow(x, p0)
+        raise ValueError(op)
+
+    def ew_binary(self, op, a, b, p0=0.0):
+        if op == B_ADD: return a + b
+        if op == B_SUB: return a - b
+        if op == B_MUL: return a * b
+        if op == B_DIV: return a / b
+        if op == B_SIGMOID_BWD: return a * b * (1 - b)
+        if op == B_TANH_BWD: return a * (1 - b * b)
+        if op == B_LEAKY_BWD: return torch.where(b > 0, a, a * p0)
+        raise ValueError(op)
+
+    def ew_bcast(self, op, x, v, vmode):
+        vv = _v(x, v, vmode)
+        return (x + vv if op == B_ADD else x * vv).contiguous()
+
+    def ew_fma_bcast(self, x, v, z, vmode):
+        return (x + _v(x, v, vmode) * z).contiguous()
+
+    def reduce(self, x, y, rmode, scale=1.0):
+        t = x if y is None else x * y
+        if t.dim() == 1:
+            t = t[None, :]
+        t = t.reshape(t.shape[0], t.shape[1], -1)
+        if rmode == R_HW: out = t.sum(2)
+        elif rmode == R_NHW: out = t.sum((0, 2))
+        elif rmode == R_CHW: out = t.sum((1, 2))
+        else: out = t.sum().reshape(1)
+        return out * scale
+
+    # ---- PReLU ---------------------------------------------------------------------------------------
+    @staticmethod
+    def _slope(x, a):
+        if a.numel() == 1:
+            return a.reshape(())
+        return a.reshape(1, -1, *((1,) * (x.dim() - 2)))
+
+    def prelu_fwd(self, x, a):
+        return torch.where(x > 0, x, self._slope(x, a) * x)
+
+    def maskscale(self, g, x, a):
+        return torch.where(x > 0, g, self._slope(x, a) * g)
+
+    def _asum(self, t, a):
+        if a.numel() == 1:
+            return t.sum().reshape(1)
+        dims = [d for d in range(t.dim()) if d != 1]
+        return t.sum(dims)
+
+    def prelu_bwd(self, gy, x, a, need_gx=True, need_ga=True):
+        gx = self.maskscale(gy, x, a) if need_gx else None
+        ga = self._asum(gy * torch.clamp(x, max=0), a) if need_ga else None
+        return gx, ga
+
+    def masked_dot(self, u, v, x, a_n):
+        t = u * v * (x <= 0).to(u.dtype)
+        if a_n == 1:
+            return t.sum().reshape(1)
+        return t.sum([d for d in range(t.dim()) if d != 1])
+
+    # ---- BatchNorm (training) --------------------------------------------------------------------------
+    @staticmethod
+    def _cview(x, v):
+        return v.reshape(1, -1, *((1,) * (x.dim() - 2)))
+
+    def bn_stats(self, x):
+        dims = [d for d in range(x.dim()) if d != 1]
+        mean = x.mean(dims)
+        var = ((x - self._cview(x, mean)) ** 2).mean(dims)
+        return mean, var
+
+    def bn_apply(self, x, mean, var, gamma, beta, running_mean, running_var, eps, momentum, count_total):
+        invstd = torch.rsqrt(var + eps)
+        y = (x - self._cview(x, mean)) * self._cview(x, invstd)
+        if gamma is not None:
+            y = y * self._cview(x, gamma)
+        if beta is not None:
+            y = y + self._cview(x, beta)
+        if running_mean is not None:
+            running_mean.mul_(1 - momentum).add_(momentum * mean)
+        if running_var is not None:
+            n = float(count_total)
+            running_var.mul_(1 - momentum).add_(momentum * (var * n / (n - 1) if n > 1 else var))
+        return y, invstd
+
+    def bn_bwd_reduce(self, gy, x, mean, invstd):
+        dims = [d for d in range(x.dim()) if d != 1]
+        xhat = (x - self._cview(x, mean)) * self._cview(x, invstd)
+        return gy.sum(dims), (gy * xhat).sum(dims)
+
+    def bn_bwd_apply(self, gy, x, mean, invstd, gamma, sum_gy, sum_gy_xhat, count_total):
+        xhat = (x - self._cview(x, mean)) * self._cview(x, invstd)
+        n = float(count_total)
+        g = gamma if gamma is not None else torch.ones_like(mean)
+        gx = self._cview(x, g * invstd) * (gy - self._cview(x, sum_gy) / n - xhat * self._cview(x, sum_gy_xhat) / n)
+        return gx, sum_gy_xhat.clone(), sum_gy.clone()
+
+    # ---- softmax over branches, MiniBatchStdDev, BCE --------------------------------------------------------
+    def softmax_m_fwd(self, x):
+        return torch.softmax(x, dim=1)
+
+    def softmax_m_bwd(self, gy, y):
+        return y * (gy - (gy * y).sum(1, keepdim=True))
+
+    def mbstd_fwd(self, x, G, eps):
+        g = x.reshape(G, -1)
+        return torch.sqrt(g.var(dim=0) + eps).mean().reshape(1)
+
+    def _mbstd_parts(self, x, G, eps):
+        g = x.reshape(G, -1)
+        d = g - g.mean(0, keepdim=True)
+        sigma = torch.sqrt((d * d).sum(0, keepdim=True) / (G - 1) + eps)
+        return d, sigma, g.shape[1]
+
+    def mbstd_bwd(self, g, x, G, eps):
+        d, sigma, L = self._mbstd_parts(x, G, eps)
+        return (g.reshape(()) * d / ((G - 1) * L * sigma)).reshape(x.shape)
+
+    def mbstd_bwd_bwd(self, g, x, ggx, G, eps):
+        d, sigma, L = self._mbstd_parts(x, G, eps)
+        gg = ggx.reshape(G, -1)
+        dot = (gg * d).sum(0, keepdim=True)
+        out_gg = (dot / ((G - 1) * L * sigma)).sum().reshape(1)
+        out_gx = g.reshape(()) / ((G - 1) * L) * ((gg - gg.mean(0, keepdim=True)) / sigma - d * dot / ((G - 1) * sigma ** 3))
+        return out_gg, out_gx.reshape(x.shape)
+
+    def bce_fwd(self, p, t):
+        bad = ((p < 0) | (p > 1) | torch.isnan(p)).any().to(torch.int32).reshape(1)
+        lp = torch.clamp(torch.log(p), min=-100)
+        lq = torch.clamp(torch.log(1 - p), min=-100)
+        return (-(t * lp + (1 - t) * lq)).mean().reshape(1), bad
+
+    def bce_bwd(self, g, p, t):
+        return g.reshape(()) / p.numel() * (p - t) / torch.clamp((1 - p) * p, min=1e-12)
+
+    # ---- misc ------------------------------------------------------------------------------------------------
+    def mixup(self, t, f, lam):
+        return lam * t + (1 - lam) * f
+
+    def mixup_wgan_f64(self, label, t, f):
+        return label * t + (1 - label) * f
+
+    def clamp_(self, x, lo, hi):
+        return x.clamp_(lo, hi)
+
+    def spectral_power_iter(self, w2d, u, v, n_iter, eps):
+        for _ in range(n_iter):
+            v.copy_(F.normalize(torch.mv(w2d.t(), u), dim=0, eps=eps))
+            u.copy_(F.normalize(torch.mv(w2d, v), dim=0, eps=eps))
+        return torch.dot(u, torch.mv(w2d, v)).reshape(1)
+
+
+def adam_reference(p, g, m, v, lr, b1, b2, eps, wd, decoupled, step, grad_scale=1.0):
+    """single-tensor torch.optim.Adam / AdamW math (torch/optim/adam.py _single_tensor_adam), in place."""
+    g = g * grad_scale
+    if wd != 0:
+        if decoupled:
+            p.mul_(1 - lr * wd)
+        else:
+            g = g + wd * p
+    m.lerp_(g, 1 - b1)
+    v.mul_(b2).addcmul_(g, g, value=1 - b2)
+    bc1 = 1 - b1 ** step
+    bc2 = 1 - b2 ** step
+    denom = (v.sqrt() / (bc2 ** 0.5)).add_(eps)
+    p.addcdiv_(m, denom, value=-(lr / bc1))

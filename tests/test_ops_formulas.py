@@ -1,0 +1,147 @@
+"""CPU, float64: the autograd formulas of gan_b200/ops.py (first and second order) against stock torch ops,
+with the kernels replaced by their CPU restatement (oracle/kernels_ref.py)."""
+import pytest
+import torch
+import torch.nn.functional as F
+from torch.autograd import gradcheck, gradgradcheck
+
+from gan_b200 import ops
+from gan_b200 import kernels as KN
+
+torch.manual_seed(0)
+D = torch.float64
+
+
+def r(*shape, grad=True):
+    return torch.randn(*shape, dtype=D, requires_grad=grad)
+
+
+@pytest.mark.parametrize("stride,pad,pad_mode,k", [(1, 1, 1, 3), (2, 1, 1, 3), (1, 0, 0, 3), (1, 2, 1, 5), (2, 1, 0, 4), (1, 0, 0, 1)])
+def test_conv2d_matches_torch_and_is_twice_differentiable(ref_backend, stride, pad, pad_mode, k):
+    x, w, b = r(2, 3, 6, 6), r(4, 3, k, k), r(4)
+    y = ops.conv2d(x, w, b, stride, pad, pad_mode, alpha=0.7)
+    xp = F.pad(x, (pad,) * 4, mode="replicate" if pad_mode else "constant") if pad else x
+    ref = F.conv2d(xp, w * 0.7, b, stride)
+    assert torch.allclose(y, ref, atol=1e-12)
+    f = lambda x, w, b: ops.conv2d(x, w, b, stride, pad, pad_mode, alpha=0.7)
+    assert gradcheck(f, (x, w, b))
+    assert gradgradcheck(f, (x, w, b))
+
+
+def test_conv_transpose_matches_torch(ref_backend):
+    x, w, b = r(2, 3, 4, 4), r(3, 5, 4, 4), r(5)
+    y = ops.conv_transpose2d(x, w, b, stride=2, pad=1)
+    assert torch.allclose(y, F.conv_transpose2d(x, w, b, stride=2, padding=1), atol=1e-12)
+    z, w1 = r(2, 6, 1, 1), r(6, 4, 4, 4)
+    assert torch.allclose(ops.conv_transpose2d(z, w1, None, 1, 0), F.conv_transpose2d(z, w1), atol=1e-12)
+    assert gradcheck(lambda x, w, b: ops.conv_transpose2d(x, w, b, 2, 1), (x, w, b))
+
+
+def test_linear(ref_backend):
+    x, w, b = r(5, 7), r(3, 7), r(3)
+    assert torch.allclose(ops.linear(x, w, b, alpha=0.3), F.linear(x, w * 0.3, b), atol=1e-12)
+    f = lambda x, w, b: ops.linear(x, w, b, 0.3)
+    assert gradcheck(f, (x, w, b)) and gradgradcheck(f, (x, w, b))
+
+
+@pytest.mark.parametrize("an", [1, 3])
+def test_prelu(ref_backend, an):
+    x, a = r(2, 3, 4, 4), (torch.rand(an, dtype=D) * 0.5).requires_grad_()
+    assert torch.allclose(ops.prelu(x, a), F.prelu(x, a))
+    assert gradcheck(ops.prelu, (x, a))
+    # second order through the input-gradient chain (what R1 needs): d/d(a), d/d(gy)
+    def chain(x, a, gy):
+        y = ops.prelu(x, a)
+        (gx,) = torch.autograd.grad(y, x, gy, create_graph=True)
+        return gx
+    gy = r(2, 3, 4, 4)
+    assert gradcheck(chain, (x, a, gy))
+
+
+def test_resample_ops_match_torch(ref_backend):
+    x = r(2, 3, 8, 8)
+    k = torch.tensor([[1., 2, 1], [2, 4, 2], [1, 2, 1]], dtype=D) / 16
+    sm = F.conv2d(F.pad(x.reshape(-1, 1, 8, 8), (1,) * 4, mode="replicate"), k[None, None]).reshape(x.shape)
+    assert torch.allclose(ops.smooth(x), sm, atol=1e-12)
+    down = F.interpolate(sm, (4, 4), mode="bicubic", align_corners=False)
+    assert torch.allclose(ops.smooth_bicubic_down2(x), down, atol=1e-12)
+    up = F.interpolate(x, scale_factor=2, mode="bicubic", align_corners=False)
+    assert torch.allclose(ops.bicubic_resize(x, 16, 16, 0.5), up, atol=1e-12)
+    sm_up = F.conv2d(F.pad(up.reshape(-1, 1, 16, 16), (1,) * 4, mode="replicate"), k[None, None]).reshape(up.shape)
+    assert torch.allclose(ops.bicubic_up2_smooth(x), sm_up, atol=1e-12)
+    for hw in (8, 16, 64, 7):
+        t = r(1, 2, hw, hw)
+        assert torch.allclose(ops.adaptive_avg_pool(t, 5), F.adaptive_avg_pool2d(t, 5), atol=1e-12)
+    assert torch.allclose(ops.global_avg_pool(x), x.mean((2, 3)), atol=1e-12)
+    assert gradcheck(ops.smooth_bicubic_down2, (x,)) and gradgradcheck(ops.smooth_bicubic_down2, (x,))
+
+
+def test_pointwise_and_broadcast(ref_backend):
+    x, v, vc = r(2, 3, 4, 4), r(2, 3), r(3)
+    assert torch.allclose(ops.mul_bc(x, v), x * v[:, :, None, None])
+    assert torch.allclose(ops.add_bc(x, vc), x + vc[None, :, None, None])
+    assert gradcheck(ops.mul_bc, (x, v)) and gradgradcheck(ops.mul_bc, (x, v))
+    assert gradcheck(ops.sigmoid, (x,)) and gradgradcheck(ops.sigmoid, (x,))
+    assert gradcheck(ops.tanh, (x,)) and gradgradcheck(ops.tanh, (x,))
+    assert gradcheck(lambda t: ops.leaky_relu(t, 0.2), (x,)) and gradgradcheck(lambda t: ops.leaky_relu(t, 0.2), (x,))
+    xp = (torch.rand(2, 3, dtype=D) + 0.5).requires_grad_()
+    assert gradcheck(ops.sqrt, (xp,)) and gradgradcheck(ops.sqrt, (xp,))
+    assert gradcheck(lambda t: ops.rsqrt_eps(t, 1e-8), (xp,))
+    assert gradcheck(ops.square, (x,)) and gradgradcheck(ops.square, (x,))
+    assert gradcheck(ops.mean, (x,)) and gradcheck(ops.sumsq_per_sample, (x,))
+    z = r(2, 3, 4, 4, grad=False)
+    assert torch.allclose(ops.noise_add(x, vc, z), x + vc[None, :, None, None] * z)
+    assert gradcheck(lambda x, vc: ops.noise_add(x, vc, z), (x, vc))
+
+
+def test_minibatch_stddev(ref_backend):
+    x = r(8, 3, 2, 2)
+    g = x.view(4, -1)
+    std = torch.sqrt(g.var(dim=0) + 1e-8).mean().view(1, 1, 1, 1).expand(8, -1, 2, 2)
+    assert torch.allclose(ops.minibatch_stddev(x), torch.cat([x, std], 1), atol=1e-12)
+    assert gradcheck(ops.minibatch_stddev, (x,)) and gradgradcheck(ops.minibatch_stddev, (x,))
+
+
+def test_bce(ref_backend):
+    p = torch.rand(6, 1, dtype=D).clamp(0.05, 0.95).requires_grad_()
+    t = torch.rand(6, 1, dtype=D)
+    assert torch.allclose(ops.bce_loss(p, t), F.binary_cross_entropy(p, t))
+    assert gradcheck(lambda p: ops.bce_loss(p, t), (p,))
+    with pytest.raises(RuntimeError, match="between 0 and 1"):
+        ops.bce_loss(p.detach() + 1.0, t)
+
+
+def test_batchnorm_and_softmax(ref_backend):
+    for shape in [(6, 4), (3, 4, 5, 5)]:
+        x, g, b = r(*shape), r(4), r(4)
+        rm, rv = torch.zeros(4, dtype=D), torch.ones(4, dtype=D)
+        rm2, rv2 = rm.clone(), rv.clone()
+        y = ops.batch_norm_train(x, g, b, rm, rv, 1e-5, 0.1)
+        ref = F.batch_norm(x, rm2, rv2, g, b, True, 0.1, 1e-5)
+        assert torch.allclose(y, ref, atol=1e-10) and torch.allclose(rm, rm2) and torch.allclose(rv, rv2)
+        assert gradcheck(lambda x, g, b: ops.batch_norm_train(x, g, b, None, None, 1e-5, 0.1), (x, g, b))
+        assert torch.allclose(ops.batch_norm_eval(x, g, b, rm, rv, 1e-5), F.batch_norm(x, rm, rv, g, b, False, 0.1, 1e-5), atol=1e-10)
+    a = r(3, 2, 5)
+    assert torch.allclose(ops.softmax_m(a), torch.softmax(a, 1))
+    assert gradcheck(ops.softmax_m, (a,))
+
+
+@pytest.mark.parametrize("k", [1, 3, 5])
+def test_modulated_conv_equals_per_sample_weight_form(ref_backend, k):
+    B, Ci, Co, H = 3, 4, 5, 6
+    x, w, s = r(B, Ci, H, H), r(Co, Ci, k, k), r(B, Ci)
+    alpha, eps, pad = 0.37, 1e-8, (k - 1) // 2
+
+    def reference_form(x, w, s):  # generators/generator_13_5.py:234-248 restated
+        ww = (w * alpha)[None] * s[:, None, :, None, None]
+        ww = ww * torch.rsqrt((ww ** 2).sum((2, 3, 4), keepdim=True) + eps)
+        xx = F.pad(x.reshape(1, -1, H, H), (pad,) * 4, mode="replicate") if pad else x.reshape(1, -1, H, H)
+        return F.conv2d(xx, ww.reshape(B * Co, Ci, k, k), groups=B).reshape(B, Co, H, H)
+
+    y = ops.modulated_conv2d(x, w, s, pad, alpha, True, eps)
+    assert torch.allclose(y, reference_form(x, w, s), atol=1e-11)
+    gy = torch.randn_like(y)
+    g1 = torch.autograd.grad(y, (x, w, s), gy)
+    g2 = torch.autograd.grad(reference_form(x, w, s), (x, w, s), gy)
+    for a, b in zip(g1, g2):
+        assert torch.allclose(a, b, atol=1e-10)
