@@ -50,7 +50,7 @@ SIGNATURES = {
     "ganb200_prelu_bwd": (c_int, [P, P, P, P, P, c_int, c_int, c_int, c_int, P]),
     "ganb200_masked_dot": (c_int, [P, P, P, P, c_int, c_int, c_int, c_int, P]),
     "ganb200_bn_stats": (c_int, [P, P, P, c_int, c_int, c_int, P]),
-    "ganb200_bn_apply": (c_int, [P, P, P, P, P, P, P, P, P, c_int, c_int, c_int, c_float, c_float, c_int64, P]),
+    "ganb200_bn_apply": (c_int, [P, P, P, P, P, P, P, P, P, P, c_int, c_int, c_int, c_float, c_float, c_int64, P]),
     "ganb200_bn_bwd_reduce": (c_int, [P, P, P, P, P, P, c_int, c_int, c_int, P]),
     "ganb200_bn_bwd_apply": (c_int, [P, P, P, P, P, P, P, P, P, P, c_int, c_int, c_int, c_int64, P]),
     "ganb200_softmax_m_fwd": (c_int, [P, P, c_int, c_int, c_int, P]),
@@ -61,7 +61,9 @@ SIGNATURES = {
     "ganb200_bce_fwd": (c_int, [P, P, P, P, c_int64, P]),
     "ganb200_bce_bwd": (c_int, [P, P, P, P, c_int64, P]),
     "ganb200_multi_tensor_adam_blocks": (c_int, [P, P, c_int, c_int64, c_float, c_float, c_float, c_float, c_float,
-                                                 c_int, c_int64, c_float, P]),
+                                                 c_int, c_int64, P, c_float, P]),
+    "ganb200_counter_add": (c_int, [P, c_int64, P]),
+    "ganb200_chan_copy": (c_int, [P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, P]),
     "ganb200_mixup": (c_int, [P, P, c_float, P, c_int64, P]),
     "ganb200_mixup_wgan_f64": (c_int, [P, P, P, P, c_int, c_int, c_int, c_int, P]),
     "ganb200_clamp_": (c_int, [P, c_int64, c_float, c_float, P]),

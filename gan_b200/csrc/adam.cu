@@ -12,6 +12,7 @@ struct AdamHyper {
   float step_size;         // lr / (1 - beta1^t)
   float inv_bc2_sqrt;      // 1 / sqrt(1 - beta2^t)
   int decoupled;
+  const int64_t* step_dev; // when non-null the 1-based step count lives on the device (CUDA-graph replay)
 };
 
 __device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, const AdamHyper& h) {
@@ -32,6 +33,17 @@ __device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, 
 __global__ void __launch_bounds__(256) multi_tensor_adam_kernel(const ganb200_adam_entry* __restrict__ tab,
                                                                 const int2* __restrict__ block_tab, int64_t chunk,
                                                                 AdamHyper h) {
+  if (h.step_dev) {  // bias corrections from the device-side step counter, once per CTA
+    __shared__ float s_bc[2];
+    if (threadIdx.x == 0) {
+      double t = (double)(*h.step_dev);
+      s_bc[0] = (float)((double)h.lr / (1.0 - pow((double)h.beta1, t)));
+      s_bc[1] = (float)(1.0 / sqrt(1.0 - pow((double)h.beta2, t)));
+    }
+    __syncthreads();
+    h.step_size = s_bc[0];
+    h.inv_bc2_sqrt = s_bc[1];
+  }
   int2 bt = block_tab[blockIdx.x];
   ganb200_adam_entry e = tab[bt.x];
   int64_t lo = (int64_t)bt.y * chunk;
@@ -64,8 +76,8 @@ using namespace ganb200;
 // block_tab: DEVICE array of n_blocks int32 pairs (tensor index, chunk index); chunk = elements per CTA.
 extern "C" int ganb200_multi_tensor_adam_blocks(const ganb200_adam_entry* tab, const int32_t* block_tab, int n_blocks,
                                                 int64_t chunk, float lr, float beta1, float beta2, float eps,
-                                                float weight_decay, int decoupled, int64_t step, float grad_scale,
-                                                void* stream) {
+                                                float weight_decay, int decoupled, int64_t step,
+                                                const int64_t* step_dev, float grad_scale, void* stream) {
   if (n_blocks <= 0) return 0;
   GB_REQUIRE(chunk > 0 && (chunk % 4) == 0, GANB200_BAD_ARG, "adam: chunk must be a positive multiple of 4");
   AdamHyper h;
@@ -75,6 +87,7 @@ extern "C" int ganb200_multi_tensor_adam_blocks(const ganb200_adam_entry* tab, c
   h.step_size = (float)((double)lr / bc1);
   h.inv_bc2_sqrt = (float)(1.0 / sqrt(bc2));
   h.decoupled = decoupled;
+  h.step_dev = step_dev;
   multi_tensor_adam_kernel<<<n_blocks, 256, 0, (cudaStream_t)stream>>>(tab, reinterpret_cast<const int2*>(block_tab),
                                                                        chunk, h);
   GB_CHECK_LAUNCH();

@@ -204,7 +204,8 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const float* __restrict__
                                                        const float* __restrict__ sgy, const float* __restrict__ sgx,
                                                        float* __restrict__ y, float* __restrict__ o0, float* __restrict__ o1,
                                                        float* __restrict__ o2, int N, int C, int HW, float eps,
-                                                       float momentum, float count) {
+                                                       float momentum, float count, int64_t* nbt) {
+  if (MODE == 0 && nbt && blockIdx.x == 0 && threadIdx.x == 0) *nbt += 1;  // num_batches_tracked
   int64_t rows = (int64_t)N * C;
   int64_t total = rows * HW;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
@@ -260,13 +261,13 @@ extern "C" int ganb200_bn_stats(const float* x, float* mean, float* var_biased, 
 
 extern "C" int ganb200_bn_apply(const float* x, const float* mean, const float* var_biased, const float* gamma,
                                 const float* beta, float* y, float* save_invstd, float* running_mean,
-                                float* running_var, int N, int C, int HW, float eps, float momentum,
-                                int64_t count_total, void* stream) {
+                                float* running_var, int64_t* num_batches_tracked, int N, int C, int HW, float eps,
+                                float momentum, int64_t count_total, void* stream) {
   cudaStream_t s = (cudaStream_t)stream;
   int64_t total = (int64_t)N * C * HW;
   bn_apply_kernel<0><<<ew_grid(total, 256, 4), 256, 0, s>>>(x, nullptr, mean, var_biased, gamma, beta, nullptr, nullptr, y,
                                                            save_invstd, running_mean, running_var, N, C, HW, eps,
-                                                           momentum, (float)count_total);
+                                                           momentum, (float)count_total, num_batches_tracked);
   GB_CHECK_LAUNCH();
   return 0;
 }
@@ -289,7 +290,7 @@ extern "C" int ganb200_bn_bwd_apply(const float* gy, const float* x, const float
   int64_t total = (int64_t)N * C * HW;
   bn_apply_kernel<1><<<ew_grid(total, 256, 4), 256, 0, s>>>(x, gy, mean, invstd, gamma, nullptr, sum_gy, sum_gy_xhat, gx,
                                                            ggamma, gbeta, nullptr, N, C, HW, 0.f, 0.f,
-                                                           (float)count_total);
+                                                           (float)count_total, nullptr);
   GB_CHECK_LAUNCH();
   return 0;
 }

@@ -223,14 +223,17 @@ class CudaBackend:
         _lib.check(self.lib.ganb200_bn_stats(self._p(x), self._p(mean), self._p(var), N, C, HW, st))
         return mean, var
 
-    def bn_apply(self, x, mean, var, gamma, beta, running_mean, running_var, eps, momentum, count_total):
+    def bn_apply(self, x, mean, var, gamma, beta, running_mean, running_var, eps, momentum, count_total, nbt=None):
         N, C, HW = _nchw(x)
         st = self._prep(x, mean, var, gamma, beta, running_mean, running_var)
+        if nbt is not None and nbt.dtype != torch.int64:
+            raise _lib.GanB200Error("num_batches_tracked must be int64")
         y = torch.empty_like(x)
         invstd = torch.empty((C,), dtype=torch.float32, device=x.device)
         _lib.check(self.lib.ganb200_bn_apply(self._p(x), self._p(mean), self._p(var), self._p(gamma), self._p(beta),
                                              self._p(y), self._p(invstd), self._p(running_mean),
-                                             self._p(running_var), N, C, HW, eps, momentum, count_total, st))
+                                             self._p(running_var), self._p(nbt), N, C, HW, eps, momentum,
+                                             count_total, st))
         return y, invstd
 
     def bn_bwd_reduce(self, gy, x, mean, invstd):
@@ -302,12 +305,29 @@ class CudaBackend:
         return gp
 
     # -- optimiser / misc -------------------------------------------------------------------------
-    def adam_blocks(self, tab, block_tab, n_blocks, chunk, lr, b1, b2, eps, wd, decoupled, step, grad_scale):
-        st = self._prep(tab, block_tab) if False else ctypes.c_void_p(
-            torch.cuda.current_stream(tab.device).cuda_stream)
+    def adam_blocks(self, tab, block_tab, n_blocks, chunk, lr, b1, b2, eps, wd, decoupled, step, grad_scale,
+                    step_dev=None):
+        """tab: uint8 device tensor holding ganb200_adam_entry[]; block_tab: int32 (n_blocks,2); step_dev: int64 (1,)"""
+        st = ctypes.c_void_p(torch.cuda.current_stream(tab.device).cuda_stream)
         LAUNCH_COUNT[0] += 1
         _lib.check(self.lib.ganb200_multi_tensor_adam_blocks(self._p(tab), self._p(block_tab), n_blocks, chunk, lr,
-                                                             b1, b2, eps, wd, int(decoupled), step, grad_scale, st))
+                                                             b1, b2, eps, wd, int(decoupled), step,
+                                                             self._p(step_dev), grad_scale, st))
+
+    def counter_add(self, ctr, inc):
+        st = ctypes.c_void_p(torch.cuda.current_stream(ctr.device).cuda_stream)
+        LAUNCH_COUNT[0] += 1
+        _lib.check(self.lib.ganb200_counter_add(self._p(ctr), int(inc), st))
+
+    def chan_copy(self, src, src_c0, dst, dst_c0, ncopy, accumulate=False):
+        """dst[:, dst_c0:dst_c0+ncopy] (+)= src[:, src_c0:src_c0+ncopy] on [N,C,...] tensors."""
+        N, Cs, HW = _nchw(src)
+        N2, Cd, HW2 = _nchw(dst)
+        assert N == N2 and HW == HW2, (src.shape, dst.shape)
+        st = self._prep(src, dst)
+        _lib.check(self.lib.ganb200_chan_copy(self._p(src), self._p(dst), N, Cs, src_c0, Cd, dst_c0, ncopy, HW,
+                                              int(accumulate), st))
+        return dst
 
     def mixup(self, t, f, lam):
         st = self._prep(t, f)

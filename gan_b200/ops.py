@@ -392,6 +392,77 @@ def sumsq_per_sample(g):
 
 
 # =====================================================================================================
+# channel cat / slice / zero-pad (closed under differentiation; replaces torch.cat(dim=1) and x[:, a:b])
+# =====================================================================================================
+class CatChannelsFn(Function):
+    @staticmethod
+    def forward(ctx, *xs):
+        xs = [_c(x) for x in xs]
+        ctx.widths = [x.shape[1] for x in xs]
+        shape = list(xs[0].shape)
+        shape[1] = sum(ctx.widths)
+        out = torch.empty(shape, dtype=xs[0].dtype, device=xs[0].device)
+        c0 = 0
+        for x in xs:
+            K().chan_copy(x, 0, out, c0, x.shape[1])
+            c0 += x.shape[1]
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        g = _c(g)
+        outs, c0 = [], 0
+        for i, wd in enumerate(ctx.widths):
+            outs.append(SliceChannelsFn.apply(g, c0, wd) if ctx.needs_input_grad[i] else None)
+            c0 += wd
+        return tuple(outs)
+
+
+class SliceChannelsFn(Function):
+    @staticmethod
+    def forward(ctx, x, c0, n):
+        x = _c(x)
+        ctx.c0, ctx.C = c0, x.shape[1]
+        shape = list(x.shape)
+        shape[1] = n
+        out = torch.empty(shape, dtype=x.dtype, device=x.device)
+        return K().chan_copy(x, c0, out, 0, n)
+
+    @staticmethod
+    def backward(ctx, g):
+        return PadChannelsFn.apply(_c(g), ctx.c0, ctx.C), None, None
+
+
+class PadChannelsFn(Function):
+    """zeros with g placed at channels [c0, c0+g.shape[1]) of a C-channel tensor (adjoint of a channel slice)."""
+
+    @staticmethod
+    def forward(ctx, g, c0, C):
+        g = _c(g)
+        ctx.c0, ctx.n = c0, g.shape[1]
+        shape = list(g.shape)
+        shape[1] = C
+        out = torch.zeros(shape, dtype=g.dtype, device=g.device)
+        return K().chan_copy(g, 0, out, c0, g.shape[1])
+
+    @staticmethod
+    def backward(ctx, gg):
+        return SliceChannelsFn.apply(_c(gg), ctx.c0, ctx.n), None, None
+
+
+def cat_channels(xs):
+    xs = list(xs)
+    return xs[0] if len(xs) == 1 else CatChannelsFn.apply(*xs)
+
+
+def slice_channels(x, c0, c1=None):
+    c1 = x.shape[1] if c1 is None else c1
+    if c0 == 0 and c1 == x.shape[1]:
+        return x
+    return SliceChannelsFn.apply(x, c0, c1 - c0)
+
+
+# =====================================================================================================
 # PReLU
 # =====================================================================================================
 class PReluFn(Function):
@@ -552,17 +623,16 @@ class BatchNormTrainFn(Function):
     """nn.BatchNorm1d/2d in training mode: batch statistics + running-stat update (momentum)."""
 
     @staticmethod
-    def forward(ctx, x, gamma, beta, running_mean, running_var, eps, momentum):
+    def forward(ctx, x, gamma, beta, running_mean, running_var, eps, momentum, nbt=None):
         x = _c(x)
         N, C, HW = KN._nchw(x)
         count = N * HW
         mean, var = K().bn_stats(x)
         if _sync_bn_hooks["stats"] is not None:
             mean, var, count = _sync_bn_hooks["stats"](mean, var, count)
-        y, invstd = K().bn_apply(x, mean, var, gamma, beta, running_mean, running_var, eps, momentum, count)
+        y, invstd = K().bn_apply(x, mean, var, gamma, beta, running_mean, running_var, eps, momentum, count, nbt)
         ctx.save_for_backward(x, mean, invstd, gamma)
         ctx.count = count
-        ctx.mark_non_differentiable(*[t for t in (running_mean, running_var) if t is not None])
         return y
 
     @staticmethod
@@ -574,11 +644,12 @@ class BatchNormTrainFn(Function):
         if _sync_bn_hooks["grads"] is not None:
             s1, s2 = _sync_bn_hooks["grads"](s1, s2)
         gx, gg, gb = K().bn_bwd_apply(gy, x, mean, invstd, gamma, s1, s2, ctx.count)
-        return gx, (gg if gamma is not None else None), (gb if ctx.needs_input_grad[2] else None), None, None, None, None
+        return (gx, (gg if gamma is not None else None), (gb if ctx.needs_input_grad[2] else None), None, None, None,
+                None, None)
 
 
-def batch_norm_train(x, gamma, beta, running_mean, running_var, eps, momentum):
-    return BatchNormTrainFn.apply(x, gamma, beta, running_mean, running_var, eps, momentum)
+def batch_norm_train(x, gamma, beta, running_mean, running_var, eps, momentum, nbt=None):
+    return BatchNormTrainFn.apply(x, gamma, beta, running_mean, running_var, eps, momentum, nbt)
 
 
 def batch_norm_eval(x, gamma, beta, running_mean, running_var, eps):

@@ -1,0 +1,512 @@
+"""generator_13_5 — drop-in for the reference's final generator, on libganb200 kernels.
+
+Class names, constructor signatures, attribute names and construction order follow
+/root/reference/generators/generator_13_5.py (state_dict keys, optimiser parameter order and the RNG stream
+consumed while building the 11 180 parameter tensors are identical).  The arithmetic is re-derived:
+
+* Conv2dWeightModulate (reference :219-248) never materialises per-sample weights (B*Cout*Cin*k*k, 2.2 GiB per
+  image in the reference).  It runs ONE implicit GEMM with the shared weight: the style scales the
+  input channels inside the operand gather, sigma_inv scales the output in the epilogue
+  (gan_b200.ops.modulated_conv2d).
+* replicate padding is an index clamp inside the conv kernels; cat/slice are channel-slice copies; SK/SE
+  products and noise injection are fused broadcast kernels; BatchNorm always uses batch statistics because the
+  reference never leaves train mode.
+* StyleConv.bias is a dead parameter in the reference (:263 computes x + bias and drops it): it is
+  kept as a parameter, never used, never receives a gradient.
+
+Channel plan for planes=48 (reference :610-631): 4^2:396 -> 8^2:396 -> 16^2:204 -> 32^2:108 -> 64^2:108 -> rgb.
+"""
+import math
+from typing import Tuple, List
+
+import torch
+import torch.nn as nn
+
+from gan_b200 import layers as L
+from gan_b200 import ops
+
+
+class EqualizedWeight(L.EqWeightBase):
+    """reference :8-16 — parameter `weights`, constant `scale`."""
+    PARAM, GAIN = "weights", "scale"
+
+    def __init__(self, shape: List[int]):
+        super(EqualizedWeight, self).__init__(shape)
+
+
+class EqualizedLinear(L.EqLinearBase):
+    """reference :19-26 — bias ~ N(0,1)."""
+    WEIGHT = EqualizedWeight
+
+    def __init__(self, in_planes: int, out_planes: int):
+        super(EqualizedLinear, self).__init__()
+        self._build(in_planes, out_planes)
+
+
+class EqualizedConv2d(L.EqConv2dBase):
+    """reference :29-38 — 'same' replicate padding, stride 1."""
+    WEIGHT = EqualizedWeight
+
+    def __init__(self, in_planes: int, out_planes: int, kernel_size: int):
+        super(EqualizedConv2d, self).__init__()
+        self._build(in_planes, out_planes, kernel_size, (kernel_size - 1) // 2)
+
+
+def _fc_bn_act(planes, n):
+    mods = []
+    for _ in range(n):
+        mods += [EqualizedLinear(planes, planes), L.BatchNorm1d(planes), L.PReLU(planes)]
+    return mods
+
+
+def _conv_bn_act(planes, n):
+    mods = []
+    for _ in range(n):
+        mods += [EqualizedConv2d(planes, planes, 3), L.BatchNorm2d(planes), L.PReLU(planes)]
+    return mods
+
+
+class _SKAttention(nn.Module):
+    """shared tail of the two SK attentions: M heads (fc,BN,PReLU,fc) on fea_z, softmax across heads."""
+
+    def _build_heads(self, planes, m):
+        self.M = m
+        for i in range(m):
+            self.__setattr__('fc_sub_%d' % i, nn.Sequential(*_fc_bn_act(planes, 1), EqualizedLinear(planes, planes)))
+        self.softmax = nn.Softmax(dim=1)
+
+    def _heads(self, fea_z, b, s, c):
+        subs = [self.__getattr__('fc_sub_%d' % i) for i in range(self.M)]
+        return L.sk_attention_vectors(fea_z, subs).view(b, s, c, 1, 1)
+
+
+class SKAttention_conv(_SKAttention):
+    """reference :41-89 — sum of branches -> 5x5 pool -> 2x(conv3x3,BN,PReLU) -> GAP -> fc,BN,PReLU -> heads."""
+
+    def __init__(self, planes: int, m: int):
+        super(SKAttention_conv, self).__init__()
+        self.gap_conv = L.AdaptiveAvgPool2d(5)
+        self.conv_main = nn.Sequential(*_conv_bn_act(planes, 2))
+        self.gap_fc = L.AdaptiveAvgPool2d(1)
+        self.fc_main = nn.Sequential(*_fc_bn_act(planes, 1))
+        self._build_heads(planes, m)
+
+    def forward(self, feas):
+        branches = L.as_branches(feas)
+        b, c, _, side = branches[0].shape
+        assert (side >= 8)
+        fea_s = self.conv_main(self.gap_conv(L.branch_sum(branches)))
+        fea_z = self.fc_main(self.gap_fc(fea_s).view(b, c))
+        return self._heads(fea_z, b, len(branches), c)
+
+
+class SKAttention_fc(_SKAttention):
+    """reference :92-131 — sum of branches -> GAP -> 2x(fc,BN,PReLU) -> heads."""
+
+    def __init__(self, planes: int, m: int):
+        super(SKAttention_fc, self).__init__()
+        self.gap_fc = L.AdaptiveAvgPool2d(1)
+        self.fc_main = nn.Sequential(*_fc_bn_act(planes, 2))
+        self._build_heads(planes, m)
+
+    def forward(self, feas):
+        branches = L.as_branches(feas)
+        b, c = branches[0].shape[:2]
+        fea_z = self.fc_main(self.gap_fc(L.branch_sum(branches)).view(b, c))
+        return self._heads(fea_z, b, len(branches), c)
+
+
+class Smooth(L.SmoothBase):
+    """reference :134-150"""
+
+
+class SKConvT(nn.Module):
+    """reference :153-170 — learned x2 (ConvT k4 s2 p1 + BN + PReLU) and fixed x2 (bicubic then Smooth, applied as
+    one separable stencil) merged by SK attention."""
+
+    def __init__(self, planes: int):
+        super(SKConvT, self).__init__()
+        self.convT = L.ConvTranspose2d(planes, planes, kernel_size=4, stride=2, padding=1)
+        self.bn = L.BatchNorm2d(planes)
+        self.activation_convT = L.PReLU(planes)
+        self.up_sample = L.BicubicUp2()
+        self.smooth = Smooth()
+        self.sk_attention = SKAttention_conv(planes, 2)
+
+    def forward(self, x: torch.Tensor):
+        learned = self.activation_convT(self.bn(self.convT(x)))
+        fixed = ops.bicubic_up2_smooth(x)
+        branches = [learned, fixed]
+        return L.sk_merge(branches, self.sk_attention(branches))
+
+
+def _pick_sk_attention(planes, m, image_size):
+    return SKAttention_conv(planes, m) if image_size > 4 else SKAttention_fc(planes, m)
+
+
+class SKConv(nn.Module):
+    """reference :173-202 — m branches EqualizedConv2d k=3,5,.. + BN + PReLU, SK merge."""
+
+    def __init__(self, in_planes: int, out_planes: int, m: int, image_size: int):
+        super(SKConv, self).__init__()
+        assert (m > 0)
+        self.M = m
+        for i in range(m):
+            self.__setattr__('conv_%d' % i, EqualizedConv2d(in_planes, out_planes, kernel_size=3 + i * 2))
+            self.__setattr__('BatchNorm_%d' % i, L.BatchNorm2d(out_planes))
+            self.__setattr__('nonlinear_%d' % i, L.PReLU(out_planes))
+        self.sk_attention = _pick_sk_attention(out_planes, m, image_size)
+
+    def forward(self, x: torch.Tensor):
+        branches = []
+        for i in range(self.M):
+            t = self.__getattr__('conv_%d' % i)(x)
+            t = self.__getattr__('BatchNorm_%d' % i)(t)
+            branches.append(self.__getattr__('nonlinear_%d' % i)(t))
+        return L.sk_merge(branches, self.sk_attention(branches))
+
+
+class MappingNetwork(nn.Module):
+    """reference :205-216"""
+
+    def __init__(self, planes: int, n_layers: int):
+        super(MappingNetwork, self).__init__()
+        self.net = nn.Sequential(*_fc_bn_act(planes, n_layers))
+
+    def forward(self, z: torch.Tensor):
+        return self.net(z)
+
+
+class Conv2dWeightModulate(nn.Module):
+    """reference :219-248, in shared-weight form (see module docstring)."""
+
+    def __init__(self, d_latent: int, in_planes: int, out_planes: int, kernel_size: int, demodulate: bool = True,
+                 eps: float = 1e-8):
+        super(Conv2dWeightModulate, self).__init__()
+        self.to_style = nn.Sequential(
+            MappingNetwork(d_latent, 1),
+            EqualizedLinear(d_latent, in_planes),
+            L.BatchNorm1d(in_planes)
+        )
+        self.out_planes = out_planes
+        self.demodulate = demodulate
+        self.padding = (kernel_size - 1) // 2
+        self.pad = nn.ReplicationPad2d(self.padding)
+        self.weight = EqualizedWeight([out_planes, in_planes, kernel_size, kernel_size])
+        self.eps = eps
+
+    def forward(self, x: torch.Tensor, s: torch.Tensor):
+        style = self.to_style(s)
+        return ops.modulated_conv2d(x, self.weight.raw, style, self.padding, self.weight.gain, self.demodulate,
+                                    self.eps)
+
+
+class StyleConv(nn.Module):
+    """reference :251-266 — modulated conv, the dead bias, optional per-channel-scaled N(0,1) noise."""
+
+    def __init__(self, d_latent: int, in_planes: int, out_planes: int, kernel_size: int, use_noise: bool = False):
+        super(StyleConv, self).__init__()
+        self.conv = Conv2dWeightModulate(d_latent, in_planes, out_planes, kernel_size=kernel_size)
+        self.use_noise = use_noise
+        if use_noise:
+            self.scale_noise = nn.Parameter(torch.nn.init.uniform_(torch.empty(out_planes), a=0.2, b=0.3))
+        self.bias = nn.Parameter(L.normal_(out_planes))
+
+    def forward(self, x: torch.Tensor, w: torch.Tensor):
+        y = self.conv(x, w)
+        if self.use_noise:
+            # the draw stays a torch.randn call of the same shape on the same generator as in the reference
+            # (SURVEY F9): identical seeds give identical noise.
+            y = ops.noise_add(y, self.scale_noise, torch.randn(*y.shape, device=y.device))
+        return y
+
+
+class SKStyleConv(nn.Module):
+    """reference :269-295"""
+
+    def __init__(self, d_latent: int, in_planes: int, out_planes: int, m: int, image_size: int, use_noise: bool):
+        super(SKStyleConv, self).__init__()
+        assert (m > 0)
+        self.M = m
+        for i in range(m):
+            self.__setattr__('conv_%d' % i,
+                             StyleConv(d_latent, in_planes, out_planes, kernel_size=3 + i * 2, use_noise=use_noise))
+            self.__setattr__('nonlinear_%d' % i, L.PReLU(out_planes))
+        self.sk_attention = _pick_sk_attention(out_planes, m, image_size)
+
+    def forward(self, x: torch.Tensor, w: torch.Tensor):
+        branches = [self.__getattr__('nonlinear_%d' % i)(self.__getattr__('conv_%d' % i)(x, w))
+                    for i in range(self.M)]
+        return L.sk_merge(branches, self.sk_attention(branches))
+
+
+class StyleBlock(nn.Module):
+    """reference :298-322 — 1x1 modconv, PReLU, (kxk modconv+noise | SK of k3,k5), 3x3 modconv."""
+
+    def __init__(self, d_latent: int, last_planes: int, in_planes: int, out_planes: int, dense_depth: int,
+                 kernel_size: int, m: int, image_size: int):
+        super(StyleBlock, self).__init__()
+        assert (m > 0)
+        self.conv1 = StyleConv(d_latent, last_planes, in_planes, kernel_size=1)
+        self.activation1 = L.PReLU(in_planes)
+        self.m = m
+        if m == 1:
+            self.conv2 = StyleConv(d_latent, in_planes, in_planes, kernel_size, True)
+            self.activation2 = L.PReLU(in_planes)
+        else:
+            self.skconv = SKStyleConv(d_latent, in_planes, in_planes, m, image_size, True)
+        self.conv3 = StyleConv(d_latent, in_planes, out_planes + dense_depth, kernel_size=3)
+
+    def forward(self, x: torch.Tensor, w: torch.Tensor):
+        t = self.activation1(self.conv1(x, w))
+        t = self.activation2(self.conv2(t, w)) if self.m == 1 else self.skconv(t, w)
+        return self.conv3(t, w)
+
+
+class ResnetInit(nn.Module):
+    """reference :325-349 — residual / transient streams with the two cross paths."""
+
+    def __init__(self, d_latent: int, last_planes: int, in_planes: int, out_planes: int, dense_depth: int,
+                 kernel_size: int, m: int, image_size: int):
+        super(ResnetInit, self).__init__()
+        a = (d_latent, last_planes, in_planes, out_planes)
+        b = (kernel_size, m, image_size)
+        self.residual = StyleBlock(*a, dense_depth, *b)
+        self.transient = StyleBlock(*a, 0, *b)
+        self.residual_across = StyleBlock(*a, 0, *b)
+        self.transient_across = StyleBlock(*a, dense_depth, *b)
+        self.activation_residual = L.PReLU(out_planes + dense_depth)
+        self.activation_transient = L.PReLU(out_planes)
+
+    def forward(self, x: Tuple[torch.Tensor, torch.Tensor], w: torch.Tensor):
+        x_res, x_tra = x
+        r_r = self.residual(x_res, w)
+        r_t = self.residual_across(x_res, w)
+        t_t = self.transient(x_tra, w)
+        t_r = self.transient_across(x_tra, w)
+        return self.activation_residual(ops.add(r_r, t_r)), self.activation_transient(ops.add(r_t, t_t))
+
+
+class SEBlock_conv(nn.Module):
+    """reference :352-382 — like SK's trunk, ending in fc -> BN1d -> sigmoid gate."""
+
+    def __init__(self, in_planes: int):
+        super(SEBlock_conv, self).__init__()
+        self.gap_conv = L.AdaptiveAvgPool2d(5)
+        self.convs = nn.Sequential(*_conv_bn_act(in_planes, 2))
+        self.gap_fc = L.AdaptiveAvgPool2d(1)
+        self.fcs = nn.Sequential(*_fc_bn_act(in_planes, 1))
+        self.fc_out = EqualizedLinear(in_planes, in_planes)
+        self.fc_bn = L.BatchNorm1d(in_planes)
+        self.activation2 = L.Sigmoid()
+
+    def forward(self, x: torch.Tensor):
+        b, c, _, side = x.shape
+        assert (side >= 8)
+        t = self.gap_fc(self.convs(self.gap_conv(x))).view(b, c)
+        t = self.fc_bn(self.fc_out(self.fcs(t)))
+        return self.activation2(t).view(b, c, 1, 1)
+
+
+class SEBlock_fc(nn.Module):
+    """reference :385-405"""
+
+    def __init__(self, in_planes: int):
+        super(SEBlock_fc, self).__init__()
+        self.gap = L.AdaptiveAvgPool2d(1)
+        self.fcs = nn.Sequential(*_fc_bn_act(in_planes, 2))
+        self.fc_out = EqualizedLinear(in_planes, in_planes)
+        self.fc_bn = L.BatchNorm1d(in_planes)
+        self.activation2 = L.Sigmoid()
+
+    def forward(self, x: torch.Tensor):
+        b, c = x.shape[:2]
+        t = self.fc_bn(self.fc_out(self.fcs(self.gap(x).view(b, c))))
+        return self.activation2(t).view(b, c, 1, 1)
+
+
+class BasicBlock(nn.Module):
+    """reference :408-467.  Channel layout of a block's input/output: [residual d | transient d | dense ...]."""
+
+    def get_out_planes(self):
+        if self.is_unify or self.root:
+            return 2 * self.out_planes + 2 * self.dense_depth
+        return self.last_planes + 1 * self.dense_depth
+
+    def __init__(self, d_latent: int, last_planes: int, in_planes: int, out_planes: int, dense_depth: int, root: bool,
+                 is_unify: bool, m: int, image_size: int):
+        super(BasicBlock, self).__init__()
+        self.root = root
+        self.last_planes = last_planes
+        self.out_planes = out_planes
+        self.dense_depth = dense_depth
+        self.is_unify = is_unify
+        if is_unify:
+            self.unify = StyleBlock(d_latent, last_planes, in_planes, 2 * out_planes, dense_depth, 3, m, image_size)
+            self.activation_unify = L.PReLU(2 * out_planes + dense_depth)
+            rir_in = out_planes + dense_depth
+        else:
+            rir_in = last_planes - out_planes
+        self.rir_3 = ResnetInit(d_latent, rir_in, in_planes, out_planes, dense_depth, 3, m, image_size)
+        if root:
+            self.shortcut = StyleBlock(d_latent, last_planes, in_planes, 0, dense_depth, 3, m, image_size)
+            self.activation_shortcut = L.PReLU(dense_depth)
+        self.se_attention_residual = SEBlock_conv(out_planes) if image_size > 4 else SEBlock_fc(out_planes)
+
+    def forward(self, x: torch.Tensor, w: torch.Tensor):
+        d = self.out_planes
+        if self.is_unify:
+            x = self.activation_unify(self.unify(x, w))
+        head = ops.slice_channels(x, 0, d)
+        dense = ops.slice_channels(x, 2 * d)
+        x_res = ops.cat_channels([head, dense])
+        x_tra = ops.slice_channels(x, d)
+        res3, tra3 = self.rir_3((x_res, x_tra), w)
+        res3_head = ops.slice_channels(res3, 0, d)
+        feas_residual = ops.add(head, L.gate(res3_head, self.se_attention_residual(res3_head)))
+        if self.root:
+            mid = self.activation_shortcut(self.shortcut(x, w))
+        else:
+            mid = dense
+        return ops.cat_channels([feas_residual, tra3, mid, ops.slice_channels(res3, d)])
+
+
+class ToRGB(nn.Module):
+    """reference :470-493"""
+
+    def __init__(self, planes: int, m: int, image_size: int):
+        super().__init__()
+        assert (m > 0)
+        self.m = m
+        if m == 1:
+            self.pre_conv = EqualizedConv2d(planes, planes, 3)
+            self.pre_bn = L.BatchNorm2d(planes)
+            self.pre_activation = L.PReLU(planes)
+        else:
+            self.skconv = SKConv(planes, planes, m, image_size)
+        self.conv = EqualizedConv2d(planes, 3, kernel_size=5)
+        self.bn = L.BatchNorm2d(3)
+
+    def forward(self, x: torch.Tensor):
+        t = self.pre_activation(self.pre_bn(self.pre_conv(x))) if self.m == 1 else self.skconv(x)
+        return self.bn(self.conv(t))
+
+
+class Tree(nn.Module):
+    """reference :496-564 — DLA-style aggregation tree.  `level_i` sub-trees, `block_i` leaves, a `root` block
+    on the concatenation of everything, and a ToRGB skip accumulated into `rgb`."""
+
+    def get_out_planes(self):
+        return self.root.get_out_planes()
+
+    def __init__(self, d_latent: int, last_planes: int, in_planes: int, out_planes: int, dense_depth: int, level: int,
+                 block_num: int, m: int, image_size: int):
+        super(Tree, self).__init__()
+        assert (block_num > 0)
+        self.level = level
+        self.block_num = block_num
+        self.out_planes = out_planes
+        self.dense_depth = dense_depth
+
+        def leaf(last, unify):
+            return BasicBlock(d_latent, last, in_planes, out_planes, dense_depth, False, unify, m, image_size)
+
+        width = 2 * out_planes * (block_num - 1)
+        first_leaf = 0
+        if level == 1:
+            blk = leaf(last_planes, last_planes < 2 * out_planes)
+            last_planes = blk.get_out_planes()
+            self.__setattr__('block_%d' % 0, blk)
+            first_leaf = 1
+        else:
+            self.prev_root = leaf(last_planes, last_planes < 2 * out_planes)
+            width += self.prev_root.get_out_planes()
+            for i in reversed(range(1, level)):
+                sub = Tree(d_latent, last_planes, in_planes, out_planes, dense_depth, i, block_num, m, image_size)
+                last_planes = sub.get_out_planes()
+                width += last_planes
+                self.__setattr__('level_%d' % i, sub)
+        for i in range(first_leaf, block_num):
+            blk = leaf(last_planes, False)
+            last_planes = blk.get_out_planes()
+            self.__setattr__('block_%d' % i, blk)
+        width += blk.get_out_planes()
+        self.root_last_planes = width
+        self.root = BasicBlock(d_latent, width, in_planes * block_num, out_planes, dense_depth, True, False, m,
+                               image_size)
+        self.to_rgb = ToRGB(self.get_out_planes(), m, image_size)
+
+    def forward(self, x: torch.Tensor, w: torch.Tensor, rgb: torch.Tensor):
+        d = self.out_planes
+        parts = [self.prev_root(x, w)] if self.level > 1 else []
+        for i in reversed(range(1, self.level)):
+            x, rgb = self.__getattr__('level_%d' % i)(x, w, rgb)
+            parts.append(x)
+        for i in range(self.block_num):
+            x = self.__getattr__('block_%d' % i)(x, w)
+            parts.append(ops.slice_channels(x, 0, 2 * d))
+        parts.append(ops.slice_channels(x, 2 * d))
+        out = self.root(ops.cat_channels(parts), w)
+        return out, ops.add(self.to_rgb(out), rgb)
+
+
+class GeneratorBlock(nn.Module):
+    """reference :567-583 — x2 both streams, then a tree."""
+
+    def get_out_planes(self):
+        return self.tree.get_out_planes()
+
+    def __init__(self, d_latent: int, last_planes: int, in_planes: int, out_planes: int, dense_depth: int, level: int,
+                 block_num: int, m: int, image_size: int):
+        super(GeneratorBlock, self).__init__()
+        self.upsample = SKConvT(last_planes)
+        self.tree = Tree(d_latent, last_planes, in_planes, out_planes, dense_depth, level, block_num, m, image_size)
+        self.upsample_rgb = SKConvT(3)
+
+    def forward(self, x: torch.Tensor, w: torch.Tensor, rgb: torch.Tensor):
+        rgb = self.upsample_rgb(rgb)
+        return self.tree(self.upsample(x), w, rgb)
+
+
+class GeneratorStart(nn.Module):
+    """reference :586-607 — mapping network z->w, ConvT z->4x4, first ToRGB and tree."""
+
+    def get_out_planes(self):
+        return self.tree.get_out_planes()
+
+    def __init__(self, z_dim: int, mapping_layer: int, in_planes: int, out_planes: int, dense_depth: int, level: int,
+                 block_num: int, m: int):
+        super(GeneratorStart, self).__init__()
+        self.mapping_network = MappingNetwork(z_dim, mapping_layer)
+        self.convT = L.ConvTranspose2d(z_dim, out_planes, kernel_size=4, stride=1, padding=0)
+        self.bn = L.BatchNorm2d(out_planes)
+        self.activation = L.PReLU(out_planes)
+        self.to_rgb = ToRGB(out_planes, m, 4)
+        self.tree = Tree(z_dim, out_planes, in_planes, out_planes // 2, dense_depth, level, block_num, m, 4)
+
+    def forward(self, x: torch.Tensor):
+        w = self.mapping_network(torch.squeeze(x))  # all singleton dims, as the reference (B=1 fails)
+        x = self.activation(self.bn(self.convT(x)))
+        rgb = self.to_rgb(x)
+        x, rgb = self.tree(x, w, rgb)
+        return x, w, rgb
+
+
+class Generator(nn.Module):
+    """reference :610-631"""
+
+    def __init__(self, z_dim, planes=48):
+        super(Generator, self).__init__()
+        dd = planes // 8
+        self.block0 = GeneratorStart(z_dim, 12, planes * 8, planes * 8, dd, 1, 2, 1)
+        last = self.block0.get_out_planes()
+        for idx, (mult, size) in enumerate([(4, 8), (2, 16), (1, 32), (1, 64)], start=1):
+            blk = GeneratorBlock(z_dim, last, planes * mult, planes * mult, dd, 2, 2, 2, size)
+            last = blk.get_out_planes()
+            self.__setattr__('block%d' % idx, blk)
+
+    def forward(self, x: torch.Tensor):
+        x, w, rgb = self.block0(x)
+        for idx in range(1, 5):
+            x, rgb = self.__getattr__('block%d' % idx)(x, w, rgb)
+        return rgb

@@ -140,6 +140,7 @@ int ganb200_masked_dot(const float* u, const float* v, const float* x, float* ou
 int ganb200_bn_stats(const float* x, float* mean, float* var_biased, int N, int C, int HW, void* stream);
 int ganb200_bn_apply(const float* x, const float* mean, const float* var_biased, const float* gamma, const float* beta,
                      float* y, float* save_invstd, float* running_mean, float* running_var,
+                     int64_t* num_batches_tracked /* += 1 when non-NULL */,
                      int N, int C, int HW, float eps, float momentum, int64_t count_total, void* stream);
 /* gx, ggamma, gbeta from (gy, x, mean, invstd, gamma).  If reduce_ws != NULL (2*C floats, holding
  * already-reduced sum(gy) and sum(gy*xhat)) the reduction phase is skipped (sync-BN). */
@@ -174,11 +175,20 @@ typedef struct {
   float* p; const float* g; float* m; float* v; int64_t n;
 } ganb200_adam_entry;
 /* block_tab: DEVICE array of n_blocks (tensor index, chunk index) int32 pairs; each CTA updates elements
- * [chunk_idx*chunk, min(n, (chunk_idx+1)*chunk)) of its tensor.  step is the 1-based Adam step count. */
+ * [chunk_idx*chunk, min(n, (chunk_idx+1)*chunk)) of its tensor.  step is the 1-based Adam step count; when
+ * step_dev != NULL the count is read from that DEVICE int64 instead (so a captured CUDA graph can be replayed:
+ * bump it with ganb200_counter_add before the update). */
 int ganb200_multi_tensor_adam_blocks(const ganb200_adam_entry* tab, const int32_t* block_tab, int n_blocks,
                                      int64_t chunk, float lr, float beta1, float beta2, float eps,
-                                     float weight_decay, int decoupled, int64_t step, float grad_scale,
-                                     void* stream);
+                                     float weight_decay, int decoupled, int64_t step, const int64_t* step_dev,
+                                     float grad_scale, void* stream);
+int ganb200_counter_add(int64_t* counter, int64_t inc, void* stream);
+
+/* Channel-slice copy on [N,C,HW] tensors: dst[:, dst_c0:dst_c0+ncopy] (+)= src[:, src_c0:src_c0+ncopy].
+ * Replaces torch.cat(dim=1) / channel slicing and their adjoints (generator_13_5.py:451-467,549-560,
+ * discriminator_9_4.py:54). */
+int ganb200_chan_copy(const float* src, float* dst, int N, int src_C, int src_c0, int dst_C, int dst_c0,
+                      int ncopy, int HW, int accumulate, void* stream);
 
 /* units/mixup.py:9-17 and :19-27 (with its (B,1)x(B,3,64,64) float64 broadcast) */
 int ganb200_mixup(const float* t, const float* f, float lam, float* out, int64_t n, void* stream);

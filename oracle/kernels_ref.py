@@ -160,7 +160,9 @@ class RefBackend:
         var = ((x - self._cview(x, mean)) ** 2).mean(dims)
         return mean, var
 
-    def bn_apply(self, x, mean, var, gamma, beta, running_mean, running_var, eps, momentum, count_total):
+    def bn_apply(self, x, mean, var, gamma, beta, running_mean, running_var, eps, momentum, count_total, nbt=None):
+        if nbt is not None:
+            nbt += 1
         invstd = torch.rsqrt(var + eps)
         y = (x - self._cview(x, mean)) * self._cview(x, invstd)
         if gamma is not None:
@@ -225,6 +227,16 @@ class RefBackend:
         return g.reshape(()) / p.numel() * (p - t) / torch.clamp((1 - p) * p, min=1e-12)
 
     # ---- misc ------------------------------------------------------------------------------------------------
+    def chan_copy(self, src, src_c0, dst, dst_c0, ncopy, accumulate=False):
+        if accumulate:
+            dst[:, dst_c0:dst_c0 + ncopy] += src[:, src_c0:src_c0 + ncopy]
+        else:
+            dst[:, dst_c0:dst_c0 + ncopy] = src[:, src_c0:src_c0 + ncopy]
+        return dst
+
+    def counter_add(self, ctr, inc):
+        ctr += inc
+
     def mixup(self, t, f, lam):
         return lam * t + (1 - lam) * f
 
