@@ -227,3 +227,15 @@ def gate(x, g):
     """x * g with g:(b,c,1,1) — the SE product (discriminator_9_4.py:160, generator_13_5.py:457)."""
     b, c = x.shape[:2]
     return ops.mul_bc(x, g.reshape(b, c), KN.V_NC)
+
+
+class BCELoss(nn.BCELoss):
+    """torch.nn.BCELoss(mean) — train/gan.py:21, ganR2.py:17.  Raises the reference's RuntimeError when an input
+    lies outside [0,1] (D9_4 emits raw logits)."""
+
+    def forward(self, input, target):
+        assert self.weight is None and self.reduction == "mean"
+        if input.shape != target.shape:
+            raise ValueError(f"Using a target size ({target.size()}) that is different to the input size "
+                             f"({input.size()}) is deprecated. Please ensure they have the same size.")
+        return ops.bce_loss(input, target)

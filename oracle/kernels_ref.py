@@ -237,6 +237,9 @@ class RefBackend:
     def counter_add(self, ctr, inc):
         ctr += inc
 
+    def adam_reference(self, *a, **k):
+        return adam_reference(*a, **k)
+
     def mixup(self, t, f, lam):
         return lam * t + (1 - lam) * f
 
