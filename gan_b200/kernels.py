@@ -31,6 +31,24 @@ def default_engine():
 LAUNCH_COUNT = [0]  # number of libganb200 kernel-launching calls (bench.py reports it as gpu_launches)
 
 
+class ConvTimer:
+    """bench.py: CUDA events around every convolution-engine call on the launching stream.  Off by default."""
+
+    def __init__(self):
+        self.records = []  # (engine "tc"|"simt", flops, start_event, end_event)
+
+    def totals(self):
+        """-> {engine: (flops, seconds, calls)}; call after a device synchronize."""
+        out = {}
+        for eng, fl, e0, e1 in self.records:
+            f, t, n = out.get(eng, (0.0, 0.0, 0))
+            out[eng] = (f + fl, t + e0.elapsed_time(e1) * 1e-3, n + 1)
+        return out
+
+
+CONV_TIMER = None
+
+
 def _nchw(t):
     """logical [N, C, HW] of a >=1-D tensor."""
     if t.dim() == 1:
@@ -85,6 +103,19 @@ class CudaBackend:
         return torch.empty(nbytes, dtype=torch.uint8, device=device)
 
     # -- convolution family ---------------------------------------------------------------------
+    def _t0(self, d, op):
+        if CONV_TIMER is None:
+            return None
+        tc = d.engine != 1 and self.lib.ganb200_conv2d_tc_eligible(ctypes.byref(d), op) == 1
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        return ("tc" if tc else "simt", 2.0 * d.N * d.K * d.P * d.Q * d.C * d.R * d.S, e0, e1)
+
+    def _t1(self, tm):
+        if tm is not None:
+            tm[3].record()
+            CONV_TIMER.records.append(tm)
+
     def _desc(self, N, C, H, W, K, R, S, stride, pad, pad_mode, alpha, engine):
         P, Q = out_hw(H, W, R, S, stride, pad)
         return ConvDesc(N, C, H, W, K, R, S, stride, pad, pad_mode, P, Q, float(alpha),
@@ -99,8 +130,10 @@ class CudaBackend:
         y = torch.empty((N, K, d.P, d.Q), dtype=torch.float32, device=x.device)
         nb = self.lib.ganb200_conv2d_workspace_bytes(ctypes.byref(d), FPROP)
         ws = self._workspace(nb, x.device)
+        tm = self._t0(d, FPROP)
         _lib.check(self.lib.ganb200_conv2d_fprop(ctypes.byref(d), self._p(x), self._p(w), self._p(bias),
                                                  self._p(iscale), self._p(oscale), self._p(y), self._p(ws), nb, st))
+        self._t1(tm)
         return y
 
     def conv_dgrad(self, dy, w, in_hw, stride, pad, pad_mode, alpha, iscale=None, oscale=None, engine=None):
@@ -114,8 +147,10 @@ class CudaBackend:
         dx = torch.empty((N, C, H, W), dtype=torch.float32, device=dy.device)
         nb = self.lib.ganb200_conv2d_workspace_bytes(ctypes.byref(d), DGRAD)
         ws = self._workspace(nb, dy.device)
+        tm = self._t0(d, DGRAD)
         _lib.check(self.lib.ganb200_conv2d_dgrad(ctypes.byref(d), self._p(dy), self._p(w), self._p(iscale),
                                                  self._p(oscale), self._p(dx), self._p(ws), nb, st))
+        self._t1(tm)
         return dx
 
     def conv_wgrad(self, x, dy, rs, stride, pad, pad_mode, alpha, iscale=None, oscale=None, engine=None):
@@ -128,8 +163,10 @@ class CudaBackend:
         dw = torch.empty((K, C, R, S), dtype=torch.float32, device=x.device)
         nb = self.lib.ganb200_conv2d_workspace_bytes(ctypes.byref(d), WGRAD)
         ws = self._workspace(nb, x.device)
+        tm = self._t0(d, WGRAD)
         _lib.check(self.lib.ganb200_conv2d_wgrad(ctypes.byref(d), self._p(x), self._p(dy), self._p(iscale),
                                                  self._p(oscale), self._p(dw), self._p(ws), nb, st))
+        self._t1(tm)
         return dw
 
     # -- resampling -----------------------------------------------------------------------------

@@ -575,10 +575,15 @@ class MbStdBwdFn(Function):
         return out_gg, out_gx, None, None
 
 
+_mbstd_reduce = [None]
+
+
 def minibatch_stddev(x, group_size=4, eps=1e-8):
     """returns cat([x, std.expand(b,1,h,w)], 1)"""
     b, _, h, w = x.shape
     s = MbStdFn.apply(x, group_size, eps)
+    if _mbstd_reduce[0] is not None:  # data parallel: mean of the rank-local scalars (gan_b200.dist)
+        s = _mbstd_reduce[0](s)
     plane = AddBcFn.apply(torch.zeros((b, 1, h, w), dtype=x.dtype, device=x.device), s, KN.V_SCALAR)
     return torch.cat([x, plane], dim=1)
 
@@ -642,8 +647,13 @@ class BatchNormTrainFn(Function):
         gy = _c(gy)
         s1, s2 = K().bn_bwd_reduce(gy, x, mean, invstd)
         if _sync_bn_hooks["grads"] is not None:
-            s1, s2 = _sync_bn_hooks["grads"](s1, s2)
-        gx, gg, gb = K().bn_bwd_apply(gy, x, mean, invstd, gamma, s1, s2, ctx.count)
+            # data parallel: dx needs the sums over the global batch; dgamma/dbeta stay rank-local partial sums
+            # (they are parameter gradients and get summed over ranks with all the others)
+            g1, g2 = _sync_bn_hooks["grads"](s1, s2)
+            gx, _, _ = K().bn_bwd_apply(gy, x, mean, invstd, gamma, g1, g2, ctx.count)
+            gg, gb = s2, s1
+        else:
+            gx, gg, gb = K().bn_bwd_apply(gy, x, mean, invstd, gamma, s1, s2, ctx.count)
         return (gx, (gg if gamma is not None else None), (gb if ctx.needs_input_grad[2] else None), None, None, None,
                 None, None)
 

@@ -28,6 +28,7 @@ class FusedAdam(torch.optim.Optimizer):
         self.capturable = capturable
         self._cache = {}
         self._step_dev = {}
+        self.pre_step = None  # data parallel: gradient all-reduce (gan_b200.dist.GradSync)
 
     # -- table ----------------------------------------------------------------------------------------
     def _table(self, key, entries, device):
@@ -61,6 +62,8 @@ class FusedAdam(torch.optim.Optimizer):
             with torch.enable_grad():
                 loss = closure()
         k = KN.backend()
+        if self.pre_step is not None:
+            self.pre_step()
         for gi, group in enumerate(self.param_groups):
             b1, b2 = group["betas"]
             by_step = {}

@@ -1,0 +1,258 @@
+"""GPU parity: every libganb200 kernel, called through the C-ABI (ctypes), against the oracle
+(oracle/kernels_ref.py — the CPU restatement in stock torch ops) on the same seeded inputs.
+
+Tolerances (BASELINE.json north_star): rel. L2 <= 1e-5 for fp32 paths, <= 1e-2 for the bf16 tcgen05 engine.
+"""
+import ctypes
+
+import pytest
+import torch
+
+from gan_b200 import kernels as KN
+from gan_b200 import resample as RS
+
+pytestmark = pytest.mark.gpu
+
+FP32_TOL = 1e-5
+BF16_TOL = 1e-2
+
+
+@pytest.fixture(scope="module")
+def cu():
+    assert torch.cuda.is_available()
+    return KN.CudaBackend()
+
+
+@pytest.fixture(scope="module")
+def ref():
+    from oracle.kernels_ref import RefBackend
+    return RefBackend()
+
+
+def rel(a, b):
+    a, b = a.detach().cpu().double(), b.detach().cpu().double()
+    den = b.norm().item()
+    return (a - b).norm().item() / (den if den > 0 else 1.0)
+
+
+def g(t):
+    return None if t is None else t.cuda()
+
+
+def rnd(*shape):
+    return torch.randn(*shape)
+
+
+CONV_CASES = [
+    # N, C, H, W, K, R, stride, pad, pad_mode
+    (4, 3, 16, 16, 64, 3, 1, 1, 1),      # stem
+    (4, 64, 16, 16, 64, 3, 1, 1, 1),     # same-width 3x3
+    (2, 64, 16, 16, 128, 3, 1, 1, 1),    # C -> 2C
+    (2, 128, 18, 18, 128, 3, 2, 1, 1),   # stride-2 down conv
+    (8, 1025, 4, 4, 1025, 3, 1, 1, 1),   # odd channel count
+    (4, 64, 5, 5, 64, 3, 1, 0, 0),       # SE conv, pad 0
+    (4, 48, 16, 16, 54, 5, 1, 2, 1),     # k5 modconv shape
+    (4, 390, 8, 8, 96, 1, 1, 0, 1),      # 1x1 on wide concat
+    (3, 7, 9, 11, 5, 3, 1, 1, 0),        # ragged, zero pad
+    (4, 256, 1, 1, 4100, 1, 1, 0, 0),    # linear
+]
+
+
+@pytest.mark.parametrize("case", CONV_CASES)
+@pytest.mark.parametrize("scales", [False, True])
+def test_conv_family_fp32(cu, ref, case, scales):
+    N, C, H, W, K, R, stride, pad, pm = case
+    torch.manual_seed(1)
+    x, w, b = rnd(N, C, H, W), rnd(K, C, R, R), rnd(K)
+    isc = torch.rand(N, C) + 0.5 if scales else None
+    osc = torch.rand(N, K) + 0.5 if scales else None
+    y_ref = ref.conv_fprop(x, w, b, stride, pad, pm, 0.1, isc, osc)
+    y = cu.conv_fprop(g(x), g(w), g(b), stride, pad, pm, 0.1, g(isc), g(osc), engine=1)
+    assert rel(y, y_ref) < FP32_TOL
+    dy = rnd(*y_ref.shape)
+    dx_ref = ref.conv_dgrad(dy, w, (H, W), stride, pad, pm, 0.1, isc, osc)
+    dx = cu.conv_dgrad(g(dy), g(w), (H, W), stride, pad, pm, 0.1, g(isc), g(osc), engine=1)
+    assert rel(dx, dx_ref) < FP32_TOL
+    dw_ref = ref.conv_wgrad(x, dy, (R, R), stride, pad, pm, 0.1, isc, osc)
+    dw = cu.conv_wgrad(g(x), g(dy), (R, R), stride, pad, pm, 0.1, g(isc), g(osc), engine=1)
+    assert rel(dw, dw_ref) < FP32_TOL
+
+
+@pytest.mark.parametrize("case", CONV_CASES)
+@pytest.mark.parametrize("scales", [False, True])
+def test_conv_family_tcgen05(cu, ref, case, scales):
+    """bf16 operands, fp32 accumulate in TMEM; only the (shape, op) pairs the engine declares eligible."""
+    N, C, H, W, K, R, stride, pad, pm = case
+    torch.manual_seed(2)
+    x, w, b = rnd(N, C, H, W), rnd(K, C, R, R), rnd(K)
+    isc = torch.rand(N, C) + 0.5 if scales else None
+    osc = torch.rand(N, K) + 0.5 if scales else None
+    P, Q = KN.out_hw(H, W, R, R, stride, pad)
+    d = KN.ConvDesc(N, C, H, W, K, R, R, stride, pad, pm, P, Q, 0.1, 0)
+    dy = rnd(N, K, P, Q)
+    ran = 0
+    if cu.lib.ganb200_conv2d_tc_eligible(ctypes.byref(d), KN.FPROP):
+        y = cu.conv_fprop(g(x), g(w), g(b), stride, pad, pm, 0.1, g(isc), g(osc), engine=2)
+        assert rel(y, ref.conv_fprop(x, w, b, stride, pad, pm, 0.1, isc, osc)) < BF16_TOL
+        ran += 1
+    if cu.lib.ganb200_conv2d_tc_eligible(ctypes.byref(d), KN.DGRAD):
+        dx = cu.conv_dgrad(g(dy), g(w), (H, W), stride, pad, pm, 0.1, g(isc), g(osc), engine=2)
+        assert rel(dx, ref.conv_dgrad(dy, w, (H, W), stride, pad, pm, 0.1, isc, osc)) < BF16_TOL
+        ran += 1
+    if cu.lib.ganb200_conv2d_tc_eligible(ctypes.byref(d), KN.WGRAD):
+        dw = cu.conv_wgrad(g(x), g(dy), (R, R), stride, pad, pm, 0.1, g(isc), g(osc), engine=2)
+        assert rel(dw, ref.conv_wgrad(x, dy, (R, R), stride, pad, pm, 0.1, isc, osc)) < BF16_TOL
+        ran += 1
+    if ran == 0:
+        pytest.skip("shape not eligible for the tcgen05 engine")
+
+
+def test_tcgen05_engine_covers_the_dominant_shapes(cu):
+    """The same-width 3x3 stride-1 convs of D9_4 (66 % of its FLOPs) must be tensor-core eligible."""
+    for (N, C, HW) in [(8, 64, 64), (8, 128, 32), (8, 256, 16), (8, 512, 8), (8, 1025, 4)]:
+        d = KN.ConvDesc(N, C, HW, HW, C, 3, 3, 1, 1, 1, HW, HW, 1.0, 0)
+        assert cu.lib.ganb200_conv2d_tc_eligible(ctypes.byref(d), KN.FPROP) == 1, (N, C, HW)
+
+
+@pytest.mark.parametrize("n", [64, 32, 5, 4])
+def test_resample_ops(cu, ref, n):
+    torch.manual_seed(3)
+    x = rnd(3, 5, n, n)
+    ops = [RS.smooth3(n), RS.adaptive_avg(n, 5) if n >= 5 else RS.identity(n), RS.replicate_pad(n, 2)]
+    if n % 2 == 0:
+        ops += [RS.smooth_then_bicubic_down2(n), RS.bicubic(n, 2 * n, 0.5), RS.bicubic_up2_then_smooth(n)]
+    for op in ops:
+        for o in (op, op.T):
+            xi = rnd(3, 5, o.n_in, o.n_in)
+            assert rel(cu.resample2d(g(xi), o, o), ref.resample2d(xi, o, o)) < FP32_TOL, o.name
+    del x
+
+
+def test_pointwise(cu, ref):
+    torch.manual_seed(4)
+    x = rnd(6, 10, 7, 9)
+    xp = x.abs() + 0.1
+    for op, inp, p0, p1 in [(KN.U_SIGMOID, x, 0, 0), (KN.U_TANH, x, 0, 0), (KN.U_SQUARE, x, 0, 0),
+                            (KN.U_AFFINE, x, 1.7, -0.3), (KN.U_RSQRT_EPS, xp, 1e-8, 0), (KN.U_SQRT, xp, 0, 0),
+                            (KN.U_LEAKY, x, 0.2, 0), (KN.U_RECIP, xp, 0, 0), (KN.U_LEAKY_MASK, x, 0.1, 0),
+                            (KN.U_COPY, x, 0, 0), (KN.U_POW, xp, 1.5, 0)]:
+        assert rel(cu.ew_unary(op, g(inp), p0, p1), ref.ew_unary(op, inp, p0, p1)) < FP32_TOL, op
+    a, b = rnd(6, 10, 7, 9), torch.rand(6, 10, 7, 9) * 0.8 + 0.1
+    for op, p0 in [(KN.B_ADD, 0), (KN.B_SUB, 0), (KN.B_MUL, 0), (KN.B_DIV, 0), (KN.B_SIGMOID_BWD, 0),
+                   (KN.B_TANH_BWD, 0), (KN.B_LEAKY_BWD, 0.2)]:
+        bb = b if op != KN.B_LEAKY_BWD else x
+        assert rel(cu.ew_binary(op, g(a), g(bb), p0), ref.ew_binary(op, a, bb, p0)) < FP32_TOL, op
+    N, C = 6, 10
+    for vmode, v in [(KN.V_NC, rnd(N, C)), (KN.V_C, rnd(C)), (KN.V_N, rnd(N)), (KN.V_SCALAR, rnd(1))]:
+        for op in (KN.B_ADD, KN.B_MUL):
+            assert rel(cu.ew_bcast(op, g(x), g(v), vmode), ref.ew_bcast(op, x, v, vmode)) < FP32_TOL
+        assert rel(cu.ew_fma_bcast(g(x), g(v), g(a), vmode), ref.ew_fma_bcast(x, v, a, vmode)) < FP32_TOL
+    for rmode in (KN.R_HW, KN.R_NHW, KN.R_CHW, KN.R_ALL):
+        for y in (None, a):
+            assert rel(cu.reduce(g(x), g(y), rmode, 0.5), ref.reduce(x, y, rmode, 0.5)) < FP32_TOL
+    big = rnd(16, 3, 64, 64)
+    assert rel(cu.reduce(g(big), g(big), KN.R_CHW, 1.0), ref.reduce(big, big, KN.R_CHW, 1.0)) < FP32_TOL
+
+
+@pytest.mark.parametrize("an", [1, 12])
+def test_prelu_family(cu, ref, an):
+    torch.manual_seed(5)
+    x, gy, u = rnd(5, 12, 6, 6), rnd(5, 12, 6, 6), rnd(5, 12, 6, 6)
+    a = torch.rand(an) * 0.5
+    assert rel(cu.prelu_fwd(g(x), g(a)), ref.prelu_fwd(x, a)) < FP32_TOL
+    assert rel(cu.maskscale(g(gy), g(x), g(a)), ref.maskscale(gy, x, a)) < FP32_TOL
+    gx, ga = cu.prelu_bwd(g(gy), g(x), g(a))
+    gx_r, ga_r = ref.prelu_bwd(gy, x, a)
+    assert rel(gx, gx_r) < FP32_TOL and rel(ga, ga_r) < FP32_TOL
+    assert rel(cu.masked_dot(g(u), g(gy), g(x), an), ref.masked_dot(u, gy, x, an)) < FP32_TOL
+
+
+@pytest.mark.parametrize("shape", [(16, 20, 8, 8), (32, 256), (8, 3, 64, 64)])
+def test_batchnorm(cu, ref, shape):
+    torch.manual_seed(6)
+    x, gy = rnd(*shape) * 2 + 0.5, rnd(*shape)
+    C = shape[1]
+    gamma, beta = rnd(C), rnd(C)
+    m, v = cu.bn_stats(g(x))
+    m_r, v_r = ref.bn_stats(x)
+    assert rel(m, m_r) < FP32_TOL and rel(v, v_r) < FP32_TOL
+    rm, rv, nbt = torch.zeros(C), torch.ones(C), torch.zeros((), dtype=torch.int64)
+    rm_g, rv_g, nbt_g = g(rm.clone()), g(rv.clone()), g(nbt.clone())
+    n, _, hw = KN._nchw(x)
+    y, inv = cu.bn_apply(g(x), m, v, g(gamma), g(beta), rm_g, rv_g, 1e-5, 0.1, n * hw, nbt_g)
+    y_r, inv_r = ref.bn_apply(x, m_r, v_r, gamma, beta, rm, rv, 1e-5, 0.1, n * hw, nbt)
+    assert rel(y, y_r) < FP32_TOL and rel(inv, inv_r) < FP32_TOL
+    assert rel(rm_g, rm) < FP32_TOL and rel(rv_g, rv) < FP32_TOL and int(nbt_g) == int(nbt) == 1
+    s1, s2 = cu.bn_bwd_reduce(g(gy), g(x), m, inv)
+    s1_r, s2_r = ref.bn_bwd_reduce(gy, x, m_r, inv_r)
+    assert rel(s1, s1_r) < 1e-4 and rel(s2, s2_r) < 1e-4
+    out = cu.bn_bwd_apply(g(gy), g(x), m, inv, g(gamma), s1, s2, n * hw)
+    out_r = ref.bn_bwd_apply(gy, x, m_r, inv_r, gamma, s1_r, s2_r, n * hw)
+    for a, b in zip(out, out_r):
+        assert rel(a, b) < 1e-4
+
+
+def test_softmax_mbstd_bce(cu, ref):
+    torch.manual_seed(7)
+    x, gy = rnd(6, 2, 48), rnd(6, 2, 48)
+    y = cu.softmax_m_fwd(g(x))
+    y_r = ref.softmax_m_fwd(x)
+    assert rel(y, y_r) < FP32_TOL
+    assert rel(cu.softmax_m_bwd(g(gy), y), ref.softmax_m_bwd(gy, y_r)) < FP32_TOL
+    xs, gg, ggx = rnd(8, 64, 4, 4), rnd(1), rnd(8, 64, 4, 4)
+    assert rel(cu.mbstd_fwd(g(xs), 4, 1e-8), ref.mbstd_fwd(xs, 4, 1e-8)) < FP32_TOL
+    assert rel(cu.mbstd_bwd(g(gg), g(xs), 4, 1e-8), ref.mbstd_bwd(gg, xs, 4, 1e-8)) < FP32_TOL
+    o1, o2 = cu.mbstd_bwd_bwd(g(gg), g(xs), g(ggx), 4, 1e-8)
+    r1, r2 = ref.mbstd_bwd_bwd(gg, xs, ggx, 4, 1e-8)
+    assert rel(o1, r1) < 1e-4 and rel(o2, r2) < 1e-4
+    p, t = torch.rand(64, 1) * 0.98 + 0.01, torch.rand(64, 1)
+    out, flag = cu.bce_fwd(g(p), g(t))
+    out_r, flag_r = ref.bce_fwd(p, t)
+    assert rel(out, out_r) < FP32_TOL and int(flag) == int(flag_r) == 0
+    _, flag = cu.bce_fwd(g(p + 1.0), g(t))
+    assert int(flag) == 1
+    assert rel(cu.bce_bwd(g(gg), g(p), g(t)), ref.bce_bwd(gg, p, t)) < FP32_TOL
+
+
+def test_misc(cu, ref):
+    torch.manual_seed(8)
+    src, dst = rnd(4, 10, 5, 5), rnd(4, 16, 5, 5)
+    for acc in (False, True):
+        want = ref.chan_copy(src, 2, dst.clone(), 3, 7, acc)
+        got = cu.chan_copy(g(src), 2, g(dst.clone()), 3, 7, acc)
+        assert rel(got, want) < FP32_TOL
+    t, f = rnd(64, 3, 64, 64), rnd(64, 3, 64, 64)
+    assert rel(cu.mixup(g(t), g(f), 0.3), ref.mixup(t, f, 0.3)) < FP32_TOL
+    label = torch.rand(64, 1, dtype=torch.float64)
+    got = cu.mixup_wgan_f64(g(label), g(t), g(f))
+    want = ref.mixup_wgan_f64(label, t, f)
+    assert got.dtype == torch.float64 and rel(got, want) < 1e-12
+    x = rnd(1000)
+    assert torch.equal(cu.clamp_(g(x.clone()), -0.5, 0.5).cpu(), x.clamp(-0.5, 0.5))
+    w2d, u, v = rnd(40, 27), torch.nn.functional.normalize(rnd(40), dim=0), torch.nn.functional.normalize(rnd(27), dim=0)
+    ug, vg = g(u.clone()), g(v.clone())
+    s = cu.spectral_power_iter(g(w2d), ug, vg, 3, 1e-12)
+    s_r = ref.spectral_power_iter(w2d, u, v, 3, 1e-12)
+    assert rel(s, s_r) < 1e-4 and rel(ug, u) < 1e-4 and rel(vg, v) < 1e-4
+
+
+@pytest.mark.parametrize("decoupled,wd,b1", [(False, 0.0, 0.0), (False, 0.0, 0.5), (True, 0.01, 0.5)])
+def test_fused_adam_matches_torch(decoupled, wd, b1):
+    """FusedAdam (one launch over all tensors) against torch.optim.Adam/AdamW on CPU, 3 steps, grad=None skipped."""
+    from gan_b200 import optim
+    torch.manual_seed(9)
+    shapes = [(64, 64, 3, 3), (1025,), (7,), (4100, 33), (1,)]
+    ps_ref = [torch.nn.Parameter(rnd(*s)) for s in shapes] + [torch.nn.Parameter(rnd(5))]
+    ps = [torch.nn.Parameter(p.detach().clone().cuda()) for p in ps_ref]
+    cls = torch.optim.AdamW if decoupled else torch.optim.Adam
+    o_ref = cls(ps_ref, lr=4e-4, betas=(b1, 0.99), weight_decay=wd)
+    o = optim.FusedAdam(ps, lr=4e-4, betas=(b1, 0.99), weight_decay=wd, decoupled=decoupled)
+    for _ in range(3):
+        for pr, p in zip(ps_ref[:-1], ps[:-1]):
+            gr = rnd(*pr.shape)
+            pr.grad, p.grad = gr, gr.cuda()
+        o_ref.step()
+        o.step()
+    for pr, p in zip(ps_ref, ps):
+        assert rel(p, pr) < 1e-6
+    assert len(o.state[ps[-1]]) == 0  # grad is None -> no state
