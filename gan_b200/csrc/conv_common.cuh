@@ -39,6 +39,8 @@ int simt_dgrad(const ganb200_conv_desc* d, const float* dy, const float* w, cons
 int simt_wgrad(const ganb200_conv_desc* d, const float* x, const float* dy, const float* iscale, const float* oscale,
                float* dw, cudaStream_t s);
 
+int fold_replicate(const float* dxp, float* dx, int64_t NC, int H, int W, int pad, cudaStream_t s);
+
 // bf16 tcgen05 engine (conv_tc.cu)
 int tc_eligible(const ganb200_conv_desc* d, int op);
 size_t tc_workspace(const ganb200_conv_desc* d, int op);

@@ -293,6 +293,13 @@ __global__ void __launch_bounds__(256) fold_replicate_kernel(const float* __rest
 }  // namespace ganb200
 using namespace ganb200;
 
+int ganb200::fold_replicate(const float* dxp, float* dx, int64_t NC, int H, int W, int pad, cudaStream_t s) {
+  int64_t total = NC * H * W;
+  fold_replicate_kernel<<<ew_grid(total, 256, 2), 256, 0, s>>>(dxp, dx, NC, H, W, pad);
+  GB_CHECK_LAUNCH();
+  return 0;
+}
+
 int ganb200::simt_fprop(const ganb200_conv_desc* d, const float* x, const float* w, const float* bias,
                         const float* iscale, const float* oscale, float* y, cudaStream_t s) {
   FpropP p;

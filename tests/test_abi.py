@@ -61,7 +61,6 @@ def test_cuda_backend_refuses_cpu_tensors(lib):
         k.ew_unary(KN.U_SIGMOID, torch.zeros(4))
 
 
-@pytest.mark.xfail(reason="tcgen05 engine lands next", strict=False)
 def test_sass_has_tcgen05_and_tma():
     """The conv engine must be real Blackwell code: UTC*MMA (tcgen05.mma), LDTM (tcgen05.ld), UTMALDG (TMA)."""
     from gan_b200 import _lib
