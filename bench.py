@@ -158,6 +158,43 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
+def replay_census(census, device, reps=3):
+    """Times every distinct convolution-engine call of one iteration (shape, op, engine) in isolation with CUDA events
+    on the launching stream — `reps` back-to-back launches after one warm-up — and weights it by its call count.
+    -> {engine: (flops, seconds, calls)} for ONE iteration."""
+    from gan_b200 import kernels as KN
+    k = KN.backend()
+    out = {}
+    for key, count in sorted(census.items(), key=lambda kv: -kv[1]):
+        op, N, C, H, W, K, R, S, stride, pad, pm, has_i, has_o, has_b, eng = key
+        P, Q = KN.out_hw(H, W, R, S, stride, pad)
+        e = 1 if eng == "simt" else 2
+        x = torch.randn(N, C, H, W, device=device)
+        w = torch.randn(K, C, R, S, device=device)
+        dy = torch.randn(N, K, P, Q, device=device)
+        isc = torch.rand(N, C, device=device) if has_i else None
+        osc = torch.rand(N, K, device=device) if has_o else None
+        b = torch.randn(K, device=device) if has_b else None
+        if op == KN.FPROP:
+            f = lambda: k.conv_fprop(x, w, b, stride, pad, pm, 1.0, isc, osc, engine=e)
+        elif op == KN.DGRAD:
+            f = lambda: k.conv_dgrad(dy, w, (H, W), stride, pad, pm, 1.0, isc, osc, engine=e)
+        else:
+            f = lambda: k.conv_wgrad(x, dy, (R, S), stride, pad, pm, 1.0, isc, osc, engine=e)
+        f()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            f()
+        e1.record()
+        e1.synchronize()
+        sec = e0.elapsed_time(e1) * 1e-3 / reps
+        fl = 2.0 * N * K * P * Q * C * R * S
+        a = out.get(eng, (0.0, 0.0, 0))
+        out[eng] = (a[0] + fl * count, a[1] + sec * count, a[2] + count)
+    return out
+
+
 def run_native(args):
     from gan_b200 import dist as gdist
     from gan_b200 import kernels as KN
@@ -189,27 +226,41 @@ def run_native(args):
             tdist.all_reduce(ms, op=tdist.ReduceOp.MAX)
         return float(ms) / steps
 
+    S = T
+    if args.graphs:
+        from gan_b200.graphed import GraphedStep
+        KN.LAUNCH_COUNT[0] = 0
+        KN.CONV_CENSUS = {}
+        S = GraphedStep(T, B, warmup=max(args.warmup, 2), images=dev_images)
+        launches_per_step = KN.LAUNCH_COUNT[0] // (max(args.warmup, 2) + 1)
+        census = {k_: v // (max(args.warmup, 2) + 1) for k_, v in KN.CONV_CENSUS.items()}
+        KN.CONV_CENSUS = None
+        dev_images = S.images
+
     def step_resident():
-        one_iteration(T, dev_images, B)
+        one_iteration(S, dev_images, B)
 
     d2h = [0]
 
     def step_e2e():
-        imgs = host_images.to(device, non_blocking=True).requires_grad_()
-        d_out, g_loss = one_iteration(T, imgs, B)
+        imgs = host_images if args.graphs else host_images.to(device, non_blocking=True).requires_grad_()
+        d_out, g_loss = one_iteration(S, imgs, B)
         losses = torch.stack([v.reshape(()) for v in d_out] + [g_loss.reshape(())]).cpu()
         d2h[0] = losses.numel() * 4
 
     for _ in range(args.warmup):
         step_resident()
     KN.LAUNCH_COUNT[0] = 0
-    KN.CONV_TIMER = KN.ConvTimer()
+    KN.CONV_TIMER = None if args.graphs else KN.ConvTimer()
     with ClockSampler(device.index or 0) as clk:
         ms = timed(step_resident, args.steps)
-    launches = KN.LAUNCH_COUNT[0]
-    conv = KN.CONV_TIMER.totals()
+    launches = launches_per_step * args.steps if args.graphs else KN.LAUNCH_COUNT[0]
+    conv = KN.CONV_TIMER.totals() if KN.CONV_TIMER is not None else {}
     KN.CONV_TIMER = None
     ms_e2e = timed(step_e2e, args.steps)
+    if args.graphs:
+        conv = {k_: (v[0] * args.steps, v[1] * args.steps, v[2] * args.steps)
+                for k_, v in replay_census(census, device).items()}
     mem_gb = torch.cuda.max_memory_allocated(device) / 2**30
     dp.remove()
 
@@ -233,7 +284,7 @@ def run_native(args):
             "config": {"workload": f"generator_13_5+discriminator_9_4 train/{args.loop}.py, batch {B}/GPU, "
                                    f"global batch {B * world}, nz {NZ}", "loop": args.loop, "batch_per_gpu": B,
                        "l2": "per-step working set (activations + 2 GB of parameters) exceeds the 126 MB L2",
-                       "parallelism": f"dp{world}"},
+                       "parallelism": f"dp{world}", "cuda_graphs": bool(args.graphs)},
             "model_tflops": FLOPS_PER_IMAGE[args.loop] * B * world / (ms * 1e-3) / 1e12 / world,
             "clocks": clk.summary(), "gpu_launches": launches // max(args.steps, 1), "peak_mem_gib": mem_gb,
             "e2e": {"value": B * world / (ms_e2e * 1e-3), "unit": "images/s",
@@ -257,6 +308,8 @@ def main():
     ap.add_argument("--cpu-batch", type=int, default=4)
     ap.add_argument("--cpu-seconds", type=float, default=25.0)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--graphs", type=int, default=int(os.environ.get("GANB200_GRAPHS", "1")),
+                    help="1: replay the two step bodies as CUDA graphs (default); 0: eager launches")
     args = ap.parse_args()
     if args.impl == "reference":
         args.cpu_seconds = 240.0

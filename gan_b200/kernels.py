@@ -47,6 +47,7 @@ class ConvTimer:
 
 
 CONV_TIMER = None
+CONV_CENSUS = None  # bench.py: dict (op, desc fields..., has_iscale, has_oscale, has_bias, engine) -> number of calls
 
 
 def _nchw(t):
@@ -103,7 +104,12 @@ class CudaBackend:
         return torch.empty(nbytes, dtype=torch.uint8, device=device)
 
     # -- convolution family ---------------------------------------------------------------------
-    def _t0(self, d, op):
+    def _t0(self, d, op, flags=(False, False, False)):
+        if CONV_CENSUS is not None:
+            tc = d.engine != 1 and self.lib.ganb200_conv2d_tc_eligible(ctypes.byref(d), op) == 1
+            key = (op, d.N, d.C, d.H, d.W, d.K, d.R, d.S, d.stride, d.pad, d.pad_mode) + tuple(flags) + (
+                "tc" if tc else "simt",)
+            CONV_CENSUS[key] = CONV_CENSUS.get(key, 0) + 1
         if CONV_TIMER is None:
             return None
         tc = d.engine != 1 and self.lib.ganb200_conv2d_tc_eligible(ctypes.byref(d), op) == 1
@@ -130,7 +136,7 @@ class CudaBackend:
         y = torch.empty((N, K, d.P, d.Q), dtype=torch.float32, device=x.device)
         nb = self.lib.ganb200_conv2d_workspace_bytes(ctypes.byref(d), FPROP)
         ws = self._workspace(nb, x.device)
-        tm = self._t0(d, FPROP)
+        tm = self._t0(d, FPROP, (iscale is not None, oscale is not None, bias is not None))
         _lib.check(self.lib.ganb200_conv2d_fprop(ctypes.byref(d), self._p(x), self._p(w), self._p(bias),
                                                  self._p(iscale), self._p(oscale), self._p(y), self._p(ws), nb, st))
         self._t1(tm)
@@ -147,7 +153,7 @@ class CudaBackend:
         dx = torch.empty((N, C, H, W), dtype=torch.float32, device=dy.device)
         nb = self.lib.ganb200_conv2d_workspace_bytes(ctypes.byref(d), DGRAD)
         ws = self._workspace(nb, dy.device)
-        tm = self._t0(d, DGRAD)
+        tm = self._t0(d, DGRAD, (iscale is not None, oscale is not None, False))
         _lib.check(self.lib.ganb200_conv2d_dgrad(ctypes.byref(d), self._p(dy), self._p(w), self._p(iscale),
                                                  self._p(oscale), self._p(dx), self._p(ws), nb, st))
         self._t1(tm)
@@ -163,7 +169,7 @@ class CudaBackend:
         dw = torch.empty((K, C, R, S), dtype=torch.float32, device=x.device)
         nb = self.lib.ganb200_conv2d_workspace_bytes(ctypes.byref(d), WGRAD)
         ws = self._workspace(nb, x.device)
-        tm = self._t0(d, WGRAD)
+        tm = self._t0(d, WGRAD, (iscale is not None, oscale is not None, False))
         _lib.check(self.lib.ganb200_conv2d_wgrad(ctypes.byref(d), self._p(x), self._p(dy), self._p(iscale),
                                                  self._p(oscale), self._p(dw), self._p(ws), nb, st))
         self._t1(tm)

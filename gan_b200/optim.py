@@ -32,28 +32,37 @@ class FusedAdam(torch.optim.Optimizer):
 
     # -- table ----------------------------------------------------------------------------------------
     def _table(self, key, entries, device):
-        """entries: list of (p, g, m, v) tensors."""
+        """entries: list of (p, g, m, v) tensors -> (device table, device block map, n_blocks).
+        The pinned staging buffers and the device tables are allocated once per key and re-filled when a pointer
+        changes, so that no host allocation happens while a CUDA graph is being captured."""
         sig = tuple((p.data_ptr(), g.data_ptr()) for p, g, _, _ in entries)
         hit = self._cache.get(key)
-        if hit is not None and hit[0] == sig:
-            return hit[1:]
-        n = len(entries)
-        tab_host = torch.empty(n * 5, dtype=torch.int64, pin_memory=device.type == "cuda")
-        blocks = []
-        vals = []
+        if hit is not None and hit["sig"] == sig:
+            return hit["tab"], hit["blk"], hit["n_blocks"]
+        vals, blocks = [], []
         for i, (p, g, m, v) in enumerate(entries):
             numel = p.numel()
             vals += [p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr(), numel]
-            for c in range((numel + CHUNK - 1) // CHUNK):
-                blocks.append((i, c))
-        tab_host.copy_(torch.tensor(vals, dtype=torch.int64))
-        blk_host = torch.tensor(blocks, dtype=torch.int32).reshape(-1, 2)
-        if device.type == "cuda":
-            blk_host = blk_host.pin_memory()
-        tab = tab_host.to(device, non_blocking=True)
-        blk = blk_host.to(device, non_blocking=True)
-        self._cache[key] = (sig, tab, blk, len(blocks), (tab_host, blk_host))
-        return tab, blk, len(blocks), None
+            blocks += [(i, c) for c in range((numel + CHUNK - 1) // CHUNK)]
+        cuda = device.type == "cuda"
+        if hit is None or hit["tab_host"].numel() != len(vals) or hit["blk_host"].numel() != 2 * len(blocks):
+            hit = {"tab_host": torch.empty(len(vals), dtype=torch.int64, pin_memory=cuda),
+                   "blk_host": torch.empty((len(blocks), 2), dtype=torch.int32, pin_memory=cuda),
+                   "tab": torch.empty(len(vals), dtype=torch.int64, device=device),
+                   "blk": torch.empty((len(blocks), 2), dtype=torch.int32, device=device), "event": None}
+            hit["blk_host"].copy_(torch.tensor(blocks, dtype=torch.int32).reshape(-1, 2))
+            hit["blk"].copy_(hit["blk_host"], non_blocking=True)
+        capturing = cuda and torch.cuda.is_current_stream_capturing()
+        if hit["event"] is not None and not capturing:  # (a capture starts after a device synchronize)
+            hit["event"].synchronize()  # the previous async upload has read the staging buffer
+        hit["tab_host"].copy_(torch.tensor(vals, dtype=torch.int64))
+        hit["tab"].copy_(hit["tab_host"], non_blocking=True)
+        if cuda and not capturing:
+            hit["event"] = torch.cuda.Event()
+            hit["event"].record()
+        hit["sig"], hit["n_blocks"] = sig, len(blocks)
+        self._cache[key] = hit
+        return hit["tab"], hit["blk"], len(blocks)
 
     @torch.no_grad()
     def step(self, closure=None):
@@ -87,7 +96,7 @@ class FusedAdam(torch.optim.Optimizer):
                         k.adam_reference(p, g, m, v, group["lr"], b1, b2, group["eps"], group["weight_decay"],
                                          group["decoupled"], step, self.grad_scale)
                     continue
-                tab, blk, n_blocks, _ = self._table((gi, 0 if len(by_step) == 1 else step), entries, device)
+                tab, blk, n_blocks = self._table((gi, 0 if len(by_step) == 1 else step), entries, device)
                 step_dev = None
                 if self.capturable:
                     step_dev = self._step_dev.get(gi)
