@@ -18,6 +18,7 @@ import torch
 
 from . import kernels as KN
 from . import ops
+from . import rng
 
 
 @dataclass(frozen=True)
@@ -66,7 +67,7 @@ class StepMixin:
     # ---- pieces shared by every variant ------------------------------------------------------------
     def _noisy_labels(self, b_size, base):
         """torch.full + 0.05 * torch.rand: one RNG call of shape (b,1) (gan.py:27-28)."""
-        u = torch.rand((b_size, 1), dtype=torch.float32, device=self.device)
+        u = rng.rand(b_size, 1, device=self.device)
         return ops.affine(u, 0.05, base)
 
     def _d_loss(self, pred, target, sign):
@@ -84,7 +85,7 @@ class StepMixin:
 
     def gradient_penalty(self, x_real, x_fake, batch_size, device, center=1.):
         """WGAN-GP on per-sample interpolates (wgangp.py:34-43)."""
-        eps = torch.rand(batch_size, device=device)
+        eps = rng.rand(batch_size, device=device)
         x_interp = lerp_per_sample(x_real.detach(), x_fake.detach(), eps).requires_grad_()
         d_out = self.discriminator(x_interp)
         norm = ops.sqrt(self.compute_grad2(d_out, x_interp))
@@ -99,7 +100,7 @@ class StepMixin:
         rc = self.recipe
         valid_ = self._noisy_labels(b_size, 0.95) if rc.bce else None
         self.optimizer_G.zero_grad()
-        z = torch.randn(b_size, self.nz, 1, 1, device=self.device)
+        z = rng.randn(b_size, self.nz, 1, 1, device=self.device)
         gen_imgs = self.generator(z)
         g_loss = self._d_loss(self.discriminator(gen_imgs), valid_, -1.0)
         g_loss.backward()
@@ -113,11 +114,11 @@ class StepMixin:
         if rc.bce:
             valid_ = self._noisy_labels(b_size, 0.95)
             fake_ = self._noisy_labels(b_size, 0.0)
-            z = torch.randn(b_size, self.nz, 1, 1, device=self.device)
+            z = rng.randn(b_size, self.nz, 1, 1, device=self.device)
             self.optimizer_D.zero_grad()
         else:
             self.optimizer_D.zero_grad()
-            z = torch.randn(b_size, self.nz, 1, 1, device=self.device)
+            z = rng.randn(b_size, self.nz, 1, 1, device=self.device)
         with torch.no_grad():
             gen_imgs = self.generator(z)
         gen_imgs.requires_grad_()

@@ -24,6 +24,7 @@ import torch.nn as nn
 
 from gan_b200 import layers as L
 from gan_b200 import ops
+from gan_b200 import rng
 
 
 class EqualizedWeight(L.EqWeightBase):
@@ -217,7 +218,7 @@ class StyleConv(nn.Module):
         if self.use_noise:
             # the draw stays a torch.randn call of the same shape on the same generator as in the reference
             # (SURVEY F9): identical seeds give identical noise.
-            y = ops.noise_add(y, self.scale_noise, torch.randn(*y.shape, device=y.device))
+            y = ops.noise_add(y, self.scale_noise, rng.randn(*y.shape, device=y.device))
         return y
 
 
