@@ -67,6 +67,13 @@ SIGNATURES = {
     "ganb200_mixup": (c_int, [P, P, c_float, P, c_int64, P]),
     "ganb200_mixup_wgan_f64": (c_int, [P, P, P, P, c_int, c_int, c_int, c_int, P]),
     "ganb200_clamp_": (c_int, [P, c_int64, c_float, c_float, P]),
+    "ganb200_noise_fill": (c_int, [P, c_int64, P, c_int, P]),
+    "ganb200_demod": (c_int, [P, P, P, c_int, c_int, c_int, c_float, c_float, P]),
+    "ganb200_demod_bwd_s": (c_int, [P, P, P, P, P, P, c_int, c_int, c_int, c_float, P]),
+    "ganb200_demod_bwd_w": (c_int, [P, P, P, P, P, c_int, c_int, c_int, c_int, c_float, P]),
+    "ganb200_style_tail_fwd": (c_int, [P, P, P, P, P, c_int, c_int, c_int, c_int, P, c_int, P]),
+    "ganb200_style_tail_bwd": (c_int, [P, P, P, P, P, c_int, P, P, P, c_int, c_int, c_int, P, c_int, P]),
+    "ganb200_scale_reduce": (c_int, [P, P, P, P, P, c_int, c_int, c_int, P]),
     "ganb200_spectral_power_iter": (c_int, [P, P, P, P, c_int, c_int, c_int, c_float, P]),
 }
 

@@ -347,6 +347,77 @@ class CudaBackend:
         _lib.check(self.lib.ganb200_bce_bwd(self._p(g), self._p(p), self._p(t), self._p(gp), p.numel(), st))
         return gp
 
+    # -- fused StyleConv layer ----------------------------------------------------------------------
+    def _prep_any(self, *tensors):
+        """like _prep but accepts the int64 rng state"""
+        st = self._prep(*[t for t in tensors if t is None or t.dtype != torch.int64])
+        return st
+
+    def noise_fill(self, shape, rng_state, layer, device):
+        z = torch.empty(shape, dtype=torch.float32, device=device)
+        st = self._prep(z)
+        _lib.check(self.lib.ganb200_noise_fill(self._p(z), z.numel(), self._p(rng_state), int(layer), st))
+        return z
+
+    def demod(self, s, wsq, alpha, eps):
+        B, C = s.shape
+        Kout = wsq.shape[0]
+        st = self._prep(s, wsq)
+        sinv = torch.empty((B, Kout), dtype=torch.float32, device=s.device)
+        _lib.check(self.lib.ganb200_demod(self._p(s), self._p(wsq), self._p(sinv), B, C, Kout, alpha, eps, st))
+        return sinv
+
+    def demod_bwd_s(self, gs1, s, Ad, sinv, wsq, alpha):
+        B, C = s.shape
+        Kout = wsq.shape[0]
+        st = self._prep(gs1, s, Ad, sinv, wsq)
+        gs = torch.empty_like(s)
+        _lib.check(self.lib.ganb200_demod_bwd_s(self._p(gs1), self._p(s), self._p(Ad), self._p(sinv), self._p(wsq),
+                                                self._p(gs), B, C, Kout, alpha, st))
+        return gs
+
+    def demod_bwd_w_(self, gw, w, Ad, sinv, s, alpha):
+        Kout, C = w.shape[:2]
+        RS = w.numel() // (Kout * C)
+        st = self._prep(gw, w, Ad, sinv, s)
+        _lib.check(self.lib.ganb200_demod_bwd_w(self._p(gw), self._p(w), self._p(Ad), self._p(sinv), self._p(s),
+                                                s.shape[0], C, Kout, RS, alpha, st))
+        return gw
+
+    def style_tail_fwd(self, y, ns, slope, rng_state, layer):
+        """-> (u, a): u = y + ns*z written IN PLACE into y (u is y) when ns is given; a = PReLU(u) or None."""
+        N, Kc, HW = _nchw(y)
+        st = self._prep(y, ns, slope)
+        a = torch.empty_like(y) if slope is not None else None
+        _lib.check(self.lib.ganb200_style_tail_fwd(self._p(y), self._p(y), self._p(a), self._p(ns), self._p(slope),
+                                                   slope.numel() if slope is not None else 0, N, Kc, HW,
+                                                   self._p(rng_state), int(layer), st))
+        return y, a
+
+    def style_tail_bwd(self, ga, u, ns, slope, rng_state, layer, need_Ad=True):
+        """-> (g_u, Ad[N,K], Z[N,K] or None, Pm[N,K] or None)"""
+        N, Kc, HW = _nchw(u)
+        st = self._prep(ga, u, ns, slope)
+        dev = u.device
+        gu = torch.empty_like(u) if slope is not None else ga
+        Ad = torch.empty((N, Kc), dtype=torch.float32, device=dev) if need_Ad else None
+        Z = torch.empty((N, Kc), dtype=torch.float32, device=dev) if ns is not None else None
+        Pm = torch.empty((N, Kc), dtype=torch.float32, device=dev) if slope is not None else None
+        _lib.check(self.lib.ganb200_style_tail_bwd(self._p(ga), self._p(u), self._p(gu) if slope is not None else None,
+                                                   self._p(ns), self._p(slope),
+                                                   slope.numel() if slope is not None else 0, self._p(Ad), self._p(Z),
+                                                   self._p(Pm), N, Kc, HW, self._p(rng_state), int(layer), st))
+        return gu, Ad, Z, Pm
+
+    def scale_reduce(self, dxs, s, x, need_gx=True, need_gs=True):
+        N, C, HW = _nchw(dxs)
+        st = self._prep(dxs, s, x)
+        gx = torch.empty_like(dxs) if need_gx else None
+        gs1 = torch.empty((N, C), dtype=torch.float32, device=dxs.device) if need_gs else None
+        _lib.check(self.lib.ganb200_scale_reduce(self._p(dxs), self._p(s), self._p(x), self._p(gx), self._p(gs1), N, C,
+                                                 HW, st))
+        return gx, gs1
+
     # -- optimiser / misc -------------------------------------------------------------------------
     def adam_blocks(self, tab, block_tab, n_blocks, chunk, lr, b1, b2, eps, wd, decoupled, step, grad_scale,
                     step_dev=None):

@@ -759,5 +759,67 @@ class ModConvFn(Function):
         return gx, gw, gs, None, None, None, None, None
 
 
+class StyleLayerFn(Function):
+    """Fused StyleConv layer: modulated conv (shared-weight form, see ModConvFn) + per-channel-scaled noise + PReLU,
+
+        u = sinv * alpha * conv(w, s * xpad) + ns * z ;  out = PReLU(u, slope)        (ns / slope optional)
+
+    in 6 launches forward (wsq, demod, pack x, pack w, tcgen05 conv, tail) with only (x, u) kept for backward: the
+    noise z is a function of (rng snapshot, layer id) regenerated in the backward kernel, the conv output is
+    overwritten by u.  generators/generator_13_5.py:234-248 + :264-265 + the nn.PReLU applied to it (:315-321)."""
+
+    @staticmethod
+    def forward(ctx, x, w, s, ns, slope, pad, alpha, demodulate, eps, engine, rng_state, layer):
+        x, w, s = _c(x), _c(w), _c(s)
+        k = K()
+        Kout, C = w.shape[:2]
+        sinv = wsq = None
+        if demodulate:
+            w3 = w.reshape(Kout, C, -1)
+            wsq = k.reduce(w3, w3, KN.R_HW, 1.0)
+            sinv = k.demod(s, wsq, alpha, eps)
+        y = k.conv_fprop(x, w, None, 1, pad, 1, alpha, iscale=s, oscale=sinv, engine=engine)
+        u, a = y, None
+        if ns is not None or slope is not None:
+            u, a = k.style_tail_fwd(y, ns, slope, rng_state, layer)
+        out = a if slope is not None else u
+        ctx.save_for_backward(x, w, s, sinv, wsq, u, ns, slope, rng_state)
+        ctx.cfg = (pad, alpha, demodulate, engine, layer)
+        return out
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, g):
+        x, w, s, sinv, wsq, u, ns, slope, rng_state = ctx.saved_tensors
+        pad, alpha, demodulate, engine, layer = ctx.cfg
+        k = K()
+        g = _c(g)
+        need_x, need_w, need_s, need_ns, need_slope = ctx.needs_input_grad[:5]
+        gu, Ad, Z, Pm = k.style_tail_bwd(g, u, ns, slope, rng_state, layer, need_Ad=demodulate)
+        gns = gslope = None
+        if ns is not None and need_ns:
+            gns = k.reduce(Z.reshape(*Z.shape, 1), None, KN.R_NHW, 1.0)
+        if slope is not None and need_slope:
+            gslope = k.reduce(Pm.reshape(*Pm.shape, 1), None, KN.R_NHW if slope.numel() > 1 else KN.R_ALL, 1.0)
+            gslope = gslope.reshape(slope.shape)
+        gx = gs = gw = None
+        if need_x or need_s:
+            dxs = k.conv_dgrad(gu, w, tuple(x.shape[2:]), 1, pad, 1, alpha, iscale=None, oscale=sinv, engine=engine)
+            gx, gs = k.scale_reduce(dxs, s, x, need_x, need_s)
+        if need_w:
+            gw = k.conv_wgrad(x, gu, tuple(w.shape[2:]), 1, pad, 1, alpha, iscale=s, oscale=sinv, engine=engine)
+        if demodulate:
+            if need_s:
+                gs = k.demod_bwd_s(gs, s, Ad, sinv, wsq, alpha)
+            if need_w:
+                gw = k.demod_bwd_w_(gw, w, Ad, sinv, s, alpha)
+        return gx, gw, gs, gns, gslope, None, None, None, None, None, None, None
+
+
+def style_layer(x, w, s, ns, slope, pad, alpha, demodulate=True, eps=1e-8, engine=None, rng_state=None, layer=0):
+    """fused StyleConv (+noise) (+PReLU); needs H*W % 4 == 0."""
+    return StyleLayerFn.apply(x, w, s, ns, slope, pad, float(alpha), demodulate, float(eps), engine, rng_state, layer)
+
+
 def modulated_conv2d(x, w, s, pad, alpha, demodulate=True, eps=1e-8, engine=None):
     return ModConvFn.apply(x, w, s, pad, float(alpha), demodulate, float(eps), engine)

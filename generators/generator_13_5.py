@@ -25,6 +25,7 @@ import torch.nn as nn
 from gan_b200 import layers as L
 from gan_b200 import ops
 from gan_b200 import rng
+from gan_b200 import kernels as KN
 
 
 class EqualizedWeight(L.EqWeightBase):
@@ -201,6 +202,12 @@ class Conv2dWeightModulate(nn.Module):
         return ops.modulated_conv2d(x, self.weight.raw, style, self.padding, self.weight.gain, self.demodulate,
                                     self.eps)
 
+    def fused(self, x, s, ns, slope, layer):
+        """modconv (+ noise scale `ns`) (+ PReLU `slope`) as one fused layer (gan_b200.ops.StyleLayerFn)."""
+        style = self.to_style(s)
+        return ops.style_layer(x, self.weight.raw, style, ns, slope, self.padding, self.weight.gain, self.demodulate,
+                               self.eps, None, rng.current(), layer)
+
 
 class StyleConv(nn.Module):
     """reference :251-266 — modulated conv, the dead bias, optional per-channel-scaled N(0,1) noise."""
@@ -212,14 +219,24 @@ class StyleConv(nn.Module):
         if use_noise:
             self.scale_noise = nn.Parameter(torch.nn.init.uniform_(torch.empty(out_planes), a=0.2, b=0.3))
         self.bias = nn.Parameter(L.normal_(out_planes))
+        self.noise_layer = 0  # unique id per StyleConv, assigned by Generator.__init__ (keys the in-kernel noise)
 
-    def forward(self, x: torch.Tensor, w: torch.Tensor):
+    def forward(self, x: torch.Tensor, w: torch.Tensor, act: nn.Module = None):
+        """`act`: the per-channel PReLU the caller applies to the result (fused into the layer when possible)."""
+        hw = x.shape[-1] * x.shape[-2]
+        if rng.fused_noise() and hw % 4 == 0:
+            ns = self.scale_noise if self.use_noise else None
+            return self.conv.fused(x, w, ns, act.weight if act is not None else None, self.noise_layer)
         y = self.conv(x, w)
         if self.use_noise:
-            # the draw stays a torch.randn call of the same shape on the same generator as in the reference
-            # (SURVEY F9): identical seeds give identical noise.
-            y = ops.noise_add(y, self.scale_noise, rng.randn(*y.shape, device=y.device))
-        return y
+            if rng.philox_noise():
+                z = KN.backend().noise_fill(tuple(y.shape), rng.current(), self.noise_layer, y.device)
+            else:
+                # the draw stays a torch.randn call of the same shape on the same generator as in the reference
+                # (SURVEY F9): identical seeds give identical noise.
+                z = rng.randn(*y.shape, device=y.device)
+            y = ops.noise_add(y, self.scale_noise, z)
+        return act(y) if act is not None else y
 
 
 class SKStyleConv(nn.Module):
@@ -236,7 +253,7 @@ class SKStyleConv(nn.Module):
         self.sk_attention = _pick_sk_attention(out_planes, m, image_size)
 
     def forward(self, x: torch.Tensor, w: torch.Tensor):
-        branches = [self.__getattr__('nonlinear_%d' % i)(self.__getattr__('conv_%d' % i)(x, w))
+        branches = [self.__getattr__('conv_%d' % i)(x, w, self.__getattr__('nonlinear_%d' % i))
                     for i in range(self.M)]
         return L.sk_merge(branches, self.sk_attention(branches))
 
@@ -259,8 +276,8 @@ class StyleBlock(nn.Module):
         self.conv3 = StyleConv(d_latent, in_planes, out_planes + dense_depth, kernel_size=3)
 
     def forward(self, x: torch.Tensor, w: torch.Tensor):
-        t = self.activation1(self.conv1(x, w))
-        t = self.activation2(self.conv2(t, w)) if self.m == 1 else self.skconv(t, w)
+        t = self.conv1(x, w, self.activation1)
+        t = self.conv2(t, w, self.activation2) if self.m == 1 else self.skconv(t, w)
         return self.conv3(t, w)
 
 
@@ -505,8 +522,12 @@ class Generator(nn.Module):
             blk = GeneratorBlock(z_dim, last, planes * mult, planes * mult, dd, 2, 2, 2, size)
             last = blk.get_out_planes()
             self.__setattr__('block%d' % idx, blk)
+        for i, m in enumerate(mod for mod in self.modules() if isinstance(mod, StyleConv)):
+            m.noise_layer = i + 1
 
     def forward(self, x: torch.Tensor):
+        if rng.philox_noise():
+            rng.begin_forward(x.device)
         x, w, rgb = self.block0(x)
         for idx in range(1, 5):
             x, rgb = self.__getattr__('block%d' % idx)(x, w, rgb)

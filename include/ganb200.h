@@ -204,6 +204,37 @@ int ganb200_clamp_(float* x, int64_t n, float lo, float hi, void* stream);
 int ganb200_spectral_power_iter(const float* W, float* u, float* v, float* sigma, int rows, int cols,
                                 int n_iter, float eps, void* stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * Fused StyleConv layer of the final generator (generators/generator_13_5.py:219-266):
+ *   y = sinv[b,o] * alpha * conv(w, s[b,i]*xpad)      Conv2dWeightModulate.forward :234-248 (shared-weight form)
+ *   u = y + scale_noise[o] * z,  z ~ N(0,1)            StyleConv.forward :264-265
+ *   a = PReLU(u)                                        the nn.PReLU that follows it (:315-321, :291)
+ * The noise is never stored: z is a pure function of (rng_state = {seed, forward counter}, layer id, element index)
+ * — Philox4x32-10 + Box-Muller — and is regenerated by the backward kernel.  Tensors are [N][K][HW], HW % 4 == 0.
+ * ---------------------------------------------------------------------------------------------- */
+/* z[i] for i < n (n % 4 == 0): the exact noise the fused kernels draw for (rng_state, layer) */
+int ganb200_noise_fill(float* z, int64_t n, const int64_t* rng_state, int layer, void* stream);
+/* sinv[b,o] = rsqrt(alpha^2 * sum_i s[b,i]^2 * wsq[o,i] + eps), wsq[o,i] = sum_taps w[o,i,:]^2   (:241-243) */
+int ganb200_demod(const float* s, const float* wsq, float* sinv, int B, int C, int K, float alpha, float eps, void* stream);
+/* adjoints of the demodulation: Ad[b,o] = sum_hw g_y*y;  dd = -0.5*Ad*sinv^2
+ *   gs[b,i] = gs1[b,i] + 2*s[b,i]*alpha^2*sum_o dd[b,o]*wsq[o,i]          (gs1 may be NULL)
+ *   gw[o,i,t] += 2*w[o,i,t]*alpha^2*sum_b dd[b,o]*s[b,i]^2 */
+int ganb200_demod_bwd_s(const float* gs1, const float* s, const float* Ad, const float* sinv, const float* wsq,
+                        float* gs, int B, int C, int K, float alpha, void* stream);
+int ganb200_demod_bwd_w(float* gw, const float* w, const float* Ad, const float* sinv, const float* s, int B, int C,
+                        int K, int RS, float alpha, void* stream);
+/* u = y + ns[k]*z (u may alias y; written only when ns != NULL);  a = PReLU(u) (written only when slope != NULL) */
+int ganb200_style_tail_fwd(const float* y, float* u, float* a, const float* ns, const float* slope, int slope_n,
+                           int N, int K, int HW, const int64_t* rng_state, int layer, void* stream);
+/* g_u = g_a*(u>0?1:slope) (written when slope != NULL); per row (n,k): Ad = sum g_u*(u - ns*z), Z = sum g_u*z,
+ * Pm = sum g_a*min(u,0).  Ad / Z / Pm may be NULL. */
+int ganb200_style_tail_bwd(const float* ga, const float* u, float* gu, const float* ns, const float* slope, int slope_n,
+                           float* Ad, float* Z, float* Pm, int N, int K, int HW, const int64_t* rng_state, int layer,
+                           void* stream);
+/* gx = dxs * s[n,c] (gx may be NULL);  gs1[n,c] = sum_hw dxs*x (gs1 may be NULL) */
+int ganb200_scale_reduce(const float* dxs, const float* s, const float* x, float* gx, float* gs1, int N, int C, int HW,
+                         void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -226,6 +226,55 @@ class RefBackend:
     def bce_bwd(self, g, p, t):
         return g.reshape(()) / p.numel() * (p - t) / torch.clamp((1 - p) * p, min=1e-12)
 
+    # ---- fused StyleConv layer (gan_b200/csrc/style.cu) --------------------------------------------------------
+    def noise_fill(self, shape, rng_state, layer, device):
+        """deterministic in (seed, forward counter, layer) like the CUDA kernel; the values themselves come from a
+        torch CPU generator (the GPU tests compare the fused kernels with `noise_fill` of the same backend)."""
+        gen = torch.Generator().manual_seed((int(rng_state[0]) * 1000003 + int(rng_state[1]) * 7919 + int(layer)) % (2**63))
+        return torch.randn(shape, generator=gen, dtype=torch.float32).to(torch.get_default_dtype())
+
+    def demod(self, s, wsq, alpha, eps):
+        return torch.rsqrt(alpha * alpha * (s * s) @ wsq.t() + eps)
+
+    def demod_bwd_s(self, gs1, s, Ad, sinv, wsq, alpha):
+        dd = -0.5 * Ad * sinv * sinv
+        gs = 2 * s * alpha * alpha * (dd @ wsq)
+        return gs if gs1 is None else gs + gs1
+
+    def demod_bwd_w_(self, gw, w, Ad, sinv, s, alpha):
+        dd = -0.5 * Ad * sinv * sinv
+        dwsq = alpha * alpha * dd.t() @ (s * s)
+        gw += 2 * w * dwsq.reshape(dwsq.shape + (1,) * (w.dim() - 2))
+        return gw
+
+    def style_tail_fwd(self, y, ns, slope, rng_state, layer):
+        u = y
+        if ns is not None:
+            z = self.noise_fill(y.shape, rng_state, layer, y.device).to(y.dtype)
+            u = y.add_(self._cview(y, ns) * z)
+        a = None
+        if slope is not None:
+            a = torch.where(u > 0, u, self._cview(u, slope) * u)
+        return u, a
+
+    def style_tail_bwd(self, ga, u, ns, slope, rng_state, layer, need_Ad=True):
+        N, K = u.shape[:2]
+        gu = ga if slope is None else ga * torch.where(u > 0, torch.ones_like(u), self._cview(u, slope) * torch.ones_like(u))
+        yconv, Z = u, None
+        if ns is not None:
+            z = self.noise_fill(u.shape, rng_state, layer, u.device).to(u.dtype)
+            yconv = u - self._cview(u, ns) * z
+            Z = (gu * z).reshape(N, K, -1).sum(-1)
+        Ad = (gu * yconv).reshape(N, K, -1).sum(-1) if need_Ad else None
+        Pm = (ga * u.clamp(max=0)).reshape(N, K, -1).sum(-1) if slope is not None else None
+        return gu, Ad, Z, Pm
+
+    def scale_reduce(self, dxs, s, x, need_gx=True, need_gs=True):
+        N, C = dxs.shape[:2]
+        gx = dxs * s.reshape(N, C, *([1] * (dxs.dim() - 2))) if need_gx else None
+        gs1 = (dxs * x).reshape(N, C, -1).sum(-1) if need_gs else None
+        return gx, gs1
+
     # ---- misc ------------------------------------------------------------------------------------------------
     def chan_copy(self, src, src_c0, dst, dst_c0, ncopy, accumulate=False):
         if accumulate:

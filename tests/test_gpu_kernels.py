@@ -256,3 +256,83 @@ def test_fused_adam_matches_torch(decoupled, wd, b1):
     for pr, p in zip(ps_ref, ps):
         assert rel(p, pr) < 1e-6
     assert len(o.state[ps[-1]]) == 0  # grad is None -> no state
+
+
+def test_philox_noise(cu):
+    st = torch.tensor([987654321, 5], dtype=torch.int64, device="cuda")
+    z = cu.noise_fill((8, 16, 64, 64), st, 3, torch.device("cuda"))
+    assert abs(float(z.mean())) < 5e-3 and abs(float(z.var()) - 1.0) < 1e-2
+    assert abs(float((z ** 4).mean()) - 3.0) < 0.1                      # Gaussian kurtosis
+    assert torch.equal(z, cu.noise_fill((8, 16, 64, 64), st, 3, torch.device("cuda")))   # pure function of the key
+    z2 = cu.noise_fill((8, 16, 64, 64), st, 4, torch.device("cuda"))    # another layer: uncorrelated
+    assert abs(float((z * z2).mean())) < 5e-3
+    st2 = torch.tensor([987654321, 6], dtype=torch.int64, device="cuda")  # next forward: uncorrelated
+    assert abs(float((z * cu.noise_fill((8, 16, 64, 64), st2, 3, torch.device("cuda"))).mean())) < 5e-3
+    flat = z.flatten()
+    assert abs(float((flat[:-1] * flat[1:]).mean())) < 5e-3             # neighbours uncorrelated
+
+
+@pytest.mark.parametrize("hw", [(4, 4), (64, 64)])
+@pytest.mark.parametrize("noise,act", [(True, True), (False, True), (True, False)])
+def test_style_tail(cu, hw, noise, act):
+    torch.manual_seed(10)
+    N, K = 6, 12
+    st = torch.tensor([42, 3], dtype=torch.int64, device="cuda")
+    y = rnd(N, K, *hw).cuda()
+    ns = (torch.rand(K) * 0.3).cuda() if noise else None
+    slope = (torch.rand(K) * 0.5).cuda() if act else None
+    z = cu.noise_fill(tuple(y.shape), st, 7, y.device)
+    u_want = y + ns.view(1, K, 1, 1) * z if noise else y
+    a_want = torch.where(u_want > 0, u_want, slope.view(1, K, 1, 1) * u_want) if act else None
+    u, a = cu.style_tail_fwd(y.clone(), ns, slope, st, 7)
+    assert rel(u, u_want) < FP32_TOL
+    if act:
+        assert rel(a, a_want) < FP32_TOL
+    ga = rnd(N, K, *hw).cuda()
+    gu, Ad, Z, Pm = cu.style_tail_bwd(ga, u, ns, slope, st, 7)
+    gu_want = ga * torch.where(u > 0, torch.ones_like(u), slope.view(1, K, 1, 1).expand_as(u)) if act else ga
+    assert rel(gu, gu_want) < FP32_TOL
+    assert rel(Ad, (gu_want * y).sum((2, 3))) < 1e-4
+    if noise:
+        assert rel(Z, (gu_want * z).sum((2, 3))) < 1e-4
+    if act:
+        assert rel(Pm, (ga * u.clamp(max=0)).sum((2, 3))) < 1e-4
+
+
+def test_demod_and_scale_reduce(cu, ref):
+    torch.manual_seed(11)
+    B, C, K, RS = 8, 48, 54, 9
+    s, wsq, Ad = rnd(B, C) + 1.5, torch.rand(K, C) * 9, rnd(B, K)
+    w, gw, gs1 = rnd(K, C, 3, 3), rnd(K, C, 3, 3), rnd(B, C)
+    sinv_r = ref.demod(s, wsq, 0.2, 1e-8)
+    sinv = cu.demod(g(s), g(wsq), 0.2, 1e-8)
+    assert rel(sinv, sinv_r) < FP32_TOL
+    assert rel(cu.demod_bwd_s(g(gs1), g(s), g(Ad), sinv, g(wsq), 0.2), ref.demod_bwd_s(gs1, s, Ad, sinv_r, wsq, 0.2)) < FP32_TOL
+    assert rel(cu.demod_bwd_s(None, g(s), g(Ad), sinv, g(wsq), 0.2), ref.demod_bwd_s(None, s, Ad, sinv_r, wsq, 0.2)) < FP32_TOL
+    assert rel(cu.demod_bwd_w_(g(gw.clone()), g(w), g(Ad), sinv, g(s), 0.2),
+               ref.demod_bwd_w_(gw.clone(), w, Ad, sinv_r, s, 0.2)) < FP32_TOL
+    for hw in [(4, 4), (64, 64)]:
+        dxs, x = rnd(B, C, *hw), rnd(B, C, *hw)
+        gx, gsr = cu.scale_reduce(g(dxs), g(s), g(x))
+        gx_r, gsr_r = ref.scale_reduce(dxs, s, x)
+        assert rel(gx, gx_r) < FP32_TOL and rel(gsr, gsr_r) < 1e-4
+
+
+def test_fused_style_layer_on_gpu_matches_unfused_ops(cu):
+    """StyleLayerFn through libganb200 (fp32 engine and tcgen05 engine) against the unfused op chain on the same noise."""
+    from gan_b200 import ops
+    torch.manual_seed(12)
+    B, C, Ko, H, k = 8, 48, 54, 16, 5
+    st = torch.tensor([77, 2], dtype=torch.int64, device="cuda")
+    for engine, tol in ((1, 1e-4), (2, BF16_TOL)):
+        leaves = [rnd(B, C, H, H).cuda().requires_grad_(), rnd(Ko, C, k, k).cuda().requires_grad_(),
+                  (rnd(B, C) + 1.5).cuda().requires_grad_(), (torch.rand(Ko) * 0.3).cuda().requires_grad_(),
+                  (torch.rand(Ko) * 0.5).cuda().requires_grad_()]
+        x, w, s, ns, slope = leaves
+        out = ops.style_layer(x, w, s, ns, slope, 2, 0.03, True, 1e-8, engine, st, 5)
+        y = ops.modulated_conv2d(x, w, s, 2, 0.03, True, 1e-8, engine=1)
+        y = ops.prelu(ops.noise_add(y, ns, cu.noise_fill(tuple(y.shape), st, 5, y.device)), slope)
+        assert rel(out, y) < tol
+        gout = torch.randn_like(out)
+        for a, b in zip(torch.autograd.grad(out, leaves, gout), torch.autograd.grad(y, leaves, gout)):
+            assert rel(a, b) < max(tol, 1e-4) * 3

@@ -1,0 +1,69 @@
+"""CPU, float64: the fused StyleConv layer (gan_b200.ops.StyleLayerFn: modconv + in-kernel noise + PReLU, 2 saved
+activations) against the unfused composition (modulated_conv2d -> noise_add -> prelu) fed the same noise, forward
+and every gradient; then the whole generator_13_5 in fused vs unfused mode."""
+import random
+
+import numpy as np
+import pytest
+import torch
+
+from gan_b200 import kernels as KN
+from gan_b200 import ops, rng
+
+D = torch.float64
+
+
+@pytest.mark.parametrize("k,noise,act", [(3, True, True), (5, True, True), (1, False, True), (3, False, False),
+                                          (3, True, False)])
+def test_fused_style_layer_matches_unfused(ref_backend, k, noise, act):
+    torch.manual_seed(0)
+    B, C, Ko, H = 3, 5, 6, 4
+    x = torch.randn(B, C, H, H, dtype=D, requires_grad=True)
+    w = torch.randn(Ko, C, k, k, dtype=D, requires_grad=True)
+    s = (torch.randn(B, C, dtype=D) + 1.5).requires_grad_()
+    ns = (torch.rand(Ko, dtype=D) * 0.3).requires_grad_() if noise else None
+    slope = (torch.rand(Ko, dtype=D) * 0.5).requires_grad_() if act else None
+    state = torch.tensor([1234, 7], dtype=torch.int64)
+    alpha, pad = 0.31, (k - 1) // 2
+    out = ops.style_layer(x, w, s, ns, slope, pad, alpha, True, 1e-8, None, state, 9)
+    y = ops.modulated_conv2d(x, w, s, pad, alpha, True, 1e-8)
+    if noise:
+        z = ref_backend.noise_fill(tuple(y.shape), state, 9, y.device).to(D)
+        y = ops.noise_add(y, ns, z)
+    if act:
+        y = ops.prelu(y, slope)
+    assert torch.allclose(out, y, atol=1e-12)
+    g = torch.randn_like(out)
+    ins = [t for t in (x, w, s, ns, slope) if t is not None]
+    got = torch.autograd.grad(out, ins, g)
+    want = torch.autograd.grad(y, ins, g)
+    for a, b in zip(got, want):
+        assert torch.allclose(a, b, atol=1e-10), (a - b).abs().max()
+
+
+def test_generator_fused_equals_unfused_noise_path(ref_backend):
+    """generator_13_5 forward + all parameter gradients: fused layers (philox) == unfused ops fed the same Philox noise."""
+    from generators import generator_13_5
+    res = {}
+    for mode in ("philox", "philox_unfused"):
+        prev = rng.noise_mode(mode)
+        rng._states.clear()
+        try:
+            torch.manual_seed(0); np.random.seed(0); random.seed(0)
+            G = generator_13_5.Generator(256)
+            torch.manual_seed(1)
+            z = torch.randn(4, 256, 1, 1)
+            img = G(z)
+            img.square().mean().backward()
+            res[mode] = (img.detach(), {n: p.grad for n, p in G.named_parameters()})
+        finally:
+            rng.noise_mode(prev)
+    a, b = res["philox"], res["philox_unfused"]
+    assert float((a[0] - b[0]).norm() / b[0].norm()) < 1e-4
+    worst = 0.0
+    for n, gb in b[1].items():
+        ga = a[1][n]
+        assert (ga is None) == (gb is None), n
+        if gb is not None and gb.norm() > 1e-4:  # biases feeding a BatchNorm have zero gradient: rounding noise
+            worst = max(worst, float((ga - gb).norm() / gb.norm()))
+    assert worst < 5e-2, worst  # fp32, ~100 layers and B=4 batch norms: see tests/test_golden_final_pair.py
