@@ -158,13 +158,14 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
-def replay_census(census, device, reps=3):
+def replay_census(census, device, reps=3, dump=None):
     """Times every distinct convolution-engine call of one iteration (shape, op, engine) in isolation with CUDA events
     on the launching stream — `reps` back-to-back launches after one warm-up — and weights it by its call count.
     -> {engine: (flops, seconds, calls)} for ONE iteration."""
     from gan_b200 import kernels as KN
     k = KN.backend()
     out = {}
+    rows = []
     for key, count in sorted(census.items(), key=lambda kv: -kv[1]):
         op, N, C, H, W, K, R, S, stride, pad, pm, has_i, has_o, has_b, eng = key
         P, Q = KN.out_hw(H, W, R, S, stride, pad)
@@ -192,6 +193,13 @@ def replay_census(census, device, reps=3):
         fl = 2.0 * N * K * P * Q * C * R * S
         a = out.get(eng, (0.0, 0.0, 0))
         out[eng] = (a[0] + fl * count, a[1] + sec * count, a[2] + count)
+        rows.append({"op": ["fprop", "dgrad", "wgrad"][op], "N": N, "C": C, "H": H, "W": W, "K": K, "R": R,
+                     "stride": stride, "pad": pad, "pad_mode": pm, "engine": eng, "calls": count, "ms_each": sec * 1e3,
+                     "ms_total": sec * count * 1e3, "tflops": fl / sec / 1e12})
+    if dump:
+        rows.sort(key=lambda r: -r["ms_total"])
+        os.makedirs(os.path.dirname(dump), exist_ok=True)
+        json.dump(rows, open(dump, "w"), indent=0)
     return out
 
 
@@ -260,7 +268,7 @@ def run_native(args):
     ms_e2e = timed(step_e2e, args.steps)
     if args.graphs:
         conv = {k_: (v[0] * args.steps, v[1] * args.steps, v[2] * args.steps)
-                for k_, v in replay_census(census, device).items()}
+                for k_, v in replay_census(census, device, dump=args.census_dump).items()}
     mem_gb = torch.cuda.max_memory_allocated(device) / 2**30
     dp.remove()
 
@@ -308,6 +316,7 @@ def main():
     ap.add_argument("--cpu-batch", type=int, default=4)
     ap.add_argument("--cpu-seconds", type=float, default=25.0)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--census-dump", default=os.path.join(ROOT, "gpurun_out", "conv_census.json"))
     ap.add_argument("--graphs", type=int, default=int(os.environ.get("GANB200_GRAPHS", "1")),
                     help="1: replay the two step bodies as CUDA graphs (default); 0: eager launches")
     args = ap.parse_args()

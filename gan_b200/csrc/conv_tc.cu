@@ -60,30 +60,41 @@ __global__ void __launch_bounds__(256) pack_act_kernel(const float* __restrict__
   }
 }
 
-// w fp32 -> out[rs][ko][cp] bf16 with out(rs,ko,ci) = w[ko*sk + ci*sc + rs'] , rs' = flip ? RS-1-rs : rs
-// (fprop: sk = C*RS, sc = RS; dgrad: roles of K and C swapped: sk = RS, sc = Cw*RS, flip = 1)
+constexpr int MAX_TAPS = 49;
+struct TapTable {
+  int n;
+  int src[MAX_TAPS];          // index of the tap inside the R*S filter
+  signed char dh[MAX_TAPS];   // input coordinate offset of the tap
+  signed char dw[MAX_TAPS];
+};
+
+// w fp32 -> out[t][ko][cp] bf16 with out(t,ko,ci) = w[ko*sk + ci*sc + taps.src[t]]
+// (fprop: sk = C*RS, sc = RS; dgrad: the roles of K and C swap: sk = RS, sc = C*RS)
 __global__ void __launch_bounds__(256) pack_weight_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ out,
-                                                          int Ko, int Ci, int Cp, int RS, int64_t sk, int64_t sc,
-                                                          int flip) {
-  int64_t total = (int64_t)RS * Ko * Cp;
+                                                          int Ko, int Ci, int Cp, int64_t sk, int64_t sc,
+                                                          const TapTable taps) {
+  int64_t total = (int64_t)taps.n * Ko * Cp;
   for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < total; i += (int64_t)gridDim.x * 256) {
     int ci = (int)(i % Cp);
     int64_t t = i / Cp;
-    int ko = (int)(t % Ko), rs = (int)(t / Ko);
+    int ko = (int)(t % Ko), tp = (int)(t / Ko);
     float v = 0.f;
-    if (ci < Ci) v = w[ko * sk + ci * sc + (flip ? RS - 1 - rs : rs)];
+    if (ci < Ci) v = w[ko * sk + ci * sc + taps.src[tp]];
     out[i] = __float2bfloat16(v);
   }
 }
 
 // ------------------------------------------------------------------------------------------------ main kernel
 struct TcConvParams {
-  int N, K, P, Q;       // output [N][K][P][Q]
-  int S, taps;          // filter width, R*S
+  int N, K, P, Q;       // output tile grid [N][K][P][Q] (one phase of the output when o_step > 1)
+  int taps;             // number of filter taps
   int C;                // reduction channels
   int bw, bh, bn;       // tile box (bw*bh*bn == 128)
   int tiles_q, tiles_p; // ceil(Q/bw), ceil(P/bh)
-  int off_h, off_w;     // tap coordinate offsets: 0 when the padding is materialised, -pad for TMA zero fill
+  int in_step;          // input coordinate of output (p,q) = (p*in_step + dh[tap], q*in_step + dw[tap])
+  int OH, OW;           // full output plane; element (p,q) is stored at (p*o_step + o_off_h, q*o_step + o_off_w)
+  int o_step, o_off_h, o_off_w;
+  signed char dh[MAX_TAPS], dw[MAX_TAPS];
   int n_umma;           // UMMA N = columns of the accumulator actually computed (multiple of 16, <= BN)
   float alpha;
   const float* oscale;  // [N][K] or null
@@ -145,9 +156,9 @@ __global__ void __launch_bounds__(TC_THREADS) tc_conv_kernel(const __grid_consta
         const uint32_t phase = (it / STAGES) & 1;
         mbar_wait(&empty[stage], phase ^ 1);
         const int tap = it / k_chunks, kc = it - tap * k_chunks;
-        const int r = tap / p.S, s = tap - r * p.S;
         mbar_expect_tx(&full[stage], A_STAGE_BYTES + B_STAGE_BYTES);
-        tma_load_4d(smA + stage * A_STAGE_BYTES, &tmA, &full[stage], kc * BK, q0 + s + p.off_w, p0 + r + p.off_h, n0);
+        tma_load_4d(smA + stage * A_STAGE_BYTES, &tmA, &full[stage], kc * BK, q0 * p.in_step + p.dw[tap],
+                    p0 * p.in_step + p.dh[tap], n0);
         tma_load_3d(smB + stage * B_STAGE_BYTES, &tmB, &full[stage], kc * BK, k0, tap);
       }
     }
@@ -177,8 +188,8 @@ __global__ void __launch_bounds__(TC_THREADS) tc_conv_kernel(const __grid_consta
     const int wl = m % p.bw, hl = (m / p.bw) % p.bh, nl = m / (p.bw * p.bh);
     const int q = q0 + wl, pp = p0 + hl, n = n0 + nl;
     const bool row_ok = (q < p.Q) && (pp < p.P) && (n < p.N);
-    const int64_t PQ = (int64_t)p.P * p.Q;
-    float* ybase = p.y + ((int64_t)n * p.K) * PQ + (int64_t)pp * p.Q + q;
+    const int64_t PQ = (int64_t)p.OH * p.OW;
+    float* ybase = p.y + ((int64_t)n * p.K) * PQ + (int64_t)(pp * p.o_step + p.o_off_h) * p.OW + q * p.o_step + p.o_off_w;
     const float* osc = p.oscale ? p.oscale + (int64_t)n * p.K : nullptr;
     mbar_wait(tmem_full, 0);
     tc_fence_after();
@@ -226,12 +237,12 @@ static EncodeTiledFn encode_fn() {
 
 // bf16 tensor, `rank` dims (innermost first), byte strides for dims 1..rank-1, SWIZZLE_128B, zero OOB fill
 int make_tmap_bf16(CUtensorMap* m, const void* base, int rank, const uint64_t* dims, const uint64_t* strides,
-                   const uint32_t* box) {
+                   const uint32_t* box, const uint32_t* estr = nullptr) {
   EncodeTiledFn fn = encode_fn();
   if (!fn) return fail(GANB200_CUDA_ERROR, "cuTensorMapEncodeTiled not available%s", "");
   cuuint64_t gd[5], gs[4];
   cuuint32_t bx[5], es[5];
-  for (int i = 0; i < rank; ++i) { gd[i] = dims[i]; bx[i] = box[i]; es[i] = 1; }
+  for (int i = 0; i < rank; ++i) { gd[i] = dims[i]; bx[i] = box[i]; es[i] = estr ? estr[i] : 1; }
   for (int i = 0; i + 1 < rank; ++i) gs[i] = strides[i];
   CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), gd, gs, bx, es,
                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -245,22 +256,33 @@ static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; 
 static inline int cpad(int c) { return (c + 7) / 8 * 8; }
 static inline void* align_ws(void* ws) { return (void*)(((uintptr_t)ws + 1023) & ~uintptr_t(1023)); }
 
-// the generic problem both fprop and stride-1 dgrad map to
+// the generic problem fprop and dgrad map to: out[n,ko,(p,q)] = alpha*oscale*sum_{tap,ci} W[tap][ko][ci] *
+// in[n, ci, p*in_step + dh[tap], q*in_step + dw[tap]] (+bias), stored at (p*o_step + o_off_h, q*o_step + o_off_w)
 struct TcProblem {
   int N, Ci, Hi, Wi;      // input  fp32 NCHW
-  int Ko, R, S;           // filter
-  int Po, Qo;             // output fp32 NCHW [N][Ko][Po][Qo]
+  int Ko;
+  int Po, Qo;             // output tile grid
+  int OH, OW, o_step, o_off_h, o_off_w;
   int mat_pad;            // replicate padding materialised while packing
-  int off_h, off_w;       // tap coordinate offsets (<= 0): zero padding through TMA OOB fill
+  int in_step;
   int64_t w_sk, w_sc;     // weight strides for (ko, ci); taps innermost
-  int w_flip;
+  TapTable taps;
   float alpha;
 };
 
-static size_t problem_act_bytes(const TcProblem& q) {
-  return align_up((size_t)q.N * (q.Hi + 2 * q.mat_pad) * (q.Wi + 2 * q.mat_pad) * cpad(q.Ci) * 2, 1024);
+static size_t act_bytes(int N, int Ci, int Hi, int Wi, int mat_pad) {
+  return align_up((size_t)N * (Hi + 2 * mat_pad) * (Wi + 2 * mat_pad) * cpad(Ci) * 2, 1024);
 }
-static size_t problem_w_bytes(const TcProblem& q) { return align_up((size_t)q.R * q.S * q.Ko * cpad(q.Ci) * 2, 1024); }
+static size_t w_bytes(int taps, int Ko, int Ci) { return align_up((size_t)taps * Ko * cpad(Ci) * 2, 1024); }
+
+static int pack_input(const float* in, const float* in_scale, __nv_bfloat16* act, int N, int Ci, int Hi, int Wi,
+                      int mat_pad, cudaStream_t s) {
+  const int Cp = cpad(Ci), Hp = Hi + 2 * mat_pad;
+  dim3 grid(N * Hp, (Cp + 63) / 64);
+  pack_act_kernel<<<grid, 256, sizeof(float) * 64 * (Wi + 1), s>>>(in, in_scale, act, Ci, Hi, Wi, Cp, mat_pad);
+  GB_CHECK_LAUNCH();
+  return 0;
+}
 
 template <int BN, int STAGES>
 static int launch_tc(const CUtensorMap& ta, const CUtensorMap& tb, const TcConvParams& p, dim3 grid, cudaStream_t s) {
@@ -275,43 +297,41 @@ static int launch_tc(const CUtensorMap& ta, const CUtensorMap& tb, const TcConvP
   return 0;
 }
 
-static int run_problem(const TcProblem& q, const float* in, const float* in_scale, const float* w, float* out,
-                       const float* out_scale, const float* bias, void* ws, cudaStream_t s) {
-  const int Cp = cpad(q.Ci), Hp = q.Hi + 2 * q.mat_pad, Wp = q.Wi + 2 * q.mat_pad, RS = q.R * q.S;
-  __nv_bfloat16* act = (__nv_bfloat16*)ws;
-  __nv_bfloat16* wb = (__nv_bfloat16*)((uint8_t*)ws + problem_act_bytes(q));
+// `act`: the packed input; `wb`: scratch for this problem's packed weights
+static int run_problem(const TcProblem& q, const __nv_bfloat16* act, const float* w, __nv_bfloat16* wb, float* out,
+                       const float* out_scale, const float* bias, cudaStream_t s) {
+  const int Cp = cpad(q.Ci), Hp = q.Hi + 2 * q.mat_pad, Wp = q.Wi + 2 * q.mat_pad, NT = q.taps.n;
   {
-    dim3 grid(q.N * Hp, (Cp + 63) / 64);
-    size_t sm = sizeof(float) * 64 * (q.Wi + 1);
-    pack_act_kernel<<<grid, 256, sm, s>>>(in, in_scale, act, q.Ci, q.Hi, q.Wi, Cp, q.mat_pad);
-    GB_CHECK_LAUNCH();
-    int64_t total = (int64_t)RS * q.Ko * Cp;
-    pack_weight_kernel<<<ew_grid(total, 256, 1), 256, 0, s>>>(w, wb, q.Ko, q.Ci, Cp, RS, q.w_sk, q.w_sc, q.w_flip);
+    int64_t total = (int64_t)NT * q.Ko * Cp;
+    pack_weight_kernel<<<ew_grid(total, 256, 1), 256, 0, s>>>(w, wb, q.Ko, q.Ci, Cp, q.w_sk, q.w_sc, q.taps);
     GB_CHECK_LAUNCH();
   }
   TcConvParams p;
-  p.N = q.N; p.K = q.Ko; p.P = q.Po; p.Q = q.Qo; p.S = q.S; p.taps = RS; p.C = q.Ci;
+  p.N = q.N; p.K = q.Ko; p.P = q.Po; p.Q = q.Qo; p.taps = NT; p.C = q.Ci;
   p.bw = std::min(pow2ceil(q.Qo), TILE_M);
   p.bh = std::min(pow2ceil(q.Po), TILE_M / p.bw);
   p.bn = TILE_M / (p.bw * p.bh);
   p.tiles_q = ceil_div(q.Qo, p.bw); p.tiles_p = ceil_div(q.Po, p.bh);
   p.alpha = q.alpha; p.oscale = out_scale; p.bias = bias; p.y = out;
+  p.in_step = q.in_step; p.OH = q.OH; p.OW = q.OW; p.o_step = q.o_step; p.o_off_h = q.o_off_h; p.o_off_w = q.o_off_w;
+  for (int t = 0; t < NT; ++t) { p.dh[t] = q.taps.dh[t]; p.dw[t] = q.taps.dw[t]; }
   const int BN = q.Ko >= 128 ? 128 : 64;
   p.n_umma = q.Ko >= BN ? BN : (q.Ko + 15) / 16 * 16;
   CUtensorMap ta, tb;
   {
+    const uint32_t st = (uint32_t)q.in_step;
     uint64_t dims[4] = {(uint64_t)q.Ci, (uint64_t)Wp, (uint64_t)Hp, (uint64_t)q.N};
     uint64_t str[3] = {(uint64_t)Cp * 2, (uint64_t)Wp * Cp * 2, (uint64_t)Hp * Wp * Cp * 2};
-    uint32_t box[4] = {BK, (uint32_t)p.bw, (uint32_t)p.bh, (uint32_t)p.bn};
-    int rc = make_tmap_bf16(&ta, act, 4, dims, str, box);
+    uint32_t box[4] = {BK, (uint32_t)p.bw * st, (uint32_t)p.bh * st, (uint32_t)p.bn};
+    uint32_t es[4] = {1, st, st, 1};
+    int rc = make_tmap_bf16(&ta, act, 4, dims, str, box, es);
     if (rc) return rc;
-    uint64_t wd[3] = {(uint64_t)q.Ci, (uint64_t)q.Ko, (uint64_t)RS};
+    uint64_t wd[3] = {(uint64_t)q.Ci, (uint64_t)q.Ko, (uint64_t)NT};
     uint64_t wst[2] = {(uint64_t)Cp * 2, (uint64_t)q.Ko * Cp * 2};
     uint32_t wbox[3] = {BK, (uint32_t)BN, 1};
     rc = make_tmap_bf16(&tb, wb, 3, wd, wst, wbox);
     if (rc) return rc;
   }
-  p.off_h = q.off_h; p.off_w = q.off_w;
   dim3 grid(p.tiles_q * p.tiles_p * ceil_div(q.N, p.bn), ceil_div(q.Ko, BN));
   if (BN == 128) return launch_tc<128, 3>(ta, tb, p, grid, s);
   return launch_tc<64, 4>(ta, tb, p, grid, s);
@@ -321,41 +341,64 @@ static int run_problem(const TcProblem& q, const float* in, const float* in_scal
 
 
 static bool shape_ok(const ganb200_conv_desc* d) {
-  return d->stride == 1 && d->H <= 128 && d->W <= 128 && d->R <= 7 && d->S <= 7;
+  return (d->stride == 1 || d->stride == 2) && d->H <= 128 && d->W <= 128 && d->R <= 7 && d->S <= 7 &&
+         d->R >= d->stride && d->S >= d->stride && d->pad <= 8;
 }
 
 int tc_eligible(const ganb200_conv_desc* d, int op) {
   if (!shape_ok(d)) return 0;
   const int64_t M = (int64_t)d->N * d->P * d->Q;
-  if (op == GANB200_CONV_FPROP) return d->C >= 8 && d->K >= 8 && M >= 64;
-  if (op == GANB200_CONV_DGRAD) return d->C >= 8 && d->K >= 8 && (int64_t)d->N * d->H * d->W >= 64;
-  return d->C >= 8 && d->K >= 8 && M >= 256;
+  if (op == GANB200_CONV_FPROP) return M >= 64;
+  if (op == GANB200_CONV_DGRAD) return (int64_t)d->N * d->H * d->W >= 64;
+  return M >= 256;
 }
 
 static size_t wgrad_workspace(const ganb200_conv_desc* d);
 
 static TcProblem fprop_problem(const ganb200_conv_desc* d) {
   TcProblem q;
-  q.N = d->N; q.Ci = d->C; q.Hi = d->H; q.Wi = d->W; q.Ko = d->K; q.R = d->R; q.S = d->S; q.Po = d->P; q.Qo = d->Q;
+  q.N = d->N; q.Ci = d->C; q.Hi = d->H; q.Wi = d->W; q.Ko = d->K; q.Po = d->P; q.Qo = d->Q;
+  q.OH = d->P; q.OW = d->Q; q.o_step = 1; q.o_off_h = q.o_off_w = 0;
   const bool rep = d->pad_mode == 1 && d->pad > 0;
   q.mat_pad = rep ? d->pad : 0;
-  q.off_h = q.off_w = rep ? 0 : -d->pad;
-  q.w_sk = (int64_t)d->C * d->R * d->S; q.w_sc = (int64_t)d->R * d->S; q.w_flip = 0;
+  q.in_step = d->stride;
+  const int off = rep ? 0 : -d->pad;
+  q.taps.n = d->R * d->S;
+  for (int r = 0; r < d->R; ++r)
+    for (int c = 0; c < d->S; ++c) {
+      const int t = r * d->S + c;
+      q.taps.src[t] = t; q.taps.dh[t] = (signed char)(r + off); q.taps.dw[t] = (signed char)(c + off);
+    }
+  q.w_sk = (int64_t)d->C * d->R * d->S; q.w_sc = (int64_t)d->R * d->S;
   q.alpha = d->alpha;
   return q;
 }
 
-// dgrad as a convolution of dy: output domain = padded input (replicate, folded afterwards) or the input itself (zeros)
-static TcProblem dgrad_problem(const ganb200_conv_desc* d) {
+// dgrad as stride*stride convolutions of dy, one per output phase (a,b) = (h % stride, w % stride) of the output
+// domain (the padded input for replicate padding — folded afterwards — or the input itself for zero padding):
+//   dx[st*i + a] = sum over taps r with (a + pz - r) % st == 0 of w[r] * dy[i + (a + pz - r)/st]
+// pz = pad for zero padding (domain = input), 0 for replicate padding (domain = padded input).
+static TcProblem dgrad_problem(const ganb200_conv_desc* d, int a, int b) {
   TcProblem q;
   const bool rep = d->pad_mode == 1 && d->pad > 0;
-  q.N = d->N; q.Ci = d->K; q.Hi = d->P; q.Wi = d->Q; q.Ko = d->C; q.R = d->R; q.S = d->S;
-  q.Po = rep ? d->H + 2 * d->pad : d->H;
-  q.Qo = rep ? d->W + 2 * d->pad : d->W;
-  q.mat_pad = 0;
-  q.off_h = -(d->R - 1 - (rep ? 0 : d->pad));
-  q.off_w = -(d->S - 1 - (rep ? 0 : d->pad));
-  q.w_sk = (int64_t)d->R * d->S; q.w_sc = (int64_t)d->C * d->R * d->S; q.w_flip = 1;
+  const int st = d->stride, pz = rep ? 0 : d->pad;
+  const int DH = rep ? d->H + 2 * d->pad : d->H, DW = rep ? d->W + 2 * d->pad : d->W;
+  q.N = d->N; q.Ci = d->K; q.Hi = d->P; q.Wi = d->Q; q.Ko = d->C;
+  q.OH = DH; q.OW = DW; q.o_step = st; q.o_off_h = a; q.o_off_w = b;
+  q.Po = (DH - a + st - 1) / st; q.Qo = (DW - b + st - 1) / st;
+  q.mat_pad = 0; q.in_step = 1;
+  q.taps.n = 0;
+  for (int r = 0; r < d->R; ++r) {
+    if (((a + pz - r) % st + st) % st != 0) continue;
+    for (int c = 0; c < d->S; ++c) {
+      if (((b + pz - c) % st + st) % st != 0) continue;
+      const int t = q.taps.n++;
+      q.taps.src[t] = r * d->S + c;
+      q.taps.dh[t] = (signed char)((a + pz - r) / st);   // exact: the numerator is a multiple of st
+      q.taps.dw[t] = (signed char)((b + pz - c) / st);
+    }
+  }
+  q.w_sk = (int64_t)d->R * d->S; q.w_sc = (int64_t)d->C * d->R * d->S;
   q.alpha = d->alpha;
   return q;
 }
@@ -368,13 +411,11 @@ static size_t dgrad_fold_bytes(const ganb200_conv_desc* d) {
 
 size_t tc_workspace(const ganb200_conv_desc* d, int op) {
   if (op == GANB200_CONV_FPROP) {
-    TcProblem q = fprop_problem(d);
-    return problem_act_bytes(q) + problem_w_bytes(q) + 1024;
+    const bool rep = d->pad_mode == 1 && d->pad > 0;
+    return act_bytes(d->N, d->C, d->H, d->W, rep ? d->pad : 0) + w_bytes(d->R * d->S, d->K, d->C) + 1024;
   }
-  if (op == GANB200_CONV_DGRAD) {
-    TcProblem q = dgrad_problem(d);
-    return problem_act_bytes(q) + problem_w_bytes(q) + dgrad_fold_bytes(d) + 1024;
-  }
+  if (op == GANB200_CONV_DGRAD)
+    return act_bytes(d->N, d->K, d->P, d->Q, 0) + w_bytes(d->R * d->S, d->C, d->K) + dgrad_fold_bytes(d) + 1024;
   return wgrad_workspace(d);
 }
 
@@ -384,7 +425,11 @@ int tc_fprop(const ganb200_conv_desc* d, const float* x, const float* w, const f
              "tc fprop: workspace too small");
   ws = align_ws(ws);
   TcProblem q = fprop_problem(d);
-  return run_problem(q, x, iscale, w, y, oscale, bias, ws, s);
+  __nv_bfloat16* act = (__nv_bfloat16*)ws;
+  __nv_bfloat16* wb = (__nv_bfloat16*)((uint8_t*)ws + act_bytes(q.N, q.Ci, q.Hi, q.Wi, q.mat_pad));
+  int rc = pack_input(x, iscale, act, q.N, q.Ci, q.Hi, q.Wi, q.mat_pad, s);
+  if (rc) return rc;
+  return run_problem(q, act, w, wb, y, oscale, bias, s);
 }
 
 int tc_dgrad(const ganb200_conv_desc* d, const float* dy, const float* w, const float* iscale, const float* oscale,
@@ -392,12 +437,23 @@ int tc_dgrad(const ganb200_conv_desc* d, const float* dy, const float* w, const 
   GB_REQUIRE(ws && ws_bytes >= tc_workspace(d, GANB200_CONV_DGRAD), GANB200_WORKSPACE_TOO_SMALL,
              "tc dgrad: workspace too small");
   ws = align_ws(ws);
-  TcProblem q = dgrad_problem(d);
   const bool rep = d->pad_mode == 1 && d->pad > 0;
+  __nv_bfloat16* act = (__nv_bfloat16*)ws;
+  uint8_t* wbase = (uint8_t*)ws + act_bytes(d->N, d->K, d->P, d->Q, 0);
   float* out = dx;
-  if (rep) out = (float*)((uint8_t*)ws + problem_act_bytes(q) + problem_w_bytes(q));
-  int rc = run_problem(q, dy, oscale, w, out, iscale, nullptr, ws, s);
+  if (rep) out = (float*)(wbase + w_bytes(d->R * d->S, d->C, d->K));
+  int rc = pack_input(dy, oscale, act, d->N, d->K, d->P, d->Q, 0, s);
   if (rc) return rc;
+  size_t woff = 0;
+  for (int a = 0; a < d->stride; ++a)
+    for (int b = 0; b < d->stride; ++b) {
+      TcProblem q = dgrad_problem(d, a, b);
+      if (q.Po <= 0 || q.Qo <= 0) continue;
+      GB_REQUIRE(q.taps.n > 0, GANB200_BAD_SHAPE, "tc dgrad: an output phase has no filter tap");
+      rc = run_problem(q, act, w, (__nv_bfloat16*)(wbase + woff), out, iscale, nullptr, s);
+      if (rc) return rc;
+      woff += w_bytes(q.taps.n, d->C, d->K);
+    }
   if (rep) return fold_replicate(out, dx, (int64_t)d->N * d->C, d->H, d->W, d->pad, s);
   return 0;
 }
@@ -418,7 +474,7 @@ struct TcWgradParams {
   int bw, bh, bn;            // pixel box, bw*bh*bn == 64
   int tiles_q, tiles_p, tiles_n;
   int chunks, chunks_per_split, splits;
-  int off_h, off_w;
+  int off_h, off_w, in_step;
   int n_umma;                // multiple of 16 <= BN
   float* part;               // [splits][taps][K][C]
 };
@@ -486,7 +542,8 @@ __global__ void __launch_bounds__(TC_THREADS) tc_wgrad_kernel(const __grid_const
         tma_load_4d(a + WG_GROUP_BYTES, &tmA, &full[stage], k0 + 64, q0, p0, n0);
 #pragma unroll
         for (int g = 0; g < BN / 64; ++g)
-          tma_load_4d(b + g * WG_GROUP_BYTES, &tmB, &full[stage], c0 + g * 64, q0 + s + p.off_w, p0 + r + p.off_h, n0);
+          tma_load_4d(b + g * WG_GROUP_BYTES, &tmB, &full[stage], c0 + g * 64, q0 * p.in_step + s + p.off_w,
+                      p0 * p.in_step + r + p.off_h, n0);
       }
     }
   } else if (warp == 1) {
@@ -613,6 +670,7 @@ int tc_wgrad(const ganb200_conv_desc* d, const float* x, const float* dy, const 
   p.bw = w.bw; p.bh = w.bh; p.bn = w.bn; p.tiles_q = w.tiles_q; p.tiles_p = w.tiles_p; p.tiles_n = w.tiles_n;
   p.chunks = w.chunks; p.chunks_per_split = w.per; p.splits = w.splits;
   p.off_h = p.off_w = rep ? 0 : -d->pad;
+  p.in_step = d->stride;
   p.n_umma = d->C >= w.BN ? w.BN : (d->C + 15) / 16 * 16;
   p.part = part;
   CUtensorMap ta, tb;
@@ -624,7 +682,10 @@ int tc_wgrad(const ganb200_conv_desc* d, const float* x, const float* dy, const 
     if (rc) return rc;
     uint64_t xd[4] = {(uint64_t)d->C, (uint64_t)Wp, (uint64_t)Hp, (uint64_t)d->N};
     uint64_t xs[3] = {(uint64_t)Cp * 2, (uint64_t)Wp * Cp * 2, (uint64_t)Hp * Wp * Cp * 2};
-    rc = make_tmap_bf16(&tb, xh, 4, xd, xs, box);
+    const uint32_t st = (uint32_t)d->stride;
+    uint32_t xbox[4] = {64, (uint32_t)w.bw * st, (uint32_t)w.bh * st, (uint32_t)w.bn};
+    uint32_t es[4] = {1, st, st, 1};
+    rc = make_tmap_bf16(&tb, xh, 4, xd, xs, xbox, es);
     if (rc) return rc;
   }
   dim3 grid(ceil_div(d->K, TILE_M), ceil_div(d->C, w.BN), RS * w.splits);

@@ -55,6 +55,10 @@ CONV_CASES = [
     (4, 390, 8, 8, 96, 1, 1, 0, 1),      # 1x1 on wide concat
     (3, 7, 9, 11, 5, 3, 1, 1, 0),        # ragged, zero pad
     (4, 256, 1, 1, 4100, 1, 1, 0, 0),    # linear
+    (4, 24, 16, 16, 32, 4, 2, 1, 0),     # the conv whose dgrad is ConvTranspose2d(k4, s2, p1)
+    (4, 108, 16, 16, 3, 5, 1, 2, 1),     # ToRGB: K = 3
+    (4, 64, 10, 10, 64, 3, 2, 1, 1),     # stride 2, replicate pad, even padded size
+    (4, 40, 7, 9, 24, 3, 2, 1, 0),       # stride 2, zero pad, odd sizes
 ]
 
 
