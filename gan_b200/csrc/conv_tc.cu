@@ -403,6 +403,11 @@ static TcProblem dgrad_problem(const ganb200_conv_desc* d, int a, int b) {
   return q;
 }
 
+// packed weights of all stride*stride phases, each region rounded up to 1024 bytes
+static size_t dgrad_w_bytes(const ganb200_conv_desc* d) {
+  return w_bytes(d->R * d->S, d->C, d->K) + (size_t)1024 * d->stride * d->stride;
+}
+
 static size_t dgrad_fold_bytes(const ganb200_conv_desc* d) {
   if (d->pad_mode == 1 && d->pad > 0)
     return align_up(sizeof(float) * (size_t)d->N * d->C * (d->H + 2 * d->pad) * (d->W + 2 * d->pad), 1024);
@@ -415,7 +420,7 @@ size_t tc_workspace(const ganb200_conv_desc* d, int op) {
     return act_bytes(d->N, d->C, d->H, d->W, rep ? d->pad : 0) + w_bytes(d->R * d->S, d->K, d->C) + 1024;
   }
   if (op == GANB200_CONV_DGRAD)
-    return act_bytes(d->N, d->K, d->P, d->Q, 0) + w_bytes(d->R * d->S, d->C, d->K) + dgrad_fold_bytes(d) + 1024;
+    return act_bytes(d->N, d->K, d->P, d->Q, 0) + dgrad_w_bytes(d) + dgrad_fold_bytes(d) + 1024;
   return wgrad_workspace(d);
 }
 
@@ -441,7 +446,7 @@ int tc_dgrad(const ganb200_conv_desc* d, const float* dy, const float* w, const 
   __nv_bfloat16* act = (__nv_bfloat16*)ws;
   uint8_t* wbase = (uint8_t*)ws + act_bytes(d->N, d->K, d->P, d->Q, 0);
   float* out = dx;
-  if (rep) out = (float*)(wbase + w_bytes(d->R * d->S, d->C, d->K));
+  if (rep) out = (float*)(wbase + dgrad_w_bytes(d));
   int rc = pack_input(dy, oscale, act, d->N, d->K, d->P, d->Q, 0, s);
   if (rc) return rc;
   size_t woff = 0;
