@@ -260,8 +260,12 @@ def run_native(args):
         step_resident()
     KN.LAUNCH_COUNT[0] = 0
     KN.CONV_TIMER = None if args.graphs else KN.ConvTimer()
+    if args.profile_range:
+        torch.cuda.profiler.start()   # ncu --profile-from-start off: only the timed steps are profiled
     with ClockSampler(device.index or 0) as clk:
         ms = timed(step_resident, args.steps)
+    if args.profile_range:
+        torch.cuda.profiler.stop()
     launches = launches_per_step * args.steps if args.graphs else KN.LAUNCH_COUNT[0]
     conv = KN.CONV_TIMER.totals() if KN.CONV_TIMER is not None else {}
     KN.CONV_TIMER = None
@@ -303,6 +307,9 @@ def run_native(args):
         line["cpu_baseline"] = {"value": rate, "unit": "images/s", "cores": threads, "kind": "port",
                                 "sample": f"{n} full iterations at batch {args.cpu_batch} on torch CPU ops (fp32)"}
     print(json.dumps(line), flush=True)
+    if world > 1:
+        tdist.barrier()
+        tdist.destroy_process_group()
 
 
 def main():
@@ -316,6 +323,7 @@ def main():
     ap.add_argument("--cpu-batch", type=int, default=4)
     ap.add_argument("--cpu-seconds", type=float, default=25.0)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--profile-range", action="store_true", help="cudaProfilerStart/Stop around the timed steps")
     ap.add_argument("--census-dump", default=os.path.join(ROOT, "gpurun_out", "conv_census.json"))
     ap.add_argument("--graphs", type=int, default=int(os.environ.get("GANB200_GRAPHS", "1")),
                     help="1: replay the two step bodies as CUDA graphs (default); 0: eager launches")

@@ -91,6 +91,7 @@ struct TcConvParams {
   int C;                // reduction channels
   int bw, bh, bn;       // tile box (bw*bh*bn == 128)
   int tiles_q, tiles_p; // ceil(Q/bw), ceil(P/bh)
+  int tiles_m, tiles_n; // pixel tiles (tiles_q*tiles_p*ceil(N/bn)), output-channel tiles (ceil(K/BN))
   int in_step;          // input coordinate of output (p,q) = (p*in_step + dh[tap], q*in_step + dw[tap])
   int OH, OW;           // full output plane; element (p,q) is stored at (p*o_step + o_off_h, q*o_step + o_off_w)
   int o_step, o_off_h, o_off_w;
@@ -108,6 +109,9 @@ struct TcSmem {
   static constexpr int BYTES = STAGES * (A_STAGE_BYTES + B_STAGE_BYTES) + 1024 /*align*/ + 256 /*barriers*/;
 };
 
+// Persistent: each CTA walks tiles blockIdx.x, +gridDim.x, ... (n-tile fastest so that concurrent CTAs share the
+// activation tile in L2).  The accumulator is double-buffered in TMEM (2 x BN columns): while the epilogue warps drain
+// tile i, the producer and the MMA issuer are already in the main loop of tile i+1.
 template <int BN, int STAGES>
 __global__ void __launch_bounds__(TC_THREADS) tc_conv_kernel(const __grid_constant__ CUtensorMap tmA,
                                                              const __grid_constant__ CUtensorMap tmB,
@@ -119,19 +123,15 @@ __global__ void __launch_bounds__(TC_THREADS) tc_conv_kernel(const __grid_consta
   uint8_t* smB = smem + STAGES * A_STAGE_BYTES;
   uint64_t* full = reinterpret_cast<uint64_t*>(smB + STAGES * B_STAGE_BYTES);
   uint64_t* empty = full + STAGES;
-  uint64_t* tmem_full = empty + STAGES;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+  uint64_t* tmem_full = empty + STAGES;    // [2]
+  uint64_t* tmem_empty = tmem_full + 2;    // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  // tile coordinates
-  int t = blockIdx.x;
-  const int tq = t % p.tiles_q; t /= p.tiles_q;
-  const int tp = t % p.tiles_p; t /= p.tiles_p;
-  const int q0 = tq * p.bw, p0 = tp * p.bh, n0 = t * p.bn;
-  const int k0 = blockIdx.y * BN;
   const int k_chunks = (p.C + BK - 1) / BK;
   const int iters = p.taps * k_chunks;
-  constexpr uint32_t TMEM_COLS = BN < 32 ? 32 : BN;
+  const int total_tiles = p.tiles_m * p.tiles_n;
+  constexpr uint32_t TMEM_COLS = 2 * BN;
 
   if (threadIdx.x == 0) {
     prefetch_tmap(&tmA);
@@ -140,7 +140,10 @@ __global__ void __launch_bounds__(TC_THREADS) tc_conv_kernel(const __grid_consta
       mbar_init(&full[i], 1);
       mbar_init(&empty[i], 1);
     }
-    mbar_init(tmem_full, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tmem_full[i], 1);
+      mbar_init(&tmem_empty[i], 4);   // one arrival per epilogue warp
+    }
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
@@ -151,34 +154,49 @@ __global__ void __launch_bounds__(TC_THREADS) tc_conv_kernel(const __grid_consta
 
   if (warp == 0) {
     if (lane == 0) {
-      for (int it = 0; it < iters; ++it) {
-        const int stage = it % STAGES;
-        const uint32_t phase = (it / STAGES) & 1;
-        mbar_wait(&empty[stage], phase ^ 1);
-        const int tap = it / k_chunks, kc = it - tap * k_chunks;
-        mbar_expect_tx(&full[stage], A_STAGE_BYTES + B_STAGE_BYTES);
-        tma_load_4d(smA + stage * A_STAGE_BYTES, &tmA, &full[stage], kc * BK, q0 * p.in_step + p.dw[tap],
-                    p0 * p.in_step + p.dh[tap], n0);
-        tma_load_3d(smB + stage * B_STAGE_BYTES, &tmB, &full[stage], kc * BK, k0, tap);
+      int it = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        int t = tile / p.tiles_n;
+        const int k0 = (tile - t * p.tiles_n) * BN;
+        const int tq = t % p.tiles_q; t /= p.tiles_q;
+        const int tp = t % p.tiles_p; t /= p.tiles_p;
+        const int q0 = tq * p.bw, p0 = tp * p.bh, n0 = t * p.bn;
+        for (int i = 0; i < iters; ++i, ++it) {
+          const int stage = it % STAGES;
+          const uint32_t phase = (it / STAGES) & 1;
+          mbar_wait(&empty[stage], phase ^ 1);
+          const int tap = i / k_chunks, kc = i - tap * k_chunks;
+          mbar_expect_tx(&full[stage], A_STAGE_BYTES + B_STAGE_BYTES);
+          tma_load_4d(smA + stage * A_STAGE_BYTES, &tmA, &full[stage], kc * BK, q0 * p.in_step + p.dw[tap],
+                      p0 * p.in_step + p.dh[tap], n0);
+          tma_load_3d(smB + stage * B_STAGE_BYTES, &tmB, &full[stage], kc * BK, k0, tap);
+        }
       }
     }
   } else if (warp == 1) {
     if (lane == 0) {
       const uint32_t idesc = make_idesc_bf16(TILE_M, p.n_umma, 0, 0);
-      for (int it = 0; it < iters; ++it) {
-        const int stage = it % STAGES;
-        const uint32_t phase = (it / STAGES) & 1;
-        mbar_wait(&full[stage], phase);
+      int it = 0, local = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++local) {
+        const int acc = local & 1;
+        mbar_wait(&tmem_empty[acc], ((local >> 1) & 1) ^ 1);   // epilogue has drained this accumulator
         tc_fence_after();
-        const int kc = it % k_chunks;
-        const int ksub = min(BK / 16, (p.C - kc * BK + 15) / 16);
-        const uint64_t adesc = make_smem_desc_sw128(smem_u32(smA + stage * A_STAGE_BYTES), 16, 1024);
-        const uint64_t bdesc = make_smem_desc_sw128(smem_u32(smB + stage * B_STAGE_BYTES), 16, 1024);
-        for (int k = 0; k < ksub; ++k)  // +32 bytes (= 2 in the >>4 address field) per 16-element k step
-          mma_bf16_ss(tmem_base, adesc + 2 * k, bdesc + 2 * k, idesc, (it > 0 || k > 0) ? 1u : 0u);
-        mma_commit(&empty[stage]);
+        const uint32_t tmem_d = tmem_base + (uint32_t)(acc * BN);
+        for (int i = 0; i < iters; ++i, ++it) {
+          const int stage = it % STAGES;
+          const uint32_t phase = (it / STAGES) & 1;
+          mbar_wait(&full[stage], phase);
+          tc_fence_after();
+          const int kc = i % k_chunks;
+          const int ksub = min(BK / 16, (p.C - kc * BK + 15) / 16);
+          const uint64_t adesc = make_smem_desc_sw128(smem_u32(smA + stage * A_STAGE_BYTES), 16, 1024);
+          const uint64_t bdesc = make_smem_desc_sw128(smem_u32(smB + stage * B_STAGE_BYTES), 16, 1024);
+          for (int k = 0; k < ksub; ++k)  // +32 bytes (= 2 in the >>4 address field) per 16-element k step
+            mma_bf16_ss(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (i > 0 || k > 0) ? 1u : 0u);
+          mma_commit(&empty[stage]);
+        }
+        mma_commit(&tmem_full[acc]);
       }
-      mma_commit(tmem_full);
     }
     __syncwarp();
   } else {
@@ -186,30 +204,41 @@ __global__ void __launch_bounds__(TC_THREADS) tc_conv_kernel(const __grid_consta
     const int quarter = warp & 3;
     const int m = quarter * 32 + lane;
     const int wl = m % p.bw, hl = (m / p.bw) % p.bh, nl = m / (p.bw * p.bh);
-    const int q = q0 + wl, pp = p0 + hl, n = n0 + nl;
-    const bool row_ok = (q < p.Q) && (pp < p.P) && (n < p.N);
     const int64_t PQ = (int64_t)p.OH * p.OW;
-    float* ybase = p.y + ((int64_t)n * p.K) * PQ + (int64_t)(pp * p.o_step + p.o_off_h) * p.OW + q * p.o_step + p.o_off_w;
-    const float* osc = p.oscale ? p.oscale + (int64_t)n * p.K : nullptr;
-    mbar_wait(tmem_full, 0);
-    tc_fence_after();
-    for (int c0 = 0; c0 < p.n_umma; c0 += 32) {
-      float v[32];
-      tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)c0, v);
-      if (row_ok) {
+    int local = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++local) {
+      int t = tile / p.tiles_n;
+      const int k0 = (tile - t * p.tiles_n) * BN;
+      const int tq = t % p.tiles_q; t /= p.tiles_q;
+      const int tp = t % p.tiles_p; t /= p.tiles_p;
+      const int q = tq * p.bw + wl, pp = tp * p.bh + hl, n = t * p.bn + nl;
+      const bool row_ok = (q < p.Q) && (pp < p.P) && (n < p.N);
+      float* ybase = p.y + ((int64_t)n * p.K) * PQ + (int64_t)(pp * p.o_step + p.o_off_h) * p.OW + q * p.o_step +
+                     p.o_off_w;
+      const float* osc = p.oscale ? p.oscale + (int64_t)n * p.K : nullptr;
+      const int acc = local & 1;
+      mbar_wait(&tmem_full[acc], (local >> 1) & 1);
+      tc_fence_after();
+      for (int c0 = 0; c0 < p.n_umma; c0 += 32) {
+        float v[32];
+        tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN + c0), v);
+        if (row_ok) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          const int k = k0 + c0 + j;
-          if (c0 + j < p.n_umma && k < p.K) {
-            float o = v[j] * p.alpha;
-            if (osc) o *= osc[k];
-            if (p.bias) o += p.bias[k];
-            ybase[(int64_t)k * PQ] = o;
+          for (int j = 0; j < 32; ++j) {
+            const int k = k0 + c0 + j;
+            if (c0 + j < p.n_umma && k < p.K) {
+              float o = v[j] * p.alpha;
+              if (osc) o *= osc[k];
+              if (p.bias) o += p.bias[k];
+              ybase[(int64_t)k * PQ] = o;
+            }
           }
         }
       }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tmem_empty[acc]);
     }
-    tc_fence_before();
   }
   __syncthreads();
   if (warp == 1) {
@@ -332,7 +361,11 @@ static int run_problem(const TcProblem& q, const __nv_bfloat16* act, const float
     rc = make_tmap_bf16(&tb, wb, 3, wd, wst, wbox);
     if (rc) return rc;
   }
-  dim3 grid(p.tiles_q * p.tiles_p * ceil_div(q.N, p.bn), ceil_div(q.Ko, BN));
+  p.tiles_m = p.tiles_q * p.tiles_p * ceil_div(q.N, p.bn);
+  p.tiles_n = ceil_div(q.Ko, BN);
+  const int64_t total = (int64_t)p.tiles_m * p.tiles_n;
+  // persistent grid: 2 CTAs per SM (shared memory: 4 x 24 KB resp. 3 x 32 KB stages; TMEM: 2 x 2*BN <= 512 columns)
+  dim3 grid((unsigned)std::min<int64_t>(total, 2 * kNumSMs));
   if (BN == 128) return launch_tc<128, 3>(ta, tb, p, grid, s);
   return launch_tc<64, 4>(ta, tb, p, grid, s);
 }

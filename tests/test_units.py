@@ -1,0 +1,69 @@
+"""units/mixup.py and units/Weight_Initialization.py drop-ins against the unmodified reference (when mounted) and against
+the plain formula; the Beta draws must be bit-identical (host numpy RNG)."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import needs_reference
+
+
+def _both(fn_name, true, fake, alpha, ref_mod, my_mod):
+    np.random.seed(3)
+    want = getattr(ref_mod, fn_name)(true, fake, alpha, true.device)
+    np.random.seed(3)
+    got = getattr(my_mod, fn_name)(true, fake, alpha, true.device)
+    return got, want
+
+
+@needs_reference
+def test_mixup_matches_reference_bit_exact_coefficients(ref_backend):
+    from oracle import reference as R
+    ref = R.load("units.mixup")
+    from units import mixup as mine
+    t, f = torch.randn(64, 3, 64, 64), torch.randn(64, 3, 64, 64)
+    got, want = _both("mixup_data", t, f, 0.4, ref, mine)
+    assert got[2] == want[2]                                   # lam: bit exact
+    assert torch.equal(got[1], want[1])
+    assert torch.allclose(got[0], want[0], atol=1e-6)
+    got, want = _both("mixup_data_wgan", t, f, 0.4, ref, mine)
+    assert torch.equal(got[1], want[1])                        # per-row Beta labels: bit exact, float64
+    assert got[0].dtype == want[0].dtype == torch.float64
+    assert torch.allclose(got[0], want[0], atol=1e-12)
+    for alpha in (0, -1.0):
+        got, want = _both("mixup_data", t, f, alpha, ref, mine)
+        assert got[2] == want[2] == 1
+    # the (B,1) x (B,3,64,64) broadcast only works for B in {1, 64}: same exception type otherwise
+    t8, f8 = torch.randn(8, 3, 64, 64), torch.randn(8, 3, 64, 64)
+    with pytest.raises(RuntimeError):
+        ref.mixup_data_wgan(t8, f8, 0.4, t8.device)
+    with pytest.raises(RuntimeError):
+        mine.mixup_data_wgan(t8, f8, 0.4, t8.device)
+
+
+def test_weights_init_by_class_name():
+    import torch.nn as nn
+    from units.Weight_Initialization import weights_init
+    torch.manual_seed(0)
+    net = nn.Sequential(nn.Conv2d(3, 4, 3), nn.BatchNorm2d(4), nn.Linear(4, 4))
+    before = net[2].weight.clone()
+    net.apply(weights_init)
+    assert abs(float(net[0].weight.std()) - 0.02) < 0.01
+    assert abs(float(net[1].weight.mean()) - 1.0) < 0.05 and float(net[1].bias.abs().sum()) == 0
+    assert torch.equal(net[2].weight, before)
+
+
+@pytest.mark.gpu
+def test_mixup_on_gpu():
+    from units import mixup as mine
+    t, f = torch.randn(64, 3, 64, 64).cuda(), torch.randn(64, 3, 64, 64).cuda()
+    np.random.seed(5)
+    mixed, label, lam = mine.mixup_data(t, f, 0.4, t.device)
+    np.random.seed(5)
+    assert lam == np.random.beta(0.4, 0.4)
+    assert torch.allclose(mixed, lam * t + (1 - lam) * f, atol=1e-6)
+    np.random.seed(5)
+    mixed, label = mine.mixup_data_wgan(t, f, 0.4, t.device)
+    np.random.seed(5)
+    lab = torch.from_numpy(np.random.beta(0.4, 0.4, size=(64, 1))).cuda()
+    assert torch.equal(label, lab) and mixed.dtype == torch.float64
+    assert torch.allclose(mixed, lab * t + (1 - lab) * f, atol=1e-12)
