@@ -73,6 +73,9 @@ SIGNATURES = {
     "ganb200_demod_bwd_w": (c_int, [P, P, P, P, P, c_int, c_int, c_int, c_int, c_float, P]),
     "ganb200_style_tail_fwd": (c_int, [P, P, P, P, P, c_int, c_int, c_int, c_int, P, c_int, P]),
     "ganb200_style_tail_bwd": (c_int, [P, P, P, P, P, c_int, P, P, P, c_int, c_int, c_int, P, c_int, P]),
+    "ganb200_modconv_bwd_workspace_bytes": (c_size_t, [_DESC_P]),
+    "ganb200_modconv_bwd_eligible": (c_int, [_DESC_P]),
+    "ganb200_modconv_bwd": (c_int, [_DESC_P, P, P, P, P, P, P, P, P, P, c_size_t, P]),
     "ganb200_scale_reduce": (c_int, [P, P, P, P, P, c_int, c_int, c_int, P]),
     "ganb200_spectral_power_iter": (c_int, [P, P, P, P, c_int, c_int, c_int, c_float, P]),
 }

@@ -470,16 +470,26 @@ int tc_fprop(const ganb200_conv_desc* d, const float* x, const float* w, const f
   return run_problem(q, act, w, wb, y, oscale, bias, s);
 }
 
+static int dgrad_run(const ganb200_conv_desc* d, const float* dy, const float* w, const float* iscale,
+                     const float* oscale, float* dx, void* ws, cudaStream_t s, bool fold, float** padded_out);
+
 int tc_dgrad(const ganb200_conv_desc* d, const float* dy, const float* w, const float* iscale, const float* oscale,
              float* dx, void* ws, size_t ws_bytes, cudaStream_t s) {
   GB_REQUIRE(ws && ws_bytes >= tc_workspace(d, GANB200_CONV_DGRAD), GANB200_WORKSPACE_TOO_SMALL,
              "tc dgrad: workspace too small");
-  ws = align_ws(ws);
+  return dgrad_run(d, dy, w, iscale, oscale, dx, align_ws(ws), s, true, nullptr);
+}
+
+// ws (1024-aligned): [dy packed][phase weights][padded fp32 output (replicate padding only)].  With fold == false the
+// padded-domain result is left in the workspace (*padded_out) for a fused consumer.
+static int dgrad_run(const ganb200_conv_desc* d, const float* dy, const float* w, const float* iscale,
+                     const float* oscale, float* dx, void* ws, cudaStream_t s, bool fold, float** padded_out) {
   const bool rep = d->pad_mode == 1 && d->pad > 0;
   __nv_bfloat16* act = (__nv_bfloat16*)ws;
   uint8_t* wbase = (uint8_t*)ws + act_bytes(d->N, d->K, d->P, d->Q, 0);
   float* out = dx;
   if (rep) out = (float*)(wbase + dgrad_w_bytes(d));
+  if (padded_out) *padded_out = out;
   int rc = pack_input(dy, oscale, act, d->N, d->K, d->P, d->Q, 0, s);
   if (rc) return rc;
   size_t woff = 0;
@@ -492,7 +502,7 @@ int tc_dgrad(const ganb200_conv_desc* d, const float* dy, const float* w, const 
       if (rc) return rc;
       woff += w_bytes(q.taps.n, d->C, d->K);
     }
-  if (rep) return fold_replicate(out, dx, (int64_t)d->N * d->C, d->H, d->W, d->pad, s);
+  if (rep && fold) return fold_replicate(out, dx, (int64_t)d->N * d->C, d->H, d->W, d->pad, s);
   return 0;
 }
 
@@ -684,21 +694,32 @@ static int launch_wg(const CUtensorMap& ta, const CUtensorMap& tb, const TcWgrad
   return 0;
 }
 
+static int wgrad_run(const ganb200_conv_desc* d, const float* x, const float* dy, const float* iscale,
+                     const float* oscale, float* dw, void* ws, cudaStream_t s, const __nv_bfloat16* dy_prepacked);
+
 int tc_wgrad(const ganb200_conv_desc* d, const float* x, const float* dy, const float* iscale, const float* oscale,
              float* dw, void* ws, size_t ws_bytes, cudaStream_t s) {
   GB_REQUIRE(ws && ws_bytes >= wgrad_workspace(d), GANB200_WORKSPACE_TOO_SMALL, "tc wgrad: workspace too small");
-  ws = align_ws(ws);
+  return wgrad_run(d, x, dy, iscale, oscale, dw, align_ws(ws), s, nullptr);
+}
+
+// ws (1024-aligned): [dy packed (unused when dy_prepacked)][x packed][partials]
+static int wgrad_run(const ganb200_conv_desc* d, const float* x, const float* dy, const float* iscale,
+                     const float* oscale, float* dw, void* ws, cudaStream_t s, const __nv_bfloat16* dy_prepacked) {
   const WgradPlan w = wgrad_plan(d);
   const bool rep = d->pad_mode == 1 && d->pad > 0;
   const int mp = rep ? d->pad : 0;
   const int Kp = cpad(d->K), Cp = cpad(d->C), Hp = d->H + 2 * mp, Wp = d->W + 2 * mp, RS = d->R * d->S;
-  __nv_bfloat16* dyh = (__nv_bfloat16*)ws;
+  const __nv_bfloat16* dyh = dy_prepacked ? dy_prepacked : (const __nv_bfloat16*)ws;
   __nv_bfloat16* xh = (__nv_bfloat16*)((uint8_t*)ws + w.dy_bytes);
   float* part = (float*)((uint8_t*)ws + w.dy_bytes + w.x_bytes);
   {
-    dim3 g1(d->N * d->P, (Kp + 63) / 64);
-    pack_act_kernel<<<g1, 256, sizeof(float) * 64 * (d->Q + 1), s>>>(dy, oscale, dyh, d->K, d->P, d->Q, Kp, 0);
-    GB_CHECK_LAUNCH();
+    if (!dy_prepacked) {
+      dim3 g1(d->N * d->P, (Kp + 63) / 64);
+      pack_act_kernel<<<g1, 256, sizeof(float) * 64 * (d->Q + 1), s>>>(dy, oscale, (__nv_bfloat16*)ws, d->K, d->P, d->Q,
+                                                                       Kp, 0);
+      GB_CHECK_LAUNCH();
+    }
     dim3 g2(d->N * Hp, (Cp + 63) / 64);
     pack_act_kernel<<<g2, 256, sizeof(float) * 64 * (d->W + 1), s>>>(x, iscale, xh, d->C, d->H, d->W, Cp, mp);
     GB_CHECK_LAUNCH();
@@ -734,4 +755,104 @@ int tc_wgrad(const ganb200_conv_desc* d, const float* x, const float* dy, const 
   return 0;
 }
 
+// ================================================================================================ fused modconv backward
+// plane (n,c): v(h,w) = sum of dxp over the padded positions that clamp to (h,w) (adjoint of replicate padding);
+//              gx = v * s[n,c];  gs1[n,c] = sum_hw v * x
+template <bool WARP_ROWS>
+__global__ void __launch_bounds__(256) fold_scale_reduce_kernel(const float* __restrict__ dxp, const float* __restrict__ s,
+                                                                const float* __restrict__ x, float* __restrict__ gx,
+                                                                float* __restrict__ gs1, int H, int W, int pad,
+                                                                int64_t rows) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int Hp = H + 2 * pad, Wp = W + 2 * pad, HW = H * W;
+  const int64_t row_step = WARP_ROWS ? (int64_t)gridDim.x * 8 : gridDim.x;
+  for (int64_t row = WARP_ROWS ? (int64_t)blockIdx.x * 8 + warp : blockIdx.x; row < rows; row += row_step) {
+    const float sv = s[row];
+    const float* src = dxp + row * Hp * Wp;
+    float acc = 0.f;
+    const int t0 = WARP_ROWS ? lane : threadIdx.x, tstep = WARP_ROWS ? 32 : 256;
+    for (int i = t0; i < HW; i += tstep) {
+      const int h = i / W, w = i - h * W;
+      int h_lo = h == 0 ? 0 : h + pad, h_hi = h == H - 1 ? Hp - 1 : h + pad;
+      int w_lo = w == 0 ? 0 : w + pad, w_hi = w == W - 1 ? Wp - 1 : w + pad;
+      if (H == 1) { h_lo = 0; h_hi = Hp - 1; }
+      if (W == 1) { w_lo = 0; w_hi = Wp - 1; }
+      float v = 0.f;
+      for (int a = h_lo; a <= h_hi; ++a)
+        for (int b = w_lo; b <= w_hi; ++b) v += src[a * Wp + b];
+      if (gs1) acc = fmaf(v, x[row * HW + i], acc);
+      if (gx) gx[row * HW + i] = v * sv;
+    }
+    if (gs1) {
+      if (WARP_ROWS) {
+        acc = warp_sum(acc);
+        if (lane == 0) gs1[row] = acc;
+      } else {
+        acc = block_sum<256>(acc);
+        if (threadIdx.x == 0) gs1[row] = acc;
+      }
+    }
+  }
+}
+
+static size_t modconv_bwd_bytes(const ganb200_conv_desc* d) {
+  const WgradPlan w = wgrad_plan(d);
+  const bool rep = d->pad_mode == 1 && d->pad > 0;
+  const size_t direct = rep ? 0 : align_up(sizeof(float) * (size_t)d->N * d->C * d->H * d->W, 1024);
+  return tc_workspace(d, GANB200_CONV_DGRAD) + w.dy_bytes + w.x_bytes + w.part_bytes + direct + 2048;
+}
+
 }  // namespace ganb200
+
+using namespace ganb200;
+
+extern "C" size_t ganb200_modconv_bwd_workspace_bytes(const ganb200_conv_desc* d) {
+  if (validate_desc(d) != 0) return 0;
+  return modconv_bwd_bytes(d);
+}
+
+extern "C" int ganb200_modconv_bwd_eligible(const ganb200_conv_desc* d) {
+  if (validate_desc(d) != 0) return 0;
+  return d->stride == 1 && d->pad_mode == 1 && tc_eligible(d, GANB200_CONV_DGRAD) && tc_eligible(d, GANB200_CONV_WGRAD);
+}
+
+// Backward of y = sinv*alpha*conv(w, s*xpad) given gu = dL/dy (generators/generator_13_5.py:234-248, shared-weight form):
+//   gx = s * dxs, gs1 = sum_hw dxs * x with dxs = fold(alpha * sum w * (sinv*gu));  gw = alpha * wgrad(s*x, sinv*gu).
+// gu is packed to bf16 NHWC once and feeds both the dgrad and the wgrad kernels; the fold of the replicate padding is
+// fused with the style scaling and the row reduction.  gx / gs1 (together) or gw may be NULL.
+extern "C" int ganb200_modconv_bwd(const ganb200_conv_desc* d, const float* x, const float* w, const float* s,
+                                   const float* sinv, const float* gu, float* gx, float* gs1, float* gw, void* ws,
+                                   size_t ws_bytes, void* stream) {
+  int rc = validate_desc(d);
+  if (rc) return rc;
+  GB_REQUIRE(ganb200_modconv_bwd_eligible(d), GANB200_BAD_SHAPE, "modconv_bwd: shape not eligible");
+  GB_REQUIRE(ws && ws_bytes >= modconv_bwd_bytes(d), GANB200_WORKSPACE_TOO_SMALL, "modconv_bwd: workspace too small");
+  cudaStream_t st = (cudaStream_t)stream;
+  uint8_t* base = (uint8_t*)align_ws(ws);
+  float* dxp = nullptr;
+  const WgradPlan wp = wgrad_plan(d);
+  uint8_t* wws = base + (tc_workspace(d, GANB200_CONV_DGRAD) / 1024) * 1024;
+  // pad == 0 (1x1 convs): no padded domain, the dgrad kernels write a plain [N,C,H,W] buffer behind the wgrad scratch
+  float* direct = (float*)(wws + wp.dy_bytes + wp.x_bytes + wp.part_bytes);
+  // dgrad part of the workspace first: its head is the packed gu, shared with wgrad
+  rc = dgrad_run(d, gu, w, nullptr, sinv, direct, base, st, false, &dxp);
+  if (rc) return rc;
+  if (gx || gs1) {
+    const int64_t rows = (int64_t)d->N * d->C;
+    const int HW = d->H * d->W;
+    const int pad = (d->pad_mode == 1) ? d->pad : 0;
+    if (HW >= 1024) {
+      int grid = (int)std::min<int64_t>(rows, (int64_t)kNumSMs * 32);
+      fold_scale_reduce_kernel<false><<<grid, 256, 0, st>>>(dxp, s, x, gx, gs1, d->H, d->W, pad, rows);
+    } else {
+      int grid = (int)std::min<int64_t>((rows + 7) / 8, (int64_t)kNumSMs * 32);
+      fold_scale_reduce_kernel<true><<<grid, 256, 0, st>>>(dxp, s, x, gx, gs1, d->H, d->W, pad, rows);
+    }
+    GB_CHECK_LAUNCH();
+  }
+  if (gw) {
+    rc = wgrad_run(d, x, gu, s, sinv, gw, wws, st, (const __nv_bfloat16*)base);
+    if (rc) return rc;
+  }
+  return 0;
+}

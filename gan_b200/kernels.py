@@ -409,6 +409,28 @@ class CudaBackend:
                                                    self._p(Pm), N, Kc, HW, self._p(rng_state), int(layer), st))
         return gu, Ad, Z, Pm
 
+    def modconv_bwd(self, x, w, s, sinv, gu, pad, alpha, need_x=True, need_s=True, need_w=True, engine=None):
+        """fused backward of the modulated conv -> (gx, gs1, gw) or None when the shape / engine is not eligible"""
+        N, C, H, W = x.shape
+        Kout, _, R, S = w.shape
+        d = self._desc(N, C, H, W, Kout, R, S, 1, pad, 1, alpha, engine)
+        if d.engine == 1 or sinv is None or not self.lib.ganb200_modconv_bwd_eligible(ctypes.byref(d)):
+            return None
+        st = self._prep(x, w, s, sinv, gu)
+        if CONV_CENSUS is not None:
+            for op in (DGRAD, WGRAD):
+                key = (op, N, C, H, W, Kout, R, S, 1, pad, 1, op == WGRAD, True, False, "tc")
+                CONV_CENSUS[key] = CONV_CENSUS.get(key, 0) + 1
+        gx = torch.empty_like(x) if need_x else None
+        gs1 = torch.empty((N, C), dtype=torch.float32, device=x.device) if need_s else None
+        gw = torch.empty_like(w) if need_w else None
+        nb = self.lib.ganb200_modconv_bwd_workspace_bytes(ctypes.byref(d))
+        ws = self._workspace(nb, x.device)
+        _lib.check(self.lib.ganb200_modconv_bwd(ctypes.byref(d), self._p(x), self._p(w), self._p(s), self._p(sinv),
+                                                self._p(gu), self._p(gx), self._p(gs1), self._p(gw), self._p(ws), nb,
+                                                st))
+        return gx, gs1, gw
+
     def scale_reduce(self, dxs, s, x, need_gx=True, need_gs=True):
         N, C, HW = _nchw(dxs)
         st = self._prep(dxs, s, x)

@@ -803,11 +803,17 @@ class StyleLayerFn(Function):
             gslope = k.reduce(Pm.reshape(*Pm.shape, 1), None, KN.R_NHW if slope.numel() > 1 else KN.R_ALL, 1.0)
             gslope = gslope.reshape(slope.shape)
         gx = gs = gw = None
-        if need_x or need_s:
-            dxs = k.conv_dgrad(gu, w, tuple(x.shape[2:]), 1, pad, 1, alpha, iscale=None, oscale=sinv, engine=engine)
-            gx, gs = k.scale_reduce(dxs, s, x, need_x, need_s)
-        if need_w:
-            gw = k.conv_wgrad(x, gu, tuple(w.shape[2:]), 1, pad, 1, alpha, iscale=s, oscale=sinv, engine=engine)
+        fused = k.modconv_bwd(x, w, s, sinv, gu, pad, alpha, need_x, need_s, need_w, engine) \
+            if hasattr(k, "modconv_bwd") else None
+        if fused is not None:
+            gx, gs, gw = fused
+        else:
+            if need_x or need_s:
+                dxs = k.conv_dgrad(gu, w, tuple(x.shape[2:]), 1, pad, 1, alpha, iscale=None, oscale=sinv,
+                                   engine=engine)
+                gx, gs = k.scale_reduce(dxs, s, x, need_x, need_s)
+            if need_w:
+                gw = k.conv_wgrad(x, gu, tuple(w.shape[2:]), 1, pad, 1, alpha, iscale=s, oscale=sinv, engine=engine)
         if demodulate:
             if need_s:
                 gs = k.demod_bwd_s(gs, s, Ad, sinv, wsq, alpha)

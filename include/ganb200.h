@@ -231,6 +231,14 @@ int ganb200_style_tail_fwd(const float* y, float* u, float* a, const float* ns, 
 int ganb200_style_tail_bwd(const float* ga, const float* u, float* gu, const float* ns, const float* slope, int slope_n,
                            float* Ad, float* Z, float* Pm, int N, int K, int HW, const int64_t* rng_state, int layer,
                            void* stream);
+/* Backward of the modulated convolution y = sinv*alpha*conv(w, s*xpad) given gu = dL/dy (stride 1, replicate padding):
+ *   gx = s*dxs, gs1[n,c] = sum_hw dxs*x with dxs = fold(alpha*sum w*(sinv*gu));   gw = alpha*wgrad(s*x, sinv*gu)
+ * One bf16 pack of gu feeds the dgrad and the wgrad tensor-core kernels; the padding adjoint, the style scaling and the
+ * row reduction are one kernel.  gx/gs1 or gw may be NULL.  Only for shapes ganb200_modconv_bwd_eligible() accepts. */
+size_t ganb200_modconv_bwd_workspace_bytes(const ganb200_conv_desc* d);
+int ganb200_modconv_bwd_eligible(const ganb200_conv_desc* d);
+int ganb200_modconv_bwd(const ganb200_conv_desc* d, const float* x, const float* w, const float* s, const float* sinv,
+                        const float* gu, float* gx, float* gs1, float* gw, void* ws, size_t ws_bytes, void* stream);
 /* gx = dxs * s[n,c] (gx may be NULL);  gs1[n,c] = sum_hw dxs*x (gs1 may be NULL) */
 int ganb200_scale_reduce(const float* dxs, const float* s, const float* x, float* gx, float* gs1, int N, int C, int HW,
                          void* stream);
