@@ -337,9 +337,16 @@ static int run_problem(const TcProblem& q, const __nv_bfloat16* act, const float
   }
   TcConvParams p;
   p.N = q.N; p.K = q.Ko; p.P = q.Po; p.Q = q.Qo; p.taps = NT; p.C = q.Ci;
-  p.bw = std::min(pow2ceil(q.Qo), TILE_M);
-  p.bh = std::min(pow2ceil(q.Po), TILE_M / p.bw);
-  p.bn = TILE_M / (p.bw * p.bh);
+  {
+    // tile box (bw x bh x bn = 128 pixels, powers of two): the shape that covers [N][Po][Qo] with the fewest tiles
+    // (padded dgrad domains such as 68x68 would waste half of a 128-wide row tile); ties go to the wider box.
+    int64_t best = -1;
+    for (int bw = std::min(pow2ceil(q.Qo), TILE_M); bw >= 1; bw >>= 1) {
+      const int bh = std::min(pow2ceil(q.Po), TILE_M / bw), bn = TILE_M / (bw * bh);
+      const int64_t tiles = (int64_t)ceil_div(q.Qo, bw) * ceil_div(q.Po, bh) * ceil_div(q.N, bn);
+      if (best < 0 || tiles < best) { best = tiles; p.bw = bw; p.bh = bh; p.bn = bn; }
+    }
+  }
   p.tiles_q = ceil_div(q.Qo, p.bw); p.tiles_p = ceil_div(q.Po, p.bh);
   p.alpha = q.alpha; p.oscale = out_scale; p.bias = bias; p.y = out;
   p.in_step = q.in_step; p.OH = q.OH; p.OW = q.OW; p.o_step = q.o_step; p.o_off_h = q.o_off_h; p.o_off_w = q.o_off_w;

@@ -1,6 +1,7 @@
 // layers.cu — PReLU, BatchNorm, softmax-over-branches, MiniBatchStdDev, BCE, separable resampling.
 // All HBM-bound; see DESIGN.md for the per-kernel algorithmic bytes.
 #include "common.cuh"
+#include <algorithm>
 
 namespace ganb200 {
 
@@ -329,12 +330,14 @@ __global__ void __launch_bounds__(256) softmax_m_bwd_kernel(const float* __restr
   }
 }
 
-// ------------------------------------------------------------------ MiniBatchStdDev scalar, x as [G,L], G <= 16
+// ------------------------------------------------------------------ MiniBatchStdDev scalar, x as [G,L]
 // MODE 0 fwd: out[0] += sum_j sigma_j / L
 // MODE 1 bwd: gx[q,j] = g * (x_qj - mu_j) / ((G-1) L sigma_j)
 // MODE 2 bwd_bwd: out[0] += sum ggx_qj (x_qj-mu_j)/((G-1) L sigma_j);
 //                 gx[r,j] = g/((G-1)L) * ((ggx_rj - mean_q ggx_qj)/sigma_j - (x_rj-mu_j)/((G-1) sigma_j^3) * sum_q ggx_qj (x_qj-mu_j))
-template <int MODE>
+// REG: the G values of a column live in registers (G <= 16); otherwise they are re-read (L2 hits; the columns of a
+// warp are contiguous so every pass is coalesced).
+template <int MODE, bool REG>
 __global__ void __launch_bounds__(256) mbstd_kernel(const float* __restrict__ g, const float* __restrict__ x,
                                                     const float* __restrict__ ggx, float* __restrict__ out,
                                                     float* __restrict__ gx, int G, int64_t L, float eps) {
@@ -342,27 +345,44 @@ __global__ void __launch_bounds__(256) mbstd_kernel(const float* __restrict__ g,
   float gv = MODE >= 1 ? g[0] : 0.f;
   float invL = 1.f / (float)L, invG1 = 1.f / (float)(G - 1);
   for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < L; j += (int64_t)gridDim.x * blockDim.x) {
-    float xv[16];
+    float xv[REG ? 16 : 1];
     float mu = 0.f;
-    for (int q = 0; q < G; ++q) { xv[q] = x[(int64_t)q * L + j]; mu += xv[q]; }
+    for (int q = 0; q < G; ++q) {
+      float v = x[(int64_t)q * L + j];
+      if (REG) xv[q] = v;
+      mu += v;
+    }
     mu /= (float)G;
     float ss = 0.f;
-    for (int q = 0; q < G; ++q) { xv[q] -= mu; ss += xv[q] * xv[q]; }
+    for (int q = 0; q < G; ++q) {
+      float d = (REG ? xv[q] : x[(int64_t)q * L + j]) - mu;
+      if (REG) xv[q] = d;
+      ss += d * d;
+    }
     float sigma = sqrtf(ss * invG1 + eps);
     if (MODE == 0) {
       acc += sigma * invL;
     } else if (MODE == 1) {
       float k = gv * invG1 * invL / sigma;
-      for (int q = 0; q < G; ++q) gx[(int64_t)q * L + j] = k * xv[q];
+      for (int q = 0; q < G; ++q) gx[(int64_t)q * L + j] = k * (REG ? xv[q] : x[(int64_t)q * L + j] - mu);
     } else {
-      float gg[16];
+      float gg[REG ? 16 : 1];
       float gmean = 0.f, dot = 0.f;
-      for (int q = 0; q < G; ++q) { gg[q] = ggx[(int64_t)q * L + j]; gmean += gg[q]; dot += gg[q] * xv[q]; }
+      for (int q = 0; q < G; ++q) {
+        float v = ggx[(int64_t)q * L + j];
+        if (REG) gg[q] = v;
+        gmean += v;
+        dot += v * (REG ? xv[q] : x[(int64_t)q * L + j] - mu);
+      }
       gmean /= (float)G;
       acc += dot * invG1 * invL / sigma;
       float k = gv * invG1 * invL;
       float c3 = dot * invG1 / (sigma * sigma * sigma);
-      for (int q = 0; q < G; ++q) gx[(int64_t)q * L + j] = k * ((gg[q] - gmean) / sigma - xv[q] * c3);
+      for (int q = 0; q < G; ++q) {
+        float d = REG ? xv[q] : x[(int64_t)q * L + j] - mu;
+        float gq = REG ? gg[q] : ggx[(int64_t)q * L + j];
+        gx[(int64_t)q * L + j] = k * ((gq - gmean) / sigma - d * c3);
+      }
     }
   }
   if (MODE != 1) {
@@ -420,6 +440,34 @@ __global__ void __launch_bounds__(256) resample2d_kernel(const float* __restrict
   }
 }
 
+// Same operator for "few outputs, many taps" (AdaptiveAvgPool2d(5) of a 64x64 map: 25 outputs x 169 taps per plane):
+// one block per plane, the plane staged in shared memory with coalesced loads, one warp per output reducing its taps.
+__global__ void __launch_bounds__(256) resample2d_plane_kernel(const float* __restrict__ x, float* __restrict__ y,
+                                                               int64_t NC, int Hi, int Wi, int Ho, int Wo,
+                                                               const int* __restrict__ ih, const float* __restrict__ wh,
+                                                               int Th, const int* __restrict__ iw,
+                                                               const float* __restrict__ ww, int Tw) {
+  extern __shared__ float plane[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int HWi = Hi * Wi, T = Th * Tw;
+  for (int64_t nc = blockIdx.x; nc < NC; nc += gridDim.x) {
+    const float* xp = x + nc * HWi;
+    __syncthreads();
+    for (int i = threadIdx.x; i < HWi; i += 256) plane[i] = xp[i];
+    __syncthreads();
+    for (int o = warp; o < Ho * Wo; o += 8) {
+      const int ho = o / Wo, wo = o - ho * Wo;
+      float acc = 0.f;
+      for (int t = lane; t < T; t += 32) {
+        const int a = t / Tw, b = t - a * Tw;
+        acc = fmaf(wh[ho * Th + a] * ww[wo * Tw + b], plane[ih[ho * Th + a] * Wi + iw[wo * Tw + b]], acc);
+      }
+      acc = warp_sum(acc);
+      if (lane == 0) y[nc * Ho * Wo + o] = acc;
+    }
+  }
+}
+
 __global__ void __launch_bounds__(256) mixup_kernel(const float* __restrict__ t, const float* __restrict__ f, float lam,
                                                     float* __restrict__ out, int64_t n) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
@@ -457,25 +505,28 @@ extern "C" int ganb200_softmax_m_bwd(const float* gy, const float* y, float* gx,
 }
 
 extern "C" int ganb200_mbstd_fwd(const float* x, float* out, int G, int64_t L, float eps, void* stream) {
-  GB_REQUIRE(G >= 2 && G <= 16 && L > 0, GANB200_BAD_SHAPE, "mbstd: need 2<=G<=16");
+  GB_REQUIRE(G >= 2 && L > 0, GANB200_BAD_SHAPE, "mbstd: need G>=2");
   cudaStream_t s = (cudaStream_t)stream;
   GB_CHECK_CUDA(cudaMemsetAsync(out, 0, sizeof(float), s));
-  mbstd_kernel<0><<<ew_grid(L, 256, 1), 256, 0, s>>>(nullptr, x, nullptr, out, nullptr, G, L, eps);
+  if (G <= 16) mbstd_kernel<0, true><<<ew_grid(L, 256, 1), 256, 0, s>>>(nullptr, x, nullptr, out, nullptr, G, L, eps);
+  else mbstd_kernel<0, false><<<ew_grid(L, 256, 1), 256, 0, s>>>(nullptr, x, nullptr, out, nullptr, G, L, eps);
   GB_CHECK_LAUNCH();
   return 0;
 }
 extern "C" int ganb200_mbstd_bwd(const float* g, const float* x, float* gx, int G, int64_t L, float eps, void* stream) {
-  GB_REQUIRE(G >= 2 && G <= 16 && L > 0, GANB200_BAD_SHAPE, "mbstd: need 2<=G<=16");
-  mbstd_kernel<1><<<ew_grid(L, 256, 1), 256, 0, (cudaStream_t)stream>>>(g, x, nullptr, nullptr, gx, G, L, eps);
+  GB_REQUIRE(G >= 2 && L > 0, GANB200_BAD_SHAPE, "mbstd: need G>=2");
+  if (G <= 16) mbstd_kernel<1, true><<<ew_grid(L, 256, 1), 256, 0, (cudaStream_t)stream>>>(g, x, nullptr, nullptr, gx, G, L, eps);
+  else mbstd_kernel<1, false><<<ew_grid(L, 256, 1), 256, 0, (cudaStream_t)stream>>>(g, x, nullptr, nullptr, gx, G, L, eps);
   GB_CHECK_LAUNCH();
   return 0;
 }
 extern "C" int ganb200_mbstd_bwd_bwd(const float* g, const float* x, const float* ggx, float* out_gg, float* out_gx,
                                      int G, int64_t L, float eps, void* stream) {
-  GB_REQUIRE(G >= 2 && G <= 16 && L > 0, GANB200_BAD_SHAPE, "mbstd: need 2<=G<=16");
+  GB_REQUIRE(G >= 2 && L > 0, GANB200_BAD_SHAPE, "mbstd: need G>=2");
   cudaStream_t s = (cudaStream_t)stream;
   GB_CHECK_CUDA(cudaMemsetAsync(out_gg, 0, sizeof(float), s));
-  mbstd_kernel<2><<<ew_grid(L, 256, 1), 256, 0, s>>>(g, x, ggx, out_gg, out_gx, G, L, eps);
+  if (G <= 16) mbstd_kernel<2, true><<<ew_grid(L, 256, 1), 256, 0, s>>>(g, x, ggx, out_gg, out_gx, G, L, eps);
+  else mbstd_kernel<2, false><<<ew_grid(L, 256, 1), 256, 0, s>>>(g, x, ggx, out_gg, out_gx, G, L, eps);
   GB_CHECK_LAUNCH();
   return 0;
 }
@@ -500,7 +551,14 @@ extern "C" int ganb200_resample2d(const float* x, float* y, int NC, int Hi, int 
   int64_t total = (int64_t)NC * Ho * Wo;
   if (total == 0) return 0;
   GB_REQUIRE(Th > 0 && Tw > 0, GANB200_BAD_SHAPE, "resample2d: empty tap table");
-  resample2d_kernel<<<ew_grid(total, 256, 2), 256, 0, (cudaStream_t)stream>>>(x, y, NC, Hi, Wi, Ho, Wo, ih, wh, Th, iw, ww, Tw);
+  if (Ho * Wo <= 64 && Th * Tw >= 16 && (size_t)Hi * Wi * sizeof(float) <= 40 * 1024) {
+    int grid = (int)std::min<int64_t>(NC, (int64_t)kNumSMs * 8);
+    resample2d_plane_kernel<<<grid, 256, sizeof(float) * Hi * Wi, (cudaStream_t)stream>>>(x, y, NC, Hi, Wi, Ho, Wo, ih,
+                                                                                         wh, Th, iw, ww, Tw);
+  } else {
+    resample2d_kernel<<<ew_grid(total, 256, 2), 256, 0, (cudaStream_t)stream>>>(x, y, NC, Hi, Wi, Ho, Wo, ih, wh, Th, iw,
+                                                                               ww, Tw);
+  }
   GB_CHECK_LAUNCH();
   return 0;
 }

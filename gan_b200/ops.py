@@ -10,6 +10,7 @@ Ops only needed by the generator (BatchNorm, softmax over branches, modulated co
 once-differentiable: the reference never differentiates G twice.
 """
 from collections import namedtuple
+import math
 
 import torch
 from torch.autograd import Function
@@ -585,7 +586,20 @@ def minibatch_stddev(x, group_size=4, eps=1e-8):
     if _mbstd_reduce[0] is not None:  # data parallel: mean of the rank-local scalars (gan_b200.dist)
         s = _mbstd_reduce[0](s)
     plane = AddBcFn.apply(torch.zeros((b, 1, h, w), dtype=x.dtype, device=x.device), s, KN.V_SCALAR)
-    return torch.cat([x, plane], dim=1)
+    return cat_channels([x, plane])
+
+
+def batch_stddev(x, eps=10e-8):
+    """ProGAN minibatch-stddev channel (discriminators/discriminator_3_wgangp_progan.py:7-16): per-position *biased*
+    std over the whole batch, averaged to one scalar, appended as a constant plane.  Same kernel as MbStdFn with
+    G = batch: sqrt(var_b + eps) = sqrt((G-1)/G) * sqrt(var_u + eps*G/(G-1))."""
+    b, _, h, w = x.shape
+    if b < 2:  # var over a single sample is 0 -> sqrt(eps); no gradient path in the reference either (d/dx of 0)
+        raise ValueError("batch_stddev needs a batch of at least 2")
+    s = MbStdFn.apply(x, b, eps * b / (b - 1.0))
+    s = affine(s, math.sqrt((b - 1.0) / b), 0.0)
+    plane = AddBcFn.apply(torch.zeros((b, 1, h, w), dtype=x.dtype, device=x.device), s, KN.V_SCALAR)
+    return cat_channels([x, plane])
 
 
 # =====================================================================================================

@@ -1,0 +1,115 @@
+"""TEST INFRASTRUCTURE — golden vectors of the other BASELINE configs, produced by running
+the UNMODIFIED reference (/root/reference through oracle/reference.py) on CPU fp32 with fixed seeds.
+
+    python -m oracle.make_golden_configs [cfg1 cfg4 cfg5]     (build container only)
+
+writes tests/golden/<cfg>.pt.  Recipe per config (the same the tests replay with the drop-in modules):
+  seed 0 -> construct G then D (weights = pure function of the seed; not stored);
+  x, z from torch.Generator(123);  D(x) and G(z) in train mode, recorded in full;
+  fresh models (seed 0 again), Train(...) of the config's loop, seed 1, one discriminator_trainstep + one
+  generator_trainstep: every returned loss, the norm of every parameter's UPDATE (after - before) and of every buffer.
+"""
+import os
+import random
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+# name -> (generator module, ctor, discriminator module, ctor, train module, batch, image shape)
+CONFIGS = {
+    "cfg1": dict(gen="generators.generator_1", g_args=lambda: (256, (3, 64, 64)), g_kw={},
+                 dis="discriminators.discriminator_1", d_args=lambda: ((3, 64, 64),), d_kw={},
+                 train="train.gan", B=8, names=("G1", "D1")),
+    "cfg4": dict(gen="generators.generator_3_progan", g_args=lambda: (1, 256, 256, 3), g_kw={},
+                 dis="discriminators.discriminator_3_wgangp_progan", d_args=lambda: (1, 64, 3), d_kw={},
+                 train="train.wgangp", B=4, names=("G3_PROGAN", "D3_WGAN_PROGAN")),
+    "cfg5": dict(gen="generators.generator_14", g_args=lambda: (256,), g_kw={},
+                 dis="discriminators.discriminator_7_wgangpsn", d_args=lambda: (), d_kw={},
+                 train="train.wgangpsnR2", B=4, names=("G14", "D7_WGANSN")),
+}
+
+
+def seed_all(s):
+    torch.manual_seed(s)
+    np.random.seed(s)
+    random.seed(s)
+
+
+def build(cfg, genmod, dismod):
+    seed_all(0)
+    G = genmod.Generator(*cfg["g_args"](), **cfg["g_kw"])
+    D = dismod.Discriminator(*cfg["d_args"](), **cfg["d_kw"])
+    return G, D
+
+
+def snapshot(model):
+    return {n: p.detach().clone() for n, p in model.named_parameters()}
+
+
+def update_norms(model, before):
+    return {n: float((p.detach().double() - before[n].double()).norm()) for n, p in model.named_parameters()}
+
+
+def buffer_norms(model):
+    return {n: float(b.detach().double().norm()) for n, b in model.named_buffers()}
+
+
+def replay(cfg, genmod, dismod, trainmod, device=torch.device("cpu"), x=None, z=None):
+    """Runs the recipe with whatever modules it is given (the reference here, the drop-in in the tests)."""
+    B = cfg["B"]
+    out = {"B": B}
+    if x is None:
+        gx = torch.Generator().manual_seed(123)
+        x = torch.randn(B, 3, 64, 64, generator=gx).clamp_(-1, 1)
+        z = torch.randn(B, 256, 1, 1, generator=gx)
+    out["x"], out["z"] = x, z
+    xd, zd = x.to(device), z.to(device)
+    G, D = build(cfg, genmod, dismod)
+    G, D = G.to(device), D.to(device)
+    out["param_names_g"] = [n for n, _ in G.named_parameters()]
+    out["param_names_d"] = [n for n, _ in D.named_parameters()]
+    out["state_keys_g"] = list(G.state_dict().keys())
+    out["state_keys_d"] = list(D.state_dict().keys())
+    out["init_norms_g"] = {n: float(p.detach().double().norm()) for n, p in G.named_parameters()}
+    out["init_norms_d"] = {n: float(p.detach().double().norm()) for n, p in D.named_parameters()}
+    with torch.no_grad():
+        out["d_out"] = D(xd).detach().cpu().clone()
+        out["g_out"] = G(zd).detach().cpu().clone()
+    # one full iteration on fresh models
+    G, D = build(cfg, genmod, dismod)
+    G, D = G.to(device), D.to(device)
+    T = trainmod.Train([(xd, torch.zeros(B))], device, 1, 256, G, cfg["names"][0], D, cfg["names"][1])
+    g0, d0 = snapshot(G), snapshot(D)
+    seed_all(1)
+    xi = xd.clone().requires_grad_()
+    d_ret = T.discriminator_trainstep(xi, B)
+    out["step_d_losses"] = [float(v.detach()) for v in d_ret]
+    gen_imgs, g_loss = T.generator_trainstep(B)
+    out["step_g_loss"] = float(g_loss.detach())
+    out["step_gen_imgs_norm"] = float(gen_imgs.detach().double().norm())
+    out["step_d_updates"] = update_norms(D, d0)
+    out["step_g_updates"] = update_norms(G, g0)
+    out["step_d_buffers"] = buffer_norms(D)
+    out["step_g_buffers"] = buffer_norms(G)
+    return out
+
+
+def main(argv):
+    from oracle import reference as R
+    for name in (argv or ["cfg1", "cfg4"]):
+        cfg = CONFIGS[name]
+        out = replay(cfg, R.load(cfg["gen"]), R.load(cfg["dis"]), R.load(cfg["train"]))
+        out["torch"] = torch.__version__
+        path = os.path.join(ROOT, "tests", "golden", name + ".pt")
+        torch.save(out, path)
+        print("wrote", path, os.path.getsize(path), "bytes;", "d losses", out["step_d_losses"], "g loss",
+              out["step_g_loss"])
+
+
+if __name__ == "__main__":
+    main(sys.argv[1:])

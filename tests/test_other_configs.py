@@ -1,0 +1,88 @@
+"""The other BASELINE configs against golden vectors recorded from the UNMODIFIED
+reference (oracle/make_golden_configs.py -> tests/golden/cfg*.pt): identical parameter names and registration order,
+identical seeded initial weights, D(x) and G(z), and one full iteration of the config's own loop (train/gan.py,
+train/wgangp.py, train/wgangpsnR2.py): every loss, the norm of every parameter's update and of every buffer.
+
+CPU: drop-in modules on the CPU restatement of the kernels.  GPU: the same through libganb200, fp32 engine and the
+bf16 tcgen05 engine (tolerances stated per test)."""
+import importlib
+import os
+import re
+
+import pytest
+import torch
+
+from oracle.make_golden_configs import CONFIGS, replay
+
+# Parameters whose gradient is analytically zero (a bias added right before a BatchNorm): what reaches Adam is fp32
+# rounding noise (~1e-9), which Adam's normalisation turns into an O(lr) update of arbitrary sign whatever the
+# implementation (the CPU port differs from the reference by up to 40 % there and by < 2e-3 everywhere else).  They
+# are excluded from the update-norm comparison.
+NOISE_PARAMS = {"cfg1": None, "cfg4": re.compile(r"^main\.\d\.0\.bias$"), "cfg5": None}
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def rel(a, b):
+    a, b = torch.as_tensor(a, dtype=torch.float64), torch.as_tensor(b, dtype=torch.float64)
+    return float((a - b).norm() / b.norm().clamp_min(1e-30))
+
+
+def compare(name, device, tol_out, tol_loss, tol_upd, floor=1e-6):
+    from gan_b200 import rng
+    cfg = CONFIGS[name]
+    gold = torch.load(os.path.join(GOLDEN, name + ".pt"), weights_only=False)
+    mods = [importlib.import_module(cfg[k]) for k in ("gen", "dis", "train")]
+    prev = rng.host_stream(True)
+    try:
+        got = replay(cfg, *mods, device=device, x=gold["x"], z=gold["z"])
+    finally:
+        rng.host_stream(prev)
+    bad = []
+    for k in ("param_names_g", "param_names_d", "state_keys_g", "state_keys_d"):
+        if got[k] != gold[k]:
+            bad.append((k, [a for a in gold[k] if a not in got[k]][:5], [a for a in got[k] if a not in gold[k]][:5]))
+    for k in ("init_norms_g", "init_norms_d"):  # same seed, same construction order -> same weights
+        for n, w in gold[k].items():
+            if abs(got[k].get(n, float("nan")) - w) > 1e-5 * max(abs(w), 1e-3):
+                bad.append((k, n, got[k].get(n), w))
+    for k in ("d_out", "g_out"):
+        e = rel(got[k], gold[k])
+        if not e < tol_out:
+            bad.append((k, e))
+    for g, w in zip(got["step_d_losses"] + [got["step_g_loss"]], gold["step_d_losses"] + [gold["step_g_loss"]]):
+        if not abs(g - w) <= tol_loss * max(abs(w), 1e-2):
+            bad.append(("loss", g, w))
+    e = abs(got["step_gen_imgs_norm"] - gold["step_gen_imgs_norm"]) / gold["step_gen_imgs_norm"]
+    if not e < tol_out:
+        bad.append(("step_gen_imgs_norm", e))
+    for k in ("step_d_updates", "step_g_updates", "step_d_buffers", "step_g_buffers"):
+        for n, w in gold[k].items():
+            g = got[k][n]
+            if k == "step_g_updates" and NOISE_PARAMS[name] is not None and NOISE_PARAMS[name].match(n):
+                continue
+            if not abs(g - w) <= tol_upd * max(abs(w), floor) + floor:
+                bad.append((k, n, g, w))
+    assert not bad, bad[:20]
+    return got
+
+
+@pytest.mark.parametrize("name", ["cfg1", "cfg4"])
+def test_config_cpu_port_matches_reference_golden(ref_backend, name):
+    compare(name, torch.device("cpu"), tol_out=1e-4, tol_loss=1e-4, tol_upd=2e-3)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["cfg1", "cfg4"])
+def test_config_cuda_fp32_matches_reference_golden(monkeypatch, name):
+    monkeypatch.setenv("GANB200_PRECISION", "fp32")
+    compare(name, torch.device("cuda"), tol_out=2e-4, tol_loss=2e-4, tol_upd=5e-3)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["cfg1", "cfg4"])
+def test_config_cuda_tcgen05_matches_reference_golden(monkeypatch, name):
+    """bf16 operands, fp32 accumulation: north_star's 1e-2 class on outputs and losses.  Adam's first update is
+    lr*sign(g)-like (|update| ~ lr per element whatever the gradient scale), so the update norms stay tight."""
+    monkeypatch.setenv("GANB200_PRECISION", "auto")
+    compare(name, torch.device("cuda"), tol_out=1e-2, tol_loss=2e-2, tol_upd=2e-2)
