@@ -78,6 +78,14 @@ SIGNATURES = {
     "ganb200_modconv_bwd": (c_int, [_DESC_P, P, P, P, P, P, P, P, P, P, c_size_t, P]),
     "ganb200_scale_reduce": (c_int, [P, P, P, P, P, c_int, c_int, c_int, P]),
     "ganb200_spectral_power_iter": (c_int, [P, P, P, P, c_int, c_int, c_int, c_float, P]),
+    "ganb200_spectral_power_iter_batched": (c_int, [P, c_int, c_int, c_int, c_float, P]),
+    "ganb200_spectral_scale": (c_int, [P, P, P, c_int64, P]),
+    "ganb200_spectral_scale_bwd": (c_int, [P, P, P, P, P, P, P, c_int, c_int, P]),
+    "ganb200_dwconv2d_fprop": (c_int, [P, P, P, P] + [c_int] * 8 + [c_float, P]),
+    "ganb200_dwconv2d_dgrad": (c_int, [P, P, P] + [c_int] * 8 + [c_float, P]),
+    "ganb200_dwconv2d_wgrad_workspace_bytes": (c_int64, [c_int, c_int]),
+    "ganb200_dwconv2d_wgrad": (c_int, [P, P, P, P, c_int64] + [c_int] * 8 + [c_float, P]),
+    "ganb200_chan_shuffle": (c_int, [P, P, c_int, c_int, c_int, c_int, P]),
 }
 
 _lib = None

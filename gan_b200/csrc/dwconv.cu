@@ -1,0 +1,220 @@
+// dwconv.cu — depthwise 3x3 convolution family (fprop / dgrad / wgrad) and channel shuffle, fp32 NCHW.
+// Used by discriminators/discriminator_7_wgangpsn.py:55,61,72 (ShuffleNetV2 units: Conv2d(C,C,3,stride,padding=1,
+// groups=C)) and :27-41 (channel_shuffle).  One multiply-add per 4 bytes moved: these are HBM-bound streaming kernels
+// (algorithmic bytes = 4 B read per input element + 4 B written per output element; the 3x3 window re-reads hit L1),
+// they stay on CUDA cores.  The three kernels are each other's derivatives (bilinear map), so the autograd
+// Functions in gan_b200/ops.py are closed under double backward exactly as for the dense convs.
+#include "common.cuh"
+
+namespace ganb200 {
+
+// y[n,c,p,q] = alpha * sum_{r,s} w[c,r,s] * x[n,c,p*st-pad+r, q*st-pad+s] + bias[c]
+template <int ST>
+__global__ void __launch_bounds__(256) dw3_fprop_kernel(const float* __restrict__ x, const float* __restrict__ w,
+                                                        const float* __restrict__ bias, float* __restrict__ y, int NC,
+                                                        int C, int H, int W, int P, int Q, int pad, float alpha) {
+  int64_t total = (int64_t)NC * P * Q;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    int q = (int)(i % Q);
+    int64_t t = i / Q;
+    int p = (int)(t % P);
+    int nc = (int)(t / P);
+    int c = nc % C;
+    const float* xp = x + (int64_t)nc * H * W;
+    const float* wp = w + c * 9;
+    int h0 = p * ST - pad, w0 = q * ST - pad;
+    float acc = 0.f;
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      int h = h0 + r;
+      if ((unsigned)h >= (unsigned)H) continue;
+#pragma unroll
+      for (int s = 0; s < 3; ++s) {
+        int ww = w0 + s;
+        if ((unsigned)ww < (unsigned)W) acc = fmaf(__ldg(wp + r * 3 + s), __ldg(xp + h * W + ww), acc);
+      }
+    }
+    y[i] = alpha * acc + (bias ? __ldg(bias + c) : 0.f);
+  }
+}
+
+// dx[n,c,h,w] = alpha * sum_{r,s} w[c,r,s] * dy[n,c,(h+pad-r)/st,(w+pad-s)/st]   (where divisible and in range)
+template <int ST>
+__global__ void __launch_bounds__(256) dw3_dgrad_kernel(const float* __restrict__ dy, const float* __restrict__ w,
+                                                        float* __restrict__ dx, int NC, int C, int H, int W, int P,
+                                                        int Q, int pad, float alpha) {
+  int64_t total = (int64_t)NC * H * W;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    int ww = (int)(i % W);
+    int64_t t = i / W;
+    int h = (int)(t % H);
+    int nc = (int)(t / H);
+    int c = nc % C;
+    const float* gp = dy + (int64_t)nc * P * Q;
+    const float* wp = w + c * 9;
+    float acc = 0.f;
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      int ph = h + pad - r;
+      if (ph < 0 || (ST == 2 && (ph & 1))) continue;
+      int p = ph / ST;
+      if (p >= P) continue;
+#pragma unroll
+      for (int s = 0; s < 3; ++s) {
+        int pw = ww + pad - s;
+        if (pw < 0 || (ST == 2 && (pw & 1))) continue;
+        int q = pw / ST;
+        if (q < Q) acc = fmaf(__ldg(wp + r * 3 + s), __ldg(gp + p * Q + q), acc);
+      }
+    }
+    dx[i] = alpha * acc;
+  }
+}
+
+// partial[split][c][9] = sum over the split's samples and all (p,q) of dy[n,c,p,q] * x[n,c,p*st-pad+r,q*st-pad+s]
+// grid (C, splits); a warp walks output rows so both reads are coalesced.
+template <int ST>
+__global__ void __launch_bounds__(256) dw3_wgrad_kernel(const float* __restrict__ x, const float* __restrict__ dy,
+                                                        float* __restrict__ partial, int N, int C, int H, int W, int P,
+                                                        int Q, int pad) {
+  const int c = blockIdx.x, split = blockIdx.y, splits = gridDim.y;
+  float acc[9];
+#pragma unroll
+  for (int k = 0; k < 9; ++k) acc[k] = 0.f;
+  const int PQ = P * Q;
+  for (int n = split; n < N; n += splits) {
+    const float* xp = x + ((int64_t)n * C + c) * H * W;
+    const float* gp = dy + ((int64_t)n * C + c) * PQ;
+    for (int i = threadIdx.x; i < PQ; i += 256) {
+      int p = i / Q, q = i - p * Q;
+      float g = __ldg(gp + i);
+      int h0 = p * ST - pad, w0 = q * ST - pad;
+#pragma unroll
+      for (int r = 0; r < 3; ++r) {
+        int h = h0 + r;
+        if ((unsigned)h >= (unsigned)H) continue;
+#pragma unroll
+        for (int s = 0; s < 3; ++s) {
+          int ww = w0 + s;
+          if ((unsigned)ww < (unsigned)W) acc[r * 3 + s] = fmaf(g, __ldg(xp + h * W + ww), acc[r * 3 + s]);
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 9; ++k) {
+    float t = block_sum<256>(acc[k]);
+    if (threadIdx.x == 0) partial[((int64_t)split * C + c) * 9 + k] = t;
+  }
+}
+
+// dw[c][k] = alpha * sum_split partial[split][c][k]   (fixed order: deterministic)
+__global__ void __launch_bounds__(256) dw3_wgrad_reduce_kernel(const float* __restrict__ partial, float* __restrict__ dw,
+                                                               int C9, int splits, float alpha) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= C9) return;
+  float acc = 0.f;
+  for (int s = 0; s < splits; ++s) acc += partial[(int64_t)s * C9 + i];
+  dw[i] = alpha * acc;
+}
+
+// channel shuffle: y[n, j*G + i] = x[n, i*(C/G) + j]
+__global__ void __launch_bounds__(256) chan_shuffle_kernel(const float* __restrict__ x, float* __restrict__ y, int N,
+                                                           int C, int HW4, int G, bool vec) {
+  int64_t total = (int64_t)N * C * HW4;
+  int cpg = C / G;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    int e = (int)(i % HW4);
+    int64_t t = i / HW4;
+    int co = (int)(t % C);
+    int n = (int)(t / C);
+    int ci = (co % G) * cpg + co / G;
+    int64_t src = ((int64_t)n * C + ci) * HW4 + e;
+    if (vec)
+      reinterpret_cast<float4*>(y)[i] = __ldg(reinterpret_cast<const float4*>(x) + src);
+    else
+      y[i] = __ldg(x + src);
+  }
+}
+
+static int dw_check(int N, int C, int H, int W, int R, int S, int stride, int pad, int* P, int* Q) {
+  GB_REQUIRE(N > 0 && C > 0 && H > 0 && W > 0, GANB200_BAD_SHAPE, "dwconv: empty tensor");
+  GB_REQUIRE(R == 3 && S == 3, GANB200_BAD_SHAPE, "dwconv: only 3x3 kernels (discriminator_7_wgangpsn.py)");
+  GB_REQUIRE(stride == 1 || stride == 2, GANB200_BAD_SHAPE, "dwconv: stride must be 1 or 2");
+  GB_REQUIRE(pad >= 0 && pad <= 2, GANB200_BAD_SHAPE, "dwconv: pad must be 0..2");
+  *P = (H + 2 * pad - 3) / stride + 1;
+  *Q = (W + 2 * pad - 3) / stride + 1;
+  GB_REQUIRE(*P > 0 && *Q > 0, GANB200_BAD_SHAPE, "dwconv: empty output");
+  return 0;
+}
+
+}  // namespace ganb200
+using namespace ganb200;
+
+extern "C" int ganb200_dwconv2d_fprop(const float* x, const float* w, const float* bias, float* y, int N, int C, int H,
+                                      int W, int R, int S, int stride, int pad, float alpha, void* stream) {
+  int P, Q;
+  if (int rc = dw_check(N, C, H, W, R, S, stride, pad, &P, &Q)) return rc;
+  int64_t total = (int64_t)N * C * P * Q;
+  int grid = ew_grid(total, 256, 2);
+  cudaStream_t s = (cudaStream_t)stream;
+  if (stride == 1)
+    dw3_fprop_kernel<1><<<grid, 256, 0, s>>>(x, w, bias, y, N * C, C, H, W, P, Q, pad, alpha);
+  else
+    dw3_fprop_kernel<2><<<grid, 256, 0, s>>>(x, w, bias, y, N * C, C, H, W, P, Q, pad, alpha);
+  GB_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int ganb200_dwconv2d_dgrad(const float* dy, const float* w, float* dx, int N, int C, int H, int W, int R,
+                                      int S, int stride, int pad, float alpha, void* stream) {
+  int P, Q;
+  if (int rc = dw_check(N, C, H, W, R, S, stride, pad, &P, &Q)) return rc;
+  int64_t total = (int64_t)N * C * H * W;
+  int grid = ew_grid(total, 256, 2);
+  cudaStream_t s = (cudaStream_t)stream;
+  if (stride == 1)
+    dw3_dgrad_kernel<1><<<grid, 256, 0, s>>>(dy, w, dx, N * C, C, H, W, P, Q, pad, alpha);
+  else
+    dw3_dgrad_kernel<2><<<grid, 256, 0, s>>>(dy, w, dx, N * C, C, H, W, P, Q, pad, alpha);
+  GB_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int64_t ganb200_dwconv2d_wgrad_workspace_bytes(int N, int C) {
+  int splits = (4 * kNumSMs + C - 1) / C;
+  if (splits > N) splits = N;
+  if (splits < 1) splits = 1;
+  return (int64_t)splits * C * 9 * sizeof(float);
+}
+
+extern "C" int ganb200_dwconv2d_wgrad(const float* x, const float* dy, float* dw, void* workspace,
+                                      int64_t workspace_bytes, int N, int C, int H, int W, int R, int S, int stride,
+                                      int pad, float alpha, void* stream) {
+  int P, Q;
+  if (int rc = dw_check(N, C, H, W, R, S, stride, pad, &P, &Q)) return rc;
+  int64_t need = ganb200_dwconv2d_wgrad_workspace_bytes(N, C);
+  GB_REQUIRE(workspace != nullptr && workspace_bytes >= need, GANB200_BAD_SHAPE, "dwconv wgrad: workspace too small");
+  int splits = (int)(need / ((int64_t)C * 9 * sizeof(float)));
+  cudaStream_t s = (cudaStream_t)stream;
+  dim3 grid(C, splits);
+  float* partial = (float*)workspace;
+  if (stride == 1)
+    dw3_wgrad_kernel<1><<<grid, 256, 0, s>>>(x, dy, partial, N, C, H, W, P, Q, pad);
+  else
+    dw3_wgrad_kernel<2><<<grid, 256, 0, s>>>(x, dy, partial, N, C, H, W, P, Q, pad);
+  dw3_wgrad_reduce_kernel<<<ceil_div(C * 9, 256), 256, 0, s>>>(partial, dw, C * 9, splits, alpha);
+  GB_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int ganb200_chan_shuffle(const float* x, float* y, int N, int C, int HW, int groups, void* stream) {
+  if ((int64_t)N * C * HW <= 0) return 0;
+  GB_REQUIRE(groups >= 1 && C % groups == 0, GANB200_BAD_SHAPE, "chan_shuffle: C must be a multiple of groups");
+  bool vec = ((HW & 3) == 0) && ((((uintptr_t)x) | ((uintptr_t)y)) & 15) == 0;
+  int HW4 = vec ? HW / 4 : HW;
+  int64_t total = (int64_t)N * C * HW4;
+  chan_shuffle_kernel<<<ew_grid(total, 256, 2), 256, 0, (cudaStream_t)stream>>>(x, y, N, C, HW4, groups, vec);
+  GB_CHECK_LAUNCH();
+  return 0;
+}

@@ -38,62 +38,113 @@ __global__ void counter_add_kernel(int64_t* ctr, int64_t inc) {
   if (threadIdx.x == 0 && blockIdx.x == 0) *ctr += inc;
 }
 
-// One CTA per weight matrix would be enough for D7's small convs; here one CTA runs the whole iteration for one
-// matrix: v = normalize(W^T u); u = normalize(W v); sigma = u . (W v).  rows x cols is at most a few 10^5 elements.
-__global__ void __launch_bounds__(256) spectral_power_iter_kernel(const float* __restrict__ W, float* __restrict__ u,
-                                                                  float* __restrict__ v, float* __restrict__ sigma,
-                                                                  int rows, int cols, int n_iter, float eps) {
-  extern __shared__ float sm[];  // [cols] for v-candidate, [rows] for u-candidate
-  float* sv = sm;
-  float* su = sm + cols;
+// Spectral-norm power iteration, torch.nn.utils.parametrizations._SpectralNorm._power_method order:
+//   u = normalize(W v);  v = normalize(W^T u);  (n_iter times)   sigma = u . (W v)
+// One CTA per weight matrix (blockIdx.x indexes a table of matrices so that all the spectrally-normalised convs of a
+// model advance in ONE launch); u and v live in shared memory for the whole iteration.
+struct SpectralJob {
+  const float* W;
+  float* u;
+  float* v;
+  float* sigma;
+  int rows, cols;
+};
+
+__device__ __forceinline__ void spectral_Wv(const float* __restrict__ W, const float* sv, float* su, int rows, int cols,
+                                            int tid, int nt) {
+  int lane = tid & 31, wid = tid >> 5, nw = nt >> 5;
+  for (int r = wid; r < rows; r += nw) {  // one warp per row, coalesced along the row
+    float acc = 0.f;
+    for (int c = lane; c < cols; c += 32) acc = fmaf(W[(int64_t)r * cols + c], sv[c], acc);
+    acc = warp_sum(acc);
+    if (lane == 0) su[r] = acc;
+  }
+}
+
+__device__ __forceinline__ void spectral_normalize(float* x, int n, float eps, int tid, int nt) {
+  float n2 = 0.f;
+  for (int i = tid; i < n; i += nt) n2 = fmaf(x[i], x[i], n2);
+  float tot = block_sum<256>(n2);
+  float inv = 1.f / fmaxf(sqrtf(tot), eps);
+  for (int i = tid; i < n; i += nt) x[i] *= inv;
+  __syncthreads();
+}
+
+__device__ void spectral_power_iter_body(const SpectralJob& job, int n_iter, float eps, float* sm) {
+  const float* __restrict__ W = job.W;
+  const int rows = job.rows, cols = job.cols;
+  float* sv = sm;          // [cols]
+  float* su = sm + cols;   // [rows]
+  float* st = su + rows;   // [rows] scratch for W v of the final sigma
   const int tid = threadIdx.x, nt = blockDim.x;
-  for (int i = tid; i < rows; i += nt) su[i] = u[i];
-  for (int i = tid; i < cols; i += nt) sv[i] = v[i];
+  for (int i = tid; i < rows; i += nt) su[i] = job.u[i];
+  for (int i = tid; i < cols; i += nt) sv[i] = job.v[i];
   __syncthreads();
   for (int it = 0; it < n_iter; ++it) {
-    // v = W^T u : column sums, coalesced over columns
-    float nrm = 0.f;
-    for (int c = tid; c < cols; c += nt) {
+    spectral_Wv(W, sv, su, rows, cols, tid, nt);
+    __syncthreads();
+    spectral_normalize(su, rows, eps, tid, nt);
+    for (int c = tid; c < cols; c += nt) {  // v = W^T u: thread per column, coalesced across the warp
       float acc = 0.f;
       for (int r = 0; r < rows; ++r) acc = fmaf(W[(int64_t)r * cols + c], su[r], acc);
       sv[c] = acc;
-      nrm = fmaf(acc, acc, nrm);
-    }
-    float tot = block_sum<256>(nrm);
-    float inv = 1.f / fmaxf(sqrtf(tot), eps);
-    for (int c = tid; c < cols; c += nt) sv[c] *= inv;
-    __syncthreads();
-    // u = W v : one warp per row
-    int lane = tid & 31, wid = tid >> 5, nw = nt >> 5;
-    for (int r = wid; r < rows; r += nw) {
-      float acc = 0.f;
-      for (int c = lane; c < cols; c += 32) acc = fmaf(W[(int64_t)r * cols + c], sv[c], acc);
-      acc = warp_sum(acc);
-      if (lane == 0) su[r] = acc;
     }
     __syncthreads();
-    float n2 = 0.f;
-    for (int r = tid; r < rows; r += nt) n2 = fmaf(su[r], su[r], n2);
-    float tot2 = block_sum<256>(n2);
-    float inv2 = 1.f / fmaxf(sqrtf(tot2), eps);
-    for (int r = tid; r < rows; r += nt) su[r] *= inv2;
-    __syncthreads();
+    spectral_normalize(sv, cols, eps, tid, nt);
   }
-  // sigma = u . (W v)
+  spectral_Wv(W, sv, st, rows, cols, tid, nt);
+  __syncthreads();
   float part = 0.f;
-  {
-    int lane = tid & 31, wid = tid >> 5, nw = nt >> 5;
-    for (int r = wid; r < rows; r += nw) {
-      float acc = 0.f;
-      for (int c = lane; c < cols; c += 32) acc = fmaf(W[(int64_t)r * cols + c], sv[c], acc);
-      acc = warp_sum(acc);
-      if (lane == 0) part = fmaf(acc, su[r], part);
-    }
-  }
+  for (int r = tid; r < rows; r += nt) part = fmaf(st[r], su[r], part);
   float s = block_sum<256>(part);
-  if (tid == 0) sigma[0] = s;
-  for (int i = tid; i < rows; i += nt) u[i] = su[i];
-  for (int i = tid; i < cols; i += nt) v[i] = sv[i];
+  if (tid == 0) job.sigma[0] = s;
+  for (int i = tid; i < rows; i += nt) job.u[i] = su[i];
+  for (int i = tid; i < cols; i += nt) job.v[i] = sv[i];
+}
+
+__global__ void __launch_bounds__(256) spectral_power_iter_kernel(SpectralJob job, int n_iter, float eps) {
+  extern __shared__ float sm[];
+  spectral_power_iter_body(job, n_iter, eps, sm);
+}
+
+__global__ void __launch_bounds__(256) spectral_power_iter_batched_kernel(const SpectralJob* __restrict__ jobs,
+                                                                          int n_iter, float eps) {
+  extern __shared__ float sm[];
+  SpectralJob job = jobs[blockIdx.x];
+  spectral_power_iter_body(job, n_iter, eps, sm);
+}
+
+// out = W / sigma[0]   (the parametrised weight)
+__global__ void __launch_bounds__(256) spectral_scale_kernel(const float* __restrict__ W, const float* __restrict__ sigma,
+                                                             float* __restrict__ out, int64_t n) {
+  float inv = 1.f / sigma[0];
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    out[i] = W[i] * inv;
+}
+
+// dot[0] = <G, W>   (zeroed by the caller)
+__global__ void __launch_bounds__(256) spectral_dot_kernel(const float* __restrict__ G, const float* __restrict__ W,
+                                                           float* __restrict__ dot, int64_t n) {
+  float acc = 0.f;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    acc = fmaf(G[i], W[i], acc);
+  float t = block_sum<256>(acc);
+  if (threadIdx.x == 0) atomicAdd(dot, t);
+}
+
+// gW[r,c] = G[r,c]/sigma - dot/sigma^2 * u[r] v[c]     (backward of W/sigma with sigma = u^T W v, u and v constants)
+__global__ void __launch_bounds__(256) spectral_scale_bwd_kernel(const float* __restrict__ G, const float* __restrict__ u,
+                                                                 const float* __restrict__ v,
+                                                                 const float* __restrict__ sigma,
+                                                                 const float* __restrict__ dot, float* __restrict__ gW,
+                                                                 int rows, int cols) {
+  float inv = 1.f / sigma[0];
+  float k = dot[0] * inv * inv;
+  int64_t n = (int64_t)rows * cols;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    int r = (int)(i / cols), c = (int)(i % cols);
+    gW[i] = G[i] * inv - k * u[r] * v[c];
+  }
 }
 
 }  // namespace ganb200
@@ -121,14 +172,61 @@ extern "C" int ganb200_counter_add(int64_t* counter, int64_t inc, void* stream) 
   return 0;
 }
 
+static int spectral_smem(int rows, int cols, size_t* out) {
+  size_t smem = sizeof(float) * ((size_t)2 * rows + cols);
+  GB_REQUIRE(smem <= 200 * 1024, GANB200_BAD_SHAPE, "spectral_power_iter: 2*rows+cols too large for one CTA");
+  *out = smem;
+  return 0;
+}
+
 extern "C" int ganb200_spectral_power_iter(const float* W, float* u, float* v, float* sigma, int rows, int cols,
                                            int n_iter, float eps, void* stream) {
   GB_REQUIRE(rows > 0 && cols > 0 && n_iter >= 0, GANB200_BAD_SHAPE, "spectral_power_iter: bad shape");
-  size_t smem = sizeof(float) * ((size_t)rows + cols);
-  GB_REQUIRE(smem <= 200 * 1024, GANB200_BAD_SHAPE, "spectral_power_iter: rows+cols too large for one CTA");
-  if (smem > 48 * 1024)
-    GB_CHECK_CUDA(cudaFuncSetAttribute(spectral_power_iter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  spectral_power_iter_kernel<<<1, 256, smem, (cudaStream_t)stream>>>(W, u, v, sigma, rows, cols, n_iter, eps);
+  size_t smem;
+  if (int rc = spectral_smem(rows, cols, &smem)) return rc;
+  static bool attr = false;
+  if (!attr) {
+    GB_CHECK_CUDA(cudaFuncSetAttribute(spectral_power_iter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    attr = true;
+  }
+  SpectralJob job{W, u, v, sigma, rows, cols};
+  spectral_power_iter_kernel<<<1, 256, smem, (cudaStream_t)stream>>>(job, n_iter, eps);
+  GB_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int ganb200_spectral_power_iter_batched(const void* jobs, int n_jobs, int max_rows2_plus_cols, int n_iter,
+                                                   float eps, void* stream) {
+  if (n_jobs <= 0) return 0;
+  size_t smem = sizeof(float) * (size_t)max_rows2_plus_cols;
+  GB_REQUIRE(smem <= 200 * 1024, GANB200_BAD_SHAPE, "spectral_power_iter_batched: matrix too large for one CTA");
+  static bool attr = false;
+  if (!attr) {
+    GB_CHECK_CUDA(cudaFuncSetAttribute(spectral_power_iter_batched_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       200 * 1024));
+    attr = true;
+  }
+  spectral_power_iter_batched_kernel<<<n_jobs, 256, smem, (cudaStream_t)stream>>>((const SpectralJob*)jobs, n_iter, eps);
+  GB_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int ganb200_spectral_scale(const float* W, const float* sigma, float* out, int64_t n, void* stream) {
+  if (n <= 0) return 0;
+  spectral_scale_kernel<<<ew_grid(n, 256, 4), 256, 0, (cudaStream_t)stream>>>(W, sigma, out, n);
+  GB_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int ganb200_spectral_scale_bwd(const float* G, const float* W, const float* u, const float* v,
+                                          const float* sigma, float* dot_scratch, float* gW, int rows, int cols,
+                                          void* stream) {
+  int64_t n = (int64_t)rows * cols;
+  if (n <= 0) return 0;
+  cudaStream_t s = (cudaStream_t)stream;
+  GB_CHECK_CUDA(cudaMemsetAsync(dot_scratch, 0, sizeof(float), s));
+  spectral_dot_kernel<<<ew_grid(n, 256, 4), 256, 0, s>>>(G, W, dot_scratch, n);
+  spectral_scale_bwd_kernel<<<ew_grid(n, 256, 4), 256, 0, s>>>(G, u, v, sigma, dot_scratch, gW, rows, cols);
   GB_CHECK_LAUNCH();
   return 0;
 }

@@ -175,6 +175,49 @@ class CudaBackend:
         self._t1(tm)
         return dw
 
+    # -- depthwise 3x3 conv (discriminator_7_wgangpsn.py:55,61,72) -----------------------------------
+    def dwconv_fprop(self, x, w, bias, stride, pad, alpha):
+        N, C, H, W = x.shape
+        assert w.shape[0] == C and w.shape[1] == 1, (x.shape, w.shape)
+        R, S = w.shape[2:]
+        P, Q = out_hw(H, W, R, S, stride, pad)
+        st = self._prep(x, w, bias)
+        y = torch.empty((N, C, P, Q), dtype=torch.float32, device=x.device)
+        _lib.check(self.lib.ganb200_dwconv2d_fprop(self._p(x), self._p(w), self._p(bias), self._p(y), N, C, H, W, R, S,
+                                                   stride, pad, alpha, st))
+        return y
+
+    def dwconv_dgrad(self, dy, w, in_hw, stride, pad, alpha):
+        N, C, P, Q = dy.shape
+        R, S = w.shape[2:]
+        H, W = in_hw
+        assert out_hw(H, W, R, S, stride, pad) == (P, Q) and w.shape[0] == C, (dy.shape, w.shape, in_hw)
+        st = self._prep(dy, w)
+        dx = torch.empty((N, C, H, W), dtype=torch.float32, device=dy.device)
+        _lib.check(self.lib.ganb200_dwconv2d_dgrad(self._p(dy), self._p(w), self._p(dx), N, C, H, W, R, S, stride, pad,
+                                                   alpha, st))
+        return dx
+
+    def dwconv_wgrad(self, x, dy, rs, stride, pad, alpha):
+        N, C, H, W = x.shape
+        R, S = rs
+        assert dy.shape[:2] == (N, C) and out_hw(H, W, R, S, stride, pad) == tuple(dy.shape[2:]), (x.shape, dy.shape)
+        st = self._prep(x, dy)
+        LAUNCH_COUNT[0] += 1
+        dw = torch.empty((C, 1, R, S), dtype=torch.float32, device=x.device)
+        nb = self.lib.ganb200_dwconv2d_wgrad_workspace_bytes(N, C)
+        ws = self._workspace(nb, x.device)
+        _lib.check(self.lib.ganb200_dwconv2d_wgrad(self._p(x), self._p(dy), self._p(dw), self._p(ws), nb, N, C, H, W,
+                                                   R, S, stride, pad, alpha, st))
+        return dw
+
+    def chan_shuffle(self, x, groups):
+        N, C, HW = _nchw(x)
+        st = self._prep(x)
+        y = torch.empty_like(x)
+        _lib.check(self.lib.ganb200_chan_shuffle(self._p(x), self._p(y), N, C, HW, groups, st))
+        return y
+
     # -- resampling -----------------------------------------------------------------------------
     def resample2d(self, x, op_h, op_w):
         *lead, Hi, Wi = x.shape
@@ -484,12 +527,35 @@ class CudaBackend:
         return x
 
     def spectral_power_iter(self, w2d, u, v, n_iter, eps):
+        """u, v advance in place (torch's order: u first); returns sigma = u.(W v) as a 1-element tensor."""
         rows, cols = w2d.shape
         st = self._prep(w2d, u, v)
         sigma = torch.empty((1,), dtype=torch.float32, device=w2d.device)
         _lib.check(self.lib.ganb200_spectral_power_iter(self._p(w2d), self._p(u), self._p(v), self._p(sigma), rows,
                                                         cols, n_iter, eps, st))
         return sigma
+
+    def spectral_power_iter_batched(self, table, n_jobs, max_smem_floats, n_iter, eps):
+        """table: device uint8 tensor holding n_jobs ganb200_spectral_job records (gan_b200.spectral.JobTable)."""
+        st = self._prep(table)
+        _lib.check(self.lib.ganb200_spectral_power_iter_batched(self._p(table), n_jobs, max_smem_floats, n_iter, eps,
+                                                                st))
+
+    def spectral_scale(self, w, sigma):
+        st = self._prep(w, sigma)
+        out = torch.empty_like(w)
+        _lib.check(self.lib.ganb200_spectral_scale(self._p(w), self._p(sigma), self._p(out), w.numel(), st))
+        return out
+
+    def spectral_scale_bwd(self, g, w, u, v, sigma):
+        st = self._prep(g, w, u, v, sigma)
+        LAUNCH_COUNT[0] += 1
+        gw = torch.empty_like(w)
+        scratch = torch.empty((1,), dtype=torch.float32, device=w.device)
+        _lib.check(self.lib.ganb200_spectral_scale_bwd(self._p(g), self._p(w), self._p(u), self._p(v), self._p(sigma),
+                                                       self._p(scratch), self._p(gw), w.shape[0],
+                                                       w.numel() // w.shape[0], st))
+        return gw
 
 
 _backend = None

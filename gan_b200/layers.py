@@ -101,11 +101,15 @@ class ConvTranspose2d(nn.ConvTranspose2d):
 
 
 class Conv2d(nn.Conv2d):
-    """plain nn.Conv2d, zero padding (DCGAN-style discriminators)."""
+    """plain nn.Conv2d, zero padding (DCGAN-style discriminators); groups == channels -> the depthwise kernels
+    (discriminator_7_wgangpsn.py:55)."""
 
     def forward(self, x):
-        assert self.groups == 1 and self.dilation[0] == 1 and self.padding_mode == 'zeros'
-        return ops.conv2d(x, self.weight, self.bias, self.stride[0], self.padding[0], 0)
+        assert self.dilation[0] == 1 and self.padding_mode == 'zeros'
+        if self.groups == 1:
+            return ops.conv2d(x, self.weight, self.bias, self.stride[0], self.padding[0], 0)
+        assert self.groups == self.in_channels == self.out_channels, "grouped convs: depthwise only"
+        return ops.depthwise_conv2d(x, self.weight, self.bias, self.stride[0], self.padding[0])
 
 
 class Linear(nn.Linear):

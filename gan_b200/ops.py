@@ -19,7 +19,25 @@ from torch.autograd.function import once_differentiable
 from . import kernels as KN
 from . import resample as RS
 
-ConvCfg = namedtuple("ConvCfg", "stride pad pad_mode alpha engine")
+ConvCfg = namedtuple("ConvCfg", "stride pad pad_mode alpha engine depthwise", defaults=(False,))
+
+
+def _fprop(cfg, x, w, bias):
+    if cfg.depthwise:
+        return K().dwconv_fprop(x, w, bias, cfg.stride, cfg.pad, cfg.alpha)
+    return K().conv_fprop(x, w, bias, cfg.stride, cfg.pad, cfg.pad_mode, cfg.alpha, engine=cfg.engine)
+
+
+def _dgrad(cfg, dy, w, in_hw):
+    if cfg.depthwise:
+        return K().dwconv_dgrad(dy, w, in_hw, cfg.stride, cfg.pad, cfg.alpha)
+    return K().conv_dgrad(dy, w, in_hw, cfg.stride, cfg.pad, cfg.pad_mode, cfg.alpha, engine=cfg.engine)
+
+
+def _wgrad(cfg, x, dy, rs):
+    if cfg.depthwise:
+        return K().dwconv_wgrad(x, dy, rs, cfg.stride, cfg.pad, cfg.alpha)
+    return K().conv_wgrad(x, dy, rs, cfg.stride, cfg.pad, cfg.pad_mode, cfg.alpha, engine=cfg.engine)
 
 
 def K():
@@ -44,7 +62,7 @@ class Conv2dFn(Function):
         ctx.save_for_backward(x, w)
         ctx.cfg = cfg
         ctx.has_bias = bias is not None
-        return K().conv_fprop(x, w, bias, cfg.stride, cfg.pad, cfg.pad_mode, cfg.alpha, engine=cfg.engine)
+        return _fprop(cfg, x, w, bias)
 
     @staticmethod
     def backward(ctx, gy):
@@ -65,7 +83,7 @@ class ConvDgradFn(Function):
         dy, w = _c(dy), _c(w)
         ctx.save_for_backward(dy, w)
         ctx.cfg = cfg
-        return K().conv_dgrad(dy, w, in_hw, cfg.stride, cfg.pad, cfg.pad_mode, cfg.alpha, engine=cfg.engine)
+        return _dgrad(cfg, dy, w, in_hw)
 
     @staticmethod
     def backward(ctx, g):
@@ -83,7 +101,7 @@ class ConvWgradFn(Function):
         x, dy = _c(x), _c(dy)
         ctx.save_for_backward(x, dy)
         ctx.cfg = cfg
-        return K().conv_wgrad(x, dy, rs, cfg.stride, cfg.pad, cfg.pad_mode, cfg.alpha, engine=cfg.engine)
+        return _wgrad(cfg, x, dy, rs)
 
     @staticmethod
     def backward(ctx, gw):
@@ -97,6 +115,11 @@ class ConvWgradFn(Function):
 
 def conv2d(x, w, bias=None, stride=1, pad=0, pad_mode=0, alpha=1.0, engine=None):
     return Conv2dFn.apply(x, w, bias, ConvCfg(stride, pad, pad_mode, float(alpha), engine))
+
+
+def depthwise_conv2d(x, w, bias=None, stride=1, pad=1, alpha=1.0):
+    """nn.Conv2d(C, C, 3, stride, pad, groups=C), zero padding — discriminator_7_wgangpsn.py:55,61,72."""
+    return Conv2dFn.apply(x, w, bias, ConvCfg(stride, pad, 0, float(alpha), None, True))
 
 
 def linear(x, w, bias=None, alpha=1.0, engine=None):
@@ -541,6 +564,44 @@ def bicubic_resize(x, out_h, out_w, scale=None):
 
 def adaptive_avg_pool(x, out):
     return Resample2dFn.apply(x, RS.adaptive_avg(x.shape[-2], out), RS.adaptive_avg(x.shape[-1], out))
+
+
+class ChanShuffleFn(Function):
+    """channel_shuffle (discriminator_7_wgangpsn.py:27-41); the adjoint is the shuffle with C/groups groups."""
+
+    @staticmethod
+    def forward(ctx, x, groups):
+        ctx.inv = x.shape[1] // groups
+        return K().chan_shuffle(_c(x), groups)
+
+    @staticmethod
+    def backward(ctx, g):
+        return ChanShuffleFn.apply(g, ctx.inv), None
+
+
+def channel_shuffle(x, groups):
+    return ChanShuffleFn.apply(x, groups)
+
+
+class SpectralScaleFn(Function):
+    """W / sigma with sigma = u^T W v and u, v constants (torch parametrizations._SpectralNorm.forward).  The
+    penalties differentiate the critic twice w.r.t. its INPUT; the weight only ever needs this first-order rule."""
+
+    @staticmethod
+    def forward(ctx, w, u, v, sigma):
+        w = _c(w)
+        ctx.save_for_backward(w, u, v, sigma)
+        return K().spectral_scale(w, sigma)
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, g):
+        w, u, v, sigma = ctx.saved_tensors
+        return K().spectral_scale_bwd(_c(g), w, u, v, sigma), None, None, None
+
+
+def spectral_scale(w, u, v, sigma):
+    return SpectralScaleFn.apply(w, u, v, sigma)
 
 
 # =====================================================================================================

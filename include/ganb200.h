@@ -198,11 +198,47 @@ int ganb200_mixup_wgan_f64(const double* label, const float* t, const float* f, 
 /* Clamp all elements to [lo,hi] in place (train/wgan.py:47-48 weight clipping). */
 int ganb200_clamp_(float* x, int64_t n, float lo, float hi, void* stream);
 
-/* Spectral norm power iteration (torch.nn.utils.parametrizations.spectral_norm, used by
- * discriminators/discriminator_7_wgangpsn.py:14): W viewed as [rows, cols];
- * one iteration: v = normalize(W^T u), u = normalize(W v) (eps 1e-12), in place; sigma = u . (W v). */
+/* Spectral norm (torch.nn.utils.parametrizations.spectral_norm as used by
+ * discriminators/discriminator_7_wgangpsn.py:14,53-76,112,121): W viewed as [rows, cols] (rows = out channels).
+ *   power_iter       : n_iter x { u = normalize(W v); v = normalize(W^T u) } (eps 1e-12, torch's order), in place;
+ *                      sigma[0] = u . (W v)
+ *   power_iter_batched: the same for a device table of n_jobs matrices in ONE launch (one CTA per matrix).  `jobs`
+ *                      is a device array of ganb200_spectral_job; max_rows2_plus_cols = max over jobs of 2*rows+cols.
+ *   scale            : out = W / sigma[0]                  (the parametrised weight)
+ *   scale_bwd        : gW = G/sigma - <G,W>/sigma^2 * u v^T (u, v constants, as in torch); dot_scratch: 1 float. */
+typedef struct ganb200_spectral_job {
+  const float* W;
+  float* u;
+  float* v;
+  float* sigma;
+  int rows, cols;
+} ganb200_spectral_job;
 int ganb200_spectral_power_iter(const float* W, float* u, float* v, float* sigma, int rows, int cols,
                                 int n_iter, float eps, void* stream);
+int ganb200_spectral_power_iter_batched(const void* jobs, int n_jobs, int max_rows2_plus_cols, int n_iter,
+                                        float eps, void* stream);
+int ganb200_spectral_scale(const float* W, const float* sigma, float* out, int64_t n, void* stream);
+int ganb200_spectral_scale_bwd(const float* G, const float* W, const float* u, const float* v,
+                               const float* sigma, float* dot_scratch, float* gW, int rows, int cols,
+                               void* stream);
+
+/* Depthwise 3x3 convolution, zero padding, stride 1|2 (discriminators/discriminator_7_wgangpsn.py:55,61,72:
+ * nn.Conv2d(C, C, 3, stride, padding=1, groups=C)).  x:[N,C,H,W]  w:[C,1,3,3]  y:[N,C,P,Q].
+ *   fprop: y  = alpha * dwconv(x, w) + bias        (bias may be NULL)
+ *   dgrad: dx = alpha * dwconv^T(dy, w)
+ *   wgrad: dw = alpha * sum_{n,p,q} dy * x_window   (workspace: ganb200_dwconv2d_wgrad_workspace_bytes) */
+int ganb200_dwconv2d_fprop(const float* x, const float* w, const float* bias, float* y, int N, int C, int H,
+                           int W, int R, int S, int stride, int pad, float alpha, void* stream);
+int ganb200_dwconv2d_dgrad(const float* dy, const float* w, float* dx, int N, int C, int H, int W, int R,
+                           int S, int stride, int pad, float alpha, void* stream);
+int64_t ganb200_dwconv2d_wgrad_workspace_bytes(int N, int C);
+int ganb200_dwconv2d_wgrad(const float* x, const float* dy, float* dw, void* workspace,
+                           int64_t workspace_bytes, int N, int C, int H, int W, int R, int S, int stride,
+                           int pad, float alpha, void* stream);
+
+/* channel_shuffle (discriminator_7_wgangpsn.py:27-41): y[n, j*groups + i] = x[n, i*(C/groups) + j].
+ * Its adjoint / inverse is the same call with groups' = C/groups. */
+int ganb200_chan_shuffle(const float* x, float* y, int N, int C, int HW, int groups, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Fused StyleConv layer of the final generator (generators/generator_13_5.py:219-266):

@@ -299,10 +299,46 @@ class RefBackend:
         return x.clamp_(lo, hi)
 
     def spectral_power_iter(self, w2d, u, v, n_iter, eps):
+        """torch/nn/utils/parametrizations.py _SpectralNorm._power_method: u first, then v."""
         for _ in range(n_iter):
-            v.copy_(F.normalize(torch.mv(w2d.t(), u), dim=0, eps=eps))
             u.copy_(F.normalize(torch.mv(w2d, v), dim=0, eps=eps))
+            v.copy_(F.normalize(torch.mv(w2d.t(), u), dim=0, eps=eps))
         return torch.dot(u, torch.mv(w2d, v)).reshape(1)
+
+    def spectral_scale(self, w, sigma):
+        return w / sigma
+
+    def spectral_scale_bwd(self, g, w, u, v, sigma):
+        dot = (g * w).sum()
+        uv = torch.outer(u, v).reshape(w.shape)
+        return g / sigma - dot / (sigma * sigma) * uv
+
+    # -- depthwise 3x3 conv, channel shuffle (discriminator_7_wgangpsn.py) ----------------------------------
+    def dwconv_fprop(self, x, w, bias, stride, pad, alpha):
+        with torch.no_grad():
+            y = F.conv2d(x, w, None, stride, pad, groups=x.shape[1]) * alpha
+            return y if bias is None else y + bias[None, :, None, None]
+
+    def dwconv_dgrad(self, dy, w, in_hw, stride, pad, alpha):
+        N, C = dy.shape[:2]
+        with torch.enable_grad():
+            x = torch.zeros((N, C, *in_hw), dtype=dy.dtype, requires_grad=True)
+            y = F.conv2d(x, w.detach(), None, stride, pad, groups=C)
+            (dx,) = torch.autograd.grad(y, x, dy.detach())
+        return (dx * alpha).detach()
+
+    def dwconv_wgrad(self, x, dy, rs, stride, pad, alpha):
+        C = x.shape[1]
+        with torch.enable_grad():
+            w = torch.zeros((C, 1, *rs), dtype=x.dtype, requires_grad=True)
+            y = F.conv2d(x.detach(), w, None, stride, pad, groups=C)
+            (dw,) = torch.autograd.grad(y, w, dy.detach())
+        return (dw * alpha).detach()
+
+    def chan_shuffle(self, x, groups):
+        n, c = x.shape[:2]
+        rest = x.shape[2:]
+        return x.reshape(n, groups, c // groups, *rest).transpose(1, 2).reshape(n, c, *rest).contiguous()
 
 
 def adam_reference(p, g, m, v, lr, b1, b2, eps, wd, decoupled, step, grad_scale=1.0):

@@ -30,7 +30,7 @@ CONFIGS = {
                  train="train.wgangp", B=4, names=("G3_PROGAN", "D3_WGAN_PROGAN")),
     "cfg5": dict(gen="generators.generator_14", g_args=lambda: (256,), g_kw={},
                  dis="discriminators.discriminator_7_wgangpsn", d_args=lambda: (), d_kw={},
-                 train="train.wgangpsnR2", B=4, names=("G14", "D7_WGANSN")),
+                 train="train.wgangpsnR2", B=8, names=("G14", "D7_WGANSN")),
 }
 
 

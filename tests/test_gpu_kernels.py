@@ -340,3 +340,102 @@ def test_fused_style_layer_on_gpu_matches_unfused_ops(cu):
         gout = torch.randn_like(out)
         for a, b in zip(torch.autograd.grad(out, leaves, gout), torch.autograd.grad(y, leaves, gout)):
             assert rel(a, b) < max(tol, 1e-4) * 3
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# kernels of the other configs: depthwise 3x3 family, channel shuffle, spectral norm, batch-wide stddev channel
+# ---------------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("case", [(4, 32, 64, 64, 2), (4, 244, 32, 32, 1), (3, 122, 16, 16, 1), (5, 976, 4, 4, 2),
+                                  (2, 7, 9, 11, 2), (2, 7, 9, 11, 1), (64, 16, 1, 1, 1)])
+def test_depthwise_conv_family(cu, ref, case):
+    N, C, H, W, stride = case
+    torch.manual_seed(11)
+    x, w, b = rnd(N, C, H, W), rnd(C, 1, 3, 3), rnd(C)
+    y_r = ref.dwconv_fprop(x, w, b, stride, 1, 0.7)
+    assert rel(cu.dwconv_fprop(g(x), g(w), g(b), stride, 1, 0.7), y_r) < FP32_TOL
+    assert rel(cu.dwconv_fprop(g(x), g(w), None, stride, 1, 1.0), ref.dwconv_fprop(x, w, None, stride, 1, 1.0)) < FP32_TOL
+    dy = rnd(*y_r.shape)
+    assert rel(cu.dwconv_dgrad(g(dy), g(w), (H, W), stride, 1, 0.7), ref.dwconv_dgrad(dy, w, (H, W), stride, 1, 0.7)) < FP32_TOL
+    assert rel(cu.dwconv_wgrad(g(x), g(dy), (3, 3), stride, 1, 0.7), ref.dwconv_wgrad(x, dy, (3, 3), stride, 1, 0.7)) < 2e-5
+
+
+def test_depthwise_conv_rejects_other_kernels(cu):
+    from gan_b200._lib import GanB200Error
+    with pytest.raises(GanB200Error):
+        cu.dwconv_fprop(g(rnd(1, 4, 8, 8)), g(rnd(4, 1, 5, 5)), None, 1, 2, 1.0)
+
+
+@pytest.mark.parametrize("shape,groups", [((4, 244, 32, 32), 2), ((3, 12, 5, 7), 3), ((2, 1952, 4, 4), 2)])
+def test_channel_shuffle(cu, ref, shape, groups):
+    torch.manual_seed(12)
+    x = rnd(*shape)
+    y = cu.chan_shuffle(g(x), groups)
+    assert torch.equal(y.cpu(), ref.chan_shuffle(x, groups))          # a permutation: bit exact
+    back = cu.chan_shuffle(y, shape[1] // groups)                      # the adjoint is the inverse
+    assert torch.equal(back.cpu(), x)
+
+
+@pytest.mark.parametrize("shape", [(32, 3, 3, 3), (244, 244, 1, 1), (976, 976, 1, 1), (1, 1952, 4, 4), (122, 1, 3, 3)])
+def test_spectral_norm_kernels(cu, ref, shape):
+    torch.manual_seed(13)
+    F = torch.nn.functional
+    w = rnd(*shape)
+    rows, cols = shape[0], w.numel() // shape[0]
+    u, v = F.normalize(rnd(rows), dim=0), F.normalize(rnd(cols), dim=0)
+    for n_iter in (1, 0, 3):
+        ug, vg = g(u.clone()), g(v.clone())
+        ur, vr = u.clone(), v.clone()
+        s = cu.spectral_power_iter(g(w).reshape(rows, cols), ug, vg, n_iter, 1e-12)
+        s_r = ref.spectral_power_iter(w.reshape(rows, cols), ur, vr, n_iter, 1e-12)
+        assert rel(s, s_r) < 1e-5 and rel(ug, ur) < 1e-5 and rel(vg, vr) < 1e-5
+    assert rel(cu.spectral_scale(g(w), s), ref.spectral_scale(w, s_r)) < FP32_TOL
+    gw = rnd(*shape)
+    assert rel(cu.spectral_scale_bwd(g(gw), g(w), ug, vg, s), ref.spectral_scale_bwd(gw, w, ur, vr, s_r)) < 2e-5
+
+
+@pytest.mark.parametrize("B", [4, 16, 17, 64])
+def test_batch_stddev_any_group_count(cu, ref, B):
+    """discriminator_3_wgangp_progan.StandardDeviation uses G = batch: the register path (G <= 16) and the re-read
+    path must agree with the oracle, including the double backward."""
+    torch.manual_seed(14)
+    xs, gg, ggx = rnd(B, 32, 4, 4), rnd(1), rnd(B, 32, 4, 4)
+    assert rel(cu.mbstd_fwd(g(xs), B, 1e-7), ref.mbstd_fwd(xs, B, 1e-7)) < FP32_TOL
+    assert rel(cu.mbstd_bwd(g(gg), g(xs), B, 1e-7), ref.mbstd_bwd(gg, xs, B, 1e-7)) < FP32_TOL
+    o1, o2 = cu.mbstd_bwd_bwd(g(gg), g(xs), g(ggx), B, 1e-7)
+    r1, r2 = ref.mbstd_bwd_bwd(gg, xs, ggx, B, 1e-7)
+    assert rel(o1, r1) < 1e-4 and rel(o2, r2) < 1e-4
+
+
+def test_spectral_norm_module_on_gpu_matches_torch(monkeypatch):
+    """gan_b200.spectral.spectral_norm vs torch.nn.utils.parametrizations.spectral_norm on the same seeded conv:
+    same buffers after construction, same normalised weight, same u/v after three train-mode forwards, same
+    gradient of the original weight."""
+    import copy
+    from torch.nn.utils.parametrizations import spectral_norm as torch_sn
+    from gan_b200 import layers as L
+    from gan_b200.spectral import spectral_norm as my_sn
+    monkeypatch.setenv("GANB200_PRECISION", "fp32")
+    torch.manual_seed(15)
+    base = torch.nn.Conv2d(24, 40, 3, padding=1)
+    mine = L.Conv2d(24, 40, 3, padding=1)
+    mine.load_state_dict(copy.deepcopy(base.state_dict()))
+    torch.manual_seed(16)
+    a = torch_sn(base)
+    torch.manual_seed(16)
+    b = my_sn(mine).cuda()
+    assert list(a.state_dict()) == list(b.state_dict())
+    x = rnd(4, 24, 8, 8)
+    for _ in range(3):
+        ya, yb = a(x), b(x.cuda())
+    assert rel(yb, ya) < 1e-4
+    for k, va in a.state_dict().items():
+        assert rel(b.state_dict()[k], va) < 1e-5, k
+    ya.square().sum().backward()
+    yb.square().sum().backward()
+    pa = a.parametrizations.weight.original.grad
+    pb = b.parametrizations.weight.original.grad
+    assert rel(pb, pa) < 1e-3
+    b.eval()
+    u0 = b.parametrizations.weight[0]._u.clone()
+    b(x.cuda())
+    assert torch.equal(u0, b.parametrizations.weight[0]._u)     # eval: no power iteration

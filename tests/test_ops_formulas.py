@@ -145,3 +145,83 @@ def test_modulated_conv_equals_per_sample_weight_form(ref_backend, k):
     g2 = torch.autograd.grad(reference_form(x, w, s), (x, w, s), gy)
     for a, b in zip(g1, g2):
         assert torch.allclose(a, b, atol=1e-10)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# ops of the other configs (cfg4 / cfg5)
+# ---------------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("stride", [1, 2])
+def test_depthwise_conv_is_twice_differentiable(ref_backend, stride):
+    import torch.nn.functional as F
+    from gan_b200 import ops
+    torch.manual_seed(0)
+    x = torch.randn(2, 6, 9, 8, dtype=torch.float64, requires_grad=True)
+    w = torch.randn(6, 1, 3, 3, dtype=torch.float64, requires_grad=True)
+    b = torch.randn(6, dtype=torch.float64, requires_grad=True)
+
+    def penalty(conv):
+        y = conv(x, w, b)
+        (gx,) = torch.autograd.grad(y.tanh().sum(), x, create_graph=True)
+        return y.square().sum() + gx.square().sum()
+
+    want = torch.autograd.grad(penalty(lambda x, w, b: F.conv2d(x, w, b, stride, 1, groups=6)), (x, w, b))
+    got = torch.autograd.grad(penalty(lambda x, w, b: ops.depthwise_conv2d(x, w, b, stride, 1)), (x, w, b))
+    for a, e in zip(got, want):
+        assert torch.allclose(a, e, rtol=1e-9, atol=1e-9)
+
+
+def test_channel_shuffle_and_batch_stddev(ref_backend):
+    from gan_b200 import ops
+    torch.manual_seed(0)
+    x = torch.randn(5, 12, 3, 4, dtype=torch.float64, requires_grad=True)
+    want = x.view(5, 2, 6, 3, 4).transpose(1, 2).contiguous().view(5, 12, 3, 4)
+    got = ops.channel_shuffle(x, 2)
+    assert torch.equal(got, want)
+    wgt = torch.randn_like(x)
+    assert torch.equal(torch.autograd.grad((got * wgt).sum(), x)[0], torch.autograd.grad((want * wgt).sum(), x)[0])
+
+    def ref_std(t):  # discriminators/discriminator_3_wgangp_progan.py:9-16 (out of place)
+        o = t - t.mean(dim=0, keepdim=True)
+        o = torch.sqrt(o.pow(2.0).mean(dim=0) + 10e-8).mean().view(1, 1, 1, 1)
+        return torch.cat([t, o.repeat(t.shape[0], 1, t.shape[2], t.shape[3])], 1)
+
+    def pen(fn):
+        y = fn(x)
+        (gx,) = torch.autograd.grad((y * y[:, -1:]).sum(), x, create_graph=True)
+        return y.sum() + gx.square().sum()
+
+    assert torch.allclose(ops.batch_stddev(x), ref_std(x), rtol=1e-10, atol=1e-12)
+    a, = torch.autograd.grad(pen(ops.batch_stddev), x)
+    e, = torch.autograd.grad(pen(ref_std), x)
+    assert torch.allclose(a, e, rtol=1e-7, atol=1e-9)
+
+
+def test_spectral_norm_module_matches_torch(ref_backend):
+    import copy
+    from torch.nn.utils.parametrizations import spectral_norm as torch_sn
+    from gan_b200 import layers as L
+    from gan_b200.spectral import spectral_norm as my_sn
+    for ctor in (lambda m: m.Conv2d(6, 10, 3, padding=1), lambda m: m.Conv2d(8, 8, 3, padding=1, groups=8)):
+        torch.manual_seed(15)
+        base = ctor(torch.nn)
+        mine = ctor(L)
+        mine.load_state_dict(copy.deepcopy(base.state_dict()))
+        torch.manual_seed(16)
+        a = torch_sn(base)
+        torch.manual_seed(16)
+        b = my_sn(mine)
+        assert list(a.state_dict()) == list(b.state_dict())
+        assert [n for n, _ in a.named_parameters()] == [n for n, _ in b.named_parameters()]
+        x = torch.randn(4, base.in_channels, 8, 8, requires_grad=True)
+        for _ in range(3):
+            ya, yb = a(x), b(x)
+        assert torch.allclose(ya, yb, atol=1e-5)
+        for k, va in a.state_dict().items():
+            assert torch.allclose(b.state_dict()[k], va, atol=1e-6), k
+        # R1-style double backward through the normalised conv
+        for m, y in ((a, ya), (b, yb)):
+            (gx,) = torch.autograd.grad(y.tanh().sum(), x, create_graph=True)
+            (y.square().sum() + gx.square().sum()).backward()
+        assert torch.allclose(a.parametrizations.weight.original.grad, b.parametrizations.weight.original.grad,
+                              rtol=1e-4, atol=1e-5)
+        assert torch.allclose(a.bias.grad, b.bias.grad, rtol=1e-4, atol=1e-5)

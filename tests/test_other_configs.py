@@ -67,20 +67,20 @@ def compare(name, device, tol_out, tol_loss, tol_upd, floor=1e-6):
     return got
 
 
-@pytest.mark.parametrize("name", ["cfg1", "cfg4"])
+@pytest.mark.parametrize("name", ["cfg1", "cfg4", "cfg5"])
 def test_config_cpu_port_matches_reference_golden(ref_backend, name):
     compare(name, torch.device("cpu"), tol_out=1e-4, tol_loss=1e-4, tol_upd=2e-3)
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("name", ["cfg1", "cfg4"])
+@pytest.mark.parametrize("name", ["cfg1", "cfg4", "cfg5"])
 def test_config_cuda_fp32_matches_reference_golden(monkeypatch, name):
     monkeypatch.setenv("GANB200_PRECISION", "fp32")
     compare(name, torch.device("cuda"), tol_out=2e-4, tol_loss=2e-4, tol_upd=5e-3)
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("name", ["cfg1", "cfg4"])
+@pytest.mark.parametrize("name", ["cfg1", "cfg4", "cfg5"])
 def test_config_cuda_tcgen05_matches_reference_golden(monkeypatch, name):
     """bf16 operands, fp32 accumulation: north_star's 1e-2 class on outputs and losses.  Adam's first update is
     lr*sign(g)-like (|update| ~ lr per element whatever the gradient scale), so the update norms stay tight."""

@@ -67,3 +67,30 @@ def test_mixup_on_gpu():
     lab = torch.from_numpy(np.random.beta(0.4, 0.4, size=(64, 1))).cuda()
     assert torch.equal(label, lab) and mixed.dtype == torch.float64
     assert torch.allclose(mixed, lab * t + (1 - lab) * f, atol=1e-12)
+
+
+def test_factories_mirror_the_reference_names():
+    """units/get_generators.py / get_discriminator.py: every reference factory name exists with the same argument
+    list; carried families build, the others say they are out of scope."""
+    import inspect
+    from units import get_discriminator, get_generators
+    cpu = torch.device("cpu")
+    g = get_generators.get_1(cpu, 256, (3, 64, 64))
+    d = get_discriminator.get_1(cpu, (3, 64, 64))
+    assert sum(p.numel() for p in g.parameters()) == 256 * 256 + 256 + 256 * 512 + 512 + 512 * 12288 + 12288
+    assert sum(p.numel() for p in d.parameters()) == 12288 * 256 + 256 + 256 * 64 + 64 + 64 + 1
+    assert list(inspect.signature(get_generators.get_3_progan).parameters) == ["ngpu", "device", "nz", "ngf", "nc"]
+    assert list(inspect.signature(get_generators.get_13).parameters) == ["ngpu", "device", "z_dim"]
+    assert inspect.signature(get_generators.get_13).parameters["z_dim"].default == 128
+    assert list(inspect.signature(get_discriminator.get_3_wgan_progan).parameters) == ["ngpu", "device", "ndf", "nc"]
+    assert list(inspect.signature(get_discriminator.get_7_wgansn).parameters) == ["ngpu", "device"]
+    for n in ("2", "4", "5", "6", "7", "8", "9", "10", "10_2", "11", "12", "13"):
+        assert callable(getattr(get_generators, "get_" + n))
+    for n in ("2", "3_wgan", "3_wgansn", "4", "5", "5_wgan", "5_wgansn", "6_wgan", "7_wgan", "8", "9"):
+        assert callable(getattr(get_discriminator, "get_" + n))
+    with pytest.raises(NotImplementedError):
+        get_generators.get_4(1, cpu)
+    with pytest.raises(NotImplementedError):
+        get_discriminator.get_8(1, cpu)
+    d4 = get_discriminator.get_3_wgan_progan(1, cpu, ndf=8, nc=3)
+    assert type(d4).__name__ == "Discriminator" and len(d4.main) == 24
