@@ -28,7 +28,7 @@ def rel(a, b):
     return float((a - b).norm() / b.norm().clamp_min(1e-30))
 
 
-def compare(name, device, tol_out, tol_loss, tol_upd, floor=1e-6):
+def compare(name, device, tol_out, tol_loss, tol_upd, floor=1e-6, chain=True):
     from gan_b200 import rng
     cfg = CONFIGS[name]
     gold = torch.load(os.path.join(GOLDEN, name + ".pt"), weights_only=False)
@@ -46,10 +46,15 @@ def compare(name, device, tol_out, tol_loss, tol_upd, floor=1e-6):
         for n, w in gold[k].items():
             if abs(got[k].get(n, float("nan")) - w) > 1e-5 * max(abs(w), 1e-3):
                 bad.append((k, n, got[k].get(n), w))
-    for k in ("d_out", "g_out"):
+    for k in ("d_out", "g_out") if chain else ("d_out",):
         e = rel(got[k], gold[k])
         if not e < tol_out:
             bad.append((k, e))
+    if not chain:  # ill-conditioned chain (see the caller): structure, init, critic output and a finite step only
+        import math
+        assert all(math.isfinite(v) for v in got["step_d_losses"] + [got["step_g_loss"], got["step_gen_imgs_norm"]])
+        assert not bad, bad[:20]
+        return got
     for g, w in zip(got["step_d_losses"] + [got["step_g_loss"]], gold["step_d_losses"] + [gold["step_g_loss"]]):
         if not abs(g - w) <= tol_loss * max(abs(w), 1e-2):
             bad.append(("loss", g, w))
@@ -72,11 +77,23 @@ def test_config_cpu_port_matches_reference_golden(ref_backend, name):
     compare(name, torch.device("cpu"), tol_out=1e-4, tol_loss=1e-4, tol_upd=2e-3)
 
 
+# cfg5 on the GPU.  The critic is spectrally normalised 79 times over: its outputs are ~5e-3 and its gradients ~1e-9, the
+# size of Adam's eps, so an update norm follows the ABSOLUTE rounding error of the gradient (measured up to 3 % between
+# the fp32 CUDA kernels and the reference's CPU run; < 2e-3 for the CPU port which shares the reference's GEMM order).
+# generator_14 over a batch of 8 amplifies a 1e-6 per-layer difference to 4e-5 at the output (40x: BatchNorm1d over 8
+# samples in every attention head), and the bf16 engine's 2e-3 per conv to ~0.2: end-to-end output parity is meaningless
+# there, so the bf16 engine is checked block by block on identical inputs instead (test_cfg5_blockwise_tcgen05).
+TOL_FP32 = {"cfg1": dict(tol_out=2e-4, tol_loss=2e-4, tol_upd=5e-3), "cfg4": dict(tol_out=2e-4, tol_loss=2e-4, tol_upd=5e-3),
+            "cfg5": dict(tol_out=1e-3, tol_loss=1e-3, tol_upd=5e-2)}
+TOL_BF16 = {"cfg1": dict(tol_out=1e-2, tol_loss=2e-2, tol_upd=2e-2), "cfg4": dict(tol_out=1e-2, tol_loss=2e-2, tol_upd=2e-2),
+            "cfg5": dict(tol_out=5e-2, tol_loss=None, tol_upd=None, chain=False)}
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("name", ["cfg1", "cfg4", "cfg5"])
 def test_config_cuda_fp32_matches_reference_golden(monkeypatch, name):
     monkeypatch.setenv("GANB200_PRECISION", "fp32")
-    compare(name, torch.device("cuda"), tol_out=2e-4, tol_loss=2e-4, tol_upd=5e-3)
+    compare(name, torch.device("cuda"), **TOL_FP32[name])
 
 
 @pytest.mark.gpu
@@ -85,4 +102,39 @@ def test_config_cuda_tcgen05_matches_reference_golden(monkeypatch, name):
     """bf16 operands, fp32 accumulation: north_star's 1e-2 class on outputs and losses.  Adam's first update is
     lr*sign(g)-like (|update| ~ lr per element whatever the gradient scale), so the update norms stay tight."""
     monkeypatch.setenv("GANB200_PRECISION", "auto")
-    compare(name, torch.device("cuda"), tol_out=1e-2, tol_loss=2e-2, tol_upd=2e-2)
+    compare(name, torch.device("cuda"), **TOL_BF16[name])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("precision,tol", [("fp32", 1e-4), ("auto", 2e-2)])
+def test_cfg5_blockwise(monkeypatch, precision, tol):
+    """generator_14 and discriminator_7_wgangpsn stage by stage: every block / stage runs on the GPU kernels and on the
+    CPU restatement from the SAME input (the CPU chain's), so conditioning of the whole chain does not enter."""
+    import copy
+    from gan_b200 import kernels
+    from oracle.kernels_ref import RefBackend
+    from discriminators import discriminator_7_wgangpsn as dmod
+    from generators import generator_14 as gmod
+    monkeypatch.setenv("GANB200_PRECISION", precision)
+    torch.manual_seed(0)
+    G, D = gmod.Generator(256), dmod.Discriminator()
+    Gc, Dc = copy.deepcopy(G).cuda(), copy.deepcopy(D).cuda()
+    gen = torch.Generator().manual_seed(5)
+    z = torch.randn(8, 256, 1, 1, generator=gen)
+    x = torch.randn(8, 3, 64, 64, generator=gen).clamp_(-1, 1)
+    g_stages = [(n, getattr(G, n), getattr(Gc, n)) for n in ("block0", "block1", "block2", "block3", "block4", "to_rgb")]
+    d_stages = [(n, getattr(D, n), getattr(Dc, n)) for n in ("pre", "stage2", "stage3", "stage4", "stage5", "conv5")]
+    worst = {}
+    for stages, t in ((g_stages, z), (d_stages, x)):
+        for n, cpu_mod, gpu_mod in stages:
+            prev = kernels.set_backend(RefBackend())
+            try:
+                with torch.no_grad():
+                    want = cpu_mod(t)
+            finally:
+                kernels.set_backend(prev)
+            with torch.no_grad():
+                got = gpu_mod(t.cuda())
+            worst[n] = rel(got.cpu(), want)
+            t = want
+    assert all(v < tol for v in worst.values()), worst
