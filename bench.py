@@ -276,6 +276,11 @@ def run_native(args):
     mem_gb = torch.cuda.max_memory_allocated(device) / 2**30
     dp.remove()
 
+    if world > 1:
+        # last collective of the run: every rank passes it, then only rank 0 has (CPU-side) work left
+        tdist.barrier()
+        torch.cuda.synchronize()
+        tdist.destroy_process_group()
     if rank != 0:
         return
     pk = peaks()
@@ -307,9 +312,6 @@ def run_native(args):
         line["cpu_baseline"] = {"value": rate, "unit": "images/s", "cores": threads, "kind": "port",
                                 "sample": f"{n} full iterations at batch {args.cpu_batch} on torch CPU ops (fp32)"}
     print(json.dumps(line), flush=True)
-    if world > 1:
-        tdist.barrier()
-        tdist.destroy_process_group()
 
 
 def main():

@@ -60,6 +60,65 @@ __global__ void __launch_bounds__(256) pack_act_kernel(const float* __restrict__
   }
 }
 
+// Vectorised variant for W % 4 == 0 (every hot shape): one block = one INPUT row (n, h) x 64 channels.  float4 loads along
+// w, the row is transposed in shared memory as bf16x2 words [w][33] (conflict-free both ways), 16-byte stores along c;
+// the replicated border rows / columns are written from the same tile, so every input byte is read once.
+__device__ __forceinline__ uint32_t pack_bf162(float lo, float hi) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+
+__global__ void __launch_bounds__(256) pack_act_vec_kernel(const float* __restrict__ x, const float* __restrict__ scale,
+                                                           __nv_bfloat16* __restrict__ out, int C, int H, int W, int Cp,
+                                                           int pad) {
+  extern __shared__ uint32_t tw[];  // [W][33]: word (w, cp) = channels (c0 + 2cp, c0 + 2cp + 1) of pixel w
+  const int Hp = H + 2 * pad, Wp = W + 2 * pad;
+  const int n = blockIdx.x / H, h = blockIdx.x % H;
+  const int c0 = blockIdx.y * 64;
+  const int G4 = W >> 2;
+  const bool tiled = (G4 & 7) == 0;  // warp = 8 w-groups x 4 channel pairs -> 32 distinct banks
+  for (int i = threadIdx.x; i < 32 * G4; i += 256) {
+    int g, cp;
+    if (tiled) {
+      const int l = i & 31, t = i >> 5, tiles_g = G4 >> 3;
+      g = (t % tiles_g) * 8 + (l >> 2);
+      cp = (t / tiles_g) * 4 + (l & 3);
+    } else {
+      g = i % G4;
+      cp = i / G4;
+    }
+    const int c = c0 + 2 * cp;
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
+    if (c < C) {
+      a = __ldg(reinterpret_cast<const float4*>(x + (((int64_t)n * C + c) * H + h) * W) + g);
+      if (scale) { float sc = __ldg(scale + (int64_t)n * C + c); a.x *= sc; a.y *= sc; a.z *= sc; a.w *= sc; }
+    }
+    if (c + 1 < C) {
+      b = __ldg(reinterpret_cast<const float4*>(x + (((int64_t)n * C + c + 1) * H + h) * W) + g);
+      if (scale) { float sc = __ldg(scale + (int64_t)n * C + c + 1); b.x *= sc; b.y *= sc; b.z *= sc; b.w *= sc; }
+    }
+    uint32_t* d = tw + (4 * g) * 33 + cp;
+    d[0] = pack_bf162(a.x, b.x);
+    d[33] = pack_bf162(a.y, b.y);
+    d[66] = pack_bf162(a.z, b.z);
+    d[99] = pack_bf162(a.w, b.w);
+  }
+  __syncthreads();
+  const int chunks = min(64, Cp - c0) >> 3;  // 16-byte chunks of valid (padded) channels
+  const int hp_lo = (h == 0) ? 0 : h + pad, hp_hi = (h == H - 1) ? Hp - 1 : h + pad;
+  for (int hp = hp_lo; hp <= hp_hi; ++hp) {
+    __nv_bfloat16* orow = out + ((int64_t)n * Hp + hp) * Wp * Cp + c0;
+    for (int i = threadIdx.x; i < 8 * Wp; i += 256) {
+      const int k = i & 7, wp = i >> 3;
+      if (k >= chunks) continue;
+      const int w = min(max(wp - pad, 0), W - 1);
+      const uint32_t* sp = tw + w * 33 + 4 * k;
+      uint4 v = make_uint4(sp[0], sp[1], sp[2], sp[3]);
+      *reinterpret_cast<uint4*>(orow + (int64_t)wp * Cp + 8 * k) = v;
+    }
+  }
+}
+
 constexpr int MAX_TAPS = 49;
 struct TapTable {
   int n;
@@ -307,6 +366,12 @@ static size_t w_bytes(int taps, int Ko, int Ci) { return align_up((size_t)taps *
 static int pack_input(const float* in, const float* in_scale, __nv_bfloat16* act, int N, int Ci, int Hi, int Wi,
                       int mat_pad, cudaStream_t s) {
   const int Cp = cpad(Ci), Hp = Hi + 2 * mat_pad;
+  if ((Wi & 3) == 0 && ((uintptr_t)in & 15) == 0 && Wi <= 1024) {
+    dim3 grid(N * Hi, (Cp + 63) / 64);
+    pack_act_vec_kernel<<<grid, 256, sizeof(uint32_t) * 33 * Wi, s>>>(in, in_scale, act, Ci, Hi, Wi, Cp, mat_pad);
+    GB_CHECK_LAUNCH();
+    return 0;
+  }
   dim3 grid(N * Hp, (Cp + 63) / 64);
   pack_act_kernel<<<grid, 256, sizeof(float) * 64 * (Wi + 1), s>>>(in, in_scale, act, Ci, Hi, Wi, Cp, mat_pad);
   GB_CHECK_LAUNCH();
@@ -647,13 +712,21 @@ __global__ void __launch_bounds__(TC_THREADS) tc_wgrad_kernel(const __grid_const
 // dw[k][c][rs] = alpha * sum_split part[split][rs][k][c]
 __global__ void __launch_bounds__(256) wgrad_reduce_kernel(const float* __restrict__ part, float* __restrict__ dw, int K,
                                                            int C, int RS, int splits, float alpha) {
-  const int64_t KC = (int64_t)K * C;
-  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < KC; i += (int64_t)gridDim.x * 256) {
-    for (int rs = 0; rs < RS; ++rs) {
-      float acc = 0.f;
-      for (int sp = 0; sp < splits; ++sp) acc += part[((int64_t)sp * RS + rs) * KC + i];
-      dw[i * RS + rs] = acc * alpha;
+  // one thread per (rs, k*C + c): reads coalesced along (k,c); the split sum runs in a fixed order (deterministic)
+  const uint32_t KC = (uint32_t)K * C, total = KC * RS;
+  for (uint32_t j = blockIdx.x * 256 + threadIdx.x; j < total; j += gridDim.x * 256) {
+    const uint32_t rs = j / KC, i = j - rs * KC;
+    const float* src = part + (size_t)rs * KC + i;
+    const size_t step = (size_t)RS * KC;
+    float acc = 0.f;
+    int sp = 0;
+    for (; sp + 4 <= splits; sp += 4) {
+      const float a0 = __ldg(src + (size_t)sp * step), a1 = __ldg(src + (size_t)(sp + 1) * step);
+      const float a2 = __ldg(src + (size_t)(sp + 2) * step), a3 = __ldg(src + (size_t)(sp + 3) * step);
+      acc += a0; acc += a1; acc += a2; acc += a3;
     }
+    for (; sp < splits; ++sp) acc += __ldg(src + (size_t)sp * step);
+    dw[(size_t)i * RS + rs] = acc * alpha;
   }
 }
 
@@ -722,14 +795,9 @@ static int wgrad_run(const ganb200_conv_desc* d, const float* x, const float* dy
   float* part = (float*)((uint8_t*)ws + w.dy_bytes + w.x_bytes);
   {
     if (!dy_prepacked) {
-      dim3 g1(d->N * d->P, (Kp + 63) / 64);
-      pack_act_kernel<<<g1, 256, sizeof(float) * 64 * (d->Q + 1), s>>>(dy, oscale, (__nv_bfloat16*)ws, d->K, d->P, d->Q,
-                                                                       Kp, 0);
-      GB_CHECK_LAUNCH();
+      if (int rc = pack_input(dy, oscale, (__nv_bfloat16*)ws, d->N, d->K, d->P, d->Q, 0, s)) return rc;
     }
-    dim3 g2(d->N * Hp, (Cp + 63) / 64);
-    pack_act_kernel<<<g2, 256, sizeof(float) * 64 * (d->W + 1), s>>>(x, iscale, xh, d->C, d->H, d->W, Cp, mp);
-    GB_CHECK_LAUNCH();
+    if (int rc = pack_input(x, iscale, xh, d->N, d->C, d->H, d->W, mp, s)) return rc;
   }
   TcWgradParams p;
   p.K = d->K; p.C = d->C; p.S = d->S; p.taps = RS;
@@ -757,7 +825,7 @@ static int wgrad_run(const ganb200_conv_desc* d, const float* x, const float* dy
   dim3 grid(ceil_div(d->K, TILE_M), ceil_div(d->C, w.BN), RS * w.splits);
   int rc = w.BN == 128 ? launch_wg<128, 4>(ta, tb, p, grid, s) : launch_wg<64, 4>(ta, tb, p, grid, s);
   if (rc) return rc;
-  wgrad_reduce_kernel<<<ew_grid((int64_t)d->K * d->C, 256, 1), 256, 0, s>>>(part, dw, d->K, d->C, RS, w.splits, d->alpha);
+  wgrad_reduce_kernel<<<ew_grid((int64_t)d->K * d->C * RS, 256, 1), 256, 0, s>>>(part, dw, d->K, d->C, RS, w.splits, d->alpha);
   GB_CHECK_LAUNCH();
   return 0;
 }

@@ -13,10 +13,9 @@ template <int ST>
 __global__ void __launch_bounds__(256) dw3_fprop_kernel(const float* __restrict__ x, const float* __restrict__ w,
                                                         const float* __restrict__ bias, float* __restrict__ y, int NC,
                                                         int C, int H, int W, int P, int Q, int pad, float alpha) {
-  int64_t total = (int64_t)NC * P * Q;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+  grid_stride((int64_t)NC * P * Q, [&](auto i) {
     int q = (int)(i % Q);
-    int64_t t = i / Q;
+    auto t = i / Q;
     int p = (int)(t % P);
     int nc = (int)(t / P);
     int c = nc % C;
@@ -35,7 +34,7 @@ __global__ void __launch_bounds__(256) dw3_fprop_kernel(const float* __restrict_
       }
     }
     y[i] = alpha * acc + (bias ? __ldg(bias + c) : 0.f);
-  }
+  });
 }
 
 // dx[n,c,h,w] = alpha * sum_{r,s} w[c,r,s] * dy[n,c,(h+pad-r)/st,(w+pad-s)/st]   (where divisible and in range)
@@ -43,10 +42,9 @@ template <int ST>
 __global__ void __launch_bounds__(256) dw3_dgrad_kernel(const float* __restrict__ dy, const float* __restrict__ w,
                                                         float* __restrict__ dx, int NC, int C, int H, int W, int P,
                                                         int Q, int pad, float alpha) {
-  int64_t total = (int64_t)NC * H * W;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+  grid_stride((int64_t)NC * H * W, [&](auto i) {
     int ww = (int)(i % W);
-    int64_t t = i / W;
+    auto t = i / W;
     int h = (int)(t % H);
     int nc = (int)(t / H);
     int c = nc % C;
@@ -68,7 +66,7 @@ __global__ void __launch_bounds__(256) dw3_dgrad_kernel(const float* __restrict_
       }
     }
     dx[i] = alpha * acc;
-  }
+  });
 }
 
 // partial[split][c][9] = sum over the split's samples and all (p,q) of dy[n,c,p,q] * x[n,c,p*st-pad+r,q*st-pad+s]
@@ -121,11 +119,10 @@ __global__ void __launch_bounds__(256) dw3_wgrad_reduce_kernel(const float* __re
 // channel shuffle: y[n, j*G + i] = x[n, i*(C/G) + j]
 __global__ void __launch_bounds__(256) chan_shuffle_kernel(const float* __restrict__ x, float* __restrict__ y, int N,
                                                            int C, int HW4, int G, bool vec) {
-  int64_t total = (int64_t)N * C * HW4;
   int cpg = C / G;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+  grid_stride((int64_t)N * C * HW4, [&](auto i) {
     int e = (int)(i % HW4);
-    int64_t t = i / HW4;
+    auto t = i / HW4;
     int co = (int)(t % C);
     int n = (int)(t / C);
     int ci = (co % G) * cpg + co / G;
@@ -134,7 +131,7 @@ __global__ void __launch_bounds__(256) chan_shuffle_kernel(const float* __restri
       reinterpret_cast<float4*>(y)[i] = __ldg(reinterpret_cast<const float4*>(x) + src);
     else
       y[i] = __ldg(x + src);
-  }
+  });
 }
 
 static int dw_check(int N, int C, int H, int W, int R, int S, int stride, int pad, int* P, int* Q) {

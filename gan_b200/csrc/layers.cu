@@ -69,16 +69,83 @@ __global__ void __launch_bounds__(256) prelu_reduce_kernel(const float* __restri
     }
   } else {
     int c = blockIdx.x;
-    for (int n = split; n < N; n += nsplit) {
-      int64_t base = ((int64_t)n * C + c) * HW;
-      for (int i = threadIdx.x; i < HW; i += blockDim.x) {
-        float xv = x[base + i];
-        if (!(xv > 0.f)) acc += MODE == 0 ? u[base + i] * xv : u[base + i] * v[base + i];
+    if (HW >= 64) {
+      for (int n = split; n < N; n += nsplit) {
+        int64_t base = ((int64_t)n * C + c) * HW;
+        for (int i = threadIdx.x; i < HW; i += blockDim.x) {
+          float xv = x[base + i];
+          if (!(xv > 0.f)) acc += MODE == 0 ? u[base + i] * xv : u[base + i] * v[base + i];
+        }
+      }
+    } else {
+      // small planes (4x4 ... 7x7): threads over (n, hw) pairs so that all 256 lanes have work
+      const int total = N * HW;
+      for (int j = split * 256 + threadIdx.x; j < total; j += nsplit * 256) {
+        const int n = j / HW, i = j - n * HW;
+        const int64_t idx = ((int64_t)n * C + c) * HW + i;
+        float xv = x[idx];
+        if (!(xv > 0.f)) acc += MODE == 0 ? u[idx] * xv : u[idx] * v[idx];
       }
     }
   }
   float t = block_sum<256>(acc);
   if (threadIdx.x == 0) atomicAdd(out + (a_n == 1 ? 0 : blockIdx.x), t);
+}
+
+// Fused PReLU backward: gx = gy * (x > 0 ? 1 : a) and ga[c] += sum gy * min(x, 0) in ONE pass over (gy, x)
+// (12 B/element instead of 20).  ROWS: one warp per (n,c) row, float4 (HW >= 64, HW % 4 == 0);
+// otherwise one block per channel with threads over (n, hw) (small planes).  ga must be zeroed by the caller.
+template <bool ROWS>
+__global__ void __launch_bounds__(256) prelu_bwd_fused_kernel(const float* __restrict__ gy, const float* __restrict__ x,
+                                                              const float* __restrict__ a, float* __restrict__ gx,
+                                                              float* __restrict__ ga, int N, int C, int HW, int a_n) {
+  if (ROWS) {
+    const int lane = threadIdx.x & 31;
+    const int64_t rows = (int64_t)N * C;
+    const int hw4 = HW >> 2;
+    float keep = 0.f;  // a_n == 1: one atomic per warp at the end
+    for (int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); row < rows; row += (int64_t)gridDim.x * 8) {
+      const int c = a_n == 1 ? 0 : (int)(row % C);
+      const float slope = __ldg(a + c);
+      const float4* g4 = reinterpret_cast<const float4*>(gy + row * HW);
+      const float4* x4 = reinterpret_cast<const float4*>(x + row * HW);
+      float4* o4 = reinterpret_cast<float4*>(gx + row * HW);
+      float acc = 0.f;
+      for (int i = lane; i < hw4; i += 32) {
+        const float4 g = __ldg(g4 + i), v = __ldg(x4 + i);
+        float4 r;
+        r.x = v.x > 0.f ? g.x : slope * g.x; r.y = v.y > 0.f ? g.y : slope * g.y;
+        r.z = v.z > 0.f ? g.z : slope * g.z; r.w = v.w > 0.f ? g.w : slope * g.w;
+        o4[i] = r;
+        acc += (v.x > 0.f ? 0.f : g.x * v.x) + (v.y > 0.f ? 0.f : g.y * v.y) + (v.z > 0.f ? 0.f : g.z * v.z) +
+               (v.w > 0.f ? 0.f : g.w * v.w);
+      }
+      if (a_n == 1) {
+        keep += acc;
+      } else {
+        acc = warp_sum(acc);
+        if (lane == 0) atomicAdd(ga + c, acc);
+      }
+    }
+    if (a_n == 1) {
+      keep = warp_sum(keep);
+      if (lane == 0) atomicAdd(ga, keep);
+    }
+  } else {
+    const int c = blockIdx.x, split = blockIdx.y, nsplit = gridDim.y;
+    const float slope = __ldg(a + c);
+    const int total = N * HW;
+    float acc = 0.f;
+    for (int j = split * 256 + threadIdx.x; j < total; j += nsplit * 256) {
+      const int n = j / HW, i = j - n * HW;
+      const int64_t idx = ((int64_t)n * C + c) * HW + i;
+      const float g = gy[idx], v = x[idx];
+      gx[idx] = v > 0.f ? g : slope * g;
+      if (!(v > 0.f)) acc += g * v;
+    }
+    float t = block_sum<256>(acc);
+    if (threadIdx.x == 0) atomicAdd(ga + c, t);
+  }
 }
 
 }  // namespace ganb200
@@ -92,7 +159,7 @@ static int rows_grid(int64_t rows, int HW) {
 static void prelu_reduce_dims(int N, int C, int HW, int a_n, dim3* grid) {
   int groups = a_n == 1 ? 1 : C;
   int64_t per_group = (int64_t)N * C * HW / groups;
-  int max_split = a_n == 1 ? (int)((per_group + 2047) / 2048) : N;
+  int max_split = a_n == 1 ? (int)((per_group + 2047) / 2048) : (HW >= 64 ? N : (int)(((int64_t)N * HW + 255) / 256));
   int want = (kNumSMs * 4 + groups - 1) / groups;
   int nsplit = want < max_split ? want : max_split;
   if (nsplit < 1) nsplit = 1;
@@ -124,6 +191,23 @@ extern "C" int ganb200_prelu_bwd(const float* gy, const float* x, const float* a
   cudaStream_t s = (cudaStream_t)stream;
   int64_t rows = (int64_t)N * C;
   if (rows * HW == 0) return 0;
+  if (gx && ga) {
+    const bool al = ((((uintptr_t)gy) | ((uintptr_t)x) | ((uintptr_t)gx)) & 15) == 0;
+    if (HW >= 64 && (HW & 3) == 0 && al) {
+      GB_CHECK_CUDA(cudaMemsetAsync(ga, 0, sizeof(float) * a_n, s));
+      int grid = (int)std::min<int64_t>((rows + 7) / 8, (int64_t)kNumSMs * 16);
+      prelu_bwd_fused_kernel<true><<<grid, 256, 0, s>>>(gy, x, a, gx, ga, N, C, HW, a_n);
+      GB_CHECK_LAUNCH();
+      return 0;
+    }
+    if (HW < 64 && a_n == C && (int64_t)N * HW < (int64_t)1 << 30) {
+      GB_CHECK_CUDA(cudaMemsetAsync(ga, 0, sizeof(float) * a_n, s));
+      int nsplit = std::max(1, std::min((kNumSMs * 4 + C - 1) / C, (N * HW + 255) / 256));
+      prelu_bwd_fused_kernel<false><<<dim3(C, nsplit), 256, 0, s>>>(gy, x, a, gx, ga, N, C, HW, a_n);
+      GB_CHECK_LAUNCH();
+      return 0;
+    }
+  }
   if (gx) {
     prelu_kernel<1><<<rows_grid(rows, HW), 256, 0, s>>>(gy, x, a, gx, rows, C, HW, a_n);
     GB_CHECK_LAUNCH();
@@ -207,10 +291,8 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const float* __restrict__
                                                        float* __restrict__ o2, int N, int C, int HW, float eps,
                                                        float momentum, float count, int64_t* nbt) {
   if (MODE == 0 && nbt && blockIdx.x == 0 && threadIdx.x == 0) *nbt += 1;  // num_batches_tracked
-  int64_t rows = (int64_t)N * C;
-  int64_t total = rows * HW;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    int64_t row = i / HW;
+  grid_stride((int64_t)N * C * HW, [&](auto i) {
+    const auto row = i / HW;
     int c = (int)(row % C);
     float m = mean[c];
     float gm = gamma ? gamma[c] : 1.f;
@@ -234,7 +316,7 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const float* __restrict__
         if (o1) o1[c] = sgy[c];
       }
     }
-  }
+  });
 }
 
 }  // namespace ganb200
@@ -440,6 +522,63 @@ __global__ void __launch_bounds__(256) resample2d_kernel(const float* __restrict
   }
 }
 
+// Separable form for whole planes that fit in shared memory (every bicubic / Smooth use of the models: planes up to
+// 64x64): one block walks planes; the plane is staged with coalesced (float4) loads, the horizontal pass writes an
+// Hi x Wo intermediate to shared memory, the vertical pass streams the output rows.  Tap tables live in shared memory
+// too.  (Th + Tw) multiply-adds per output instead of Th*Tw and no global gathers: HBM-bound, (in + out) * 4 B.
+// Summation order per output equals resample2d_kernel's (taps b inside, taps a outside).
+__global__ void __launch_bounds__(256) resample2d_sep_kernel(const float* __restrict__ x, float* __restrict__ y,
+                                                             int64_t NC, int Hi, int Wi, int Ho, int Wo,
+                                                             const int* __restrict__ ih, const float* __restrict__ wh,
+                                                             int Th, const int* __restrict__ iw,
+                                                             const float* __restrict__ ww, int Tw) {
+  extern __shared__ float sm[];
+  const int HWi = Hi * Wi, HWo = Ho * Wo, HiWo = Hi * Wo;
+  float* pin = sm;                               // [Hi][Wi]
+  float* tmp = pin + ((HWi + 3) & ~3);           // [Hi][Wo]
+  float* s_ww = tmp + HiWo;                      // [Tw][Wo]
+  float* s_wh = s_ww + Wo * Tw;                  // [Ho][Th]
+  int* s_iw = reinterpret_cast<int*>(s_wh + Ho * Th);
+  int* s_ih = s_iw + Wo * Tw;
+  for (int i = threadIdx.x; i < Wo * Tw; i += 256) {  // transposed [Tw][Wo]: lanes (consecutive wo) hit distinct banks
+    const int wo = i / Tw, b = i - wo * Tw;
+    s_ww[b * Wo + wo] = ww[i];
+    s_iw[b * Wo + wo] = iw[i];
+  }
+  for (int i = threadIdx.x; i < Ho * Th; i += 256) { s_wh[i] = wh[i]; s_ih[i] = ih[i] * Wo; }
+  const bool vec = (HWi & 3) == 0 && aligned16(x);
+  for (int64_t nc = blockIdx.x; nc < NC; nc += gridDim.x) {
+    const float* xp = x + nc * HWi;
+    __syncthreads();
+    if (vec) {
+      for (int i = threadIdx.x; i < (HWi >> 2); i += 256)
+        reinterpret_cast<float4*>(pin)[i] = __ldg(reinterpret_cast<const float4*>(xp) + i);
+    } else {
+      for (int i = threadIdx.x; i < HWi; i += 256) pin[i] = __ldg(xp + i);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < HiWo; i += 256) {
+      const int h = i / Wo, wo = i - h * Wo;
+      const float* row = pin + h * Wi;
+      float acc = 0.f;
+      for (int b = 0; b < Tw; ++b) acc = fmaf(s_ww[b * Wo + wo], row[s_iw[b * Wo + wo]], acc);
+      tmp[i] = acc;
+    }
+    __syncthreads();
+    float* yp = y + nc * HWo;
+    for (int i = threadIdx.x; i < HWo; i += 256) {
+      const int ho = i / Wo, wo = i - ho * Wo;
+      float acc = 0.f;
+      for (int a = 0; a < Th; ++a) {
+        const float wa = s_wh[ho * Th + a];
+        if (wa == 0.f) continue;
+        acc = fmaf(wa, tmp[s_ih[ho * Th + a] + wo], acc);
+      }
+      yp[i] = acc;
+    }
+  }
+}
+
 // Same operator for "few outputs, many taps" (AdaptiveAvgPool2d(5) of a 64x64 map: 25 outputs x 169 taps per plane):
 // one block per plane, the plane staged in shared memory with coalesced loads, one warp per output reducing its taps.
 __global__ void __launch_bounds__(256) resample2d_plane_kernel(const float* __restrict__ x, float* __restrict__ y,
@@ -556,8 +695,16 @@ extern "C" int ganb200_resample2d(const float* x, float* y, int NC, int Hi, int 
     resample2d_plane_kernel<<<grid, 256, sizeof(float) * Hi * Wi, (cudaStream_t)stream>>>(x, y, NC, Hi, Wi, Ho, Wo, ih,
                                                                                          wh, Th, iw, ww, Tw);
   } else {
-    resample2d_kernel<<<ew_grid(total, 256, 2), 256, 0, (cudaStream_t)stream>>>(x, y, NC, Hi, Wi, Ho, Wo, ih, wh, Th, iw,
-                                                                               ww, Tw);
+    const size_t sep_smem = sizeof(float) * (((size_t)Hi * Wi + 3) / 4 * 4 + (size_t)Hi * Wo) +
+                            (sizeof(float) + sizeof(int)) * ((size_t)Wo * Tw + (size_t)Ho * Th);
+    if (sep_smem <= 48 * 1024 && Ho * Wo >= 64) {
+      int grid = (int)std::min<int64_t>(NC, (int64_t)kNumSMs * 16);
+      resample2d_sep_kernel<<<grid, 256, sep_smem, (cudaStream_t)stream>>>(x, y, NC, Hi, Wi, Ho, Wo, ih, wh, Th, iw, ww,
+                                                                         Tw);
+    } else {
+      resample2d_kernel<<<ew_grid(total, 256, 2), 256, 0, (cudaStream_t)stream>>>(x, y, NC, Hi, Wi, Ho, Wo, ih, wh, Th,
+                                                                                 iw, ww, Tw);
+    }
   }
   GB_CHECK_LAUNCH();
   return 0;

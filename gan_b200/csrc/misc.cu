@@ -9,28 +9,27 @@ template <bool ACC>
 __global__ void __launch_bounds__(256) chan_copy_kernel(const float* __restrict__ src, float* __restrict__ dst, int N,
                                                         int src_C, int src_c0, int dst_C, int dst_c0, int ncopy,
                                                         int HW, bool vec) {
+  // the (n, c) pair of a source row: consecutive copied rows are contiguous in neither tensor, only within a row
   if (vec) {
-    int hw4 = HW >> 2;
-    int64_t total = (int64_t)N * ncopy * hw4;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-      int j = (int)(i % hw4);
-      int64_t r = i / hw4;
-      int c = (int)(r % ncopy), n = (int)(r / ncopy);
-      float4 v = reinterpret_cast<const float4*>(src + ((int64_t)n * src_C + src_c0 + c) * HW)[j];
+    const int hw4 = HW >> 2;
+    grid_stride((int64_t)N * ncopy * hw4, [&](auto i) {
+      const int j = (int)(i % hw4);
+      const auto r = i / hw4;
+      const int c = (int)(r % ncopy), n = (int)(r / ncopy);
+      float4 v = __ldg(reinterpret_cast<const float4*>(src + ((int64_t)n * src_C + src_c0 + c) * HW) + j);
       float4* d = reinterpret_cast<float4*>(dst + ((int64_t)n * dst_C + dst_c0 + c) * HW) + j;
       if (ACC) { float4 o = *d; v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w; }
       *d = v;
-    }
+    });
   } else {
-    int64_t total = (int64_t)N * ncopy * HW;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-      int j = (int)(i % HW);
-      int64_t r = i / HW;
-      int c = (int)(r % ncopy), n = (int)(r / ncopy);
+    grid_stride((int64_t)N * ncopy * HW, [&](auto i) {
+      const int j = (int)(i % HW);
+      const auto r = i / HW;
+      const int c = (int)(r % ncopy), n = (int)(r / ncopy);
       float v = src[((int64_t)n * src_C + src_c0 + c) * HW + j];
       float* d = dst + ((int64_t)n * dst_C + dst_c0 + c) * HW + j;
       *d = ACC ? *d + v : v;
-    }
+    });
   }
 }
 

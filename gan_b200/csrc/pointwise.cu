@@ -176,10 +176,20 @@ __global__ void __launch_bounds__(256) reduce_groups_kernel(const float* __restr
   float acc = 0.f;
   if (rmode == 1) {
     // iterate over n in [split::nsplit], hw by threads
-    for (int n = split; n < N; n += nsplit) {
-      const float* xr = x + ((int64_t)n * C + g) * HW;
-      const float* yr = y ? y + ((int64_t)n * C + g) * HW : nullptr;
-      for (int i = threadIdx.x; i < HW; i += blockDim.x) acc += yr ? xr[i] * yr[i] : xr[i];
+    if (HW >= 64) {
+      for (int n = split; n < N; n += nsplit) {
+        const float* xr = x + ((int64_t)n * C + g) * HW;
+        const float* yr = y ? y + ((int64_t)n * C + g) * HW : nullptr;
+        for (int i = threadIdx.x; i < HW; i += blockDim.x) acc += yr ? xr[i] * yr[i] : xr[i];
+      }
+    } else {
+      // small planes: threads over (n, hw) pairs so that all lanes have work
+      const int total = N * HW;
+      for (int j = split * 256 + threadIdx.x; j < total; j += nsplit * 256) {
+        const int n = j / HW, i = j - n * HW;
+        const int64_t idx = ((int64_t)n * C + g) * HW + i;
+        acc += y ? x[idx] * y[idx] : x[idx];
+      }
     }
   } else {
     int64_t len = rmode == 2 ? (int64_t)C * HW : (int64_t)N * C * HW;
@@ -282,7 +292,7 @@ extern "C" int ganb200_reduce(const float* x, const float* y, float* out, int N,
   } else if (rmode >= 1 && rmode <= 3) {
     int groups = rmode == 1 ? C : (rmode == 2 ? N : 1);
     int64_t per_group = (int64_t)N * C * HW / groups;
-    int max_split = rmode == 1 ? N : (int)((per_group + 2047) / 2048);
+    int max_split = rmode == 1 ? (HW >= 64 ? N : (int)(((int64_t)N * HW + 255) / 256)) : (int)((per_group + 2047) / 2048);
     int want = (kNumSMs * 4 + groups - 1) / groups;
     int nsplit = want < max_split ? want : max_split;
     if (nsplit < 1) nsplit = 1;
