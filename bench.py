@@ -276,13 +276,12 @@ def run_native(args):
     mem_gb = torch.cuda.max_memory_allocated(device) / 2**30
     dp.remove()
 
-    if world > 1:
-        # last collective of the run: every rank passes it, then only rank 0 has (CPU-side) work left
-        tdist.barrier()
-        torch.cuda.synchronize()
-        tdist.destroy_process_group()
+    torch.cuda.synchronize()
     if rank != 0:
-        return
+        # no collective and no communicator teardown after the timed region: the captured CUDA graphs still reference
+        # the NCCL communicator, and a rank must never wait for rank 0's CPU-side reporting.  Hard exit, status 0.
+        sys.stdout.flush()
+        os._exit(0)
     pk = peaks()
     eng = "tc" if "tc" in conv and conv["tc"][1] >= conv.get("simt", (0, 0, 0))[1] * 0.25 else "simt"
     fl, sec, calls = conv.get(eng, (0.0, 1.0, 0))
@@ -312,6 +311,9 @@ def run_native(args):
         line["cpu_baseline"] = {"value": rate, "unit": "images/s", "cores": threads, "kind": "port",
                                 "sample": f"{n} full iterations at batch {args.cpu_batch} on torch CPU ops (fp32)"}
     print(json.dumps(line), flush=True)
+    if world > 1:
+        sys.stdout.flush()
+        os._exit(0)
 
 
 def main():
