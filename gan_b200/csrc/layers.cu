@@ -69,7 +69,7 @@ __global__ void __launch_bounds__(256) prelu_reduce_kernel(const float* __restri
     }
   } else {
     int c = blockIdx.x;
-    if (HW >= 64) {
+    if (HW >= 1024) {
       for (int n = split; n < N; n += nsplit) {
         int64_t base = ((int64_t)n * C + c) * HW;
         for (int i = threadIdx.x; i < HW; i += blockDim.x) {
@@ -159,7 +159,7 @@ static int rows_grid(int64_t rows, int HW) {
 static void prelu_reduce_dims(int N, int C, int HW, int a_n, dim3* grid) {
   int groups = a_n == 1 ? 1 : C;
   int64_t per_group = (int64_t)N * C * HW / groups;
-  int max_split = a_n == 1 ? (int)((per_group + 2047) / 2048) : (HW >= 64 ? N : (int)(((int64_t)N * HW + 255) / 256));
+  int max_split = a_n == 1 ? (int)((per_group + 2047) / 2048) : (HW >= 1024 ? N : (int)(((int64_t)N * HW + 255) / 256));
   int want = (kNumSMs * 4 + groups - 1) / groups;
   int nsplit = want < max_split ? want : max_split;
   if (nsplit < 1) nsplit = 1;
@@ -249,7 +249,7 @@ __global__ void __launch_bounds__(256) bn_reduce_kernel(const float* __restrict_
   float m = PASS >= 1 ? mean[c] : 0.f;
   float is = PASS == 2 ? invstd[c] : 0.f;
   float a = 0.f, b = 0.f;
-  if (HW >= 32) {
+  if (HW >= 1024) {
     for (int n = split; n < N; n += nsplit) {
       int64_t base = ((int64_t)n * C + c) * HW;
       for (int i = threadIdx.x; i < HW; i += blockDim.x) {
@@ -261,9 +261,9 @@ __global__ void __launch_bounds__(256) bn_reduce_kernel(const float* __restrict_
     }
   } else {
     // small HW: threads over (n, hw) pairs
-    int64_t total = (int64_t)N * HW;
-    for (int64_t j = (int64_t)split * blockDim.x + threadIdx.x; j < total; j += (int64_t)nsplit * blockDim.x) {
-      int n = (int)(j / HW), i = (int)(j % HW);
+    const int total = N * HW;  // < 2^31: N * HW < N * 1024
+    for (int j = split * 256 + threadIdx.x; j < total; j += nsplit * 256) {
+      const int n = j / HW, i = j - n * HW;
       int64_t idx = ((int64_t)n * C + c) * HW + i;
       float xv = x[idx];
       if (PASS == 0) a += xv;
@@ -323,7 +323,7 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const float* __restrict__
 
 static dim3 bn_reduce_grid(int N, int C, int HW) {
   int want = (kNumSMs * 4 + C - 1) / C;
-  int max_split = HW >= 32 ? N : (int)(((int64_t)N * HW + 255) / 256);
+  int max_split = HW >= 1024 ? N : (int)(((int64_t)N * HW + 255) / 256);
   int nsplit = want < max_split ? want : max_split;
   if (nsplit < 1) nsplit = 1;
   return dim3(C, nsplit);

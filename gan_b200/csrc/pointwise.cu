@@ -176,7 +176,7 @@ __global__ void __launch_bounds__(256) reduce_groups_kernel(const float* __restr
   float acc = 0.f;
   if (rmode == 1) {
     // iterate over n in [split::nsplit], hw by threads
-    if (HW >= 64) {
+    if (HW >= 1024) {
       for (int n = split; n < N; n += nsplit) {
         const float* xr = x + ((int64_t)n * C + g) * HW;
         const float* yr = y ? y + ((int64_t)n * C + g) * HW : nullptr;
@@ -292,7 +292,7 @@ extern "C" int ganb200_reduce(const float* x, const float* y, float* out, int N,
   } else if (rmode >= 1 && rmode <= 3) {
     int groups = rmode == 1 ? C : (rmode == 2 ? N : 1);
     int64_t per_group = (int64_t)N * C * HW / groups;
-    int max_split = rmode == 1 ? (HW >= 64 ? N : (int)(((int64_t)N * HW + 255) / 256)) : (int)((per_group + 2047) / 2048);
+    int max_split = rmode == 1 ? (HW >= 1024 ? N : (int)(((int64_t)N * HW + 255) / 256)) : (int)((per_group + 2047) / 2048);
     int want = (kNumSMs * 4 + groups - 1) / groups;
     int nsplit = want < max_split ? want : max_split;
     if (nsplit < 1) nsplit = 1;

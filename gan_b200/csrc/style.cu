@@ -47,23 +47,36 @@ __global__ void __launch_bounds__(256) noise_fill_kernel(float4* __restrict__ z,
 }
 
 // ------------------------------------------------------------------------------------------------ demodulation
-// sinv[b,o] = rsqrt(alpha^2 * sum_i s[b,i]^2 * wsq[o,i] + eps);  one block per b, s^2 staged in shared memory
-__global__ void __launch_bounds__(128) demod_kernel(const float* __restrict__ s, const float* __restrict__ wsq,
-                                                    float* __restrict__ sinv, int C, int K, float alpha2, float eps) {
-  extern __shared__ float s2[];
-  const int b = blockIdx.x;
-  for (int i = threadIdx.x; i < C; i += 128) {
-    float v = s[(int64_t)b * C + i];
+// sinv[b,o] = rsqrt(alpha^2 * sum_i s[b,i]^2 * wsq[o,i] + eps).  A [B,C]x[C,K] product: one block = DEMOD_BT samples
+// (s^2 staged in shared memory) x a slice of the output channels, so a wsq row is read once per DEMOD_BT samples.
+constexpr int DEMOD_BT = 8;
+__global__ void __launch_bounds__(256) demod_kernel(const float* __restrict__ s, const float* __restrict__ wsq,
+                                                    float* __restrict__ sinv, int B, int C, int K, float alpha2,
+                                                    float eps) {
+  extern __shared__ float s2[];  // [DEMOD_BT][C]
+  const int b0 = blockIdx.x * DEMOD_BT;
+  for (int i = threadIdx.x; i < DEMOD_BT * C; i += 256) {
+    const int bl = i / C, c = i - bl * C;
+    const float v = (b0 + bl < B) ? s[(int64_t)(b0 + bl) * C + c] : 0.f;
     s2[i] = v * v;
   }
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  for (int o = warp; o < K; o += 4) {
+  for (int o = blockIdx.y * 8 + warp; o < K; o += gridDim.y * 8) {
     const float* wr = wsq + (int64_t)o * C;
-    float acc = 0.f;
-    for (int i = lane; i < C; i += 32) acc = fmaf(s2[i], wr[i], acc);
-    acc = warp_sum(acc);
-    if (lane == 0) sinv[(int64_t)b * K + o] = rsqrtf(alpha2 * acc + eps);
+    float acc[DEMOD_BT];
+#pragma unroll
+    for (int j = 0; j < DEMOD_BT; ++j) acc[j] = 0.f;
+    for (int i = lane; i < C; i += 32) {
+      const float w = __ldg(wr + i);
+#pragma unroll
+      for (int j = 0; j < DEMOD_BT; ++j) acc[j] = fmaf(s2[j * C + i], w, acc[j]);
+    }
+#pragma unroll
+    for (int j = 0; j < DEMOD_BT; ++j) {
+      const float t = warp_sum(acc[j]);
+      if (lane == 0 && b0 + j < B) sinv[(int64_t)(b0 + j) * K + o] = rsqrtf(alpha2 * t + eps);
+    }
   }
 }
 
@@ -232,7 +245,12 @@ extern "C" int ganb200_noise_fill(float* z, int64_t n, const int64_t* rng_state,
 
 extern "C" int ganb200_demod(const float* s, const float* wsq, float* sinv, int B, int C, int K, float alpha, float eps,
                              void* stream) {
-  demod_kernel<<<B, 128, sizeof(float) * C, GB_S(stream)>>>(s, wsq, sinv, C, K, alpha * alpha, eps);
+  const int bx = (B + DEMOD_BT - 1) / DEMOD_BT;
+  int by = (2 * kNumSMs + bx - 1) / bx;
+  by = std::max(1, std::min(by, (K + 7) / 8));
+  const size_t smem = sizeof(float) * DEMOD_BT * C;
+  GB_REQUIRE(smem <= 48 * 1024, GANB200_BAD_SHAPE, "demod: C too large for the shared-memory stage");
+  demod_kernel<<<dim3(bx, by), 256, smem, GB_S(stream)>>>(s, wsq, sinv, B, C, K, alpha * alpha, eps);
   GB_CHECK_LAUNCH();
   return 0;
 }
