@@ -249,7 +249,13 @@ extern "C" int ganb200_demod(const float* s, const float* wsq, float* sinv, int 
   int by = (2 * kNumSMs + bx - 1) / bx;
   by = std::max(1, std::min(by, (K + 7) / 8));
   const size_t smem = sizeof(float) * DEMOD_BT * C;
-  GB_REQUIRE(smem <= 48 * 1024, GANB200_BAD_SHAPE, "demod: C too large for the shared-memory stage");
+  constexpr size_t kDemodSmemMax = 160 * 1024;  // C <= 5120 (the widest concat of the final pair is 1590)
+  GB_REQUIRE(smem <= kDemodSmemMax, GANB200_BAD_SHAPE, "demod: C too large for the shared-memory stage");
+  static bool configured = false;
+  if (!configured) {
+    GB_CHECK_CUDA(cudaFuncSetAttribute(demod_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kDemodSmemMax));
+    configured = true;
+  }
   demod_kernel<<<dim3(bx, by), 256, smem, GB_S(stream)>>>(s, wsq, sinv, B, C, K, alpha * alpha, eps);
   GB_CHECK_LAUNCH();
   return 0;

@@ -59,6 +59,14 @@ CONV_CASES = [
     (4, 108, 16, 16, 3, 5, 1, 2, 1),     # ToRGB: K = 3
     (4, 64, 10, 10, 64, 3, 2, 1, 1),     # stride 2, replicate pad, even padded size
     (4, 40, 7, 9, 24, 3, 2, 1, 0),       # stride 2, zero pad, odd sizes
+    (4, 64, 64, 64, 64, 3, 2, 1, 0),     # cfg4 critic: stride-2 3x3, zero pad, 64 -> 32
+    (4, 32, 64, 64, 64, 3, 1, 1, 0),     # cfg4 critic: 3x3 zero pad at full resolution
+    (4, 513, 4, 4, 512, 3, 1, 1, 0),     # cfg4 critic: conv after the batch-stddev channel
+    (4, 512, 4, 4, 512, 4, 1, 0, 0),     # cfg4 critic: 4x4 valid conv -> 1x1
+    (4, 48, 64, 64, 48, 3, 1, 1, 1),     # dominant G13_5 modconv shape (k3 @ 64x64)
+    (2, 96, 64, 64, 96, 5, 1, 2, 1),     # dominant G13_5 modconv shape (k5 @ 64x64)
+    (4, 96, 32, 32, 96, 5, 1, 2, 1),     # k5 @ 32x32
+    (4, 192, 16, 16, 96, 3, 1, 1, 1),    # k3 @ 16x16
 ]
 
 
@@ -106,6 +114,41 @@ def test_conv_family_tcgen05(cu, ref, case, scales):
     if cu.lib.ganb200_conv2d_tc_eligible(ctypes.byref(d), KN.WGRAD):
         dw = cu.conv_wgrad(g(x), g(dy), (R, R), stride, pad, pm, 0.1, g(isc), g(osc), engine=2)
         assert rel(dw, ref.conv_wgrad(x, dy, (R, R), stride, pad, pm, 0.1, isc, osc)) < BF16_TOL
+        ran += 1
+    if ran == 0:
+        pytest.skip("shape not eligible for the tcgen05 engine")
+
+
+def bf16r(t):
+    return t.to(torch.bfloat16).to(torch.float32)
+
+
+@pytest.mark.parametrize("case", CONV_CASES)
+def test_conv_family_tcgen05_exact_on_rounded_operands(cu, ref, case):
+    """The engine rounds (x*iscale), (dy*oscale) and w to bf16 and accumulates in fp32: against the oracle fed the SAME
+    rounded operands only the summation order differs, so any indexing / border / tap error shows (the 1e-2 test above
+    would hide a wrong border pixel)."""
+    N, C, H, W, K, R, stride, pad, pm = case
+    torch.manual_seed(7)
+    x, w, b = rnd(N, C, H, W), rnd(K, C, R, R), rnd(K)
+    isc, osc = torch.rand(N, C) + 0.5, torch.rand(N, K) + 0.5
+    P, Q = KN.out_hw(H, W, R, R, stride, pad)
+    d = KN.ConvDesc(N, C, H, W, K, R, R, stride, pad, pm, P, Q, 0.1, 0)
+    dy = rnd(N, K, P, Q)
+    xr, wr = bf16r(x * isc[:, :, None, None]), bf16r(w)
+    dyr = bf16r(dy * osc[:, :, None, None])
+    tol, ran = 2e-4, 0
+    if cu.lib.ganb200_conv2d_tc_eligible(ctypes.byref(d), KN.FPROP):
+        y = cu.conv_fprop(g(x), g(w), g(b), stride, pad, pm, 0.1, g(isc), g(osc), engine=2)
+        assert rel(y, ref.conv_fprop(xr, wr, b, stride, pad, pm, 0.1, None, osc)) < tol
+        ran += 1
+    if cu.lib.ganb200_conv2d_tc_eligible(ctypes.byref(d), KN.DGRAD):
+        dx = cu.conv_dgrad(g(dy), g(w), (H, W), stride, pad, pm, 0.1, g(isc), g(osc), engine=2)
+        assert rel(dx, ref.conv_dgrad(dyr, wr, (H, W), stride, pad, pm, 0.1, isc, None)) < tol
+        ran += 1
+    if cu.lib.ganb200_conv2d_tc_eligible(ctypes.byref(d), KN.WGRAD):
+        dw = cu.conv_wgrad(g(x), g(dy), (R, R), stride, pad, pm, 0.1, g(isc), g(osc), engine=2)
+        assert rel(dw, ref.conv_wgrad(xr, dyr, (R, R), stride, pad, pm, 0.1, None, None)) < tol
         ran += 1
     if ran == 0:
         pytest.skip("shape not eligible for the tcgen05 engine")
@@ -320,6 +363,14 @@ def test_demod_and_scale_reduce(cu, ref):
         gx, gsr = cu.scale_reduce(g(dxs), g(s), g(x))
         gx_r, gsr_r = ref.scale_reduce(dxs, s, x)
         assert rel(gx, gx_r) < FP32_TOL and rel(gsr, gsr_r) < 1e-4
+
+
+@pytest.mark.parametrize("B,C,K", [(12, 1590, 396), (3, 2049, 17), (256, 780, 396)])
+def test_demod_wide_inputs(cu, ref, B, C, K):
+    """root 1x1 modconvs read the whole concat (780 ... 1590 channels): the staged s^2 tile exceeds 48 KB"""
+    torch.manual_seed(12)
+    s, wsq = rnd(B, C) + 1.5, torch.rand(K, C) * 9
+    assert rel(cu.demod(g(s), g(wsq), 0.2, 1e-8), ref.demod(s, wsq, 0.2, 1e-8)) < FP32_TOL
 
 
 def test_fused_style_layer_on_gpu_matches_unfused_ops(cu):

@@ -85,7 +85,11 @@ def test_config_cpu_port_matches_reference_golden(ref_backend, name):
 # there, so the bf16 engine is checked block by block on identical inputs instead (test_cfg5_blockwise_tcgen05).
 TOL_FP32 = {"cfg1": dict(tol_out=2e-4, tol_loss=2e-4, tol_upd=5e-3), "cfg4": dict(tol_out=2e-4, tol_loss=2e-4, tol_upd=5e-3),
             "cfg5": dict(tol_out=1e-3, tol_loss=1e-3, tol_upd=5e-2)}
-TOL_BF16 = {"cfg1": dict(tol_out=1e-2, tol_loss=2e-2, tol_upd=2e-2), "cfg4": dict(tol_out=1e-2, tol_loss=2e-2, tol_upd=2e-2),
+# cfg4's third critic loss is the WGAN-GP term mean((|g|-1)^2) with |g| ~ 0.45 at init: d(term)/term = 2|g|/(|g|-1) * d|g|/|g|
+# ~ -1.6x the relative error of the gradient norm, itself the product of a 12-conv double backward in bf16 (measured
+# 2.7 % on the term = 1.6 % on |g|; the fp32 engine matches to 2e-4, and the engine is exact on bf16-rounded operands,
+# test_conv_family_tcgen05_exact_on_rounded_operands) -> 5e-2 on the losses of this config.
+TOL_BF16 = {"cfg1": dict(tol_out=1e-2, tol_loss=2e-2, tol_upd=2e-2), "cfg4": dict(tol_out=1e-2, tol_loss=5e-2, tol_upd=2e-2),
             "cfg5": dict(tol_out=5e-2, tol_loss=None, tol_upd=None, chain=False)}
 
 
