@@ -168,6 +168,51 @@ struct TcSmem {
   static constexpr int BYTES = STAGES * (A_STAGE_BYTES + B_STAGE_BYTES) + 1024 /*align*/ + 256 /*barriers*/;
 };
 
+// ------------------------------------------------------------------------------------------------ epilogue
+// One thread = one output pixel, v[j] = accumulator of output channel kc + j (32 consecutive channels out of TMEM).
+// y[k] = v * alpha * oscale[k] + bias[k], stored to the NCHW plane of channel k (plane stride `plane_bytes`); a warp
+// writes 32 consecutive pixels of one channel per store instruction (128 B).  The epilogue warps are the only ones
+// that touch global memory from registers, and with one or two CTAs per SM there are 4-8 of them per SM: every
+// instruction per element counts (the first version spent ~25 on 64-bit index math and per-element null checks and
+// was the kernel's critical path), so the pointer checks are template parameters, the channel guard only exists in
+// the tail variant and the address advances by one 32-bit add per channel.
+template <bool HAS_OSC, bool HAS_BIAS, bool FULL>
+__device__ __forceinline__ void epi_store32(const float (&v)[32], char* yk, uint32_t plane_bytes, int nvalid, float alpha,
+                                            const float* __restrict__ osc, const float* __restrict__ bias) {
+  uint32_t off = 0;
+#pragma unroll
+  for (int j = 0; j < 32; ++j, off += plane_bytes) {
+    if (FULL || j < nvalid) {
+      float sc = alpha;
+      if (HAS_OSC) sc *= __ldg(osc + j);
+      float o = v[j] * sc;
+      if (HAS_BIAS) o += __ldg(bias + j);
+      *reinterpret_cast<float*>(yk + off) = o;
+    }
+  }
+}
+
+__device__ __forceinline__ void epi_chunk(const float (&v)[32], char* yk, uint32_t plane_bytes, int nvalid, float alpha,
+                                          const float* osc, const float* bias) {
+  if (nvalid >= 32) {
+    if (osc) {
+      if (bias) epi_store32<true, true, true>(v, yk, plane_bytes, 32, alpha, osc, bias);
+      else epi_store32<true, false, true>(v, yk, plane_bytes, 32, alpha, osc, bias);
+    } else {
+      if (bias) epi_store32<false, true, true>(v, yk, plane_bytes, 32, alpha, osc, bias);
+      else epi_store32<false, false, true>(v, yk, plane_bytes, 32, alpha, osc, bias);
+    }
+  } else {
+    if (osc) {
+      if (bias) epi_store32<true, true, false>(v, yk, plane_bytes, nvalid, alpha, osc, bias);
+      else epi_store32<true, false, false>(v, yk, plane_bytes, nvalid, alpha, osc, bias);
+    } else {
+      if (bias) epi_store32<false, true, false>(v, yk, plane_bytes, nvalid, alpha, osc, bias);
+      else epi_store32<false, false, false>(v, yk, plane_bytes, nvalid, alpha, osc, bias);
+    }
+  }
+}
+
 // Persistent: each CTA walks tiles blockIdx.x, +gridDim.x, ... (n-tile fastest so that concurrent CTAs share the
 // activation tile in L2).  The accumulator is double-buffered in TMEM (2 x BN columns): while the epilogue warps drain
 // tile i, the producer and the MMA issuer are already in the main loop of tile i+1.
@@ -188,7 +233,6 @@ __global__ void __launch_bounds__(TC_THREADS) tc_conv_kernel(const __grid_consta
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int k_chunks = (p.C + BK - 1) / BK;
-  const int iters = p.taps * k_chunks;
   const int total_tiles = p.tiles_m * p.tiles_n;
   constexpr uint32_t TMEM_COLS = 2 * BN;
 
@@ -212,50 +256,54 @@ __global__ void __launch_bounds__(TC_THREADS) tc_conv_kernel(const __grid_consta
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    if (lane == 0) {
-      int it = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        int t = tile / p.tiles_n;
-        const int k0 = (tile - t * p.tiles_n) * BN;
-        const int tq = t % p.tiles_q; t /= p.tiles_q;
-        const int tp = t % p.tiles_p; t /= p.tiles_p;
-        const int q0 = tq * p.bw, p0 = tp * p.bh, n0 = t * p.bn;
-        for (int i = 0; i < iters; ++i, ++it) {
-          const int stage = it % STAGES;
-          const uint32_t phase = (it / STAGES) & 1;
+    // producer: the whole warp walks the loop (uniform control flow), the elected lane issues
+    const bool leader = elect_one();
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      int t = tile / p.tiles_n;
+      const int k0 = (tile - t * p.tiles_n) * BN;
+      const int tq = t % p.tiles_q; t /= p.tiles_q;
+      const int tp = t % p.tiles_p; t /= p.tiles_p;
+      const int q0 = tq * p.bw, p0 = tp * p.bh, n0 = t * p.bn;
+      for (int tap = 0; tap < p.taps; ++tap)
+        for (int kc = 0; kc < k_chunks; ++kc) {
           mbar_wait(&empty[stage], phase ^ 1);
-          const int tap = i / k_chunks, kc = i - tap * k_chunks;
-          mbar_expect_tx(&full[stage], A_STAGE_BYTES + B_STAGE_BYTES);
-          tma_load_4d(smA + stage * A_STAGE_BYTES, &tmA, &full[stage], kc * BK, q0 * p.in_step + p.dw[tap],
-                      p0 * p.in_step + p.dh[tap], n0);
-          tma_load_3d(smB + stage * B_STAGE_BYTES, &tmB, &full[stage], kc * BK, k0, tap);
+          if (leader) {
+            mbar_expect_tx(&full[stage], A_STAGE_BYTES + B_STAGE_BYTES);
+            tma_load_4d(smA + stage * A_STAGE_BYTES, &tmA, &full[stage], kc * BK, q0 * p.in_step + p.dw[tap],
+                        p0 * p.in_step + p.dh[tap], n0);
+            tma_load_3d(smB + stage * B_STAGE_BYTES, &tmB, &full[stage], kc * BK, k0, tap);
+          }
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
-      }
     }
+    __syncwarp();
   } else if (warp == 1) {
-    if (lane == 0) {
-      const uint32_t idesc = make_idesc_bf16(TILE_M, p.n_umma, 0, 0);
-      int it = 0, local = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++local) {
-        const int acc = local & 1;
-        mbar_wait(&tmem_empty[acc], ((local >> 1) & 1) ^ 1);   // epilogue has drained this accumulator
-        tc_fence_after();
-        const uint32_t tmem_d = tmem_base + (uint32_t)(acc * BN);
-        for (int i = 0; i < iters; ++i, ++it) {
-          const int stage = it % STAGES;
-          const uint32_t phase = (it / STAGES) & 1;
+    const bool leader = elect_one();
+    const uint32_t idesc = make_idesc_bf16(TILE_M, p.n_umma, 0, 0);
+    int stage = 0, local = 0;
+    uint32_t phase = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++local) {
+      const int acc = local & 1;
+      mbar_wait(&tmem_empty[acc], ((local >> 1) & 1) ^ 1);   // epilogue has drained this accumulator
+      tc_fence_after();
+      const uint32_t tmem_d = tmem_base + (uint32_t)(acc * BN);
+      for (int tap = 0; tap < p.taps; ++tap)
+        for (int kc = 0; kc < k_chunks; ++kc) {
           mbar_wait(&full[stage], phase);
           tc_fence_after();
-          const int kc = i % k_chunks;
           const int ksub = min(BK / 16, (p.C - kc * BK + 15) / 16);
           const uint64_t adesc = make_smem_desc_sw128(smem_u32(smA + stage * A_STAGE_BYTES), 16, 1024);
           const uint64_t bdesc = make_smem_desc_sw128(smem_u32(smB + stage * B_STAGE_BYTES), 16, 1024);
-          for (int k = 0; k < ksub; ++k)  // +32 bytes (= 2 in the >>4 address field) per 16-element k step
-            mma_bf16_ss(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (i > 0 || k > 0) ? 1u : 0u);
-          mma_commit(&empty[stage]);
+          if (leader) {
+            for (int k = 0; k < ksub; ++k)  // +32 bytes (= 2 in the >>4 address field) per 16-element k step
+              mma_bf16_ss(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (tap > 0 || kc > 0 || k > 0) ? 1u : 0u);
+            mma_commit(&empty[stage]);
+          }
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
-        mma_commit(&tmem_full[acc]);
-      }
+      if (leader) mma_commit(&tmem_full[acc]);
     }
     __syncwarp();
   } else {
@@ -278,20 +326,213 @@ __global__ void __launch_bounds__(TC_THREADS) tc_conv_kernel(const __grid_consta
       const int acc = local & 1;
       mbar_wait(&tmem_full[acc], (local >> 1) & 1);
       tc_fence_after();
+      const uint32_t plane_bytes = (uint32_t)PQ * 4u;
       for (int c0 = 0; c0 < p.n_umma; c0 += 32) {
         float v[32];
         tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN + c0), v);
-        if (row_ok) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            const int k = k0 + c0 + j;
-            if (c0 + j < p.n_umma && k < p.K) {
-              float o = v[j] * p.alpha;
-              if (osc) o *= osc[k];
-              if (p.bias) o += p.bias[k];
-              ybase[(int64_t)k * PQ] = o;
-            }
+        const int kc = k0 + c0;
+        const int nvalid = min(p.n_umma - c0, p.K - kc);
+        if (row_ok && nvalid > 0)
+          epi_chunk(v, reinterpret_cast<char*>(ybase + (int64_t)kc * PQ), plane_bytes, nvalid, p.alpha,
+                    osc ? osc + kc : nullptr, p.bias ? p.bias + kc : nullptr);
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+    }
+  }
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
+
+// ------------------------------------------------------------------------------------------------ halo kernel
+// Stride-1 problems on planes of >= 256 output pixels whose taps form a dense R x S grid.  tc_conv_kernel fetches one
+// activation box per filter tap, so every input pixel crosses L2 -> shared memory R*S times and the narrow 64x64
+// convolutions of the generator are bound by that fill, not by the tensor pipe.  Here one CTA tile is MT stacked
+// sub-tiles (MT*bh output rows x bw columns, bw*bh = 128) of ONE image, and per (filter column s, 64-channel chunk) ONE
+// box of MT*bh + R - 1 input rows is loaded: the R taps of that column are the same box read from a start address
+// shifted by whole rows (bw * 128 bytes, a multiple of the 1024-byte swizzle atom, so the SWIZZLE_128B phase is
+// unchanged), and the MT sub-tiles are two more row shifts feeding MT accumulators.  Activation fill per output pixel
+// drops from R*S to S * (MT*bh + R - 1) / (MT*bh) boxes, and each weight box now serves MT*128 pixels.
+// Rings: A (halo boxes; as many stages as fit beside the B ring, >= 3) and B (weight boxes, HALO_B_STAGES x BN*128 B)
+// with their own barriers.  Measured (ncu, r01): L2 -> shared-memory fill runs at ~(bytes in flight per SM) / 2.3 us,
+// so the win comes from fewer bytes per tile AND as many of them in flight as 227 KB allow.
+constexpr int HALO_SMEM_MAX = 227 * 1024;   // opt-in shared memory of one CTA (one CTA per SM)
+constexpr int HALO_MAX_STAGES = 8;          // per ring (barrier slots)
+constexpr int HALO_B_STAGES = 4;
+constexpr int HALO_MIN_A_STAGES = 3;        // fill is latency-bound: at least two halo boxes in flight behind the one in use
+
+struct TcHaloParams {
+  int N, K, P, Q, C;
+  int R, S;             // dense tap grid; tap (r, s) reads input (p + dh0 + r, q + dw0 + s)
+  int dh0, dw0;
+  int bw, bh, mt;       // sub-tile box (bw * bh == 128) and sub-tiles per CTA tile (stacked along rows)
+  int a_bytes;          // bytes of one halo box = bw * (mt*bh + R - 1) * 128 (a multiple of 1024)
+  int a_stages;         // stages of the A ring (3..8)
+  int tiles_q, tiles_p, tiles_m, tiles_n;
+  int OH, OW, o_step, o_off_h, o_off_w;
+  int n_umma;
+  float alpha;
+  const float* oscale;
+  const float* bias;
+  float* y;
+  unsigned char tap_idx[MAX_TAPS];  // packed-weight index of grid point r * S + s
+};
+
+template <int BN>
+struct TcHaloSmem {
+  static constexpr int B_STAGE_BYTES = BN * BK * 2;
+  static constexpr int FIXED = HALO_B_STAGES * B_STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+  static constexpr int A_REGION = HALO_SMEM_MAX - FIXED;
+};
+
+template <int BN>
+__global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_halo_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                                  const __grid_constant__ CUtensorMap tmB,
+                                                                  const TcHaloParams p) {
+  constexpr int B_STAGE_BYTES = BN * BK * 2;
+  constexpr int MT_MAX = 2;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int SA = p.a_stages;
+  uint8_t* smA = smem;
+  uint8_t* smB = smem + SA * p.a_bytes;
+  uint64_t* fullA = reinterpret_cast<uint64_t*>(smB + HALO_B_STAGES * B_STAGE_BYTES);
+  uint64_t* emptyA = fullA + HALO_MAX_STAGES;
+  uint64_t* fullB = emptyA + HALO_MAX_STAGES;
+  uint64_t* emptyB = fullB + HALO_B_STAGES;
+  uint64_t* tmem_full = emptyB + HALO_B_STAGES;  // [2]
+  uint64_t* tmem_empty = tmem_full + 2;          // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int k_chunks = (p.C + BK - 1) / BK;
+  const int total_tiles = p.tiles_m * p.tiles_n;
+  const int rows_per_tile = p.mt * p.bh;
+  constexpr uint32_t TMEM_COLS = 2 * MT_MAX * BN;  // double-buffered, MT accumulators each
+
+  if (threadIdx.x == 0) {
+    prefetch_tmap(&tmA);
+    prefetch_tmap(&tmB);
+    for (int i = 0; i < SA; ++i) { mbar_init(&fullA[i], 1); mbar_init(&emptyA[i], 1); }
+    for (int i = 0; i < HALO_B_STAGES; ++i) { mbar_init(&fullB[i], 1); mbar_init(&emptyB[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 4); }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // producer: warp-uniform loops, the elected lane issues
+    const bool leader = elect_one();
+    int sa = 0, sb = 0;
+    uint32_t pa = 0, pb = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      int t = tile / p.tiles_n;
+      const int k0 = (tile - t * p.tiles_n) * BN;
+      const int tq = t % p.tiles_q; t /= p.tiles_q;
+      const int tp = t % p.tiles_p; t /= p.tiles_p;
+      const int q0 = tq * p.bw, p0 = tp * rows_per_tile, n0 = t;
+      for (int kc = 0; kc < k_chunks; ++kc)
+        for (int s = 0; s < p.S; ++s) {
+          mbar_wait(&emptyA[sa], pa ^ 1);
+          if (leader) {
+            mbar_expect_tx(&fullA[sa], (uint32_t)p.a_bytes);
+            tma_load_4d(smA + sa * p.a_bytes, &tmA, &fullA[sa], kc * BK, q0 + p.dw0 + s, p0 + p.dh0, n0);
           }
+          if (++sa == SA) { sa = 0; pa ^= 1; }
+          for (int r = 0; r < p.R; ++r) {
+            mbar_wait(&emptyB[sb], pb ^ 1);
+            if (leader) {
+              mbar_expect_tx(&fullB[sb], B_STAGE_BYTES);
+              tma_load_3d(smB + sb * B_STAGE_BYTES, &tmB, &fullB[sb], kc * BK, k0, (int)p.tap_idx[r * p.S + s]);
+            }
+            if (++sb == HALO_B_STAGES) { sb = 0; pb ^= 1; }
+          }
+        }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    const bool leader = elect_one();
+    const uint32_t idesc = make_idesc_bf16(TILE_M, p.n_umma, 0, 0);
+    const uint32_t row_bytes = (uint32_t)p.bw * 128u;  // one input row of the halo box
+    const uint32_t sub_bytes = (uint32_t)p.bh * row_bytes;
+    int sa = 0, sb = 0, local = 0;
+    uint32_t pa = 0, pb = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++local) {
+      const int acc = local & 1;
+      mbar_wait(&tmem_empty[acc], ((local >> 1) & 1) ^ 1);
+      tc_fence_after();
+      const uint32_t tmem_d = tmem_base + (uint32_t)(acc * MT_MAX * BN);
+      for (int kc = 0; kc < k_chunks; ++kc) {
+        const int ksub = min(BK / 16, (p.C - kc * BK + 15) / 16);
+        for (int s = 0; s < p.S; ++s) {
+          mbar_wait(&fullA[sa], pa);
+          tc_fence_after();
+          const uint32_t a_base = smem_u32(smA + sa * p.a_bytes);
+          for (int r = 0; r < p.R; ++r) {
+            mbar_wait(&fullB[sb], pb);
+            tc_fence_after();
+            const uint64_t bdesc = make_smem_desc_sw128(smem_u32(smB + sb * B_STAGE_BYTES), 16, 1024);
+            const uint64_t adesc0 = make_smem_desc_sw128(a_base + (uint32_t)r * row_bytes, 16, 1024);
+            const uint32_t fresh = (kc == 0 && s == 0 && r == 0) ? 0u : 1u;
+            if (leader) {
+              for (int k = 0; k < ksub; ++k)
+                mma_bf16_ss(tmem_d, adesc0 + 2 * k, bdesc + 2 * k, idesc, k == 0 ? fresh : 1u);
+              if (p.mt == 2) {
+                const uint64_t adesc1 = adesc0 + (uint64_t)(sub_bytes >> 4);
+                for (int k = 0; k < ksub; ++k)
+                  mma_bf16_ss(tmem_d + (uint32_t)BN, adesc1 + 2 * k, bdesc + 2 * k, idesc, k == 0 ? fresh : 1u);
+              }
+              mma_commit(&emptyB[sb]);
+            }
+            if (++sb == HALO_B_STAGES) { sb = 0; pb ^= 1; }
+          }
+          if (leader) mma_commit(&emptyA[sa]);
+          if (++sa == SA) { sa = 0; pa ^= 1; }
+        }
+      }
+      if (leader) mma_commit(&tmem_full[acc]);
+    }
+    __syncwarp();
+  } else {
+    const int quarter = warp & 3;
+    const int m = quarter * 32 + lane;
+    const int wl = m % p.bw, hl = m / p.bw;
+    const int64_t PQ = (int64_t)p.OH * p.OW;
+    const uint32_t plane_bytes = (uint32_t)PQ * 4u;
+    int local = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++local) {
+      int t = tile / p.tiles_n;
+      const int k0 = (tile - t * p.tiles_n) * BN;
+      const int tq = t % p.tiles_q; t /= p.tiles_q;
+      const int tp = t % p.tiles_p; t /= p.tiles_p;
+      const int n = t;
+      const int q = tq * p.bw + wl;
+      const float* osc = p.oscale ? p.oscale + (int64_t)n * p.K : nullptr;
+      const int acc = local & 1;
+      mbar_wait(&tmem_full[acc], (local >> 1) & 1);
+      tc_fence_after();
+      for (int j = 0; j < p.mt; ++j) {
+        const int pp = tp * rows_per_tile + j * p.bh + hl;
+        const bool row_ok = (q < p.Q) && (pp < p.P);
+        float* ybase = p.y + ((int64_t)n * p.K) * PQ + (int64_t)(pp * p.o_step + p.o_off_h) * p.OW + q * p.o_step +
+                       p.o_off_w;
+        for (int c0 = 0; c0 < p.n_umma; c0 += 32) {
+          float v[32];
+          tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)((acc * MT_MAX + j) * BN + c0), v);
+          const int kc = k0 + c0;
+          const int nvalid = min(p.n_umma - c0, p.K - kc);
+          if (row_ok && nvalid > 0)
+            epi_chunk(v, reinterpret_cast<char*>(ybase + (int64_t)kc * PQ), plane_bytes, nvalid, p.alpha,
+                      osc ? osc + kc : nullptr, p.bias ? p.bias + kc : nullptr);
         }
       }
       tc_fence_before();
@@ -363,6 +604,56 @@ static size_t act_bytes(int N, int Ci, int Hi, int Wi, int mat_pad) {
 }
 static size_t w_bytes(int taps, int Ko, int Ci) { return align_up((size_t)taps * Ko * cpad(Ci) * 2, 1024); }
 
+// Fills `h` and returns true when problem `q` can run on the halo kernel.
+static bool halo_plan(const TcProblem& q, int BN, TcHaloParams& h) {
+  if (q.in_step != 1 || q.taps.n < 1 || q.taps.n > MAX_TAPS) return false;
+  if ((int64_t)q.Po * q.Qo < 256 || q.Qo < 8) return false;
+  // Measured (tools/conv_bench.py, B = 256): 3-tap-wide filters over channel counts that are multiples of 64 (the
+  // critic's 64/128/256-channel 3x3 convs) run 5-10 % faster on the per-tap kernel, whose 128-byte-pitch boxes the TMA
+  // streams at full rate with two CTAs per SM; everything else (k5, 48/96/108-channel, 1x1, strided-dgrad phases) is
+  // 1.1-2.2x faster here.
+  if (q.taps.n == 9 && q.Ci % 64 == 0 && q.Ko % 64 == 0) return false;
+  int dh_lo = 127, dh_hi = -128, dw_lo = 127, dw_hi = -128;
+  for (int t = 0; t < q.taps.n; ++t) {
+    dh_lo = std::min(dh_lo, (int)q.taps.dh[t]); dh_hi = std::max(dh_hi, (int)q.taps.dh[t]);
+    dw_lo = std::min(dw_lo, (int)q.taps.dw[t]); dw_hi = std::max(dw_hi, (int)q.taps.dw[t]);
+  }
+  const int R = dh_hi - dh_lo + 1, S = dw_hi - dw_lo + 1;
+  if (R * S != q.taps.n) return false;
+  bool seen[MAX_TAPS] = {false};
+  for (int t = 0; t < q.taps.n; ++t) {
+    const int g = (q.taps.dh[t] - dh_lo) * S + (q.taps.dw[t] - dw_lo);
+    if (seen[g]) return false;
+    seen[g] = true;
+    h.tap_idx[g] = (unsigned char)t;
+  }
+  // tile: the (bw, bh, mt) with the least L2 -> shared-memory fill over the whole problem
+  double best = -1.0;
+  // bw >= 32 keeps the epilogue's warp stores at 128 contiguous bytes (planes narrower than 32: the whole row)
+  const int a_region = BN == 128 ? TcHaloSmem<128>::A_REGION : TcHaloSmem<64>::A_REGION;
+  for (int bw = std::min(32, pow2ceil(q.Qo)); bw <= TILE_M; bw <<= 1) {
+    const int bh = TILE_M / bw;
+    if (bw > pow2ceil(q.Qo)) continue;
+    for (int mt = 1; mt <= 2; ++mt) {
+      const int rows = mt * bh + R - 1;
+      const int64_t a_bytes = (int64_t)bw * rows * 128;
+      if (a_bytes * HALO_MIN_A_STAGES > a_region || rows > 256) continue;
+      const int64_t tiles = (int64_t)ceil_div(q.Qo, bw) * ceil_div(q.Po, mt * bh) * q.N;
+      const double cost = (double)tiles * ((double)S * a_bytes + (double)R * S * std::min(q.Ko, BN) * 128.0);
+      if (best < 0 || cost < best) { best = cost; h.bw = bw; h.bh = bh; h.mt = mt; }
+    }
+  }
+  if (best < 0) return false;
+  h.N = q.N; h.K = q.Ko; h.P = q.Po; h.Q = q.Qo; h.C = q.Ci;
+  h.R = R; h.S = S; h.dh0 = dh_lo; h.dw0 = dw_lo;
+  h.a_bytes = h.bw * (h.mt * h.bh + R - 1) * 128;
+  h.a_stages = std::min(HALO_MAX_STAGES, a_region / h.a_bytes);
+  h.tiles_q = ceil_div(q.Qo, h.bw); h.tiles_p = ceil_div(q.Po, h.mt * h.bh);
+  h.tiles_m = h.tiles_q * h.tiles_p * q.N; h.tiles_n = ceil_div(q.Ko, BN);
+  h.OH = q.OH; h.OW = q.OW; h.o_step = q.o_step; h.o_off_h = q.o_off_h; h.o_off_w = q.o_off_w;
+  return true;
+}
+
 static int pack_input(const float* in, const float* in_scale, __nv_bfloat16* act, int N, int Ci, int Hi, int Wi,
                       int mat_pad, cudaStream_t s) {
   const int Cp = cpad(Ci), Hp = Hi + 2 * mat_pad;
@@ -391,6 +682,31 @@ static int launch_tc(const CUtensorMap& ta, const CUtensorMap& tb, const TcConvP
   return 0;
 }
 
+template <int BN>
+static int launch_halo(const CUtensorMap& ta, const CUtensorMap& tb, const TcHaloParams& p, dim3 grid, cudaStream_t s) {
+  static bool configured = false;
+  if (!configured) {
+    GB_CHECK_CUDA(cudaFuncSetAttribute(tc_conv_halo_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       HALO_SMEM_MAX));
+    configured = true;
+  }
+  const int smem = TcHaloSmem<BN>::FIXED + p.a_stages * p.a_bytes;
+  tc_conv_halo_kernel<BN><<<grid, TC_THREADS, smem, s>>>(ta, tb, p);
+  GB_CHECK_LAUNCH();
+  return 0;
+}
+
+// 1 = use the halo kernel where it applies (default), 0 = always the per-tap kernel.  GANB200_CONV_HALO=0 in the
+// environment or ganb200_conv_halo_mode(0) switch it off (parity tests run both).
+static int g_halo_mode = -1;
+static int halo_mode() {
+  if (g_halo_mode < 0) {
+    const char* e = getenv("GANB200_CONV_HALO");
+    g_halo_mode = (e && e[0] == '0') ? 0 : 1;
+  }
+  return g_halo_mode;
+}
+
 // `act`: the packed input; `wb`: scratch for this problem's packed weights
 static int run_problem(const TcProblem& q, const __nv_bfloat16* act, const float* w, __nv_bfloat16* wb, float* out,
                        const float* out_scale, const float* bias, cudaStream_t s) {
@@ -399,6 +715,28 @@ static int run_problem(const TcProblem& q, const __nv_bfloat16* act, const float
     int64_t total = (int64_t)NT * q.Ko * Cp;
     pack_weight_kernel<<<ew_grid(total, 256, 1), 256, 0, s>>>(w, wb, q.Ko, q.Ci, Cp, q.w_sk, q.w_sc, q.taps);
     GB_CHECK_LAUNCH();
+  }
+  const int BN = q.Ko > 64 ? 128 : 64;   // 64 < Ko < 128 (96, 108): one 128-wide tile, the activations are read once
+  {
+    TcHaloParams h;
+    if (halo_mode() == 1 && halo_plan(q, BN, h)) {
+      h.n_umma = q.Ko >= BN ? BN : (q.Ko + 15) / 16 * 16;
+      h.alpha = q.alpha; h.oscale = out_scale; h.bias = bias; h.y = out;
+      CUtensorMap ta, tb;
+      uint64_t dims[4] = {(uint64_t)q.Ci, (uint64_t)Wp, (uint64_t)Hp, (uint64_t)q.N};
+      uint64_t str[3] = {(uint64_t)Cp * 2, (uint64_t)Wp * Cp * 2, (uint64_t)Hp * Wp * Cp * 2};
+      uint32_t box[4] = {BK, (uint32_t)h.bw, (uint32_t)(h.mt * h.bh + h.R - 1), 1};
+      int rc = make_tmap_bf16(&ta, act, 4, dims, str, box);
+      if (rc) return rc;
+      uint64_t wd[3] = {(uint64_t)q.Ci, (uint64_t)q.Ko, (uint64_t)NT};
+      uint64_t wst[2] = {(uint64_t)Cp * 2, (uint64_t)q.Ko * Cp * 2};
+      uint32_t wbox[3] = {BK, (uint32_t)BN, 1};
+      rc = make_tmap_bf16(&tb, wb, 3, wd, wst, wbox);
+      if (rc) return rc;
+      const int64_t total = (int64_t)h.tiles_m * h.tiles_n;
+      dim3 grid((unsigned)std::min<int64_t>(total, kNumSMs));  // one CTA per SM (shared memory and TMEM are per-SM here)
+      return BN == 128 ? launch_halo<128>(ta, tb, h, grid, s) : launch_halo<64>(ta, tb, h, grid, s);
+    }
   }
   TcConvParams p;
   p.N = q.N; p.K = q.Ko; p.P = q.Po; p.Q = q.Qo; p.taps = NT; p.C = q.Ci;
@@ -416,7 +754,6 @@ static int run_problem(const TcProblem& q, const __nv_bfloat16* act, const float
   p.alpha = q.alpha; p.oscale = out_scale; p.bias = bias; p.y = out;
   p.in_step = q.in_step; p.OH = q.OH; p.OW = q.OW; p.o_step = q.o_step; p.o_off_h = q.o_off_h; p.o_off_w = q.o_off_w;
   for (int t = 0; t < NT; ++t) { p.dh[t] = q.taps.dh[t]; p.dw[t] = q.taps.dw[t]; }
-  const int BN = q.Ko >= 128 ? 128 : 64;
   p.n_umma = q.Ko >= BN ? BN : (q.Ko + 15) / 16 * 16;
   CUtensorMap ta, tb;
   {
@@ -646,15 +983,16 @@ __global__ void __launch_bounds__(TC_THREADS) tc_wgrad_kernel(const __grid_const
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    if (lane == 0) {
-      for (int it = 0; it < iters; ++it) {
-        const int stage = it % STAGES;
-        const uint32_t phase = (it / STAGES) & 1;
-        mbar_wait(&empty[stage], phase ^ 1);
-        int t = ch_beg + it;
-        const int tq = t % p.tiles_q; t /= p.tiles_q;
-        const int tp = t % p.tiles_p; t /= p.tiles_p;
-        const int q0 = tq * p.bw, p0 = tp * p.bh, n0 = t * p.bn;
+    const bool leader = elect_one();   // warp-uniform loop, the elected lane issues (see tc_ptx.cuh)
+    for (int it = 0; it < iters; ++it) {
+      const int stage = it % STAGES;
+      const uint32_t phase = (it / STAGES) & 1;
+      mbar_wait(&empty[stage], phase ^ 1);
+      int t = ch_beg + it;
+      const int tq = t % p.tiles_q; t /= p.tiles_q;
+      const int tp = t % p.tiles_p; t /= p.tiles_p;
+      const int q0 = tq * p.bw, p0 = tp * p.bh, n0 = t * p.bn;
+      if (leader) {
         mbar_expect_tx(&full[stage], A_BYTES + B_BYTES);
         uint8_t* a = smA + stage * A_BYTES;
         uint8_t* b = smB + stage * B_BYTES;
@@ -666,24 +1004,26 @@ __global__ void __launch_bounds__(TC_THREADS) tc_wgrad_kernel(const __grid_const
                       p0 * p.in_step + r + p.off_h, n0);
       }
     }
+    __syncwarp();
   } else if (warp == 1) {
-    if (lane == 0) {
-      const uint32_t idesc = make_idesc_bf16(TILE_M, p.n_umma, 1, 1);
-      for (int it = 0; it < iters; ++it) {
-        const int stage = it % STAGES;
-        const uint32_t phase = (it / STAGES) & 1;
-        mbar_wait(&full[stage], phase);
-        tc_fence_after();
-        // MN-major SWIZZLE_128B: LBO = next 64-channel group, SBO = next 8 pixels
-        const uint64_t adesc = make_smem_desc_sw128(smem_u32(smA + stage * A_BYTES), WG_GROUP_BYTES, 1024);
-        const uint64_t bdesc = make_smem_desc_sw128(smem_u32(smB + stage * B_BYTES), WG_GROUP_BYTES, 1024);
+    const bool leader = elect_one();
+    const uint32_t idesc = make_idesc_bf16(TILE_M, p.n_umma, 1, 1);
+    for (int it = 0; it < iters; ++it) {
+      const int stage = it % STAGES;
+      const uint32_t phase = (it / STAGES) & 1;
+      mbar_wait(&full[stage], phase);
+      tc_fence_after();
+      // MN-major SWIZZLE_128B: LBO = next 64-channel group, SBO = next 8 pixels
+      const uint64_t adesc = make_smem_desc_sw128(smem_u32(smA + stage * A_BYTES), WG_GROUP_BYTES, 1024);
+      const uint64_t bdesc = make_smem_desc_sw128(smem_u32(smB + stage * B_BYTES), WG_GROUP_BYTES, 1024);
+      if (leader) {
 #pragma unroll
         for (int k = 0; k < WG_PIX / 16; ++k)  // 16 pixels = 2048 bytes = 128 in the >>4 address field
           mma_bf16_ss(tmem_base, adesc + 128 * k, bdesc + 128 * k, idesc, (it > 0 || k > 0) ? 1u : 0u);
         mma_commit(&empty[stage]);
       }
-      mma_commit(tmem_full);
     }
+    if (leader) mma_commit(tmem_full);
     __syncwarp();
   } else {
     const int quarter = warp & 3;
@@ -880,6 +1220,12 @@ static size_t modconv_bwd_bytes(const ganb200_conv_desc* d) {
 }  // namespace ganb200
 
 using namespace ganb200;
+
+extern "C" int ganb200_conv_halo_mode(int mode) {
+  const int prev = halo_mode();
+  if (mode == 0 || mode == 1) g_halo_mode = mode;
+  return prev;
+}
 
 extern "C" size_t ganb200_modconv_bwd_workspace_bytes(const ganb200_conv_desc* d) {
   if (validate_desc(d) != 0) return 0;

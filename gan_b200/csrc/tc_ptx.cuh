@@ -38,6 +38,20 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   }
 }
 
+// One lane of a converged warp (the leader).  The producer and MMA warps run their loops warp-uniformly and predicate
+// only the TMA / tcgen05 issue on the leader: inside an `if (lane == 0)` region the compiler cannot prove operands
+// uniform and wraps every UTMALDG / UTCHMMA / UTCBAR in an ELECT ... BRA.U.ANY loop (measured: ~200 cycles per MMA
+// issued, five times the tensor pipe's own time for a 128x64x16 MMA).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.b32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok));
+  return ok != 0;
+}
+
 // ---- TMA tiled loads (global -> shared, completion on an mbarrier) -----------------------------------------
 __device__ __forceinline__ void prefetch_tmap(const CUtensorMap* m) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(m) : "memory");

@@ -70,6 +70,11 @@ enum { GANB200_CONV_FPROP = 0, GANB200_CONV_DGRAD = 1, GANB200_CONV_WGRAD = 2 };
 size_t ganb200_conv2d_workspace_bytes(const ganb200_conv_desc* d, int op);
 /* 1 if the tcgen05 engine can run this (desc, op); engine 0 picks it when this returns 1. */
 int ganb200_conv2d_tc_eligible(const ganb200_conv_desc* d, int op);
+/* tcgen05 engine, stride-1 fprop / dgrad on planes of >= 256 pixels: 1 (default) loads one halo box per filter
+ * column and feeds the filter rows from row-shifted views of it; 0 loads one box per filter tap.  Same results
+ * (identical operands and accumulation order per output element).  Returns the previous mode; any other value
+ * only queries.  Process-wide; also GANB200_CONV_HALO=0 in the environment. */
+int ganb200_conv_halo_mode(int mode);
 int ganb200_conv2d_fprop(const ganb200_conv_desc* d, const float* x, const float* w, const float* bias,
                          const float* iscale, const float* oscale, float* y,
                          void* ws, size_t ws_bytes, void* stream);

@@ -67,6 +67,10 @@ CONV_CASES = [
     (2, 96, 64, 64, 96, 5, 1, 2, 1),     # dominant G13_5 modconv shape (k5 @ 64x64)
     (4, 96, 32, 32, 96, 5, 1, 2, 1),     # k5 @ 32x32
     (4, 192, 16, 16, 96, 3, 1, 1, 1),    # k3 @ 16x16
+    (3, 72, 20, 36, 200, 3, 1, 1, 0),    # halo kernel: ragged plane, two output-channel tiles, zero pad
+    (2, 130, 33, 17, 70, 5, 1, 2, 1),    # halo kernel: odd plane, three channel chunks, k5
+    (2, 24, 40, 24, 16, 7, 1, 3, 1),     # halo kernel: k7
+    (2, 64, 32, 32, 32, 4, 2, 1, 0),     # ConvTranspose2d(k4, s2, p1) as dgrad: 2x2 tap phases at 32x32 (halo eligible)
 ]
 
 
@@ -123,8 +127,15 @@ def bf16r(t):
     return t.to(torch.bfloat16).to(torch.float32)
 
 
+@pytest.fixture(params=[1, 0], ids=["halo", "per-tap"])
+def halo_mode(cu, request):
+    prev = cu.lib.ganb200_conv_halo_mode(request.param)
+    yield request.param
+    cu.lib.ganb200_conv_halo_mode(prev)
+
+
 @pytest.mark.parametrize("case", CONV_CASES)
-def test_conv_family_tcgen05_exact_on_rounded_operands(cu, ref, case):
+def test_conv_family_tcgen05_exact_on_rounded_operands(cu, ref, case, halo_mode):
     """The engine rounds (x*iscale), (dy*oscale) and w to bf16 and accumulates in fp32: against the oracle fed the SAME
     rounded operands only the summation order differs, so any indexing / border / tap error shows (the 1e-2 test above
     would hide a wrong border pixel)."""
