@@ -297,8 +297,8 @@ __global__ void __launch_bounds__(TC_THREADS) tc_conv_kernel(const __grid_consta
           const uint64_t adesc = make_smem_desc_sw128(smem_u32(smA + stage * A_STAGE_BYTES), 16, 1024);
           const uint64_t bdesc = make_smem_desc_sw128(smem_u32(smB + stage * B_STAGE_BYTES), 16, 1024);
           if (leader) {
-            for (int k = 0; k < ksub; ++k)  // +32 bytes (= 2 in the >>4 address field) per 16-element k step
-              mma_bf16_ss(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (tap > 0 || kc > 0 || k > 0) ? 1u : 0u);
+            // +32 bytes (= 2 in the >>4 address field) per 16-element k step
+            mma_chain_n(ksub, tmem_d, adesc, bdesc, idesc, (tap > 0 || kc > 0) ? 1u : 0u, 2u);
             mma_commit(&empty[stage]);
           }
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -484,13 +484,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_halo_kernel(const __gri
             const uint64_t adesc0 = make_smem_desc_sw128(a_base + (uint32_t)r * row_bytes, 16, 1024);
             const uint32_t fresh = (kc == 0 && s == 0 && r == 0) ? 0u : 1u;
             if (leader) {
-              for (int k = 0; k < ksub; ++k)
-                mma_bf16_ss(tmem_d, adesc0 + 2 * k, bdesc + 2 * k, idesc, k == 0 ? fresh : 1u);
-              if (p.mt == 2) {
-                const uint64_t adesc1 = adesc0 + (uint64_t)(sub_bytes >> 4);
-                for (int k = 0; k < ksub; ++k)
-                  mma_bf16_ss(tmem_d + (uint32_t)BN, adesc1 + 2 * k, bdesc + 2 * k, idesc, k == 0 ? fresh : 1u);
-              }
+              mma_chain_n(ksub, tmem_d, adesc0, bdesc, idesc, fresh, 2u);
+              if (p.mt == 2)
+                mma_chain_n(ksub, tmem_d + (uint32_t)BN, adesc0 + (uint64_t)(sub_bytes >> 4), bdesc, idesc, fresh, 2u);
               mma_commit(&emptyB[sb]);
             }
             if (++sb == HALO_B_STAGES) { sb = 0; pb ^= 1; }
@@ -1017,9 +1013,8 @@ __global__ void __launch_bounds__(TC_THREADS) tc_wgrad_kernel(const __grid_const
       const uint64_t adesc = make_smem_desc_sw128(smem_u32(smA + stage * A_BYTES), WG_GROUP_BYTES, 1024);
       const uint64_t bdesc = make_smem_desc_sw128(smem_u32(smB + stage * B_BYTES), WG_GROUP_BYTES, 1024);
       if (leader) {
-#pragma unroll
-        for (int k = 0; k < WG_PIX / 16; ++k)  // 16 pixels = 2048 bytes = 128 in the >>4 address field
-          mma_bf16_ss(tmem_base, adesc + 128 * k, bdesc + 128 * k, idesc, (it > 0 || k > 0) ? 1u : 0u);
+        // 16 pixels = 2048 bytes = 128 in the >>4 address field
+        mma_chain<WG_PIX / 16>(tmem_base, adesc, bdesc, idesc, it > 0 ? 1u : 0u, 128u);
         mma_commit(&empty[stage]);
       }
     }
@@ -1049,6 +1044,175 @@ __global__ void __launch_bounds__(TC_THREADS) tc_wgrad_kernel(const __grid_const
   }
 }
 
+// ------------------------------------------------------------------------------------------------ wgrad, row ring
+// tc_wgrad_kernel gives every filter tap its own CTAs, so dy and x cross L2 -> shared memory R*S times each and the
+// narrow 64x64 layers (K = C = 48: an N = 48 MMA per 16 pixels) run at 80-100 TFLOP/s, all fill.  Here one CTA owns a
+// filter COLUMN s and a range of output rows: per output row (n, p) it loads the dy row once and ONE new x row; the R
+// rows p .. p+R-1 of the padded input sit in a ring of shared-memory slots (each 1024-aligned, so every slot is a valid
+// MN-major SWIZZLE_128B operand) and feed R MMAs chains into R accumulators (R * n_umma <= 512 TMEM columns).
+// Fill per output row drops from R * (dy + x) to (dy + x).  Rows are global indices g = n * P + p; a CTA's range may
+// span images: at an image boundary the R-1 rows left in the ring are released and the ring is primed again.
+constexpr int WGR_MAX_D = 4;    // dy stages
+constexpr int WGR_MAX_X = 12;   // x row slots
+
+struct TcWgRingParams {
+  int K, C, R, S, P, Q;
+  int rows_total, rows_per_split;
+  int off_h, off_w;
+  int a_groups, b_groups;   // 64-channel groups of the dy tile (128 filters: 2) and of the x tile (BN / 64)
+  int BN, n_umma, acc_pitch;
+  int d_stages, x_slots;
+  int row_bytes;            // Q * 128: one image row of one 64-channel group
+  uint32_t tmem_cols;
+  float* part;              // [splits][R*S][K][C]
+};
+
+__global__ void __launch_bounds__(TC_THREADS, 1) tc_wgrad_ring_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                                      const __grid_constant__ CUtensorMap tmB,
+                                                                      const TcWgRingParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int d_bytes = p.a_groups * p.row_bytes, x_bytes = p.b_groups * p.row_bytes;
+  uint8_t* smD = smem;
+  uint8_t* smX = smem + p.d_stages * d_bytes;
+  uint64_t* full_d = reinterpret_cast<uint64_t*>(smX + p.x_slots * x_bytes);
+  uint64_t* empty_d = full_d + WGR_MAX_D;
+  uint64_t* full_x = empty_d + WGR_MAX_D;
+  uint64_t* empty_x = full_x + WGR_MAX_X;
+  uint64_t* tmem_full = empty_x + WGR_MAX_X;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int k0 = blockIdx.x * TILE_M, c0 = blockIdx.y * p.BN;
+  const int s = blockIdx.z % p.S, split = blockIdx.z / p.S;
+  const int g_beg = min(split * p.rows_per_split, p.rows_total);
+  const int g_end = min(g_beg + p.rows_per_split, p.rows_total);
+  const int NS = p.x_slots, ND = p.d_stages, R = p.R;
+
+  if (threadIdx.x == 0) {
+    prefetch_tmap(&tmA);
+    prefetch_tmap(&tmB);
+    for (int i = 0; i < ND; ++i) { mbar_init(&full_d[i], 1); mbar_init(&empty_d[i], 1); }
+    for (int i = 0; i < NS; ++i) { mbar_init(&full_x[i], 1); mbar_init(&empty_x[i], 1); }
+    mbar_init(tmem_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, p.tmem_cols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    const bool leader = elect_one();
+    int sd = 0, sx = 0;
+    uint32_t pd = 0, px = 0;
+    for (int g = g_beg; g < g_end;) {
+      const int n = g / p.P;
+      int pr = g - n * p.P;
+      const int seg_end = min(g_end, (n + 1) * p.P);
+      // x rows of this segment in load order: the R-1 rows that prime the ring, then one per output row
+      const int first_row = pr + p.off_h;
+      const int n_x = (seg_end - g) + R - 1;
+      int xi = 0;
+      for (; g < seg_end; ++g, ++pr) {
+        const int want = (pr + p.off_h + R - 1) - first_row + 1;   // x rows needed up to this output row
+        for (; xi < want && xi < n_x; ++xi) {
+          mbar_wait(&empty_x[sx], px ^ 1);
+          if (leader) {
+            mbar_expect_tx(&full_x[sx], (uint32_t)x_bytes);
+            for (int gi = 0; gi < p.b_groups; ++gi)
+              tma_load_4d(smX + sx * x_bytes + gi * p.row_bytes, &tmB, &full_x[sx], c0 + gi * 64, s + p.off_w,
+                          first_row + xi, n);
+          }
+          if (++sx == NS) { sx = 0; px ^= 1; }
+        }
+        mbar_wait(&empty_d[sd], pd ^ 1);
+        if (leader) {
+          mbar_expect_tx(&full_d[sd], (uint32_t)d_bytes);
+          for (int gi = 0; gi < p.a_groups; ++gi)
+            tma_load_4d(smD + sd * d_bytes + gi * p.row_bytes, &tmA, &full_d[sd], k0 + gi * 64, 0, pr, n);
+        }
+        if (++sd == ND) { sd = 0; pd ^= 1; }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    const bool leader = elect_one();
+    const uint32_t idesc = make_idesc_bf16(TILE_M, p.n_umma, 1, 1);
+    int sd = 0, sx = 0;          // sx / px: slot and fill parity of the OLDEST row in the ring window
+    uint32_t pd = 0, px = 0;
+    bool fresh = true;
+    for (int g = g_beg; g < g_end;) {
+      const int n = g / p.P;
+      const int seg_end = min(g_end, (n + 1) * p.P);
+      bool primed = false;
+      for (; g < seg_end; ++g) {
+        mbar_wait(&full_d[sd], pd);
+        {
+          // the first output row of a segment needs all R ring rows, every later one only the newest
+          int sl = sx;
+          uint32_t par = px;
+          for (int r = 0; r < R; ++r) {
+            if (!primed || r == R - 1) mbar_wait(&full_x[sl], par);
+            if (++sl == NS) { sl = 0; par ^= 1; }
+          }
+          primed = true;
+        }
+        tc_fence_after();
+        // MN-major SWIZZLE_128B: LBO = next 64-channel group, SBO = next 8 pixels
+        const uint64_t adesc = make_smem_desc_sw128(smem_u32(smD + sd * d_bytes), (uint32_t)p.row_bytes, 1024);
+        if (leader) {
+          int sl = sx;
+          const uint32_t acc = fresh ? 0u : 1u;
+          for (int r = 0; r < R; ++r) {
+            const uint64_t bdesc = make_smem_desc_sw128(smem_u32(smX + sl * x_bytes), (uint32_t)p.row_bytes, 1024);
+            // 16 pixels = 2048 bytes = 128 in the >>4 address field; rows are 64 pixels = 4 k steps
+            mma_chain<4>(tmem_base + (uint32_t)(r * p.acc_pitch), adesc, bdesc, idesc, acc, 128u);
+            if (++sl == NS) sl = 0;
+          }
+          mma_commit(&empty_d[sd]);
+          mma_commit(&empty_x[sx]);   // the oldest row is not needed by any later output row
+        }
+        fresh = false;
+        if (++sd == ND) { sd = 0; pd ^= 1; }
+        if (++sx == NS) { sx = 0; px ^= 1; }
+      }
+      // image (or range) boundary: release the R-1 rows still in the ring
+      for (int r = 0; r + 1 < R; ++r) {
+        if (leader) mma_commit(&empty_x[sx]);
+        if (++sx == NS) { sx = 0; px ^= 1; }
+      }
+    }
+    if (leader) mma_commit(tmem_full);
+    __syncwarp();
+  } else {
+    const int quarter = warp & 3;
+    const int k = k0 + quarter * 32 + lane;
+    const bool any = g_end > g_beg;
+    mbar_wait(tmem_full, 0);
+    tc_fence_after();
+    for (int r = 0; r < R; ++r) {
+      float* row = p.part + (((int64_t)split * (R * p.S) + (r * p.S + s)) * p.K + k) * p.C + c0;
+      for (int j0 = 0; j0 < p.n_umma; j0 += 32) {
+        float v[32];
+        tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(r * p.acc_pitch + j0), v);
+        if (k < p.K) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (j0 + j < p.n_umma && c0 + j0 + j < p.C) row[j0 + j] = any ? v[j] : 0.f;
+        }
+      }
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, p.tmem_cols);
+  }
+}
+
 // dw[k][c][rs] = alpha * sum_split part[split][rs][k][c]
 __global__ void __launch_bounds__(256) wgrad_reduce_kernel(const float* __restrict__ part, float* __restrict__ dw, int K,
                                                            int C, int RS, int splits, float alpha) {
@@ -1073,7 +1237,40 @@ __global__ void __launch_bounds__(256) wgrad_reduce_kernel(const float* __restri
 struct WgradPlan {
   int bw, bh, bn, tiles_q, tiles_p, tiles_n, chunks, splits, per, BN;
   size_t dy_bytes, x_bytes, part_bytes;
+  // row-ring kernel (ring.ok): stride 1, rows of 32 or 64 pixels, more than one filter row
+  struct { bool ok; int BN, n_umma, acc_pitch, a_groups, b_groups, d_stages, x_slots, splits, rows_per_split, smem;
+           uint32_t tmem_cols; } ring;
 };
+
+static void wgrad_ring_plan(const ganb200_conv_desc* d, WgradPlan& w) {
+  w.ring.ok = false;
+  if (d->stride != 1 || d->Q != 64 || d->R < 2 || d->R > 7 || d->S > 7) return;
+  const int n16 = (d->C + 15) / 16 * 16;
+  const int BN = d->C > 64 ? 128 : 64;
+  const int n_umma = std::min(n16, BN);
+  const int pitch = (n_umma + 31) / 32 * 32;
+  if (d->R * pitch > 512) return;
+  w.ring.BN = BN; w.ring.n_umma = n_umma; w.ring.acc_pitch = pitch;
+  w.ring.tmem_cols = (uint32_t)std::max(32, pow2ceil(d->R * pitch));
+  w.ring.a_groups = d->K > 64 ? 2 : 1;
+  w.ring.b_groups = BN / 64;
+  const int row_bytes = d->Q * 128;
+  int ds = WGR_MAX_D, xs = std::min(WGR_MAX_X, d->R + 4);
+  auto bytes = [&](int a, int b) { return a * w.ring.a_groups * row_bytes + b * w.ring.b_groups * row_bytes + 1024 + 512; };
+  while (bytes(ds, xs) > HALO_SMEM_MAX && xs > d->R + 1) --xs;
+  while (bytes(ds, xs) > HALO_SMEM_MAX && ds > 2) --ds;
+  if (bytes(ds, xs) > HALO_SMEM_MAX) return;
+  w.ring.d_stages = ds; w.ring.x_slots = xs; w.ring.smem = bytes(ds, xs);
+  const int units = ceil_div(d->K, TILE_M) * ceil_div(d->C, BN) * d->S;
+  const int rows = d->N * d->P;
+  // whole waves: the TMEM allocation (and usually shared memory) admits one CTA per SM, two when both halve
+  const int per_sm = (w.ring.tmem_cols <= 256 && 2 * (w.ring.smem + 1024) <= HALO_SMEM_MAX) ? 2 : 1;
+  int splits = std::max(1, per_sm * kNumSMs / units);
+  splits = std::min(splits, std::max(1, rows / 16));     // at least 16 rows behind every ring priming
+  w.ring.rows_per_split = ceil_div(rows, splits);
+  w.ring.splits = ceil_div(rows, w.ring.rows_per_split);
+  w.ring.ok = true;
+}
 
 static WgradPlan wgrad_plan(const ganb200_conv_desc* d) {
   WgradPlan w;
@@ -1092,7 +1289,9 @@ static WgradPlan wgrad_plan(const ganb200_conv_desc* d) {
   const int mp = rep ? d->pad : 0;
   w.dy_bytes = align_up((size_t)d->N * d->P * d->Q * cpad(d->K) * 2, 1024);
   w.x_bytes = align_up((size_t)d->N * (d->H + 2 * mp) * (d->W + 2 * mp) * cpad(d->C) * 2, 1024);
-  w.part_bytes = align_up((size_t)w.splits * d->R * d->S * d->K * d->C * 4, 1024);
+  wgrad_ring_plan(d, w);
+  const int max_splits = w.ring.ok ? std::max(w.splits, w.ring.splits) : w.splits;   // either kernel may run
+  w.part_bytes = align_up((size_t)max_splits * d->R * d->S * d->K * d->C * 4, 1024);
   return w;
 }
 
@@ -1138,6 +1337,39 @@ static int wgrad_run(const ganb200_conv_desc* d, const float* x, const float* dy
       if (int rc = pack_input(dy, oscale, (__nv_bfloat16*)ws, d->N, d->K, d->P, d->Q, 0, s)) return rc;
     }
     if (int rc = pack_input(x, iscale, xh, d->N, d->C, d->H, d->W, mp, s)) return rc;
+  }
+  if (w.ring.ok && halo_mode() == 1) {
+    TcWgRingParams r;
+    r.K = d->K; r.C = d->C; r.R = d->R; r.S = d->S; r.P = d->P; r.Q = d->Q;
+    r.rows_total = d->N * d->P; r.rows_per_split = w.ring.rows_per_split;
+    r.off_h = r.off_w = rep ? 0 : -d->pad;
+    r.a_groups = w.ring.a_groups; r.b_groups = w.ring.b_groups;
+    r.BN = w.ring.BN; r.n_umma = w.ring.n_umma; r.acc_pitch = w.ring.acc_pitch;
+    r.d_stages = w.ring.d_stages; r.x_slots = w.ring.x_slots;
+    r.row_bytes = d->Q * 128; r.tmem_cols = w.ring.tmem_cols; r.part = part;
+    CUtensorMap ta, tb;
+    uint64_t dims[4] = {(uint64_t)d->K, (uint64_t)d->Q, (uint64_t)d->P, (uint64_t)d->N};
+    uint64_t str[3] = {(uint64_t)Kp * 2, (uint64_t)d->Q * Kp * 2, (uint64_t)d->P * d->Q * Kp * 2};
+    uint32_t box[4] = {64, (uint32_t)d->Q, 1, 1};
+    int rc = make_tmap_bf16(&ta, dyh, 4, dims, str, box);
+    if (rc) return rc;
+    uint64_t xd[4] = {(uint64_t)d->C, (uint64_t)Wp, (uint64_t)Hp, (uint64_t)d->N};
+    uint64_t xs[3] = {(uint64_t)Cp * 2, (uint64_t)Wp * Cp * 2, (uint64_t)Hp * Wp * Cp * 2};
+    rc = make_tmap_bf16(&tb, xh, 4, xd, xs, box);
+    if (rc) return rc;
+    static bool configured = false;
+    if (!configured) {
+      GB_CHECK_CUDA(cudaFuncSetAttribute(tc_wgrad_ring_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         HALO_SMEM_MAX));
+      configured = true;
+    }
+    dim3 grid(ceil_div(d->K, TILE_M), ceil_div(d->C, w.ring.BN), d->S * w.ring.splits);
+    tc_wgrad_ring_kernel<<<grid, TC_THREADS, w.ring.smem, s>>>(ta, tb, r);
+    GB_CHECK_LAUNCH();
+    wgrad_reduce_kernel<<<ew_grid((int64_t)d->K * d->C * RS, 256, 1), 256, 0, s>>>(part, dw, d->K, d->C, RS,
+                                                                                 w.ring.splits, d->alpha);
+    GB_CHECK_LAUNCH();
+    return 0;
   }
   TcWgradParams p;
   p.K = d->K; p.C = d->C; p.S = d->S; p.taps = RS;

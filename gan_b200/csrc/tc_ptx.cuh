@@ -114,6 +114,27 @@ __device__ __forceinline__ void mma_bf16_ss(uint32_t tmem_d, uint64_t adesc, uin
       ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// KS back-to-back MMAs over consecutive 16-element k steps of one operand pair (descriptor address field += step per
+// k step); fully unrolled so that the issuing thread spends ~3 uniform-datapath instructions per MMA.  `first_acc` is
+// the accumulate flag of the first MMA (0 starts a new accumulation), the others accumulate.
+template <int KS>
+__device__ __forceinline__ void mma_chain(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                          uint32_t first_acc, uint32_t step) {
+  mma_bf16_ss(tmem_d, adesc, bdesc, idesc, first_acc);
+#pragma unroll
+  for (int k = 1; k < KS; ++k)
+    mma_bf16_ss(tmem_d, adesc + (uint64_t)(step * k), bdesc + (uint64_t)(step * k), idesc, 1u);
+}
+__device__ __forceinline__ void mma_chain_n(int ks, uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                            uint32_t first_acc, uint32_t step) {
+  switch (ks) {
+    case 4: mma_chain<4>(tmem_d, adesc, bdesc, idesc, first_acc, step); break;
+    case 3: mma_chain<3>(tmem_d, adesc, bdesc, idesc, first_acc, step); break;
+    case 2: mma_chain<2>(tmem_d, adesc, bdesc, idesc, first_acc, step); break;
+    default: mma_chain<1>(tmem_d, adesc, bdesc, idesc, first_acc, step); break;
+  }
+}
+
 // arrive on an mbarrier when all previously issued MMAs of this thread have completed (implies fence::before_thread_sync)
 __device__ __forceinline__ void mma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))

@@ -71,6 +71,9 @@ CONV_CASES = [
     (2, 130, 33, 17, 70, 5, 1, 2, 1),    # halo kernel: odd plane, three channel chunks, k5
     (2, 24, 40, 24, 16, 7, 1, 3, 1),     # halo kernel: k7
     (2, 64, 32, 32, 32, 4, 2, 1, 0),     # ConvTranspose2d(k4, s2, p1) as dgrad: 2x2 tap phases at 32x32 (halo eligible)
+    (3, 40, 21, 64, 72, 5, 1, 2, 1),     # row-ring wgrad: 63 rows over 3 images (ranges cross image boundaries), K > 64
+    (5, 130, 9, 32, 200, 3, 1, 1, 0),    # row-ring wgrad: 32-pixel rows, zero pad, three channel tiles, two filter tiles
+    (2, 16, 70, 32, 16, 7, 1, 3, 1),     # row-ring wgrad: k7 (seven accumulators)
 ]
 
 
