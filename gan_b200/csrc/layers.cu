@@ -527,16 +527,22 @@ __global__ void __launch_bounds__(256) resample2d_kernel(const float* __restrict
 // Hi x Wo intermediate to shared memory, the vertical pass streams the output rows.  Tap tables live in shared memory
 // too.  (Th + Tw) multiply-adds per output instead of Th*Tw and no global gathers: HBM-bound, (in + out) * 4 B.
 // Summation order per output equals resample2d_kernel's (taps b inside, taps a outside).
+// The first version was issue-bound (ncu: IPC 2.96, DRAM 20 %): an integer division and three shared-memory reads per
+// multiply-add.  When Wo is a power of two <= 256 (every hot shape) a thread now keeps ONE output column for the
+// horizontal pass (its T tap weights / indices in registers, loaded once per kernel, T a template parameter) and one
+// group of four columns for the vertical pass (one 16-byte shared-memory read and four FMAs per tap, 16-byte stores).
+template <int T>   // taps per output of both passes when > 0 (exact unrolling); 0 = run-time Th / Tw
 __global__ void __launch_bounds__(256) resample2d_sep_kernel(const float* __restrict__ x, float* __restrict__ y,
                                                              int64_t NC, int Hi, int Wi, int Ho, int Wo,
                                                              const int* __restrict__ ih, const float* __restrict__ wh,
-                                                             int Th, const int* __restrict__ iw,
-                                                             const float* __restrict__ ww, int Tw) {
+                                                             int Th_, const int* __restrict__ iw,
+                                                             const float* __restrict__ ww, int Tw_, int fast) {
   extern __shared__ float sm[];
+  const int Th = T > 0 ? T : Th_, Tw = T > 0 ? T : Tw_;
   const int HWi = Hi * Wi, HWo = Ho * Wo, HiWo = Hi * Wo;
   float* pin = sm;                               // [Hi][Wi]
   float* tmp = pin + ((HWi + 3) & ~3);           // [Hi][Wo]
-  float* s_ww = tmp + HiWo;                      // [Tw][Wo]
+  float* s_ww = tmp + ((HiWo + 3) & ~3);         // [Tw][Wo]
   float* s_wh = s_ww + Wo * Tw;                  // [Ho][Th]
   int* s_iw = reinterpret_cast<int*>(s_wh + Ho * Th);
   int* s_ih = s_iw + Wo * Tw;
@@ -547,6 +553,19 @@ __global__ void __launch_bounds__(256) resample2d_sep_kernel(const float* __rest
   }
   for (int i = threadIdx.x; i < Ho * Th; i += 256) { s_wh[i] = wh[i]; s_ih[i] = ih[i] * Wo; }
   const bool vec = (HWi & 3) == 0 && aligned16(x);
+  constexpr int TR = T > 0 ? T : 1;
+  // horizontal pass: column wo0, rows h0, h0 + hstep, ...
+  const int wo0 = fast ? (int)threadIdx.x % Wo : 0, h0 = fast ? (int)threadIdx.x / Wo : 0, hstep = fast ? 256 / Wo : 1;
+  // vertical pass: columns 4*q0 .. 4*q0+3, rows v0, v0 + vstep, ...
+  const int Wq = Wo >> 2;
+  const int q0 = fast ? (int)threadIdx.x % Wq : 0, v0 = fast ? (int)threadIdx.x / Wq : 0, vstep = fast ? 256 / Wq : 1;
+  float rw[TR];
+  int ri[TR];
+#pragma unroll
+  for (int b = 0; b < TR; ++b) {
+    rw[b] = (fast && T > 0) ? ww[wo0 * Tw + b] : 0.f;
+    ri[b] = (fast && T > 0) ? iw[wo0 * Tw + b] : 0;
+  }
   for (int64_t nc = blockIdx.x; nc < NC; nc += gridDim.x) {
     const float* xp = x + nc * HWi;
     __syncthreads();
@@ -557,24 +576,65 @@ __global__ void __launch_bounds__(256) resample2d_sep_kernel(const float* __rest
       for (int i = threadIdx.x; i < HWi; i += 256) pin[i] = __ldg(xp + i);
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < HiWo; i += 256) {
-      const int h = i / Wo, wo = i - h * Wo;
-      const float* row = pin + h * Wi;
-      float acc = 0.f;
-      for (int b = 0; b < Tw; ++b) acc = fmaf(s_ww[b * Wo + wo], row[s_iw[b * Wo + wo]], acc);
-      tmp[i] = acc;
-    }
-    __syncthreads();
     float* yp = y + nc * HWo;
-    for (int i = threadIdx.x; i < HWo; i += 256) {
-      const int ho = i / Wo, wo = i - ho * Wo;
-      float acc = 0.f;
-      for (int a = 0; a < Th; ++a) {
-        const float wa = s_wh[ho * Th + a];
-        if (wa == 0.f) continue;
-        acc = fmaf(wa, tmp[s_ih[ho * Th + a] + wo], acc);
+    if (fast) {
+      for (int h = h0; h < Hi; h += hstep) {
+        const float* row = pin + h * Wi;
+        float acc = 0.f;
+        if (T > 0) {
+#pragma unroll
+          for (int b = 0; b < TR; ++b) acc = fmaf(rw[b], row[ri[b]], acc);
+        } else {
+          for (int b = 0; b < Tw; ++b) acc = fmaf(s_ww[b * Wo + wo0], row[s_iw[b * Wo + wo0]], acc);
+        }
+        tmp[h * Wo + wo0] = acc;
       }
-      yp[i] = acc;
+      __syncthreads();
+      for (int ho = v0; ho < Ho; ho += vstep) {
+        const float* wrow = s_wh + ho * Th;
+        const int* irow = s_ih + ho * Th;
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int a = 0; a < (T > 0 ? T : 1); ++a) {
+          if (T > 0) {
+            const float wa = wrow[a];
+            if (wa != 0.f) {   // skipped exactly like the scalar kernel: -0.0 / NaN handling stays identical
+              const float4 t = *reinterpret_cast<const float4*>(tmp + irow[a] + 4 * q0);
+              acc.x = fmaf(wa, t.x, acc.x); acc.y = fmaf(wa, t.y, acc.y);
+              acc.z = fmaf(wa, t.z, acc.z); acc.w = fmaf(wa, t.w, acc.w);
+            }
+          }
+        }
+        if (T == 0) {
+          for (int a = 0; a < Th; ++a) {
+            const float wa = wrow[a];
+            if (wa == 0.f) continue;
+            const float4 t = *reinterpret_cast<const float4*>(tmp + irow[a] + 4 * q0);
+            acc.x = fmaf(wa, t.x, acc.x); acc.y = fmaf(wa, t.y, acc.y);
+            acc.z = fmaf(wa, t.z, acc.z); acc.w = fmaf(wa, t.w, acc.w);
+          }
+        }
+        *reinterpret_cast<float4*>(yp + ho * Wo + 4 * q0) = acc;
+      }
+    } else {
+      for (int i = threadIdx.x; i < HiWo; i += 256) {
+        const int h = i / Wo, wo = i - h * Wo;
+        const float* row = pin + h * Wi;
+        float acc = 0.f;
+        for (int b = 0; b < Tw; ++b) acc = fmaf(s_ww[b * Wo + wo], row[s_iw[b * Wo + wo]], acc);
+        tmp[i] = acc;
+      }
+      __syncthreads();
+      for (int i = threadIdx.x; i < HWo; i += 256) {
+        const int ho = i / Wo, wo = i - ho * Wo;
+        float acc = 0.f;
+        for (int a = 0; a < Th; ++a) {
+          const float wa = s_wh[ho * Th + a];
+          if (wa == 0.f) continue;
+          acc = fmaf(wa, tmp[s_ih[ho * Th + a] + wo], acc);
+        }
+        yp[i] = acc;
+      }
     }
   }
 }
@@ -690,17 +750,35 @@ extern "C" int ganb200_resample2d(const float* x, float* y, int NC, int Hi, int 
   int64_t total = (int64_t)NC * Ho * Wo;
   if (total == 0) return 0;
   GB_REQUIRE(Th > 0 && Tw > 0, GANB200_BAD_SHAPE, "resample2d: empty tap table");
-  if (Ho * Wo <= 64 && Th * Tw >= 16 && (size_t)Hi * Wi * sizeof(float) <= 40 * 1024) {
+  const size_t sep_bytes = sizeof(float) * (((size_t)Hi * Wi + 3) / 4 * 4 + ((size_t)Hi * Wo + 3) / 4 * 4) +
+                           (sizeof(float) + sizeof(int)) * ((size_t)Wo * Tw + (size_t)Ho * Th);
+  static const bool plane_first = [] { const char* e = getenv("GANB200_RESAMPLE_PLANE"); return e && e[0] == '1'; }();
+  // AdaptiveAvgPool2d(5) of a 64x64 plane: 25 outputs x 169 taps.  Separable it is 320 x 13 + 25 x 13 multiply-adds from
+  // shared-memory tables (the plane kernel re-reads four global tap tables per multiply-add): prefer it when it fits.
+  const bool sep_fits = sep_bytes <= 48 * 1024;
+  if (Ho * Wo <= 64 && Th * Tw >= 16 && (size_t)Hi * Wi * sizeof(float) <= 40 * 1024 && (plane_first || !sep_fits)) {
     int grid = (int)std::min<int64_t>(NC, (int64_t)kNumSMs * 8);
     resample2d_plane_kernel<<<grid, 256, sizeof(float) * Hi * Wi, (cudaStream_t)stream>>>(x, y, NC, Hi, Wi, Ho, Wo, ih,
                                                                                          wh, Th, iw, ww, Tw);
   } else {
-    const size_t sep_smem = sizeof(float) * (((size_t)Hi * Wi + 3) / 4 * 4 + (size_t)Hi * Wo) +
-                            (sizeof(float) + sizeof(int)) * ((size_t)Wo * Tw + (size_t)Ho * Th);
-    if (sep_smem <= 48 * 1024 && Ho * Wo >= 64) {
+    const size_t sep_smem = sep_bytes;
+    if (sep_smem <= 48 * 1024 && (Ho * Wo >= 64 || Th * Tw >= 16)) {
       int grid = (int)std::min<int64_t>(NC, (int64_t)kNumSMs * 16);
-      resample2d_sep_kernel<<<grid, 256, sep_smem, (cudaStream_t)stream>>>(x, y, NC, Hi, Wi, Ho, Wo, ih, wh, Th, iw, ww,
-                                                                         Tw);
+      // fast path: Wo a power of two in [4, 256] (thread <-> column mappings without division, 16-byte stores)
+      const int fast = (Wo >= 4 && Wo <= 256 && (Wo & (Wo - 1)) == 0 && ((uintptr_t)y & 15) == 0) ? 1 : 0;
+      const int T = (fast && Th == Tw && Th <= 6) ? Th : 0;
+      cudaStream_t st = (cudaStream_t)stream;
+#define GB_SEP(TT) resample2d_sep_kernel<TT><<<grid, 256, sep_smem, st>>>(x, y, NC, Hi, Wi, Ho, Wo, ih, wh, Th, iw, ww, Tw, fast)
+      switch (T) {
+        case 1: GB_SEP(1); break;
+        case 2: GB_SEP(2); break;
+        case 3: GB_SEP(3); break;
+        case 4: GB_SEP(4); break;
+        case 5: GB_SEP(5); break;
+        case 6: GB_SEP(6); break;
+        default: GB_SEP(0); break;
+      }
+#undef GB_SEP
     } else {
       resample2d_kernel<<<ew_grid(total, 256, 2), 256, 0, (cudaStream_t)stream>>>(x, y, NC, Hi, Wi, Ho, Wo, ih, wh, Th,
                                                                                  iw, ww, Tw);

@@ -47,6 +47,7 @@ class ConvTimer:
 
 
 CONV_TIMER = None
+OP_CENSUS = None    # tools/kernel_profile.py: dict (kernel family, operator / shape ...) -> number of calls
 CONV_CENSUS = None  # bench.py: dict (op, desc fields..., has_iscale, has_oscale, has_bias, engine) -> number of calls
 
 
@@ -229,6 +230,9 @@ class CudaBackend:
         y = torch.empty((*lead, op_h.n_out, op_w.n_out), dtype=torch.float32, device=x.device)
         ih, wh, th = op_h.taps(x.device)
         iw, ww, tw = op_w.taps(x.device)
+        if OP_CENSUS is not None:
+            key = ("resample2d", op_h.name, nc, Hi, Wi, op_h.n_out, op_w.n_out, th)
+            OP_CENSUS[key] = OP_CENSUS.get(key, 0) + 1
         _lib.check(self.lib.ganb200_resample2d(self._p(x), self._p(y), nc, Hi, Wi, op_h.n_out, op_w.n_out,
                                                self._p(ih), self._p(wh), th, self._p(iw), self._p(ww), tw, st))
         return y

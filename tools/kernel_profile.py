@@ -21,6 +21,8 @@ for _ in range(2):
 torch.cuda.synchronize()
 from torch.profiler import ProfilerActivity, profile  # noqa: E402
 
+from gan_b200 import kernels as KN  # noqa: E402
+KN.OP_CENSUS = {}
 with profile(activities=[ProfilerActivity.CUDA]) as prof:
     bench.one_iteration(T, images, B)
     torch.cuda.synchronize()
@@ -38,3 +40,6 @@ for name, (us, n) in sorted(agg.items(), key=lambda kv: -kv[1][0]):
     if us / tot < 0.0005:
         continue
     print(f"{100 * us / tot:6.2f}% {us / 1e3:9.2f} {n:7d} {us / n:8.1f}  {name[:110]}")
+print("\n# resampling calls of the iteration (operator, planes, in, out, taps): calls")
+for k, v in sorted(KN.OP_CENSUS.items(), key=lambda kv: -kv[1] * kv[0][2] * kv[0][3] * kv[0][4]):
+    print(f"{v:5d}  {k[1]:40s} planes {k[2]:7d}  {k[3]}x{k[4]} -> {k[5]}x{k[6]}  T={k[7]}")
