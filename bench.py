@@ -160,7 +160,8 @@ def run_reference(args):
 
 def replay_census(census, device, reps=3, dump=None):
     """Times every distinct convolution-engine call of one iteration (shape, op, engine) in isolation with CUDA events
-    on the launching stream — `reps` back-to-back launches after one warm-up — and weights it by its call count.
+    on the launching stream — a CUDA graph of `reps` back-to-back launches, replayed once warm and once timed — and
+    weights it by its call count.
     -> {engine: (flops, seconds, calls)} for ONE iteration."""
     from gan_b200 import kernels as KN
     k = KN.backend()
@@ -169,7 +170,7 @@ def replay_census(census, device, reps=3, dump=None):
     for key, count in sorted(census.items(), key=lambda kv: -kv[1]):
         op, N, C, H, W, K, R, S, stride, pad, pm, has_i, has_o, has_b, eng = key
         P, Q = KN.out_hw(H, W, R, S, stride, pad)
-        e = 1 if eng == "simt" else 2
+        e = {"simt": 1, "tc": 2, "linear": 0}[eng]
         x = torch.randn(N, C, H, W, device=device)
         w = torch.randn(K, C, R, S, device=device)
         dy = torch.randn(N, K, P, Q, device=device)
@@ -183,13 +184,21 @@ def replay_census(census, device, reps=3, dump=None):
         else:
             f = lambda: k.conv_wgrad(x, dy, (R, S), stride, pad, pm, 1.0, isc, osc, engine=e)
         f()
+        torch.cuda.synchronize()
+        # `reps` launches captured in one CUDA graph: the timed replay holds device time only (issued from Python the
+        # 4-5 us calls of the linear layers were host-bound and understated the engine)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            for _ in range(reps):
+                f()
+        g.replay()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        for _ in range(reps):
-            f()
+        g.replay()
         e1.record()
         e1.synchronize()
         sec = e0.elapsed_time(e1) * 1e-3 / reps
+        del g
         fl = 2.0 * N * K * P * Q * C * R * S
         a = out.get(eng, (0.0, 0.0, 0))
         out[eng] = (a[0] + fl * count, a[1] + sec * count, a[2] + count)

@@ -39,6 +39,15 @@ int simt_dgrad(const ganb200_conv_desc* d, const float* dy, const float* w, cons
 int simt_wgrad(const ganb200_conv_desc* d, const float* x, const float* dy, const float* iscale, const float* oscale,
                float* dw, cudaStream_t s);
 
+// fp32 one-launch kernels for 1x1 convolutions on 1x1 maps = nn.Linear (conv_linear.cu)
+int linear_eligible(const ganb200_conv_desc* d);
+int linear_fprop(const ganb200_conv_desc* d, const float* x, const float* w, const float* bias, const float* iscale,
+                 const float* oscale, float* y, cudaStream_t s);
+int linear_dgrad(const ganb200_conv_desc* d, const float* dy, const float* w, const float* iscale, const float* oscale,
+                 float* dx, cudaStream_t s);
+int linear_wgrad(const ganb200_conv_desc* d, const float* x, const float* dy, const float* iscale, const float* oscale,
+                 float* dw, cudaStream_t s);
+
 int fold_replicate(const float* dxp, float* dx, int64_t NC, int H, int W, int pad, cudaStream_t s);
 
 // bf16 tcgen05 engine (conv_tc.cu)

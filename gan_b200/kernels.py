@@ -107,16 +107,15 @@ class CudaBackend:
     # -- convolution family ---------------------------------------------------------------------
     def _t0(self, d, op, flags=(False, False, False)):
         if CONV_CENSUS is not None:
-            tc = d.engine != 1 and self.lib.ganb200_conv2d_tc_eligible(ctypes.byref(d), op) == 1
-            key = (op, d.N, d.C, d.H, d.W, d.K, d.R, d.S, d.stride, d.pad, d.pad_mode) + tuple(flags) + (
-                "tc" if tc else "simt",)
+            route = {1: "simt", 2: "tc", 3: "linear"}[self.lib.ganb200_conv2d_route(ctypes.byref(d), op)]
+            key = (op, d.N, d.C, d.H, d.W, d.K, d.R, d.S, d.stride, d.pad, d.pad_mode) + tuple(flags) + (route,)
             CONV_CENSUS[key] = CONV_CENSUS.get(key, 0) + 1
         if CONV_TIMER is None:
             return None
-        tc = d.engine != 1 and self.lib.ganb200_conv2d_tc_eligible(ctypes.byref(d), op) == 1
+        route = {1: "simt", 2: "tc", 3: "linear"}[self.lib.ganb200_conv2d_route(ctypes.byref(d), op)]
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        return ("tc" if tc else "simt", 2.0 * d.N * d.K * d.P * d.Q * d.C * d.R * d.S, e0, e1)
+        return (route, 2.0 * d.N * d.K * d.P * d.Q * d.C * d.R * d.S, e0, e1)
 
     def _t1(self, tm):
         if tm is not None:

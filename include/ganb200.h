@@ -70,6 +70,10 @@ enum { GANB200_CONV_FPROP = 0, GANB200_CONV_DGRAD = 1, GANB200_CONV_WGRAD = 2 };
 size_t ganb200_conv2d_workspace_bytes(const ganb200_conv_desc* d, int op);
 /* 1 if the tcgen05 engine can run this (desc, op); engine 0 picks it when this returns 1. */
 int ganb200_conv2d_tc_eligible(const ganb200_conv_desc* d, int op);
+/* Which implementation ganb200_conv2d_{fprop,dgrad,wgrad} runs for (desc, op): 1 fp32 CUDA-core implicit GEMM,
+ * 2 bf16 tcgen05 implicit GEMM, 3 fp32 one-launch linear kernel (1x1 filter on a 1x1 map, N <= 1024, N*C*K <= 2^26, engines 0 and 1:
+ * nn.Linear / EqualizedLinear, generators/generator_13_5.py:19-26).  0 for an invalid descriptor. */
+int ganb200_conv2d_route(const ganb200_conv_desc* d, int op);
 /* tcgen05 engine, stride-1 fprop / dgrad on planes of >= 256 pixels: 1 (default) loads one halo box per filter
  * column and feeds the filter rows from row-shifted views of it; 0 loads one box per filter tap.  Same results
  * (identical operands and accumulation order per output element).  Returns the previous mode; any other value

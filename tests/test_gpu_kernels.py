@@ -126,6 +126,24 @@ def test_conv_family_tcgen05(cu, ref, case, scales):
         pytest.skip("shape not eligible for the tcgen05 engine")
 
 
+@pytest.mark.parametrize("N,C,K", [(256, 256, 256), (64, 256, 48), (5, 7, 3), (33, 1590, 97), (4, 2048, 2048)])
+@pytest.mark.parametrize("scales", [False, True])
+def test_linear_one_launch_kernels(cu, ref, N, C, K, scales):
+    """engine 0 routes nn.Linear shapes (1x1 filter, 1x1 map) to the fp32 one-launch kernels: fp32 tolerance"""
+    torch.manual_seed(9)
+    x, w, b, dy = rnd(N, C, 1, 1), rnd(K, C, 1, 1), rnd(K), rnd(N, K, 1, 1)
+    isc = torch.rand(N, C) + 0.5 if scales else None
+    osc = torch.rand(N, K) + 0.5 if scales else None
+    d = KN.ConvDesc(N, C, 1, 1, K, 1, 1, 1, 0, 0, 1, 1, 0.3, 0)
+    assert cu.lib.ganb200_conv2d_route(ctypes.byref(d), KN.FPROP) == 3
+    assert rel(cu.conv_fprop(g(x), g(w), g(b), 1, 0, 0, 0.3, g(isc), g(osc), engine=0),
+               ref.conv_fprop(x, w, b, 1, 0, 0, 0.3, isc, osc)) < FP32_TOL
+    assert rel(cu.conv_dgrad(g(dy), g(w), (1, 1), 1, 0, 0, 0.3, g(isc), g(osc), engine=0),
+               ref.conv_dgrad(dy, w, (1, 1), 1, 0, 0, 0.3, isc, osc)) < FP32_TOL
+    assert rel(cu.conv_wgrad(g(x), g(dy), (1, 1), 1, 0, 0, 0.3, g(isc), g(osc), engine=0),
+               ref.conv_wgrad(x, dy, (1, 1), 1, 0, 0, 0.3, isc, osc)) < FP32_TOL
+
+
 def bf16r(t):
     return t.to(torch.bfloat16).to(torch.float32)
 
