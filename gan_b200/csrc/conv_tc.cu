@@ -270,7 +270,7 @@ __global__ void __launch_bounds__(TC_THREADS) tc_conv_kernel(const __grid_consta
         for (int kc = 0; kc < k_chunks; ++kc) {
           mbar_wait(&empty[stage], phase ^ 1);
           if (leader) {
-            mbar_expect_tx(&full[stage], A_STAGE_BYTES + B_STAGE_BYTES);
+            mbar_expect_tx(&full[stage], A_STAGE_BYTES + (uint32_t)p.n_umma * 128u);   // weight box = n_umma rows
             tma_load_4d(smA + stage * A_STAGE_BYTES, &tmA, &full[stage], kc * BK, q0 * p.in_step + p.dw[tap],
                         p0 * p.in_step + p.dh[tap], n0);
             tma_load_3d(smB + stage * B_STAGE_BYTES, &tmB, &full[stage], kc * BK, k0, tap);
@@ -451,7 +451,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_halo_kernel(const __gri
           for (int r = 0; r < p.R; ++r) {
             mbar_wait(&emptyB[sb], pb ^ 1);
             if (leader) {
-              mbar_expect_tx(&fullB[sb], B_STAGE_BYTES);
+              mbar_expect_tx(&fullB[sb], (uint32_t)p.n_umma * 128u);   // weight box = n_umma rows
               tma_load_3d(smB + sb * B_STAGE_BYTES, &tmB, &fullB[sb], kc * BK, k0, (int)p.tap_idx[r * p.S + s]);
             }
             if (++sb == HALO_B_STAGES) { sb = 0; pb ^= 1; }
@@ -600,6 +600,17 @@ static size_t act_bytes(int N, int Ci, int Hi, int Wi, int mat_pad) {
 }
 static size_t w_bytes(int taps, int Ko, int Ci) { return align_up((size_t)taps * Ko * cpad(Ci) * 2, 1024); }
 
+// 1 = use the halo kernel where it applies (default), 0 = always the per-tap kernel.  GANB200_CONV_HALO=0 in the
+// environment or ganb200_conv_halo_mode(0) switch it off (parity tests run both).
+static int g_halo_mode = -1;
+static int halo_mode() {
+  if (g_halo_mode < 0) {
+    const char* e = getenv("GANB200_CONV_HALO");
+    g_halo_mode = (e && e[0] == '0') ? 0 : (e && e[0] == '2') ? 2 : 1;
+  }
+  return g_halo_mode;
+}
+
 // Fills `h` and returns true when problem `q` can run on the halo kernel.
 static bool halo_plan(const TcProblem& q, int BN, TcHaloParams& h) {
   if (q.in_step != 1 || q.taps.n < 1 || q.taps.n > MAX_TAPS) return false;
@@ -608,7 +619,7 @@ static bool halo_plan(const TcProblem& q, int BN, TcHaloParams& h) {
   // critic's 64/128/256-channel 3x3 convs) run 5-10 % faster on the per-tap kernel, whose 128-byte-pitch boxes the TMA
   // streams at full rate with two CTAs per SM; everything else (k5, 48/96/108-channel, 1x1, strided-dgrad phases) is
   // 1.1-2.2x faster here.
-  if (q.taps.n == 9 && q.Ci % 64 == 0 && q.Ko % 64 == 0) return false;
+  if (halo_mode() != 2 && q.taps.n == 9 && q.Ci % 64 == 0 && q.Ko % 64 == 0) return false;
   int dh_lo = 127, dh_hi = -128, dw_lo = 127, dw_hi = -128;
   for (int t = 0; t < q.taps.n; ++t) {
     dh_lo = std::min(dh_lo, (int)q.taps.dh[t]); dh_hi = std::max(dh_hi, (int)q.taps.dh[t]);
@@ -692,17 +703,6 @@ static int launch_halo(const CUtensorMap& ta, const CUtensorMap& tb, const TcHal
   return 0;
 }
 
-// 1 = use the halo kernel where it applies (default), 0 = always the per-tap kernel.  GANB200_CONV_HALO=0 in the
-// environment or ganb200_conv_halo_mode(0) switch it off (parity tests run both).
-static int g_halo_mode = -1;
-static int halo_mode() {
-  if (g_halo_mode < 0) {
-    const char* e = getenv("GANB200_CONV_HALO");
-    g_halo_mode = (e && e[0] == '0') ? 0 : 1;
-  }
-  return g_halo_mode;
-}
-
 // `act`: the packed input; `wb`: scratch for this problem's packed weights
 static int run_problem(const TcProblem& q, const __nv_bfloat16* act, const float* w, __nv_bfloat16* wb, float* out,
                        const float* out_scale, const float* bias, cudaStream_t s) {
@@ -715,7 +715,7 @@ static int run_problem(const TcProblem& q, const __nv_bfloat16* act, const float
   const int BN = q.Ko > 64 ? 128 : 64;   // 64 < Ko < 128 (96, 108): one 128-wide tile, the activations are read once
   {
     TcHaloParams h;
-    if (halo_mode() == 1 && halo_plan(q, BN, h)) {
+    if (halo_mode() >= 1 && halo_plan(q, BN, h)) {
       h.n_umma = q.Ko >= BN ? BN : (q.Ko + 15) / 16 * 16;
       h.alpha = q.alpha; h.oscale = out_scale; h.bias = bias; h.y = out;
       CUtensorMap ta, tb;
@@ -726,7 +726,9 @@ static int run_problem(const TcProblem& q, const __nv_bfloat16* act, const float
       if (rc) return rc;
       uint64_t wd[3] = {(uint64_t)q.Ci, (uint64_t)q.Ko, (uint64_t)NT};
       uint64_t wst[2] = {(uint64_t)Cp * 2, (uint64_t)q.Ko * Cp * 2};
-      uint32_t wbox[3] = {BK, (uint32_t)BN, 1};
+      // only the n_umma filter rows the MMA reads (K = 96: 12 KB instead of 16 KB per tap and chunk; the weights are
+      // 60 % of this kernel's L2 -> shared-memory traffic on the k5 layers)
+      uint32_t wbox[3] = {BK, (uint32_t)h.n_umma, 1};
       rc = make_tmap_bf16(&tb, wb, 3, wd, wst, wbox);
       if (rc) return rc;
       const int64_t total = (int64_t)h.tiles_m * h.tiles_n;
@@ -762,7 +764,7 @@ static int run_problem(const TcProblem& q, const __nv_bfloat16* act, const float
     if (rc) return rc;
     uint64_t wd[3] = {(uint64_t)q.Ci, (uint64_t)q.Ko, (uint64_t)NT};
     uint64_t wst[2] = {(uint64_t)Cp * 2, (uint64_t)q.Ko * Cp * 2};
-    uint32_t wbox[3] = {BK, (uint32_t)BN, 1};
+    uint32_t wbox[3] = {BK, (uint32_t)p.n_umma, 1};
     rc = make_tmap_bf16(&tb, wb, 3, wd, wst, wbox);
     if (rc) return rc;
   }
@@ -1338,7 +1340,7 @@ static int wgrad_run(const ganb200_conv_desc* d, const float* x, const float* dy
     }
     if (int rc = pack_input(x, iscale, xh, d->N, d->C, d->H, d->W, mp, s)) return rc;
   }
-  if (w.ring.ok && halo_mode() == 1) {
+  if (w.ring.ok && halo_mode() >= 1) {
     TcWgRingParams r;
     r.K = d->K; r.C = d->C; r.R = d->R; r.S = d->S; r.P = d->P; r.Q = d->Q;
     r.rows_total = d->N * d->P; r.rows_per_split = w.ring.rows_per_split;
@@ -1455,7 +1457,7 @@ using namespace ganb200;
 
 extern "C" int ganb200_conv_halo_mode(int mode) {
   const int prev = halo_mode();
-  if (mode == 0 || mode == 1) g_halo_mode = mode;
+  if (mode >= 0 && mode <= 2) g_halo_mode = mode;
   return prev;
 }
 

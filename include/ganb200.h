@@ -75,7 +75,8 @@ int ganb200_conv2d_tc_eligible(const ganb200_conv_desc* d, int op);
  * nn.Linear / EqualizedLinear, generators/generator_13_5.py:19-26).  0 for an invalid descriptor. */
 int ganb200_conv2d_route(const ganb200_conv_desc* d, int op);
 /* tcgen05 engine, stride-1 fprop / dgrad on planes of >= 256 pixels: 1 (default) loads one halo box per filter
- * column and feeds the filter rows from row-shifted views of it; 0 loads one box per filter tap.  Same results
+ * column and feeds the filter rows from row-shifted views of it; 0 loads one box per filter tap (and runs wgrad per tap); 2 uses the halo kernel even for
+ * the shapes the measured heuristic leaves on the per-tap kernel (tuning).  Same results
  * (identical operands and accumulation order per output element).  Returns the previous mode; any other value
  * only queries.  Process-wide; also GANB200_CONV_HALO=0 in the environment. */
 int ganb200_conv_halo_mode(int mode);

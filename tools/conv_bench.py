@@ -10,6 +10,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from gan_b200 import kernels as KN  # noqa: E402
 
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 256
+HALO = int(sys.argv[2]) if len(sys.argv) > 2 else 1   # 2: halo kernel also where the heuristic prefers per-tap
 REPS = 5
 # C, HW, K, R, stride, pad, pad_mode
 SHAPES = [(96, 64, 96, 5, 1, 2, 1), (48, 64, 48, 5, 1, 2, 1), (48, 64, 48, 3, 1, 1, 1), (96, 64, 96, 3, 1, 1, 1),
@@ -50,7 +51,7 @@ def main():
                        ("wgrad", lambda: cu.conv_wgrad(x, dy, (R, R), stride, pad, pm, 0.1, engine=2))):
             res = {}
             for mode in (0, 1):
-                cu.lib.ganb200_conv_halo_mode(mode)
+                cu.lib.ganb200_conv_halo_mode(HALO if mode else 0)
                 out = fn()
                 res[mode] = (timed(fn), out)
             cu.lib.ganb200_conv_halo_mode(1)
