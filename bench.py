@@ -34,6 +34,12 @@ D_F = 11.922e9    # discriminator_9_4 forward FLOPs / image
 FLOPS_PER_IMAGE = {"ganR2": 4 * G_F + 19.16 * D_F, "wgangpR2": 4 * G_F + 25.24 * D_F}
 
 
+# DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) of ONE launch of the engine's dominant kernel shape, from
+# the ncu --set full capture summarised in profiles/r01_conv_ncu_full_end.txt (not measured by this script).
+NCU_TRAFFIC = {"bytes": 577.24e6, "of": "tc_conv_halo_kernel<128>, fprop 96->96 5x5 @64x64, N=256 (ncu --set full, "
+                                        "profiles/r01_conv_ncu_full_end.txt)"}
+
+
 def seed_all(s):
     torch.manual_seed(s)
     np.random.seed(s)
@@ -205,10 +211,11 @@ def replay_census(census, device, reps=3, dump=None):
         rows.append({"op": ["fprop", "dgrad", "wgrad"][op], "N": N, "C": C, "H": H, "W": W, "K": K, "R": R,
                      "stride": stride, "pad": pad, "pad_mode": pm, "engine": eng, "calls": count, "ms_each": sec * 1e3,
                      "ms_total": sec * count * 1e3, "tflops": fl / sec / 1e12})
+    rows.sort(key=lambda r: -r["ms_total"])
     if dump:
-        rows.sort(key=lambda r: -r["ms_total"])
         os.makedirs(os.path.dirname(dump), exist_ok=True)
         json.dump(rows, open(dump, "w"), indent=0)
+    replay_census.top = [r for r in rows if r["engine"] == "tc"][:3]
     return out
 
 
@@ -298,7 +305,9 @@ def run_native(args):
     conv_share = sum(v[1] for v in conv.values()) / (ms * 1e-3 * args.steps)
     roofline = {"bound": "tensor", "kernel": "conv_tc (tcgen05 implicit GEMM)" if eng == "tc" else
                 "conv_simt (fp32 CUDA-core implicit GEMM)", "achieved": achieved, "peak": pk["tflops"],
-                "unit": "TFLOP/s", "frac": achieved / pk["tflops"], "traffic": None, "peak_source": pk["src"],
+                "unit": "TFLOP/s", "frac": achieved / pk["tflops"], "traffic": NCU_TRAFFIC["bytes"],
+                "traffic_of": NCU_TRAFFIC["of"], "top_shapes": getattr(replay_census, "top", []),
+                "peak_source": pk["src"],
                 "launches": calls, "conv_share_of_step": conv_share,
                 "by_engine": {k: {"tflops": v[0] / v[1] / 1e12 if v[1] > 0 else 0.0, "seconds": v[1], "calls": v[2]}
                               for k, v in conv.items()}}
