@@ -321,6 +321,125 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const float* __restrict__
 
 }  // namespace ganb200
 
+// ---- fused training-mode batch norm for small per-channel populations (N*HW <= BN_SMALL_MAX) -------------------
+// The generator runs 1 888 batch norms per forward, nearly all BatchNorm1d over (256, C) or BatchNorm2d on 5x5 / 3x3 /
+// 1x1 attention maps.  The generic path is memset, memset, mean pass, variance pass, apply: five graph nodes of 1-7 us
+// each (and atomics).  Here one block owns one channel, keeps its N*HW values in registers, and does mean, variance
+// (two-pass, as the reference's native_batch_norm), normalisation, running statistics in ONE launch; the backward
+// (sums, dx, dgamma, dbeta) likewise.  Deterministic: fixed-order block reductions, no atomics.
+namespace ganb200 {
+constexpr int BN_SMALL_THREADS = 128;
+constexpr int BN_SMALL_PER = 32;                                   // values per thread
+constexpr int BN_SMALL_MAX = BN_SMALL_THREADS * BN_SMALL_PER;      // 4096
+
+__global__ void __launch_bounds__(BN_SMALL_THREADS) bn_small_fwd_kernel(
+    const float* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ beta, float* __restrict__ y,
+    float* __restrict__ mean_out, float* __restrict__ invstd_out, float* __restrict__ running_mean,
+    float* __restrict__ running_var, int64_t* nbt, int N, int C, int HW, float eps, float momentum) {
+  const int c = blockIdx.x, cnt = N * HW;
+  float v[BN_SMALL_PER];
+  float s = 0.f;
+#pragma unroll
+  for (int e = 0; e < BN_SMALL_PER; ++e) {
+    const int j = threadIdx.x + e * BN_SMALL_THREADS;
+    const bool ok = j < cnt;
+    const int n = ok ? j / HW : 0, i = ok ? j - n * HW : 0;
+    v[e] = __ldg(x + ((int64_t)n * C + c) * HW + i);
+    if (!ok) v[e] = 0.f;
+    s += v[e];
+  }
+  const float mean = block_sum<BN_SMALL_THREADS>(s) / (float)cnt;
+  float q = 0.f;
+#pragma unroll
+  for (int e = 0; e < BN_SMALL_PER; ++e) {
+    const float d = (threadIdx.x + e * BN_SMALL_THREADS < cnt) ? v[e] - mean : 0.f;
+    q = fmaf(d, d, q);
+  }
+  const float var = block_sum<BN_SMALL_THREADS>(q) / (float)cnt;
+  const float is = 1.f / sqrtf(var + eps);
+  const float gm = gamma ? gamma[c] : 1.f, bt = beta ? beta[c] : 0.f;
+#pragma unroll
+  for (int e = 0; e < BN_SMALL_PER; ++e) {
+    const int j = threadIdx.x + e * BN_SMALL_THREADS;
+    if (j < cnt) {
+      const int n = j / HW, i = j - n * HW;
+      y[((int64_t)n * C + c) * HW + i] = (v[e] - mean) * is * gm + bt;
+    }
+  }
+  if (threadIdx.x == 0) {
+    mean_out[c] = mean;
+    invstd_out[c] = is;
+    if (running_mean) running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+    if (running_var)
+      running_var[c] = (1.f - momentum) * running_var[c] + momentum * (cnt > 1 ? var * (float)cnt / (float)(cnt - 1) : var);
+    if (nbt && c == 0) *nbt += 1;
+  }
+}
+
+__global__ void __launch_bounds__(BN_SMALL_THREADS) bn_small_bwd_kernel(
+    const float* __restrict__ gy, const float* __restrict__ x, const float* __restrict__ mean,
+    const float* __restrict__ invstd, const float* __restrict__ gamma, float* __restrict__ gx,
+    float* __restrict__ ggamma, float* __restrict__ gbeta, int N, int C, int HW) {
+  const int c = blockIdx.x, cnt = N * HW;
+  const float m = mean[c], is = invstd[c], gm = gamma ? gamma[c] : 1.f;
+  float g[BN_SMALL_PER], xh[BN_SMALL_PER];
+  float a = 0.f, b = 0.f;
+#pragma unroll
+  for (int e = 0; e < BN_SMALL_PER; ++e) {
+    const int j = threadIdx.x + e * BN_SMALL_THREADS;
+    const bool ok = j < cnt;
+    const int n = ok ? j / HW : 0, i = ok ? j - n * HW : 0;
+    const int64_t idx = ((int64_t)n * C + c) * HW + i;
+    g[e] = __ldg(gy + idx);
+    xh[e] = (__ldg(x + idx) - m) * is;
+    if (!ok) { g[e] = 0.f; xh[e] = 0.f; }
+    a += g[e];
+    b = fmaf(g[e], xh[e], b);
+  }
+  const float s1 = block_sum<BN_SMALL_THREADS>(a);
+  const float s2 = block_sum<BN_SMALL_THREADS>(b);
+  const float ia = s1 / (float)cnt, ib = s2 / (float)cnt;
+#pragma unroll
+  for (int e = 0; e < BN_SMALL_PER; ++e) {
+    const int j = threadIdx.x + e * BN_SMALL_THREADS;
+    if (j < cnt) {
+      const int n = j / HW, i = j - n * HW;
+      gx[((int64_t)n * C + c) * HW + i] = gm * is * (g[e] - ia - xh[e] * ib);
+    }
+  }
+  if (threadIdx.x == 0) {
+    if (ggamma) ggamma[c] = s2;
+    if (gbeta) gbeta[c] = s1;
+  }
+}
+}  // namespace ganb200
+
+extern "C" int ganb200_bn_small_eligible(int N, int C, int HW) {
+  return N > 0 && C > 0 && HW > 0 && (int64_t)N * HW <= BN_SMALL_MAX;
+}
+
+extern "C" int ganb200_bn_small_fwd(const float* x, const float* gamma, const float* beta, float* y, float* mean,
+                                    float* invstd, float* running_mean, float* running_var,
+                                    int64_t* num_batches_tracked, int N, int C, int HW, float eps, float momentum,
+                                    void* stream) {
+  GB_REQUIRE(ganb200_bn_small_eligible(N, C, HW), GANB200_BAD_SHAPE, "bn_small_fwd: N*HW must be in [1, 4096]");
+  bn_small_fwd_kernel<<<C, BN_SMALL_THREADS, 0, (cudaStream_t)stream>>>(x, gamma, beta, y, mean, invstd, running_mean,
+                                                                        running_var, num_batches_tracked, N, C, HW, eps,
+                                                                        momentum);
+  GB_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int ganb200_bn_small_bwd(const float* gy, const float* x, const float* mean, const float* invstd,
+                                    const float* gamma, float* gx, float* ggamma, float* gbeta, int N, int C, int HW,
+                                    void* stream) {
+  GB_REQUIRE(ganb200_bn_small_eligible(N, C, HW), GANB200_BAD_SHAPE, "bn_small_bwd: N*HW must be in [1, 4096]");
+  bn_small_bwd_kernel<<<C, BN_SMALL_THREADS, 0, (cudaStream_t)stream>>>(gy, x, mean, invstd, gamma, gx, ggamma, gbeta, N,
+                                                                        C, HW);
+  GB_CHECK_LAUNCH();
+  return 0;
+}
+
 static dim3 bn_reduce_grid(int N, int C, int HW) {
   int want = (kNumSMs * 4 + C - 1) / C;
   int max_split = HW >= 1024 ? N : (int)(((int64_t)N * HW + 255) / 256);

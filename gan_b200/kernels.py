@@ -325,6 +325,37 @@ class CudaBackend:
                                              count_total, st))
         return y, invstd
 
+    BN_SMALL_MAX = 4096
+
+    def bn_small_ok(self, x):
+        N, C, HW = _nchw(x)
+        return N * HW <= self.BN_SMALL_MAX
+
+    def bn_small_fwd(self, x, gamma, beta, running_mean, running_var, eps, momentum, nbt=None):
+        """one launch: batch statistics, y, running statistics -> (y, mean, invstd)"""
+        N, C, HW = _nchw(x)
+        st = self._prep(x, gamma, beta, running_mean, running_var)
+        if nbt is not None and nbt.dtype != torch.int64:
+            raise _lib.GanB200Error("num_batches_tracked must be int64")
+        y = torch.empty_like(x)
+        mean = torch.empty((C,), dtype=torch.float32, device=x.device)
+        invstd = torch.empty((C,), dtype=torch.float32, device=x.device)
+        _lib.check(self.lib.ganb200_bn_small_fwd(self._p(x), self._p(gamma), self._p(beta), self._p(y), self._p(mean),
+                                                 self._p(invstd), self._p(running_mean), self._p(running_var),
+                                                 self._p(nbt), N, C, HW, eps, momentum, st))
+        return y, mean, invstd
+
+    def bn_small_bwd(self, gy, x, mean, invstd, gamma):
+        """one launch: (gx, ggamma, gbeta)"""
+        N, C, HW = _nchw(x)
+        st = self._prep(gy, x, mean, invstd, gamma)
+        gx = torch.empty_like(x)
+        gg = torch.empty((C,), dtype=torch.float32, device=x.device)
+        gb = torch.empty((C,), dtype=torch.float32, device=x.device)
+        _lib.check(self.lib.ganb200_bn_small_bwd(self._p(gy), self._p(x), self._p(mean), self._p(invstd),
+                                                 self._p(gamma), self._p(gx), self._p(gg), self._p(gb), N, C, HW, st))
+        return gx, gg, gb
+
     def bn_bwd_reduce(self, gy, x, mean, invstd):
         N, C, HW = _nchw(x)
         st = self._prep(gy, x, mean, invstd)

@@ -707,10 +707,14 @@ class BatchNormTrainFn(Function):
         x = _c(x)
         N, C, HW = KN._nchw(x)
         count = N * HW
-        mean, var = K().bn_stats(x)
-        if _sync_bn_hooks["stats"] is not None:
-            mean, var, count = _sync_bn_hooks["stats"](mean, var, count)
-        y, invstd = K().bn_apply(x, mean, var, gamma, beta, running_mean, running_var, eps, momentum, count, nbt)
+        ctx.small = _sync_bn_hooks["stats"] is None and _sync_bn_hooks["grads"] is None and K().bn_small_ok(x)
+        if ctx.small:  # single rank, small per-channel population: statistics + apply + running stats in one launch
+            y, mean, invstd = K().bn_small_fwd(x, gamma, beta, running_mean, running_var, eps, momentum, nbt)
+        else:
+            mean, var = K().bn_stats(x)
+            if _sync_bn_hooks["stats"] is not None:
+                mean, var, count = _sync_bn_hooks["stats"](mean, var, count)
+            y, invstd = K().bn_apply(x, mean, var, gamma, beta, running_mean, running_var, eps, momentum, count, nbt)
         ctx.save_for_backward(x, mean, invstd, gamma)
         ctx.count = count
         return y
@@ -720,6 +724,10 @@ class BatchNormTrainFn(Function):
     def backward(ctx, gy):
         x, mean, invstd, gamma = ctx.saved_tensors
         gy = _c(gy)
+        if ctx.small and _sync_bn_hooks["grads"] is None:
+            gx, gg, gb = K().bn_small_bwd(gy, x, mean, invstd, gamma)
+            return (gx, (gg if gamma is not None else None), (gb if ctx.needs_input_grad[2] else None), None, None,
+                    None, None, None)
         s1, s2 = K().bn_bwd_reduce(gy, x, mean, invstd)
         if _sync_bn_hooks["grads"] is not None:
             # data parallel: dx needs the sums over the global batch; dgamma/dbeta stay rank-local partial sums

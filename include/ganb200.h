@@ -160,6 +160,18 @@ int ganb200_bn_bwd_apply(const float* gy, const float* x, const float* mean, con
                          const float* sum_gy, const float* sum_gy_xhat, float* gx, float* ggamma, float* gbeta,
                          int N, int C, int HW, int64_t count_total, void* stream);
 
+/* Fused training-mode batch norm for small per-channel populations (N*HW <= 4096: every BatchNorm1d and the
+ * BatchNorm2d of the 5x5 / 3x3 / 1x1 attention maps, generator_13_5.py:60-66,100-118,212-214): ONE launch computes the
+ * batch mean and biased variance (two-pass), y, save_mean / save_invstd, the running statistics (unbiased variance,
+ * momentum) and num_batches_tracked += 1; the backward ONE launch computes dx, dgamma, dbeta.  Same results as
+ * ganb200_bn_stats + ganb200_bn_apply resp. ganb200_bn_bwd_reduce + ganb200_bn_bwd_apply; deterministic. */
+int ganb200_bn_small_eligible(int N, int C, int HW);
+int ganb200_bn_small_fwd(const float* x, const float* gamma, const float* beta, float* y, float* mean, float* invstd,
+                         float* running_mean, float* running_var, int64_t* num_batches_tracked, int N, int C, int HW,
+                         float eps, float momentum, void* stream);
+int ganb200_bn_small_bwd(const float* gy, const float* x, const float* mean, const float* invstd, const float* gamma,
+                         float* gx, float* ggamma, float* gbeta, int N, int C, int HW, void* stream);
+
 /* softmax over dim=1 of a [B,M,C] tensor (nn.Softmax(dim=1), generator_13_5.py:72,87) */
 int ganb200_softmax_m_fwd(const float* x, float* y, int B, int M, int C, void* stream);
 int ganb200_softmax_m_bwd(const float* gy, const float* y, float* gx, int B, int M, int C, void* stream);

@@ -176,6 +176,20 @@ class RefBackend:
             running_var.mul_(1 - momentum).add_(momentum * (var * n / (n - 1) if n > 1 else var))
         return y, invstd
 
+    def bn_small_ok(self, x):
+        n = x.numel() // x.shape[1] if x.dim() > 1 else 1
+        return n <= 4096
+
+    def bn_small_fwd(self, x, gamma, beta, running_mean, running_var, eps, momentum, nbt=None):
+        mean, var = self.bn_stats(x)
+        count = x.numel() // x.shape[1]
+        y, invstd = self.bn_apply(x, mean, var, gamma, beta, running_mean, running_var, eps, momentum, count, nbt)
+        return y, mean, invstd
+
+    def bn_small_bwd(self, gy, x, mean, invstd, gamma):
+        s1, s2 = self.bn_bwd_reduce(gy, x, mean, invstd)
+        return self.bn_bwd_apply(gy, x, mean, invstd, gamma, s1, s2, x.numel() // x.shape[1])
+
     def bn_bwd_reduce(self, gy, x, mean, invstd):
         dims = [d for d in range(x.dim()) if d != 1]
         xhat = (x - self._cview(x, mean)) * self._cview(x, invstd)

@@ -271,6 +271,29 @@ def test_batchnorm(cu, ref, shape):
         assert rel(a, b) < 1e-4
 
 
+@pytest.mark.parametrize("shape", [(256, 256), (4, 48), (256, 12, 4, 4), (7, 33, 5, 5), (1024, 3, 2, 2), (6, 5, 1, 1)])
+@pytest.mark.parametrize("affine", [True, False])
+def test_batchnorm_fused_small(cu, ref, shape, affine):
+    """one-launch training-mode batch norm (N*HW <= 4096) against the oracle's stats + apply / reduce + apply"""
+    torch.manual_seed(16)
+    x, gy = rnd(*shape) * 2 + 0.5, rnd(*shape)
+    C = shape[1]
+    gamma, beta = (rnd(C), rnd(C)) if affine else (None, None)
+    assert cu.bn_small_ok(g(x)) and ref.bn_small_ok(x)
+    rm, rv, nbt = rnd(C), torch.rand(C) + 0.5, torch.full((), 3, dtype=torch.int64)
+    rm_g, rv_g, nbt_g = g(rm.clone()), g(rv.clone()), g(nbt.clone())
+    y, m, inv = cu.bn_small_fwd(g(x), g(gamma), g(beta), rm_g, rv_g, 1e-5, 0.1, nbt_g)
+    y_r, m_r, inv_r = ref.bn_small_fwd(x, gamma, beta, rm, rv, 1e-5, 0.1, nbt)
+    assert rel(y, y_r) < FP32_TOL and rel(m, m_r) < FP32_TOL and rel(inv, inv_r) < FP32_TOL
+    assert rel(rm_g, rm) < FP32_TOL and rel(rv_g, rv) < FP32_TOL and int(nbt_g) == int(nbt) == 4
+    out = cu.bn_small_bwd(g(gy), g(x), m, inv, g(gamma))
+    out_r = ref.bn_small_bwd(gy, x, m_r, inv_r, gamma)
+    for a, b in zip(out, out_r):
+        assert rel(a, b) < 1e-4
+    big = rnd(64, 3, 16, 16)
+    assert not cu.bn_small_ok(g(big)) and not ref.bn_small_ok(big)
+
+
 def test_softmax_mbstd_bce(cu, ref):
     torch.manual_seed(7)
     x, gy = rnd(6, 2, 48), rnd(6, 2, 48)
