@@ -56,8 +56,8 @@ SIGNATURES = {
     "ganb200_bn_bwd_reduce": (c_int, [P, P, P, P, P, P, c_int, c_int, c_int, P]),
     "ganb200_bn_bwd_apply": (c_int, [P, P, P, P, P, P, P, P, P, P, c_int, c_int, c_int, c_int64, P]),
     "ganb200_bn_small_eligible": (c_int, [c_int, c_int, c_int]),
-    "ganb200_bn_small_fwd": (c_int, [P, P, P, P, P, P, P, P, P, c_int, c_int, c_int, c_float, c_float, P]),
-    "ganb200_bn_small_bwd": (c_int, [P, P, P, P, P, P, P, P, c_int, c_int, c_int, P]),
+    "ganb200_bn_small_fwd": (c_int, [P, P, P, P, P, P, P, P, P, c_int, c_int, c_int, c_float, c_float, P, P]),
+    "ganb200_bn_small_bwd": (c_int, [P, P, P, P, P, P, P, P, c_int, c_int, c_int, P, P, P, P]),
     "ganb200_softmax_m_fwd": (c_int, [P, P, c_int, c_int, c_int, P]),
     "ganb200_softmax_m_bwd": (c_int, [P, P, P, c_int, c_int, c_int, P]),
     "ganb200_mbstd_fwd": (c_int, [P, P, c_int, c_int64, c_float, P]),

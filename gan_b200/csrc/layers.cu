@@ -335,7 +335,8 @@ constexpr int BN_SMALL_MAX = BN_SMALL_THREADS * BN_SMALL_PER;      // 4096
 __global__ void __launch_bounds__(BN_SMALL_THREADS) bn_small_fwd_kernel(
     const float* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ beta, float* __restrict__ y,
     float* __restrict__ mean_out, float* __restrict__ invstd_out, float* __restrict__ running_mean,
-    float* __restrict__ running_var, int64_t* nbt, int N, int C, int HW, float eps, float momentum) {
+    float* __restrict__ running_var, int64_t* nbt, int N, int C, int HW, float eps, float momentum,
+    const float* __restrict__ slope) {
   const int c = blockIdx.x, cnt = N * HW;
   float v[BN_SMALL_PER];
   float s = 0.f;
@@ -358,12 +359,14 @@ __global__ void __launch_bounds__(BN_SMALL_THREADS) bn_small_fwd_kernel(
   const float var = block_sum<BN_SMALL_THREADS>(q) / (float)cnt;
   const float is = 1.f / sqrtf(var + eps);
   const float gm = gamma ? gamma[c] : 1.f, bt = beta ? beta[c] : 0.f;
+  const float sl = slope ? slope[c] : 1.f;   // following nn.PReLU(C), fused: y = u > 0 ? u : slope * u
 #pragma unroll
   for (int e = 0; e < BN_SMALL_PER; ++e) {
     const int j = threadIdx.x + e * BN_SMALL_THREADS;
     if (j < cnt) {
       const int n = j / HW, i = j - n * HW;
-      y[((int64_t)n * C + c) * HW + i] = (v[e] - mean) * is * gm + bt;
+      const float u = (v[e] - mean) * is * gm + bt;
+      y[((int64_t)n * C + c) * HW + i] = u > 0.f ? u : sl * u;
     }
   }
   if (threadIdx.x == 0) {
@@ -379,11 +382,13 @@ __global__ void __launch_bounds__(BN_SMALL_THREADS) bn_small_fwd_kernel(
 __global__ void __launch_bounds__(BN_SMALL_THREADS) bn_small_bwd_kernel(
     const float* __restrict__ gy, const float* __restrict__ x, const float* __restrict__ mean,
     const float* __restrict__ invstd, const float* __restrict__ gamma, float* __restrict__ gx,
-    float* __restrict__ ggamma, float* __restrict__ gbeta, int N, int C, int HW) {
+    float* __restrict__ ggamma, float* __restrict__ gbeta, int N, int C, int HW, const float* __restrict__ beta,
+    const float* __restrict__ slope, float* __restrict__ gslope) {
   const int c = blockIdx.x, cnt = N * HW;
   const float m = mean[c], is = invstd[c], gm = gamma ? gamma[c] : 1.f;
+  const float bt = beta ? beta[c] : 0.f, sl = slope ? slope[c] : 1.f;
   float g[BN_SMALL_PER], xh[BN_SMALL_PER];
-  float a = 0.f, b = 0.f;
+  float a = 0.f, b = 0.f, ps = 0.f;
 #pragma unroll
   for (int e = 0; e < BN_SMALL_PER; ++e) {
     const int j = threadIdx.x + e * BN_SMALL_THREADS;
@@ -393,11 +398,17 @@ __global__ void __launch_bounds__(BN_SMALL_THREADS) bn_small_bwd_kernel(
     g[e] = __ldg(gy + idx);
     xh[e] = (__ldg(x + idx) - m) * is;
     if (!ok) { g[e] = 0.f; xh[e] = 0.f; }
+    if (slope) {   // fused PReLU: the batch-norm output u is recomputed; d/dslope = sum gy * min(u, 0)
+      const float u = xh[e] * gm + bt;
+      ps = fmaf(g[e], fminf(u, 0.f), ps);
+      g[e] *= u > 0.f ? 1.f : sl;
+    }
     a += g[e];
     b = fmaf(g[e], xh[e], b);
   }
   const float s1 = block_sum<BN_SMALL_THREADS>(a);
   const float s2 = block_sum<BN_SMALL_THREADS>(b);
+  const float s3 = slope ? block_sum<BN_SMALL_THREADS>(ps) : 0.f;
   const float ia = s1 / (float)cnt, ib = s2 / (float)cnt;
 #pragma unroll
   for (int e = 0; e < BN_SMALL_PER; ++e) {
@@ -410,6 +421,7 @@ __global__ void __launch_bounds__(BN_SMALL_THREADS) bn_small_bwd_kernel(
   if (threadIdx.x == 0) {
     if (ggamma) ggamma[c] = s2;
     if (gbeta) gbeta[c] = s1;
+    if (gslope) gslope[c] = s3;
   }
 }
 }  // namespace ganb200
@@ -421,21 +433,22 @@ extern "C" int ganb200_bn_small_eligible(int N, int C, int HW) {
 extern "C" int ganb200_bn_small_fwd(const float* x, const float* gamma, const float* beta, float* y, float* mean,
                                     float* invstd, float* running_mean, float* running_var,
                                     int64_t* num_batches_tracked, int N, int C, int HW, float eps, float momentum,
-                                    void* stream) {
+                                    const float* prelu_slope, void* stream) {
   GB_REQUIRE(ganb200_bn_small_eligible(N, C, HW), GANB200_BAD_SHAPE, "bn_small_fwd: N*HW must be in [1, 4096]");
   bn_small_fwd_kernel<<<C, BN_SMALL_THREADS, 0, (cudaStream_t)stream>>>(x, gamma, beta, y, mean, invstd, running_mean,
                                                                         running_var, num_batches_tracked, N, C, HW, eps,
-                                                                        momentum);
+                                                                        momentum, prelu_slope);
   GB_CHECK_LAUNCH();
   return 0;
 }
 
 extern "C" int ganb200_bn_small_bwd(const float* gy, const float* x, const float* mean, const float* invstd,
                                     const float* gamma, float* gx, float* ggamma, float* gbeta, int N, int C, int HW,
-                                    void* stream) {
+                                    const float* beta, const float* prelu_slope, float* gslope, void* stream) {
   GB_REQUIRE(ganb200_bn_small_eligible(N, C, HW), GANB200_BAD_SHAPE, "bn_small_bwd: N*HW must be in [1, 4096]");
+  GB_REQUIRE(!prelu_slope || gslope, GANB200_BAD_ARG, "bn_small_bwd: prelu_slope without gslope");
   bn_small_bwd_kernel<<<C, BN_SMALL_THREADS, 0, (cudaStream_t)stream>>>(gy, x, mean, invstd, gamma, gx, ggamma, gbeta, N,
-                                                                        C, HW);
+                                                                        C, HW, beta, prelu_slope, gslope);
   GB_CHECK_LAUNCH();
   return 0;
 }

@@ -331,10 +331,13 @@ class CudaBackend:
         N, C, HW = _nchw(x)
         return N * HW <= self.BN_SMALL_MAX
 
-    def bn_small_fwd(self, x, gamma, beta, running_mean, running_var, eps, momentum, nbt=None):
-        """one launch: batch statistics, y, running statistics -> (y, mean, invstd)"""
+    def bn_small_fwd(self, x, gamma, beta, running_mean, running_var, eps, momentum, nbt=None, slope=None):
+        """one launch: batch statistics, y (optionally through the following per-channel PReLU), running statistics
+        -> (y, mean, invstd)"""
         N, C, HW = _nchw(x)
-        st = self._prep(x, gamma, beta, running_mean, running_var)
+        st = self._prep(x, gamma, beta, running_mean, running_var, slope)
+        if slope is not None and slope.numel() != C:
+            raise _lib.GanB200Error("bn_small_fwd: the fused PReLU needs one slope per channel")
         if nbt is not None and nbt.dtype != torch.int64:
             raise _lib.GanB200Error("num_batches_tracked must be int64")
         y = torch.empty_like(x)
@@ -342,19 +345,21 @@ class CudaBackend:
         invstd = torch.empty((C,), dtype=torch.float32, device=x.device)
         _lib.check(self.lib.ganb200_bn_small_fwd(self._p(x), self._p(gamma), self._p(beta), self._p(y), self._p(mean),
                                                  self._p(invstd), self._p(running_mean), self._p(running_var),
-                                                 self._p(nbt), N, C, HW, eps, momentum, st))
+                                                 self._p(nbt), N, C, HW, eps, momentum, self._p(slope), st))
         return y, mean, invstd
 
-    def bn_small_bwd(self, gy, x, mean, invstd, gamma):
-        """one launch: (gx, ggamma, gbeta)"""
+    def bn_small_bwd(self, gy, x, mean, invstd, gamma, beta=None, slope=None):
+        """one launch: (gx, ggamma, gbeta[, gslope when the PReLU is fused])"""
         N, C, HW = _nchw(x)
-        st = self._prep(gy, x, mean, invstd, gamma)
+        st = self._prep(gy, x, mean, invstd, gamma, beta, slope)
         gx = torch.empty_like(x)
         gg = torch.empty((C,), dtype=torch.float32, device=x.device)
         gb = torch.empty((C,), dtype=torch.float32, device=x.device)
+        gs = torch.empty((C,), dtype=torch.float32, device=x.device) if slope is not None else None
         _lib.check(self.lib.ganb200_bn_small_bwd(self._p(gy), self._p(x), self._p(mean), self._p(invstd),
-                                                 self._p(gamma), self._p(gx), self._p(gg), self._p(gb), N, C, HW, st))
-        return gx, gg, gb
+                                                 self._p(gamma), self._p(gx), self._p(gg), self._p(gb), N, C, HW,
+                                                 self._p(beta), self._p(slope), self._p(gs), st))
+        return (gx, gg, gb) if slope is None else (gx, gg, gb, gs)
 
     def bn_bwd_reduce(self, gy, x, mean, invstd):
         N, C, HW = _nchw(x)

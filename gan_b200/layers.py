@@ -64,6 +64,33 @@ class _BatchNormMixin:
         return ops.batch_norm_eval(x, self.weight, self.bias, self.running_mean, self.running_var, self.eps)
 
 
+class Sequential(nn.Sequential):
+    """nn.Sequential (same child names, so the same state_dict keys) that runs a training-mode BatchNorm immediately
+    followed by PReLU(C) as one fused launch when the per-channel population is small — the (linear | conv, BN, PReLU)
+    triples of generators/generator_13_5.py:60-66.  Anything else is executed module by module."""
+
+    def forward(self, x):
+        mods = list(self)
+        i = 0
+        while i < len(mods):
+            m = mods[i]
+            nxt = mods[i + 1] if i + 1 < len(mods) else None
+            if (isinstance(m, _BatchNormMixin) and isinstance(nxt, PReLU) and m.training and m.track_running_stats
+                    and m.weight is not None and m.bias is not None and not m._forward_hooks and
+                    not nxt._forward_hooks and not nxt._forward_pre_hooks and ops.bn_prelu_fusable(x, nxt.weight)):
+                m._check_input_dim(x)
+                n, _, hw = KN._nchw(x)
+                if n * hw <= 1:
+                    raise ValueError(f"Expected more than 1 value per channel when training, got input size {x.size()}")
+                x = ops.batch_norm_prelu_train(x, m.weight, m.bias, nxt.weight, m.running_mean, m.running_var, m.eps,
+                                               0.0 if m.momentum is None else m.momentum, m.num_batches_tracked)
+                i += 2
+                continue
+            x = m(x)
+            i += 1
+        return x
+
+
 class BatchNorm2d(_BatchNormMixin, nn.BatchNorm2d):
     """nn.BatchNorm2d in the generators (generator_13_5.py:49,157,...): batch statistics whenever the module
     is in train mode — which in the reference is always — running stats updated on every call."""

@@ -741,6 +741,37 @@ class BatchNormTrainFn(Function):
                 None, None)
 
 
+class BnPReluTrainFn(Function):
+    """nn.BatchNorm1d/2d (training mode) followed by nn.PReLU(C) as ONE launch each way — the `_fc_bn_act` /
+    `_conv_bn_act` triples of generators/generator_13_5.py:60-66 on small per-channel populations (N*HW <= 4096).
+    The batch-norm output is not stored: the backward recomputes it from x, mean, invstd, gamma, beta."""
+
+    @staticmethod
+    def forward(ctx, x, gamma, beta, slope, running_mean, running_var, eps, momentum, nbt=None):
+        x = _c(x)
+        y, mean, invstd = K().bn_small_fwd(x, gamma, beta, running_mean, running_var, eps, momentum, nbt, slope)
+        ctx.save_for_backward(x, mean, invstd, gamma, beta, slope)
+        return y
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, gy):
+        x, mean, invstd, gamma, beta, slope = ctx.saved_tensors
+        gx, gg, gb, gs = K().bn_small_bwd(_c(gy), x, mean, invstd, gamma, beta, slope)
+        return (gx, (gg if gamma is not None else None), (gb if beta is not None else None), gs.reshape(slope.shape),
+                None, None, None, None, None)
+
+
+def bn_prelu_fusable(x, slope):
+    """single rank (no sync-BN exchange between statistics and apply), per-channel slope, small population"""
+    return (_sync_bn_hooks["stats"] is None and _sync_bn_hooks["grads"] is None and x.dim() >= 2 and
+            slope.numel() == x.shape[1] and K().bn_small_ok(x))
+
+
+def batch_norm_prelu_train(x, gamma, beta, slope, running_mean, running_var, eps, momentum, nbt=None):
+    return BnPReluTrainFn.apply(x, gamma, beta, slope, running_mean, running_var, eps, momentum, nbt)
+
+
 def batch_norm_train(x, gamma, beta, running_mean, running_var, eps, momentum, nbt=None):
     return BatchNormTrainFn.apply(x, gamma, beta, running_mean, running_var, eps, momentum, nbt)
 

@@ -74,7 +74,7 @@ class _SKAttention(nn.Module):
     def _build_heads(self, planes, m):
         self.M = m
         for i in range(m):
-            self.__setattr__('fc_sub_%d' % i, nn.Sequential(*_fc_bn_act(planes, 1), EqualizedLinear(planes, planes)))
+            self.__setattr__('fc_sub_%d' % i, L.Sequential(*_fc_bn_act(planes, 1), EqualizedLinear(planes, planes)))
         self.softmax = nn.Softmax(dim=1)
 
     def _heads(self, fea_z, b, s, c):
@@ -88,9 +88,9 @@ class SKAttention_conv(_SKAttention):
     def __init__(self, planes: int, m: int):
         super(SKAttention_conv, self).__init__()
         self.gap_conv = L.AdaptiveAvgPool2d(5)
-        self.conv_main = nn.Sequential(*_conv_bn_act(planes, 2))
+        self.conv_main = L.Sequential(*_conv_bn_act(planes, 2))
         self.gap_fc = L.AdaptiveAvgPool2d(1)
-        self.fc_main = nn.Sequential(*_fc_bn_act(planes, 1))
+        self.fc_main = L.Sequential(*_fc_bn_act(planes, 1))
         self._build_heads(planes, m)
 
     def forward(self, feas):
@@ -108,7 +108,7 @@ class SKAttention_fc(_SKAttention):
     def __init__(self, planes: int, m: int):
         super(SKAttention_fc, self).__init__()
         self.gap_fc = L.AdaptiveAvgPool2d(1)
-        self.fc_main = nn.Sequential(*_fc_bn_act(planes, 2))
+        self.fc_main = L.Sequential(*_fc_bn_act(planes, 2))
         self._build_heads(planes, m)
 
     def forward(self, feas):
@@ -173,7 +173,7 @@ class MappingNetwork(nn.Module):
 
     def __init__(self, planes: int, n_layers: int):
         super(MappingNetwork, self).__init__()
-        self.net = nn.Sequential(*_fc_bn_act(planes, n_layers))
+        self.net = L.Sequential(*_fc_bn_act(planes, n_layers))
 
     def forward(self, z: torch.Tensor):
         return self.net(z)
@@ -311,9 +311,9 @@ class SEBlock_conv(nn.Module):
     def __init__(self, in_planes: int):
         super(SEBlock_conv, self).__init__()
         self.gap_conv = L.AdaptiveAvgPool2d(5)
-        self.convs = nn.Sequential(*_conv_bn_act(in_planes, 2))
+        self.convs = L.Sequential(*_conv_bn_act(in_planes, 2))
         self.gap_fc = L.AdaptiveAvgPool2d(1)
-        self.fcs = nn.Sequential(*_fc_bn_act(in_planes, 1))
+        self.fcs = L.Sequential(*_fc_bn_act(in_planes, 1))
         self.fc_out = EqualizedLinear(in_planes, in_planes)
         self.fc_bn = L.BatchNorm1d(in_planes)
         self.activation2 = L.Sigmoid()
@@ -332,7 +332,7 @@ class SEBlock_fc(nn.Module):
     def __init__(self, in_planes: int):
         super(SEBlock_fc, self).__init__()
         self.gap = L.AdaptiveAvgPool2d(1)
-        self.fcs = nn.Sequential(*_fc_bn_act(in_planes, 2))
+        self.fcs = L.Sequential(*_fc_bn_act(in_planes, 2))
         self.fc_out = EqualizedLinear(in_planes, in_planes)
         self.fc_bn = L.BatchNorm1d(in_planes)
         self.activation2 = L.Sigmoid()

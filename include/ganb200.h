@@ -164,13 +164,17 @@ int ganb200_bn_bwd_apply(const float* gy, const float* x, const float* mean, con
  * BatchNorm2d of the 5x5 / 3x3 / 1x1 attention maps, generator_13_5.py:60-66,100-118,212-214): ONE launch computes the
  * batch mean and biased variance (two-pass), y, save_mean / save_invstd, the running statistics (unbiased variance,
  * momentum) and num_batches_tracked += 1; the backward ONE launch computes dx, dgamma, dbeta.  Same results as
- * ganb200_bn_stats + ganb200_bn_apply resp. ganb200_bn_bwd_reduce + ganb200_bn_bwd_apply; deterministic. */
+ * ganb200_bn_stats + ganb200_bn_apply resp. ganb200_bn_bwd_reduce + ganb200_bn_bwd_apply; deterministic.
+ * prelu_slope ([C] or NULL) fuses the nn.PReLU(C) that follows the norm in _fc_bn_act / _conv_bn_act
+ * (generator_13_5.py:60-66): y = prelu(bn(x)); the backward then takes gy = dL/dy, recomputes bn(x) from x, mean,
+ * invstd, gamma, beta, and also returns gslope[c] = sum gy * min(bn(x), 0). */
 int ganb200_bn_small_eligible(int N, int C, int HW);
 int ganb200_bn_small_fwd(const float* x, const float* gamma, const float* beta, float* y, float* mean, float* invstd,
                          float* running_mean, float* running_var, int64_t* num_batches_tracked, int N, int C, int HW,
-                         float eps, float momentum, void* stream);
+                         float eps, float momentum, const float* prelu_slope, void* stream);
 int ganb200_bn_small_bwd(const float* gy, const float* x, const float* mean, const float* invstd, const float* gamma,
-                         float* gx, float* ggamma, float* gbeta, int N, int C, int HW, void* stream);
+                         float* gx, float* ggamma, float* gbeta, int N, int C, int HW, const float* beta,
+                         const float* prelu_slope, float* gslope, void* stream);
 
 /* softmax over dim=1 of a [B,M,C] tensor (nn.Softmax(dim=1), generator_13_5.py:72,87) */
 int ganb200_softmax_m_fwd(const float* x, float* y, int B, int M, int C, void* stream);

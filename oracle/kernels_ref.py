@@ -180,15 +180,27 @@ class RefBackend:
         n = x.numel() // x.shape[1] if x.dim() > 1 else 1
         return n <= 4096
 
-    def bn_small_fwd(self, x, gamma, beta, running_mean, running_var, eps, momentum, nbt=None):
+    def bn_small_fwd(self, x, gamma, beta, running_mean, running_var, eps, momentum, nbt=None, slope=None):
         mean, var = self.bn_stats(x)
         count = x.numel() // x.shape[1]
         y, invstd = self.bn_apply(x, mean, var, gamma, beta, running_mean, running_var, eps, momentum, count, nbt)
+        if slope is not None:
+            y = self.prelu_fwd(y, slope)
         return y, mean, invstd
 
-    def bn_small_bwd(self, gy, x, mean, invstd, gamma):
+    def bn_small_bwd(self, gy, x, mean, invstd, gamma, beta=None, slope=None):
+        count = x.numel() // x.shape[1]
+        gs = None
+        if slope is not None:  # recompute the batch-norm output, then the PReLU adjoint
+            u = (x - self._cview(x, mean)) * self._cview(x, invstd)
+            if gamma is not None:
+                u = u * self._cview(x, gamma)
+            if beta is not None:
+                u = u + self._cview(x, beta)
+            gy, gs = self.prelu_bwd(gy, u, slope)
         s1, s2 = self.bn_bwd_reduce(gy, x, mean, invstd)
-        return self.bn_bwd_apply(gy, x, mean, invstd, gamma, s1, s2, x.numel() // x.shape[1])
+        out = self.bn_bwd_apply(gy, x, mean, invstd, gamma, s1, s2, count)
+        return out if slope is None else (*out, gs)
 
     def bn_bwd_reduce(self, gy, x, mean, invstd):
         dims = [d for d in range(x.dim()) if d != 1]

@@ -292,6 +292,17 @@ def test_batchnorm_fused_small(cu, ref, shape, affine):
         assert rel(a, b) < 1e-4
     big = rnd(64, 3, 16, 16)
     assert not cu.bn_small_ok(g(big)) and not ref.bn_small_ok(big)
+    if affine:  # with the following nn.PReLU(C) fused in
+        slope = torch.rand(C) * 0.5
+        rm_g, rv_g, nbt_g = g(rm.clone()), g(rv.clone()), g(nbt.clone())
+        y, m, inv = cu.bn_small_fwd(g(x), g(gamma), g(beta), rm_g, rv_g, 1e-5, 0.1, nbt_g, g(slope))
+        y_r, m_r, inv_r = ref.bn_small_fwd(x, gamma, beta, rm.clone(), rv.clone(), 1e-5, 0.1, nbt.clone(), slope)
+        assert rel(y, y_r) < FP32_TOL and rel(m, m_r) < FP32_TOL and rel(inv, inv_r) < FP32_TOL
+        out = cu.bn_small_bwd(g(gy), g(x), m, inv, g(gamma), g(beta), g(slope))
+        out_r = ref.bn_small_bwd(gy, x, m_r, inv_r, gamma, beta, slope)
+        assert len(out) == len(out_r) == 4
+        for a, b in zip(out, out_r):
+            assert rel(a, b) < 1e-4
 
 
 def test_softmax_mbstd_bce(cu, ref):
