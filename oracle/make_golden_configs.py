@@ -1,7 +1,8 @@
-"""TEST INFRASTRUCTURE — golden vectors of the other BASELINE configs, produced by running
+"""TEST INFRASTRUCTURE — golden vectors of the other BASELINE configs and of the pair the
+reference's main.py builds as committed ("main"), produced by running
 the UNMODIFIED reference (/root/reference through oracle/reference.py) on CPU fp32 with fixed seeds.
 
-    python -m oracle.make_golden_configs [cfg1 cfg4 cfg5]     (build container only)
+    python -m oracle.make_golden_configs [cfg1 cfg4 cfg5 main]     (build container only)
 
 writes tests/golden/<cfg>.pt.  Recipe per config (the same the tests replay with the drop-in modules):
   seed 0 -> construct G then D (weights = pure function of the seed; not stored);
@@ -28,6 +29,11 @@ CONFIGS = {
     "cfg4": dict(gen="generators.generator_3_progan", g_args=lambda: (1, 256, 256, 3), g_kw={},
                  dis="discriminators.discriminator_3_wgangp_progan", d_args=lambda: (1, 64, 3), d_kw={},
                  train="train.wgangp", B=4, names=("G3_PROGAN", "D3_WGAN_PROGAN")),
+    # what the reference's main.py builds as committed (main.py:44,60,77): generator_1 + the DCGAN-shaped critic
+    # behind get_discriminator.get_3_wgan(ndf=128) + train/wgangpR2.py
+    "main": dict(gen="generators.generator_1", g_args=lambda: (256, (3, 64, 64)), g_kw={},
+                 dis="discriminators.discriminator_3_wgangp", d_args=lambda: (1, 128, 3), d_kw={},
+                 train="train.wgangpR2", B=4, names=("G13", "D3_WGAN")),
     "cfg5": dict(gen="generators.generator_14", g_args=lambda: (256,), g_kw={},
                  dis="discriminators.discriminator_7_wgangpsn", d_args=lambda: (), d_kw={},
                  train="train.wgangpsnR2", B=8, names=("G14", "D7_WGANSN")),

@@ -6,7 +6,7 @@ not carry (outside SURVEY §8(a)) raises NotImplementedError when asked for, not
 import importlib
 import math
 
-_CARRIED = ("discriminator_1", "discriminator_3_wgangp_progan", "discriminator_7_wgangpsn", "discriminator_9_4")
+_CARRIED = ("discriminator_1", "discriminator_3_wgangp", "discriminator_3_wgangp_progan", "discriminator_7_wgangpsn", "discriminator_9_4")
 
 
 def _module(name):
