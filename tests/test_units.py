@@ -94,3 +94,28 @@ def test_factories_mirror_the_reference_names():
         get_discriminator.get_8(1, cpu)
     d4 = get_discriminator.get_3_wgan_progan(1, cpu, ndf=8, nc=3)
     assert type(d4).__name__ == "Discriminator" and len(d4.main) == 24
+
+
+def test_dataloader_mirrors_the_reference_pipeline(tmp_path):
+    """units/dataloader.py: same three functions as the reference's (units/dataloader.py:5-32) — ImageFolder ->
+    ToTensor -> flip -> bicubic Resize((size, size)) -> ImageNet Normalize; DataLoader(shuffle, drop_last)."""
+    import numpy as np
+    from PIL import Image
+    from units import dataloader
+    root = tmp_path / "imgs" / "cls"
+    root.mkdir(parents=True)
+    rs = np.random.RandomState(0)
+    for i in range(5):
+        Image.fromarray(rs.randint(0, 255, (40 + i, 52, 3), dtype=np.uint8)).save(root / f"{i}.png")
+    ds = dataloader.get_dataset(str(tmp_path / "imgs"), size=64)
+    assert len(ds) == 5
+    x, y = ds[0]
+    assert x.shape == (3, 64, 64) and x.dtype == torch.float32 and y == 0
+    names = [type(t).__name__ for t in ds.transform.transforms]
+    assert names == ["ToTensor", "RandomHorizontalFlip", "Resize", "Normalize"]
+    assert tuple(ds.transform.transforms[3].mean) == (0.485, 0.456, 0.406)
+    dl = dataloader.get_dataloader(ds, 2)
+    batches = list(dl)
+    assert len(dl) == 2 and len(batches) == 2 and batches[0][0].shape == (2, 3, 64, 64)   # drop_last
+    assert dl.drop_last and type(dl.sampler).__name__ == "RandomSampler"
+    assert callable(dataloader.get_MNIST)
