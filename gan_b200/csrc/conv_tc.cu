@@ -9,9 +9,13 @@
 //                 that is the whole im2col) and one 3-D box of weights into a SWIZZLE_128B ring
 //        warp 1 : tcgen05.mma issuer (one thread), fp32 accumulator 128 lanes x BN columns in TMEM
 //        warps 2-5 : epilogue — tcgen05.ld, alpha / oscale / bias, fp32 NCHW stores
-// dgrad (stride 1) = the same kernel on dy with the flipped, transposed weights and zero padding R-1, written to the
-//   padded domain and folded (adjoint of replicate padding) when needed.
-// wgrad = conv_tc_wgrad.cu.
+//      tc_conv_halo_kernel (stride-1 problems on planes >= 256 pixels): one box per filter COLUMN, the filter rows and
+//        two stacked sub-tiles are row-shifted views of it (see the kernel's comment).
+// dgrad (stride 1) = the same kernels on dy with the flipped, transposed weights and zero padding R-1, written to the
+//   padded domain and folded (adjoint of replicate padding) when needed; stride 2 = one problem per output phase.
+// wgrad = tc_wgrad_kernel (one CTA per tap and pixel split) / tc_wgrad_ring_kernel (one CTA per filter column, rows of
+//   the input in a shared-memory ring), both below, + a deterministic split reduction.
+// Producer and MMA warps run warp-uniform loops and predicate the issue on elect.sync (tc_ptx.cuh: elect_one).
 #include "common.cuh"
 #include "conv_common.cuh"
 #include "tc_ptx.cuh"
