@@ -126,6 +126,42 @@ def test_batchnorm_and_softmax(ref_backend):
     assert gradcheck(ops.softmax_m, (a,))
 
 
+@pytest.mark.parametrize("shape", [(16, 12), (6, 12, 3, 3)])
+def test_fused_batchnorm_prelu_sequential_matches_torch(ref_backend, shape):
+    """gan_b200.layers.Sequential runs (BatchNorm, PReLU(C)) as one fused op each way: output, input / gamma / beta /
+    slope gradients, running statistics and num_batches_tracked against torch's own modules, fp64; same state_dict."""
+    from gan_b200 import layers as L
+    torch.manual_seed(0)
+    one_d = len(shape) == 2
+    seq = L.Sequential((L.BatchNorm1d if one_d else L.BatchNorm2d)(12), L.PReLU(12)).double()
+    want = torch.nn.Sequential((torch.nn.BatchNorm1d if one_d else torch.nn.BatchNorm2d)(12), torch.nn.PReLU(12)).double()
+    with torch.no_grad():
+        seq[0].weight.normal_()
+        seq[0].bias.normal_()
+        seq[1].weight.uniform_(0.1, 0.4)
+    assert list(seq.state_dict().keys()) == list(want.state_dict().keys())
+    want.load_state_dict(seq.state_dict())
+    x = torch.randn(*shape, dtype=torch.float64, requires_grad=True)
+    x2 = x.detach().clone().requires_grad_()
+    y, y2 = seq(x), want(x2)
+    assert type(y.grad_fn).__name__ == "BnPReluTrainFnBackward"   # the fused path ran
+    gy = torch.randn_like(y)
+    y.backward(gy)
+    y2.backward(gy)
+    assert torch.allclose(y, y2, atol=1e-12) and torch.allclose(x.grad, x2.grad, atol=1e-12)
+    for a, b in zip(seq.parameters(), want.parameters()):
+        assert torch.allclose(a.grad, b.grad, atol=1e-12)
+    for a, b in zip(seq.buffers(), want.buffers()):
+        assert torch.allclose(a.double(), b.double(), atol=1e-12)
+    # eval mode and a scalar-slope PReLU fall back to module-by-module execution
+    seq.eval()
+    want.eval()
+    assert torch.allclose(seq(x.detach()), want(x.detach()), atol=1e-12)
+    seq.train()
+    loose = L.Sequential((L.BatchNorm1d if one_d else L.BatchNorm2d)(12), L.PReLU()).double()
+    assert type(loose(x).grad_fn).__name__ != "BnPReluTrainFnBackward"
+
+
 @pytest.mark.parametrize("k", [1, 3, 5])
 def test_modulated_conv_equals_per_sample_weight_form(ref_backend, k):
     B, Ci, Co, H = 3, 4, 5, 6
