@@ -144,7 +144,7 @@ class DiscriminatorBlock(nn.Module):
     def forward(self, x):
         skip = self.residual(x)
         y = self.down_sample(self.block(x))
-        return ops.add(L.gate(y, self.se(y)), skip)
+        return L.gated_residual(skip, y, self.se(y))
 
 
 class Discriminator(nn.Module):

@@ -249,8 +249,7 @@ def sk_merge(branches, att):
     out = None
     for i, fea in enumerate(branches):
         a_i = ops.slice_channels(att, i, i + 1).reshape(b, -1)
-        t = ops.mul_bc(fea, a_i, KN.V_NC)
-        out = t if out is None else ops.add(out, t)
+        out = ops.mul_bc(fea, a_i, KN.V_NC) if out is None else ops.fma_bc(out, a_i, fea, KN.V_NC)
     return out
 
 
@@ -258,6 +257,13 @@ def gate(x, g):
     """x * g with g:(b,c,1,1) — the SE product (discriminator_9_4.py:160, generator_13_5.py:457)."""
     b, c = x.shape[:2]
     return ops.mul_bc(x, g.reshape(b, c), KN.V_NC)
+
+
+def gated_residual(skip, x, g):
+    """skip + x * g in one pass (the SE product followed by the residual add: discriminator_9_4.py:160-161,
+    generator_13_5.py:457-458)."""
+    b, c = x.shape[:2]
+    return ops.fma_bc(skip, g.reshape(b, c), x, KN.V_NC)
 
 
 class BCELoss(nn.BCELoss):

@@ -207,22 +207,26 @@ class AddBcFn(Function):
 
 
 class FmaBcFn(Function):
-    """y = x + v*z (noise injection, generators/generator_13_5.py:265): z is a constant."""
+    """y = x + v*z in one pass: noise injection (generators/generator_13_5.py:265, z a constant), the selective-kernel
+    merge sum_i fea_i * a_i (generator_13_5.py:169,201,294) and the gated residuals x + r * se(r)
+    (generator_13_5.py:384, discriminator_9_4.py:160) — there z carries a gradient too (g * v)."""
 
     @staticmethod
     def forward(ctx, x, v, z, vmode):
         x, v, z = _c(x), _c(v), _c(z)
-        ctx.save_for_backward(z)
+        ctx.save_for_backward(z, v)
         ctx.vmode, ctx.vshape = vmode, v.shape
         return K().ew_fma_bcast(x, v, z, vmode)
 
     @staticmethod
     def backward(ctx, g):
-        (z,) = ctx.saved_tensors
-        gv = None
+        z, v = ctx.saved_tensors
+        gv = gz = None
         if ctx.needs_input_grad[1]:
             gv = ReduceFn.apply(_c(g), z, _RMODE_OF_VMODE[ctx.vmode], 1.0).reshape(ctx.vshape)
-        return g, gv, None, None
+        if ctx.needs_input_grad[2]:
+            gz = MulBcFn.apply(_c(g), v, ctx.vmode)
+        return g, gv, gz, None
 
 
 # =====================================================================================================
@@ -393,6 +397,11 @@ def add_bc(x, v, vmode=KN.V_C):
 
 def noise_add(x, scale_c, z):
     return FmaBcFn.apply(x, scale_c, z, KN.V_C)
+
+
+def fma_bc(x, v, z, vmode=KN.V_NC):
+    """x + v*z with v broadcast like mul_bc's; differentiable in all three."""
+    return FmaBcFn.apply(x, v, z, vmode)
 
 
 def global_avg_pool(x):

@@ -381,7 +381,7 @@ class BasicBlock(nn.Module):
         x_tra = ops.slice_channels(x, d)
         res3, tra3 = self.rir_3((x_res, x_tra), w)
         res3_head = ops.slice_channels(res3, 0, d)
-        feas_residual = ops.add(head, L.gate(res3_head, self.se_attention_residual(res3_head)))
+        feas_residual = L.gated_residual(head, res3_head, self.se_attention_residual(res3_head))
         if self.root:
             mid = self.activation_shortcut(self.shortcut(x, w))
         else:

@@ -92,6 +92,14 @@ def test_pointwise_and_broadcast(ref_backend):
     z = r(2, 3, 4, 4, grad=False)
     assert torch.allclose(ops.noise_add(x, vc, z), x + vc[None, :, None, None] * z)
     assert gradcheck(lambda x, vc: ops.noise_add(x, vc, z), (x, vc))
+    # x + v*z with a differentiable z: the selective-kernel merge and the gated residuals (twice: R1 runs through D's)
+    zz = r(2, 3, 4, 4)
+    assert torch.allclose(ops.fma_bc(x, v, zz), x + v[:, :, None, None] * zz)
+    assert gradcheck(ops.fma_bc, (x, v, zz)) and gradgradcheck(ops.fma_bc, (x, v, zz))
+    from gan_b200 import layers as L
+    assert torch.allclose(L.gated_residual(x, zz, v.reshape(2, 3, 1, 1)), x + zz * v[:, :, None, None])
+    att = torch.softmax(r(2, 2, 3, grad=False), 1)
+    assert torch.allclose(L.sk_merge([x, zz], att), x * att[:, 0, :, None, None] + zz * att[:, 1, :, None, None])
 
 
 def test_minibatch_stddev(ref_backend):
