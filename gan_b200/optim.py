@@ -64,6 +64,12 @@ class FusedAdam(torch.optim.Optimizer):
         self._cache[key] = hit
         return hit["tab"], hit["blk"], len(blocks)
 
+    def load_state_dict(self, state_dict):
+        """torch.optim semantics; the pointer tables and the device-side step counters are rebuilt on the next step."""
+        super().load_state_dict(state_dict)
+        self._cache.clear()
+        self._step_dev.clear()
+
     @torch.no_grad()
     def step(self, closure=None):
         loss = None

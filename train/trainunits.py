@@ -12,6 +12,7 @@ from pathlib import Path
 
 import torch
 
+from gan_b200 import checkpoint as ckpt_io
 from gan_b200 import optim
 
 try:  # no graphics stack on the GPU boxes; the preview is a convenience, never part of the step
@@ -79,13 +80,25 @@ class Units():
             return
         vutils.save_image(vutils.make_grid(gen_imgs, padding=2, normalize=True).squeeze(), target + ".png")
 
-    # ---- checkpoints (whole-module pickles, reference :58-131) -----------------------------------------
+    # ---- checkpoints (whole-module pickles, reference :58-131; interop rules in gan_b200/checkpoint.py) -----------
+    # Opt-in departures from the reference (environment, read at call time):
+    #   GANB200_CKPT_OPTIMIZER=1  save_ckpt adds both optimiser states; the loaders restore them
+    #   GANB200_CKPT_INPLACE=1    the loaders copy the file's weights INTO the live modules, so the optimisers built in
+    #                             __init__ keep training them (the reference replaces self.generator / self.discriminator
+    #                             with the unpickled object and leaves the optimisers bound to the old parameters:
+    #                             after a resume its Adam steps update modules nobody runs — kept by default)
     def save_ckpt(self, train_name, epoch, i):
         print('Saving.....')
         stem, e, ii = _ckpt_stem(self, train_name, epoch, i)
         state = {'generator': self.generator, 'generator_name': self.generator_name,
                  'discriminator': self.discriminator, 'discriminator_name': self.discriminator_name,
-                 'method': train_name, 'epoch': e, 'i': ii}
+                 'method': train_name, 'epoch': e, 'i': ii,
+                 # extra keys (the reference's loader ignores them): same storages as the modules, no extra bytes
+                 'generator_state': self.generator.state_dict(),
+                 'discriminator_state': self.discriminator.state_dict()}
+        if os.environ.get('GANB200_CKPT_OPTIMIZER') == '1':
+            state['optimizer_G'] = self.optimizer_G.state_dict()
+            state['optimizer_D'] = self.optimizer_D.state_dict()
         os.makedirs('checkpoint', exist_ok=True)
         torch.save(state, './checkpoint/' + stem + '_ckpt.pth')
 
@@ -111,10 +124,18 @@ class Units():
         print(what + ' i: ', checkpoint['i'])
         return checkpoint
 
+    def _adopt(self, checkpoint, what, live, optimizer, opt_key):
+        """The module to run after a load: never the stock-torch hybrid a reference pickle unpickles into."""
+        inplace = os.environ.get('GANB200_CKPT_INPLACE') == '1'
+        module = ckpt_io.load_into(checkpoint[what], live) if inplace else ckpt_io.adopt(checkpoint[what], live)
+        if inplace and opt_key in checkpoint and os.environ.get('GANB200_CKPT_OPTIMIZER') == '1':
+            optimizer.load_state_dict(checkpoint[opt_key])
+        return module
+
     def load_generator_ckpt(self, name):
         checkpoint = self._load(name, 'generator')
         if checkpoint is not None:
-            self.generator = checkpoint['generator']
+            self.generator = self._adopt(checkpoint, 'generator', self.generator, self.optimizer_G, 'optimizer_G')
             self.epoch = checkpoint['epoch']
             self.i = checkpoint['i']
             self.record.update({'epoch': self.epoch, 'i': self.i})
@@ -122,7 +143,8 @@ class Units():
     def load_discriminator_ckpt(self, name):
         checkpoint = self._load(name, 'discriminator')
         if checkpoint is not None:
-            self.discriminator = checkpoint['discriminator']
+            self.discriminator = self._adopt(checkpoint, 'discriminator', self.discriminator, self.optimizer_D,
+                                             'optimizer_D')
 
     def draw_plt_record(self, name_png, per_iteration):
         if plt is None:
