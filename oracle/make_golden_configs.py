@@ -37,6 +37,27 @@ CONFIGS = {
     "cfg5": dict(gen="generators.generator_14", g_args=lambda: (256,), g_kw={},
                  dis="discriminators.discriminator_7_wgangpsn", d_args=lambda: (), d_kw={},
                  train="train.wgangpsnR2", B=8, names=("G14", "D7_WGANSN")),
+    # SURVEY §8(f) rank 3 — pairs outside the BASELINE configs whose layers are all in the kernel set: the DCGAN pair of
+    # get_2 (with the factories' weights_init), the spectrally normalised DCGAN critic, the plain ShuffleNetV2 critic and
+    # the three ResNet-in-ResNet critics, each under a loop the reference pairs that kind of critic with.
+    "dcgan": dict(gen="generators.generator_2", g_args=lambda: (1, 256, 64, 3), g_kw={},
+                  dis="discriminators.discriminator_2", d_args=lambda: (1, 64, 3), d_kw={},
+                  train="train.gan", B=8, names=("G2", "D2"), weights_init=True),
+    "sn3": dict(gen="generators.generator_2", g_args=lambda: (1, 256, 64, 3), g_kw={},
+                dis="discriminators.discriminator_3_wgangpsn", d_args=lambda: (1, 64, 3), d_kw={},
+                train="train.wgansnR2", B=4, names=("G2", "D3_WGANSN")),
+    "shuffle": dict(gen="generators.generator_2", g_args=lambda: (1, 256, 64, 3), g_kw={},
+                    dis="discriminators.discriminator_7_wgangp", d_args=lambda: (), d_kw={},
+                    train="train.wgangpR2", B=4, names=("G2", "D7_WGAN")),
+    "rir_gp": dict(gen="generators.generator_2", g_args=lambda: (1, 256, 64, 3), g_kw={},
+                   dis="discriminators.discriminator_5_wgangp", d_args=lambda: (), d_kw={},
+                   train="train.wgangp", B=4, names=("G2", "D5_WGAN")),
+    "rir_sn": dict(gen="generators.generator_2", g_args=lambda: (1, 256, 64, 3), g_kw={},
+                   dis="discriminators.discriminator_5_wgangpsn", d_args=lambda: (), d_kw={},
+                   train="train.wgansn", B=4, names=("G2", "D5_WGANSN")),
+    "rir_bce": dict(gen="generators.generator_2", g_args=lambda: (1, 256, 64, 3), g_kw={},
+                    dis="discriminators.discriminator_5", d_args=lambda: (), d_kw={},
+                    train="train.gan", B=4, names=("G2", "D5")),  # BatchNorm critic: BCE loop without R-penalties
 }
 
 
@@ -46,10 +67,14 @@ def seed_all(s):
     random.seed(s)
 
 
-def build(cfg, genmod, dismod):
+def build(cfg, genmod, dismod, init_fn=None):
     seed_all(0)
     G = genmod.Generator(*cfg["g_args"](), **cfg["g_kw"])
+    if cfg.get("weights_init"):  # units/get_generators.py:18-23, get_discriminator.py:20-25 (get_2 only)
+        G.apply(init_fn)
     D = dismod.Discriminator(*cfg["d_args"](), **cfg["d_kw"])
+    if cfg.get("weights_init"):
+        D.apply(init_fn)
     return G, D
 
 
@@ -65,7 +90,7 @@ def buffer_norms(model):
     return {n: float(b.detach().double().norm()) for n, b in model.named_buffers()}
 
 
-def replay(cfg, genmod, dismod, trainmod, device=torch.device("cpu"), x=None, z=None):
+def replay(cfg, genmod, dismod, trainmod, device=torch.device("cpu"), x=None, z=None, init_fn=None):
     """Runs the recipe with whatever modules it is given (the reference here, the drop-in in the tests)."""
     B = cfg["B"]
     out = {"B": B}
@@ -75,7 +100,7 @@ def replay(cfg, genmod, dismod, trainmod, device=torch.device("cpu"), x=None, z=
         z = torch.randn(B, 256, 1, 1, generator=gx)
     out["x"], out["z"] = x, z
     xd, zd = x.to(device), z.to(device)
-    G, D = build(cfg, genmod, dismod)
+    G, D = build(cfg, genmod, dismod, init_fn)
     G, D = G.to(device), D.to(device)
     out["param_names_g"] = [n for n, _ in G.named_parameters()]
     out["param_names_d"] = [n for n, _ in D.named_parameters()]
@@ -87,7 +112,7 @@ def replay(cfg, genmod, dismod, trainmod, device=torch.device("cpu"), x=None, z=
         out["d_out"] = D(xd).detach().cpu().clone()
         out["g_out"] = G(zd).detach().cpu().clone()
     # one full iteration on fresh models
-    G, D = build(cfg, genmod, dismod)
+    G, D = build(cfg, genmod, dismod, init_fn)
     G, D = G.to(device), D.to(device)
     T = trainmod.Train([(xd, torch.zeros(B))], device, 1, 256, G, cfg["names"][0], D, cfg["names"][1])
     g0, d0 = snapshot(G), snapshot(D)
@@ -109,7 +134,8 @@ def main(argv):
     from oracle import reference as R
     for name in (argv or ["cfg1", "cfg4"]):
         cfg = CONFIGS[name]
-        out = replay(cfg, R.load(cfg["gen"]), R.load(cfg["dis"]), R.load(cfg["train"]))
+        init_fn = R.load("units.Weight_Initialization").weights_init if cfg.get("weights_init") else None
+        out = replay(cfg, R.load(cfg["gen"]), R.load(cfg["dis"]), R.load(cfg["train"]), init_fn=init_fn)
         out["torch"] = torch.__version__
         path = os.path.join(ROOT, "tests", "golden", name + ".pt")
         torch.save(out, path)

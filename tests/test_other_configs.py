@@ -18,7 +18,9 @@ from oracle.make_golden_configs import CONFIGS, replay
 # rounding noise (~1e-9), which Adam's normalisation turns into an O(lr) update of arbitrary sign whatever the
 # implementation (the CPU port differs from the reference by up to 40 % there and by < 2e-3 everywhere else).  They
 # are excluded from the update-norm comparison.
-NOISE_PARAMS = {"cfg1": None, "cfg4": re.compile(r"^main\.\d\.0\.bias$"), "cfg5": None, "main": None}
+NOISE_PARAMS = {"cfg1": None, "cfg4": re.compile(r"^main\.\d\.0\.bias$"), "cfg5": None, "main": None,
+                "rir_bce": re.compile(r"(stream_conv|stream_conv_across|short_cut\.0|pre_conv\.0)\.bias$")}
+ZOO = ["dcgan", "sn3", "shuffle", "rir_gp", "rir_sn", "rir_bce"]  # SURVEY §8(f) rank 3 pairs (make_golden_configs.py)
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 
@@ -28,14 +30,15 @@ def rel(a, b):
     return float((a - b).norm() / b.norm().clamp_min(1e-30))
 
 
-def compare(name, device, tol_out, tol_loss, tol_upd, floor=1e-6, chain=True):
+def compare(name, device, tol_out, tol_loss, tol_upd, floor=1e-6, chain=True, tol_gloss=None):
     from gan_b200 import rng
     cfg = CONFIGS[name]
     gold = torch.load(os.path.join(GOLDEN, name + ".pt"), weights_only=False)
     mods = [importlib.import_module(cfg[k]) for k in ("gen", "dis", "train")]
+    init_fn = importlib.import_module("units.Weight_Initialization").weights_init if cfg.get("weights_init") else None
     prev = rng.host_stream(True)
     try:
-        got = replay(cfg, *mods, device=device, x=gold["x"], z=gold["z"])
+        got = replay(cfg, *mods, device=device, x=gold["x"], z=gold["z"], init_fn=init_fn)
     finally:
         rng.host_stream(prev)
     bad = []
@@ -55,16 +58,20 @@ def compare(name, device, tol_out, tol_loss, tol_upd, floor=1e-6, chain=True):
         assert all(math.isfinite(v) for v in got["step_d_losses"] + [got["step_g_loss"], got["step_gen_imgs_norm"]])
         assert not bad, bad[:20]
         return got
-    for g, w in zip(got["step_d_losses"] + [got["step_g_loss"]], gold["step_d_losses"] + [gold["step_g_loss"]]):
+    for g, w in zip(got["step_d_losses"], gold["step_d_losses"]):
         if not abs(g - w) <= tol_loss * max(abs(w), 1e-2):
-            bad.append(("loss", g, w))
+            bad.append(("d loss", g, w))
+    g, w = got["step_g_loss"], gold["step_g_loss"]  # evaluated AFTER the critic's Adam step
+    if not abs(g - w) <= (tol_loss if tol_gloss is None else tol_gloss) * max(abs(w), 1e-2):
+        bad.append(("g loss", g, w))
     e = abs(got["step_gen_imgs_norm"] - gold["step_gen_imgs_norm"]) / gold["step_gen_imgs_norm"]
     if not e < tol_out:
         bad.append(("step_gen_imgs_norm", e))
     for k in ("step_d_updates", "step_g_updates", "step_d_buffers", "step_g_buffers"):
         for n, w in gold[k].items():
             g = got[k][n]
-            if k == "step_g_updates" and NOISE_PARAMS[name] is not None and NOISE_PARAMS[name].match(n):
+            noise = NOISE_PARAMS.get(name)
+            if noise is not None and k == ("step_d_updates" if name == "rir_bce" else "step_g_updates") and noise.search(n):
                 continue
             if not abs(g - w) <= tol_upd * max(abs(w), floor) + floor:
                 bad.append((k, n, g, w))
@@ -72,9 +79,21 @@ def compare(name, device, tol_out, tol_loss, tol_upd, floor=1e-6, chain=True):
     return got
 
 
-@pytest.mark.parametrize("name", ["cfg1", "cfg4", "cfg5", "main"])
+# The critics of these pairs start nearly constant (default init, |D(x)| ~ 1e-2, R1 ~ 1e-12): many of their gradients
+# are ~1e-9, the size of Adam's eps, so the first update of those tensors follows fp32 rounding (update norms differ by up
+# to 3.5e-3 from the reference's, all D-step losses — computed before any update — agree to 1e-6) and the generator loss,
+# evaluated on the UPDATED critic, inherits it (measured 2.7 % / 6e-4 / 1.4e-4).
+# rir_bce (27 BatchNorms over a batch of 4): the reference's own fp32 weight gradients are 2.3e-4 off its fp64 run (this
+# port: 5e-5 off the same fp64 run), the real and fake passes then partly cancel (3e-3 on the accumulated gradient), and
+# ~4 600 of 26 M critic weights get the opposite Adam sign: update NORMS agree to 1e-4, the generator loss to 2.8e-3.
+# Conv biases feeding a BatchNorm have an analytically zero gradient (NOISE_PARAMS).
+TOL_CPU = {"shuffle": dict(tol_gloss=5e-2, tol_upd=5e-3), "rir_gp": dict(tol_gloss=2e-3), "rir_sn": dict(tol_gloss=1e-3),
+           "rir_bce": dict(tol_gloss=1e-2)}
+
+
+@pytest.mark.parametrize("name", ["cfg1", "cfg4", "cfg5", "main"] + ZOO)
 def test_config_cpu_port_matches_reference_golden(ref_backend, name):
-    compare(name, torch.device("cpu"), tol_out=1e-4, tol_loss=1e-4, tol_upd=2e-3)
+    compare(name, torch.device("cpu"), **{**dict(tol_out=1e-4, tol_loss=1e-4, tol_upd=2e-3), **TOL_CPU.get(name, {})})
 
 
 # cfg5 on the GPU.  The critic is spectrally normalised 79 times over: its outputs are ~5e-3 and its gradients ~1e-9, the
@@ -108,6 +127,18 @@ def test_config_cuda_tcgen05_matches_reference_golden(monkeypatch, name):
     lr*sign(g)-like (|update| ~ lr per element whatever the gradient scale), so the update norms stay tight."""
     monkeypatch.setenv("GANB200_PRECISION", "auto")
     compare(name, torch.device("cuda"), **TOL_BF16[name])
+
+
+# Written after this round's GPU minutes were spent: never run on a B200 yet, so opt-in (GANB200_TEST_ZOO_GPU=1) until a
+# GPU call has confirmed it — a first run belongs in a `gpurun`, not in the driver's round-end suite.  Every kernel these
+# pairs launch is covered by tests/test_gpu_kernels.py and by the BASELINE configs above.
+@pytest.mark.gpu
+@pytest.mark.skipif(os.environ.get("GANB200_TEST_ZOO_GPU") != "1", reason="unconfirmed on GPU: set GANB200_TEST_ZOO_GPU=1")
+@pytest.mark.parametrize("name", ZOO)
+def test_zoo_cuda_fp32_matches_reference_golden(monkeypatch, name):
+    monkeypatch.setenv("GANB200_PRECISION", "fp32")
+    tol = {**dict(tol_out=2e-4, tol_loss=1e-3, tol_upd=5e-3, tol_gloss=5e-2), **({"tol_upd": 2e-2} if name == "shuffle" else {})}
+    compare(name, torch.device("cuda"), **tol)
 
 
 @pytest.mark.gpu

@@ -94,6 +94,18 @@ def test_factories_mirror_the_reference_names():
         get_discriminator.get_8(1, cpu)
     d4 = get_discriminator.get_3_wgan_progan(1, cpu, ndf=8, nc=3)
     assert type(d4).__name__ == "Discriminator" and len(d4.main) == 24
+    # get_2 (both factories) applies the DCGAN weights_init: conv weights N(0, 0.02), BatchNorm weights N(1, 0.02)
+    torch.manual_seed(0)
+    g2, d2 = get_generators.get_2(1, cpu, 16, 8, 3), get_discriminator.get_2(1, cpu, 8, 3)
+    assert abs(float(g2.main[0].weight.std()) - 0.02) < 0.005 and abs(float(g2.main[1].weight.mean()) - 1.0) < 0.02
+    assert abs(float(d2.main[2].weight.std()) - 0.02) < 0.005 and float(d2.main[3].bias.abs().max()) == 0.0
+    # the other carried critics build through their factories with the reference's widths
+    count = lambda m: sum(p.numel() for p in m.parameters())
+    assert count(get_discriminator.get_3_wgansn(1, cpu, 8, 3)) == 3 * 8 * 16 + 16 * (8 * 16 + 16 * 32 + 32 * 64) + 64 * 16
+    assert count(get_discriminator.get_7_wgan(1, cpu)) == 2747849
+    assert count(get_discriminator.get_5_wgan(1, cpu)) == 25338113
+    assert count(get_discriminator.get_5_wgansn(1, cpu)) == 26103041
+    assert count(get_discriminator.get_5(1, cpu)) == 26118657
 
 
 def test_dataloader_mirrors_the_reference_pipeline(tmp_path):

@@ -6,7 +6,9 @@ not carry (outside SURVEY §8(a)) raises NotImplementedError when asked for, not
 import importlib
 import math
 
-_CARRIED = ("discriminator_1", "discriminator_3_wgangp", "discriminator_3_wgangp_progan", "discriminator_7_wgangpsn", "discriminator_9_4")
+_CARRIED = ("discriminator_1", "discriminator_2", "discriminator_3_wgangp", "discriminator_3_wgangp_progan",
+            "discriminator_3_wgangpsn", "discriminator_5", "discriminator_5_wgangp", "discriminator_5_wgangpsn",
+            "discriminator_7_wgangp", "discriminator_7_wgangpsn", "discriminator_9_4")
 
 
 def _module(name):
@@ -34,7 +36,14 @@ def _plain_factory(fn_name, name, *args):
     return get
 
 
-get_2 = _dcgan_factory("get_2", "discriminator_2")
+def get_2(ngpu, device, ndf, nc):
+    """reference :20-25 — the only discriminator factory that applies the DCGAN `weights_init`."""
+    from units import Weight_Initialization
+    discriminator = _module("discriminator_2").Discriminator(ngpu=ngpu, ndf=ndf, nc=nc).to(device)
+    discriminator.apply(Weight_Initialization.weights_init)
+    return discriminator
+
+
 get_3_wgan = _dcgan_factory("get_3_wgan", "discriminator_3_wgangp")
 get_3_wgan_progan = _dcgan_factory("get_3_wgan_progan", "discriminator_3_wgangp_progan")
 get_3_wgansn = _dcgan_factory("get_3_wgansn", "discriminator_3_wgangpsn")

@@ -1,13 +1,13 @@
 """units.get_generators — drop-in for the reference's units/get_generators.py:12-111: `get_<name>(...)` builds a
 generator and moves it to `device`, same names and argument lists.  Generators are imported lazily, so the factory of
-a family this repo does not carry (everything outside SURVEY §8(a): generator_2, 4-13) raises a clear
+a family this repo does not carry (everything outside SURVEY §8(a) and §8(f): generator_4-13) raises a clear
 NotImplementedError instead of failing the whole module at import as a missing file would.
 
 `get_13_5` and `get_14` are additions: the reference has no factory for its two newest generators (its main.py builds
 them by hand)."""
 import importlib
 
-_CARRIED = ("generator_1", "generator_3_progan", "generator_13_5", "generator_14")
+_CARRIED = ("generator_1", "generator_2", "generator_3_progan", "generator_13_5", "generator_14")
 
 
 def _module(name):
@@ -21,7 +21,11 @@ def get_1(device, z_dim, target_image_size):
 
 
 def get_2(ngpu, device, nz, ngf, nc):
-    return _module("generator_2").Generator(ngpu=ngpu, nz=nz, ngf=ngf, nc=nc).to(device)
+    """reference :17-22 — the only generator factory that applies the DCGAN `weights_init`."""
+    from units import Weight_Initialization
+    generator = _module("generator_2").Generator(ngpu=ngpu, nz=nz, ngf=ngf, nc=nc).to(device)
+    generator.apply(Weight_Initialization.weights_init)
+    return generator
 
 
 def get_3_progan(ngpu, device, nz, ngf, nc):
