@@ -6,8 +6,9 @@ backward is written with other Functions of this file, so that `torch.autograd.g
 R1/R2/WGAN-GP double backward through D runs on explicit dgrad-of-dgrad / wgrad-of-dgrad / mask-scale /
 gate-product kernels, not on ATen's generic double-backward graph.
 
-Ops only needed by the generator (BatchNorm, softmax over branches, modulated conv, noise) are
-once-differentiable: the reference never differentiates G twice.
+Ops only needed by the generator (softmax over branches, modulated conv, noise, the fused BatchNorm+PReLU) are
+once-differentiable: the reference never differentiates G twice.  Plain BatchNorm is twice differentiable (DCGAN / RiR
+critics under R-penalties): its create_graph backward goes through `_bn_composed`.
 """
 from collections import namedtuple
 import math
@@ -703,9 +704,25 @@ def bce_loss(p, t):
 
 
 # =====================================================================================================
-# generator-only ops (once differentiable)
+# generator-only ops (once differentiable; BatchNorm: see _bn_composed)
 # =====================================================================================================
 _sync_bn_hooks = {"stats": None, "grads": None}  # installed by gan_b200.dist for data-parallel sync-BN
+
+
+def _bn_composed(x, gamma, beta, eps, count):
+    """Training-mode BatchNorm written with the twice-differentiable ops of this file (mean, centred second moment,
+    rsqrt, scale, shift).  Only the double backward uses it: when a penalty differentiates a BatchNorm critic
+    (discriminator_2, discriminator_5 under ganR2-style loops) with create_graph=True, BatchNormTrainFn.backward
+    rebuilds the layer from its saved input with this graph and differentiates that — dx then carries the dependence of
+    the batch statistics on x, as ATen's batch_norm double backward does.  No running-stat update here."""
+    mean = ReduceFn.apply(x, None, KN.R_NHW, 1.0 / count)
+    xc = AddBcFn.apply(x, affine(mean, -1.0, 0.0), KN.V_C)
+    var = ReduceFn.apply(xc, xc, KN.R_NHW, 1.0 / count)
+    scale = rsqrt_eps(var, eps)
+    if gamma is not None:
+        scale = MulFn.apply(scale, gamma)
+    y = MulBcFn.apply(xc, scale, KN.V_C)
+    return y if beta is None else AddBcFn.apply(y, beta, KN.V_C)
 
 
 class BatchNormTrainFn(Function):
@@ -724,15 +741,25 @@ class BatchNormTrainFn(Function):
             if _sync_bn_hooks["stats"] is not None:
                 mean, var, count = _sync_bn_hooks["stats"](mean, var, count)
             y, invstd = K().bn_apply(x, mean, var, gamma, beta, running_mean, running_var, eps, momentum, count, nbt)
-        ctx.save_for_backward(x, mean, invstd, gamma)
-        ctx.count = count
+        ctx.save_for_backward(x, mean, invstd, gamma, beta)
+        ctx.count, ctx.eps = count, eps
         return y
 
     @staticmethod
-    @once_differentiable
     def backward(ctx, gy):
-        x, mean, invstd, gamma = ctx.saved_tensors
+        x, mean, invstd, gamma, beta = ctx.saved_tensors
         gy = _c(gy)
+        if torch.is_grad_enabled():  # create_graph=True: this backward will itself be differentiated
+            if _sync_bn_hooks["stats"] is not None or _sync_bn_hooks["grads"] is not None:
+                raise NotImplementedError("double backward through a data-parallel (sync) BatchNorm")
+            wrt = [t for t, need in zip((x, gamma, beta), ctx.needs_input_grad[:3]) if need and t is not None]
+            if not wrt:
+                return (None,) * 8
+            y = _bn_composed(x, gamma, beta, ctx.eps, ctx.count)
+            got = iter(torch.autograd.grad(y, wrt, gy, create_graph=True))
+            gx, gg, gb = (next(got) if (need and t is not None) else None
+                          for t, need in zip((x, gamma, beta), ctx.needs_input_grad[:3]))
+            return gx, gg, gb, None, None, None, None, None
         if ctx.small and _sync_bn_hooks["grads"] is None:
             gx, gg, gb = K().bn_small_bwd(gy, x, mean, invstd, gamma)
             return (gx, (gg if gamma is not None else None), (gb if ctx.needs_input_grad[2] else None), None, None,

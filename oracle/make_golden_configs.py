@@ -57,7 +57,11 @@ CONFIGS = {
                    train="train.wgansn", B=4, names=("G2", "D5_WGANSN")),
     "rir_bce": dict(gen="generators.generator_2", g_args=lambda: (1, 256, 64, 3), g_kw={},
                     dis="discriminators.discriminator_5", d_args=lambda: (), d_kw={},
-                    train="train.gan", B=4, names=("G2", "D5")),  # BatchNorm critic: BCE loop without R-penalties
+                    train="train.gan", B=4, names=("G2", "D5")),
+    # the same BatchNorm critic under R1 + R2: the penalties differentiate 27 BatchNorms twice
+    "rir_r1": dict(gen="generators.generator_2", g_args=lambda: (1, 256, 64, 3), g_kw={},
+                   dis="discriminators.discriminator_5", d_args=lambda: (), d_kw={},
+                   train="train.ganR2", B=4, names=("G2", "D5")),
 }
 
 

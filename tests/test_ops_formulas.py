@@ -128,6 +128,13 @@ def test_batchnorm_and_softmax(ref_backend):
         ref = F.batch_norm(x, rm2, rv2, g, b, True, 0.1, 1e-5)
         assert torch.allclose(y, ref, atol=1e-10) and torch.allclose(rm, rm2) and torch.allclose(rv, rv2)
         assert gradcheck(lambda x, g, b: ops.batch_norm_train(x, g, b, None, None, 1e-5, 0.1), (x, g, b))
+        # twice differentiable (a BatchNorm critic under an R1 / gradient penalty): the create_graph backward re-derives
+        # the layer from differentiable pieces; its first derivative must equal the fused backward's
+        assert gradgradcheck(lambda x, g, b: ops.batch_norm_train(x, g, b, None, None, 1e-5, 0.1), (x, g, b))
+        gy = r(*shape, grad=False)
+        fused = torch.autograd.grad(ops.batch_norm_train(x, g, b, None, None, 1e-5, 0.1), (x, g, b), gy)
+        graph = torch.autograd.grad(ops.batch_norm_train(x, g, b, None, None, 1e-5, 0.1), (x, g, b), gy, create_graph=True)
+        assert all(torch.allclose(u, v, atol=1e-10) for u, v in zip(fused, graph))
         assert torch.allclose(ops.batch_norm_eval(x, g, b, rm, rv, 1e-5), F.batch_norm(x, rm, rv, g, b, False, 0.1, 1e-5), atol=1e-10)
     a = r(3, 2, 5)
     assert torch.allclose(ops.softmax_m(a), torch.softmax(a, 1))
