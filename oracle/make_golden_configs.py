@@ -58,6 +58,10 @@ CONFIGS = {
     "rir_bce": dict(gen="generators.generator_2", g_args=lambda: (1, 256, 64, 3), g_kw={},
                     dis="discriminators.discriminator_5", d_args=lambda: (), d_kw={},
                     train="train.gan", B=4, names=("G2", "D5")),
+    # the StyleGAN2 critic of get_8 (log_resolution 6) under R1 + R2 + GP
+    "style_d": dict(gen="generators.generator_2", g_args=lambda: (1, 256, 64, 3), g_kw={},
+                    dis="discriminators.discriminator_8", d_args=lambda: (6,), d_kw={},
+                    train="train.wgangpR2", B=4, names=("G2", "D8")),
     # the same BatchNorm critic under R1 + R2: the penalties differentiate 27 BatchNorms twice
     "rir_r1": dict(gen="generators.generator_2", g_args=lambda: (1, 256, 64, 3), g_kw={},
                    dis="discriminators.discriminator_5", d_args=lambda: (), d_kw={},

@@ -8,7 +8,7 @@ import math
 
 _CARRIED = ("discriminator_1", "discriminator_2", "discriminator_3_wgangp", "discriminator_3_wgangp_progan",
             "discriminator_3_wgangpsn", "discriminator_5", "discriminator_5_wgangp", "discriminator_5_wgangpsn",
-            "discriminator_7_wgangp", "discriminator_7_wgangpsn", "discriminator_9_4")
+            "discriminator_7_wgangp", "discriminator_7_wgangpsn", "discriminator_8", "discriminator_9_4")
 
 
 def _module(name):
