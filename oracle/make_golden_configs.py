@@ -58,6 +58,10 @@ CONFIGS = {
     "rir_bce": dict(gen="generators.generator_2", g_args=lambda: (1, 256, 64, 3), g_kw={},
                     dis="discriminators.discriminator_5", d_args=lambda: (), d_kw={},
                     train="train.gan", B=4, names=("G2", "D5")),
+    # the dense ShuffleNet-style discriminator of get_4 under the BCE loop with R1 + R2
+    "dense4": dict(gen="generators.generator_2", g_args=lambda: (1, 256, 64, 3), g_kw={},
+                   dis="discriminators.discriminator_4", d_args=lambda: (), d_kw={},
+                   train="train.ganR2", B=4, names=("G2", "D4")),
     # the StyleGAN2 critic of get_8 (log_resolution 6) under R1 + R2 + GP
     "style_d": dict(gen="generators.generator_2", g_args=lambda: (1, 256, 64, 3), g_kw={},
                     dis="discriminators.discriminator_8", d_args=lambda: (6,), d_kw={},

@@ -7,7 +7,7 @@ import importlib
 import math
 
 _CARRIED = ("discriminator_1", "discriminator_2", "discriminator_3_wgangp", "discriminator_3_wgangp_progan",
-            "discriminator_3_wgangpsn", "discriminator_5", "discriminator_5_wgangp", "discriminator_5_wgangpsn",
+            "discriminator_3_wgangpsn", "discriminator_4", "discriminator_5", "discriminator_5_wgangp", "discriminator_5_wgangpsn",
             "discriminator_7_wgangp", "discriminator_7_wgangpsn", "discriminator_8", "discriminator_9_4")
 
 
