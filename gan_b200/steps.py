@@ -12,6 +12,8 @@ sigmoid', gate products, minibatch-stddev second derivative), see gan_b200/ops.p
 Reference lines: train/gan.py:26-53, ganR2.py:19-63, wgan.py:20-49, wgansn.py:17-39, wgansnR2.py:17-52,
 wgangp.py:20-71, wgangpR2.py:17-67, wgangpsnR2.py:22-70, wganlazygp.py:17-70, wganlazygpR2.py:17-77.
 """
+import contextlib
+import os
 from dataclasses import dataclass
 
 import torch
@@ -60,6 +62,25 @@ def lerp_per_sample(x_real, x_fake, eps):
         return ops.add(ops.mul_bc(x_real, one_minus, KN.V_N), ops.mul_bc(x_fake, eps, KN.V_N))
 
 
+@contextlib.contextmanager
+def weights_frozen(module):
+    """No parameter of `module` requires grad inside the block: autograd then skips every wgrad / bias / slope reduction of
+    it and only propagates to its input.  Used for the critic in the generator step, where the reference's backward also
+    fills D.*.grad (ganR2.py:25-26 — SURVEY B9, §8(a) a2: "1 D_f is wasted D-wgrad"): nobody reads those gradients and the
+    next discriminator step zeroes them.  GANB200_G_STEP_D_GRADS=1 keeps the reference's accumulation."""
+    if os.environ.get("GANB200_G_STEP_D_GRADS") == "1":
+        yield
+        return
+    live = [p for p in module.parameters() if p.requires_grad]
+    for p in live:
+        p.requires_grad_(False)
+    try:
+        yield
+    finally:
+        for p in live:
+            p.requires_grad_(True)
+
+
 class StepMixin:
     """Needs: self.generator, self.discriminator, self.optimizer_G/D, self.device, self.nz, self.recipe
     (and self.criterion for the BCE recipes)."""
@@ -102,8 +123,9 @@ class StepMixin:
         self.optimizer_G.zero_grad()
         z = rng.randn(b_size, self.nz, 1, 1, device=self.device)
         gen_imgs = self.generator(z)
-        g_loss = self._d_loss(self.discriminator(gen_imgs), valid_, -1.0)
-        g_loss.backward()
+        with weights_frozen(self.discriminator):
+            g_loss = self._d_loss(self.discriminator(gen_imgs), valid_, -1.0)
+            g_loss.backward()
         self.optimizer_G.step()
         return gen_imgs, g_loss
 
