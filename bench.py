@@ -318,7 +318,9 @@ def run_native(args):
             "config": {"workload": f"generator_13_5+discriminator_9_4 train/{args.loop}.py, batch {B}/GPU, "
                                    f"global batch {B * world}, nz {NZ}", "loop": args.loop, "batch_per_gpu": B,
                        "l2": "per-step working set (activations + 2 GB of parameters) exceeds the 126 MB L2",
-                       "parallelism": f"dp{world}", "cuda_graphs": bool(args.graphs)},
+                       "parallelism": f"dp{world}", "cuda_graphs": bool(args.graphs),
+                       "g_step_critic_wgrad": "computed (as the reference)" if os.environ.get("GANB200_G_STEP_D_GRADS") == "1"
+                       else "skipped: unread by the reference (SURVEY B9); parameters and losses identical"},
             "model_tflops": FLOPS_PER_IMAGE[args.loop] * B * world / (ms * 1e-3) / 1e12 / world,
             "clocks": clk.summary(), "gpu_launches": launches // max(args.steps, 1), "peak_mem_gib": mem_gb,
             "e2e": {"value": B * world / (ms_e2e * 1e-3), "unit": "images/s",
