@@ -131,3 +131,48 @@ def test_dataloader_mirrors_the_reference_pipeline(tmp_path):
     assert len(dl) == 2 and len(batches) == 2 and batches[0][0].shape == (2, 3, 64, 64)   # drop_last
     assert dl.drop_last and type(dl.sampler).__name__ == "RandomSampler"
     assert callable(dataloader.get_MNIST)
+
+
+def test_cached_loader_equals_the_dataset_pipeline_and_shards_quarter_major(tmp_path):
+    """gan_b200.data.CachedImageLoader: every yielded image is the dataset's own pipeline output
+    (un-flipped, or flipped left-right), an epoch visits each kept sample once, drop_last, and two ranks together hold
+    exactly the single-process global batch in quarter-major order."""
+    import numpy as np
+    from PIL import Image
+    from gan_b200.data import CachedImageLoader
+    from gan_b200.dist import shard_quarter_major
+    from units import dataloader
+    root = tmp_path / "imgs" / "cls"
+    root.mkdir(parents=True)
+    rs = np.random.RandomState(1)
+    for i in range(19):
+        Image.fromarray(rs.randint(0, 255, (33 + i, 47, 3), dtype=np.uint8)).save(root / f"{i:02d}.png")
+    ds = dataloader.get_dataset(str(tmp_path / "imgs"), size=64)
+    single = CachedImageLoader(ds, 8, seed=3)
+    assert [type(t).__name__ for t in ds.transform.transforms][1] == "RandomHorizontalFlip"  # the dataset is left as it was
+    assert single.flip_p == 0.5 and len(single) == 2 and single.images.shape == (19, 3, 64, 64)
+    plain = [ds.transform.transforms[3](ds.transform.transforms[2](ds.transform.transforms[0](Image.open(p).convert("RGB"))))
+             for p, _ in ds.samples]
+    for i in range(19):
+        assert torch.equal(single.images[i], plain[i])
+    seen, n_flipped = [], 0
+    for x, y in single:
+        assert x.shape == (8, 3, 64, 64) and y.shape == (8,) and int(y.max()) == 0
+        for img in x:
+            hit = [i for i in range(19) if torch.equal(img, plain[i]) or torch.equal(img, plain[i].flip(-1))]
+            assert len(hit) == 1
+            seen.append(hit[0])
+            n_flipped += int(not torch.equal(img, plain[hit[0]]))
+    assert len(seen) == 16 == len(set(seen)) and 0 < n_flipped < 16
+    second = torch.cat([x for x, _ in single])  # a second epoch: new permutation / flips (seed + epoch)
+    first = torch.cat([x for x, _ in CachedImageLoader(ds, 8, seed=3)])
+    assert second.shape == first.shape and not torch.equal(second, first)
+    # two ranks: same permutation and flips, quarter-major slices of each global batch of 8
+    g = CachedImageLoader(ds, 8, seed=3)
+    r0, r1 = (CachedImageLoader(ds, 4, rank=r, world=2, seed=3) for r in (0, 1))
+    for (xg, _), (x0, _), (x1, _) in zip(g, r0, r1):
+        assert torch.equal(x0, shard_quarter_major(xg, 0, 2)) and torch.equal(x1, shard_quarter_major(xg, 1, 2))
+        # the ranks' MiniBatchStdDev rows (x.view(4, -1)) side by side are the global batch's rows
+        assert torch.equal(torch.cat([x0.reshape(4, -1), x1.reshape(4, -1)], 1), xg.reshape(4, -1))
+    with pytest.raises(ValueError):
+        CachedImageLoader(ds, 6, rank=0, world=2)
