@@ -17,6 +17,7 @@ consumed while building the 11 180 parameter tensors are identical).  The arithm
 Channel plan for planes=48 (reference :610-631): 4^2:396 -> 8^2:396 -> 16^2:204 -> 32^2:108 -> 64^2:108 -> rgb.
 """
 import math
+import os
 from typing import Tuple, List
 
 import torch
@@ -197,16 +198,64 @@ class Conv2dWeightModulate(nn.Module):
         self.weight = EqualizedWeight([out_planes, in_planes, kernel_size, kernel_size])
         self.eps = eps
 
+    # filled by StyleBank (below) when GANB200_STYLE_BANK is set; consumed once per forward
+    _style = None
+    _style_ready = None
+
+    def _take_style(self, s: torch.Tensor):
+        style, ready = self._style, self._style_ready
+        if style is None:
+            return self.to_style(s)
+        self._style = self._style_ready = None
+        if ready is not None:  # computed on the bank's side stream
+            cur = torch.cuda.current_stream(style.device)
+            cur.wait_event(ready)
+            style.record_stream(cur)
+        return style
+
     def forward(self, x: torch.Tensor, s: torch.Tensor):
-        style = self.to_style(s)
+        style = self._take_style(s)
         return ops.modulated_conv2d(x, self.weight.raw, style, self.padding, self.weight.gain, self.demodulate,
                                     self.eps)
 
     def fused(self, x, s, ns, slope, layer):
         """modconv (+ noise scale `ns`) (+ PReLU `slope`) as one fused layer (gan_b200.ops.StyleLayerFn)."""
-        style = self.to_style(s)
+        style = self._take_style(s)
         return ops.style_layer(x, self.weight.raw, style, ns, slope, self.padding, self.weight.gain, self.demodulate,
                                self.eps, None, rng.current(), layer)
+
+
+class StyleBank:
+    """The 519 per-layer style vectors `to_style(w)` depend on w alone, not on the feature maps.  With
+    GANB200_STYLE_BANK=1 they are all computed right after the mapping network (GeneratorStart.forward) instead of one by
+    one in front of their convolution: same kernels, same results (`tests/test_style_layer.py`), but the ~2 000 tiny
+    launches form one independent group — in the backward too, where autograd then runs them after the last convolution
+    — which is what a grouped launch or a side stream needs.  GANB200_STYLE_BANK=2 (experimental, GPU only, never timed
+    or run yet) issues the group on a side stream with one event per layer, so that inside a captured graph it becomes a
+    branch parallel to the convolution chain.  Default 0: styles are computed where the reference computes them."""
+
+    def __init__(self, layers):
+        self.layers = list(layers)
+        self.stream = None
+
+    def fill(self, w: torch.Tensor):
+        mode = os.environ.get("GANB200_STYLE_BANK", "0")
+        if mode not in ("1", "2"):
+            return
+        if mode == "2" and w.is_cuda:
+            cur = torch.cuda.current_stream(w.device)
+            if self.stream is None:
+                self.stream = torch.cuda.Stream(device=w.device)
+            self.stream.wait_stream(cur)
+            w.record_stream(self.stream)
+            with torch.cuda.stream(self.stream):
+                for m in self.layers:
+                    m._style = m.to_style(w)
+                    m._style_ready = torch.cuda.Event()
+                    m._style_ready.record(self.stream)
+            return
+        for m in self.layers:
+            m._style = m.to_style(w)
 
 
 class StyleConv(nn.Module):
@@ -501,9 +550,12 @@ class GeneratorStart(nn.Module):
         self.activation = L.PReLU(out_planes)
         self.to_rgb = ToRGB(out_planes, m, 4)
         self.tree = Tree(z_dim, out_planes, in_planes, out_planes // 2, dense_depth, level, block_num, m, 4)
+        self.style_bank = None  # set by Generator.__init__: every modulated conv of the whole generator
 
     def forward(self, x: torch.Tensor):
         w = self.mapping_network(torch.squeeze(x))  # all singleton dims, as the reference (B=1 fails)
+        if self.style_bank is not None:
+            self.style_bank.fill(w)
         x = self.activation(self.bn(self.convT(x)))
         rgb = self.to_rgb(x)
         x, rgb = self.tree(x, w, rgb)
@@ -524,6 +576,7 @@ class Generator(nn.Module):
             self.__setattr__('block%d' % idx, blk)
         for i, m in enumerate(mod for mod in self.modules() if isinstance(mod, StyleConv)):
             m.noise_layer = i + 1
+        self.block0.style_bank = StyleBank(mod for mod in self.modules() if isinstance(mod, Conv2dWeightModulate))
 
     def forward(self, x: torch.Tensor):
         if rng.philox_noise():

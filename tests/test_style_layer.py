@@ -1,6 +1,7 @@
 """CPU, float64: the fused StyleConv layer (gan_b200.ops.StyleLayerFn: modconv + in-kernel noise + PReLU, 2 saved
 activations) against the unfused composition (modulated_conv2d -> noise_add -> prelu) fed the same noise, forward
 and every gradient; then the whole generator_13_5 in fused vs unfused mode."""
+import os
 import random
 
 import numpy as np
@@ -48,6 +49,7 @@ def test_generator_fused_equals_unfused_noise_path(ref_backend):
     for mode in ("philox", "philox_unfused"):
         prev = rng.noise_mode(mode)
         rng._states.clear()
+        os.environ["GANB200_STYLE_BANK"] = "1" if mode == "philox" else "0"  # the fused leg also runs banked styles
         try:
             torch.manual_seed(0); np.random.seed(0); random.seed(0)
             G = generator_13_5.Generator(256)
@@ -58,6 +60,7 @@ def test_generator_fused_equals_unfused_noise_path(ref_backend):
             res[mode] = (img.detach(), {n: p.grad for n, p in G.named_parameters()})
         finally:
             rng.noise_mode(prev)
+            os.environ.pop("GANB200_STYLE_BANK", None)
     a, b = res["philox"], res["philox_unfused"]
     assert float((a[0] - b[0]).norm() / b[0].norm()) < 1e-4
     worst = 0.0
@@ -67,3 +70,23 @@ def test_generator_fused_equals_unfused_noise_path(ref_backend):
         if gb is not None and gb.norm() > 1e-4:  # biases feeding a BatchNorm have zero gradient: rounding noise
             worst = max(worst, float((ga - gb).norm() / gb.norm()))
     assert worst < 5e-2, worst  # fp32, ~100 layers and B=4 batch norms: see tests/test_golden_final_pair.py
+
+
+def test_style_bank_is_the_same_computation(ref_backend, monkeypatch):
+    """GANB200_STYLE_BANK=1: every to_style(w) evaluated right after the mapping network instead of in front of its
+    convolution — the image is bit-identical (same kernels on the same operands).  Gradients with the bank on are covered
+    by test_generator_fused_equals_unfused_noise_path, whose fused leg runs banked."""
+    from generators import generator_13_5
+    torch.manual_seed(0); np.random.seed(0); random.seed(0)
+    G = generator_13_5.Generator(256)
+    assert len(G.block0.style_bank.layers) == 519
+    z = torch.randn(2, 256, 1, 1)
+    out = {}
+    for bank in ("0", "1"):
+        monkeypatch.setenv("GANB200_STYLE_BANK", bank)
+        rng._states.clear()
+        torch.manual_seed(1)
+        with torch.no_grad():
+            out[bank] = G(z)  # train mode: batch statistics, so the second pass sees the same arithmetic
+        assert all(m._style is None for m in G.block0.style_bank.layers)  # every banked style was consumed
+    assert torch.equal(out["0"], out["1"])
