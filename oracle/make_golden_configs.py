@@ -66,6 +66,17 @@ CONFIGS = {
     "style_d": dict(gen="generators.generator_2", g_args=lambda: (1, 256, 64, 3), g_kw={},
                     dis="discriminators.discriminator_8", d_args=lambda: (6,), d_kw={},
                     train="train.wgangpR2", B=4, names=("G2", "D8")),
+    # the remaining loops of SURVEY §8(a) a1 / a7: the lazy-penalty variants (idx 0: penalties on and scaled by 5, idx 1: off)
+    # and weight clipping (train/wgan.py:47-48; the StyleGAN2 critic's N(0,1) weights make the clamp bite)
+    "lazy": dict(gen="generators.generator_2", g_args=lambda: (1, 256, 64, 3), g_kw={},
+                 dis="discriminators.discriminator_3_wgangp", d_args=lambda: (1, 64, 3), d_kw={},
+                 train="train.wganlazygp", B=4, names=("G2", "D3_WGAN"), d_idx=(0, 1)),
+    "lazy_r2": dict(gen="generators.generator_2", g_args=lambda: (1, 256, 64, 3), g_kw={},
+                    dis="discriminators.discriminator_8", d_args=lambda: (6,), d_kw={},
+                    train="train.wganlazygpR2", B=4, names=("G2", "D8"), d_idx=(0, 1)),
+    "clip": dict(gen="generators.generator_2", g_args=lambda: (1, 256, 64, 3), g_kw={},
+                 dis="discriminators.discriminator_8", d_args=lambda: (6,), d_kw={},
+                 train="train.wgan", B=4, names=("G2", "D8")),
     # the same BatchNorm critic under R1 + R2: the penalties differentiate 27 BatchNorms twice
     "rir_r1": dict(gen="generators.generator_2", g_args=lambda: (1, 256, 64, 3), g_kw={},
                    dis="discriminators.discriminator_5", d_args=lambda: (), d_kw={},
@@ -130,7 +141,13 @@ def replay(cfg, genmod, dismod, trainmod, device=torch.device("cpu"), x=None, z=
     g0, d0 = snapshot(G), snapshot(D)
     seed_all(1)
     xi = xd.clone().requires_grad_()
-    d_ret = T.discriminator_trainstep(xi, B)
+    if cfg.get("d_idx"):  # lazy loops: one critic step per idx value, losses concatenated
+        d_ret = []
+        for idx in cfg["d_idx"]:
+            xi.grad = None
+            d_ret += list(T.discriminator_trainstep(xi, B, idx))
+    else:
+        d_ret = T.discriminator_trainstep(xi, B)
     out["step_d_losses"] = [float(v.detach()) for v in d_ret]
     gen_imgs, g_loss = T.generator_trainstep(B)
     out["step_g_loss"] = float(g_loss.detach())

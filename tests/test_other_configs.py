@@ -25,8 +25,9 @@ NOISE_PARAMS["rir_r1"] = NOISE_PARAMS["rir_bce"]
 # terms cancel on them up to the LeakyReLU masks and what is left (~1e-9 per element, gradient penalty included) is at
 # Adam's eps: update norms 0.0013 / 0.0024 here / in the reference against 0.009 for a full sign step.
 NOISE_PARAMS["style_d"] = re.compile(r"^blocks\.3\.(residual\.1|block\.2)\.bias$")
-NOISE_IN_D = ("rir_bce", "rir_r1", "style_d")
-ZOO = ["dcgan", "sn3", "shuffle", "rir_gp", "rir_sn", "rir_bce", "rir_r1", "style_d", "dense4"]  # SURVEY §8(f) rank 3 pairs (make_golden_configs.py)
+NOISE_PARAMS["lazy_r2"] = NOISE_PARAMS["clip"] = NOISE_PARAMS["style_d"]  # the same critic
+NOISE_IN_D = ("rir_bce", "rir_r1", "style_d", "lazy_r2", "clip")
+ZOO = ["dcgan", "sn3", "shuffle", "rir_gp", "rir_sn", "rir_bce", "rir_r1", "style_d", "dense4", "lazy", "lazy_r2", "clip"]  # SURVEY §8(f) rank 3 pairs (make_golden_configs.py)
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 
