@@ -176,3 +176,40 @@ def test_every_reference_class_path_exists_in_the_drop_in():
             classes = [n.name for n in ast.parse(f.read()).body if isinstance(n, ast.ClassDef)]
         ours = importlib.import_module(pkg + "." + mod)
         assert [c for c in classes if not isinstance(getattr(ours, c, None), type)] == [], (pkg, mod)
+
+
+def test_train_loop_side_effects_and_resume(ref_backend, tmp_path, monkeypatch):
+    """Train.train() of the drop-in loops (reference train/wgangp.py:73-96, wgan.py:51-75, wganlazygp.py:72-103): image
+    grid every 10 iterations, a checkpoint per epoch under the reference's file name, records every 30 iterations for
+    the lazy loops, wgan's NameError after its first iteration — and a second run resuming from the file."""
+    from train import wgan, wganlazygp, wgangp
+    monkeypatch.chdir(tmp_path)
+    os.makedirs("generated_images")
+    gen = torch.Generator().manual_seed(0)
+    batches = [(torch.randn(4, 3, 64, 64, generator=gen).clamp_(-1, 1), torch.zeros(4)) for _ in range(2)]
+    G, D = small_pair()
+    T = wgangp.Train(batches, torch.device("cpu"), 1, 16, G, "G3_PROGAN", D, "D3_WGAN_PROGAN")
+    before = [p.detach().clone() for p in G.parameters()]
+    T.train()
+    assert any(not torch.equal(a, b) for a, b in zip(before, G.parameters()))
+    assert os.path.isfile("generated_images/0-0.png") or os.path.isfile("generated_images/0-0.pt")
+    name = "G3_PROGAN D3_WGAN_PROGAN WGANGP epoch_1 i_0_ckpt"
+    assert os.path.isfile(os.path.join("checkpoint", name + ".pth"))
+    G2, D2 = small_pair()
+    T2 = wgangp.Train(batches, torch.device("cpu"), 1, 16, G2, "G3_PROGAN", D2, "D3_WGAN_PROGAN")
+    T2.load_generator_ckpt(name)
+    T2.load_discriminator_ckpt(name)
+    assert T2.epoch == 1 and T2.i == 0
+    for a, b in zip(T2.generator.state_dict().values(), G.state_dict().values()):
+        assert torch.equal(a, b)
+    # lazy loop: records at i % 30 == 0 go to memory and to <file>.txt
+    G3, D3 = small_pair()
+    T3 = wganlazygp.Train(batches, torch.device("cpu"), 1, 16, G3, "g", D3, "d")
+    T3.train()
+    assert len(T3.record["Generator loss"]) == 1 and os.path.isfile("wganlazygp.txt")
+    # wgan: the reference's loop reads an undefined `gp` right after the first iteration
+    G4, D4 = small_pair()
+    T4 = wgan.Train(batches, torch.device("cpu"), 1, 16, G4, "g", D4, "d")
+    with pytest.raises(NameError):
+        T4.train()
+    assert all(float(p.detach().abs().max()) <= 1.0 for p in D4.parameters())  # the critic was clipped before the crash
