@@ -124,7 +124,10 @@ def depthwise_conv2d(x, w, bias=None, stride=1, pad=1, alpha=1.0):
 
 
 def linear(x, w, bias=None, alpha=1.0, engine=None):
-    """x:(B,in) w:(out,in) — a 1x1 conv on a 1x1 map."""
+    """x:(B,in) w:(out,in) — a 1x1 conv on a 1x1 map.  A 1-D x is one row, as in F.linear (the reference reaches that
+    with a batch of one: torch.squeeze drops the batch dimension and the next BatchNorm1d rejects the input)."""
+    if x.dim() == 1:
+        return linear(x.reshape(1, -1), w, bias, alpha, engine).reshape(-1)
     B = x.shape[0]
     y = Conv2dFn.apply(x.reshape(B, -1, 1, 1), w.reshape(w.shape[0], w.shape[1], 1, 1), bias,
                        ConvCfg(1, 0, 0, float(alpha), engine))
