@@ -109,6 +109,35 @@ class AdaptiveAvgPool2d(nn.AdaptiveAvgPool2d):
         return ops.adaptive_avg_pool(x, out)
 
 
+class AvgPool2d(nn.AvgPool2d):
+    """nn.AvgPool2d(k) with the default stride (= k), no padding — the SE squeeze of the tree generators / critics
+    (generators/generator_7.py:19, discriminators/discriminator_6_wgangp.py:18)."""
+
+    def forward(self, x):
+        k = self.kernel_size if isinstance(self.kernel_size, int) else self.kernel_size[0]
+        assert self.padding in (0, (0, 0)) and self.stride in (k, (k, k))
+        return ops.avg_pool(x, k)
+
+
+class InstanceNorm2d(nn.InstanceNorm2d):
+    """nn.InstanceNorm2d (affine / track_running_stats as constructed) — generators/generator_4.py, generator_5.py."""
+
+    def forward(self, x):
+        self._check_input_dim(x)
+        use_input = self.training or not self.track_running_stats
+        track = self.training and self.track_running_stats  # (torch does not advance num_batches_tracked here)
+        return ops.instance_norm(x, self.weight, self.bias, self.running_mean if (track or not use_input) else None,
+                                 self.running_var if (track or not use_input) else None, self.eps,
+                                 0.0 if self.momentum is None else self.momentum, use_input)
+
+
+class ReflectionPad2d(nn.ReflectionPad2d):
+    def forward(self, x):
+        p = self.padding if isinstance(self.padding, int) else self.padding[0]
+        assert isinstance(self.padding, int) or len(set(self.padding)) == 1, "same padding on all four sides"
+        return ops.reflect_pad(x, p)
+
+
 class BicubicUp2(nn.Upsample):
     """nn.Upsample(scale_factor=2, mode='bicubic', align_corners=False) — generator_13_5.py:160."""
 
@@ -132,11 +161,17 @@ class Conv2d(nn.Conv2d):
     (discriminator_7_wgangpsn.py:55)."""
 
     def forward(self, x):
-        assert self.dilation[0] == 1 and self.padding_mode == 'zeros'
+        assert self.dilation[0] == 1 and self.padding_mode in ('zeros', 'reflect', 'replicate')
+        pad, mode = self.padding[0], 0
+        if self.padding_mode == 'reflect' and pad:   # mirror first (a separable gather), then an unpadded conv
+            x, pad = ops.reflect_pad(x, pad), 0
+        elif self.padding_mode == 'replicate':
+            mode = 1                                  # an index clamp inside the conv kernel
         if self.groups == 1:
-            return ops.conv2d(x, self.weight, self.bias, self.stride[0], self.padding[0], 0)
+            return ops.conv2d(x, self.weight, self.bias, self.stride[0], pad, mode)
         assert self.groups == self.in_channels == self.out_channels, "grouped convs: depthwise only"
-        return ops.depthwise_conv2d(x, self.weight, self.bias, self.stride[0], self.padding[0])
+        assert mode == 0, "depthwise: zero or reflect padding"
+        return ops.depthwise_conv2d(x, self.weight, self.bias, self.stride[0], pad)
 
 
 class Linear(nn.Linear):

@@ -575,6 +575,21 @@ def bicubic_resize(x, out_h, out_w, scale=None):
     return Resample2dFn.apply(x, RS.bicubic(x.shape[-2], out_h, scale), RS.bicubic(x.shape[-1], out_w, scale))
 
 
+def reflect_pad(x, p):
+    """ReflectionPad2d(p) as a separable gather (one tap per output sample; the adjoint scatters with up to two)."""
+    if p == 0:
+        return x
+    return Resample2dFn.apply(x, RS.reflect_pad(x.shape[-2], p), RS.reflect_pad(x.shape[-1], p))
+
+
+def avg_pool(x, k):
+    """nn.AvgPool2d(k) / F.avg_pool2d(x, k) with stride k on maps whose sides are multiples of k."""
+    h, w = x.shape[-2:]
+    if h % k or w % k:
+        raise NotImplementedError("avg_pool: sides must be multiples of the kernel")
+    return Resample2dFn.apply(x, RS.adaptive_avg(h, h // k), RS.adaptive_avg(w, w // k))
+
+
 def adaptive_avg_pool(x, out):
     return Resample2dFn.apply(x, RS.adaptive_avg(x.shape[-2], out), RS.adaptive_avg(x.shape[-1], out))
 
@@ -815,6 +830,33 @@ def batch_norm_train(x, gamma, beta, running_mean, running_var, eps, momentum, n
     return BatchNormTrainFn.apply(x, gamma, beta, running_mean, running_var, eps, momentum, nbt)
 
 
+def instance_norm(x, gamma, beta, running_mean, running_var, eps, momentum, use_input_stats=True):
+    """F.instance_norm semantics (nn.InstanceNorm2d, e.g. generators/generator_4.py:29-86): statistics per (sample,
+    channel) over H*W, biased variance for the normalisation; with running buffers the batch-mean of the instance means
+    and of the UNBIASED instance variances is blended in with `momentum`.  Composed of the twice-differentiable reduce /
+    broadcast kernels (no dedicated kernel: these layers are off the BASELINE path)."""
+    if not use_input_stats:
+        return batch_norm_eval(x, gamma, beta, running_mean, running_var, eps)
+    n, c = x.shape[:2]
+    hw = x.numel() // (n * c)
+    mean = ReduceFn.apply(x, None, KN.R_HW, 1.0 / hw)                     # (N, C)
+    xc = AddBcFn.apply(x, affine(mean, -1.0, 0.0), KN.V_NC)
+    var = ReduceFn.apply(xc, xc, KN.R_HW, 1.0 / hw)
+    y = MulBcFn.apply(xc, rsqrt_eps(var, eps), KN.V_NC)
+    if running_mean is not None:
+        with torch.no_grad():
+            unbiased = hw / max(hw - 1.0, 1.0)
+            rm = ReduceFn.apply(mean.reshape(n, c, 1), None, KN.R_NHW, 1.0 / n)
+            rv = ReduceFn.apply(var.reshape(n, c, 1), None, KN.R_NHW, unbiased / n)
+            running_mean.copy_(add(affine(running_mean, 1.0 - momentum, 0.0), affine(rm, momentum, 0.0)))
+            running_var.copy_(add(affine(running_var, 1.0 - momentum, 0.0), affine(rv, momentum, 0.0)))
+    if gamma is not None:
+        y = MulBcFn.apply(y, gamma, KN.V_C)
+    if beta is not None:
+        y = AddBcFn.apply(y, beta, KN.V_C)
+    return y
+
+
 def batch_norm_eval(x, gamma, beta, running_mean, running_var, eps):
     scale = rsqrt_eps(running_var, eps)
     if gamma is not None:
@@ -835,10 +877,20 @@ class SoftmaxMFn(Function):
         return y
 
     @staticmethod
-    @once_differentiable
     def backward(ctx, gy):
         (y,) = ctx.saved_tensors
-        return K().softmax_m_bwd(_c(gy), y)
+        if not torch.is_grad_enabled():  # plain first-order backward: one kernel
+            return K().softmax_m_bwd(_c(gy), y)
+        # create_graph (a selective-kernel attention inside a critic under an R-penalty, discriminator_9_small.py:112):
+        # gx_m = y_m * (g_m - sum_j g_j y_j), written with differentiable ops on the saved OUTPUT, whose own graph leads
+        # back through this Function — so any order of differentiation works
+        M = y.shape[1]
+        parts = [(slice_channels(gy, m, m + 1), slice_channels(y, m, m + 1)) for m in range(M)]
+        dot = None
+        for g_m, y_m in parts:
+            t = MulFn.apply(g_m, y_m)
+            dot = t if dot is None else AddFn.apply(dot, t)
+        return cat_channels([MulFn.apply(y_m, SubFn.apply(g_m, dot)) for g_m, y_m in parts])
 
 
 def softmax_m(x):

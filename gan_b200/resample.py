@@ -74,6 +74,19 @@ def replicate_pad(n, p):
 
 
 @functools.lru_cache(maxsize=None)
+def reflect_pad(n, p):
+    """padding_mode='reflect' of nn.Conv2d / nn.ReflectionPad2d: the border is mirrored WITHOUT repeating the edge sample
+    (generators/generator_7.py:13-14, discriminators/discriminator_6_wgangp.py:12-13)."""
+    assert 0 <= p < n, "reflect padding needs pad < size"
+    m = np.zeros((n + 2 * p, n))
+    for o in range(n + 2 * p):
+        i = o - p
+        i = -i if i < 0 else (2 * (n - 1) - i if i > n - 1 else i)
+        m[o, i] = 1.0
+    return LinOp1d(m, f"reflect{p}_{n}")
+
+
+@functools.lru_cache(maxsize=None)
 def smooth3(n):
     """[1,2,1]/4 with replicate padding (the 2-D kernel [[1,2,1],[2,4,2],[1,2,1]]/16 is its outer product)."""
     m = np.zeros((n, n))

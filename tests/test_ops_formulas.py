@@ -276,3 +276,45 @@ def test_spectral_norm_module_matches_torch(ref_backend):
         assert torch.allclose(a.parametrizations.weight.original.grad, b.parametrizations.weight.original.grad,
                               rtol=1e-4, atol=1e-5)
         assert torch.allclose(a.bias.grad, b.bias.grad, rtol=1e-4, atol=1e-5)
+
+
+def test_second_wave_layers_match_torch(ref_backend):
+    """Building blocks of the models outside the BASELINE configs, composed of existing kernels:
+    reflect padding (also as Conv2d(padding_mode='reflect')), AvgPool2d, InstanceNorm2d with affine parameters and
+    running statistics, and the twice-differentiable softmax over branches — against torch in float64."""
+    from gan_b200 import layers as L
+    x = r(2, 3, 6, 8)
+    assert torch.equal(ops.reflect_pad(x, 2), F.pad(x, (2, 2, 2, 2), mode="reflect"))
+    assert gradcheck(lambda t: ops.reflect_pad(t, 2), (x,)) and gradgradcheck(lambda t: ops.reflect_pad(t, 2), (x,))
+    assert torch.allclose(ops.avg_pool(x, 2), F.avg_pool2d(x, 2)) and gradcheck(lambda t: ops.avg_pool(t, 2), (x,))
+    torch.manual_seed(0)
+    for mode in ("reflect", "replicate", "zeros"):
+        ours, ref = L.Conv2d(3, 4, 5, padding=2, padding_mode=mode).double(), None
+        ref = torch.nn.Conv2d(3, 4, 5, padding=2, padding_mode=mode).double()
+        ref.load_state_dict(ours.state_dict())
+        assert torch.allclose(ours(x), ref(x), atol=1e-10), mode
+    pool = L.AvgPool2d(kernel_size=2)
+    assert torch.allclose(pool(x), F.avg_pool2d(x, 2))
+    # InstanceNorm2d: affine + running statistics, train and eval
+    ours, ref = L.InstanceNorm2d(3, affine=True, track_running_stats=True).double(), None
+    ref = torch.nn.InstanceNorm2d(3, affine=True, track_running_stats=True).double()
+    with torch.no_grad():
+        ours.weight.copy_(torch.rand(3) + 0.5); ours.bias.copy_(torch.randn(3))
+    ref.load_state_dict(ours.state_dict())
+    for _ in range(2):
+        assert torch.allclose(ours(x), ref(x), atol=1e-10)
+    assert torch.allclose(ours.running_mean, ref.running_mean) and torch.allclose(ours.running_var, ref.running_var)
+    ours.eval(); ref.eval()
+    assert torch.allclose(ours(x), ref(x), atol=1e-10)
+    plain = L.InstanceNorm2d(3).double()  # the defaults: no affine, no running statistics
+    assert torch.allclose(plain(x), F.instance_norm(x), atol=1e-10)
+    g, b = r(3), r(3)
+    f = lambda x, g, b: ops.instance_norm(x, g, b, None, None, 1e-5, 0.1)
+    assert gradcheck(f, (x, g, b)) and gradgradcheck(f, (x, g, b))
+    # softmax over the branch dimension, differentiated twice
+    a = r(3, 2, 5)
+    assert gradgradcheck(ops.softmax_m, (a,))
+    gy = r(3, 2, 5, grad=False)
+    one = torch.autograd.grad(ops.softmax_m(a), a, gy)[0]
+    two = torch.autograd.grad(ops.softmax_m(a), a, gy, create_graph=True)[0]
+    assert torch.allclose(one, two, atol=1e-12)
