@@ -727,15 +727,24 @@ def bce_loss(p, t):
 _sync_bn_hooks = {"stats": None, "grads": None}  # installed by gan_b200.dist for data-parallel sync-BN
 
 
-def _bn_composed(x, gamma, beta, eps, count):
+def _bn_composed(x, gamma, beta, eps, rank_mean=None):
     """Training-mode BatchNorm written with the twice-differentiable ops of this file (mean, centred second moment,
     rsqrt, scale, shift).  Only the double backward uses it: when a penalty differentiates a BatchNorm critic
     (discriminator_2, discriminator_5 under ganR2-style loops) with create_graph=True, BatchNormTrainFn.backward
     rebuilds the layer from its saved input with this graph and differentiates that — dx then carries the dependence of
-    the batch statistics on x, as ATen's batch_norm double backward does.  No running-stat update here."""
+    the batch statistics on x, as ATen's batch_norm double backward does.  No running-stat update here.
+    Data parallel (sync-BN): `rank_mean` is the differentiable mean over ranks (gan_b200.dist.AllReduceMeanFn); with equal
+    shards the global mean is the mean of the local means and the global variance the mean of the local second moments
+    about the GLOBAL mean, and the adjoints of those two exchanges carry the cross-rank terms of dx."""
+    n, _, hw = KN._nchw(x)
+    count = n * hw
     mean = ReduceFn.apply(x, None, KN.R_NHW, 1.0 / count)
+    if rank_mean is not None:
+        mean = rank_mean(mean)
     xc = AddBcFn.apply(x, affine(mean, -1.0, 0.0), KN.V_C)
     var = ReduceFn.apply(xc, xc, KN.R_NHW, 1.0 / count)
+    if rank_mean is not None:
+        var = rank_mean(var)
     scale = rsqrt_eps(var, eps)
     if gamma is not None:
         scale = MulFn.apply(scale, gamma)
@@ -768,12 +777,13 @@ class BatchNormTrainFn(Function):
         x, mean, invstd, gamma, beta = ctx.saved_tensors
         gy = _c(gy)
         if torch.is_grad_enabled():  # create_graph=True: this backward will itself be differentiated
-            if _sync_bn_hooks["stats"] is not None or _sync_bn_hooks["grads"] is not None:
-                raise NotImplementedError("double backward through a data-parallel (sync) BatchNorm")
+            synced = _sync_bn_hooks["stats"] is not None
+            if synced and _mbstd_reduce[0] is None:
+                raise NotImplementedError("double backward through a sync BatchNorm needs gan_b200.dist's rank mean")
             wrt = [t for t, need in zip((x, gamma, beta), ctx.needs_input_grad[:3]) if need and t is not None]
             if not wrt:
                 return (None,) * 8
-            y = _bn_composed(x, gamma, beta, ctx.eps, ctx.count)
+            y = _bn_composed(x, gamma, beta, ctx.eps, _mbstd_reduce[0] if synced else None)
             got = iter(torch.autograd.grad(y, wrt, gy, create_graph=True))
             gx, gg, gb = (next(got) if (need and t is not None) else None
                           for t, need in zip((x, gamma, beta), ctx.needs_input_grad[:3]))

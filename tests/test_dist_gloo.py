@@ -1,7 +1,8 @@
 """CPU, gloo, world_size 2: the data-parallel exchanges of gan_b200.dist make 2 ranks x B/2 images compute the
 gradients and the Adam update a single rank computes on B images: gradient all-reduce (1/N folded into
-the fused Adam grad_scale), sync-BN statistics forward and backward, the global MiniBatchStdDev scalar and its adjoint
-(including through the R1 double backward), quarter-major batch sharding."""
+the fused Adam grad_scale), sync-BN statistics forward and backward (in G, and in the critic — there also through the
+R1 / R2 / GP double backward), the global MiniBatchStdDev scalar and its adjoint (including through the double
+backward), quarter-major batch sharding."""
 import os
 import sys
 
@@ -13,7 +14,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 def _build():
-    """a miniature G (linear+BN1d+PReLU -> convT -> BN2d) and D (conv+PReLU -> mbstd -> conv -> linear) on our layers"""
+    """a miniature G (linear+BN1d+PReLU -> convT -> BN2d) and D (conv+PReLU -> BN2d -> mbstd -> conv -> linear) on our layers"""
     import torch.nn as nn
     from gan_b200 import layers as L
     from gan_b200 import ops
@@ -50,11 +51,12 @@ def _build():
         def __init__(self):
             super().__init__()
             self.c1, self.a1 = EqConv(3, 6, 3, 1), L.PReLU(6)
+            self.bn = L.BatchNorm2d(6)  # a BatchNorm critic: sync statistics, also through the penalties' double backward
             self.c2, self.a2 = EqConv(7, 4, 3, 1, 2), L.PReLU(4)
             self.fc = EqLin(4 * 2 * 2, 1)
 
         def forward(self, x):
-            t = self.a1(self.c1(x))
+            t = self.bn(self.a1(self.c1(x)))
             t = ops.minibatch_stddev(t, 4, 1e-8)
             t = self.a2(self.c2(t))
             return self.fc(t.reshape(t.shape[0], -1))
