@@ -685,6 +685,17 @@ def batch_stddev(x, eps=10e-8):
     b, _, h, w = x.shape
     if b < 2:  # var over a single sample is 0 -> sqrt(eps); no gradient path in the reference either (d/dx of 0)
         raise ValueError("batch_stddev needs a batch of at least 2")
+    if _mbstd_reduce[0] is not None:
+        # data parallel: the statistic runs over the GLOBAL batch.  Per-position mean and second moment about the global
+        # mean, each averaged over (equal) ranks by the self-adjoint rank mean, from twice-differentiable pieces.
+        rank_mean = _mbstd_reduce[0]
+        x3 = x.reshape(b, -1, 1)
+        mu = rank_mean(ReduceFn.apply(x3, None, KN.R_NHW, 1.0 / b))
+        xc = AddBcFn.apply(x3, affine(mu, -1.0, 0.0), KN.V_C)
+        var = rank_mean(ReduceFn.apply(xc, xc, KN.R_NHW, 1.0 / b))
+        s = mean(sqrt(affine(var, 1.0, eps))).reshape(1)
+        plane = AddBcFn.apply(torch.zeros((b, 1, h, w), dtype=x.dtype, device=x.device), s, KN.V_SCALAR)
+        return cat_channels([x, plane])
     s = MbStdFn.apply(x, b, eps * b / (b - 1.0))
     s = affine(s, math.sqrt((b - 1.0) / b), 0.0)
     plane = AddBcFn.apply(torch.zeros((b, 1, h, w), dtype=x.dtype, device=x.device), s, KN.V_SCALAR)

@@ -14,7 +14,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 def _build():
-    """a miniature G (linear+BN1d+PReLU -> convT -> BN2d) and D (conv+PReLU -> BN2d -> mbstd -> conv -> linear) on our layers"""
+    """a miniature G (linear+BN1d+PReLU -> convT -> BN2d) and D (conv+PReLU -> BN2d -> mbstd -> batch-std -> conv -> linear) on our layers"""
     import torch.nn as nn
     from gan_b200 import layers as L
     from gan_b200 import ops
@@ -52,12 +52,13 @@ def _build():
             super().__init__()
             self.c1, self.a1 = EqConv(3, 6, 3, 1), L.PReLU(6)
             self.bn = L.BatchNorm2d(6)  # a BatchNorm critic: sync statistics, also through the penalties' double backward
-            self.c2, self.a2 = EqConv(7, 4, 3, 1, 2), L.PReLU(4)
+            self.c2, self.a2 = EqConv(8, 4, 3, 1, 2), L.PReLU(4)
             self.fc = EqLin(4 * 2 * 2, 1)
 
         def forward(self, x):
             t = self.bn(self.a1(self.c1(x)))
             t = ops.minibatch_stddev(t, 4, 1e-8)
+            t = ops.batch_stddev(t)  # the ProGAN per-position batch statistic (discriminator_3_wgangp_progan.py:7-16)
             t = self.a2(self.c2(t))
             return self.fc(t.reshape(t.shape[0], -1))
 
