@@ -64,6 +64,7 @@ SIGNATURES = {
     "ganb200_mbstd_bwd": (c_int, [P, P, P, c_int, c_int64, c_float, P]),
     "ganb200_mbstd_bwd_bwd": (c_int, [P, P, P, P, P, c_int, c_int64, c_float, P]),
     "ganb200_bce_fwd": (c_int, [P, P, P, P, c_int64, P]),
+    "ganb200_bce_fwd_sticky": (c_int, [P, P, P, P, c_int64, P]),
     "ganb200_bce_bwd": (c_int, [P, P, P, P, c_int64, P]),
     "ganb200_multi_tensor_adam_blocks": (c_int, [P, P, c_int, c_int64, c_float, c_float, c_float, c_float, c_float,
                                                  c_int, c_int64, P, c_float, P]),

@@ -871,6 +871,18 @@ extern "C" int ganb200_bce_fwd(const float* p, const float* t, float* out, int* 
   GB_CHECK_LAUNCH();
   return 0;
 }
+extern "C" int ganb200_bce_fwd_sticky(const float* p, const float* t, float* out, int* sticky_flag, int64_t n,
+                                      void* stream) {
+  // as ganb200_bce_fwd, but the flag is only ever SET (never cleared): inside a replayed CUDA graph the host cannot read a
+  // per-call flag, so the caller keeps one flag per device, polls it between replays and clears it itself
+  cudaStream_t s = (cudaStream_t)stream;
+  GB_REQUIRE(n > 0, GANB200_BAD_SHAPE, "bce: empty");
+  GB_REQUIRE(sticky_flag != nullptr, GANB200_BAD_ARG, "bce_fwd_sticky: null flag");
+  GB_CHECK_CUDA(cudaMemsetAsync(out, 0, sizeof(float), s));
+  bce_fwd_kernel<<<ew_grid(n, 256, 4), 256, 0, s>>>(p, t, out, sticky_flag, n);
+  GB_CHECK_LAUNCH();
+  return 0;
+}
 extern "C" int ganb200_bce_bwd(const float* g, const float* p, const float* t, float* gp, int64_t n, void* stream) {
   bce_bwd_kernel<<<ew_grid(n, 256, 4), 256, 0, (cudaStream_t)stream>>>(g, p, t, gp, n);
   GB_CHECK_LAUNCH();

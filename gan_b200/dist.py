@@ -23,6 +23,7 @@ from torch.autograd import Function
 from . import ops
 
 BUCKET_BYTES = 256 << 20  # NVSwitch: size buckets for launch latency / overlap, not for link count
+CALLS = [0]               # collective calls issued by this process (bench.py: nccl_calls_per_step)
 
 
 def init_from_env(backend=None):
@@ -48,6 +49,7 @@ class AllReduceMeanFn(Function):
     def forward(ctx, x, group):
         ctx.group = group
         y = x.detach().clone()
+        CALLS[0] += 1
         dist.all_reduce(y, op=dist.ReduceOp.SUM, group=group)
         return ops.affine(y, 1.0 / dist.get_world_size(group), 0.0)
 
@@ -100,6 +102,7 @@ class GradSync:
 
     def _launch(self, grads):
         flat = torch.cat([g.reshape(-1) for g in grads])
+        CALLS[0] += 1
         work = dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
         return flat, grads, work
 
@@ -125,6 +128,7 @@ class DataParallelStep:
             def stats(mean, var, count):
                 # combine (mean, biased var) of equal-sized shards: var_g = E[var] + E[mean^2] - E[mean]^2
                 pack = torch.stack([mean, var + mean * mean])
+                CALLS[0] += 1
                 dist.all_reduce(pack, op=dist.ReduceOp.SUM, group=group)
                 pack /= world
                 m = pack[0].contiguous()
@@ -132,6 +136,7 @@ class DataParallelStep:
 
             def grads(s1, s2):
                 pack = torch.stack([s1, s2])
+                CALLS[0] += 1
                 dist.all_reduce(pack, op=dist.ReduceOp.SUM, group=group)
                 return pack[0].contiguous(), pack[1].contiguous()
 

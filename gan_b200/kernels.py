@@ -416,9 +416,14 @@ class CudaBackend:
                                                   self._p(out_gx), G, x.numel() // G, eps, st))
         return out_gg, out_gx
 
-    def bce_fwd(self, p, t):
+    def bce_fwd(self, p, t, sticky=None):
+        """-> (loss[1], flag[1] int32).  `sticky`: a caller-owned int32[1] that is only ever set (CUDA-graph replays)."""
         st = self._prep(p, t)
         out = torch.empty((1,), dtype=torch.float32, device=p.device)
+        if sticky is not None:
+            _lib.check(self.lib.ganb200_bce_fwd_sticky(self._p(p), self._p(t), self._p(out), self._p(sticky),
+                                                       p.numel(), st))
+            return out, sticky
         flag = torch.empty((1,), dtype=torch.int32, device=p.device)
         _lib.check(self.lib.ganb200_bce_fwd(self._p(p), self._p(t), self._p(out), self._p(flag), p.numel(), st))
         return out, flag

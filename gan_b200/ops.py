@@ -708,16 +708,28 @@ def batch_stddev(x, eps=10e-8):
 class BceFn(Function):
     """torch.nn.BCELoss (mean).  Raises like the reference when an input is outside [0,1]."""
     check_range = True
+    RANGE_ERROR = "all elements of input should be between 0 and 1"
+    # device -> int32[1] that the kernel only ever sets.  Inside a captured CUDA graph the host cannot read a per-call
+    # flag (a D2H copy is not capturable), so the range check moves to this flag: gan_b200.graphed.GraphedStep polls it
+    # between replays and raises the same RuntimeError the eager path (and the reference) raises.
+    sticky = {}
+
+    @staticmethod
+    def sticky_flag(device):
+        f = BceFn.sticky.get(device)
+        if f is None:
+            f = BceFn.sticky[device] = torch.zeros((1,), dtype=torch.int32, device=device)
+        return f
 
     @staticmethod
     def forward(ctx, p, t):
         p, t = _c(p), _c(t)
-        out, flag = K().bce_fwd(p, t)
-        do_check = BceFn.check_range
-        if do_check and p.is_cuda and torch.cuda.is_current_stream_capturing():
-            do_check = False  # a D2H read cannot be captured; the eager warm-up iterations have checked
-        if do_check and int(flag.item()) != 0:
-            raise RuntimeError("all elements of input should be between 0 and 1")
+        if BceFn.check_range and p.is_cuda and torch.cuda.is_current_stream_capturing():
+            out, _ = K().bce_fwd(p, t, sticky=BceFn.sticky_flag(p.device))
+        else:
+            out, flag = K().bce_fwd(p, t)
+            if BceFn.check_range and int(flag.item()) != 0:
+                raise RuntimeError(BceFn.RANGE_ERROR)
         ctx.save_for_backward(p, t)
         return out.reshape(())
 

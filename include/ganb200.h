@@ -192,6 +192,10 @@ int ganb200_mbstd_bwd_bwd(const float* g, const float* x, const float* ggx, floa
 /* BCELoss, mean reduction, log clamped at -100 (torch.nn.BCELoss, train/gan.py:21, ganR2.py:17).
  * range_flag[0] is set to 1 if any p is outside [0,1] (the caller raises, as the reference does). */
 int ganb200_bce_fwd(const float* p, const float* t, float* out, int* range_flag, int64_t n, void* stream);
+/* Same loss, but sticky_flag[0] is only ever set to 1, never cleared: the form used inside a captured CUDA graph, where the
+ * host cannot read a per-call flag; the caller polls and clears the flag between replays (gan_b200/graphed.py) and raises
+ * the reference's RuntimeError (torch.nn.BCELoss input range check) when it tripped. */
+int ganb200_bce_fwd_sticky(const float* p, const float* t, float* out, int* sticky_flag, int64_t n, void* stream);
 int ganb200_bce_bwd(const float* g, const float* p, const float* t, float* gp, int64_t n, void* stream);
 
 /* Fused multi-tensor Adam / AdamW (torch.optim.Adam train/trainunits.py:18-19; AdamW train/wgangp.py:17-18).

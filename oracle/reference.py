@@ -1,8 +1,10 @@
 """TEST INFRASTRUCTURE — loads the UNMODIFIED reference (xxxxx23124/-GAN-) from /root/reference as the oracle.
 
 Only tests/, oracle/make_golden.py and bench.py's `--impl reference` / cpu_baseline leg may import this.
-/root/reference exists only in the build container; on the GPU box `available()` is False and callers fall
-back to the committed fixtures under tests/golden/ (parity) or to the restated loops (CPU baseline).
+/root/reference exists only in the build container; on the GPU box the tree is read from oracle/_ref/, the byte-for-byte
+copy that oracle/build_ref.py makes at build time (git-ignored, shipped like a built .so); when neither exists
+`available()` is False and callers fall back to the committed fixtures under tests/golden/ (parity) or to the restated
+loops (CPU baseline, kind "port").
 
 The reference imports matplotlib, tkinter (through tqdm.tk) and torchsummary at module top
 (train/trainunits.py:7, train/ganR2.py:2, discriminators/discriminator_4.py:6); none is installed here, so
@@ -18,7 +20,9 @@ import os
 import sys
 import types
 
-ROOT = os.environ.get("GAN_REFERENCE_ROOT", "/root/reference")
+_COPY = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")   # written by oracle/build_ref.py (git-ignored)
+ROOT = os.environ.get("GAN_REFERENCE_ROOT") or (
+    "/root/reference" if os.path.isdir("/root/reference/generators") else _COPY)
 PREFIX = "_gan_ref"
 _PKGS = ("generators", "discriminators", "train", "units")
 

@@ -141,9 +141,7 @@ def test_own_checkpoint_round_trip_with_optimiser_state(ref_backend, workdir, mo
         assert torch.equal(p, q), n
 
 
-# Written after this round's GPU minutes were spent: opt-in until a GPU call has confirmed it (see test_other_configs.py).
 @pytest.mark.gpu
-@pytest.mark.skipif(os.environ.get("GANB200_TEST_ZOO_GPU") != "1", reason="unconfirmed on GPU: set GANB200_TEST_ZOO_GPU=1")
 def test_load_reference_checkpoint_on_gpu(workdir, monkeypatch):
     """The adopted modules run on libganb200 (fp32 engine here: 2e-4 against the reference's CPU outputs)."""
     from gan_b200 import checkpoint as C

@@ -139,11 +139,7 @@ def test_config_cuda_tcgen05_matches_reference_golden(monkeypatch, name):
     compare(name, torch.device("cuda"), **TOL_BF16[name])
 
 
-# Written after this round's GPU minutes were spent: never run on a B200 yet, so opt-in (GANB200_TEST_ZOO_GPU=1) until a
-# GPU call has confirmed it — a first run belongs in a `gpurun`, not in the driver's round-end suite.  Every kernel these
-# pairs launch is covered by tests/test_gpu_kernels.py and by the BASELINE configs above.
 @pytest.mark.gpu
-@pytest.mark.skipif(os.environ.get("GANB200_TEST_ZOO_GPU") != "1", reason="unconfirmed on GPU: set GANB200_TEST_ZOO_GPU=1")
 @pytest.mark.parametrize("name", ZOO)
 def test_zoo_cuda_fp32_matches_reference_golden(monkeypatch, name):
     monkeypatch.setenv("GANB200_PRECISION", "fp32")

@@ -63,13 +63,20 @@ def test_generator_fused_equals_unfused_noise_path(ref_backend):
             os.environ.pop("GANB200_STYLE_BANK", None)
     a, b = res["philox"], res["philox_unfused"]
     assert float((a[0] - b[0]).norm() / b[0].norm()) < 1e-4
-    worst = 0.0
+    worst, num, den = 0.0, 0.0, 0.0
     for n, gb in b[1].items():
         ga = a[1][n]
         assert (ga is None) == (gb is None), n
-        if gb is not None and gb.norm() > 1e-4:  # biases feeding a BatchNorm have zero gradient: rounding noise
+        if gb is None:
+            continue
+        num += float((ga - gb).norm() ** 2)
+        den += float(gb.norm() ** 2)
+        # biases feeding a BatchNorm have an analytically zero gradient: what is left is rounding noise whose norm
+        # (2e-4 for block0.mapping_network.net.6.bias) depends on the noise realisation -> floor at 1e-3
+        if gb.norm() > 1e-3:
             worst = max(worst, float((ga - gb).norm() / gb.norm()))
     assert worst < 5e-2, worst  # fp32, ~100 layers and B=4 batch norms: see tests/test_golden_final_pair.py
+    assert (num / den) ** 0.5 < 5e-3, (num / den) ** 0.5  # all 8 766 gradient tensors together (measured 4.5e-4)
 
 
 def test_style_bank_is_the_same_computation(ref_backend, monkeypatch):
