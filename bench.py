@@ -504,20 +504,30 @@ def adam_roofline(T, device):
                 total += p.numel()
     if total == 0:
         return {"gbs": 0.0, "bytes": 0, "ms": 0.0}
-    for opt in (T.optimizer_G, T.optimizer_D):
-        opt.pre_step_saved, opt.pre_step = opt.pre_step, None
+    saved = [(opt, opt.pre_step) for opt in (T.optimizer_G, T.optimizer_D)]
+    for opt, _ in saved:
+        opt.pre_step = None
+        opt.capturable = True
+    # device time only: issued eagerly, FusedAdam.step spends ~20 ms on the host walking 10 653 parameters, which is
+    # what CUDA events would then measure; captured in a graph the two launches run back to back
     for _ in range(2):
         T.optimizer_G.step(); T.optimizer_D.step()
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g, capture_error_mode="thread_local"):
+        T.optimizer_G.step(); T.optimizer_D.step()
+    g.replay()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     reps = 5
     e0.record()
     for _ in range(reps):
-        T.optimizer_G.step(); T.optimizer_D.step()
+        g.replay()
     e1.record()
     e1.synchronize()
-    for opt in (T.optimizer_G, T.optimizer_D):
-        opt.pre_step = opt.pre_step_saved
+    del g
+    for opt, hook in saved:
+        opt.pre_step = hook
     ms = e0.elapsed_time(e1) / reps
     return {"gbs": 28.0 * total / (ms * 1e-3) / 1e9, "bytes": 28 * total, "ms": ms}
 

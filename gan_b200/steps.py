@@ -23,6 +23,9 @@ from . import ops
 from . import rng
 
 
+SEPARATE_BACKWARD = os.environ.get("GANB200_SEPARATE_BACKWARD") == "1"
+
+
 @dataclass(frozen=True)
 class Recipe:
     name: str
@@ -155,11 +158,21 @@ class StepMixin:
             if weight and penal:
                 if not x.requires_grad:
                     raise RuntimeError("One of the differentiated Tensors does not require grad")
-                loss.backward(retain_graph=True)
+                if SEPARATE_BACKWARD:
+                    loss.backward(retain_graph=True)
                 reg = ops.mean(self.compute_grad2(pred, x))
                 if weight * scale != 1.0:
                     reg = ops.affine(reg, weight * scale, 0.0)
-                reg.backward()
+                if SEPARATE_BACKWARD:
+                    reg.backward()
+                else:
+                    # ONE sweep for the loss and its penalty (ganR2.py:53-56 runs two: real_loss.backward(retain_graph=True)
+                    # then r2_reg_r.backward()).  Both sweeps walk the critic's forward graph backwards — a dgrad and a
+                    # wgrad per convolution, 2 of the ~7 critic-forwards of work per side — with different seeds; the
+                    # backward is linear in the seed, so seeding both roots at once and walking the shared part once
+                    # gives the same parameter gradients (sums re-associated: fp32 rounding only) for 2 D_f less per
+                    # side.  GANB200_SEPARATE_BACKWARD=1 restores the reference's two calls.
+                    torch.autograd.backward([loss, reg])
                 out[tag] = reg
             else:
                 loss.backward()
