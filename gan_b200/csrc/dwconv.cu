@@ -205,6 +205,61 @@ extern "C" int ganb200_dwconv2d_wgrad(const float* x, const float* dy, float* dw
   return 0;
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Allocation-free variant of the depthwise wgrad (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: code under CUDA-graph capture, tight serving loops, harnesses that
+// forbid allocation).  The split partials live in a file-scope device array instead of a caller-provided workspace.
+// Every GPU that loads the library holds the array (256 KiB) until the process exits.  All calls share it: two calls
+// that overlap on the GPU (different streams) race; calls on one stream are ordered and safe.  Nothing has to start at
+// zero: dw3_wgrad_kernel writes every partial[split][c][k] that dw3_wgrad_reduce_kernel of the same call reads, so the
+// previous call's contents are simply overwritten.
+constexpr int64_t kDwWgradStaticFloats = 65536;   // 256 KiB: splits * C * 9 floats, i.e. C up to ~6 600 channels
+static __device__ __align__(256) float g_dw_wgrad_partials[kDwWgradStaticFloats];
+
+// The array's name is a host-side stand-in in host code, not a device address: the address a kernel can use comes from
+// cudaGetSymbolAddress, asked once per device with that device current.
+static int dw_static_partials(float** out) {
+  constexpr int kMaxDev = 64;
+  static float* ptr[kMaxDev] = {nullptr};
+  int dev = -1;
+  GB_CHECK_CUDA(cudaGetDevice(&dev));
+  GB_REQUIRE(dev >= 0 && dev < kMaxDev, GANB200_BAD_ARG, "dwconv wgrad (static scratch): device index out of range");
+  if (ptr[dev] == nullptr) {
+    void* p = nullptr;
+    GB_CHECK_CUDA(cudaGetSymbolAddress(&p, g_dw_wgrad_partials));
+    GB_REQUIRE(p != nullptr, GANB200_CUDA_ERROR, "dwconv wgrad (static scratch): null symbol address");
+    ptr[dev] = (float*)p;   // same value from any thread: a benign race
+  }
+  *out = ptr[dev];
+  return 0;
+}
+
+extern "C" int64_t ganb200_dwconv2d_wgrad_static_max_bytes(void) { return kDwWgradStaticFloats * (int64_t)sizeof(float); }
+
+extern "C" int ganb200_dwconv2d_wgrad_static(const float* x, const float* dy, float* dw, int N, int C, int H, int W,
+                                             int R, int S, int stride, int pad, float alpha, void* stream) {
+  int P, Q;
+  if (int rc = dw_check(N, C, H, W, R, S, stride, pad, &P, &Q)) return rc;
+  const int64_t need = ganb200_dwconv2d_wgrad_workspace_bytes(N, C);
+  if (need > kDwWgradStaticFloats * (int64_t)sizeof(float))
+    return fail(GANB200_WORKSPACE_TOO_SMALL,
+                "dwconv wgrad (static scratch): this shape needs %s%lld bytes of split partials, the built-in scratch "
+                "holds %lld; use ganb200_dwconv2d_wgrad with a caller workspace", "", (long long)need,
+                (long long)(kDwWgradStaticFloats * sizeof(float)));
+  float* partial = nullptr;
+  if (int rc = dw_static_partials(&partial)) return rc;
+  const int splits = (int)(need / ((int64_t)C * 9 * sizeof(float)));
+  cudaStream_t s = (cudaStream_t)stream;
+  dim3 grid(C, splits);
+  if (stride == 1)
+    dw3_wgrad_kernel<1><<<grid, 256, 0, s>>>(x, dy, partial, N, C, H, W, P, Q, pad);
+  else
+    dw3_wgrad_kernel<2><<<grid, 256, 0, s>>>(x, dy, partial, N, C, H, W, P, Q, pad);
+  dw3_wgrad_reduce_kernel<<<ceil_div(C * 9, 256), 256, 0, s>>>(partial, dw, C * 9, splits, alpha);
+  GB_CHECK_LAUNCH();
+  return 0;
+}
+
 extern "C" int ganb200_chan_shuffle(const float* x, float* y, int N, int C, int HW, int groups, void* stream) {
   if ((int64_t)N * C * HW <= 0) return 0;
   GB_REQUIRE(groups >= 1 && C % groups == 0, GANB200_BAD_SHAPE, "chan_shuffle: C must be a multiple of groups");

@@ -266,6 +266,17 @@ int ganb200_dwconv2d_wgrad(const float* x, const float* dy, float* dw, void* wor
                            int64_t workspace_bytes, int N, int C, int H, int W, int R, int S, int stride,
                            int pad, float alpha, void* stream);
 
+/* Allocation-free depthwise wgrad.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).
+ * Same result as ganb200_dwconv2d_wgrad, but the split partials live in a 256 KiB file-scope device array inside the
+ * library (held by every GPU that loads it, until exit) instead of a caller workspace; the call performs no cudaMalloc /
+ * cudaFree / allocating library call.  Shapes whose partials exceed ganb200_dwconv2d_wgrad_static_max_bytes()
+ * (splits * C * 36 bytes > 256 KiB, i.e. C above ~6 600) are rejected with GANB200_WORKSPACE_TOO_SMALL.  All calls share
+ * the array: calls on one stream are ordered; calls that overlap on the GPU (different streams) race. */
+int64_t ganb200_dwconv2d_wgrad_static_max_bytes(void);
+int ganb200_dwconv2d_wgrad_static(const float* x, const float* dy, float* dw, int N, int C, int H, int W, int R, int S,
+                                  int stride, int pad, float alpha, void* stream);
+
 /* channel_shuffle (discriminator_7_wgangpsn.py:27-41): y[n, j*groups + i] = x[n, i*(C/groups) + j].
  * Its adjoint / inverse is the same call with groups' = C/groups. */
 int ganb200_chan_shuffle(const float* x, float* y, int N, int C, int HW, int groups, void* stream);
