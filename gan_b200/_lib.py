@@ -25,6 +25,21 @@ class AdamEntry(ctypes.Structure):
     _fields_ = [("p", c_void_p), ("g", c_void_p), ("m", c_void_p), ("v", c_void_p), ("n", c_int64)]
 
 
+class GlinJobC(ctypes.Structure):
+    """Mirror of ganb200_glin_job (96 bytes)."""
+    _fields_ = [("a", c_void_p), ("b", c_void_p), ("out", c_void_p), ("bias", c_void_p),
+                ("a_off", c_int64), ("b_off", c_int64), ("out_off", c_int64),
+                ("ni", c_int), ("nj", c_int), ("nr", c_int), ("lda", c_int), ("ldb", c_int), ("ldo", c_int),
+                ("a_red_is_row", c_int), ("b_red_is_row", c_int), ("alpha", c_float), ("first_block", c_int)]
+
+
+class GbnJobC(ctypes.Structure):
+    """Mirror of ganb200_gbn_job (72 bytes)."""
+    _fields_ = [("gamma", c_void_p), ("beta", c_void_p), ("slope", c_void_p), ("running_mean", c_void_p),
+                ("running_var", c_void_p), ("nbt", c_void_p), ("x_off", c_int64), ("stat_off", c_int64),
+                ("C", c_int), ("first_block", c_int)]
+
+
 P = c_void_p
 _DESC_P = ctypes.POINTER(ConvDesc)
 
@@ -63,6 +78,11 @@ SIGNATURES = {
     "ganb200_mbstd_fwd": (c_int, [P, P, c_int, c_int64, c_float, P]),
     "ganb200_mbstd_bwd": (c_int, [P, P, P, c_int, c_int64, c_float, P]),
     "ganb200_mbstd_bwd_bwd": (c_int, [P, P, P, P, P, c_int, c_int64, c_float, P]),
+    "ganb200_linear_group": (c_int, [P, c_int, c_int, P, P, P, P]),
+    "ganb200_bn1d_group_stats": (c_int, [P, c_int, c_int, P, c_int, P, P, P]),
+    "ganb200_bn1d_group_apply": (c_int, [P, c_int, c_int, P, P, c_int, P, P, P, c_float, c_float, c_int64, P]),
+    "ganb200_bn1d_group_bwd_reduce": (c_int, [P, c_int, c_int, P, P, c_int, P, P, P, P, P, P]),
+    "ganb200_bn1d_group_bwd_apply": (c_int, [P, c_int, c_int, P, P, P, c_int, P, P, P, P, c_int64, P, P]),
     "ganb200_bce_fwd": (c_int, [P, P, P, P, c_int64, P]),
     "ganb200_bce_fwd_sticky": (c_int, [P, P, P, P, c_int64, P]),
     "ganb200_bce_bwd": (c_int, [P, P, P, P, c_int64, P]),

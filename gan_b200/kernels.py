@@ -454,11 +454,11 @@ class CudaBackend:
         _lib.check(self.lib.ganb200_demod(self._p(s), self._p(wsq), self._p(sinv), B, C, Kout, alpha, eps, st))
         return sinv
 
-    def demod_bwd_s(self, gs1, s, Ad, sinv, wsq, alpha):
+    def demod_bwd_s(self, gs1, s, Ad, sinv, wsq, alpha, out=None):
         B, C = s.shape
         Kout = wsq.shape[0]
-        st = self._prep(gs1, s, Ad, sinv, wsq)
-        gs = torch.empty_like(s)
+        st = self._prep(gs1, s, Ad, sinv, wsq, out)
+        gs = out if out is not None else torch.empty_like(s)
         _lib.check(self.lib.ganb200_demod_bwd_s(self._p(gs1), self._p(s), self._p(Ad), self._p(sinv), self._p(wsq),
                                                 self._p(gs), B, C, Kout, alpha, st))
         return gs
@@ -526,6 +526,58 @@ class CudaBackend:
         _lib.check(self.lib.ganb200_scale_reduce(self._p(dxs), self._p(s), self._p(x), self._p(gx), self._p(gs1), N, C,
                                                  HW, st))
         return gx, gs1
+
+    # -- grouped launches (gan_b200/group.py, csrc/group.cu) ------------------------------------------
+    def linear_group(self, plan, a_base, b_base, o_base):
+        from . import group as GR
+        st = self._prep(a_base, b_base, o_base)
+        tab, n, blocks = GR.glin_table(plan, o_base.device)
+        _lib.check(self.lib.ganb200_linear_group(self._p(tab), n, blocks, self._p(a_base), self._p(b_base),
+                                                 self._p(o_base), st))
+        return o_base
+
+    def bn1d_group_stats(self, plan, x_base, N, total_c):
+        from . import group as GR
+        st = self._prep(x_base)
+        tab, n, blocks = GR.gbn_table(plan, x_base.device)
+        mean = torch.empty((total_c,), dtype=torch.float32, device=x_base.device)
+        var = torch.empty((total_c,), dtype=torch.float32, device=x_base.device)
+        _lib.check(self.lib.ganb200_bn1d_group_stats(self._p(tab), n, blocks, self._p(x_base), N, self._p(mean),
+                                                     self._p(var), st))
+        return mean, var
+
+    def bn1d_group_apply(self, plan, x_base, N, mean, var, eps, momentum, count_total):
+        from . import group as GR
+        st = self._prep(x_base, mean, var)
+        tab, n, blocks = GR.gbn_table(plan, x_base.device)
+        y = torch.empty_like(x_base)
+        invstd = torch.empty_like(mean)
+        _lib.check(self.lib.ganb200_bn1d_group_apply(self._p(tab), n, blocks, self._p(x_base), self._p(y), N,
+                                                     self._p(mean), self._p(var), self._p(invstd), eps, momentum,
+                                                     int(count_total), st))
+        return y, invstd
+
+    def bn1d_group_bwd_reduce(self, plan, gy_base, x_base, N, mean, invstd, total_c, has_slope):
+        from . import group as GR
+        st = self._prep(gy_base, x_base, mean, invstd)
+        tab, n, blocks = GR.gbn_table(plan, x_base.device)
+        s1, s2 = torch.empty_like(mean), torch.empty_like(mean)
+        gsl = torch.empty_like(mean) if has_slope else None
+        _lib.check(self.lib.ganb200_bn1d_group_bwd_reduce(self._p(tab), n, blocks, self._p(gy_base), self._p(x_base), N,
+                                                          self._p(mean), self._p(invstd), self._p(s1), self._p(s2),
+                                                          self._p(gsl), st))
+        return s1, s2, gsl
+
+    def bn1d_group_bwd_apply(self, plan, gy_base, x_base, N, mean, invstd, s1, s2, count_total, total_c):
+        from . import group as GR
+        st = self._prep(gy_base, x_base, mean, invstd, s1, s2)
+        tab, n, blocks = GR.gbn_table(plan, x_base.device)
+        gx = torch.empty_like(x_base)
+        gbias = torch.empty_like(mean)
+        _lib.check(self.lib.ganb200_bn1d_group_bwd_apply(self._p(tab), n, blocks, self._p(gy_base), self._p(x_base),
+                                                         self._p(gx), N, self._p(mean), self._p(invstd), self._p(s1),
+                                                         self._p(s2), int(count_total), self._p(gbias), st))
+        return gx, gbias
 
     # -- optimiser / misc -------------------------------------------------------------------------
     def adam_blocks(self, tab, block_tab, n_blocks, chunk, lr, b1, b2, eps, wd, decoupled, step, grad_scale,

@@ -1054,7 +1054,9 @@ class StyleLayerFn(Function):
                 gw = k.conv_wgrad(x, gu, tuple(w.shape[2:]), 1, pad, 1, alpha, iscale=s, oscale=sinv, engine=engine)
         if demodulate:
             if need_s:
-                gs = k.demod_bwd_s(gs, s, Ad, sinv, wsq, alpha)
+                # a style produced by the grouped bank carries the segment of the bank's gradient buffer it belongs to
+                # (gan_b200/group.py): write there, the bank's backward then needs no gather
+                gs = k.demod_bwd_s(gs, s, Ad, sinv, wsq, alpha, out=getattr(s, "_gb_grad_out", None))
             if need_w:
                 gw = k.demod_bwd_w_(gw, w, Ad, sinv, s, alpha)
         return gx, gw, gs, gns, gslope, None, None, None, None, None, None, None

@@ -198,7 +198,7 @@ class Conv2dWeightModulate(nn.Module):
         self.weight = EqualizedWeight([out_planes, in_planes, kernel_size, kernel_size])
         self.eps = eps
 
-    # filled by StyleBank (below) when GANB200_STYLE_BANK is set; consumed once per forward
+    # filled by StyleBank (below); consumed once per forward
     _style = None
     _style_ready = None
 
@@ -226,20 +226,31 @@ class Conv2dWeightModulate(nn.Module):
 
 
 class StyleBank:
-    """The 519 per-layer style vectors `to_style(w)` depend on w alone, not on the feature maps.  With
-    GANB200_STYLE_BANK=1 they are all computed right after the mapping network (GeneratorStart.forward) instead of one by
-    one in front of their convolution: same kernels, same results (`tests/test_style_layer.py`), but the ~2 000 tiny
-    launches form one independent group — in the backward too, where autograd then runs them after the last convolution
-    — which is what a grouped launch or a side stream needs.  GANB200_STYLE_BANK=2 (experimental, GPU only, never timed
-    or run yet) issues the group on a side stream with one event per layer, so that inside a captured graph it becomes a
-    branch parallel to the convolution chain.  Default 0: styles are computed where the reference computes them."""
+    """The 519 per-layer style vectors `to_style(w)` depend on w alone, not on the feature maps, so they are all computed
+    right after the mapping network (GeneratorStart.forward) instead of one by one in front of their convolution.
+    GANB200_STYLE_BANK selects how:
+      "3" (default) grouped launches — gan_b200.group.GroupedStyles: the whole family in 6 launches forward / 11 backward
+          (csrc/group.cu) instead of 4 / 8 per layer; same arithmetic per layer, same parameters and running statistics.
+          Falls back to "0" when a to_style module is observed by hooks or is not in training mode.
+      "1" the same per-layer kernels as "0", only issued up front (bit-identical to "0", tests/test_style_layer.py);
+      "2" like "1" on a side stream (measured on B200: no gain, the step is not latency- but throughput-bound there);
+      "0" styles computed where the reference computes them (generator_13_5.py:239)."""
 
     def __init__(self, layers):
         self.layers = list(layers)
         self.stream = None
+        self.grouped = None
 
     def fill(self, w: torch.Tensor):
-        mode = os.environ.get("GANB200_STYLE_BANK", "0")
+        mode = os.environ.get("GANB200_STYLE_BANK", "3")
+        if mode == "3":
+            if self.grouped is None:
+                from gan_b200.group import GroupedStyles
+                self.grouped = GroupedStyles([m.to_style for m in self.layers])
+            if w.dim() == 2 and self.grouped.eligible():
+                for m, s in zip(self.layers, self.grouped(w)):
+                    m._style = s
+            return
         if mode not in ("1", "2"):
             return
         if mode == "2" and w.is_cuda:

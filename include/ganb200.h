@@ -189,6 +189,52 @@ int ganb200_mbstd_bwd(const float* g, const float* x, float* gx, int G, int64_t 
 int ganb200_mbstd_bwd_bwd(const float* g, const float* x, const float* ggx, float* out_gg, float* out_gx,
                           int G, int64_t L, float eps, void* stream);
 
+/* Grouped launches: a device table of jobs describes a whole family of small independent layers and ONE launch runs
+ * them all (gan_b200/csrc/group.cu).  Built for the 519 per-layer style MLPs of generators/generator_13_5.py:205-216,
+ * 223-227 (to_style = EqualizedLinear, BatchNorm1d, PReLU, EqualizedLinear, BatchNorm1d on the same w), which layer by
+ * layer are ~12 000 launches of 8 us per training iteration.
+ *
+ * linear_group: out = alpha * A B^T (+ bias) per job, fp32.  An operand is a fixed pointer (a parameter) or, when the
+ * pointer is NULL, an element offset into the base pointer given at launch (activations: new memory every call, same
+ * table).  Element (i, r) of A sits at a[r*lda + i] when a_red_is_row else a[i*lda + r]; B likewise with (j, r).
+ * first_block = index of the job's first CTA in the flattened list of 32 x 32 output tiles (prefix sum). */
+typedef struct {
+  const float* a; const float* b; float* out; const float* bias;
+  int64_t a_off, b_off, out_off;
+  int ni, nj, nr, lda, ldb, ldo, a_red_is_row, b_red_is_row;
+  float alpha;
+  int first_block;
+} ganb200_glin_job;
+int ganb200_linear_group(const ganb200_glin_job* jobs, int n_jobs, int n_blocks, const float* a_base,
+                         const float* b_base, float* out_base, void* stream);
+
+/* Training-mode BatchNorm1d (+ the per-channel PReLU that follows it when slope != NULL) on row-major [N][C] matrices,
+ * one job per norm (torch.nn.BatchNorm1d + nn.PReLU of generator_13_5.py:60-62, 189-193).  x / y / gy / gx share the layout
+ * base + x_off; per-channel arrays (mean, var, invstd, sums, bias gradient) are flat with the job's C entries at stat_off.
+ *   stats     : mean, biased variance over the N rows
+ *   apply     : y = PReLU((x - mean) / sqrt(var + eps) * gamma + beta), invstd out, running statistics with momentum
+ *               (unbiased variance from count_total = N * world_size), num_batches_tracked += 1
+ *   bwd_reduce: gu = gy * PReLU'(u);  s1 = sum_n gu (= dbeta),  s2 = sum_n gu * xhat (= dgamma),  gslope = sum_n gy*min(u,0)
+ *   bwd_apply : gx = gamma * invstd * (gu - s1/count - xhat * s2/count) with the (all-reduced) sums; gbias = sum_n gx
+ * first_block = prefix sum of ceil(C / 32) (one CTA per job and 32 channels). */
+typedef struct {
+  const float* gamma; const float* beta; const float* slope;
+  float* running_mean; float* running_var; int64_t* num_batches_tracked;
+  int64_t x_off, stat_off;
+  int C, first_block;
+} ganb200_gbn_job;
+int ganb200_bn1d_group_stats(const ganb200_gbn_job* jobs, int n_jobs, int n_blocks, const float* x_base, int N,
+                             float* mean, float* var, void* stream);
+int ganb200_bn1d_group_apply(const ganb200_gbn_job* jobs, int n_jobs, int n_blocks, const float* x_base, float* y_base,
+                             int N, const float* mean, const float* var, float* invstd, float eps, float momentum,
+                             int64_t count_total, void* stream);
+int ganb200_bn1d_group_bwd_reduce(const ganb200_gbn_job* jobs, int n_jobs, int n_blocks, const float* gy_base,
+                                  const float* x_base, int N, const float* mean, const float* invstd, float* s1,
+                                  float* s2, float* gslope, void* stream);
+int ganb200_bn1d_group_bwd_apply(const ganb200_gbn_job* jobs, int n_jobs, int n_blocks, const float* gy_base,
+                                 const float* x_base, float* gx_base, int N, const float* mean, const float* invstd,
+                                 const float* s1, const float* s2, int64_t count_total, float* gbias, void* stream);
+
 /* BCELoss, mean reduction, log clamped at -100 (torch.nn.BCELoss, train/gan.py:21, ganR2.py:17).
  * range_flag[0] is set to 1 if any p is outside [0,1] (the caller raises, as the reference does). */
 int ganb200_bce_fwd(const float* p, const float* t, float* out, int* range_flag, int64_t n, void* stream);

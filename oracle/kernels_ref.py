@@ -262,10 +262,94 @@ class RefBackend:
     def demod(self, s, wsq, alpha, eps):
         return torch.rsqrt(alpha * alpha * (s * s) @ wsq.t() + eps)
 
-    def demod_bwd_s(self, gs1, s, Ad, sinv, wsq, alpha):
+    def demod_bwd_s(self, gs1, s, Ad, sinv, wsq, alpha, out=None):
         dd = -0.5 * Ad * sinv * sinv
         gs = 2 * s * alpha * alpha * (dd @ wsq)
-        return gs if gs1 is None else gs + gs1
+        gs = gs if gs1 is None else gs + gs1
+        if out is not None:
+            out.copy_(gs)
+            return out
+        return gs
+
+    # ---- grouped launches (gan_b200/csrc/group.cu; job lists from gan_b200/group.py) ---------------------------
+    @staticmethod
+    def _mat(flat, off, n_i, n_r, ld, red_is_row):
+        """(n_i, n_r) view with element (i, r) at flat[off + r*ld + i] (red_is_row) or flat[off + i*ld + r]"""
+        return torch.as_strided(flat, (n_i, n_r), (1, ld) if red_is_row else (ld, 1), off)
+
+    def linear_group(self, plan, a_base, b_base, o_base):
+        of = o_base.reshape(-1)
+        for j in plan.jobs:
+            af, ao = (j.a.detach().reshape(-1), 0) if j.a is not None else (a_base.reshape(-1), j.a_off)
+            bf, bo = (j.b.detach().reshape(-1), 0) if j.b is not None else (b_base.reshape(-1), j.b_off)
+            A = self._mat(af, ao, j.ni, j.nr, j.lda, j.a_red_is_row)
+            Bm = self._mat(bf, bo, j.nj, j.nr, j.ldb, j.b_red_is_row)
+            y = (A @ Bm.t()) * j.alpha
+            if j.bias is not None:
+                y = y + j.bias.detach()
+            torch.as_strided(of, (j.ni, j.nj), (j.ldo, 1), j.out_off).copy_(y)
+        return o_base
+
+    @staticmethod
+    def _rows(flat, j, N):
+        return torch.as_strided(flat.reshape(-1), (N, j.C), (j.C, 1), j.x_off)
+
+    def bn1d_group_stats(self, plan, x_base, N, total_c):
+        mean, var = x_base.new_empty(total_c), x_base.new_empty(total_c)
+        for j in plan.jobs:
+            x = self._rows(x_base, j, N)
+            mean[j.stat_off:j.stat_off + j.C] = x.mean(0)
+            var[j.stat_off:j.stat_off + j.C] = x.var(0, unbiased=False)
+        return mean, var
+
+    def bn1d_group_apply(self, plan, x_base, N, mean, var, eps, momentum, count_total):
+        y_base, invstd = torch.empty_like(x_base), torch.empty_like(mean)
+        with torch.no_grad():
+            for j in plan.jobs:
+                sl = slice(j.stat_off, j.stat_off + j.C)
+                x = self._rows(x_base, j, N)
+                is_ = torch.rsqrt(var[sl] + eps)
+                u = (x - mean[sl]) * is_ * j.gamma.detach() + j.beta.detach()
+                if j.slope is not None:
+                    u = torch.where(u > 0, u, j.slope.detach() * u)
+                self._rows(y_base, j, N).copy_(u)
+                invstd[sl] = is_
+                unb = var[sl] * (count_total / (count_total - 1.0)) if count_total > 1 else var[sl]
+                j.running_mean.mul_(1 - momentum).add_(momentum * mean[sl])
+                j.running_var.mul_(1 - momentum).add_(momentum * unb)
+                j.nbt.add_(1)
+        return y_base, invstd
+
+    def _bn_gu(self, j, gy_base, x_base, N, mean, invstd):
+        sl = slice(j.stat_off, j.stat_off + j.C)
+        xh = (self._rows(x_base, j, N) - mean[sl]) * invstd[sl]
+        g = self._rows(gy_base, j, N)
+        ps = None
+        if j.slope is not None:
+            u = xh * j.gamma.detach() + j.beta.detach()
+            neg = ~(u > 0)
+            ps = (g * u * neg).sum(0)
+            g = torch.where(neg, g * j.slope.detach(), g)
+        return sl, xh, g, ps
+
+    def bn1d_group_bwd_reduce(self, plan, gy_base, x_base, N, mean, invstd, total_c, has_slope):
+        s1, s2 = torch.empty_like(mean), torch.empty_like(mean)
+        gsl = torch.empty_like(mean) if has_slope else None
+        for j in plan.jobs:
+            sl, xh, g, ps = self._bn_gu(j, gy_base, x_base, N, mean, invstd)
+            s1[sl], s2[sl] = g.sum(0), (g * xh).sum(0)
+            if has_slope:
+                gsl[sl] = ps
+        return s1, s2, gsl
+
+    def bn1d_group_bwd_apply(self, plan, gy_base, x_base, N, mean, invstd, s1, s2, count_total, total_c):
+        gx_base, gbias = torch.empty_like(x_base), torch.empty_like(mean)
+        for j in plan.jobs:
+            sl, xh, g, _ = self._bn_gu(j, gy_base, x_base, N, mean, invstd)
+            gx = j.gamma.detach() * invstd[sl] * (g - s1[sl] / count_total - xh * s2[sl] / count_total)
+            self._rows(gx_base, j, N).copy_(gx)
+            gbias[sl] = gx.sum(0)
+        return gx_base, gbias
 
     def demod_bwd_w_(self, gw, w, Ad, sinv, s, alpha):
         dd = -0.5 * Ad * sinv * sinv

