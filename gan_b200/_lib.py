@@ -88,6 +88,7 @@ SIGNATURES = {
     "ganb200_bce_bwd": (c_int, [P, P, P, P, c_int64, P]),
     "ganb200_multi_tensor_adam_blocks": (c_int, [P, P, c_int, c_int64, c_float, c_float, c_float, c_float, c_float,
                                                  c_int, c_int64, P, c_float, P]),
+    "ganb200_multi_tensor_copy": (c_int, [P, P, c_int, c_int64, P]),
     "ganb200_counter_add": (c_int, [P, c_int64, P]),
     "ganb200_chan_copy": (c_int, [P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, P]),
     "ganb200_mixup": (c_int, [P, P, c_float, P, c_int64, P]),

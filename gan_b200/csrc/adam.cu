@@ -70,8 +70,38 @@ __global__ void __launch_bounds__(256) multi_tensor_adam_kernel(const ganb200_ad
   }
 }
 
+// dst[i] = src[i] for every table entry (p = destination, g = source; m, v unused): gathers the gradient tensors of a
+// data-parallel bucket into its flat all-reduce buffer in ONE launch (gan_b200/dist.py) instead of torch.cat + copy_.
+__global__ void __launch_bounds__(256) multi_tensor_copy_kernel(const ganb200_adam_entry* __restrict__ tab,
+                                                                const int2* __restrict__ block_tab, int64_t chunk) {
+  const int2 bt = block_tab[blockIdx.x];
+  const ganb200_adam_entry e = tab[bt.x];
+  const int64_t lo = (int64_t)bt.y * chunk;
+  const int64_t hi = lo + chunk < e.n ? lo + chunk : e.n;
+  float* dst = e.p + lo;
+  const float* src = e.g + lo;
+  const int64_t n = hi - lo;
+  if (((((uintptr_t)dst) | ((uintptr_t)src)) & 15) == 0) {
+    const int64_t n4 = n >> 2;
+    for (int64_t i = threadIdx.x; i < n4; i += blockDim.x)
+      reinterpret_cast<float4*>(dst)[i] = __ldg(reinterpret_cast<const float4*>(src) + i);
+    for (int64_t i = (n4 << 2) + threadIdx.x; i < n; i += blockDim.x) dst[i] = src[i];
+  } else {
+    for (int64_t i = threadIdx.x; i < n; i += blockDim.x) dst[i] = src[i];
+  }
+}
+
 }  // namespace ganb200
 using namespace ganb200;
+
+extern "C" int ganb200_multi_tensor_copy(const ganb200_adam_entry* tab, const int32_t* block_tab, int n_blocks,
+                                         int64_t chunk, void* stream) {
+  if (n_blocks <= 0) return 0;
+  GB_REQUIRE(chunk > 0 && (chunk % 4) == 0, GANB200_BAD_ARG, "multi_tensor_copy: chunk must be a positive multiple of 4");
+  multi_tensor_copy_kernel<<<n_blocks, 256, 0, (cudaStream_t)stream>>>(tab, reinterpret_cast<const int2*>(block_tab), chunk);
+  GB_CHECK_LAUNCH();
+  return 0;
+}
 
 // block_tab: DEVICE array of n_blocks int32 pairs (tensor index, chunk index); chunk = elements per CTA.
 extern "C" int ganb200_multi_tensor_adam_blocks(const ganb200_adam_entry* tab, const int32_t* block_tab, int n_blocks,

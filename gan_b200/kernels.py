@@ -589,6 +589,12 @@ class CudaBackend:
                                                              b1, b2, eps, wd, int(decoupled), step,
                                                              self._p(step_dev), grad_scale, st))
 
+    def multi_tensor_copy(self, tab, block_tab, n_blocks, chunk, stream=None):
+        """tab: device table of ganb200_adam_entry (p = dst, g = src); one launch copies every entry"""
+        st = ctypes.c_void_p((stream or torch.cuda.current_stream(tab.device)).cuda_stream)
+        LAUNCH_COUNT[0] += 1
+        _lib.check(self.lib.ganb200_multi_tensor_copy(self._p(tab), self._p(block_tab), n_blocks, chunk, st))
+
     def counter_add(self, ctr, inc):
         st = ctypes.c_void_p(torch.cuda.current_stream(ctr.device).cuda_stream)
         LAUNCH_COUNT[0] += 1

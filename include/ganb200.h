@@ -258,6 +258,13 @@ int ganb200_multi_tensor_adam_blocks(const ganb200_adam_entry* tab, const int32_
                                      int64_t chunk, float lr, float beta1, float beta2, float eps,
                                      float weight_decay, int decoupled, int64_t step, const int64_t* step_dev,
                                      float grad_scale, void* stream);
+
+/* dst = src for every table entry (entry.p = destination, entry.g = source, entry.n elements; m / v ignored), same block
+ * table as the Adam launch: the gradients of a data-parallel bucket gathered into the flat buffer that ncclAllReduce
+ * sums in place and the fused Adam then reads — one launch per bucket (gan_b200/dist.py; no reference counterpart: the
+ * reference is single-device, main.py:23-25). */
+int ganb200_multi_tensor_copy(const ganb200_adam_entry* tab, const int32_t* block_tab, int n_blocks, int64_t chunk,
+                              void* stream);
 int ganb200_counter_add(int64_t* counter, int64_t inc, void* stream);
 
 /* Channel-slice copy on [N,C,HW] tensors: dst[:, dst_c0:dst_c0+ncopy] (+)= src[:, src_c0:src_c0+ncopy].

@@ -588,7 +588,7 @@ def test_grouped_style_bank_cuda_matches_oracle(cu, ref, B):
     for leg, mods, dev in (("ref", cpu_mods, "cpu"), ("cuda", gpu_mods, "cuda")):
         prev = KN.set_backend(ref if leg == "ref" else cu)
         try:
-            w_ = w.to(dev).requires_grad_()
+            w_ = w.detach().clone().to(dev).requires_grad_()
             bank = GroupedStyles(mods)
             assert bank.eligible()
             outs = bank(w_)
@@ -601,10 +601,13 @@ def test_grouped_style_bank_cuda_matches_oracle(cu, ref, B):
     for u, v in zip(a[0], b[0]):
         assert rel(u, v) < FP32_TOL
     assert rel(a[1], b[1]) < FP32_TOL
+    n_par = len(a[2]) // len(cpu_mods)
     for i, (u, v) in enumerate(zip(a[2], b[2])):
-        # biases feeding a BatchNorm have an analytically zero gradient: compare those on the scale of their layer
-        scale = max(v.norm().item(), 1e-3 * B)
-        assert (u - v).norm().item() / scale < 5e-5, (i, rel(u, v))
+        # the two linear biases feed a BatchNorm: analytically zero gradient, what both sides compute is rounding noise
+        # (|g| ~ 1e-6 next to 1e+1 for the weights) -> measured on the scale of the module's largest gradient
+        m0 = (i // n_par) * n_par
+        scale = max(t.norm().item() for t in b[2][m0:m0 + n_par])
+        assert (u - v).norm().item() <= FP32_TOL * max(v.norm().item(), scale), (i, rel(u, v))
     for u, v in zip(a[3], b[3]):
         assert rel(u.double(), v.double()) < FP32_TOL
 
@@ -627,8 +630,8 @@ def test_grouped_style_bank_cuda_equals_layer_by_layer(cu):
         assert rel(u, v) < FP32_TOL
     assert rel(wa.grad, wb.grad) < FP32_TOL
     for ma, mb in zip(mods_a, mods_b):
+        scale = max(q.grad.norm().item() for q in mb.parameters())
         for (n, p), (_, q) in zip(ma.named_parameters(), mb.named_parameters()):
-            scale = max(q.grad.norm().item(), 1e-3 * B)
-            assert (p.grad - q.grad).norm().item() / scale < 5e-5, n
+            assert (p.grad - q.grad).norm().item() <= FP32_TOL * max(q.grad.norm().item(), scale), n
         for (n, p), (_, q) in zip(ma.named_buffers(), mb.named_buffers()):
             assert rel(p.double(), q.double()) < FP32_TOL, n

@@ -49,28 +49,54 @@ def _params(T):
     return out
 
 
-@pytest.mark.timeout(1800)
-def test_graph_replay_equals_eager_iterations_on_the_final_pair():
+def _eager_leg(dev, images):
     from gan_b200 import rng
-    from gan_b200.graphed import GraphedStep
-    assert rng.noise_mode() == "philox" and rng.fused_noise(), "the benched mode uses the fused in-kernel noise"
-    dev = torch.device("cuda:0")
-    images = torch.randn(B, 3, 64, 64, generator=torch.Generator().manual_seed(3)).to(dev)
-
-    # eager leg
     rng._states.clear()
     T = _trainer(dev)
     _seed(1)
-    eager_losses = []
+    losses = []
     x = images.clone().requires_grad_()
     for _ in range(ITERS):
         d = T.discriminator_trainstep(x, B)
         _, g = T.generator_trainstep(B)
         x.grad = None
-        eager_losses.append([float(v) for v in d] + [float(g)])
-    eager = _params(T)
+        losses.append([float(v) for v in d] + [float(g)])
+    out = (losses, _params(T))
     del T
     torch.cuda.empty_cache()
+    return out
+
+
+def _distance(a, b):
+    """-> (worst relative loss difference, worst per-tensor rel-L2 over parameters and buffers, its name)"""
+    dl = max(abs(u - v) / max(1.0, abs(u)) for la, lb in zip(a[0], b[0]) for u, v in zip(la, lb))
+    worst = ("", 0.0)
+    for n, v in a[1].items():
+        w = b[1][n]
+        if not v.is_floating_point():
+            assert torch.equal(v, w), n
+            continue
+        r = float((v - w).norm() / max(float(v.norm()), 1e-12))
+        if r > worst[1]:
+            worst = (n, r)
+    return dl, worst[1], worst[0]
+
+
+@pytest.mark.timeout(2400)
+def test_graph_replay_equals_eager_iterations_on_the_final_pair():
+    """ITERS replays == ITERS eager iterations from the same seeds: losses and every parameter / buffer of both networks.
+    The step is not bit-reproducible run to run — a handful of reductions end in fp32 atomics (BatchNorm statistics, loss
+    and stddev sums), and generator_13_5 over a batch of 8 (BatchNorm1d over 8 samples in every attention head) amplifies
+    that 1e-7 to ~5e-3 at its output (measured on B200, tools/gpu/diag_graph.py) — so the yardstick is the step itself:
+    two EAGER runs from the same seeds give the noise floor, and the graph replay must sit within 3x of it."""
+    from gan_b200 import rng
+    from gan_b200.graphed import GraphedStep
+    assert rng.noise_mode() == "philox" and rng.fused_noise(), "the benched mode uses the fused in-kernel noise"
+    dev = torch.device("cuda:0")
+    images = torch.randn(B, 3, 64, 64, generator=torch.Generator().manual_seed(3)).to(dev)
+    eager_a = _eager_leg(dev, images)
+    eager_b = _eager_leg(dev, images)
+    floor_loss, floor_par, _ = _distance(eager_a, eager_b)
 
     # graph leg: same seeds; construction (warm-up + capture) must leave the state untouched
     rng._states.clear()
@@ -90,23 +116,14 @@ def test_graph_replay_equals_eager_iterations_on_the_final_pair():
         _, g = S.generator_trainstep(B)
         graph_losses.append([float(v) for v in d] + [float(g)])
     S.check_bce_range()
-    graphed = _params(T)
-
-    for a, b in zip(eager_losses, graph_losses):
-        for u, v in zip(a, b):
-            # same kernels on the same operands; the only order-dependent arithmetic is fp32 atomics (loss / stddev /
-            # reduction sums), which Adam's g/sqrt(v) then carries into the next iteration: measured 2e-6 after 2 steps
-            assert abs(u - v) <= 2e-5 * max(1.0, abs(u)), (eager_losses, graph_losses)
-    worst = ("", 0.0)
-    for n, v in eager.items():
-        w = graphed[n]
-        if not v.is_floating_point():
-            assert torch.equal(v, w), n
-            continue
-        rel = float((v - w).norm() / max(float(v.norm()), 1e-12))
-        if rel > worst[1]:
-            worst = (n, rel)
-    assert worst[1] <= 2e-5, worst
+    graphed = (graph_losses, _params(T))
+    d_loss, d_par, name = _distance(eager_a, graphed)
+    print(f"eager vs eager: losses {floor_loss:.2e} params {floor_par:.2e}; graph vs eager: losses {d_loss:.2e} "
+          f"params {d_par:.2e} ({name})")
+    assert d_loss <= 3 * max(floor_loss, 1e-6), (d_loss, floor_loss, eager_a[0], graph_losses)
+    assert d_par <= 3 * max(floor_par, 1e-6), (d_par, floor_par, name)
+    # a different RNG stream (z, label noise, in-kernel noise counter) or a skipped update shows up in the losses' 2nd digit
+    assert d_loss < 2e-2, (d_loss, eager_a[0], graph_losses)
     for opt in (T.optimizer_G, T.optimizer_D):
         assert all(st["step"] == ITERS for st in opt.state.values() if "step" in st)
 
