@@ -69,42 +69,148 @@ def shard_quarter_major(x, rank, world, groups=4):
 
 
 class GradSync:
-    """Sums .grad of the live parameters over ranks in flat buckets.  Called right before optimizer.step()."""
+    """Sums the gradients of the live parameters over ranks in flat fp32 buckets, overlapped with the backward pass.
 
-    def __init__(self, params, group=None):
-        self.params = list(params)
+    One learning pass (the first optimizer step) runs the exchange after the backward and records, per parameter, how
+    many times autograd accumulates into it during one step (a discriminator step calls backward two or three times) and
+    in which order the parameters receive their LAST accumulation.  Buckets of BUCKET_BYTES are then laid out in that
+    order.  From the second step on a post-accumulate hook counts the accumulations; the moment the last parameter of a
+    bucket has its final gradient the bucket is launched on a side stream — ONE multi-tensor copy kernel gathers the
+    gradients into the flat buffer (ganb200_multi_tensor_copy), ncclAllReduce sums it in place — while autograd keeps
+    running the rest of the backward on the main stream.  `__call__` (the optimiser's pre-step hook) launches whatever is
+    left, joins the side stream and points every p.grad at its slice of the reduced flat buffer, which is what the fused
+    Adam then reads: no torch.cat, no per-tensor copy back.  Steps whose accumulation counts differ from the learnt ones
+    (lazy-penalty recipes alternate two step bodies) are detected and exchanged after the backward instead.
+    Under CUDA-graph capture the side-stream work is captured as a fork / join of the graph."""
+
+    def __init__(self, params, group=None, opt=None, overlap=True):
+        self.params = [p for p in params]
         self.group = group
+        self.opt = opt
+        self.overlap = overlap and os.environ.get("GANB200_DP_OVERLAP", "1") != "0"
         self.calls = 0
+        self.expected = None           # {param: accumulations per step}
+        self.buckets = None            # list of dicts: params, offsets, flat, pending, launched
+        self.bucket_of = {}
+        self.count = {}
+        self.order = {}
+        self.seq = 0
+        self.stream = None
+        self.hooks = [p.register_post_accumulate_grad_hook(self._on_grad) for p in self.params if p.requires_grad]
+        self.overlapped_buckets = 0    # buckets launched from inside the backward during the current step
+        self.last_overlapped = 0       # ... during the last finished step (tests / bench)
+
+    def remove(self):
+        for h in self.hooks:
+            h.remove()
+        self.hooks = []
+
+    # ---- hook: runs inside autograd, right after a gradient has been accumulated into p.grad ----------------------
+    def _on_grad(self, p):
+        c = self.count.get(p, 0) + 1
+        self.count[p] = c
+        self.seq += 1
+        self.order[p] = self.seq
+        if self.buckets is None or not self.overlap:
+            return
+        b = self.bucket_of.get(p)
+        if b is None:
+            return
+        if c == self.expected[p]:
+            b["pending"] -= 1
+            if b["pending"] == 0 and not b["launched"]:
+                self._launch(b, overlapped=True)
+        elif c > self.expected[p]:
+            b["dirty"] = True          # more accumulations than learnt: whatever was sent is stale, redo after backward
+
+    def _launch(self, b, overlapped):
+        from . import kernels as KN
+        dev = b["flat"].device
+        cur = torch.cuda.current_stream(dev) if dev.type == "cuda" else None
+        if cur is not None:
+            if self.stream is None:
+                self.stream = torch.cuda.Stream(device=dev)
+            ev = torch.cuda.Event()
+            ev.record(cur)
+            self.stream.wait_event(ev)
+        ctx = torch.cuda.stream(self.stream) if cur is not None else _null()
+        with ctx:
+            entries = [(b["flat"][o:o + p.numel()].view_as(p), p.grad if p.grad.is_contiguous() else p.grad.contiguous(),
+                        None, None) for p, o in zip(b["params"], b["offsets"])]
+            if dev.type == "cuda" and self.opt is not None:
+                tab, blk, n_blocks = self.opt._table(("gather", id(self), b["index"]),
+                                                     [(d, g, d, d) for d, g, _, _ in entries], dev)
+                from .optim import CHUNK
+                KN.backend().multi_tensor_copy(tab, blk, n_blocks, CHUNK, stream=self.stream)
+            else:   # CPU / gloo tests
+                for d, g, _, _ in entries:
+                    d.copy_(g)
+            CALLS[0] += 1
+            b["work"] = dist.all_reduce(b["flat"], op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+        b["launched"] = True
+        b["dirty"] = False
+        if overlapped:
+            self.overlapped_buckets += 1
+
+    def _learn(self, live):
+        """lay the buckets out in the order the parameters received their final gradient"""
+        live = sorted(live, key=lambda p: self.order.get(p, 0))
+        self.expected = {p: self.count.get(p, 0) for p in live}
+        self.buckets, self.bucket_of = [], {}
+        cur, nbytes = [], 0
+        for p in live:
+            cur.append(p)
+            nbytes += p.numel() * 4
+            if nbytes >= BUCKET_BYTES:
+                self._new_bucket(cur)
+                cur, nbytes = [], 0
+        if cur:
+            self._new_bucket(cur)
+
+    def _new_bucket(self, params):
+        offs, n = [], 0
+        for p in params:
+            offs.append(n)
+            n += (p.numel() + 3) // 4 * 4       # 16-byte aligned slices: the copy and Adam kernels stay vectorised
+        b = {"index": len(self.buckets), "params": list(params), "offsets": offs,
+             "flat": torch.zeros(n, dtype=params[0].dtype, device=params[0].device), "pending": len(params),
+             "launched": False, "dirty": False, "work": None}
+        self.buckets.append(b)
+        for p in params:
+            self.bucket_of[p] = b
 
     def __call__(self):
         world = dist.get_world_size(self.group)
         if world == 1:
             return
         live = [p for p in self.params if p.grad is not None]
-        bucket, nbytes = [], 0
-        handles = []
-        for p in live:
-            bucket.append(p.grad)
-            nbytes += p.grad.numel() * 4
-            if nbytes >= BUCKET_BYTES:
-                handles.append(self._launch(bucket))
-                bucket, nbytes = [], 0
-        if bucket:
-            handles.append(self._launch(bucket))
-        for flat, grads, work in handles:
-            work.wait()
-            off = 0
-            for g in grads:
-                n = g.numel()
-                g.copy_(flat[off:off + n].view_as(g))
-                off += n
+        if self.buckets is None or set(live) != set(self.expected):
+            self._learn(live)          # first step (or the set of live parameters changed): exchange everything now
+        for b in self.buckets:
+            if b["dirty"] or not b["launched"] or any(self.count.get(p, 0) != self.expected[p] for p in b["params"]):
+                if b["launched"] and b["work"] is not None:
+                    b["work"].wait()
+                self._launch(b, overlapped=False)
+        for b in self.buckets:
+            b["work"].wait()           # the current stream waits for NCCL's stream
+            if self.stream is not None:
+                torch.cuda.current_stream(b["flat"].device).wait_stream(self.stream)
+            for p, o in zip(b["params"], b["offsets"]):
+                p.grad = b["flat"][o:o + p.numel()].view_as(p)
+            b["pending"], b["launched"], b["work"] = len(b["params"]), False, None
+        self.count.clear()
+        self.order.clear()
+        self.seq = 0
         self.calls += 1
+        self.last_overlapped, self.overlapped_buckets = self.overlapped_buckets, 0
 
-    def _launch(self, grads):
-        flat = torch.cat([g.reshape(-1) for g in grads])
-        CALLS[0] += 1
-        work = dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
-        return flat, grads, work
+
+class _null:
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        return False
 
 
 class DataParallelStep:
@@ -122,7 +228,7 @@ class DataParallelStep:
         T, world, group = self.T, self.world, self.group
         for opt, net in ((T.optimizer_G, T.generator), (T.optimizer_D, T.discriminator)):
             opt.grad_scale = 1.0 / world
-            opt.pre_step = GradSync(net.parameters(), group)
+            opt.pre_step = GradSync(net.parameters(), group, opt=opt, overlap=self.T.recipe.lazy == 1)
         ops._mbstd_reduce[0] = lambda s: AllReduceMeanFn.apply(s, group)
         if self.sync_bn:
             def stats(mean, var, count):
@@ -148,4 +254,6 @@ class DataParallelStep:
         ops._sync_bn_hooks["stats"] = ops._sync_bn_hooks["grads"] = None
         for opt in (self.T.optimizer_G, self.T.optimizer_D):
             opt.grad_scale = 1.0
+            if isinstance(opt.pre_step, GradSync):
+                opt.pre_step.remove()
             opt.pre_step = None

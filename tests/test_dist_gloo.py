@@ -11,6 +11,7 @@ import torch
 import torch.multiprocessing as mp
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ITERS = 2
 
 
 def _build():
@@ -85,31 +86,38 @@ def _step(rank, world, B, out_dir, port):
     G, D = G.double(), D.double()
     gen = torch.Generator().manual_seed(5)
     images = torch.randn(B, 3, 4, 4, generator=gen, dtype=torch.float64)
-    zs = torch.randn(2, B, 8, 1, 1, generator=gen, dtype=torch.float64)
-    eps = torch.rand(B, generator=gen, dtype=torch.float64)
+    zs = torch.randn(2 * ITERS, B, 8, 1, 1, generator=gen, dtype=torch.float64)
+    eps = torch.rand(ITERS, B, generator=gen, dtype=torch.float64)
     if world > 1:
-        images, eps = (gdist.shard_quarter_major(t, rank, world) for t in (images, eps))
-        zs = torch.stack([gdist.shard_quarter_major(zs[i], rank, world) for i in range(2)])
+        images = gdist.shard_quarter_major(images, rank, world)
+        eps = torch.stack([gdist.shard_quarter_major(eps[i], rank, world) for i in range(ITERS)])
+        zs = torch.stack([gdist.shard_quarter_major(zs[i], rank, world) for i in range(2 * ITERS)])
     Bl = images.shape[0]
     T = wgangpR2.Train([(images, torch.zeros(Bl))], torch.device("cpu"), 1, 8, G, "g", D, "d")
     dp = gdist.DataParallelStep(T).install() if world > 1 else None
     # feed the same z / eps to both layouts: patch the draws of the step
-    draws = iter([zs[0], eps, zs[1]])
+    draws = iter([t for i in range(ITERS) for t in (zs[2 * i], eps[i], zs[2 * i + 1])])
     orig_randn, orig_rand = rng.randn, rng.rand
     rng.randn = lambda *s, device=None: next(draws)
     rng.rand = lambda *s, device=None: next(draws)
+    overlapped = []
     try:
-        d_out = T.discriminator_trainstep(images.clone().requires_grad_(), Bl)
-        d_grads = {n: p.grad.clone() for n, p in D.named_parameters() if p.grad is not None}
-        _, g_loss = T.generator_trainstep(Bl)
-        g_grads = {n: p.grad.clone() for n, p in G.named_parameters() if p.grad is not None}
+        # iteration 1 is the learning pass of the bucketed all-reduce (exchange after the backward); from iteration 2 on
+        # the buckets are launched from inside the backward (gan_b200.dist.GradSync)
+        for _ in range(ITERS):
+            d_out = T.discriminator_trainstep(images.clone().requires_grad_(), Bl)
+            d_grads = {n: p.grad.clone() for n, p in D.named_parameters() if p.grad is not None}
+            _, g_loss = T.generator_trainstep(Bl)
+            g_grads = {n: p.grad.clone() for n, p in G.named_parameters() if p.grad is not None}
+            if dp is not None:
+                overlapped.append((T.optimizer_D.pre_step.last_overlapped, T.optimizer_G.pre_step.last_overlapped))
     finally:
         rng.randn, rng.rand = orig_randn, orig_rand
     res = {"d_losses": [float(v) for v in d_out], "g_loss": float(g_loss),
            "d_params": {n: p.detach().clone() for n, p in D.named_parameters()},
            "g_params": {n: p.detach().clone() for n, p in G.named_parameters()},
            "bn_mean": G.bn2.running_mean.clone(), "bn_var": G.bn2.running_var.clone(),
-           "d_grads": d_grads, "g_grads": g_grads}
+           "d_grads": d_grads, "g_grads": g_grads, "overlapped": overlapped}
     if dp is not None:
         dp.remove()
         dist.barrier()
@@ -139,6 +147,7 @@ def test_two_rank_data_parallel_equals_single_rank_big_batch(tmp_path):
         for key in ("d_params", "g_params"):
             for n, v in single[key].items():
                 assert torch.allclose(m[key][n], v, rtol=1e-9, atol=1e-12), (key, n, (m[key][n] - v).abs().max())
+        assert m["overlapped"][0] == (0, 0) and m["overlapped"][1][0] >= 1 and m["overlapped"][1][1] >= 1, m["overlapped"]
         assert torch.allclose(m["bn_mean"], single["bn_mean"], atol=1e-12)
         assert torch.allclose(m["bn_var"], single["bn_var"], atol=1e-12)
     # rank-local losses are means over the shard: their average is the global mean (GP/R1/R2 included)

@@ -14,6 +14,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
 
 pytestmark = pytest.mark.gpu
+ITERS = 2
 
 
 def _step(rank, world, B, out_dir, port):
@@ -33,30 +34,38 @@ def _step(rank, world, B, out_dir, port):
     G, D = G.to(dev), D.to(dev)
     gen = torch.Generator().manual_seed(5)
     images = torch.randn(B, 3, 4, 4, generator=gen)
-    zs = torch.randn(2, B, 8, 1, 1, generator=gen)
-    eps = torch.rand(B, generator=gen)
+    zs = torch.randn(2 * ITERS, B, 8, 1, 1, generator=gen)
+    eps = torch.rand(ITERS, B, generator=gen)
     if world > 1:
-        images, eps = (gdist.shard_quarter_major(t, rank, world) for t in (images, eps))
-        zs = torch.stack([gdist.shard_quarter_major(zs[i], rank, world) for i in range(2)])
+        images = gdist.shard_quarter_major(images, rank, world)
+        eps = torch.stack([gdist.shard_quarter_major(eps[i], rank, world) for i in range(ITERS)])
+        zs = torch.stack([gdist.shard_quarter_major(zs[i], rank, world) for i in range(2 * ITERS)])
     images, zs, eps = images.to(dev), zs.to(dev), eps.to(dev)
     Bl = images.shape[0]
     T = wgangpR2.Train([(images, torch.zeros(Bl))], dev, 1, 8, G, "g", D, "d")
     dp = gdist.DataParallelStep(T).install() if world > 1 else None
-    draws = iter([zs[0].contiguous(), eps.contiguous(), zs[1].contiguous()])
+    draws = iter([t.contiguous() for i in range(ITERS) for t in (zs[2 * i], eps[i], zs[2 * i + 1])])
     orig_randn, orig_rand = rng.randn, rng.rand
     rng.randn = lambda *s, device=None: next(draws)
     rng.rand = lambda *s, device=None: next(draws)
+    overlapped = []
     try:
-        d_out = T.discriminator_trainstep(images.clone().requires_grad_(), Bl)
-        d_grads = {n: p.grad.detach().cpu() / world for n, p in D.named_parameters() if p.grad is not None}
-        _, g_loss = T.generator_trainstep(Bl)
-        g_grads = {n: p.grad.detach().cpu() / world for n, p in G.named_parameters() if p.grad is not None}
+        # iteration 1: learning pass of the bucketed all-reduce; iteration 2: buckets launched from inside the backward
+        for _ in range(ITERS):
+            d_out = T.discriminator_trainstep(images.clone().requires_grad_(), Bl)
+            d_grads = {n: p.grad.detach().cpu() / world for n, p in D.named_parameters() if p.grad is not None}
+            _, g_loss = T.generator_trainstep(Bl)
+            g_grads = {n: p.grad.detach().cpu() / world for n, p in G.named_parameters() if p.grad is not None}
+            if dp is not None:
+                overlapped.append((T.optimizer_D.pre_step.last_overlapped, T.optimizer_G.pre_step.last_overlapped))
     finally:
         rng.randn, rng.rand = orig_randn, orig_rand
     torch.cuda.synchronize()
     res = {"d_losses": [float(v) for v in d_out], "g_loss": float(g_loss),
            "bn_mean": G.bn2.running_mean.cpu(), "bn_var": G.bn2.running_var.cpu(),
-           "d_grads": d_grads, "g_grads": g_grads, "calls": gdist.CALLS[0]}
+           "d_grads": d_grads, "g_grads": g_grads, "calls": gdist.CALLS[0], "overlapped": overlapped,
+           "d_params": {n: p.detach().cpu() for n, p in D.named_parameters()},
+           "g_params": {n: p.detach().cpu() for n, p in G.named_parameters()}}
     if dp is not None:
         dp.remove()
         dist.barrier()
@@ -94,6 +103,10 @@ def test_two_rank_nccl_step_equals_single_rank_big_batch(tmp_path):
         assert torch.allclose(m["bn_mean"], single["bn_mean"], atol=1e-6)
         assert torch.allclose(m["bn_var"], single["bn_var"], rtol=1e-5, atol=1e-6)
         assert m["calls"] > 0
+        assert m["overlapped"][0] == (0, 0) and m["overlapped"][1][0] >= 1 and m["overlapped"][1][1] >= 1, m["overlapped"]
+        for key in ("d_params", "g_params"):   # after two Adam updates (a sign flip of a ~0 gradient moves an element by 2 lr)
+            for n, v in single[key].items():
+                assert float((m[key][n] - v).norm()) <= 1e-4 * max(float(v.norm()), 1.0), (key, n)
     for i, v in enumerate(single["d_losses"]):
         avg = 0.5 * (multi[0]["d_losses"][i] + multi[1]["d_losses"][i])
         assert abs(avg - v) <= 1e-5 * max(1.0, abs(v)), (i, avg, v)
