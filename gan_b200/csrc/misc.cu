@@ -146,8 +146,92 @@ __global__ void __launch_bounds__(256) spectral_scale_bwd_kernel(const float* __
   }
 }
 
+// ------------------------------------------------------------------ preview grid (train/trainunits.py:52-56)
+// out[0] = min(x), out[1] = max(x).  One CTA: the preview batch is at most a few MB, and one CTA keeps the result
+// independent of any launch geometry.
+__global__ void __launch_bounds__(1024) minmax_kernel(const float* __restrict__ x, int64_t n, float* __restrict__ out) {
+  float lo = INFINITY, hi = -INFINITY;
+  for (int64_t i = threadIdx.x; i < n; i += 1024) {
+    const float v = x[i];
+    lo = fminf(lo, v);
+    hi = fmaxf(hi, v);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+    hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+  }
+  __shared__ float slo[32], shi[32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane == 0) { slo[warp] = lo; shi[warp] = hi; }
+  __syncthreads();
+  if (warp == 0) {
+    lo = slo[lane]; hi = shi[lane];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+      hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+    }
+    if (lane == 0) { out[0] = lo; out[1] = hi; }
+  }
+}
+
+// torchvision.utils.make_grid(x, nrow, padding, normalize=True) followed by save_image's quantisation, as ONE pass that
+// writes the uint8 HWC image a PNG encoder takes:
+//   v = (clamp(x, lo, hi) - lo) / max(hi - lo, 1e-5);  pixel = (uint8) clamp(v * 255 + 0.5, 0, 255);  padding pixels = 0.
+// The arithmetic is torch's, operation by operation (fp32 subtract, IEEE divide, multiply, add — no FMA contraction, the
+// divisor formed in double like the Python expression), so the bytes equal torchvision's.
+__global__ void __launch_bounds__(256) make_grid_u8_kernel(const float* __restrict__ x, const float* __restrict__ mm,
+                                                           unsigned char* __restrict__ out, int N, int C, int H, int W,
+                                                           int xmaps, int ymaps, int pad) {
+  const int cell_h = H + pad, cell_w = W + pad;
+  const int GH = (N == 1) ? H : cell_h * ymaps + pad, GW = (N == 1) ? W : cell_w * xmaps + pad;
+  const float lo = mm[0], hi = mm[1];
+  const float div = (float)fmax((double)hi - (double)lo, 1e-5);
+  const int64_t total = (int64_t)GH * GW * 3;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int ch = (int)(i % 3);
+    const int gx = (int)((i / 3) % GW), gy = (int)(i / (3 * (int64_t)GW));
+    float v = 0.f;
+    int n = -1, h = 0, w = 0;
+    if (N == 1) { n = 0; h = gy; w = gx; }
+    else {
+      const int cy = gy / cell_h, cx = gx / cell_w;
+      h = gy - cy * cell_h - pad; w = gx - cx * cell_w - pad;
+      if (cy < ymaps && cx < xmaps && h >= 0 && w >= 0 && cy * xmaps + cx < N) n = cy * xmaps + cx;
+    }
+    if (n >= 0) {
+      const float xv = x[(((int64_t)n * C + (C == 1 ? 0 : ch)) * H + h) * W + w];
+      v = __fdiv_rn(__fsub_rn(fminf(fmaxf(xv, lo), hi), lo), div);
+    }
+    float q = __fadd_rn(__fmul_rn(v, 255.f), 0.5f);
+    q = fminf(fmaxf(q, 0.f), 255.f);
+    out[i] = (unsigned char)q;
+  }
+}
+
 }  // namespace ganb200
 using namespace ganb200;
+
+extern "C" int ganb200_minmax(const float* x, int64_t n, float* out2, void* stream) {
+  GB_REQUIRE(n > 0 && x && out2, GANB200_BAD_ARG, "minmax: empty input");
+  minmax_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(x, n, out2);
+  GB_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int ganb200_make_grid_u8(const float* x, const float* minmax, unsigned char* out, int N, int C, int H, int W,
+                                    int nrow, int padding, void* stream) {
+  GB_REQUIRE(N > 0 && H > 0 && W > 0 && (C == 1 || C == 3), GANB200_BAD_SHAPE, "make_grid_u8: need [N,1|3,H,W]");
+  GB_REQUIRE(nrow > 0 && padding >= 0, GANB200_BAD_ARG, "make_grid_u8: nrow > 0, padding >= 0");
+  const int xmaps = nrow < N ? nrow : N, ymaps = (N + xmaps - 1) / xmaps;
+  const int64_t GH = N == 1 ? H : (int64_t)(H + padding) * ymaps + padding;
+  const int64_t GW = N == 1 ? W : (int64_t)(W + padding) * xmaps + padding;
+  make_grid_u8_kernel<<<ew_grid(GH * GW * 3, 256, 4), 256, 0, (cudaStream_t)stream>>>(x, minmax, out, N, C, H, W, xmaps,
+                                                                                    ymaps, padding);
+  GB_CHECK_LAUNCH();
+  return 0;
+}
 
 extern "C" int ganb200_chan_copy(const float* src, float* dst, int N, int src_C, int src_c0, int dst_C, int dst_c0,
                                  int ncopy, int HW, int accumulate, void* stream) {

@@ -25,7 +25,10 @@ _ENGINE = {"auto": 0, "fp32": 1, "simt": 1, "bf16": 0, "tc": 2}
 
 
 def default_engine():
-    return _ENGINE[os.environ.get("GANB200_PRECISION", "auto")]
+    v = os.environ.get("GANB200_PRECISION", "auto")
+    if v not in _ENGINE:
+        raise ValueError(f"GANB200_PRECISION={v!r}: expected one of {sorted(_ENGINE)}")
+    return _ENGINE[v]
 
 
 LAUNCH_COUNT = [0]  # number of libganb200 kernel-launching calls (bench.py reports it as gpu_launches)
@@ -75,14 +78,14 @@ class CudaBackend:
         self._ws = {}
 
     # -- plumbing -------------------------------------------------------------------------------
-    def _prep(self, *tensors):
+    def _prep(self, *tensors, allow_f64=False):
         dev = None
         for t in tensors:
             if t is None:
                 continue
             if not t.is_cuda:
                 raise _lib.GanB200Error("gan_b200 kernels need CUDA tensors (there is no CPU fallback)")
-            if t.dtype != torch.float32 and t.dtype not in (torch.int32, torch.float64):
+            if t.dtype != torch.float32 and t.dtype != torch.int32 and not (allow_f64 and t.dtype == torch.float64):
                 raise _lib.GanB200Error(f"gan_b200 kernels are float32, got {t.dtype}")
             if not t.is_contiguous():
                 raise _lib.GanB200Error("gan_b200 kernels need contiguous tensors")
@@ -595,6 +598,21 @@ class CudaBackend:
         LAUNCH_COUNT[0] += 1
         _lib.check(self.lib.ganb200_multi_tensor_copy(self._p(tab), self._p(block_tab), n_blocks, chunk, st))
 
+    def make_grid_u8(self, x, nrow=8, padding=2):
+        """torchvision make_grid(normalize=True) + save_image quantisation on the device -> uint8 [GH, GW, 3]"""
+        N, C, H, W = x.shape
+        st = self._prep(x)
+        LAUNCH_COUNT[0] += 1
+        mm = torch.empty((2,), dtype=torch.float32, device=x.device)
+        _lib.check(self.lib.ganb200_minmax(self._p(x), x.numel(), self._p(mm), st))
+        xm = min(nrow, N)
+        ym = (N + xm - 1) // xm
+        gh, gw = (H, W) if N == 1 else ((H + padding) * ym + padding, (W + padding) * xm + padding)
+        out = torch.empty((gh, gw, 3), dtype=torch.uint8, device=x.device)
+        _lib.check(self.lib.ganb200_make_grid_u8(self._p(x), self._p(mm), ctypes.c_void_p(out.data_ptr()), N, C, H, W,
+                                                 nrow, padding, st))
+        return out
+
     def counter_add(self, ctr, inc):
         st = ctypes.c_void_p(torch.cuda.current_stream(ctr.device).cuda_stream)
         LAUNCH_COUNT[0] += 1
@@ -618,7 +636,7 @@ class CudaBackend:
 
     def mixup_wgan_f64(self, label, t, f):
         B, C, H, W = t.shape
-        st = self._prep(label, t, f)
+        st = self._prep(label, t, f, allow_f64=True)   # the reference's float64 label quirk (units/mixup.py:19-27)
         out = torch.empty(t.shape, dtype=torch.float64, device=t.device)
         _lib.check(self.lib.ganb200_mixup_wgan_f64(self._p(label), self._p(t), self._p(f), self._p(out), B, C, H, W, st))
         return out
@@ -663,10 +681,36 @@ class CudaBackend:
 _backend = None
 
 
+def _nvtx_wrap(obj):
+    """GANB200_NVTX=1: an NVTX range per kernel-class call (range name = the backend method: conv_fprop, bn_small_fwd,
+    style_tail_bwd, linear_group, ...), so that an nsys / ncu timeline groups the launches of one logical operator.
+    Off by default: ~1 us of host time per call."""
+    import functools
+    nv = torch.cuda.nvtx
+    for name in dir(obj):
+        fn = getattr(obj, name)
+        if name.startswith("_") or not callable(fn) or name in ("bn_small_ok",):
+            continue
+
+        def make(f, label):
+            @functools.wraps(f)
+            def wrapped(*a, **k):
+                nv.range_push(label)
+                try:
+                    return f(*a, **k)
+                finally:
+                    nv.range_pop()
+            return wrapped
+        setattr(obj, name, make(fn, "ganb200." + name))
+    return obj
+
+
 def backend():
     global _backend
     if _backend is None:
         _backend = CudaBackend()
+        if os.environ.get("GANB200_NVTX") == "1":
+            _nvtx_wrap(_backend)
     return _backend
 
 

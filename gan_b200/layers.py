@@ -56,7 +56,10 @@ class _BatchNormMixin:
             n, _, hw = KN._nchw(x)
             if n * hw <= 1:
                 raise ValueError(f"Expected more than 1 value per channel when training, got input size {x.size()}")
-            momentum = 0.0 if self.momentum is None else self.momentum
+            if self.momentum is None:
+                raise NotImplementedError("BatchNorm(momentum=None) (cumulative moving average) is not implemented; the "
+                                          "reference's models all use the default momentum 0.1")
+            momentum = self.momentum
             track = self.training and self.track_running_stats
             return ops.batch_norm_train(x, self.weight, self.bias,
                                         self.running_mean if track else None, self.running_var if track else None,

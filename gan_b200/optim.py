@@ -35,7 +35,7 @@ class FusedAdam(torch.optim.Optimizer):
         """entries: list of (p, g, m, v) tensors -> (device table, device block map, n_blocks).
         The pinned staging buffers and the device tables are allocated once per key and re-filled when a pointer
         changes, so that no host allocation happens while a CUDA graph is being captured."""
-        sig = tuple((p.data_ptr(), g.data_ptr()) for p, g, _, _ in entries)
+        sig = tuple((p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr(), p.numel()) for p, g, m, v in entries)
         hit = self._cache.get(key)
         if hit is not None and hit["sig"] == sig:
             return hit["tab"], hit["blk"], hit["n_blocks"]
@@ -45,13 +45,18 @@ class FusedAdam(torch.optim.Optimizer):
             vals += [p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr(), numel]
             blocks += [(i, c) for c in range((numel + CHUNK - 1) // CHUNK)]
         cuda = device.type == "cuda"
-        if hit is None or hit["tab_host"].numel() != len(vals) or hit["blk_host"].numel() != 2 * len(blocks):
+        rebuilt = hit is None or hit["tab_host"].numel() != len(vals) or hit["blk_host"].numel() != 2 * len(blocks)
+        if rebuilt:
             hit = {"tab_host": torch.empty(len(vals), dtype=torch.int64, pin_memory=cuda),
                    "blk_host": torch.empty((len(blocks), 2), dtype=torch.int32, pin_memory=cuda),
                    "tab": torch.empty(len(vals), dtype=torch.int64, device=device),
                    "blk": torch.empty((len(blocks), 2), dtype=torch.int32, device=device), "event": None}
+        if rebuilt or hit.get("blocks") != blocks:
+            # the CTA -> (tensor, chunk) map follows the SIZES of the entries: re-uploaded whenever they change, also when the
+            # entry and block counts happen to stay the same (a different set of live parameters)
             hit["blk_host"].copy_(torch.tensor(blocks, dtype=torch.int32).reshape(-1, 2))
             hit["blk"].copy_(hit["blk_host"], non_blocking=True)
+            hit["blocks"] = blocks
         capturing = cuda and torch.cuda.is_current_stream_capturing()
         if hit["event"] is not None and not capturing:  # (a capture starts after a device synchronize)
             hit["event"].synchronize()  # the previous async upload has read the staging buffer
@@ -87,6 +92,9 @@ class FusedAdam(torch.optim.Optimizer):
                     continue
                 if p.grad.is_sparse:
                     raise RuntimeError("FusedAdam does not support sparse gradients")
+                if p.dtype != torch.float32 or not p.is_contiguous():
+                    raise RuntimeError(f"FusedAdam updates contiguous float32 parameters, got {p.dtype} "
+                                       f"{'contiguous' if p.is_contiguous() else 'strided'} {tuple(p.shape)}")
                 st = self.state[p]
                 if len(st) == 0:
                     st["step"] = 0
@@ -105,10 +113,11 @@ class FusedAdam(torch.optim.Optimizer):
                 tab, blk, n_blocks = self._table((gi, 0 if len(by_step) == 1 else step), entries, device)
                 step_dev = None
                 if self.capturable:
-                    step_dev = self._step_dev.get(gi)
+                    dkey = (gi, 0 if len(by_step) == 1 else step)   # one device counter per (group, step-count bucket)
+                    step_dev = self._step_dev.get(dkey)
                     if step_dev is None:
                         step_dev = torch.full((1,), step - 1, dtype=torch.int64, device=device)
-                        self._step_dev[gi] = step_dev
+                        self._step_dev[dkey] = step_dev
                     k.counter_add(step_dev, 1)
                 k.adam_blocks(tab, blk, n_blocks, CHUNK, group["lr"], b1, b2, group["eps"], group["weight_decay"],
                               group["decoupled"], step, self.grad_scale, step_dev=step_dev)

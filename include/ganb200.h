@@ -235,6 +235,16 @@ int ganb200_bn1d_group_bwd_apply(const ganb200_gbn_job* jobs, int n_jobs, int n_
                                  const float* x_base, float* gx_base, int N, const float* mean, const float* invstd,
                                  const float* s1, const float* s2, int64_t count_total, float* gbias, void* stream);
 
+/* Preview grid of the sampling path (train/trainunits.py:52-56: generator(fixed_noise) -> torchvision
+ * make_grid(padding=2, normalize=True) -> save_image).  minmax: out2 = {min(x), max(x)} over all n elements.
+ * make_grid_u8: x [N,C,H,W] fp32 (C = 1 is shown as grey, like torchvision) -> out uint8 [GH][GW][3], the bytes torchvision's
+ * save_image would hand to the PNG encoder: v = (clamp(x,min,max) - min) / max(max - min, 1e-5), pixel =
+ * (uint8)clamp(v*255 + 0.5, 0, 255), padding pixels 0; GH = (H+padding)*ceil(N/nrow) + padding, GW = (W+padding)*min(nrow,N)
+ * + padding, and the bare image when N == 1. */
+int ganb200_minmax(const float* x, int64_t n, float* out2, void* stream);
+int ganb200_make_grid_u8(const float* x, const float* minmax, unsigned char* out, int N, int C, int H, int W, int nrow,
+                         int padding, void* stream);
+
 /* BCELoss, mean reduction, log clamped at -100 (torch.nn.BCELoss, train/gan.py:21, ganR2.py:17).
  * range_flag[0] is set to 1 if any p is outside [0,1] (the caller raises, as the reference does). */
 int ganb200_bce_fwd(const float* p, const float* t, float* out, int* range_flag, int64_t n, void* stream);

@@ -379,6 +379,27 @@ class RefBackend:
         Pm = (ga * u.clamp(max=0)).reshape(N, K, -1).sum(-1) if slope is not None else None
         return gu, Ad, Z, Pm
 
+    def make_grid_u8(self, x, nrow=8, padding=2):
+        """torchvision.utils.make_grid(normalize=True) + save_image's quantisation, restated op by op (the GPU test and
+        tests/test_units.py compare it with torchvision itself)."""
+        t = x.detach().clone().float()
+        if t.shape[1] == 1:
+            t = torch.cat((t, t, t), 1)
+        lo, hi = float(t.min()), float(t.max())
+        t.clamp_(min=lo, max=hi)
+        t.sub_(lo).div_(max(hi - lo, 1e-5))
+        n, c, h, w = t.shape
+        if n == 1:
+            grid = t[0]
+        else:
+            xm = min(nrow, n)
+            ym = (n + xm - 1) // xm
+            grid = t.new_zeros((c, (h + padding) * ym + padding, (w + padding) * xm + padding))
+            for k in range(n):
+                y0, x0 = (k // xm) * (h + padding) + padding, (k % xm) * (w + padding) + padding
+                grid[:, y0:y0 + h, x0:x0 + w] = t[k]
+        return grid.mul(255).add_(0.5).clamp_(0, 255).permute(1, 2, 0).to(torch.uint8).contiguous()
+
     def scale_reduce(self, dxs, s, x, need_gx=True, need_gs=True):
         N, C = dxs.shape[:2]
         gx = dxs * s.reshape(N, C, *([1] * (dxs.dim() - 2))) if need_gx else None

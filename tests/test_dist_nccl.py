@@ -100,8 +100,8 @@ def test_two_rank_nccl_step_equals_single_rank_big_batch(tmp_path):
                     continue  # analytically zero gradients (a bias feeding a BatchNorm): rounding noise only
                 rel = float((m[key][n] - v).norm() / v.norm())
                 assert rel <= tol, (key, n, rel)
-        assert torch.allclose(m["bn_mean"], single["bn_mean"], atol=1e-6)
-        assert torch.allclose(m["bn_var"], single["bn_var"], rtol=1e-5, atol=1e-6)
+        assert torch.allclose(m["bn_mean"], single["bn_mean"], rtol=1e-4, atol=1e-6)   # running stats: 0.1 * batch mean, fp32 sums in another order
+        assert torch.allclose(m["bn_var"], single["bn_var"], rtol=1e-4, atol=1e-6)
         assert m["calls"] > 0
         assert m["overlapped"][0] == (0, 0) and m["overlapped"][1][0] >= 1 and m["overlapped"][1][1] >= 1, m["overlapped"]
         for key in ("d_params", "g_params"):   # after two Adam updates (a sign flip of a ~0 gradient moves an element by 2 lr)

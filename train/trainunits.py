@@ -72,13 +72,19 @@ class Units():
             plt.imshow(grid.squeeze().permute(1, 2, 0))
 
     def save_images(self, path, epoch, i):
+        """reference :52-56.  The generator runs in train mode (batch statistics, running stats updated: SURVEY B4).
+        Min/max normalisation, grid assembly and uint8 quantisation happen on the device, the PNG is written by a worker
+        thread once an asynchronous copy has landed (gan_b200/preview.py): same file bytes-for-pixels as the reference's
+        make_grid(padding=2, normalize=True) + save_image, but no device synchronisation in the training loop.
+        GANB200_PREVIEW=sync restores the reference's blocking host path (needs torchvision)."""
         with torch.no_grad():
-            gen_imgs = self.generator(self.fixed_noise).cpu()  # train-mode BN, as in the reference
+            gen_imgs = self.generator(self.fixed_noise)
         target = path + str(epoch) + "-" + str(i)
-        if vutils is None:
-            torch.save(gen_imgs, target + ".pt")
+        if os.environ.get("GANB200_PREVIEW") == "sync" and vutils is not None:
+            vutils.save_image(vutils.make_grid(gen_imgs.cpu(), padding=2, normalize=True).squeeze(), target + ".png")
             return
-        vutils.save_image(vutils.make_grid(gen_imgs, padding=2, normalize=True).squeeze(), target + ".png")
+        from gan_b200 import preview
+        preview.save_grid_async(gen_imgs, target + ".png", nrow=8, padding=2)
 
     # ---- checkpoints (whole-module pickles, reference :58-131; interop rules in gan_b200/checkpoint.py) -----------
     # Opt-in departures from the reference (environment, read at call time):
@@ -99,6 +105,8 @@ class Units():
         if os.environ.get('GANB200_CKPT_OPTIMIZER') == '1':
             state['optimizer_G'] = self.optimizer_G.state_dict()
             state['optimizer_D'] = self.optimizer_D.state_dict()
+        from gan_b200 import rng
+        state['ganb200_noise_rng'] = rng.state_dict()   # {device: [seed, forward counter]} of the in-kernel noise stream
         os.makedirs('checkpoint', exist_ok=True)
         torch.save(state, './checkpoint/' + stem + '_ckpt.pth')
 
@@ -122,6 +130,12 @@ class Units():
         print(what + ' ' + checkpoint[what + '_name'])
         print(what + ' epoch: ', checkpoint['epoch'])
         print(what + ' i: ', checkpoint['i'])
+        if what == 'generator' and checkpoint.get('ganb200_noise_rng'):
+            from gan_b200 import rng
+            try:
+                rng.load_state_dict(checkpoint['ganb200_noise_rng'])   # a resume continues the same noise stream
+            except Exception:
+                pass   # written on another device layout: start a fresh stream
         return checkpoint
 
     def _adopt(self, checkpoint, what, live, optimizer, opt_key):
