@@ -56,6 +56,14 @@ SIGNATURES = {
     "ganb200_conv2d_fprop": (c_int, [_DESC_P, P, P, P, P, P, P, P, c_size_t, P]),
     "ganb200_conv2d_dgrad": (c_int, [_DESC_P, P, P, P, P, P, P, c_size_t, P]),
     "ganb200_conv2d_wgrad": (c_int, [_DESC_P, P, P, P, P, P, P, c_size_t, P]),
+    "ganb200_tc_packed_act_bytes": (c_size_t, [c_int, c_int, c_int, c_int, c_int]),
+    "ganb200_tc_pack_act": (c_int, [P, P, P, c_int, c_int, c_int, c_int, c_int, P]),
+    "ganb200_conv2d_packed_weight_bytes": (c_size_t, [_DESC_P, c_int]),
+    "ganb200_conv2d_pack_weight": (c_int, [_DESC_P, c_int, P, P, P]),
+    "ganb200_conv2d_fprop_pk": (c_int, [_DESC_P, P, P, P, P, P, P]),
+    "ganb200_conv2d_dgrad_pk": (c_int, [_DESC_P, P, P, P, P, P, P, P, P, c_size_t, P]),
+    "ganb200_conv2d_wgrad_pk": (c_int, [_DESC_P, P, P, P, P, P, P, P, P, c_size_t, P]),
+    "ganb200_modconv_bwd_pk": (c_int, [_DESC_P, P, P, P, P, P, P, P, P, P, P, c_size_t, P]),
     "ganb200_resample2d": (c_int, [P, P, c_int, c_int, c_int, c_int, c_int, P, P, c_int, P, P, c_int, P]),
     "ganb200_ew_unary": (c_int, [c_int, P, P, c_int64, c_float, c_float, P]),
     "ganb200_ew_binary": (c_int, [c_int, P, P, P, c_int64, c_float, P]),

@@ -54,10 +54,16 @@ int fold_replicate(const float* dxp, float* dx, int64_t NC, int H, int W, int pa
 int tc_eligible(const ganb200_conv_desc* d, int op);
 size_t tc_workspace(const ganb200_conv_desc* d, int op);
 int tc_fprop(const ganb200_conv_desc* d, const float* x, const float* w, const float* bias, const float* iscale,
-             const float* oscale, float* y, void* ws, size_t ws_bytes, cudaStream_t s);
+             const float* oscale, float* y, void* ws, size_t ws_bytes, cudaStream_t s, const void* xp = nullptr,
+             const void* wp = nullptr);
 int tc_dgrad(const ganb200_conv_desc* d, const float* dy, const float* w, const float* iscale, const float* oscale,
-             float* dx, void* ws, size_t ws_bytes, cudaStream_t s);
+             float* dx, void* ws, size_t ws_bytes, cudaStream_t s, const void* dyp = nullptr, const void* wp = nullptr);
 int tc_wgrad(const ganb200_conv_desc* d, const float* x, const float* dy, const float* iscale, const float* oscale,
-             float* dw, void* ws, size_t ws_bytes, cudaStream_t s);
+             float* dw, void* ws, size_t ws_bytes, cudaStream_t s, const void* xp = nullptr, const void* dyp = nullptr);
+// packed bf16 operands of the engine as caller-owned buffers (conv_tc.cu)
+size_t tc_packed_act_bytes(int N, int C, int H, int W, int pad);
+int tc_pack_act(const float* x, const float* scale, void* out, int N, int C, int H, int W, int pad, cudaStream_t s);
+size_t tc_packed_weight_bytes(const ganb200_conv_desc* d, int op);
+int tc_pack_weight(const ganb200_conv_desc* d, int op, const float* w, void* out, cudaStream_t s);
 
 }  // namespace ganb200

@@ -709,9 +709,9 @@ static int launch_halo(const CUtensorMap& ta, const CUtensorMap& tb, const TcHal
 
 // `act`: the packed input; `wb`: scratch for this problem's packed weights
 static int run_problem(const TcProblem& q, const __nv_bfloat16* act, const float* w, __nv_bfloat16* wb, float* out,
-                       const float* out_scale, const float* bias, cudaStream_t s) {
+                       const float* out_scale, const float* bias, cudaStream_t s, bool w_packed = false) {
   const int Cp = cpad(q.Ci), Hp = q.Hi + 2 * q.mat_pad, Wp = q.Wi + 2 * q.mat_pad, NT = q.taps.n;
-  {
+  if (!w_packed) {
     int64_t total = (int64_t)NT * q.Ko * Cp;
     pack_weight_kernel<<<ew_grid(total, 256, 1), 256, 0, s>>>(w, wb, q.Ko, q.Ci, Cp, q.w_sk, q.w_sc, q.taps);
     GB_CHECK_LAUNCH();
@@ -869,47 +869,96 @@ size_t tc_workspace(const ganb200_conv_desc* d, int op) {
 }
 
 int tc_fprop(const ganb200_conv_desc* d, const float* x, const float* w, const float* bias, const float* iscale,
-             const float* oscale, float* y, void* ws, size_t ws_bytes, cudaStream_t s) {
-  GB_REQUIRE(ws && ws_bytes >= tc_workspace(d, GANB200_CONV_FPROP), GANB200_WORKSPACE_TOO_SMALL,
+             const float* oscale, float* y, void* ws, size_t ws_bytes, cudaStream_t s, const void* xp, const void* wp) {
+  GB_REQUIRE((xp && wp) || (ws && ws_bytes >= tc_workspace(d, GANB200_CONV_FPROP)), GANB200_WORKSPACE_TOO_SMALL,
              "tc fprop: workspace too small");
   ws = align_ws(ws);
   TcProblem q = fprop_problem(d);
-  __nv_bfloat16* act = (__nv_bfloat16*)ws;
-  __nv_bfloat16* wb = (__nv_bfloat16*)((uint8_t*)ws + act_bytes(q.N, q.Ci, q.Hi, q.Wi, q.mat_pad));
-  int rc = pack_input(x, iscale, act, q.N, q.Ci, q.Hi, q.Wi, q.mat_pad, s);
-  if (rc) return rc;
-  return run_problem(q, act, w, wb, y, oscale, bias, s);
+  __nv_bfloat16* act = xp ? (__nv_bfloat16*)xp : (__nv_bfloat16*)ws;
+  __nv_bfloat16* wb = wp ? (__nv_bfloat16*)wp
+                         : (__nv_bfloat16*)((uint8_t*)ws + act_bytes(q.N, q.Ci, q.Hi, q.Wi, q.mat_pad));
+  if (!xp) {
+    int rc = pack_input(x, iscale, act, q.N, q.Ci, q.Hi, q.Wi, q.mat_pad, s);
+    if (rc) return rc;
+  }
+  return run_problem(q, act, w, wb, y, oscale, bias, s, wp != nullptr);
+}
+
+// ---- packed operands as first-class buffers (cached by the caller across the passes that share them) ----------------
+size_t tc_packed_act_bytes(int N, int C, int H, int W, int pad) { return act_bytes(N, C, H, W, pad) + 1024; }
+
+int tc_pack_act(const float* x, const float* scale, void* out, int N, int C, int H, int W, int pad, cudaStream_t s) {
+  GB_REQUIRE(((uintptr_t)out & 1023) == 0, GANB200_BAD_ARG, "pack_act: output must be 1024-byte aligned");
+  return pack_input(x, scale, (__nv_bfloat16*)out, N, C, H, W, pad, s);
+}
+
+size_t tc_packed_weight_bytes(const ganb200_conv_desc* d, int op) {
+  if (op == GANB200_CONV_FPROP) return w_bytes(d->R * d->S, d->K, d->C) + 1024;
+  if (op == GANB200_CONV_DGRAD) return dgrad_w_bytes(d) + 1024;
+  return 0;
+}
+
+int tc_pack_weight(const ganb200_conv_desc* d, int op, const float* w, void* out, cudaStream_t s) {
+  GB_REQUIRE(((uintptr_t)out & 1023) == 0, GANB200_BAD_ARG, "pack_weight: output must be 1024-byte aligned");
+  auto pack = [&](const TcProblem& q, __nv_bfloat16* dst) {
+    const int Cp = cpad(q.Ci);
+    int64_t total = (int64_t)q.taps.n * q.Ko * Cp;
+    pack_weight_kernel<<<ew_grid(total, 256, 1), 256, 0, s>>>(w, dst, q.Ko, q.Ci, Cp, q.w_sk, q.w_sc, q.taps);
+  };
+  if (op == GANB200_CONV_FPROP) {
+    pack(fprop_problem(d), (__nv_bfloat16*)out);
+  } else if (op == GANB200_CONV_DGRAD) {
+    size_t woff = 0;   // the same phase order and offsets as dgrad_run
+    for (int a = 0; a < d->stride; ++a)
+      for (int b = 0; b < d->stride; ++b) {
+        TcProblem q = dgrad_problem(d, a, b);
+        if (q.Po <= 0 || q.Qo <= 0) continue;
+        GB_REQUIRE(q.taps.n > 0, GANB200_BAD_SHAPE, "tc dgrad: an output phase has no filter tap");
+        pack(q, (__nv_bfloat16*)((uint8_t*)out + woff));
+        woff += w_bytes(q.taps.n, d->C, d->K);
+      }
+  } else {
+    return fail(GANB200_BAD_ARG, "pack_weight: wgrad has no weight operand%s", "");
+  }
+  GB_CHECK_LAUNCH();
+  return 0;
 }
 
 static int dgrad_run(const ganb200_conv_desc* d, const float* dy, const float* w, const float* iscale,
-                     const float* oscale, float* dx, void* ws, cudaStream_t s, bool fold, float** padded_out);
+                     const float* oscale, float* dx, void* ws, cudaStream_t s, bool fold, float** padded_out,
+                     const void* dyp = nullptr, const void* wp = nullptr);
 
 int tc_dgrad(const ganb200_conv_desc* d, const float* dy, const float* w, const float* iscale, const float* oscale,
-             float* dx, void* ws, size_t ws_bytes, cudaStream_t s) {
+             float* dx, void* ws, size_t ws_bytes, cudaStream_t s, const void* dyp, const void* wp) {
   GB_REQUIRE(ws && ws_bytes >= tc_workspace(d, GANB200_CONV_DGRAD), GANB200_WORKSPACE_TOO_SMALL,
              "tc dgrad: workspace too small");
-  return dgrad_run(d, dy, w, iscale, oscale, dx, align_ws(ws), s, true, nullptr);
+  return dgrad_run(d, dy, w, iscale, oscale, dx, align_ws(ws), s, true, nullptr, dyp, wp);
 }
 
 // ws (1024-aligned): [dy packed][phase weights][padded fp32 output (replicate padding only)].  With fold == false the
 // padded-domain result is left in the workspace (*padded_out) for a fused consumer.
 static int dgrad_run(const ganb200_conv_desc* d, const float* dy, const float* w, const float* iscale,
-                     const float* oscale, float* dx, void* ws, cudaStream_t s, bool fold, float** padded_out) {
+                     const float* oscale, float* dx, void* ws, cudaStream_t s, bool fold, float** padded_out,
+                     const void* dyp, const void* wp) {
   const bool rep = d->pad_mode == 1 && d->pad > 0;
-  __nv_bfloat16* act = (__nv_bfloat16*)ws;
-  uint8_t* wbase = (uint8_t*)ws + act_bytes(d->N, d->K, d->P, d->Q, 0);
+  const __nv_bfloat16* act = dyp ? (const __nv_bfloat16*)dyp : (const __nv_bfloat16*)ws;
+  uint8_t* ws_w = (uint8_t*)ws + act_bytes(d->N, d->K, d->P, d->Q, 0);
+  uint8_t* wbase = wp ? (uint8_t*)wp : ws_w;
   float* out = dx;
-  if (rep) out = (float*)(wbase + dgrad_w_bytes(d));
+  if (rep) out = (float*)(ws_w + dgrad_w_bytes(d));
   if (padded_out) *padded_out = out;
-  int rc = pack_input(dy, oscale, act, d->N, d->K, d->P, d->Q, 0, s);
-  if (rc) return rc;
+  int rc = 0;
+  if (!dyp) {
+    rc = pack_input(dy, oscale, (__nv_bfloat16*)ws, d->N, d->K, d->P, d->Q, 0, s);
+    if (rc) return rc;
+  }
   size_t woff = 0;
   for (int a = 0; a < d->stride; ++a)
     for (int b = 0; b < d->stride; ++b) {
       TcProblem q = dgrad_problem(d, a, b);
       if (q.Po <= 0 || q.Qo <= 0) continue;
       GB_REQUIRE(q.taps.n > 0, GANB200_BAD_SHAPE, "tc dgrad: an output phase has no filter tap");
-      rc = run_problem(q, act, w, (__nv_bfloat16*)(wbase + woff), out, iscale, nullptr, s);
+      rc = run_problem(q, act, w, (__nv_bfloat16*)(wbase + woff), out, iscale, nullptr, s, wp != nullptr);
       if (rc) return rc;
       woff += w_bytes(q.taps.n, d->C, d->K);
     }
@@ -1320,29 +1369,34 @@ static int launch_wg(const CUtensorMap& ta, const CUtensorMap& tb, const TcWgrad
 }
 
 static int wgrad_run(const ganb200_conv_desc* d, const float* x, const float* dy, const float* iscale,
-                     const float* oscale, float* dw, void* ws, cudaStream_t s, const __nv_bfloat16* dy_prepacked);
+                     const float* oscale, float* dw, void* ws, cudaStream_t s, const __nv_bfloat16* dy_prepacked,
+                     const __nv_bfloat16* x_prepacked = nullptr);
 
 int tc_wgrad(const ganb200_conv_desc* d, const float* x, const float* dy, const float* iscale, const float* oscale,
-             float* dw, void* ws, size_t ws_bytes, cudaStream_t s) {
+             float* dw, void* ws, size_t ws_bytes, cudaStream_t s, const void* xp, const void* dyp) {
   GB_REQUIRE(ws && ws_bytes >= wgrad_workspace(d), GANB200_WORKSPACE_TOO_SMALL, "tc wgrad: workspace too small");
-  return wgrad_run(d, x, dy, iscale, oscale, dw, align_ws(ws), s, nullptr);
+  return wgrad_run(d, x, dy, iscale, oscale, dw, align_ws(ws), s, (const __nv_bfloat16*)dyp, (const __nv_bfloat16*)xp);
 }
 
 // ws (1024-aligned): [dy packed (unused when dy_prepacked)][x packed][partials]
 static int wgrad_run(const ganb200_conv_desc* d, const float* x, const float* dy, const float* iscale,
-                     const float* oscale, float* dw, void* ws, cudaStream_t s, const __nv_bfloat16* dy_prepacked) {
+                     const float* oscale, float* dw, void* ws, cudaStream_t s, const __nv_bfloat16* dy_prepacked,
+                     const __nv_bfloat16* x_prepacked) {
   const WgradPlan w = wgrad_plan(d);
   const bool rep = d->pad_mode == 1 && d->pad > 0;
   const int mp = rep ? d->pad : 0;
   const int Kp = cpad(d->K), Cp = cpad(d->C), Hp = d->H + 2 * mp, Wp = d->W + 2 * mp, RS = d->R * d->S;
   const __nv_bfloat16* dyh = dy_prepacked ? dy_prepacked : (const __nv_bfloat16*)ws;
-  __nv_bfloat16* xh = (__nv_bfloat16*)((uint8_t*)ws + w.dy_bytes);
+  const __nv_bfloat16* xh = x_prepacked ? x_prepacked : (const __nv_bfloat16*)((uint8_t*)ws + w.dy_bytes);
   float* part = (float*)((uint8_t*)ws + w.dy_bytes + w.x_bytes);
   {
     if (!dy_prepacked) {
       if (int rc = pack_input(dy, oscale, (__nv_bfloat16*)ws, d->N, d->K, d->P, d->Q, 0, s)) return rc;
     }
-    if (int rc = pack_input(x, iscale, xh, d->N, d->C, d->H, d->W, mp, s)) return rc;
+    if (!x_prepacked) {
+      if (int rc = pack_input(x, iscale, (__nv_bfloat16*)((uint8_t*)ws + w.dy_bytes), d->N, d->C, d->H, d->W, mp, s))
+        return rc;
+    }
   }
   if (w.ring.ok && halo_mode() >= 1) {
     TcWgRingParams r;
@@ -1479,9 +1533,27 @@ extern "C" int ganb200_modconv_bwd_eligible(const ganb200_conv_desc* d) {
 //   gx = s * dxs, gs1 = sum_hw dxs * x with dxs = fold(alpha * sum w * (sinv*gu));  gw = alpha * wgrad(s*x, sinv*gu).
 // gu is packed to bf16 NHWC once and feeds both the dgrad and the wgrad kernels; the fold of the replicate padding is
 // fused with the style scaling and the row reduction.  gx / gs1 (together) or gw may be NULL.
+static int modconv_bwd_impl(const ganb200_conv_desc* d, const float* x, const float* w, const float* s,
+                            const float* sinv, const float* gu, float* gx, float* gs1, float* gw, void* ws,
+                            size_t ws_bytes, void* stream, const void* wp_dgrad);
+
 extern "C" int ganb200_modconv_bwd(const ganb200_conv_desc* d, const float* x, const float* w, const float* s,
                                    const float* sinv, const float* gu, float* gx, float* gs1, float* gw, void* ws,
                                    size_t ws_bytes, void* stream) {
+  return modconv_bwd_impl(d, x, w, s, sinv, gu, gx, gs1, gw, ws, ws_bytes, stream, nullptr);
+}
+
+// same, with the dgrad-layout packed weights supplied by the caller (ganb200_conv2d_pack_weight(op = DGRAD), cached per
+// optimiser step)
+extern "C" int ganb200_modconv_bwd_pk(const ganb200_conv_desc* d, const float* x, const float* w, const void* wp_dgrad,
+                                      const float* s, const float* sinv, const float* gu, float* gx, float* gs1,
+                                      float* gw, void* ws, size_t ws_bytes, void* stream) {
+  return modconv_bwd_impl(d, x, w, s, sinv, gu, gx, gs1, gw, ws, ws_bytes, stream, wp_dgrad);
+}
+
+static int modconv_bwd_impl(const ganb200_conv_desc* d, const float* x, const float* w, const float* s,
+                            const float* sinv, const float* gu, float* gx, float* gs1, float* gw, void* ws,
+                            size_t ws_bytes, void* stream, const void* wp_dgrad) {
   int rc = validate_desc(d);
   if (rc) return rc;
   GB_REQUIRE(ganb200_modconv_bwd_eligible(d), GANB200_BAD_SHAPE, "modconv_bwd: shape not eligible");
@@ -1494,7 +1566,7 @@ extern "C" int ganb200_modconv_bwd(const ganb200_conv_desc* d, const float* x, c
   // pad == 0 (1x1 convs): no padded domain, the dgrad kernels write a plain [N,C,H,W] buffer behind the wgrad scratch
   float* direct = (float*)(wws + wp.dy_bytes + wp.x_bytes + wp.part_bytes);
   // dgrad part of the workspace first: its head is the packed gu, shared with wgrad
-  rc = dgrad_run(d, gu, w, nullptr, sinv, direct, base, st, false, &dxp);
+  rc = dgrad_run(d, gu, w, nullptr, sinv, direct, base, st, false, &dxp, nullptr, wp_dgrad);
   if (rc) return rc;
   if (gx || gs1) {
     const int64_t rows = (int64_t)d->N * d->C;

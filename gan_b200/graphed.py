@@ -26,6 +26,7 @@ bodies and are not graphed.
 """
 import torch
 
+from . import kernels as KN
 from . import ops
 from . import rng
 
@@ -52,6 +53,7 @@ class StateSnapshot:
 
     @torch.no_grad()
     def restore(self):
+        KN.bump_param_epoch()
         torch._foreach_copy_([t.detach() for t in self.live], self.saved)
         for opt, st, dev in self.opt:
             for p, s in opt.state.items():
@@ -109,10 +111,14 @@ class GraphedStep:
                 self.images.grad = None
         torch.cuda.current_stream(dev).wait_stream(side)
         torch.cuda.synchronize(dev)
+        # each graph must re-pack every weight it uses at its own start (a replay may follow ANY other replay): start the
+        # captures with the packed-weight cache cold
+        KN.bump_param_epoch()
         self.graph_d = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self.graph_d, capture_error_mode="thread_local"):
             self.d_out = T.discriminator_trainstep(self.images, batch)
             self.images.grad = None
+        KN.bump_param_epoch()
         self.graph_g = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self.graph_g, pool=self.graph_d.pool(), capture_error_mode="thread_local"):
             self.g_out = T.generator_trainstep(batch)
@@ -128,12 +134,14 @@ class GraphedStep:
             with torch.no_grad():
                 self.images.copy_(images, non_blocking=True)
         self.graph_d.replay()
+        KN.bump_param_epoch()   # the replay moved the parameters: packed weights cached by eager code are stale
         self._advance(self.T.optimizer_D)
         return self.d_out
 
     def generator_trainstep(self, b_size):
         assert b_size == self.batch
         self.graph_g.replay()
+        KN.bump_param_epoch()
         self._advance(self.T.optimizer_G)
         self._replays += 1
         if self.poll_every and self._replays % self.poll_every == 0:

@@ -49,6 +49,17 @@ class ConvTimer:
         return out
 
 
+# Packed-operand caches (tcgen05 engine).  PARAM_EPOCH counts in-place parameter updates that do not go through torch
+# (the fused Adam, weight clipping, CUDA-graph replays): a packed weight is valid for the (tensor._version, PARAM_EPOCH) it
+# was made at.  GANB200_PACK_CACHE=0 switches both caches off (every pass packs its own operands, as in round 1).
+PARAM_EPOCH = [0]
+PACK_CACHE = os.environ.get("GANB200_PACK_CACHE", "1") != "0"
+
+
+def bump_param_epoch():
+    PARAM_EPOCH[0] += 1
+
+
 CONV_TIMER = None
 OP_CENSUS = None    # tools/kernel_profile.py: dict (kernel family, operator / shape ...) -> number of calls
 CONV_CENSUS = None  # bench.py: dict (op, desc fields..., has_iscale, has_oscale, has_bias, engine) -> number of calls
@@ -107,6 +118,74 @@ class CudaBackend:
         # a fresh tensor from the caching allocator: stream-ordered reuse is handled by torch
         return torch.empty(nbytes, dtype=torch.uint8, device=device)
 
+    # -- packed operands of the tcgen05 engine -----------------------------------------------------
+    def _aligned_buffer(self, nbytes, device):
+        buf = torch.empty(nbytes + 1024, dtype=torch.uint8, device=device)
+        off = (-buf.data_ptr()) % 1024
+        return buf[off:off + nbytes]
+
+    def packed_weight(self, w, d, op):
+        """bf16 packed form of weight `w` for (desc, op), cached on the tensor until it changes: w._version moves with
+        every torch in-place op, PARAM_EPOCH with the updates torch does not see.  None when caching is off."""
+        if not PACK_CACHE:
+            return None
+        key = (op, d.N if op == DGRAD else 0, d.C, d.H, d.W, d.K, d.R, d.S, d.stride, d.pad, d.pad_mode)
+        stamp = (w._version, PARAM_EPOCH[0], w.data_ptr())
+        cache = getattr(w, "_gb_wpack", None)
+        if cache is None:
+            cache = {}
+            try:
+                w._gb_wpack = cache
+            except Exception:
+                return None
+        hit = cache.get(key)
+        if hit is not None and hit[0] == stamp:
+            return hit[1]
+        nb = self.lib.ganb200_conv2d_packed_weight_bytes(ctypes.byref(d), op)
+        if nb == 0:
+            return None
+        buf = hit[1] if (hit is not None and hit[1].numel() == nb) else self._aligned_buffer(nb, w.device)
+        LAUNCH_COUNT[0] += 1
+        st = ctypes.c_void_p(torch.cuda.current_stream(w.device).cuda_stream)
+        _lib.check(self.lib.ganb200_conv2d_pack_weight(ctypes.byref(d), op, self._p(w), self._p(buf), st))
+        cache[key] = (stamp, buf)
+        return buf
+
+    def packed_act(self, t, scale, pad, keep, transient=False):
+        """bf16 NHWC packed form of activation `t` (scale folded in, replicate padding `pad` materialised).  With `keep`
+        the buffer stays on the tensor (t._gb_pack) for the other passes that need the same operand — x: the wgrad of the
+        layer after its fprop; dy: wgrad after dgrad — and dies with it.  None when there is nothing cached and keep is
+        False (the engine then packs into its own workspace)."""
+        if not PACK_CACHE:
+            return None
+        cache = getattr(t, "_gb_pack", None)
+        key = (pad, 0 if scale is None else scale.data_ptr())
+        if cache is not None and cache[0] == t._version:
+            hit = cache[1].get(key)
+            if hit is not None and hit[1] is scale:
+                return hit[0]
+        if not keep and not transient:
+            return None
+        N, C, H, W = t.shape
+        nb = self.lib.ganb200_tc_packed_act_bytes(N, C, H, W, pad)
+        buf = self._aligned_buffer(nb, t.device)
+        LAUNCH_COUNT[0] += 1
+        st = ctypes.c_void_p(torch.cuda.current_stream(t.device).cuda_stream)
+        _lib.check(self.lib.ganb200_tc_pack_act(self._p(t), self._p(scale), self._p(buf), N, C, H, W, pad, st))
+        if not keep:
+            return buf                 # transient: used by this call only
+        if cache is None or cache[0] != t._version:
+            cache = (t._version, {})
+            try:
+                t._gb_pack = cache
+            except Exception:
+                return buf
+        cache[1][key] = (buf, scale)   # the reference to `scale` keeps its address from being reused while cached
+        return buf
+
+    def _is_tc(self, d, op):
+        return PACK_CACHE and self.lib.ganb200_conv2d_route(ctypes.byref(d), op) == 2
+
     # -- convolution family ---------------------------------------------------------------------
     def _t0(self, d, op, flags=(False, False, False)):
         if CONV_CENSUS is not None:
@@ -130,22 +209,36 @@ class CudaBackend:
         return ConvDesc(N, C, H, W, K, R, S, stride, pad, pad_mode, P, Q, float(alpha),
                         default_engine() if engine is None else engine)
 
-    def conv_fprop(self, x, w, bias, stride, pad, pad_mode, alpha, iscale=None, oscale=None, engine=None):
+    def conv_fprop(self, x, w, bias, stride, pad, pad_mode, alpha, iscale=None, oscale=None, engine=None,
+                   keep_x=False):
+        """keep_x: the packed x stays cached on the tensor for the wgrad of the same layer (callers that save x)."""
         N, C, H, W = x.shape
         K, C2, R, S = w.shape
         assert C == C2, (x.shape, w.shape)
         d = self._desc(N, C, H, W, K, R, S, stride, pad, pad_mode, alpha, engine)
         st = self._prep(x, w, bias, iscale, oscale)
         y = torch.empty((N, K, d.P, d.Q), dtype=torch.float32, device=x.device)
+        tm = self._t0(d, FPROP, (iscale is not None, oscale is not None, bias is not None))
+        if self._is_tc(d, FPROP):
+            wp = self.packed_weight(w, d, FPROP)
+            xp = None
+            if wp is not None:   # (the _pk entry takes both operands packed: x is packed here, kept only on request)
+                xp = self.packed_act(x, iscale, pad if (pad_mode == 1 and pad > 0) else 0, keep_x, transient=True)
+            if xp is not None and wp is not None:
+                _lib.check(self.lib.ganb200_conv2d_fprop_pk(ctypes.byref(d), self._p(xp), self._p(wp), self._p(bias),
+                                                            self._p(oscale), self._p(y), st))
+                self._t1(tm)
+                return y
         nb = self.lib.ganb200_conv2d_workspace_bytes(ctypes.byref(d), FPROP)
         ws = self._workspace(nb, x.device)
-        tm = self._t0(d, FPROP, (iscale is not None, oscale is not None, bias is not None))
         _lib.check(self.lib.ganb200_conv2d_fprop(ctypes.byref(d), self._p(x), self._p(w), self._p(bias),
                                                  self._p(iscale), self._p(oscale), self._p(y), self._p(ws), nb, st))
         self._t1(tm)
         return y
 
-    def conv_dgrad(self, dy, w, in_hw, stride, pad, pad_mode, alpha, iscale=None, oscale=None, engine=None):
+    def conv_dgrad(self, dy, w, in_hw, stride, pad, pad_mode, alpha, iscale=None, oscale=None, engine=None,
+                   keep_dy=False):
+        """keep_dy: the packed dy stays cached on the tensor for the wgrad that shares it."""
         N, K, P, Q = dy.shape
         K2, C, R, S = w.shape
         assert K == K2, (dy.shape, w.shape)
@@ -157,12 +250,22 @@ class CudaBackend:
         nb = self.lib.ganb200_conv2d_workspace_bytes(ctypes.byref(d), DGRAD)
         ws = self._workspace(nb, dy.device)
         tm = self._t0(d, DGRAD, (iscale is not None, oscale is not None, False))
+        if self._is_tc(d, DGRAD):
+            wp = self.packed_weight(w, d, DGRAD)
+            dyp = self.packed_act(dy, oscale, 0, keep_dy)
+            if wp is not None or dyp is not None:
+                _lib.check(self.lib.ganb200_conv2d_dgrad_pk(ctypes.byref(d), self._p(dy), self._p(dyp), self._p(w),
+                                                            self._p(wp), self._p(iscale), self._p(oscale), self._p(dx),
+                                                            self._p(ws), nb, st))
+                self._t1(tm)
+                return dx
         _lib.check(self.lib.ganb200_conv2d_dgrad(ctypes.byref(d), self._p(dy), self._p(w), self._p(iscale),
                                                  self._p(oscale), self._p(dx), self._p(ws), nb, st))
         self._t1(tm)
         return dx
 
-    def conv_wgrad(self, x, dy, rs, stride, pad, pad_mode, alpha, iscale=None, oscale=None, engine=None):
+    def conv_wgrad(self, x, dy, rs, stride, pad, pad_mode, alpha, iscale=None, oscale=None, engine=None,
+                   keep_x=False, keep_dy=False):
         N, C, H, W = x.shape
         N2, K, P, Q = dy.shape
         R, S = rs
@@ -173,6 +276,15 @@ class CudaBackend:
         nb = self.lib.ganb200_conv2d_workspace_bytes(ctypes.byref(d), WGRAD)
         ws = self._workspace(nb, x.device)
         tm = self._t0(d, WGRAD, (iscale is not None, oscale is not None, False))
+        if self._is_tc(d, WGRAD):
+            xp = self.packed_act(x, iscale, pad if (pad_mode == 1 and pad > 0) else 0, keep_x)
+            dyp = self.packed_act(dy, oscale, 0, keep_dy)
+            if xp is not None or dyp is not None:
+                _lib.check(self.lib.ganb200_conv2d_wgrad_pk(ctypes.byref(d), self._p(x), self._p(xp), self._p(dy),
+                                                            self._p(dyp), self._p(iscale), self._p(oscale), self._p(dw),
+                                                            self._p(ws), nb, st))
+                self._t1(tm)
+                return dw
         _lib.check(self.lib.ganb200_conv2d_wgrad(ctypes.byref(d), self._p(x), self._p(dy), self._p(iscale),
                                                  self._p(oscale), self._p(dw), self._p(ws), nb, st))
         self._t1(tm)
@@ -516,6 +628,12 @@ class CudaBackend:
         gw = torch.empty_like(w) if need_w else None
         nb = self.lib.ganb200_modconv_bwd_workspace_bytes(ctypes.byref(d))
         ws = self._workspace(nb, x.device)
+        wp = self.packed_weight(w, d, DGRAD) if (need_x or need_s) else None
+        if wp is not None:
+            _lib.check(self.lib.ganb200_modconv_bwd_pk(ctypes.byref(d), self._p(x), self._p(w), self._p(wp), self._p(s),
+                                                       self._p(sinv), self._p(gu), self._p(gx), self._p(gs1),
+                                                       self._p(gw), self._p(ws), nb, st))
+            return gx, gs1, gw
         _lib.check(self.lib.ganb200_modconv_bwd(ctypes.byref(d), self._p(x), self._p(w), self._p(s), self._p(sinv),
                                                 self._p(gu), self._p(gx), self._p(gs1), self._p(gw), self._p(ws), nb,
                                                 st))
@@ -642,6 +760,7 @@ class CudaBackend:
         return out
 
     def clamp_(self, x, lo, hi):
+        bump_param_epoch()   # in-place parameter update torch does not see (wgan weight clipping)
         st = self._prep(x)
         _lib.check(self.lib.ganb200_clamp_(self._p(x), x.numel(), lo, hi, st))
         return x

@@ -23,22 +23,27 @@ from . import resample as RS
 ConvCfg = namedtuple("ConvCfg", "stride pad pad_mode alpha engine depthwise", defaults=(False,))
 
 
-def _fprop(cfg, x, w, bias):
+# keep_*: the bf16 packed operand the tcgen05 engine builds stays cached on the tensor (kernels.packed_act) when another
+# pass of the same layer needs the same operand: x is packed by fprop and reused by the layer's wgrad (and by the second
+# wgrad of an R-penalty sweep); dy is packed once for the dgrad and the wgrad of a backward node.
+def _fprop(cfg, x, w, bias, keep_x=False):
     if cfg.depthwise:
         return K().dwconv_fprop(x, w, bias, cfg.stride, cfg.pad, cfg.alpha)
-    return K().conv_fprop(x, w, bias, cfg.stride, cfg.pad, cfg.pad_mode, cfg.alpha, engine=cfg.engine)
+    return K().conv_fprop(x, w, bias, cfg.stride, cfg.pad, cfg.pad_mode, cfg.alpha, engine=cfg.engine, keep_x=keep_x)
 
 
-def _dgrad(cfg, dy, w, in_hw):
+def _dgrad(cfg, dy, w, in_hw, keep_dy=False):
     if cfg.depthwise:
         return K().dwconv_dgrad(dy, w, in_hw, cfg.stride, cfg.pad, cfg.alpha)
-    return K().conv_dgrad(dy, w, in_hw, cfg.stride, cfg.pad, cfg.pad_mode, cfg.alpha, engine=cfg.engine)
+    return K().conv_dgrad(dy, w, in_hw, cfg.stride, cfg.pad, cfg.pad_mode, cfg.alpha, engine=cfg.engine,
+                          keep_dy=keep_dy)
 
 
-def _wgrad(cfg, x, dy, rs):
+def _wgrad(cfg, x, dy, rs, keep_x=False, keep_dy=False):
     if cfg.depthwise:
         return K().dwconv_wgrad(x, dy, rs, cfg.stride, cfg.pad, cfg.alpha)
-    return K().conv_wgrad(x, dy, rs, cfg.stride, cfg.pad, cfg.pad_mode, cfg.alpha, engine=cfg.engine)
+    return K().conv_wgrad(x, dy, rs, cfg.stride, cfg.pad, cfg.pad_mode, cfg.alpha, engine=cfg.engine, keep_x=keep_x,
+                          keep_dy=keep_dy)
 
 
 def K():
@@ -63,7 +68,7 @@ class Conv2dFn(Function):
         ctx.save_for_backward(x, w)
         ctx.cfg = cfg
         ctx.has_bias = bias is not None
-        return _fprop(cfg, x, w, bias)
+        return _fprop(cfg, x, w, bias, keep_x=ctx.needs_input_grad[1])   # the wgrad of this layer reads the same x
 
     @staticmethod
     def backward(ctx, gy):
@@ -84,7 +89,7 @@ class ConvDgradFn(Function):
         dy, w = _c(dy), _c(w)
         ctx.save_for_backward(dy, w)
         ctx.cfg = cfg
-        return _dgrad(cfg, dy, w, in_hw)
+        return _dgrad(cfg, dy, w, in_hw, keep_dy=True)   # backward nodes run dgrad then wgrad on the same dy
 
     @staticmethod
     def backward(ctx, g):
@@ -102,7 +107,7 @@ class ConvWgradFn(Function):
         x, dy = _c(x), _c(dy)
         ctx.save_for_backward(x, dy)
         ctx.cfg = cfg
-        return _wgrad(cfg, x, dy, rs)
+        return _wgrad(cfg, x, dy, rs, keep_x=True, keep_dy=True)
 
     @staticmethod
     def backward(ctx, gw):

@@ -82,6 +82,7 @@ class FusedAdam(torch.optim.Optimizer):
             with torch.enable_grad():
                 loss = closure()
         k = KN.backend()
+        KN.bump_param_epoch()   # the kernel below rewrites parameters behind torch's back: cached packed weights are stale
         if self.pre_step is not None:
             self.pre_step()
         for gi, group in enumerate(self.param_groups):

@@ -90,6 +90,27 @@ int ganb200_conv2d_wgrad(const ganb200_conv_desc* d, const float* x, const float
                          const float* iscale, const float* oscale, float* dw,
                          void* ws, size_t ws_bytes, void* stream);
 
+/* Packed operands of the tcgen05 engine as caller-owned buffers.  Every tcgen05-routed pass first re-packs its fp32 NCHW /
+ * KCRS operands to bf16 ([N][H+2p][W+2p][C8] activations with the per-sample scale folded in and replicate padding
+ * materialised; [tap][K][C8] weights per output phase).  The same packed tensor serves several passes — x: fprop and the
+ * wgrad of the same layer; dy: dgrad and wgrad; the weights: every pass until the next optimiser step — so the host side
+ * may pack once, keep the buffer (1024-byte aligned, sizes below) and hand it to the *_pk entry points
+ * (gan_b200/kernels.py caches them on the tensors).  A NULL packed pointer means "pack the fp32 operand as before".
+ *   pack_act(x, scale[N,C]|NULL, pad): pad = desc.pad for a replicate-padded x (fprop / wgrad), 0 for dy and zero padding
+ *   pack_weight(desc, op): op = FPROP or DGRAD layout (wgrad has no weight operand); 0 bytes when (desc, op) is not
+ *   routed to the tcgen05 engine.  iscale / oscale given to a *_pk call must be the ones folded into the packed operand
+ *   (they are only applied to operands packed inside the call and, for dgrad, to the output). */
+size_t ganb200_tc_packed_act_bytes(int N, int C, int H, int W, int pad);
+int ganb200_tc_pack_act(const float* x, const float* scale, void* out, int N, int C, int H, int W, int pad, void* stream);
+size_t ganb200_conv2d_packed_weight_bytes(const ganb200_conv_desc* d, int op);
+int ganb200_conv2d_pack_weight(const ganb200_conv_desc* d, int op, const float* w, void* out, void* stream);
+int ganb200_conv2d_fprop_pk(const ganb200_conv_desc* d, const void* xp, const void* wp, const float* bias,
+                            const float* oscale, float* y, void* stream);
+int ganb200_conv2d_dgrad_pk(const ganb200_conv_desc* d, const float* dy, const void* dyp, const float* w, const void* wp,
+                            const float* iscale, const float* oscale, float* dx, void* ws, size_t ws_bytes, void* stream);
+int ganb200_conv2d_wgrad_pk(const ganb200_conv_desc* d, const float* x, const void* xp, const float* dy, const void* dyp,
+                            const float* iscale, const float* oscale, float* dw, void* ws, size_t ws_bytes, void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * Separable linear resampling with per-output tap tables:
  *   y[nc,ho,wo] = sum_{a<Th} sum_{b<Tw} wh[ho,a]*ww[wo,b] * x[nc, ih[ho,a], iw[wo,b]]
@@ -379,6 +400,10 @@ size_t ganb200_modconv_bwd_workspace_bytes(const ganb200_conv_desc* d);
 int ganb200_modconv_bwd_eligible(const ganb200_conv_desc* d);
 int ganb200_modconv_bwd(const ganb200_conv_desc* d, const float* x, const float* w, const float* s, const float* sinv,
                         const float* gu, float* gx, float* gs1, float* gw, void* ws, size_t ws_bytes, void* stream);
+/* the same with the dgrad-layout packed weights supplied by the caller (ganb200_conv2d_pack_weight, op = DGRAD) */
+int ganb200_modconv_bwd_pk(const ganb200_conv_desc* d, const float* x, const float* w, const void* wp_dgrad,
+                           const float* s, const float* sinv, const float* gu, float* gx, float* gs1, float* gw,
+                           void* ws, size_t ws_bytes, void* stream);
 /* gx = dxs * s[n,c] (gx may be NULL);  gs1[n,c] = sum_hw dxs*x (gs1 may be NULL) */
 int ganb200_scale_reduce(const float* dxs, const float* s, const float* x, float* gx, float* gs1, int N, int C, int HW,
                          void* stream);

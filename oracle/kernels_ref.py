@@ -36,7 +36,7 @@ class RefBackend:
     name = "ref"
 
     # ---- convolution family (include/ganb200.h: fprop / dgrad / wgrad) ---------------------------------
-    def conv_fprop(self, x, w, bias, stride, pad, pad_mode, alpha, iscale=None, oscale=None, engine=None):
+    def conv_fprop(self, x, w, bias, stride, pad, pad_mode, alpha, iscale=None, oscale=None, engine=None, keep_x=False):
         with torch.no_grad():
             if iscale is not None:
                 x = x * iscale[:, :, None, None]
@@ -47,7 +47,8 @@ class RefBackend:
                 y = y + bias[None, :, None, None]
             return y
 
-    def conv_dgrad(self, dy, w, in_hw, stride, pad, pad_mode, alpha, iscale=None, oscale=None, engine=None):
+    def conv_dgrad(self, dy, w, in_hw, stride, pad, pad_mode, alpha, iscale=None, oscale=None, engine=None,
+                   keep_dy=False):
         N, K = dy.shape[:2]
         C = w.shape[1]
         with torch.enable_grad():
@@ -60,7 +61,8 @@ class RefBackend:
             dx = dx * iscale[:, :, None, None]
         return dx.detach()
 
-    def conv_wgrad(self, x, dy, rs, stride, pad, pad_mode, alpha, iscale=None, oscale=None, engine=None):
+    def conv_wgrad(self, x, dy, rs, stride, pad, pad_mode, alpha, iscale=None, oscale=None, engine=None,
+                   keep_x=False, keep_dy=False):
         K, C = dy.shape[1], x.shape[1]
         with torch.enable_grad():
             w = torch.zeros((K, C, *rs), dtype=x.dtype, requires_grad=True)
