@@ -164,6 +164,11 @@ struct TcConvParams {
   const float* oscale;  // [N][K] or null
   const float* bias;    // [K] or null
   float* y;
+  // scatter epilogue (dgrad of a replicate-padded convolution, see epi_fold32): the tile grid covers the PADDED input
+  // domain, the value of padded pixel (ph, pw) is ADDED to pixel (clamp(ph - pad), clamp(pw - pad)) of the FH x FW plane
+  int fold, fold_pad, FH, FW;
+  const float* red_x;   // [N][K][FH][FW] or null: red_out[n][k] += sum over pixels of (alpha * acc) * red_x
+  float* red_out;       // [N][K]
 };
 
 template <int BN, int STAGES>
@@ -214,6 +219,68 @@ __device__ __forceinline__ void epi_chunk(const float (&v)[32], char* yk, uint32
       if (bias) epi_store32<false, true, false>(v, yk, plane_bytes, nvalid, alpha, osc, bias);
       else epi_store32<false, false, false>(v, yk, plane_bytes, nvalid, alpha, osc, bias);
     }
+  }
+}
+
+// Scatter epilogue: dgrad of a replicate-padded convolution WITHOUT the padded fp32 intermediate and the fold pass.
+// The accumulator of a thread belongs to pixel (ph, pw) of the padded input; the adjoint of replicate padding adds it to
+// the clamped pixel of the unpadded plane.  Only pixels on the border of the plane receive more than one contribution
+// (`multi`): those go through red.global.add into a border that the host zeroed, every other pixel is a plain store.
+// With red_x the per-(sample, channel) sum of (alpha * acc) * x — the style gradient of the modulated convolution,
+// sum_hw dxs * x (generator_13_5.py:239 backward) — is formed here as well: by linearity the sum over the padded
+// domain against x at the clamped position equals the sum over the folded plane.  32 channel values per lane are
+// reduced over the warp's 32 pixels by recursive halving (31 shuffles, lane j ends with channel j) and added to
+// red_out[n][k] with one coalesced atomic per warp and chunk.
+template <bool HAS_OSC, bool HAS_RED>
+__device__ __forceinline__ void epi_fold32(const float (&v)[32], char* yk, const char* xk, uint32_t plane_bytes, int nvalid,
+                                           float alpha, const float* __restrict__ osc, bool ok, bool multi,
+                                           float* __restrict__ red, int lane, float* racc = nullptr) {
+  float r[32];
+  uint32_t off = 0;
+  if (HAS_RED) {
+    // all 32 loads first (independent, ~one memory latency for the batch): interleaved with the stores below the compiler
+    // must assume aliasing and serialises load -> store -> load, ~30 latencies per chunk (measured: 4x the whole kernel)
+#pragma unroll
+    for (int j = 0; j < 32; ++j, off += plane_bytes)
+      r[j] = (ok && j < nvalid) ? __ldg(reinterpret_cast<const float*>(xk + off)) : 0.f;
+    off = 0;
+  }
+#pragma unroll
+  for (int j = 0; j < 32; ++j, off += plane_bytes) {
+    const bool okj = ok && j < nvalid;
+    const float t = v[j] * alpha;
+    if (HAS_RED) r[j] *= t;
+    if (okj) {
+      const float o = HAS_OSC ? t * __ldg(osc + j) : t;
+      float* dst = reinterpret_cast<float*>(yk + off);
+      if (multi) atomicAdd(dst, o); else *dst = o;
+    }
+  }
+  if (HAS_RED) {
+#pragma unroll
+    for (int w = 16; w >= 1; w >>= 1) {
+      const bool upper = (lane & w) != 0;
+#pragma unroll
+      for (int j = 0; j < w; ++j) {
+        const float keep = upper ? r[j + w] : r[j];
+        const float send = upper ? r[j] : r[j + w];
+        r[j] = keep + __shfl_xor_sync(0xffffffffu, send, w);
+      }
+    }
+    if (racc) *racc += r[0];                       // the caller flushes when the (image, channel tile) changes
+    else if (lane < nvalid) atomicAdd(red + lane, r[0]);
+  }
+}
+
+__device__ __forceinline__ void epi_fold_chunk(const float (&v)[32], char* yk, const char* xk, uint32_t plane_bytes,
+                                               int nvalid, float alpha, const float* osc, bool ok, bool multi, float* red,
+                                               int lane, float* racc = nullptr) {
+  if (red) {
+    if (osc) epi_fold32<true, true>(v, yk, xk, plane_bytes, nvalid, alpha, osc, ok, multi, red, lane, racc);
+    else epi_fold32<false, true>(v, yk, xk, plane_bytes, nvalid, alpha, osc, ok, multi, red, lane, racc);
+  } else {
+    if (osc) epi_fold32<true, false>(v, yk, xk, plane_bytes, nvalid, alpha, osc, ok, multi, red, lane);
+    else epi_fold32<false, false>(v, yk, xk, plane_bytes, nvalid, alpha, osc, ok, multi, red, lane);
   }
 }
 
@@ -324,19 +391,36 @@ __global__ void __launch_bounds__(TC_THREADS) tc_conv_kernel(const __grid_consta
       const int tp = t % p.tiles_p; t /= p.tiles_p;
       const int q = tq * p.bw + wl, pp = tp * p.bh + hl, n = t * p.bn + nl;
       const bool row_ok = (q < p.Q) && (pp < p.P) && (n < p.N);
-      float* ybase = p.y + ((int64_t)n * p.K) * PQ + (int64_t)(pp * p.o_step + p.o_off_h) * p.OW + q * p.o_step +
-                     p.o_off_w;
-      const float* osc = p.oscale ? p.oscale + (int64_t)n * p.K : nullptr;
+      int64_t pix = (int64_t)(pp * p.o_step + p.o_off_h) * p.OW + q * p.o_step + p.o_off_w;
+      int64_t plane = PQ;
+      bool multi = false;
+      if (p.fold) {
+        const int fh = min(max(pp * p.o_step + p.o_off_h - p.fold_pad, 0), p.FH - 1);
+        const int fw = min(max(q * p.o_step + p.o_off_w - p.fold_pad, 0), p.FW - 1);
+        multi = p.fold_pad > 0 && (fh == 0 || fh == p.FH - 1 || fw == 0 || fw == p.FW - 1);
+        pix = (int64_t)fh * p.FW + fw;
+        plane = (int64_t)p.FH * p.FW;
+      }
+      const int64_t nbase = row_ok ? ((int64_t)n * p.K) * plane + pix : 0;
+      float* ybase = p.y + nbase;
+      const float* osc = p.oscale ? p.oscale + (int64_t)(row_ok ? n : 0) * p.K : nullptr;
       const int acc = local & 1;
       mbar_wait(&tmem_full[acc], (local >> 1) & 1);
       tc_fence_after();
-      const uint32_t plane_bytes = (uint32_t)PQ * 4u;
+      const uint32_t plane_bytes = (uint32_t)plane * 4u;
       for (int c0 = 0; c0 < p.n_umma; c0 += 32) {
         float v[32];
         tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN + c0), v);
         const int kc = k0 + c0;
         const int nvalid = min(p.n_umma - c0, p.K - kc);
-        if (row_ok && nvalid > 0)
+        if (p.fold) {
+          // bn == 1 whenever red_out is set (host side): a warp's 32 pixels belong to one image
+          if (nvalid > 0)
+            epi_fold_chunk(v, reinterpret_cast<char*>(ybase + (int64_t)kc * plane),
+                           reinterpret_cast<const char*>(p.red_x ? p.red_x + nbase + (int64_t)kc * plane : nullptr),
+                           plane_bytes, nvalid, p.alpha, osc ? osc + kc : nullptr, row_ok, multi,
+                           p.red_out ? p.red_out + (int64_t)min(t * p.bn, p.N - 1) * p.K + kc : nullptr, lane);
+        } else if (row_ok && nvalid > 0)
           epi_chunk(v, reinterpret_cast<char*>(ybase + (int64_t)kc * PQ), plane_bytes, nvalid, p.alpha,
                     osc ? osc + kc : nullptr, p.bias ? p.bias + kc : nullptr);
       }
@@ -384,6 +468,12 @@ struct TcHaloParams {
   const float* oscale;
   const float* bias;
   float* y;
+  int fold, fold_pad, FH, FW;       // scatter epilogue, as in TcConvParams
+  const float* red_x;
+  float* red_out;
+  // range_mode (set with red_out): a CTA walks a CONTIGUOUS range of tiles, pixel tiles fastest, so that consecutive tiles
+  // belong to one (image, channel tile) and the epilogue keeps the reduction in registers until that key changes
+  int range_mode, tiles_per_cta;
   unsigned char tap_idx[MAX_TAPS];  // packed-weight index of grid point r * S + s
 };
 
@@ -418,6 +508,26 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_halo_kernel(const __gri
   const int total_tiles = p.tiles_m * p.tiles_n;
   const int rows_per_tile = p.mt * p.bh;
   constexpr uint32_t TMEM_COLS = 2 * MT_MAX * BN;  // double-buffered, MT accumulators each
+  // tile walk: strided over the grid (default: concurrent CTAs share activation rows in L2) or a contiguous range
+  const int t_first = p.range_mode ? (int)blockIdx.x * p.tiles_per_cta : (int)blockIdx.x;
+  const int t_end = p.range_mode ? min(total_tiles, t_first + p.tiles_per_cta) : total_tiles;
+  const int t_step = p.range_mode ? 1 : (int)gridDim.x;
+  // tile -> (k0, tq, tp, n): channel tile fastest by default, pixel tiles fastest in range mode
+  auto decode = [&](int tile, int& k0, int& tq, int& tp, int& n) {
+    if (p.range_mode) {
+      int t = tile;
+      tq = t % p.tiles_q; t /= p.tiles_q;
+      tp = t % p.tiles_p; t /= p.tiles_p;
+      k0 = (t % p.tiles_n) * BN;
+      n = t / p.tiles_n;
+    } else {
+      int t = tile / p.tiles_n;
+      k0 = (tile - t * p.tiles_n) * BN;
+      tq = t % p.tiles_q; t /= p.tiles_q;
+      tp = t % p.tiles_p; t /= p.tiles_p;
+      n = t;
+    }
+  };
 
   if (threadIdx.x == 0) {
     prefetch_tmap(&tmA);
@@ -438,12 +548,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_halo_kernel(const __gri
     const bool leader = elect_one();
     int sa = 0, sb = 0;
     uint32_t pa = 0, pb = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-      int t = tile / p.tiles_n;
-      const int k0 = (tile - t * p.tiles_n) * BN;
-      const int tq = t % p.tiles_q; t /= p.tiles_q;
-      const int tp = t % p.tiles_p; t /= p.tiles_p;
-      const int q0 = tq * p.bw, p0 = tp * rows_per_tile, n0 = t;
+    for (int tile = t_first; tile < t_end; tile += t_step) {
+      int k0, tq, tp, n0;
+      decode(tile, k0, tq, tp, n0);
+      const int q0 = tq * p.bw, p0 = tp * rows_per_tile;
       for (int kc = 0; kc < k_chunks; ++kc)
         for (int s = 0; s < p.S; ++s) {
           mbar_wait(&emptyA[sa], pa ^ 1);
@@ -470,7 +578,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_halo_kernel(const __gri
     const uint32_t sub_bytes = (uint32_t)p.bh * row_bytes;
     int sa = 0, sb = 0, local = 0;
     uint32_t pa = 0, pb = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++local) {
+    for (int tile = t_first; tile < t_end; tile += t_step, ++local) {
       const int acc = local & 1;
       mbar_wait(&tmem_empty[acc], ((local >> 1) & 1) ^ 1);
       tc_fence_after();
@@ -509,12 +617,24 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_halo_kernel(const __gri
     const int64_t PQ = (int64_t)p.OH * p.OW;
     const uint32_t plane_bytes = (uint32_t)PQ * 4u;
     int local = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++local) {
-      int t = tile / p.tiles_n;
-      const int k0 = (tile - t * p.tiles_n) * BN;
-      const int tq = t % p.tiles_q; t /= p.tiles_q;
-      const int tp = t % p.tiles_p; t /= p.tiles_p;
-      const int n = t;
+    float racc[BN / 32];            // range mode: this lane's running sums, one per 32-channel chunk
+    int racc_n = -1, racc_k0 = 0;
+#pragma unroll
+    for (int c = 0; c < BN / 32; ++c) racc[c] = 0.f;
+    auto flush = [&]() {
+      if (racc_n >= 0) {
+#pragma unroll
+        for (int c = 0; c < BN / 32; ++c) {
+          const int k = racc_k0 + c * 32 + lane;
+          if (c * 32 < p.n_umma && k < p.K) atomicAdd(p.red_out + (int64_t)racc_n * p.K + k, racc[c]);
+          racc[c] = 0.f;
+        }
+      }
+    };
+    for (int tile = t_first; tile < t_end; tile += t_step, ++local) {
+      int k0, tq, tp, n;
+      decode(tile, k0, tq, tp, n);
+      if (p.range_mode && p.red_out && (n != racc_n || k0 != racc_k0)) { flush(); racc_n = n; racc_k0 = k0; }
       const int q = tq * p.bw + wl;
       const float* osc = p.oscale ? p.oscale + (int64_t)n * p.K : nullptr;
       const int acc = local & 1;
@@ -523,14 +643,34 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_halo_kernel(const __gri
       for (int j = 0; j < p.mt; ++j) {
         const int pp = tp * rows_per_tile + j * p.bh + hl;
         const bool row_ok = (q < p.Q) && (pp < p.P);
-        float* ybase = p.y + ((int64_t)n * p.K) * PQ + (int64_t)(pp * p.o_step + p.o_off_h) * p.OW + q * p.o_step +
-                       p.o_off_w;
-        for (int c0 = 0; c0 < p.n_umma; c0 += 32) {
+        int64_t pix = (int64_t)(pp * p.o_step + p.o_off_h) * p.OW + q * p.o_step + p.o_off_w;
+        int64_t plane = PQ;
+        bool multi = false;
+        if (p.fold) {
+          const int fh = min(max(pp * p.o_step + p.o_off_h - p.fold_pad, 0), p.FH - 1);
+          const int fw = min(max(q * p.o_step + p.o_off_w - p.fold_pad, 0), p.FW - 1);
+          multi = p.fold_pad > 0 && (fh == 0 || fh == p.FH - 1 || fw == 0 || fw == p.FW - 1);
+          pix = (int64_t)fh * p.FW + fw;
+          plane = (int64_t)p.FH * p.FW;
+        }
+        const int64_t nbase = ((int64_t)n * p.K) * plane + (row_ok ? pix : 0);
+        float* ybase = p.y + nbase;
+        const uint32_t pb = p.fold ? (uint32_t)plane * 4u : plane_bytes;
+#pragma unroll
+        for (int c0 = 0; c0 < BN; c0 += 32) {   // static trip count: racc[c0 >> 5] stays in registers
+          if (c0 >= p.n_umma) break;
           float v[32];
           tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)((acc * MT_MAX + j) * BN + c0), v);
           const int kc = k0 + c0;
           const int nvalid = min(p.n_umma - c0, p.K - kc);
-          if (row_ok && nvalid > 0)
+          if (p.fold) {
+            if (nvalid > 0)
+              epi_fold_chunk(v, reinterpret_cast<char*>(ybase + (int64_t)kc * plane),
+                             reinterpret_cast<const char*>(p.red_x ? p.red_x + nbase + (int64_t)kc * plane : nullptr), pb,
+                             nvalid, p.alpha, osc ? osc + kc : nullptr, row_ok, multi,
+                             p.red_out ? p.red_out + (int64_t)n * p.K + kc : nullptr, lane,
+                             p.range_mode ? &racc[c0 >> 5] : nullptr);
+          } else if (row_ok && nvalid > 0)
             epi_chunk(v, reinterpret_cast<char*>(ybase + (int64_t)kc * PQ), plane_bytes, nvalid, p.alpha,
                       osc ? osc + kc : nullptr, p.bias ? p.bias + kc : nullptr);
         }
@@ -539,6 +679,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_halo_kernel(const __gri
       __syncwarp();
       if (lane == 0) mbar_arrive(&tmem_empty[acc]);
     }
+    if (p.range_mode && p.red_out) flush();
   }
   __syncthreads();
   if (warp == 1) {
@@ -597,6 +738,10 @@ struct TcProblem {
   int64_t w_sk, w_sc;     // weight strides for (ko, ci); taps innermost
   TapTable taps;
   float alpha;
+  // scatter epilogue (dgrad of replicate padding fused, optional style-gradient reduction): see epi_fold32
+  int fold = 0, fold_pad = 0, FH = 0, FW = 0;
+  const float* red_x = nullptr;
+  float* red_out = nullptr;
 };
 
 static size_t act_bytes(int N, int Ci, int Hi, int Wi, int mat_pad) {
@@ -722,6 +867,9 @@ static int run_problem(const TcProblem& q, const __nv_bfloat16* act, const float
     if (halo_mode() >= 1 && halo_plan(q, BN, h)) {
       h.n_umma = q.Ko >= BN ? BN : (q.Ko + 15) / 16 * 16;
       h.alpha = q.alpha; h.oscale = out_scale; h.bias = bias; h.y = out;
+      h.fold = q.fold; h.fold_pad = q.fold_pad; h.FH = q.FH; h.FW = q.FW; h.red_x = q.red_x; h.red_out = q.red_out;
+      h.range_mode = q.red_out ? 1 : 0;
+      h.tiles_per_cta = 0;
       CUtensorMap ta, tb;
       uint64_t dims[4] = {(uint64_t)q.Ci, (uint64_t)Wp, (uint64_t)Hp, (uint64_t)q.N};
       uint64_t str[3] = {(uint64_t)Cp * 2, (uint64_t)Wp * Cp * 2, (uint64_t)Hp * Wp * Cp * 2};
@@ -737,23 +885,30 @@ static int run_problem(const TcProblem& q, const __nv_bfloat16* act, const float
       if (rc) return rc;
       const int64_t total = (int64_t)h.tiles_m * h.tiles_n;
       dim3 grid((unsigned)std::min<int64_t>(total, kNumSMs));  // one CTA per SM (shared memory and TMEM are per-SM here)
+      if (h.range_mode) {
+        h.tiles_per_cta = ceil_div(total, grid.x);
+        grid.x = (unsigned)ceil_div(total, h.tiles_per_cta);
+      }
       return BN == 128 ? launch_halo<128>(ta, tb, h, grid, s) : launch_halo<64>(ta, tb, h, grid, s);
     }
   }
   TcConvParams p;
   p.N = q.N; p.K = q.Ko; p.P = q.Po; p.Q = q.Qo; p.taps = NT; p.C = q.Ci;
+  int64_t best = -1;
   {
     // tile box (bw x bh x bn = 128 pixels, powers of two): the shape that covers [N][Po][Qo] with the fewest tiles
     // (padded dgrad domains such as 68x68 would waste half of a 128-wide row tile); ties go to the wider box.
-    int64_t best = -1;
     for (int bw = std::min(pow2ceil(q.Qo), TILE_M); bw >= 1; bw >>= 1) {
       const int bh = std::min(pow2ceil(q.Po), TILE_M / bw), bn = TILE_M / (bw * bh);
+      if (q.red_out && (bn != 1 || (bw * bh) % 32 != 0)) continue;   // the warp reduction assumes one image per warp
       const int64_t tiles = (int64_t)ceil_div(q.Qo, bw) * ceil_div(q.Po, bh) * ceil_div(q.N, bn);
       if (best < 0 || tiles < best) { best = tiles; p.bw = bw; p.bh = bh; p.bn = bn; }
     }
   }
   p.tiles_q = ceil_div(q.Qo, p.bw); p.tiles_p = ceil_div(q.Po, p.bh);
+  GB_REQUIRE(best >= 0, GANB200_BAD_SHAPE, "tc conv: no tile box for the fused reduction");
   p.alpha = q.alpha; p.oscale = out_scale; p.bias = bias; p.y = out;
+  p.fold = q.fold; p.fold_pad = q.fold_pad; p.FH = q.FH; p.FW = q.FW; p.red_x = q.red_x; p.red_out = q.red_out;
   p.in_step = q.in_step; p.OH = q.OH; p.OW = q.OW; p.o_step = q.o_step; p.o_off_h = q.o_off_h; p.o_off_w = q.o_off_w;
   for (int t = 0; t < NT; ++t) { p.dh[t] = q.taps.dh[t]; p.dw[t] = q.taps.dw[t]; }
   p.n_umma = q.Ko >= BN ? BN : (q.Ko + 15) / 16 * 16;
@@ -926,7 +1081,8 @@ int tc_pack_weight(const ganb200_conv_desc* d, int op, const float* w, void* out
 
 static int dgrad_run(const ganb200_conv_desc* d, const float* dy, const float* w, const float* iscale,
                      const float* oscale, float* dx, void* ws, cudaStream_t s, bool fold, float** padded_out,
-                     const void* dyp = nullptr, const void* wp = nullptr);
+                     const void* dyp = nullptr, const void* wp = nullptr, const float* red_x = nullptr,
+                     float* red_out = nullptr);
 
 int tc_dgrad(const ganb200_conv_desc* d, const float* dy, const float* w, const float* iscale, const float* oscale,
              float* dx, void* ws, size_t ws_bytes, cudaStream_t s, const void* dyp, const void* wp) {
@@ -935,18 +1091,56 @@ int tc_dgrad(const ganb200_conv_desc* d, const float* dy, const float* w, const 
   return dgrad_run(d, dy, w, iscale, oscale, dx, align_ws(ws), s, true, nullptr, dyp, wp);
 }
 
+// 1 (default): dgrad of replicate-padded convolutions scatters straight into the unpadded plane from the MMA epilogue
+// (epi_fold32); 0: round-1 path — padded fp32 domain in the workspace + a fold pass.  GANB200_DGRAD_SCATTER=0 or
+// ganb200_conv_scatter_mode(0).
+static int g_scatter_mode = -1;
+static int scatter_mode() {
+  if (g_scatter_mode < 0) {
+    const char* e = getenv("GANB200_DGRAD_SCATTER");
+    g_scatter_mode = (e && e[0] == '0') ? 0 : 1;
+  }
+  return g_scatter_mode;
+}
+
+// zero the border pixels of every H x W plane (the only pixels the scatter epilogue accumulates into)
+__global__ void __launch_bounds__(256) zero_border_kernel(float* __restrict__ x, int64_t planes, int H, int W) {
+  const int per = (H <= 2 || W <= 2) ? H * W : 2 * W + 2 * (H - 2);
+  grid_stride(planes * per, [&](auto i) {
+    const int e = (int)(i % per);
+    const int64_t pl = (int64_t)(i / per);
+    int h, w;
+    if (H <= 2 || W <= 2) { h = e / W; w = e - h * W; }
+    else if (e < W) { h = 0; w = e; }
+    else if (e < 2 * W) { h = H - 1; w = e - W; }
+    else { const int r = e - 2 * W; h = 1 + (r >> 1); w = (r & 1) ? W - 1 : 0; }
+    x[(pl * H + h) * W + w] = 0.f;
+  });
+}
+
 // ws (1024-aligned): [dy packed][phase weights][padded fp32 output (replicate padding only)].  With fold == false the
 // padded-domain result is left in the workspace (*padded_out) for a fused consumer.
 static int dgrad_run(const ganb200_conv_desc* d, const float* dy, const float* w, const float* iscale,
                      const float* oscale, float* dx, void* ws, cudaStream_t s, bool fold, float** padded_out,
-                     const void* dyp, const void* wp) {
+                     const void* dyp, const void* wp, const float* red_x, float* red_out) {
   const bool rep = d->pad_mode == 1 && d->pad > 0;
   const __nv_bfloat16* act = dyp ? (const __nv_bfloat16*)dyp : (const __nv_bfloat16*)ws;
   uint8_t* ws_w = (uint8_t*)ws + act_bytes(d->N, d->K, d->P, d->Q, 0);
   uint8_t* wbase = wp ? (uint8_t*)wp : ws_w;
   float* out = dx;
-  if (rep) out = (float*)(ws_w + dgrad_w_bytes(d));
-  if (padded_out) *padded_out = out;
+  // scatter epilogue: straight into dx (callers that pass fold == true, or a reduction target)
+  const bool scatter = (fold || red_out) && dx && (rep || red_out) && scatter_mode() == 1;
+  if (rep && !scatter) out = (float*)(ws_w + dgrad_w_bytes(d));
+  if (padded_out) *padded_out = scatter ? nullptr : out;
+  if (scatter) {
+    if (rep) {
+      const int64_t planes = (int64_t)d->N * d->C;
+      const int per = (d->H <= 2 || d->W <= 2) ? d->H * d->W : 2 * d->W + 2 * (d->H - 2);
+      zero_border_kernel<<<ew_grid(planes * per, 256, 1), 256, 0, s>>>(dx, planes, d->H, d->W);
+      GB_CHECK_LAUNCH();
+    }
+    if (red_out) GB_CHECK_CUDA(cudaMemsetAsync(red_out, 0, sizeof(float) * (size_t)d->N * d->C, s));
+  }
   int rc = 0;
   if (!dyp) {
     rc = pack_input(dy, oscale, (__nv_bfloat16*)ws, d->N, d->K, d->P, d->Q, 0, s);
@@ -958,11 +1152,14 @@ static int dgrad_run(const ganb200_conv_desc* d, const float* dy, const float* w
       TcProblem q = dgrad_problem(d, a, b);
       if (q.Po <= 0 || q.Qo <= 0) continue;
       GB_REQUIRE(q.taps.n > 0, GANB200_BAD_SHAPE, "tc dgrad: an output phase has no filter tap");
+      if (scatter) {
+        q.fold = 1; q.fold_pad = rep ? d->pad : 0; q.FH = d->H; q.FW = d->W; q.red_x = red_x; q.red_out = red_out;
+      }
       rc = run_problem(q, act, w, (__nv_bfloat16*)(wbase + woff), out, iscale, nullptr, s, wp != nullptr);
       if (rc) return rc;
       woff += w_bytes(q.taps.n, d->C, d->K);
     }
-  if (rep && fold) return fold_replicate(out, dx, (int64_t)d->N * d->C, d->H, d->W, d->pad, s);
+  if (rep && fold && !scatter) return fold_replicate(out, dx, (int64_t)d->N * d->C, d->H, d->W, d->pad, s);
   return 0;
 }
 
@@ -1513,6 +1710,12 @@ static size_t modconv_bwd_bytes(const ganb200_conv_desc* d) {
 
 using namespace ganb200;
 
+extern "C" int ganb200_conv_scatter_mode(int mode) {
+  const int prev = scatter_mode();
+  if (mode == 0 || mode == 1) g_scatter_mode = mode;
+  return prev;
+}
+
 extern "C" int ganb200_conv_halo_mode(int mode) {
   const int prev = halo_mode();
   if (mode >= 0 && mode <= 2) g_halo_mode = mode;
@@ -1566,12 +1769,30 @@ static int modconv_bwd_impl(const ganb200_conv_desc* d, const float* x, const fl
   // pad == 0 (1x1 convs): no padded domain, the dgrad kernels write a plain [N,C,H,W] buffer behind the wgrad scratch
   float* direct = (float*)(wws + wp.dy_bytes + wp.x_bytes + wp.part_bytes);
   // dgrad part of the workspace first: its head is the packed gu, shared with wgrad
-  rc = dgrad_run(d, gu, w, nullptr, sinv, direct, base, st, false, &dxp, nullptr, wp_dgrad);
-  if (rc) return rc;
-  if (gx || gs1) {
+  // GANB200_MODCONV_RED=1 (experimental): the dgrad epilogue also scales by s and reduces sum_hw dxs * x into gs1
+  // (epi_fold32 with red_x; contiguous tile ranges so the sums stay in registers per image).  Measured at B = 256
+  // (tools/scatter_bench.py): it wins where the main loop is long enough to hide the four epilogue warps' extra loads
+  // (96->96 5x5 @64x64: 1.54 -> 1.38 ms) and loses where it is not (48->48 3x3: 0.54 -> 0.60 ms; 96->96 3x3: 1.06 -> 1.25)
+  // — ~0 over the generator's mix, so the default keeps the padded domain + fold_scale_reduce pass for the modulated
+  // convolution and uses the scatter epilogue for the plain dgrads (the critic's: 0.45 -> 0.31 ms at 64 channels).
+  static int red_mode = -1;
+  if (red_mode < 0) { const char* e = getenv("GANB200_MODCONV_RED"); red_mode = (e && e[0] == '1') ? 1 : 0; }
+  const bool rep0 = d->pad_mode == 1 && d->pad > 0;
+  const bool fused = red_mode == 1 && scatter_mode() == 1 && (gx || gs1) && (int64_t)d->H * d->W >= 256;
+  bool folded = false;   // dxp holds the folded (unpadded) dxs
+  if (fused) {
+    // gs1 alone (gx not wanted): the scaled scatter still needs a target; the padded-output region of the workspace serves
+    float* tgt = gx ? gx : (rep0 ? (float*)(base + act_bytes(d->N, d->K, d->P, d->Q, 0) + dgrad_w_bytes(d)) : direct);
+    rc = dgrad_run(d, gu, w, s, sinv, tgt, base, st, true, nullptr, nullptr, wp_dgrad, gs1 ? x : nullptr, gs1);
+    if (rc) return rc;
+  } else {
+    rc = dgrad_run(d, gu, w, nullptr, sinv, direct, base, st, false, &dxp, nullptr, wp_dgrad);
+    if (rc) return rc;
+  }
+  if (!fused && (gx || gs1)) {
     const int64_t rows = (int64_t)d->N * d->C;
     const int HW = d->H * d->W;
-    const int pad = (d->pad_mode == 1) ? d->pad : 0;
+    const int pad = (d->pad_mode == 1 && !folded) ? d->pad : 0;
     if (HW >= 1024) {
       int grid = (int)std::min<int64_t>(rows, (int64_t)kNumSMs * 32);
       fold_scale_reduce_kernel<false><<<grid, 256, 0, st>>>(dxp, s, x, gx, gs1, d->H, d->W, pad, rows);

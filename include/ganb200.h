@@ -80,6 +80,13 @@ int ganb200_conv2d_route(const ganb200_conv_desc* d, int op);
  * (identical operands and accumulation order per output element).  Returns the previous mode; any other value
  * only queries.  Process-wide; also GANB200_CONV_HALO=0 in the environment. */
 int ganb200_conv_halo_mode(int mode);
+/* tcgen05 engine, dgrad of replicate-padded convolutions (and the fused modulated-conv backward): 1 (default) the MMA
+ * epilogue scatters each padded-domain value straight into the clamped pixel of the unpadded plane (plain stores inside,
+ * red.global.add on the border ring, which the host zeroes first) and, for the modulated convolution, also forms the style
+ * gradient sum_hw dxs * x; 0 = the round-1 path: padded fp32 domain in the workspace, then a fold (+ scale + reduce) pass.
+ * Same sums in another order on the border pixels.  Returns the previous mode; any other value only queries.
+ * Process-wide; also GANB200_DGRAD_SCATTER=0 in the environment. */
+int ganb200_conv_scatter_mode(int mode);
 int ganb200_conv2d_fprop(const ganb200_conv_desc* d, const float* x, const float* w, const float* bias,
                          const float* iscale, const float* oscale, float* y,
                          void* ws, size_t ws_bytes, void* stream);

@@ -635,3 +635,66 @@ def test_grouped_style_bank_cuda_equals_layer_by_layer(cu):
             assert (p.grad - q.grad).norm().item() <= FP32_TOL * max(q.grad.norm().item(), scale), n
         for (n, p), (_, q) in zip(ma.named_buffers(), mb.named_buffers()):
             assert rel(p.double(), q.double()) < FP32_TOL, n
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# scatter epilogue (round 2): dgrad of replicate padding straight into the unpadded plane, style-gradient reduce fused
+# ---------------------------------------------------------------------------------------------------------------
+SCATTER_CASES = [
+    # N, C, H, W, K, R, stride, pad
+    (4, 96, 64, 64, 96, 5, 1, 2),    # halo kernel, k5
+    (4, 48, 64, 64, 54, 3, 1, 1),    # halo kernel, K not a multiple of 32
+    (4, 64, 64, 64, 64, 3, 1, 1),    # per-tap kernel (the critic's)
+    (8, 128, 16, 16, 128, 3, 1, 1),  # small plane: padded domain 18 x 18
+    (8, 192, 8, 8, 192, 5, 1, 2),    # 8 x 8 plane (several images per tile)
+    (16, 1025, 4, 4, 1025, 3, 1, 1), # 4 x 4 plane, odd channels
+    (4, 64, 18, 18, 64, 3, 2, 1),    # stride 2: four output phases scatter into one plane
+    (4, 3, 32, 32, 64, 3, 1, 1),     # C = 3 outputs (the stem's dgrad)
+]
+
+
+@pytest.mark.parametrize("case", SCATTER_CASES)
+def test_dgrad_scatter_epilogue_equals_fold_pass(cu, ref, case):
+    N, C, H, W, K, R, stride, pad = case
+    torch.manual_seed(21)
+    P, Q = KN.out_hw(H, W, R, R, stride, pad)
+    dy, w = rnd(N, K, P, Q).cuda(), rnd(K, C, R, R).cuda()
+    isc = (torch.rand(N, C) + 0.5).cuda()
+    out = {}
+    for mode in (0, 1):
+        prev = cu.lib.ganb200_conv_scatter_mode(mode)
+        try:
+            out[mode] = (cu.conv_dgrad(dy, w, (H, W), stride, pad, 1, 0.05, engine=2),
+                         cu.conv_dgrad(dy, w, (H, W), stride, pad, 1, 0.05, iscale=isc, engine=2))
+        finally:
+            cu.lib.ganb200_conv_scatter_mode(prev)
+    for a, b in zip(out[1], out[0]):
+        assert rel(a, b) < FP32_TOL   # the same bf16 products, fp32 sums re-ordered on the border pixels only
+    want = ref.conv_dgrad(dy.cpu(), w.cpu(), (H, W), stride, pad, 1, 0.05)
+    assert rel(out[1][0], want) < BF16_TOL
+
+
+@pytest.mark.parametrize("case", [(4, 96, 64, 96, 5), (4, 48, 64, 54, 3), (4, 390, 32, 96, 1), (8, 96, 16, 96, 3),
+                                  (8, 192, 8, 192, 5), (16, 384, 4, 384, 3)])
+@pytest.mark.parametrize("needs", [(True, True, True), (False, True, True), (True, False, False)])
+def test_modconv_bwd_fused_scatter_equals_unfused(cu, case, needs):
+    """ganb200_modconv_bwd with the scatter epilogue (gx = s * fold(dxs) and gs1 = sum_hw dxs * x from the MMA epilogue)
+    against the round-1 sequence (padded domain, then fold_scale_reduce)."""
+    N, C, HW, K, R = case
+    need_x, need_s, need_w = needs
+    torch.manual_seed(22)
+    x, w = rnd(N, C, HW, HW).cuda(), rnd(K, C, R, R).cuda()
+    s, sinv = (torch.rand(N, C) + 0.5).cuda(), (torch.rand(N, K) + 0.5).cuda()
+    gu = rnd(N, K, HW, HW).cuda()
+    out = {}
+    for mode in (0, 1):
+        prev = cu.lib.ganb200_conv_scatter_mode(mode)
+        try:
+            out[mode] = cu.modconv_bwd(x, w, s, sinv, gu, R // 2, 0.02, need_x, need_s, need_w, engine=2)
+        finally:
+            cu.lib.ganb200_conv_scatter_mode(prev)
+    assert out[0] is not None and out[1] is not None
+    for a, b, name in zip(out[1], out[0], ("gx", "gs1", "gw")):
+        assert (a is None) == (b is None), name
+        if a is not None:
+            assert rel(a, b) < 2e-5, (name, rel(a, b))
