@@ -111,6 +111,8 @@ class GraphedStep:
                 self.images.grad = None
         torch.cuda.current_stream(dev).wait_stream(side)
         torch.cuda.synchronize(dev)
+        # the eager warm-up's cached blocks are of no use to the graphs' private pool: hand them back first
+        torch.cuda.empty_cache()
         # each graph must re-pack every weight it uses at its own start (a replay may follow ANY other replay): start the
         # captures with the packed-weight cache cold
         KN.bump_param_epoch()

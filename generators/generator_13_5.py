@@ -26,6 +26,7 @@ import torch.nn as nn
 from gan_b200 import layers as L
 from gan_b200 import ops
 from gan_b200 import rng
+from gan_b200 import streams
 from gan_b200 import kernels as KN
 
 
@@ -358,10 +359,11 @@ class ResnetInit(nn.Module):
 
     def forward(self, x: Tuple[torch.Tensor, torch.Tensor], w: torch.Tensor):
         x_res, x_tra = x
-        r_r = self.residual(x_res, w)
-        r_t = self.residual_across(x_res, w)
-        t_t = self.transient(x_tra, w)
-        t_r = self.transient_across(x_tra, w)
+        # four independent StyleBlocks: on four CUDA streams (gan_b200/streams.py) their latency-bound SK-attention
+        # tails overlap; same kernels, same results
+        r_r, r_t, t_t, t_r = streams.run_parallel(
+            [lambda: self.residual(x_res, w), lambda: self.residual_across(x_res, w),
+             lambda: self.transient(x_tra, w), lambda: self.transient_across(x_tra, w)], x_res.device)
         return self.activation_residual(ops.add(r_r, t_r)), self.activation_transient(ops.add(r_t, t_t))
 
 
