@@ -123,40 +123,46 @@ __global__ void __launch_bounds__(256) pack_act_vec_kernel(const float* __restri
   }
 }
 
-// Second generation of the vectorised pack for W = 16 / 32 / 64 (every large plane of the models).  ncu on the first
-// (profiles/r02: 4.26 TB/s, 0.69 issued warp-instructions per scheduler and cycle) showed it bound by instruction issue,
-// not by memory: runtime divisions in the index maths, four 32-bit shared loads per 16-byte store.  Here W is a template
-// parameter (shifts), a warp loads a 4 w-group x 8 channel-pair tile, the transposed tile has a 34-word pitch — stores
-// hit 32 distinct banks (8*g + 2*j + cp) and the store phase reads two conflict-free 64-bit words per 16-byte store.
-template <int LOG_G4>
+// Second generation of the vectorised pack (used for 16 x 16 planes).  W is a template parameter (shifts instead of
+// divisions), a warp loads a 4 w-group x 8 channel-pair tile, the transposed tile has a 34-word pitch — stores hit 32
+// distinct banks (8*g + 2*j + cp) and the store phase reads two conflict-free 64-bit words per 16-byte store.
+// (ncu on the first generation at 64 x 64: 4.26 TB/s with 0.69 issued warp-instructions per scheduler and cycle; cutting
+// its instruction count this way did NOT make it faster there, so it stays in use for the wide planes.)
+// ROWS input rows per block: every channel then contributes ROWS * W * 4 contiguous bytes (1 KB at W = 64) instead of
+// one 256-byte row — the first generation read 64 separate 256-byte pieces 16 KB apart per block, one DRAM page each.
+template <int LOG_G4, int ROWS>
 __global__ void __launch_bounds__(256) pack_act_vec2_kernel(const float* __restrict__ x, const float* __restrict__ scale,
                                                             __nv_bfloat16* __restrict__ out, int C, int H, int Cp,
                                                             int pad) {
   constexpr int G4 = 1 << LOG_G4, W = 4 * G4, PITCH = 34;
-  __shared__ __align__(16) uint32_t tw[W * PITCH];
+  __shared__ __align__(16) uint32_t tw[ROWS][W * PITCH];
   const int Hp = H + 2 * pad, Wp = W + 2 * pad;
-  const int n = blockIdx.x / H, h = blockIdx.x - n * H;
+  const int hb = (H + ROWS - 1) / ROWS;
+  const int n = blockIdx.x / hb, h0 = (blockIdx.x - n * hb) * ROWS;
   const int c0 = blockIdx.y * 64;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int gl = lane >> 3, cl = lane & 7;
-  constexpr int TILES_G = G4 / 4, TILES = TILES_G * 4;       // tiles of 4 w-groups x 8 channel pairs
-  const float* xrow = x + (((int64_t)n * C + c0) * H + h) * W;
+  constexpr int TILES_G = G4 / 4, TILES = TILES_G * 4;       // tiles of 4 w-groups x 8 channel pairs, per row
+  const float* xrow = x + (((int64_t)n * C + c0) * H + h0) * W;
   const float* srow = scale ? scale + (int64_t)n * C + c0 : nullptr;
   const int64_t cstride = (int64_t)H * W;
+  const int rows = min(ROWS, H - h0);
 #pragma unroll
-  for (int t = warp; t < TILES; t += 8) {
-    const int g = (t % TILES_G) * 4 + gl, cp = (t / TILES_G) * 8 + cl;
+  for (int t = warp; t < TILES * ROWS; t += 8) {
+    const int r = t / TILES, tt = t - r * TILES;
+    if (r >= rows) break;
+    const int g = (tt % TILES_G) * 4 + gl, cp = (tt / TILES_G) * 8 + cl;
     const int c = c0 + 2 * cp;
     float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
     if (c < C) {
-      a = __ldg(reinterpret_cast<const float4*>(xrow + (2 * cp) * cstride) + g);
+      a = __ldg(reinterpret_cast<const float4*>(xrow + (2 * cp) * cstride + r * W) + g);
       if (srow) { const float sc = __ldg(srow + 2 * cp); a.x *= sc; a.y *= sc; a.z *= sc; a.w *= sc; }
     }
     if (c + 1 < C) {
-      b = __ldg(reinterpret_cast<const float4*>(xrow + (2 * cp + 1) * cstride) + g);
+      b = __ldg(reinterpret_cast<const float4*>(xrow + (2 * cp + 1) * cstride + r * W) + g);
       if (srow) { const float sc = __ldg(srow + 2 * cp + 1); b.x *= sc; b.y *= sc; b.z *= sc; b.w *= sc; }
     }
-    uint32_t* d = tw + (4 * g) * PITCH + cp;
+    uint32_t* d = tw[r] + (4 * g) * PITCH + cp;
     d[0] = pack_bf162(a.x, b.x);
     d[PITCH] = pack_bf162(a.y, b.y);
     d[2 * PITCH] = pack_bf162(a.z, b.z);
@@ -164,16 +170,19 @@ __global__ void __launch_bounds__(256) pack_act_vec2_kernel(const float* __restr
   }
   __syncthreads();
   const int chunks = min(64, Cp - c0) >> 3;   // 16-byte chunks of valid (padded) channels
-  const int hp_lo = (h == 0) ? 0 : h + pad, hp_hi = (h == H - 1) ? Hp - 1 : h + pad;
   const int k = threadIdx.x & 7;
   if (k < chunks) {
-    for (int hp = hp_lo; hp <= hp_hi; ++hp) {
-      __nv_bfloat16* orow = out + ((int64_t)n * Hp + hp) * Wp * Cp + c0 + 8 * k;
-      for (int wp = threadIdx.x >> 3; wp < Wp; wp += 32) {
-        const int w = min(max(wp - pad, 0), W - 1);
-        const uint2* sp = reinterpret_cast<const uint2*>(tw + w * PITCH + 4 * k);
-        const uint2 lo = sp[0], hi = sp[1];
-        *reinterpret_cast<uint4*>(orow + (int64_t)wp * Cp) = make_uint4(lo.x, lo.y, hi.x, hi.y);
+    for (int r = 0; r < rows; ++r) {
+      const int h = h0 + r;
+      const int hp_lo = (h == 0) ? 0 : h + pad, hp_hi = (h == H - 1) ? Hp - 1 : h + pad;
+      for (int hp = hp_lo; hp <= hp_hi; ++hp) {
+        __nv_bfloat16* orow = out + ((int64_t)n * Hp + hp) * Wp * Cp + c0 + 8 * k;
+        for (int wp = threadIdx.x >> 3; wp < Wp; wp += 32) {
+          const int w = min(max(wp - pad, 0), W - 1);
+          const uint2* sp = reinterpret_cast<const uint2*>(tw[r] + w * PITCH + 4 * k);
+          const uint2 lo = sp[0], hi = sp[1];
+          *reinterpret_cast<uint4*>(orow + (int64_t)wp * Cp) = make_uint4(lo.x, lo.y, hi.x, hi.y);
+        }
       }
     }
   }
@@ -871,11 +880,12 @@ static int pack_input(const float* in, const float* in_scale, __nv_bfloat16* act
   const int Cp = cpad(Ci), Hp = Hi + 2 * mat_pad;
   static int pack_v2 = -1;
   if (pack_v2 < 0) { const char* e = getenv("GANB200_PACK_V2"); pack_v2 = (e && e[0] == '0') ? 0 : 1; }
-  if (pack_v2 && (Wi == 64 || Wi == 32 || Wi == 16) && ((uintptr_t)in & 15) == 0) {
-    dim3 grid(N * Hi, (Cp + 63) / 64);
-    if (Wi == 64) pack_act_vec2_kernel<4><<<grid, 256, 0, s>>>(in, in_scale, act, Ci, Hi, Cp, mat_pad);
-    else if (Wi == 32) pack_act_vec2_kernel<3><<<grid, 256, 0, s>>>(in, in_scale, act, Ci, Hi, Cp, mat_pad);
-    else pack_act_vec2_kernel<2><<<grid, 256, 0, s>>>(in, in_scale, act, Ci, Hi, Cp, mat_pad);
+  // measured at N = 256 (tools/pack_bench.py): the 4-rows-per-block kernel wins on 16 x 16 planes (2.9 -> 3.9 TB/s: the
+  // one-row kernel's blocks are too small there), ties at 32 x 32 and loses at 64 x 64 (4.4 -> 4.1 TB/s)
+  if (pack_v2 && Wi == 16 && ((uintptr_t)in & 15) == 0) {
+    constexpr int ROWS = 4;
+    dim3 grid(N * ((Hi + ROWS - 1) / ROWS), (Cp + 63) / 64);
+    pack_act_vec2_kernel<2, ROWS><<<grid, 256, 0, s>>>(in, in_scale, act, Ci, Hi, Cp, mat_pad);
     GB_CHECK_LAUNCH();
     return 0;
   }

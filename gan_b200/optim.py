@@ -93,7 +93,7 @@ class FusedAdam(torch.optim.Optimizer):
                     continue
                 if p.grad.is_sparse:
                     raise RuntimeError("FusedAdam does not support sparse gradients")
-                if p.dtype != torch.float32 or not p.is_contiguous():
+                if not hasattr(k, "adam_reference") and (p.dtype != torch.float32 or not p.is_contiguous()):
                     raise RuntimeError(f"FusedAdam updates contiguous float32 parameters, got {p.dtype} "
                                        f"{'contiguous' if p.is_contiguous() else 'strided'} {tuple(p.shape)}")
                 st = self.state[p]
