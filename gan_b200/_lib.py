@@ -92,6 +92,7 @@ SIGNATURES = {
     "ganb200_bn1d_group_apply": (c_int, [P, c_int, c_int, P, P, c_int, P, P, P, c_float, c_float, c_int64, P]),
     "ganb200_bn1d_group_bwd_reduce": (c_int, [P, c_int, c_int, P, P, c_int, P, P, P, P, P, P]),
     "ganb200_bn1d_group_bwd_apply": (c_int, [P, c_int, c_int, P, P, P, c_int, P, P, P, P, c_int64, P, P]),
+    "ganb200_gather_flip": (c_int, [P, P, P, P, c_int, c_int, c_int, c_int, P]),
     "ganb200_minmax": (c_int, [P, c_int64, P, P]),
     "ganb200_make_grid_u8": (c_int, [P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, P]),
     "ganb200_bce_fwd": (c_int, [P, P, P, P, c_int64, P]),

@@ -210,8 +210,36 @@ __global__ void __launch_bounds__(256) make_grid_u8_kernel(const float* __restri
   }
 }
 
+// ------------------------------------------------------------------ input pipeline (units/dataloader.py:5-32)
+// batch[b] = cache[idx[b]] with the columns reversed when flip[b] != 0 (RandomHorizontalFlip on the cached, already
+// resized + normalised image: the flip commutes with the symmetric bicubic resize and the per-channel normalisation).
+// cache: [n][CHW] fp32 resident in HBM; one launch per batch, no host work.
+__global__ void __launch_bounds__(256) gather_flip_kernel(const float* __restrict__ cache, const int64_t* __restrict__ idx,
+                                                          const unsigned char* __restrict__ flip, float* __restrict__ out,
+                                                          int B, int CH, int W) {
+  const int64_t per = (int64_t)CH * W;
+  grid_stride((int64_t)B * per, [&](auto i) {
+    const int w = (int)(i % W);
+    const auto t = i / W;
+    const int ch = (int)(t % CH);
+    const int b = (int)(t / CH);
+    const int ws = flip[b] ? W - 1 - w : w;
+    out[i] = __ldg(cache + idx[b] * per + (int64_t)ch * W + ws);
+  });
+}
+
 }  // namespace ganb200
 using namespace ganb200;
+
+extern "C" int ganb200_gather_flip(const float* cache, const int64_t* idx, const unsigned char* flip, float* out, int B,
+                                   int C, int H, int W, void* stream) {
+  if ((int64_t)B * C * H * W <= 0) return 0;
+  GB_REQUIRE(cache && idx && flip && out, GANB200_BAD_ARG, "gather_flip: null pointer");
+  gather_flip_kernel<<<ew_grid((int64_t)B * C * H * W, 256, 4), 256, 0, (cudaStream_t)stream>>>(cache, idx, flip, out, B,
+                                                                                             C * H, W);
+  GB_CHECK_LAUNCH();
+  return 0;
+}
 
 extern "C" int ganb200_minmax(const float* x, int64_t n, float* out2, void* stream) {
   GB_REQUIRE(n > 0 && x && out2, GANB200_BAD_ARG, "minmax: empty input");

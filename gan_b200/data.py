@@ -35,9 +35,12 @@ def _split_flip(transform):
 
 
 class CachedImageLoader:
-    def __init__(self, dataset, batch_size, device=None, rank=0, world=1, seed=0, flip_p=None):
+    def __init__(self, dataset, batch_size, device=None, rank=0, world=1, seed=0, flip_p=None, device_cache=False):
         """`dataset`: a torchvision-style dataset with a `.transform` (units.dataloader.get_dataset / get_MNIST).
-        `batch_size` is per rank; the global batch is batch_size * world."""
+        `batch_size` is per rank; the global batch is batch_size * world.
+        `device_cache`: keep the cached data set in HBM (48 KB per 64x64 RGB image: 200 000 images = 9.6 GB) and build
+        every batch with ONE kernel launch (ganb200_gather_flip: row gather + horizontal flip), no host work and no
+        host-to-device copy per batch; the batches equal the host path's bit for bit."""
         self.batch_size, self.rank, self.world, self.seed = int(batch_size), int(rank), int(world), int(seed)
         self.device = torch.device(device) if device is not None else torch.device("cpu")
         self.epoch = 0
@@ -62,6 +65,10 @@ class CachedImageLoader:
         if self.world > 1 and self.batch_size % 4 != 0:
             raise ValueError("data parallel: the per-rank batch must be a multiple of 4 (MiniBatchStdDev groups)")
         self._stage = None
+        self.device_cache = bool(device_cache) and self.device.type == "cuda"
+        if self.device_cache:
+            self.images_dev = self.images.to(self.device)
+            self.labels_dev = self.labels.to(self.device)
 
     def __len__(self):
         return self.images.shape[0] // (self.batch_size * self.world)
@@ -87,6 +94,12 @@ class CachedImageLoader:
         for k in range(len(self)):
             glob = perm[k * bg:(k + 1) * bg]
             idx = shard_quarter_major(glob, self.rank, self.world) if self.world > 1 else glob
+            if self.device_cache:
+                from . import kernels as KN
+                idx_dev = idx.to(self.device, non_blocking=True)
+                yield (KN.backend().gather_flip(self.images_dev, idx_dev, flips[idx].to(self.device, non_blocking=True)),
+                       self.labels_dev.index_select(0, idx_dev))
+                continue
             if not cuda:
                 out = torch.empty((self.batch_size,) + tuple(self.images.shape[1:]), dtype=torch.float32)
                 yield self._host_batch(idx, flips[idx], out), self.labels[idx]

@@ -716,6 +716,19 @@ class CudaBackend:
         LAUNCH_COUNT[0] += 1
         _lib.check(self.lib.ganb200_multi_tensor_copy(self._p(tab), self._p(block_tab), n_blocks, chunk, st))
 
+    def gather_flip(self, cache, idx, flips):
+        """cache:[n,C,H,W] fp32 on the device, idx: int64[B], flips: uint8/bool[B] -> [B,C,H,W] (flipped where asked)"""
+        st = self._prep(cache)
+        B = idx.numel()
+        _, C, H, W = cache.shape
+        if idx.dtype != torch.int64 or not idx.is_cuda or not flips.is_cuda:
+            raise _lib.GanB200Error("gather_flip: idx must be int64 and idx / flips on the device")
+        flips = flips.to(torch.uint8)
+        out = torch.empty((B, C, H, W), dtype=torch.float32, device=cache.device)
+        _lib.check(self.lib.ganb200_gather_flip(self._p(cache), ctypes.c_void_p(idx.data_ptr()),
+                                                ctypes.c_void_p(flips.data_ptr()), self._p(out), B, C, H, W, st))
+        return out
+
     def make_grid_u8(self, x, nrow=8, padding=2):
         """torchvision make_grid(normalize=True) + save_image quantisation on the device -> uint8 [GH, GW, 3]"""
         N, C, H, W = x.shape

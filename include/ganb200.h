@@ -263,6 +263,13 @@ int ganb200_bn1d_group_bwd_apply(const ganb200_gbn_job* jobs, int n_jobs, int n_
                                  const float* x_base, float* gx_base, int N, const float* mean, const float* invstd,
                                  const float* s1, const float* s2, int64_t count_total, float* gbias, void* stream);
 
+/* Input pipeline with the data set cached in HBM (gan_b200/data.py; reference units/dataloader.py:5-32 decodes, flips,
+ * resizes and normalises every image again every epoch on the host): out[b] = cache[idx[b]] ([C,H,W] fp32 images, already
+ * resized and normalised once), columns reversed where flip[b] != 0 (RandomHorizontalFlip).  idx: int64[B], flip: uint8[B],
+ * both on the device. */
+int ganb200_gather_flip(const float* cache, const int64_t* idx, const unsigned char* flip, float* out, int B, int C,
+                        int H, int W, void* stream);
+
 /* Preview grid of the sampling path (train/trainunits.py:52-56: generator(fixed_noise) -> torchvision
  * make_grid(padding=2, normalize=True) -> save_image).  minmax: out2 = {min(x), max(x)} over all n elements.
  * make_grid_u8: x [N,C,H,W] fp32 (C = 1 is shown as grey, like torchvision) -> out uint8 [GH][GW][3], the bytes torchvision's

@@ -381,6 +381,12 @@ class RefBackend:
         Pm = (ga * u.clamp(max=0)).reshape(N, K, -1).sum(-1) if slope is not None else None
         return gu, Ad, Z, Pm
 
+    def gather_flip(self, cache, idx, flips):
+        out = cache.index_select(0, idx).clone()
+        sel = flips.to(torch.bool).nonzero().flatten()
+        out[sel] = out[sel].flip(-1)
+        return out
+
     def make_grid_u8(self, x, nrow=8, padding=2):
         """torchvision.utils.make_grid(normalize=True) + save_image's quantisation, restated op by op (the GPU test and
         tests/test_units.py compare it with torchvision itself)."""

@@ -176,3 +176,27 @@ def test_cached_loader_equals_the_dataset_pipeline_and_shards_quarter_major(tmp_
         assert torch.equal(torch.cat([x0.reshape(4, -1), x1.reshape(4, -1)], 1), xg.reshape(4, -1))
     with pytest.raises(ValueError):
         CachedImageLoader(ds, 6, rank=0, world=2)
+
+
+@pytest.mark.gpu
+def test_device_cached_loader_equals_the_host_path_bit_for_bit(tmp_path):
+    """CachedImageLoader(device_cache=True): the data set lives in HBM and every batch is ONE ganb200_gather_flip launch;
+    same permutation, same flips, same bytes as the host-gather path (and therefore as the dataset's own pipeline)."""
+    import numpy as np
+    from PIL import Image
+    from gan_b200.data import CachedImageLoader
+    from units import dataloader
+    root = tmp_path / "imgs" / "cls"
+    root.mkdir(parents=True)
+    rs = np.random.RandomState(2)
+    for i in range(37):
+        Image.fromarray(rs.randint(0, 255, (40 + i, 51, 3), dtype=np.uint8)).save(root / f"{i:02d}.png")
+    ds = dataloader.get_dataset(str(tmp_path / "imgs"), size=64)
+    host = CachedImageLoader(ds, 8, seed=5)
+    dev = CachedImageLoader(ds, 8, device="cuda", seed=5, device_cache=True)
+    n = 0
+    for _ in range(2):  # two epochs: permutation and flips change with seed + epoch on both
+        for (xh, yh), (xd, yd) in zip(host, dev):
+            assert xd.is_cuda and torch.equal(xd.cpu(), xh) and torch.equal(yd.cpu(), yh)
+            n += 1
+    assert n == 2 * len(host) == 8
