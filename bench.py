@@ -300,6 +300,7 @@ def replay_census(census, device, reps=3, dump=None):
 def run_native(args):
     from gan_b200 import dist as gdist
     from gan_b200 import kernels as KN
+    from gan_b200 import peer as gpeer
     import torch.distributed as tdist
     rank, world, device = gdist.init_from_env()
     assert device.type == "cuda", "bench.py's own arm needs a B200 (there is no CPU fallback)"
@@ -324,10 +325,12 @@ def run_native(args):
             KN.LAUNCH_COUNT[0] = 0
             KN.CONV_CENSUS = {} if want_census else None
             gdist.CALLS[0] = 0
+            gpeer.CALLS[0] = 0
             nw = max(warmup, 2)
             S = GraphedStep(T, B, warmup=nw, images=dev_images, poll_every=0)
             out["launches_per_step"] = KN.LAUNCH_COUNT[0] // (nw + 1)
             out["nccl_calls_per_step"] = gdist.CALLS[0] // (nw + 1)
+            out["peer_calls_per_step"] = gpeer.CALLS[0] // (nw + 1)
             if want_census:
                 out["census"] = {k_: v // (nw + 1) for k_, v in KN.CONV_CENSUS.items()}
             KN.CONV_CENSUS = None
@@ -407,6 +410,7 @@ def run_native(args):
         out["losses"] = last.get("losses")
         out["bce_in_range"] = bool(in_range[0])
         out.setdefault("nccl_calls_per_step", 0)
+        out.setdefault("peer_calls_per_step", 0)
         out["mem_gb"] = torch.cuda.max_memory_allocated(device) / 2**30
         out["adam"] = adam_roofline(T, device)
         dp.remove()
@@ -474,7 +478,8 @@ def run_native(args):
                        else "skipped: unread by the reference (SURVEY B9); parameters and losses identical"},
             "model_tflops": FLOPS_PER_IMAGE[args.loop] * B * world / (ms * 1e-3) / 1e12 / world,
             "clocks": main_run["clocks"], "gpu_launches": main_run["launches_per_step"],
-            "nccl_calls_per_step": main_run["nccl_calls_per_step"], "peak_mem_gib": main_run["mem_gb"],
+            "nccl_calls_per_step": main_run["nccl_calls_per_step"],
+            "peer_calls_per_step": main_run["peer_calls_per_step"], "peak_mem_gib": main_run["mem_gb"],
             "bce_in_range": main_run["bce_in_range"], "losses": main_run["losses"],
             "e2e": {"value": B * world / (ms_e2e * 1e-3), "unit": "images/s",
                     "h2d_bytes_per_step": main_run["h2d"], "d2h_bytes_per_step": main_run["d2h"]},

@@ -102,6 +102,14 @@ SIGNATURES = {
                                                  c_int, c_int64, P, c_float, P]),
     "ganb200_multi_tensor_copy": (c_int, [P, P, c_int, c_int64, P]),
     "ganb200_counter_add": (c_int, [P, c_int64, P]),
+    "ganb200_peer_bytes": (c_int64, [c_int64]),
+    "ganb200_peer_alloc": (c_int, [c_int64, P]),
+    "ganb200_peer_free": (c_int, [P]),
+    "ganb200_peer_export": (c_int, [P, P]),
+    "ganb200_peer_open": (c_int, [P, P]),
+    "ganb200_peer_close": (c_int, [P]),
+    "ganb200_peer_allreduce": (c_int, [P, c_int, c_int, c_int64, P, P, P, P, c_int64, c_int, P]),
+    "ganb200_peer_error": (c_int, [P, P]),
     "ganb200_chan_copy": (c_int, [P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, P]),
     "ganb200_mixup": (c_int, [P, P, c_float, P, c_int64, P]),
     "ganb200_mixup_wgan_f64": (c_int, [P, P, P, P, c_int, c_int, c_int, c_int, P]),

@@ -4,6 +4,7 @@
 // (no im2col buffer, replicate padding folded into the index clamp).
 #include "common.cuh"
 #include "conv_common.cuh"
+#include "det_reduce.cuh"
 
 namespace ganb200 {
 
@@ -206,9 +207,26 @@ struct DgradP : ConvGeom {
   }
 };
 
-// ------------------------------------------------------------------ wgrad: M = K, Ncols = C*R*S, Kdim = N*P*Q (split-K, atomics)
+// ------------------------------------------------------------------ wgrad: M = K, Ncols = C*R*S, Kdim = N*P*Q (split-K)
+// Split-K partials go to slice blockIdx.z of a scratch array and simt_splitk_sum_kernel adds the slices in order
+// (`slice` = K*CRS).  slice == 0: no scratch for this launch (see simt_wgrad) — atomics into a zeroed dw.
+constexpr int kWgradRegions = 4;
+constexpr size_t kWgradScratch = (size_t)1 << 22;   // floats per region (16 MB)
+static __device__ __align__(16) float g_wgrad_part[kWgradRegions * kWgradScratch];
+
+__global__ void __launch_bounds__(256) simt_splitk_sum_kernel(float* __restrict__ dw, int region, int64_t slice,
+                                                              int splits) {
+  const float* part = g_wgrad_part + (size_t)region * kWgradScratch;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < slice; i += (int64_t)gridDim.x * blockDim.x) {
+    float acc = 0.f;
+    for (int z = 0; z < splits; ++z) acc += __ldcg(part + z * slice + i);
+    dw[i] = acc;
+  }
+}
+
 struct WgradP : ConvGeom {
   const float* x; const float* dy; const float* iscale; const float* oscale; float* dw;
+  int64_t slice; int region;
   static constexpr bool A_KFAST = true;
   struct ACtx { int dummy; };
   struct BCtx { int ci[4], r_[4], s_[4]; bool ok[4]; };
@@ -266,7 +284,9 @@ struct WgradP : ConvGeom {
   }
   __device__ void store(int ko, int col, float v) const {
     if (ko >= K || col >= CRS) return;
-    atomicAdd(dw + (int64_t)ko * CRS + col, v * alpha);
+    if (gridDim.z == 1) dw[(int64_t)ko * CRS + col] = v * alpha;
+    else if (slice) g_wgrad_part[(size_t)region * kWgradScratch + blockIdx.z * slice + (int64_t)ko * CRS + col] = v * alpha;
+    else atomicAdd(dw + (int64_t)ko * CRS + col, v * alpha);
   }
 };
 
@@ -369,9 +389,20 @@ int ganb200::simt_wgrad(const ganb200_conv_desc* d, const float* x, const float*
   if (splits > max_splits) splits = max_splits;
   if (splits < 1) splits = 1;
   if (splits > 65535) splits = 65535;
-  GB_CHECK_CUDA(cudaMemsetAsync(dw, 0, sizeof(float) * (size_t)p.K * p.CRS, s));
+  const int64_t slice = (int64_t)p.K * p.CRS;
+  const int region = det_region(s);
+  const bool det = region >= 0 && region < kWgradRegions;
+  if (det && splits > 1 && (size_t)slice * splits > kWgradScratch)   // fewer, longer splits rather than atomics
+    splits = (int)std::max<int64_t>(1, (int64_t)(kWgradScratch / (size_t)slice));
+  p.slice = det && splits > 1 ? slice : 0;
+  p.region = det ? region : 0;
+  if (splits > 1 && !p.slice) GB_CHECK_CUDA(cudaMemsetAsync(dw, 0, sizeof(float) * (size_t)slice, s));
   dim3 grid(ceil_div(p.K, BM), ceil_div(p.CRS, BN), splits);
   simt_gemm_kernel<WgradP><<<grid, 256, 0, s>>>(p);
   GB_CHECK_LAUNCH();
+  if (p.slice) {
+    simt_splitk_sum_kernel<<<ew_grid(slice, 256, 1), 256, 0, s>>>(dw, region, slice, splits);
+    GB_CHECK_LAUNCH();
+  }
   return 0;
 }

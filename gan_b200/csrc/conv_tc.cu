@@ -1167,14 +1167,15 @@ int tc_dgrad(const ganb200_conv_desc* d, const float* dy, const float* w, const 
   return dgrad_run(d, dy, w, iscale, oscale, dx, align_ws(ws), s, true, nullptr, dyp, wp);
 }
 
-// 1 (default): dgrad of replicate-padded convolutions scatters straight into the unpadded plane from the MMA epilogue
-// (epi_fold32); 0: round-1 path — padded fp32 domain in the workspace + a fold pass.  GANB200_DGRAD_SCATTER=0 or
-// ganb200_conv_scatter_mode(0).
+// 0 (default): dgrad of replicate-padded convolutions writes the padded fp32 domain to the workspace and a fold pass adds
+// the border back — every sum in a fixed order.  1: scatter straight into the unpadded plane from the MMA epilogue
+// (epi_fold32; no intermediate, ~0.2 % of the step at batch 256) — the border pixels then take red.global.add from
+// several CTAs, so their low bits depend on the schedule.  GANB200_DGRAD_SCATTER=1 or ganb200_conv_scatter_mode(1).
 static int g_scatter_mode = -1;
 static int scatter_mode() {
   if (g_scatter_mode < 0) {
     const char* e = getenv("GANB200_DGRAD_SCATTER");
-    g_scatter_mode = (e && e[0] == '0') ? 0 : 1;
+    g_scatter_mode = (e && e[0] == '1') ? 1 : 0;
   }
   return g_scatter_mode;
 }

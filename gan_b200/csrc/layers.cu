@@ -1,6 +1,7 @@
 // layers.cu — PReLU, BatchNorm, softmax-over-branches, MiniBatchStdDev, BCE, separable resampling.
 // All HBM-bound; see DESIGN.md for the per-kernel algorithmic bytes.
 #include "common.cuh"
+#include "det_reduce.cuh"
 #include <algorithm>
 
 namespace ganb200 {
@@ -56,7 +57,7 @@ __global__ void __launch_bounds__(256) prelu_kernel(const float* __restrict__ g,
 template <int MODE>
 __global__ void __launch_bounds__(256) prelu_reduce_kernel(const float* __restrict__ u, const float* __restrict__ v,
                                                            const float* __restrict__ x, float* __restrict__ out,
-                                                           int N, int C, int HW, int a_n) {
+                                                           int N, int C, int HW, int a_n, int region) {
   float acc = 0.f;
   int split = blockIdx.y, nsplit = gridDim.y;
   if (a_n == 1) {
@@ -89,7 +90,8 @@ __global__ void __launch_bounds__(256) prelu_reduce_kernel(const float* __restri
     }
   }
   float t = block_sum<256>(acc);
-  if (threadIdx.x == 0) atomicAdd(out + (a_n == 1 ? 0 : blockIdx.x), t);
+  const int g = a_n == 1 ? 0 : (int)blockIdx.x;
+  det_group_store<256, 1>(region, g, split, nsplit, 1.f, t, out + g);
 }
 
 // Fused PReLU backward: gx = gy * (x > 0 ? 1 : a) and ga[c] += sum gy * min(x, 0) in ONE pass over (gy, x)
@@ -98,12 +100,17 @@ __global__ void __launch_bounds__(256) prelu_reduce_kernel(const float* __restri
 template <bool ROWS>
 __global__ void __launch_bounds__(256) prelu_bwd_fused_kernel(const float* __restrict__ gy, const float* __restrict__ x,
                                                               const float* __restrict__ a, float* __restrict__ gx,
-                                                              float* __restrict__ ga, int N, int C, int HW, int a_n) {
+                                                              float* __restrict__ ga, int N, int C, int HW, int a_n,
+                                                              int region) {
   if (ROWS) {
     const int lane = threadIdx.x & 31;
     const int64_t rows = (int64_t)N * C;
     const int hw4 = HW >> 2;
-    float keep = 0.f;  // a_n == 1: one atomic per warp at the end
+    // rows_fit: every (n, c) row sum goes to g_det_part[row]; the last CTA then adds them per channel in n order
+    const bool rows_fit = region >= 0;
+    float* part = g_det_part + (size_t)(rows_fit ? region : 0) * kDetPartials;
+    unsigned int* count = g_det_count + (rows_fit ? region : 0) * kDetGroups;
+    float keep = 0.f;  // !rows_fit && a_n == 1: one atomic per warp at the end
     for (int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); row < rows; row += (int64_t)gridDim.x * 8) {
       const int c = a_n == 1 ? 0 : (int)(row % C);
       const float slope = __ldg(a + c);
@@ -120,14 +127,43 @@ __global__ void __launch_bounds__(256) prelu_bwd_fused_kernel(const float* __res
         acc += (v.x > 0.f ? 0.f : g.x * v.x) + (v.y > 0.f ? 0.f : g.y * v.y) + (v.z > 0.f ? 0.f : g.z * v.z) +
                (v.w > 0.f ? 0.f : g.w * v.w);
       }
-      if (a_n == 1) {
+      if (rows_fit) {
+        acc = warp_sum(acc);
+        if (lane == 0) part[row] = acc;
+      } else if (a_n == 1) {
         keep += acc;
       } else {
         acc = warp_sum(acc);
         if (lane == 0) atomicAdd(ga + c, acc);
       }
     }
-    if (a_n == 1) {
+    if (rows_fit) {
+      __shared__ bool last;
+      __threadfence();
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        last = atomicAdd(count, 1u) == gridDim.x - 1;
+        if (last) *count = 0u;
+      }
+      __syncthreads();
+      if (last) {
+        __threadfence();
+        if (a_n == 1) {
+          float acc = 0.f;
+          for (int64_t r = threadIdx.x; r < rows; r += 256) acc += __ldcg(part + r);
+          acc = block_sum<256>(acc);
+          if (threadIdx.x == 0) ga[0] = acc;
+        } else {
+          // one warp per channel: lanes over the samples, then the warp tree — a fixed order
+          for (int c = threadIdx.x >> 5; c < C; c += 8) {
+            float acc = 0.f;
+            for (int n = lane; n < N; n += 32) acc += __ldcg(part + (int64_t)n * C + c);
+            acc = warp_sum(acc);
+            if (lane == 0) ga[c] = acc;
+          }
+        }
+      }
+    } else if (a_n == 1) {
       keep = warp_sum(keep);
       if (lane == 0) atomicAdd(ga, keep);
     }
@@ -144,7 +180,7 @@ __global__ void __launch_bounds__(256) prelu_bwd_fused_kernel(const float* __res
       if (!(v > 0.f)) acc += g * v;
     }
     float t = block_sum<256>(acc);
-    if (threadIdx.x == 0) atomicAdd(ga + c, t);
+    det_group_store<256, 1>(region, c, split, nsplit, 1.f, t, ga + c);
   }
 }
 
@@ -194,16 +230,18 @@ extern "C" int ganb200_prelu_bwd(const float* gy, const float* x, const float* a
   if (gx && ga) {
     const bool al = ((((uintptr_t)gy) | ((uintptr_t)x) | ((uintptr_t)gx)) & 15) == 0;
     if (HW >= 64 && (HW & 3) == 0 && al) {
-      GB_CHECK_CUDA(cudaMemsetAsync(ga, 0, sizeof(float) * a_n, s));
+      const int region = rows <= kDetPartials ? det_region(s) : -1;   // per-row partials
+      if (region < 0) GB_CHECK_CUDA(cudaMemsetAsync(ga, 0, sizeof(float) * a_n, s));
       int grid = (int)std::min<int64_t>((rows + 7) / 8, (int64_t)kNumSMs * 16);
-      prelu_bwd_fused_kernel<true><<<grid, 256, 0, s>>>(gy, x, a, gx, ga, N, C, HW, a_n);
+      prelu_bwd_fused_kernel<true><<<grid, 256, 0, s>>>(gy, x, a, gx, ga, N, C, HW, a_n, region);
       GB_CHECK_LAUNCH();
       return 0;
     }
     if (HW < 64 && a_n == C && (int64_t)N * HW < (int64_t)1 << 30) {
-      GB_CHECK_CUDA(cudaMemsetAsync(ga, 0, sizeof(float) * a_n, s));
       int nsplit = std::max(1, std::min((kNumSMs * 4 + C - 1) / C, (N * HW + 255) / 256));
-      prelu_bwd_fused_kernel<false><<<dim3(C, nsplit), 256, 0, s>>>(gy, x, a, gx, ga, N, C, HW, a_n);
+      const int region = det_region_for(s, C, nsplit);
+      if (region < 0) GB_CHECK_CUDA(cudaMemsetAsync(ga, 0, sizeof(float) * a_n, s));
+      prelu_bwd_fused_kernel<false><<<dim3(C, nsplit), 256, 0, s>>>(gy, x, a, gx, ga, N, C, HW, a_n, region);
       GB_CHECK_LAUNCH();
       return 0;
     }
@@ -215,8 +253,9 @@ extern "C" int ganb200_prelu_bwd(const float* gy, const float* x, const float* a
   if (ga) {
     dim3 grid;
     prelu_reduce_dims(N, C, HW, a_n, &grid);
-    GB_CHECK_CUDA(cudaMemsetAsync(ga, 0, sizeof(float) * a_n, s));
-    prelu_reduce_kernel<0><<<grid, 256, 0, s>>>(gy, nullptr, x, ga, N, C, HW, a_n);
+    const int region = det_region_for(s, grid.x, grid.y);
+    if (region < 0) GB_CHECK_CUDA(cudaMemsetAsync(ga, 0, sizeof(float) * a_n, s));
+    prelu_reduce_kernel<0><<<grid, 256, 0, s>>>(gy, nullptr, x, ga, N, C, HW, a_n, region);
     GB_CHECK_LAUNCH();
   }
   return 0;
@@ -228,8 +267,9 @@ extern "C" int ganb200_masked_dot(const float* u, const float* v, const float* x
   cudaStream_t s = (cudaStream_t)stream;
   dim3 grid;
   prelu_reduce_dims(N, C, HW, a_n, &grid);
-  GB_CHECK_CUDA(cudaMemsetAsync(out, 0, sizeof(float) * a_n, s));
-  prelu_reduce_kernel<1><<<grid, 256, 0, s>>>(u, v, x, out, N, C, HW, a_n);
+  const int region = det_region_for(s, grid.x, grid.y);
+  if (region < 0) GB_CHECK_CUDA(cudaMemsetAsync(out, 0, sizeof(float) * a_n, s));
+  prelu_reduce_kernel<1><<<grid, 256, 0, s>>>(u, v, x, out, N, C, HW, a_n, region);
   GB_CHECK_LAUNCH();
   return 0;
 }
@@ -244,7 +284,7 @@ template <int PASS>
 __global__ void __launch_bounds__(256) bn_reduce_kernel(const float* __restrict__ x, const float* __restrict__ gy,
                                                         const float* __restrict__ mean, const float* __restrict__ invstd,
                                                         float* __restrict__ out_a, float* __restrict__ out_b,
-                                                        int N, int C, int HW, float inv_count) {
+                                                        int N, int C, int HW, float inv_count, int region) {
   int c = blockIdx.x, split = blockIdx.y, nsplit = gridDim.y;
   float m = PASS >= 1 ? mean[c] : 0.f;
   float is = PASS == 2 ? invstd[c] : 0.f;
@@ -274,9 +314,9 @@ __global__ void __launch_bounds__(256) bn_reduce_kernel(const float* __restrict_
   float ta = block_sum<256>(a);
   if (PASS == 2) {
     float tb = block_sum<256>(b);
-    if (threadIdx.x == 0) { atomicAdd(out_a + c, ta); atomicAdd(out_b + c, tb); }
+    det_group_store<256, 2>(region, c, split, nsplit, 1.f, ta, out_a + c, tb, out_b + c);
   } else {
-    if (threadIdx.x == 0) atomicAdd(out_a + c, ta * inv_count);
+    det_group_store<256, 1>(region, c, split, nsplit, inv_count, ta, out_a + c);
   }
 }
 
@@ -466,10 +506,13 @@ extern "C" int ganb200_bn_stats(const float* x, float* mean, float* var_biased, 
   GB_REQUIRE(N > 0 && C > 0 && HW > 0, GANB200_BAD_SHAPE, "bn_stats: empty");
   float inv = 1.f / ((float)N * (float)HW);
   dim3 grid = bn_reduce_grid(N, C, HW);
-  GB_CHECK_CUDA(cudaMemsetAsync(mean, 0, sizeof(float) * C, s));
-  GB_CHECK_CUDA(cudaMemsetAsync(var_biased, 0, sizeof(float) * C, s));
-  bn_reduce_kernel<0><<<grid, 256, 0, s>>>(x, nullptr, nullptr, nullptr, mean, nullptr, N, C, HW, inv);
-  bn_reduce_kernel<1><<<grid, 256, 0, s>>>(x, nullptr, mean, nullptr, var_biased, nullptr, N, C, HW, inv);
+  const int region = det_region_for(s, grid.x, grid.y);
+  if (region < 0) {
+    GB_CHECK_CUDA(cudaMemsetAsync(mean, 0, sizeof(float) * C, s));
+    GB_CHECK_CUDA(cudaMemsetAsync(var_biased, 0, sizeof(float) * C, s));
+  }
+  bn_reduce_kernel<0><<<grid, 256, 0, s>>>(x, nullptr, nullptr, nullptr, mean, nullptr, N, C, HW, inv, region);
+  bn_reduce_kernel<1><<<grid, 256, 0, s>>>(x, nullptr, mean, nullptr, var_biased, nullptr, N, C, HW, inv, region);
   GB_CHECK_LAUNCH();
   return 0;
 }
@@ -490,9 +533,13 @@ extern "C" int ganb200_bn_apply(const float* x, const float* mean, const float* 
 extern "C" int ganb200_bn_bwd_reduce(const float* gy, const float* x, const float* mean, const float* invstd,
                                      float* sum_gy, float* sum_gy_xhat, int N, int C, int HW, void* stream) {
   cudaStream_t s = (cudaStream_t)stream;
-  GB_CHECK_CUDA(cudaMemsetAsync(sum_gy, 0, sizeof(float) * C, s));
-  GB_CHECK_CUDA(cudaMemsetAsync(sum_gy_xhat, 0, sizeof(float) * C, s));
-  bn_reduce_kernel<2><<<bn_reduce_grid(N, C, HW), 256, 0, s>>>(x, gy, mean, invstd, sum_gy, sum_gy_xhat, N, C, HW, 1.f);
+  const dim3 grid = bn_reduce_grid(N, C, HW);
+  const int region = det_region_for(s, grid.x, grid.y, 2);
+  if (region < 0) {
+    GB_CHECK_CUDA(cudaMemsetAsync(sum_gy, 0, sizeof(float) * C, s));
+    GB_CHECK_CUDA(cudaMemsetAsync(sum_gy_xhat, 0, sizeof(float) * C, s));
+  }
+  bn_reduce_kernel<2><<<grid, 256, 0, s>>>(x, gy, mean, invstd, sum_gy, sum_gy_xhat, N, C, HW, 1.f, region);
   GB_CHECK_LAUNCH();
   return 0;
 }
@@ -554,7 +601,7 @@ __global__ void __launch_bounds__(256) softmax_m_bwd_kernel(const float* __restr
 template <int MODE, bool REG>
 __global__ void __launch_bounds__(256) mbstd_kernel(const float* __restrict__ g, const float* __restrict__ x,
                                                     const float* __restrict__ ggx, float* __restrict__ out,
-                                                    float* __restrict__ gx, int G, int64_t L, float eps) {
+                                                    float* __restrict__ gx, int G, int64_t L, float eps, int region) {
   float acc = 0.f;
   float gv = MODE >= 1 ? g[0] : 0.f;
   float invL = 1.f / (float)L, invG1 = 1.f / (float)(G - 1);
@@ -601,13 +648,14 @@ __global__ void __launch_bounds__(256) mbstd_kernel(const float* __restrict__ g,
   }
   if (MODE != 1) {
     float t = block_sum<256>(acc);
-    if (threadIdx.x == 0) atomicAdd(out, t);
+    det_group_store<256, 1>(region, 0, (int)blockIdx.x, (int)gridDim.x, 1.f, t, out);
   }
 }
 
 // ------------------------------------------------------------------ BCE (mean), torch semantics
 __global__ void __launch_bounds__(256) bce_fwd_kernel(const float* __restrict__ p, const float* __restrict__ t,
-                                                      float* __restrict__ out, int* __restrict__ flag, int64_t n) {
+                                                      float* __restrict__ out, int* __restrict__ flag, int64_t n,
+                                                      int region) {
   float acc = 0.f;
   bool bad = false;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
@@ -618,7 +666,7 @@ __global__ void __launch_bounds__(256) bce_fwd_kernel(const float* __restrict__ 
   }
   if (bad && flag) atomicExch(flag, 1);
   float s = block_sum<256>(acc);
-  if (threadIdx.x == 0) atomicAdd(out, s / (float)n);
+  det_group_store<256, 1>(region, 0, (int)blockIdx.x, (int)gridDim.x, 1.f / (float)n, s, out);
 }
 
 __global__ void __launch_bounds__(256) bce_bwd_kernel(const float* __restrict__ g, const float* __restrict__ p,
@@ -838,16 +886,17 @@ extern "C" int ganb200_softmax_m_bwd(const float* gy, const float* y, float* gx,
 extern "C" int ganb200_mbstd_fwd(const float* x, float* out, int G, int64_t L, float eps, void* stream) {
   GB_REQUIRE(G >= 2 && L > 0, GANB200_BAD_SHAPE, "mbstd: need G>=2");
   cudaStream_t s = (cudaStream_t)stream;
-  GB_CHECK_CUDA(cudaMemsetAsync(out, 0, sizeof(float), s));
-  if (G <= 16) mbstd_kernel<0, true><<<ew_grid(L, 256, 1), 256, 0, s>>>(nullptr, x, nullptr, out, nullptr, G, L, eps);
-  else mbstd_kernel<0, false><<<ew_grid(L, 256, 1), 256, 0, s>>>(nullptr, x, nullptr, out, nullptr, G, L, eps);
+  const int grid = ew_grid(L, 256, 1), region = det_region_for(s, 1, grid);
+  if (region < 0) GB_CHECK_CUDA(cudaMemsetAsync(out, 0, sizeof(float), s));
+  if (G <= 16) mbstd_kernel<0, true><<<grid, 256, 0, s>>>(nullptr, x, nullptr, out, nullptr, G, L, eps, region);
+  else mbstd_kernel<0, false><<<grid, 256, 0, s>>>(nullptr, x, nullptr, out, nullptr, G, L, eps, region);
   GB_CHECK_LAUNCH();
   return 0;
 }
 extern "C" int ganb200_mbstd_bwd(const float* g, const float* x, float* gx, int G, int64_t L, float eps, void* stream) {
   GB_REQUIRE(G >= 2 && L > 0, GANB200_BAD_SHAPE, "mbstd: need G>=2");
-  if (G <= 16) mbstd_kernel<1, true><<<ew_grid(L, 256, 1), 256, 0, (cudaStream_t)stream>>>(g, x, nullptr, nullptr, gx, G, L, eps);
-  else mbstd_kernel<1, false><<<ew_grid(L, 256, 1), 256, 0, (cudaStream_t)stream>>>(g, x, nullptr, nullptr, gx, G, L, eps);
+  if (G <= 16) mbstd_kernel<1, true><<<ew_grid(L, 256, 1), 256, 0, (cudaStream_t)stream>>>(g, x, nullptr, nullptr, gx, G, L, eps, 0);
+  else mbstd_kernel<1, false><<<ew_grid(L, 256, 1), 256, 0, (cudaStream_t)stream>>>(g, x, nullptr, nullptr, gx, G, L, eps, 0);
   GB_CHECK_LAUNCH();
   return 0;
 }
@@ -855,9 +904,10 @@ extern "C" int ganb200_mbstd_bwd_bwd(const float* g, const float* x, const float
                                      int G, int64_t L, float eps, void* stream) {
   GB_REQUIRE(G >= 2 && L > 0, GANB200_BAD_SHAPE, "mbstd: need G>=2");
   cudaStream_t s = (cudaStream_t)stream;
-  GB_CHECK_CUDA(cudaMemsetAsync(out_gg, 0, sizeof(float), s));
-  if (G <= 16) mbstd_kernel<2, true><<<ew_grid(L, 256, 1), 256, 0, s>>>(g, x, ggx, out_gg, out_gx, G, L, eps);
-  else mbstd_kernel<2, false><<<ew_grid(L, 256, 1), 256, 0, s>>>(g, x, ggx, out_gg, out_gx, G, L, eps);
+  const int grid = ew_grid(L, 256, 1), region = det_region_for(s, 1, grid);
+  if (region < 0) GB_CHECK_CUDA(cudaMemsetAsync(out_gg, 0, sizeof(float), s));
+  if (G <= 16) mbstd_kernel<2, true><<<grid, 256, 0, s>>>(g, x, ggx, out_gg, out_gx, G, L, eps, region);
+  else mbstd_kernel<2, false><<<grid, 256, 0, s>>>(g, x, ggx, out_gg, out_gx, G, L, eps, region);
   GB_CHECK_LAUNCH();
   return 0;
 }
@@ -865,9 +915,10 @@ extern "C" int ganb200_mbstd_bwd_bwd(const float* g, const float* x, const float
 extern "C" int ganb200_bce_fwd(const float* p, const float* t, float* out, int* range_flag, int64_t n, void* stream) {
   cudaStream_t s = (cudaStream_t)stream;
   GB_REQUIRE(n > 0, GANB200_BAD_SHAPE, "bce: empty");
-  GB_CHECK_CUDA(cudaMemsetAsync(out, 0, sizeof(float), s));
+  const int grid = ew_grid(n, 256, 4), region = det_region_for(s, 1, grid);
+  if (region < 0) GB_CHECK_CUDA(cudaMemsetAsync(out, 0, sizeof(float), s));
   if (range_flag) GB_CHECK_CUDA(cudaMemsetAsync(range_flag, 0, sizeof(int), s));
-  bce_fwd_kernel<<<ew_grid(n, 256, 4), 256, 0, s>>>(p, t, out, range_flag, n);
+  bce_fwd_kernel<<<grid, 256, 0, s>>>(p, t, out, range_flag, n, region);
   GB_CHECK_LAUNCH();
   return 0;
 }
@@ -878,8 +929,9 @@ extern "C" int ganb200_bce_fwd_sticky(const float* p, const float* t, float* out
   cudaStream_t s = (cudaStream_t)stream;
   GB_REQUIRE(n > 0, GANB200_BAD_SHAPE, "bce: empty");
   GB_REQUIRE(sticky_flag != nullptr, GANB200_BAD_ARG, "bce_fwd_sticky: null flag");
-  GB_CHECK_CUDA(cudaMemsetAsync(out, 0, sizeof(float), s));
-  bce_fwd_kernel<<<ew_grid(n, 256, 4), 256, 0, s>>>(p, t, out, sticky_flag, n);
+  const int grid = ew_grid(n, 256, 4), region = det_region_for(s, 1, grid);
+  if (region < 0) GB_CHECK_CUDA(cudaMemsetAsync(out, 0, sizeof(float), s));
+  bce_fwd_kernel<<<grid, 256, 0, s>>>(p, t, out, sticky_flag, n, region);
   GB_CHECK_LAUNCH();
   return 0;
 }

@@ -1,6 +1,7 @@
 // misc.cu — channel-slice copies (cat / slice / zero-pad along C without ATen), device counters, and the
 // spectral-norm power iteration.  All HBM-bound; algorithmic bytes = 4 B read + 4 B written per element.
 #include "common.cuh"
+#include "det_reduce.cuh"
 
 namespace ganb200 {
 
@@ -121,14 +122,14 @@ __global__ void __launch_bounds__(256) spectral_scale_kernel(const float* __rest
     out[i] = W[i] * inv;
 }
 
-// dot[0] = <G, W>   (zeroed by the caller)
+// dot[0] = <G, W>   (det_reduce.cuh: ordered sum of the CTA partials)
 __global__ void __launch_bounds__(256) spectral_dot_kernel(const float* __restrict__ G, const float* __restrict__ W,
-                                                           float* __restrict__ dot, int64_t n) {
+                                                           float* __restrict__ dot, int64_t n, int region) {
   float acc = 0.f;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
     acc = fmaf(G[i], W[i], acc);
   float t = block_sum<256>(acc);
-  if (threadIdx.x == 0) atomicAdd(dot, t);
+  det_group_store<256, 1>(region, 0, (int)blockIdx.x, (int)gridDim.x, 1.f, t, dot);
 }
 
 // gW[r,c] = G[r,c]/sigma - dot/sigma^2 * u[r] v[c]     (backward of W/sigma with sigma = u^T W v, u and v constants)
@@ -335,8 +336,9 @@ extern "C" int ganb200_spectral_scale_bwd(const float* G, const float* W, const 
   int64_t n = (int64_t)rows * cols;
   if (n <= 0) return 0;
   cudaStream_t s = (cudaStream_t)stream;
-  GB_CHECK_CUDA(cudaMemsetAsync(dot_scratch, 0, sizeof(float), s));
-  spectral_dot_kernel<<<ew_grid(n, 256, 4), 256, 0, s>>>(G, W, dot_scratch, n);
+  const int grid = ew_grid(n, 256, 4), region = det_region_for(s, 1, grid);
+  if (region < 0) GB_CHECK_CUDA(cudaMemsetAsync(dot_scratch, 0, sizeof(float), s));
+  spectral_dot_kernel<<<grid, 256, 0, s>>>(G, W, dot_scratch, n, region);
   spectral_scale_bwd_kernel<<<ew_grid(n, 256, 4), 256, 0, s>>>(G, u, v, sigma, dot_scratch, gW, rows, cols);
   GB_CHECK_LAUNCH();
   return 0;

@@ -1,6 +1,7 @@
 // pointwise.cu — HBM-bound elementwise / broadcast / reduction kernels (fp32, 128-bit accesses when aligned).
 // Roofline: HBM.  Algorithmic bytes = 4 B per element read + 4 B per element written, each tensor once.
 #include "common.cuh"
+#include "det_reduce.cuh"
 
 namespace ganb200 {
 
@@ -166,11 +167,11 @@ __global__ void __launch_bounds__(256) reduce_rows_kernel(const float* __restric
   }
 }
 
-// rmode 1 ([C] over n,hw) / rmode 2 ([N] over c,hw) / rmode 3 (all): grid (groups, splits); atomics into zeroed out.
+// rmode 1 ([C] over n,hw) / rmode 2 ([N] over c,hw) / rmode 3 (all): grid (groups, splits); det_reduce.cuh sums the splits in order.
 // element (g, j): rmode1: g=c, j over (n,hw): idx = (n*C + c)*HW + hw ;  rmode2: g=n, contiguous C*HW ; rmode3: g=0 all.
 __global__ void __launch_bounds__(256) reduce_groups_kernel(const float* __restrict__ x, const float* __restrict__ y,
                                                             float* __restrict__ out, int N, int C, int HW, int rmode,
-                                                            float scale) {
+                                                            float scale, int region) {
   int g = blockIdx.x;
   int split = blockIdx.y, nsplit = gridDim.y;
   float acc = 0.f;
@@ -200,7 +201,7 @@ __global__ void __launch_bounds__(256) reduce_groups_kernel(const float* __restr
     for (int64_t i = lo + threadIdx.x; i < hi; i += blockDim.x) acc += yr ? xr[i] * yr[i] : xr[i];
   }
   float t = block_sum<256>(acc);
-  if (threadIdx.x == 0) atomicAdd(out + g, t * scale);
+  det_group_store<256, 1>(region, g, split, nsplit, scale, t, out + g);
 }
 
 }  // namespace ganb200
@@ -296,8 +297,9 @@ extern "C" int ganb200_reduce(const float* x, const float* y, float* out, int N,
     int want = (kNumSMs * 4 + groups - 1) / groups;
     int nsplit = want < max_split ? want : max_split;
     if (nsplit < 1) nsplit = 1;
-    GB_CHECK_CUDA(cudaMemsetAsync(out, 0, sizeof(float) * groups, s));
-    reduce_groups_kernel<<<dim3(groups, nsplit), 256, 0, s>>>(x, y, out, N, C, HW, rmode, scale);
+    const int region = det_region_for(s, groups, nsplit);
+    if (region < 0) GB_CHECK_CUDA(cudaMemsetAsync(out, 0, sizeof(float) * groups, s));
+    reduce_groups_kernel<<<dim3(groups, nsplit), 256, 0, s>>>(x, y, out, N, C, HW, rmode, scale, region);
   } else {
     return fail(GANB200_BAD_ARG, "reduce: bad rmode%s %lld", "", rmode);
   }

@@ -7,6 +7,8 @@ B/N images each compute the step the reference computes on B images (SURVEY §8(
     kernel's grad_scale (`GradSync`, installed as the optimiser's pre-step hook);
   * BatchNorm batch statistics in G (`sync-BN`): per-channel (mean, biased var) forward and (sum dy, sum dy*xhat)
     backward are combined across ranks (hooks in gan_b200.ops);
+    — each of these small exchanges is ONE launch over NVLink peer memory (gan_b200/peer.py, csrc/peer.cu: stage,
+    signal, wait, add in rank order, epilogue); vectors that do not fit its slot go through ncclAllReduce;
   * MiniBatchStdDev's scalar in D: the rank-local mean of sqrt(var) is averaged across ranks, and so is its
     adjoint (twice differentiable: the R1/R2/GP double backward passes through it).  Rank r must hold, for each
     quarter q of the global batch, the r-th slice of that quarter (`shard_quarter_major`) so that the local
@@ -22,6 +24,7 @@ from torch.autograd import Function
 
 from . import ops
 
+PEER = [None]             # gan_b200.peer.PeerExchange of the installed DataParallelStep (small exchanges over NVLink)
 BUCKET_BYTES = 256 << 20  # NVSwitch: size buckets for launch latency / overlap, not for link count
 CALLS = [0]               # collective calls issued by this process (bench.py: nccl_calls_per_step)
 
@@ -48,6 +51,9 @@ class AllReduceMeanFn(Function):
     @staticmethod
     def forward(ctx, x, group):
         ctx.group = group
+        px = PEER[0]
+        if px is not None and x.is_cuda and x.dtype == torch.float32 and px.fits(x.numel()):
+            return px.mean(x)          # one launch: stage, signal, wait, add in rank order, scale (csrc/peer.cu)
         y = x.detach().clone()
         CALLS[0] += 1
         dist.all_reduce(y, op=dist.ReduceOp.SUM, group=group)
@@ -216,16 +222,23 @@ class _null:
 class DataParallelStep:
     """Installs the three exchanges on a Train object (train/*.py) and removes them again."""
 
-    def __init__(self, trainer, group=None, sync_bn=True):
+    def __init__(self, trainer, group=None, sync_bn=True, peer=None):
         self.T = trainer
         self.group = group
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.sync_bn = sync_bn
+        # small exchanges over NVLink peer memory (gan_b200.peer) instead of NCCL: default on CUDA, GANB200_PEER=0 = off
+        self.use_peer = (os.environ.get("GANB200_PEER", "1") != "0") if peer is None else bool(peer)
+        self.peer = None
 
     def install(self):
         if self.world == 1:
             return self
         T, world, group = self.T, self.world, self.group
+        if self.use_peer and torch.device(T.device).type == "cuda":
+            from .peer import PeerExchange
+            self.peer = PEER[0] = PeerExchange.connect(group, T.device)
+        px = self.peer
         for opt, net in ((T.optimizer_G, T.generator), (T.optimizer_D, T.discriminator)):
             opt.grad_scale = 1.0 / world
             opt.pre_step = GradSync(net.parameters(), group, opt=opt, overlap=self.T.recipe.lazy == 1)
@@ -233,6 +246,9 @@ class DataParallelStep:
         if self.sync_bn:
             def stats(mean, var, count):
                 # combine (mean, biased var) of equal-sized shards: var_g = E[var] + E[mean^2] - E[mean]^2
+                if px is not None and mean.is_cuda and mean.dtype == torch.float32 and px.fits(mean.numel(), 2):
+                    m, v = px.stats(mean, var)
+                    return m, v, count * world
                 pack = torch.stack([mean, var + mean * mean])
                 CALLS[0] += 1
                 dist.all_reduce(pack, op=dist.ReduceOp.SUM, group=group)
@@ -241,6 +257,8 @@ class DataParallelStep:
                 return m, (pack[1] - m * m).contiguous(), count * world
 
             def grads(s1, s2):
+                if px is not None and s1.is_cuda and s1.dtype == torch.float32 and px.fits(s1.numel(), 2):
+                    return px.grads(s1, s2)
                 pack = torch.stack([s1, s2])
                 CALLS[0] += 1
                 dist.all_reduce(pack, op=dist.ReduceOp.SUM, group=group)
@@ -250,6 +268,10 @@ class DataParallelStep:
         return self
 
     def remove(self):
+        if self.peer is not None:
+            self.peer.check()
+            self.peer.close()
+            self.peer = PEER[0] = None
         ops._mbstd_reduce[0] = None
         ops._sync_bn_hooks["stats"] = ops._sync_bn_hooks["grads"] = None
         for opt in (self.T.optimizer_G, self.T.optimizer_D):

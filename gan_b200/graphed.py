@@ -78,6 +78,18 @@ class StateSnapshot:
                 v[1:].zero_()               # noise counter created after the snapshot: back to forward 0
 
 
+_WARMUP_STREAMS = {}
+
+
+def _warmup_stream(dev):
+    """One warm-up stream per device for every GraphedStep of the process (csrc/det_reduce.cuh hands each stream that
+    launches a split reduction its own scratch region, and there are 16)."""
+    key = torch.device(dev).index or 0
+    if key not in _WARMUP_STREAMS:
+        _WARMUP_STREAMS[key] = torch.cuda.Stream(device=dev)
+    return _WARMUP_STREAMS[key]
+
+
 class GraphedStep:
     def __init__(self, trainer, batch, warmup=3, images=None, poll_every=16):
         T = self.T = trainer
@@ -102,7 +114,7 @@ class GraphedStep:
         self.snapshot = StateSnapshot(T)
         for opt in (T.optimizer_G, T.optimizer_D):
             opt.capturable = True
-        side = torch.cuda.Stream(device=dev)
+        side = _warmup_stream(dev)
         side.wait_stream(torch.cuda.current_stream(dev))
         with torch.cuda.stream(side):
             for _ in range(max(warmup, 1)):

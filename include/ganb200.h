@@ -80,12 +80,12 @@ int ganb200_conv2d_route(const ganb200_conv_desc* d, int op);
  * (identical operands and accumulation order per output element).  Returns the previous mode; any other value
  * only queries.  Process-wide; also GANB200_CONV_HALO=0 in the environment. */
 int ganb200_conv_halo_mode(int mode);
-/* tcgen05 engine, dgrad of replicate-padded convolutions (and the fused modulated-conv backward): 1 (default) the MMA
- * epilogue scatters each padded-domain value straight into the clamped pixel of the unpadded plane (plain stores inside,
- * red.global.add on the border ring, which the host zeroes first) and, for the modulated convolution, also forms the style
- * gradient sum_hw dxs * x; 0 = the round-1 path: padded fp32 domain in the workspace, then a fold (+ scale + reduce) pass.
- * Same sums in another order on the border pixels.  Returns the previous mode; any other value only queries.
- * Process-wide; also GANB200_DGRAD_SCATTER=0 in the environment. */
+/* tcgen05 engine, dgrad of replicate-padded convolutions: 0 (default) = padded fp32 domain in the workspace, then a fold
+ * pass — every sum in a fixed order, the result is reproducible bit for bit; 1 = the MMA epilogue scatters each
+ * padded-domain value straight into the clamped pixel of the unpadded plane (plain stores inside, red.global.add on the
+ * border ring, which the host zeroes first): no intermediate, but the border pixels' low bits depend on the schedule.
+ * Returns the previous mode; any other value only queries.  Process-wide; also GANB200_DGRAD_SCATTER=1 in the
+ * environment. */
 int ganb200_conv_scatter_mode(int mode);
 int ganb200_conv2d_fprop(const ganb200_conv_desc* d, const float* x, const float* w, const float* bias,
                          const float* iscale, const float* oscale, float* y,
@@ -311,6 +311,31 @@ int ganb200_multi_tensor_adam_blocks(const ganb200_adam_entry* tab, const int32_
 int ganb200_multi_tensor_copy(const ganb200_adam_entry* tab, const int32_t* block_tab, int n_blocks, int64_t chunk,
                               void* stream);
 int ganb200_counter_add(int64_t* counter, int64_t inc, void* stream);
+
+/* Small all-reduces of the data-parallel step over NVLink peer memory (csrc/peer.cu; no reference counterpart: the
+ * reference is single-device, main.py:23-25).  Every rank allocates one exchange buffer (ganb200_peer_alloc: cudaMalloc of
+ * ganb200_peer_bytes(cap_floats), zeroed), exports it (64-byte cudaIpc handle), opens the other ranks' handles, and keeps a
+ * DEVICE array of the `world` buffer addresses (its own at index `rank`).  ganb200_peer_allreduce is then one single-CTA
+ * launch: stage -> signal every rank -> wait for every rank -> add the staged vectors in rank order -> epilogue:
+ *   GANB200_PEER_SUM       out0 = sum_r in0, out1 = sum_r in1             (BatchNorm backward: sum dy, sum dy * xhat)
+ *   GANB200_PEER_MEAN      out0 = mean_r in0 (, out1 = mean_r in1)        (MiniBatchStdDev scalar and its adjoint)
+ *   GANB200_PEER_BN_STATS  in0 = local mean, in1 = local biased variance of equal shards ->
+ *                          out0 = global mean, out1 = global biased variance
+ * in1 / out1 may both be null (one vector).  n elements per vector, n * (1 or 2) <= cap_floats.  All ranks must issue the
+ * same calls in the same order; the call is stream-ordered and CUDA-graph capturable (the sequence number is on the
+ * device).  A wait longer than ~20 s sets the buffer's error word (ganb200_peer_error) instead of hanging. */
+#define GANB200_PEER_SUM 0
+#define GANB200_PEER_MEAN 1
+#define GANB200_PEER_BN_STATS 2
+int64_t ganb200_peer_bytes(int64_t cap_floats);
+int ganb200_peer_alloc(int64_t cap_floats, void** buf);
+int ganb200_peer_free(void* buf);
+int ganb200_peer_export(void* buf, unsigned char* handle64);
+int ganb200_peer_open(const unsigned char* handle64, void** buf);
+int ganb200_peer_close(void* buf);
+int ganb200_peer_allreduce(const void* bufs_dev, int rank, int world, int64_t cap_floats, const float* in0,
+                           const float* in1, float* out0, float* out1, int64_t n, int op, void* stream);
+int ganb200_peer_error(const void* buf, int* error);
 
 /* Channel-slice copy on [N,C,HW] tensors: dst[:, dst_c0:dst_c0+ncopy] (+)= src[:, src_c0:src_c0+ncopy].
  * Replaces torch.cat(dim=1) / channel slicing and their adjoints (generator_13_5.py:451-467,549-560,
