@@ -325,12 +325,13 @@ def run_native(args):
             KN.LAUNCH_COUNT[0] = 0
             KN.CONV_CENSUS = {} if want_census else None
             gdist.CALLS[0] = 0
-            gpeer.CALLS[0] = 0
+            gpeer.CALLS[0] = gpeer.FUSED[0] = 0
             nw = max(warmup, 2)
             S = GraphedStep(T, B, warmup=nw, images=dev_images, poll_every=0)
             out["launches_per_step"] = KN.LAUNCH_COUNT[0] // (nw + 1)
             out["nccl_calls_per_step"] = gdist.CALLS[0] // (nw + 1)
             out["peer_calls_per_step"] = gpeer.CALLS[0] // (nw + 1)
+            out["peer_fused_per_step"] = gpeer.FUSED[0] // (nw + 1)
             if want_census:
                 out["census"] = {k_: v // (nw + 1) for k_, v in KN.CONV_CENSUS.items()}
             KN.CONV_CENSUS = None
@@ -411,6 +412,7 @@ def run_native(args):
         out["bce_in_range"] = bool(in_range[0])
         out.setdefault("nccl_calls_per_step", 0)
         out.setdefault("peer_calls_per_step", 0)
+        out.setdefault("peer_fused_per_step", 0)
         out["mem_gb"] = torch.cuda.max_memory_allocated(device) / 2**30
         out["adam"] = adam_roofline(T, device)
         dp.remove()
@@ -479,7 +481,8 @@ def run_native(args):
             "model_tflops": FLOPS_PER_IMAGE[args.loop] * B * world / (ms * 1e-3) / 1e12 / world,
             "clocks": main_run["clocks"], "gpu_launches": main_run["launches_per_step"],
             "nccl_calls_per_step": main_run["nccl_calls_per_step"],
-            "peer_calls_per_step": main_run["peer_calls_per_step"], "peak_mem_gib": main_run["mem_gb"],
+            "peer_calls_per_step": main_run["peer_calls_per_step"],
+            "peer_fused_per_step": main_run["peer_fused_per_step"], "peak_mem_gib": main_run["mem_gb"],
             "bce_in_range": main_run["bce_in_range"], "losses": main_run["losses"],
             "e2e": {"value": B * world / (ms_e2e * 1e-3), "unit": "images/s",
                     "h2d_bytes_per_step": main_run["h2d"], "d2h_bytes_per_step": main_run["d2h"]},

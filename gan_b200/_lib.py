@@ -110,6 +110,10 @@ SIGNATURES = {
     "ganb200_peer_close": (c_int, [P]),
     "ganb200_peer_allreduce": (c_int, [P, c_int, c_int, c_int64, P, P, P, P, c_int64, c_int, P]),
     "ganb200_peer_error": (c_int, [P, P]),
+    "ganb200_bn_small_sync_max_channels": (c_int, []),
+    "ganb200_bn_small_fwd_sync": (c_int, [P, P, P, P, P, P, P, P, P, c_int, c_int, c_int, c_float, c_float, P, P, c_int,
+                                          c_int, P]),
+    "ganb200_bn_small_bwd_sync": (c_int, [P, P, P, P, P, P, P, P, c_int, c_int, c_int, P, P, P, P, c_int, c_int, P]),
     "ganb200_chan_copy": (c_int, [P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, P]),
     "ganb200_mixup": (c_int, [P, P, c_float, P, c_int64, P]),
     "ganb200_mixup_wgan_f64": (c_int, [P, P, P, P, c_int, c_int, c_int, c_int, P]),

@@ -2,6 +2,7 @@
 // All HBM-bound; see DESIGN.md for the per-kernel algorithmic bytes.
 #include "common.cuh"
 #include "det_reduce.cuh"
+#include "peer.cuh"
 #include <algorithm>
 
 namespace ganb200 {
@@ -367,6 +368,10 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const float* __restrict__
 // each (and atomics).  Here one block owns one channel, keeps its N*HW values in registers, and does mean, variance
 // (two-pass, as the reference's native_batch_norm), normalisation, running statistics in ONE launch; the backward
 // (sums, dx, dgamma, dbeta) likewise.  Deterministic: fixed-order block reductions, no atomics.
+// Data parallel (sync-BN, `peer.bufs` set): between its statistics and its apply phase every block swaps two floats with
+// the block of the same channel on every other rank over NVLink (peer_ll_sum2, peer.cuh) — (mean, var + mean^2) forward,
+// (sum dy, sum dy * xhat) backward — so the layer stays ONE launch under data parallelism.  All C blocks must be
+// co-resident (they wait for their partners; the host wrapper checks C against the occupancy).
 namespace ganb200 {
 constexpr int BN_SMALL_THREADS = 128;
 constexpr int BN_SMALL_PER = 32;                                   // values per thread
@@ -376,8 +381,9 @@ __global__ void __launch_bounds__(BN_SMALL_THREADS) bn_small_fwd_kernel(
     const float* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ beta, float* __restrict__ y,
     float* __restrict__ mean_out, float* __restrict__ invstd_out, float* __restrict__ running_mean,
     float* __restrict__ running_var, int64_t* nbt, int N, int C, int HW, float eps, float momentum,
-    const float* __restrict__ slope) {
+    const float* __restrict__ slope, PeerRef peer) {
   const int c = blockIdx.x, cnt = N * HW;
+  const unsigned int seq = peer.bufs ? peer_seq_begin(peer) : 0u;
   float v[BN_SMALL_PER];
   float s = 0.f;
 #pragma unroll
@@ -389,14 +395,22 @@ __global__ void __launch_bounds__(BN_SMALL_THREADS) bn_small_fwd_kernel(
     if (!ok) v[e] = 0.f;
     s += v[e];
   }
-  const float mean = block_sum<BN_SMALL_THREADS>(s) / (float)cnt;
+  float mean = block_sum<BN_SMALL_THREADS>(s) / (float)cnt;
   float q = 0.f;
 #pragma unroll
   for (int e = 0; e < BN_SMALL_PER; ++e) {
     const float d = (threadIdx.x + e * BN_SMALL_THREADS < cnt) ? v[e] - mean : 0.f;
     q = fmaf(d, d, q);
   }
-  const float var = block_sum<BN_SMALL_THREADS>(q) / (float)cnt;
+  float var = block_sum<BN_SMALL_THREADS>(q) / (float)cnt;
+  float cnt_g = (float)cnt;
+  if (peer.bufs) {   // equal shards: global mean = mean of means, global biased variance = E[var + mean^2] - mean_g^2
+    const float2 t = peer_ll_sum2(peer, seq, c, mean, fmaf(mean, mean, var));
+    const float inv = 1.f / (float)peer.world;
+    mean = t.x * inv;
+    var = fmaf(-mean, mean, t.y * inv);
+    cnt_g *= (float)peer.world;
+  }
   const float is = 1.f / sqrtf(var + eps);
   const float gm = gamma ? gamma[c] : 1.f, bt = beta ? beta[c] : 0.f;
   const float sl = slope ? slope[c] : 1.f;   // following nn.PReLU(C), fused: y = u > 0 ? u : slope * u
@@ -414,17 +428,19 @@ __global__ void __launch_bounds__(BN_SMALL_THREADS) bn_small_fwd_kernel(
     invstd_out[c] = is;
     if (running_mean) running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
     if (running_var)
-      running_var[c] = (1.f - momentum) * running_var[c] + momentum * (cnt > 1 ? var * (float)cnt / (float)(cnt - 1) : var);
+      running_var[c] = (1.f - momentum) * running_var[c] + momentum * (cnt_g > 1.f ? var * cnt_g / (cnt_g - 1.f) : var);
     if (nbt && c == 0) *nbt += 1;
   }
+  if (peer.bufs) peer_seq_commit(peer, seq);
 }
 
 __global__ void __launch_bounds__(BN_SMALL_THREADS) bn_small_bwd_kernel(
     const float* __restrict__ gy, const float* __restrict__ x, const float* __restrict__ mean,
     const float* __restrict__ invstd, const float* __restrict__ gamma, float* __restrict__ gx,
     float* __restrict__ ggamma, float* __restrict__ gbeta, int N, int C, int HW, const float* __restrict__ beta,
-    const float* __restrict__ slope, float* __restrict__ gslope) {
+    const float* __restrict__ slope, float* __restrict__ gslope, PeerRef peer) {
   const int c = blockIdx.x, cnt = N * HW;
+  const unsigned int seq = peer.bufs ? peer_seq_begin(peer) : 0u;
   const float m = mean[c], is = invstd[c], gm = gamma ? gamma[c] : 1.f;
   const float bt = beta ? beta[c] : 0.f, sl = slope ? slope[c] : 1.f;
   float g[BN_SMALL_PER], xh[BN_SMALL_PER];
@@ -449,7 +465,13 @@ __global__ void __launch_bounds__(BN_SMALL_THREADS) bn_small_bwd_kernel(
   const float s1 = block_sum<BN_SMALL_THREADS>(a);
   const float s2 = block_sum<BN_SMALL_THREADS>(b);
   const float s3 = slope ? block_sum<BN_SMALL_THREADS>(ps) : 0.f;
-  const float ia = s1 / (float)cnt, ib = s2 / (float)cnt;
+  float ia = s1 / (float)cnt, ib = s2 / (float)cnt;
+  if (peer.bufs) {   // dx needs the sums over the global batch; dgamma / dbeta / dslope stay rank-local partial sums
+    const float2 t = peer_ll_sum2(peer, seq, c, s1, s2);
+    const float cnt_g = (float)cnt * (float)peer.world;
+    ia = t.x / cnt_g;
+    ib = t.y / cnt_g;
+  }
 #pragma unroll
   for (int e = 0; e < BN_SMALL_PER; ++e) {
     const int j = threadIdx.x + e * BN_SMALL_THREADS;
@@ -463,6 +485,7 @@ __global__ void __launch_bounds__(BN_SMALL_THREADS) bn_small_bwd_kernel(
     if (gbeta) gbeta[c] = s1;
     if (gslope) gslope[c] = s3;
   }
+  if (peer.bufs) peer_seq_commit(peer, seq);
 }
 }  // namespace ganb200
 
@@ -477,7 +500,38 @@ extern "C" int ganb200_bn_small_fwd(const float* x, const float* gamma, const fl
   GB_REQUIRE(ganb200_bn_small_eligible(N, C, HW), GANB200_BAD_SHAPE, "bn_small_fwd: N*HW must be in [1, 4096]");
   bn_small_fwd_kernel<<<C, BN_SMALL_THREADS, 0, (cudaStream_t)stream>>>(x, gamma, beta, y, mean, invstd, running_mean,
                                                                         running_var, num_batches_tracked, N, C, HW, eps,
-                                                                        momentum, prelu_slope);
+                                                                        momentum, prelu_slope, PeerRef{nullptr, 0, 1});
+  GB_CHECK_LAUNCH();
+  return 0;
+}
+
+// channels (= blocks that wait for their partners on the other ranks) the fused sync kernels can keep co-resident
+extern "C" int ganb200_bn_small_sync_max_channels(void) {
+  static int cap = -1;
+  if (cap < 0) {
+    int dev = 0, sms = 0, a = 0, b = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess ||
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&a, bn_small_fwd_kernel, BN_SMALL_THREADS, 0) != cudaSuccess ||
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, bn_small_bwd_kernel, BN_SMALL_THREADS, 0) != cudaSuccess)
+      return 0;
+    // half of what fits: other kernels (NCCL on the bucket stream) may hold SM slots
+    cap = std::min(std::min(a, b) * sms / 2, kPeerLLSlots);
+  }
+  return cap;
+}
+
+extern "C" int ganb200_bn_small_fwd_sync(const float* x, const float* gamma, const float* beta, float* y, float* mean,
+                                         float* invstd, float* running_mean, float* running_var,
+                                         int64_t* num_batches_tracked, int N, int C, int HW, float eps, float momentum,
+                                         const float* prelu_slope, const void* peer_bufs_dev, int rank, int world,
+                                         void* stream) {
+  GB_REQUIRE(ganb200_bn_small_eligible(N, C, HW), GANB200_BAD_SHAPE, "bn_small_fwd_sync: N*HW must be in [1, 4096]");
+  GB_REQUIRE(peer_bufs_dev && world >= 1 && world <= kPeerMaxWorld && rank >= 0 && rank < world, GANB200_BAD_ARG,
+             "bn_small_fwd_sync: bad peer table / rank / world");
+  GB_REQUIRE(C <= ganb200_bn_small_sync_max_channels(), GANB200_BAD_SHAPE, "bn_small_fwd_sync: too many channels to be co-resident");
+  bn_small_fwd_kernel<<<C, BN_SMALL_THREADS, 0, (cudaStream_t)stream>>>(
+      x, gamma, beta, y, mean, invstd, running_mean, running_var, num_batches_tracked, N, C, HW, eps, momentum, prelu_slope,
+      PeerRef{(char* const*)peer_bufs_dev, rank, world});
   GB_CHECK_LAUNCH();
   return 0;
 }
@@ -488,7 +542,24 @@ extern "C" int ganb200_bn_small_bwd(const float* gy, const float* x, const float
   GB_REQUIRE(ganb200_bn_small_eligible(N, C, HW), GANB200_BAD_SHAPE, "bn_small_bwd: N*HW must be in [1, 4096]");
   GB_REQUIRE(!prelu_slope || gslope, GANB200_BAD_ARG, "bn_small_bwd: prelu_slope without gslope");
   bn_small_bwd_kernel<<<C, BN_SMALL_THREADS, 0, (cudaStream_t)stream>>>(gy, x, mean, invstd, gamma, gx, ggamma, gbeta, N,
-                                                                        C, HW, beta, prelu_slope, gslope);
+                                                                        C, HW, beta, prelu_slope, gslope,
+                                                                        PeerRef{nullptr, 0, 1});
+  GB_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int ganb200_bn_small_bwd_sync(const float* gy, const float* x, const float* mean, const float* invstd,
+                                         const float* gamma, float* gx, float* ggamma, float* gbeta, int N, int C, int HW,
+                                         const float* beta, const float* prelu_slope, float* gslope,
+                                         const void* peer_bufs_dev, int rank, int world, void* stream) {
+  GB_REQUIRE(ganb200_bn_small_eligible(N, C, HW), GANB200_BAD_SHAPE, "bn_small_bwd_sync: N*HW must be in [1, 4096]");
+  GB_REQUIRE(!prelu_slope || gslope, GANB200_BAD_ARG, "bn_small_bwd_sync: prelu_slope without gslope");
+  GB_REQUIRE(peer_bufs_dev && world >= 1 && world <= kPeerMaxWorld && rank >= 0 && rank < world, GANB200_BAD_ARG,
+             "bn_small_bwd_sync: bad peer table / rank / world");
+  GB_REQUIRE(C <= ganb200_bn_small_sync_max_channels(), GANB200_BAD_SHAPE, "bn_small_bwd_sync: too many channels to be co-resident");
+  bn_small_bwd_kernel<<<C, BN_SMALL_THREADS, 0, (cudaStream_t)stream>>>(
+      gy, x, mean, invstd, gamma, gx, ggamma, gbeta, N, C, HW, beta, prelu_slope, gslope,
+      PeerRef{(char* const*)peer_bufs_dev, rank, world});
   GB_CHECK_LAUNCH();
   return 0;
 }

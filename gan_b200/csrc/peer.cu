@@ -14,19 +14,14 @@
 //           applies the epilogue (mean over ranks; var = E[x^2] - mean^2) and writes the results.
 //
 // Buffer of one rank (ganb200_peer_bytes): [flags: one 128-byte line per source rank][control: sequence number, error
-// flag][data slot 0][data slot 1].  Slots alternate with the sequence number: a rank can only reach call s+2 (which
+// word, done counter][LL slots of the per-block exchanges, peer.cuh][data slot 0][data slot 1].  Slots alternate with the sequence number: a rank can only reach call s+2 (which
 // rewrites the slot of call s) after every rank has signalled call s+1, i.e. after every rank has finished reading call s.
 // The sequence number lives on the device, so the launch is CUDA-graph capturable and replays keep counting.
 // All ranks must issue the same exchanges in the same order on their step stream (they run the same program).
 // A wait that exceeds ~20 s (a dead peer) sets the error word and returns, so that a failed rank cannot hang the box.
-#include "common.cuh"
+#include "peer.cuh"
 
 namespace ganb200 {
-
-constexpr int kPeerMaxWorld = 16;
-constexpr int kPeerFlagStride = 32;                       // uint32 per flag line (128 B)
-constexpr size_t kPeerCtlOffset = kPeerMaxWorld * 128;     // bytes
-constexpr size_t kPeerDataOffset = kPeerCtlOffset + 128;   // bytes
 
 struct PeerArgs {
   char* const* bufs;   // device array [world] of exchange buffers (own mapping at [rank])
@@ -37,25 +32,6 @@ struct PeerArgs {
   int n;               // elements per vector
   int op;
 };
-
-__device__ __forceinline__ void st_release_sys(unsigned int* p, unsigned int v) {
-  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int* p) {
-  unsigned int v;
-  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ float ld_relaxed_sys(const float* p) {
-  float v;
-  asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ unsigned long long global_ns() {
-  unsigned long long t;
-  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
-  return t;
-}
 
 __global__ void __launch_bounds__(1024) peer_allreduce_kernel(PeerArgs a) {
   char* own = a.bufs[a.rank];
@@ -82,7 +58,7 @@ __global__ void __launch_bounds__(1024) peer_allreduce_kernel(PeerArgs a) {
     const unsigned long long t0 = global_ns();
     unsigned int spins = 0;
     while ((int)(ld_acquire_sys(flag) - seq) < 0) {
-      if ((++spins & 0xfffu) == 0 && global_ns() - t0 > 20000000000ull) { ctl[1] = 1u; break; }
+      if ((++spins & 0xfffu) == 0 && global_ns() - t0 > kPeerTimeoutNs) { ctl[1] = 1u; break; }
     }
   }
   __syncthreads();

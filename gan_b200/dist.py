@@ -265,6 +265,7 @@ class DataParallelStep:
                 return pack[0].contiguous(), pack[1].contiguous()
 
             ops._sync_bn_hooks["stats"], ops._sync_bn_hooks["grads"] = stats, grads
+            ops._sync_bn_hooks["peer"] = px     # the one-launch BatchNorm kernels carry the exchange themselves
         return self
 
     def remove(self):
@@ -273,7 +274,7 @@ class DataParallelStep:
             self.peer.close()
             self.peer = PEER[0] = None
         ops._mbstd_reduce[0] = None
-        ops._sync_bn_hooks["stats"] = ops._sync_bn_hooks["grads"] = None
+        ops._sync_bn_hooks["stats"] = ops._sync_bn_hooks["grads"] = ops._sync_bn_hooks["peer"] = None
         for opt in (self.T.optimizer_G, self.T.optimizer_D):
             opt.grad_scale = 1.0
             if isinstance(opt.pre_step, GradSync):

@@ -446,9 +446,21 @@ class CudaBackend:
         N, C, HW = _nchw(x)
         return N * HW <= self.BN_SMALL_MAX
 
-    def bn_small_fwd(self, x, gamma, beta, running_mean, running_var, eps, momentum, nbt=None, slope=None):
+    def bn_small_sync_ok(self, x, peer):
+        """data parallel: can the fused launch carry the sync-BN exchange (gan_b200.peer.PeerExchange, all C blocks
+        co-resident)?"""
+        if peer is None or not self.bn_small_ok(x):
+            return False
+        if self._bn_sync_cap is None:
+            self._bn_sync_cap = int(self.lib.ganb200_bn_small_sync_max_channels())
+        return x.shape[1] <= self._bn_sync_cap
+
+    _bn_sync_cap = None
+
+    def bn_small_fwd(self, x, gamma, beta, running_mean, running_var, eps, momentum, nbt=None, slope=None, peer=None):
         """one launch: batch statistics, y (optionally through the following per-channel PReLU), running statistics
-        -> (y, mean, invstd)"""
+        -> (y, mean, invstd).  `peer` (gan_b200.peer.PeerExchange): statistics over the GLOBAL batch, swapped between
+        the ranks inside the launch."""
         N, C, HW = _nchw(x)
         st = self._prep(x, gamma, beta, running_mean, running_var, slope)
         if slope is not None and slope.numel() != C:
@@ -458,19 +470,34 @@ class CudaBackend:
         y = torch.empty_like(x)
         mean = torch.empty((C,), dtype=torch.float32, device=x.device)
         invstd = torch.empty((C,), dtype=torch.float32, device=x.device)
+        if peer is not None:
+            peer.count()
+            _lib.check(self.lib.ganb200_bn_small_fwd_sync(self._p(x), self._p(gamma), self._p(beta), self._p(y),
+                                                          self._p(mean), self._p(invstd), self._p(running_mean),
+                                                          self._p(running_var), self._p(nbt), N, C, HW, eps, momentum,
+                                                          self._p(slope), self._p(peer.table), peer.rank, peer.world, st))
+            return y, mean, invstd
         _lib.check(self.lib.ganb200_bn_small_fwd(self._p(x), self._p(gamma), self._p(beta), self._p(y), self._p(mean),
                                                  self._p(invstd), self._p(running_mean), self._p(running_var),
                                                  self._p(nbt), N, C, HW, eps, momentum, self._p(slope), st))
         return y, mean, invstd
 
-    def bn_small_bwd(self, gy, x, mean, invstd, gamma, beta=None, slope=None):
-        """one launch: (gx, ggamma, gbeta[, gslope when the PReLU is fused])"""
+    def bn_small_bwd(self, gy, x, mean, invstd, gamma, beta=None, slope=None, peer=None):
+        """one launch: (gx, ggamma, gbeta[, gslope when the PReLU is fused]).  `peer`: dx from the sums over the global
+        batch (swapped inside the launch); ggamma / gbeta / gslope stay rank-local partial sums."""
         N, C, HW = _nchw(x)
         st = self._prep(gy, x, mean, invstd, gamma, beta, slope)
         gx = torch.empty_like(x)
         gg = torch.empty((C,), dtype=torch.float32, device=x.device)
         gb = torch.empty((C,), dtype=torch.float32, device=x.device)
         gs = torch.empty((C,), dtype=torch.float32, device=x.device) if slope is not None else None
+        if peer is not None:
+            peer.count()
+            _lib.check(self.lib.ganb200_bn_small_bwd_sync(self._p(gy), self._p(x), self._p(mean), self._p(invstd),
+                                                          self._p(gamma), self._p(gx), self._p(gg), self._p(gb), N, C, HW,
+                                                          self._p(beta), self._p(slope), self._p(gs), self._p(peer.table),
+                                                          peer.rank, peer.world, st))
+            return (gx, gg, gb) if slope is None else (gx, gg, gb, gs)
         _lib.check(self.lib.ganb200_bn_small_bwd(self._p(gy), self._p(x), self._p(mean), self._p(invstd),
                                                  self._p(gamma), self._p(gx), self._p(gg), self._p(gb), N, C, HW,
                                                  self._p(beta), self._p(slope), self._p(gs), st))

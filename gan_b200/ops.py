@@ -752,7 +752,19 @@ def bce_loss(p, t):
 # =====================================================================================================
 # generator-only ops (once differentiable; BatchNorm: see _bn_composed)
 # =====================================================================================================
-_sync_bn_hooks = {"stats": None, "grads": None}  # installed by gan_b200.dist for data-parallel sync-BN
+# installed by gan_b200.dist for data-parallel sync-BN; "peer": gan_b200.peer.PeerExchange (NVLink) or None
+_sync_bn_hooks = {"stats": None, "grads": None, "peer": None}
+
+
+def _bn_small_mode(x):
+    """-> (use the one-launch kernels?, peer exchange to hand them): single rank, or data parallel with the exchange
+    carried inside the launch"""
+    if _sync_bn_hooks["stats"] is None and _sync_bn_hooks["grads"] is None:
+        return K().bn_small_ok(x), None
+    px = _sync_bn_hooks["peer"]
+    if px is not None and x.is_cuda and x.dtype == torch.float32 and K().bn_small_sync_ok(x, px):
+        return True, px
+    return False, None
 
 
 def _bn_composed(x, gamma, beta, eps, rank_mean=None):
@@ -788,9 +800,12 @@ class BatchNormTrainFn(Function):
         x = _c(x)
         N, C, HW = KN._nchw(x)
         count = N * HW
-        ctx.small = _sync_bn_hooks["stats"] is None and _sync_bn_hooks["grads"] is None and K().bn_small_ok(x)
-        if ctx.small:  # single rank, small per-channel population: statistics + apply + running stats in one launch
-            y, mean, invstd = K().bn_small_fwd(x, gamma, beta, running_mean, running_var, eps, momentum, nbt)
+        ctx.small, ctx.peer = _bn_small_mode(x)
+        if ctx.small:  # small per-channel population: statistics (+ rank exchange) + apply + running stats in one launch
+            kw = {"peer": ctx.peer} if ctx.peer is not None else {}
+            y, mean, invstd = K().bn_small_fwd(x, gamma, beta, running_mean, running_var, eps, momentum, nbt, **kw)
+            if ctx.peer is not None:
+                count *= ctx.peer.world
         else:
             mean, var = K().bn_stats(x)
             if _sync_bn_hooks["stats"] is not None:
@@ -816,8 +831,9 @@ class BatchNormTrainFn(Function):
             gx, gg, gb = (next(got) if (need and t is not None) else None
                           for t, need in zip((x, gamma, beta), ctx.needs_input_grad[:3]))
             return gx, gg, gb, None, None, None, None, None
-        if ctx.small and _sync_bn_hooks["grads"] is None:
-            gx, gg, gb = K().bn_small_bwd(gy, x, mean, invstd, gamma)
+        if ctx.small and (_sync_bn_hooks["grads"] is None or ctx.peer is not None):
+            kw = {"peer": ctx.peer} if ctx.peer is not None else {}
+            gx, gg, gb = K().bn_small_bwd(gy, x, mean, invstd, gamma, **kw)
             return (gx, (gg if gamma is not None else None), (gb if ctx.needs_input_grad[2] else None), None, None,
                     None, None, None)
         s1, s2 = K().bn_bwd_reduce(gy, x, mean, invstd)
@@ -841,7 +857,9 @@ class BnPReluTrainFn(Function):
     @staticmethod
     def forward(ctx, x, gamma, beta, slope, running_mean, running_var, eps, momentum, nbt=None):
         x = _c(x)
-        y, mean, invstd = K().bn_small_fwd(x, gamma, beta, running_mean, running_var, eps, momentum, nbt, slope)
+        _, ctx.peer = _bn_small_mode(x)
+        kw = {"peer": ctx.peer} if ctx.peer is not None else {}
+        y, mean, invstd = K().bn_small_fwd(x, gamma, beta, running_mean, running_var, eps, momentum, nbt, slope, **kw)
         ctx.save_for_backward(x, mean, invstd, gamma, beta, slope)
         return y
 
@@ -849,15 +867,15 @@ class BnPReluTrainFn(Function):
     @once_differentiable
     def backward(ctx, gy):
         x, mean, invstd, gamma, beta, slope = ctx.saved_tensors
-        gx, gg, gb, gs = K().bn_small_bwd(_c(gy), x, mean, invstd, gamma, beta, slope)
+        kw = {"peer": ctx.peer} if ctx.peer is not None else {}
+        gx, gg, gb, gs = K().bn_small_bwd(_c(gy), x, mean, invstd, gamma, beta, slope, **kw)
         return (gx, (gg if gamma is not None else None), (gb if beta is not None else None), gs.reshape(slope.shape),
                 None, None, None, None, None)
 
 
 def bn_prelu_fusable(x, slope):
-    """single rank (no sync-BN exchange between statistics and apply), per-channel slope, small population"""
-    return (_sync_bn_hooks["stats"] is None and _sync_bn_hooks["grads"] is None and x.dim() >= 2 and
-            slope.numel() == x.shape[1] and K().bn_small_ok(x))
+    """per-channel slope, small population; data parallel: only with the sync-BN exchange inside the launch"""
+    return x.dim() >= 2 and slope.numel() == x.shape[1] and _bn_small_mode(x)[0]
 
 
 def batch_norm_prelu_train(x, gamma, beta, slope, running_mean, running_var, eps, momentum, nbt=None):

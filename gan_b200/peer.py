@@ -24,6 +24,7 @@ from . import kernels as KN
 SUM, MEAN, BN_STATS = 0, 1, 2
 CAP_FLOATS = 1 << 14          # floats per slot: two vectors of 8 192 channels
 CALLS = [0]                   # launches issued by this process (bench.py: peer_calls_per_step)
+FUSED = [0]                   # exchanges that ran inside a BatchNorm launch (bench.py: peer_fused_per_step)
 
 
 class PeerExchange:
@@ -92,6 +93,10 @@ class PeerExchange:
         print(f"[gan_b200.peer] rank {dist.get_rank(group)}: NVLink peer exchange unavailable ({why or 'another rank failed'}); "
               "small exchanges stay on NCCL", file=sys.stderr, flush=True)
         return None
+
+    def count(self):
+        """an exchange carried inside another kernel's launch (the fused sync BatchNorm)"""
+        FUSED[0] += 1
 
     def fits(self, n, vectors=1):
         return 0 < n * vectors <= self.cap

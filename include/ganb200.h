@@ -336,6 +336,20 @@ int ganb200_peer_close(void* buf);
 int ganb200_peer_allreduce(const void* bufs_dev, int rank, int world, int64_t cap_floats, const float* in0,
                            const float* in1, float* out0, float* out1, int64_t n, int op, void* stream);
 int ganb200_peer_error(const void* buf, int* error);
+/* The fused small-population BatchNorm launches (ganb200_bn_small_fwd / _bwd) under data parallelism: every block swaps
+ * its two statistics with the same channel's block on the other ranks in the middle of the kernel (8-byte {value, sequence
+ * number} stores over NVLink, peer.cuh), so sync-BN stays one launch each way.  mean / invstd returned are the global ones,
+ * running_var is unbiased with the global count; ggamma / gbeta / gslope stay rank-local partial sums.
+ * C <= ganb200_bn_small_sync_max_channels() (all blocks must be co-resident). */
+int ganb200_bn_small_sync_max_channels(void);
+int ganb200_bn_small_fwd_sync(const float* x, const float* gamma, const float* beta, float* y, float* mean, float* invstd,
+                              float* running_mean, float* running_var, int64_t* num_batches_tracked, int N, int C, int HW,
+                              float eps, float momentum, const float* prelu_slope, const void* peer_bufs_dev, int rank,
+                              int world, void* stream);
+int ganb200_bn_small_bwd_sync(const float* gy, const float* x, const float* mean, const float* invstd, const float* gamma,
+                              float* gx, float* ggamma, float* gbeta, int N, int C, int HW, const float* beta,
+                              const float* prelu_slope, float* gslope, const void* peer_bufs_dev, int rank, int world,
+                              void* stream);
 
 /* Channel-slice copy on [N,C,HW] tensors: dst[:, dst_c0:dst_c0+ncopy] (+)= src[:, src_c0:src_c0+ncopy].
  * Replaces torch.cat(dim=1) / channel slicing and their adjoints (generator_13_5.py:451-467,549-560,

@@ -65,6 +65,7 @@ def _step(rank, world, B, out_dir, port):
            "bn_mean": G.bn2.running_mean.cpu(), "bn_var": G.bn2.running_var.cpu(),
            "d_grads": d_grads, "g_grads": g_grads, "calls": gdist.CALLS[0], "overlapped": overlapped,
            "peer_calls": __import__("gan_b200.peer", fromlist=["CALLS"]).CALLS[0],
+           "peer_fused": __import__("gan_b200.peer", fromlist=["FUSED"]).FUSED[0],
            "d_params": {n: p.detach().cpu() for n, p in D.named_parameters()},
            "g_params": {n: p.detach().cpu() for n, p in G.named_parameters()}}
     if dp is not None:
@@ -106,6 +107,7 @@ def test_two_rank_nccl_step_equals_single_rank_big_batch(tmp_path):
             assert torch.allclose(m[key], single[key], rtol=1e-4, atol=1e-5), (key, (m[key] - single[key]).abs().max())
         assert m["calls"] > 0
         assert m["peer_calls"] > 0, "the small exchanges must run over NVLink peer memory (gan_b200.peer), not NCCL"
+        assert m["peer_fused"] > 0, "the one-launch BatchNorm kernels must carry the sync-BN exchange themselves"
         assert m["overlapped"][0] == (0, 0) and m["overlapped"][1][0] >= 1 and m["overlapped"][1][1] >= 1, m["overlapped"]
         for key in ("d_params", "g_params"):   # after two Adam updates (a sign flip of a ~0 gradient moves an element by 2 lr)
             for n, v in single[key].items():
