@@ -753,6 +753,213 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_halo_kernel(const __gri
   }
 }
 
+// ------------------------------------------------------------------------------------------------ flat kernel
+// Stride-1 forward problems whose taps all fall inside the MATERIALISED padding of the packed input (replicate-padded
+// convolutions: every layer of the generator and the critic).  The padded NHWC input is read as what it is in memory, a
+// 2-D matrix [N*Hp*Wp flat pixels][C], and the convolution as a 1-D one over flat pixels: output o = (n*Hp + y)*Wp + x
+// needs input rows o + (dh0 + r)*Wp + (dw0 + s).  One CTA tile is MT*128 CONSECUTIVE flat pixels of one image, and per
+// 64-channel chunk ONE contiguous range of MT*128 + (R-1)*Wp + (S-1) flat rows is loaded (as 64-row TMA boxes): every
+// tap of the filter is that same shared-memory range read from a start address shifted by (r*Wp + s) rows of 128 bytes.
+// The shifts are not multiples of the 8-row SWIZZLE_128B atom; the tensor core applies the swizzle to the absolute
+// shared-memory address, so any 128-byte shift addresses the rows TMA wrote (csrc/probe.cu / ganb200_tc_shift_probe is the
+// hardware check, tests/test_gpu_kernels.py).  Activation fill per output pixel drops from S * (rows + R - 1) / rows boxes
+// (halo kernel; measured 48 -> 48 5x5 at 64x64: 1.64 GB L2 -> shared memory per launch at 6.3 TB/s, tensor pipe 23 %) to
+// (MT*128 + (R-1)*Wp + S-1) / (MT*128) rows — 2.1 instead of 7.5 input rows per output row on that layer.
+// Outputs at x >= Q (the Wp - Q columns of row padding) and y >= P are computed and dropped: (Wp - Q) / Wp of the MMA work.
+// Same tap order and k order per output element as the halo kernel: identical results.
+// Warps: 0 = activation producer, 1 = MMA issuer, 2-5 = epilogue, 6 = weight producer (its own ring, so that the next
+// tile's activations are requested while the current tile's weight boxes still stream).
+constexpr int FLAT_THREADS = 224;
+constexpr int FLAT_BOX_ROWS = 64;                           // rows per TMA box (8 KB)
+constexpr int FLAT_BOX_BYTES = FLAT_BOX_ROWS * 128;
+constexpr int FLAT_MAX_B_STAGES = 16;                       // weight ring (barrier slots)
+constexpr int FLAT_FIXED_BYTES = 1024 /*align*/ + 512 /*barriers*/;
+
+struct TcFlatParams {
+  int N, K, P, Q, C;
+  int R, S, dh0, dw0;
+  int Hp, Wp;            // padded input plane
+  int mt;                // sub-tiles (accumulators) of 128 flat pixels per CTA tile
+  int nbox;              // 64-row boxes per activation stage
+  int a_stages;
+  int b_stages;          // weight ring: boxes of n_umma * 128 bytes; the fill is latency-bound, so as deep as fits
+  int tiles_img;         // tiles per image = ceil(P * Wp / (mt * 128))
+  int tiles_m, tiles_n;
+  int OH, OW, o_step, o_off_h, o_off_w;
+  int n_umma;
+  float alpha;
+  const float* oscale;
+  const float* bias;
+  float* y;
+  unsigned char tap_idx[MAX_TAPS];  // packed-weight index of grid point r * S + s
+};
+
+template <int BN>
+__global__ void __launch_bounds__(FLAT_THREADS, 1) tc_conv_flat_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                                       const __grid_constant__ CUtensorMap tmB,
+                                                                       const TcFlatParams p) {
+  constexpr int MT_MAX = 2;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int SA = p.a_stages, SB = p.b_stages;
+  const int a_bytes = p.nbox * FLAT_BOX_BYTES;
+  const int b_bytes = p.n_umma * 128;            // a multiple of 1024 (n_umma is a multiple of 8)
+  uint8_t* smA = smem;
+  uint8_t* smB = smem + SA * a_bytes;
+  uint64_t* fullA = reinterpret_cast<uint64_t*>(smB + SB * b_bytes);
+  uint64_t* emptyA = fullA + HALO_MAX_STAGES;
+  uint64_t* fullB = emptyA + HALO_MAX_STAGES;
+  uint64_t* emptyB = fullB + FLAT_MAX_B_STAGES;
+  uint64_t* tmem_full = emptyB + FLAT_MAX_B_STAGES;  // [2]
+  uint64_t* tmem_empty = tmem_full + 2;          // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int k_chunks = (p.C + BK - 1) / BK;
+  const int total_tiles = p.tiles_m * p.tiles_n;
+  const int tile_px = p.mt * TILE_M;
+  constexpr uint32_t TMEM_COLS = 2 * MT_MAX * BN;
+  // tile -> (k0, position of the tile inside its image, image): channel tile fastest
+  auto decode = [&](int tile, int& k0, int& ti, int& n) {
+    const int t = tile / p.tiles_n;
+    k0 = (tile - t * p.tiles_n) * BN;
+    n = t / p.tiles_img;
+    ti = t - n * p.tiles_img;
+  };
+
+  if (threadIdx.x == 0) {
+    prefetch_tmap(&tmA);
+    prefetch_tmap(&tmB);
+    for (int i = 0; i < SA; ++i) { mbar_init(&fullA[i], 1); mbar_init(&emptyA[i], 1); }
+    for (int i = 0; i < SB; ++i) { mbar_init(&fullB[i], 1); mbar_init(&emptyB[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 4); }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // activation producer
+    const bool leader = elect_one();
+    int sa = 0;
+    uint32_t pa = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      int k0, ti, n;
+      decode(tile, k0, ti, n);
+      const int row0 = n * p.Hp * p.Wp + ti * tile_px + p.dh0 * p.Wp + p.dw0;
+      for (int kc = 0; kc < k_chunks; ++kc) {
+        mbar_wait(&emptyA[sa], pa ^ 1);
+        if (leader) {
+          mbar_expect_tx(&fullA[sa], (uint32_t)a_bytes);
+          for (int b = 0; b < p.nbox; ++b)
+            tma_load_3d(smA + sa * a_bytes + b * FLAT_BOX_BYTES, &tmA, &fullA[sa], kc * BK, row0 + b * FLAT_BOX_ROWS, 0);
+        }
+        if (++sa == SA) { sa = 0; pa ^= 1; }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 6) {
+    // weight producer: one box per (chunk, tap), in the order the MMA warp consumes them
+    const bool leader = elect_one();
+    int sb = 0;
+    uint32_t pb = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      int k0, ti, n;
+      decode(tile, k0, ti, n);
+      for (int kc = 0; kc < k_chunks; ++kc)
+        for (int s = 0; s < p.S; ++s)
+          for (int r = 0; r < p.R; ++r) {
+            mbar_wait(&emptyB[sb], pb ^ 1);
+            if (leader) {
+              mbar_expect_tx(&fullB[sb], (uint32_t)p.n_umma * 128u);
+              tma_load_3d(smB + sb * b_bytes, &tmB, &fullB[sb], kc * BK, k0, (int)p.tap_idx[r * p.S + s]);
+            }
+            if (++sb == SB) { sb = 0; pb ^= 1; }
+          }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    const bool leader = elect_one();
+    const uint32_t idesc = make_idesc_bf16(TILE_M, p.n_umma, 0, 0);
+    int sa = 0, sb = 0, local = 0;
+    uint32_t pa = 0, pb = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++local) {
+      const int acc = local & 1;
+      mbar_wait(&tmem_empty[acc], ((local >> 1) & 1) ^ 1);
+      tc_fence_after();
+      const uint32_t tmem_d = tmem_base + (uint32_t)(acc * MT_MAX * BN);
+      for (int kc = 0; kc < k_chunks; ++kc) {
+        const int ksub = min(BK / 16, (p.C - kc * BK + 15) / 16);
+        mbar_wait(&fullA[sa], pa);
+        tc_fence_after();
+        const uint32_t a_base = smem_u32(smA + sa * a_bytes);
+        for (int s = 0; s < p.S; ++s)
+          for (int r = 0; r < p.R; ++r) {
+            mbar_wait(&fullB[sb], pb);
+            tc_fence_after();
+            const uint64_t bdesc = make_smem_desc_sw128(smem_u32(smB + sb * b_bytes), 16, 1024);
+            const uint64_t adesc0 = make_smem_desc_sw128(a_base + (uint32_t)(r * p.Wp + s) * 128u, 16, 1024);
+            const uint32_t fresh = (kc == 0 && s == 0 && r == 0) ? 0u : 1u;
+            if (leader) {
+              mma_chain_n(ksub, tmem_d, adesc0, bdesc, idesc, fresh, 2u);
+              if (p.mt == 2)
+                mma_chain_n(ksub, tmem_d + (uint32_t)BN, adesc0 + (uint64_t)((TILE_M * 128) >> 4), bdesc, idesc, fresh, 2u);
+              mma_commit(&emptyB[sb]);
+            }
+            if (++sb == SB) { sb = 0; pb ^= 1; }
+          }
+        if (leader) mma_commit(&emptyA[sa]);
+        if (++sa == SA) { sa = 0; pa ^= 1; }
+      }
+      if (leader) mma_commit(&tmem_full[acc]);
+    }
+    __syncwarp();
+  } else {
+    const int quarter = warp & 3;
+    const int m = quarter * 32 + lane;
+    const int64_t PQ = (int64_t)p.OH * p.OW;
+    const uint32_t plane_bytes = (uint32_t)PQ * 4u;
+    int local = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++local) {
+      int k0, ti, n;
+      decode(tile, k0, ti, n);
+      const float* osc = p.oscale ? p.oscale + (int64_t)n * p.K : nullptr;
+      const int acc = local & 1;
+      mbar_wait(&tmem_full[acc], (local >> 1) & 1);
+      tc_fence_after();
+      for (int j = 0; j < p.mt; ++j) {
+        const int o = ti * tile_px + j * TILE_M + m;      // flat position inside the image's padded plane
+        const int yy = o / p.Wp, xx = o - yy * p.Wp;
+        const bool row_ok = (xx < p.Q) && (yy < p.P);
+        const int64_t pix = (int64_t)(yy * p.o_step + p.o_off_h) * p.OW + xx * p.o_step + p.o_off_w;
+        float* ybase = p.y + ((int64_t)n * p.K) * PQ + (row_ok ? pix : 0);
+#pragma unroll
+        for (int c0 = 0; c0 < BN; c0 += 32) {
+          if (c0 >= p.n_umma) break;
+          float v[32];
+          tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)((acc * MT_MAX + j) * BN + c0), v);
+          const int kc = k0 + c0;
+          const int nvalid = min(p.n_umma - c0, p.K - kc);
+          if (row_ok && nvalid > 0)
+            epi_chunk(v, reinterpret_cast<char*>(ybase + (int64_t)kc * PQ), plane_bytes, nvalid, p.alpha,
+                      osc ? osc + kc : nullptr, p.bias ? p.bias + kc : nullptr);
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+    }
+  }
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
 // ------------------------------------------------------------------------------------------------ host side
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -875,6 +1082,91 @@ static bool halo_plan(const TcProblem& q, int BN, TcHaloParams& h) {
   return true;
 }
 
+// 1 (default) = the flat kernel where it measured faster than the halo / per-tap kernels (tools/flat_bench.py, B = 256:
+// the generator's 3x3 layers of up to 96 channels on 64 x 64 planes, 1.03-1.07x); 2 = wherever a forward problem
+// qualifies (parity tests); 0 = never.  GANB200_CONV_FLAT or ganb200_conv_flat_mode().
+// What the experiment showed (profiles/r02_flat_kernel_experiments.txt): the 48-channel layers are NOT bound by the bytes
+// they move from L2 — with a quarter of the activation fill (this kernel), or with the weight ring 13 deep instead of 4,
+// or with no weight traffic at all, the launch takes the same time to 5 %; with the MMAs removed it still takes 60 % of
+// it.  The floor is the latency of the per-tile activation stage (two 72 KB stages in flight move ~3 TB/s chip-wide), on
+// top of which the shared-memory-bound N = 48 MMAs (4 KB of A per 24-cycle instruction) add instead of overlapping.
+static int g_flat_mode = -1;
+static int flat_mode() {
+  if (g_flat_mode < 0) {
+    const char* e = getenv("GANB200_CONV_FLAT");
+    g_flat_mode = (e && e[0] == '0') ? 0 : (e && e[0] == '2') ? 2 : 1;
+  }
+  return g_flat_mode;
+}
+
+// Fills `f` and returns true when problem `q` can run on the flat kernel.
+static bool flat_plan(const TcProblem& q, int BN, TcFlatParams& f) {
+  if (q.in_step != 1 || q.taps.n < 1 || q.taps.n > MAX_TAPS || q.fold || q.red_out) return false;
+  if (q.Qo < 32 || q.Po < 8) return false;     // narrow planes: the row padding would be too large a share of the work
+  const int Hp = q.Hi + 2 * q.mat_pad, Wp = q.Wi + 2 * q.mat_pad;
+  int dh_lo = 127, dh_hi = -128, dw_lo = 127, dw_hi = -128;
+  for (int t = 0; t < q.taps.n; ++t) {
+    dh_lo = std::min(dh_lo, (int)q.taps.dh[t]); dh_hi = std::max(dh_hi, (int)q.taps.dh[t]);
+    dw_lo = std::min(dw_lo, (int)q.taps.dw[t]); dw_hi = std::max(dw_hi, (int)q.taps.dw[t]);
+  }
+  const int R = dh_hi - dh_lo + 1, S = dw_hi - dw_lo + 1;
+  if (R * S != q.taps.n) return false;
+  // every tap of every valid output must read a pixel of the SAME image's padded plane: the flat view has no border
+  if (dh_lo < 0 || dw_lo < 0 || q.Po - 1 + dh_hi > Hp - 1 || q.Qo - 1 + dw_hi > Wp - 1) return false;
+  bool seen[MAX_TAPS] = {false};
+  for (int t = 0; t < q.taps.n; ++t) {
+    const int g = (q.taps.dh[t] - dh_lo) * S + (q.taps.dw[t] - dw_lo);
+    if (seen[g]) return false;
+    seen[g] = true;
+    f.tap_idx[g] = (unsigned char)t;
+  }
+  f.n_umma = q.Ko >= BN ? BN : (q.Ko + 15) / 16 * 16;
+  const int b_bytes = f.n_umma * 128;
+  const int room = HALO_SMEM_MAX - FLAT_FIXED_BYTES;
+  int best_mt = 0;
+  double best_cost = 0;
+  for (int mt = 2; mt >= 1; --mt) {
+    const int rows = mt * TILE_M + (R - 1) * Wp + (S - 1);
+    const int nbox = ceil_div(rows, FLAT_BOX_ROWS);
+    const int a_bytes = nbox * FLAT_BOX_BYTES;
+    // two activation stages; the rest goes to the weight ring (its boxes are small and the ring is latency-bound: 4
+    // stages of 6 KB kept the 48-channel 5x5 layers at 23 % tensor pipe whatever the activation traffic was); what is
+    // left after 16 weight stages buys a third activation stage
+    int a_stages = 2;
+    int b_stages = std::min(FLAT_MAX_B_STAGES, (room - a_stages * a_bytes) / b_bytes);
+    if (b_stages < 4) continue;
+    if (b_stages == FLAT_MAX_B_STAGES && room - a_stages * a_bytes - b_stages * b_bytes >= a_bytes) a_stages = 3;
+    const int tiles_img = ceil_div(q.Po * Wp, mt * TILE_M);
+    // cost per image: bytes filled + MMA work expressed in bytes (one 128-pixel MMA row block ~ 2 KB of fill time)
+    const double cost = (double)tiles_img * (a_bytes + (double)R * S * b_bytes + mt * 2048.0 * R * S / 4.0);
+    if (!best_mt || cost < best_cost) {
+      best_mt = mt; best_cost = cost; f.nbox = nbox; f.a_stages = a_stages; f.b_stages = b_stages; f.tiles_img = tiles_img;
+    }
+  }
+  if (!best_mt) return false;
+  f.mt = best_mt;
+  f.N = q.N; f.K = q.Ko; f.P = q.Po; f.Q = q.Qo; f.C = q.Ci;
+  f.R = R; f.S = S; f.dh0 = dh_lo; f.dw0 = dw_lo; f.Hp = Hp; f.Wp = Wp;
+  f.tiles_m = f.tiles_img * q.N; f.tiles_n = ceil_div(q.Ko, BN);
+  f.OH = q.OH; f.OW = q.OW; f.o_step = q.o_step; f.o_off_h = q.o_off_h; f.o_off_w = q.o_off_w;
+  if ((int64_t)q.N * Hp * Wp + 4096 >= ((int64_t)1 << 31)) return false;
+  return true;
+}
+
+template <int BN>
+static int launch_flat(const CUtensorMap& ta, const CUtensorMap& tb, const TcFlatParams& p, dim3 grid, cudaStream_t s) {
+  static bool configured = false;
+  if (!configured) {
+    GB_CHECK_CUDA(cudaFuncSetAttribute(tc_conv_flat_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       HALO_SMEM_MAX));
+    configured = true;
+  }
+  const int smem = FLAT_FIXED_BYTES + p.b_stages * p.n_umma * 128 + p.a_stages * p.nbox * FLAT_BOX_BYTES;
+  tc_conv_flat_kernel<BN><<<grid, FLAT_THREADS, smem, s>>>(ta, tb, p);
+  GB_CHECK_LAUNCH();
+  return 0;
+}
+
 static int pack_input(const float* in, const float* in_scale, __nv_bfloat16* act, int N, int Ci, int Hi, int Wi,
                       int mat_pad, cudaStream_t s) {
   const int Cp = cpad(Ci), Hp = Hi + 2 * mat_pad;
@@ -938,6 +1230,27 @@ static int run_problem(const TcProblem& q, const __nv_bfloat16* act, const float
     GB_CHECK_LAUNCH();
   }
   const int BN = q.Ko > 64 ? 128 : 64;   // 64 < Ko < 128 (96, 108): one 128-wide tile, the activations are read once
+  {
+    TcFlatParams f;
+    const bool flat_wins = q.taps.n == 9 && q.Ci <= 96 && q.Ko <= 96 && q.Ci % 64 != 0 && q.Qo >= 64;
+    if (halo_mode() >= 1 && (flat_mode() == 2 || (flat_mode() == 1 && flat_wins)) && flat_plan(q, BN, f)) {
+      f.alpha = q.alpha; f.oscale = out_scale; f.bias = bias; f.y = out;
+      CUtensorMap ta, tb;
+      uint64_t dims[3] = {(uint64_t)q.Ci, (uint64_t)q.N * Hp * Wp, 1};
+      uint64_t str[2] = {(uint64_t)Cp * 2, (uint64_t)q.N * Hp * Wp * Cp * 2};
+      uint32_t box[3] = {BK, FLAT_BOX_ROWS, 1};
+      int rc = make_tmap_bf16(&ta, act, 3, dims, str, box);
+      if (rc) return rc;
+      uint64_t wd[3] = {(uint64_t)q.Ci, (uint64_t)q.Ko, (uint64_t)NT};
+      uint64_t wst[2] = {(uint64_t)Cp * 2, (uint64_t)q.Ko * Cp * 2};
+      uint32_t wbox[3] = {BK, (uint32_t)f.n_umma, 1};
+      rc = make_tmap_bf16(&tb, wb, 3, wd, wst, wbox);
+      if (rc) return rc;
+      const int64_t total = (int64_t)f.tiles_m * f.tiles_n;
+      dim3 grid((unsigned)std::min<int64_t>(total, kNumSMs));
+      return BN == 128 ? launch_flat<128>(ta, tb, f, grid, s) : launch_flat<64>(ta, tb, f, grid, s);
+    }
+  }
   {
     TcHaloParams h;
     if (halo_mode() >= 1 && halo_plan(q, BN, h)) {
@@ -1776,6 +2089,67 @@ __global__ void __launch_bounds__(256) fold_scale_reduce_kernel(const float* __r
   }
 }
 
+// The same for planes of >= 1024 pixels with W % 4 == 0 (the generator's 32 x 32 and 64 x 64 layers — where the time is):
+// ncu on the scalar kernel above, 96 channels at 64 x 64, N = 256: 592 us for 1.24 GB = 2.1 TB/s — one dependent 4-byte
+// load per thread and iteration cannot cover the HBM latency.  Here a thread owns UNROLL float4 quads per trip: all centre
+// loads of the padded plane (the only ones an interior quad needs) and the float4 loads of x are issued first; quads on
+// the border ring of the plane then add what the replicate padding folds onto them.  One block per (n, c) plane.
+template <int UNROLL>
+__global__ void __launch_bounds__(256) fold_scale_reduce_vec_kernel(const float* __restrict__ dxp, const float* __restrict__ s,
+                                                                     const float* __restrict__ x, float* __restrict__ gx,
+                                                                     float* __restrict__ gs1, int H, int W, int pad,
+                                                                     int64_t rows) {
+  const int Hp = H + 2 * pad, Wp = W + 2 * pad, HW = H * W, Wq = W >> 2, quads = HW >> 2;
+  for (int64_t row = blockIdx.x; row < rows; row += gridDim.x) {
+    const float sv = s[row];
+    const float* src = dxp + row * Hp * Wp;
+    const float4* xr = reinterpret_cast<const float4*>(x + row * HW);
+    float4* gr = reinterpret_cast<float4*>(gx + row * HW);
+    float acc = 0.f;
+    for (int q0 = threadIdx.x; q0 < quads; q0 += 256 * UNROLL) {
+      float4 c[UNROLL], xv[UNROLL];
+#pragma unroll
+      for (int u = 0; u < UNROLL; ++u) {
+        const int q = q0 + u * 256;
+        c[u] = xv[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (q < quads) {
+          const int h = q / Wq, w0 = (q - h * Wq) << 2;
+          const float* p = src + (h + pad) * Wp + w0 + pad;
+          c[u] = make_float4(__ldg(p), __ldg(p + 1), __ldg(p + 2), __ldg(p + 3));
+          if (gs1) xv[u] = __ldg(xr + q);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < UNROLL; ++u) {
+        const int q = q0 + u * 256;
+        if (q >= quads) continue;
+        const int h = q / Wq, w0 = (q - h * Wq) << 2;
+        if (h == 0 || h == H - 1 || w0 == 0 || w0 + 4 == W) {   // a quad on the ring: the general clamp sums
+          int h_lo = h == 0 ? 0 : h + pad, h_hi = h == H - 1 ? Hp - 1 : h + pad;
+          if (H == 1) { h_lo = 0; h_hi = Hp - 1; }
+          float v[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const int w = w0 + j;
+            const int w_lo = w == 0 ? 0 : w + pad, w_hi = w == W - 1 ? Wp - 1 : w + pad;
+            float t = 0.f;
+            for (int a = h_lo; a <= h_hi; ++a)
+              for (int b = w_lo; b <= w_hi; ++b) t += __ldg(src + a * Wp + b);
+            v[j] = t;
+          }
+          c[u] = make_float4(v[0], v[1], v[2], v[3]);
+        }
+        if (gs1) acc = fmaf(c[u].x, xv[u].x, fmaf(c[u].y, xv[u].y, fmaf(c[u].z, xv[u].z, fmaf(c[u].w, xv[u].w, acc))));
+        if (gx) gr[q] = make_float4(c[u].x * sv, c[u].y * sv, c[u].z * sv, c[u].w * sv);
+      }
+    }
+    if (gs1) {
+      acc = block_sum<256>(acc);
+      if (threadIdx.x == 0) gs1[row] = acc;
+    }
+  }
+}
+
 static size_t modconv_bwd_bytes(const ganb200_conv_desc* d) {
   const WgradPlan w = wgrad_plan(d);
   const bool rep = d->pad_mode == 1 && d->pad > 0;
@@ -1790,6 +2164,12 @@ using namespace ganb200;
 extern "C" int ganb200_conv_scatter_mode(int mode) {
   const int prev = scatter_mode();
   if (mode == 0 || mode == 1) g_scatter_mode = mode;
+  return prev;
+}
+
+extern "C" int ganb200_conv_flat_mode(int mode) {
+  const int prev = flat_mode();
+  if (mode >= 0 && mode <= 2) g_flat_mode = mode;
   return prev;
 }
 
@@ -1870,7 +2250,12 @@ static int modconv_bwd_impl(const ganb200_conv_desc* d, const float* x, const fl
     const int64_t rows = (int64_t)d->N * d->C;
     const int HW = d->H * d->W;
     const int pad = (d->pad_mode == 1 && !folded) ? d->pad : 0;
-    if (HW >= 1024) {
+    const bool vec = HW >= 1024 && (d->W & 3) == 0 && ((((uintptr_t)x) | ((uintptr_t)gx)) & 15) == 0;
+    if (vec) {
+      int grid = (int)std::min<int64_t>(rows, (int64_t)kNumSMs * 32);
+      if (HW >= 4096) fold_scale_reduce_vec_kernel<4><<<grid, 256, 0, st>>>(dxp, s, x, gx, gs1, d->H, d->W, pad, rows);
+      else fold_scale_reduce_vec_kernel<1><<<grid, 256, 0, st>>>(dxp, s, x, gx, gs1, d->H, d->W, pad, rows);
+    } else if (HW >= 1024) {
       int grid = (int)std::min<int64_t>(rows, (int64_t)kNumSMs * 32);
       fold_scale_reduce_kernel<false><<<grid, 256, 0, st>>>(dxp, s, x, gx, gs1, d->H, d->W, pad, rows);
     } else {

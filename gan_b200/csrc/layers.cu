@@ -362,7 +362,7 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const float* __restrict__
 
 }  // namespace ganb200
 
-// ---- fused training-mode batch norm for small per-channel populations (N*HW <= BN_SMALL_MAX) -------------------
+// ---- fused training-mode batch norm for small per-channel populations (N*HW <= BN_SMALL_MAX = 8192) -------------------
 // The generator runs 1 888 batch norms per forward, nearly all BatchNorm1d over (256, C) or BatchNorm2d on 5x5 / 3x3 /
 // 1x1 attention maps.  The generic path is memset, memset, mean pass, variance pass, apply: five graph nodes of 1-7 us
 // each (and atomics).  Here one block owns one channel, keeps its N*HW values in registers, and does mean, variance
@@ -373,10 +373,10 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const float* __restrict__
 // (sum dy, sum dy * xhat) backward — so the layer stays ONE launch under data parallelism.  All C blocks must be
 // co-resident (they wait for their partners; the host wrapper checks C against the occupancy).
 namespace ganb200 {
-constexpr int BN_SMALL_THREADS = 128;
 constexpr int BN_SMALL_PER = 32;                                   // values per thread
-constexpr int BN_SMALL_MAX = BN_SMALL_THREADS * BN_SMALL_PER;      // 4096
+constexpr int BN_SMALL_MAX = 256 * BN_SMALL_PER;                   // 8192: 128 threads up to 4096 values, 256 above
 
+template <int BN_SMALL_THREADS>
 __global__ void __launch_bounds__(BN_SMALL_THREADS) bn_small_fwd_kernel(
     const float* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ beta, float* __restrict__ y,
     float* __restrict__ mean_out, float* __restrict__ invstd_out, float* __restrict__ running_mean,
@@ -434,6 +434,7 @@ __global__ void __launch_bounds__(BN_SMALL_THREADS) bn_small_fwd_kernel(
   if (peer.bufs) peer_seq_commit(peer, seq);
 }
 
+template <int BN_SMALL_THREADS>
 __global__ void __launch_bounds__(BN_SMALL_THREADS) bn_small_bwd_kernel(
     const float* __restrict__ gy, const float* __restrict__ x, const float* __restrict__ mean,
     const float* __restrict__ invstd, const float* __restrict__ gamma, float* __restrict__ gx,
@@ -493,16 +494,39 @@ extern "C" int ganb200_bn_small_eligible(int N, int C, int HW) {
   return N > 0 && C > 0 && HW > 0 && (int64_t)N * HW <= BN_SMALL_MAX;
 }
 
+static int bn_small_fwd_launch(const float* x, const float* gamma, const float* beta, float* y, float* mean, float* invstd,
+                               float* running_mean, float* running_var, int64_t* nbt, int N, int C, int HW, float eps,
+                               float momentum, const float* slope, PeerRef peer, cudaStream_t s) {
+  if ((int64_t)N * HW <= 128 * BN_SMALL_PER)
+    bn_small_fwd_kernel<128><<<C, 128, 0, s>>>(x, gamma, beta, y, mean, invstd, running_mean, running_var, nbt, N, C, HW, eps,
+                                               momentum, slope, peer);
+  else
+    bn_small_fwd_kernel<256><<<C, 256, 0, s>>>(x, gamma, beta, y, mean, invstd, running_mean, running_var, nbt, N, C, HW, eps,
+                                               momentum, slope, peer);
+  GB_CHECK_LAUNCH();
+  return 0;
+}
+
+static int bn_small_bwd_launch(const float* gy, const float* x, const float* mean, const float* invstd, const float* gamma,
+                               float* gx, float* ggamma, float* gbeta, int N, int C, int HW, const float* beta,
+                               const float* slope, float* gslope, PeerRef peer, cudaStream_t s) {
+  if ((int64_t)N * HW <= 128 * BN_SMALL_PER)
+    bn_small_bwd_kernel<128><<<C, 128, 0, s>>>(gy, x, mean, invstd, gamma, gx, ggamma, gbeta, N, C, HW, beta, slope, gslope,
+                                               peer);
+  else
+    bn_small_bwd_kernel<256><<<C, 256, 0, s>>>(gy, x, mean, invstd, gamma, gx, ggamma, gbeta, N, C, HW, beta, slope, gslope,
+                                               peer);
+  GB_CHECK_LAUNCH();
+  return 0;
+}
+
 extern "C" int ganb200_bn_small_fwd(const float* x, const float* gamma, const float* beta, float* y, float* mean,
                                     float* invstd, float* running_mean, float* running_var,
                                     int64_t* num_batches_tracked, int N, int C, int HW, float eps, float momentum,
                                     const float* prelu_slope, void* stream) {
-  GB_REQUIRE(ganb200_bn_small_eligible(N, C, HW), GANB200_BAD_SHAPE, "bn_small_fwd: N*HW must be in [1, 4096]");
-  bn_small_fwd_kernel<<<C, BN_SMALL_THREADS, 0, (cudaStream_t)stream>>>(x, gamma, beta, y, mean, invstd, running_mean,
-                                                                        running_var, num_batches_tracked, N, C, HW, eps,
-                                                                        momentum, prelu_slope, PeerRef{nullptr, 0, 1});
-  GB_CHECK_LAUNCH();
-  return 0;
+  GB_REQUIRE(ganb200_bn_small_eligible(N, C, HW), GANB200_BAD_SHAPE, "bn_small_fwd: N*HW must be in [1, 8192]");
+  return bn_small_fwd_launch(x, gamma, beta, y, mean, invstd, running_mean, running_var, num_batches_tracked, N, C, HW, eps,
+                             momentum, prelu_slope, PeerRef{nullptr, 0, 1}, (cudaStream_t)stream);
 }
 
 // channels (= blocks that wait for their partners on the other ranks) the fused sync kernels can keep co-resident
@@ -511,8 +535,8 @@ extern "C" int ganb200_bn_small_sync_max_channels(void) {
   if (cap < 0) {
     int dev = 0, sms = 0, a = 0, b = 0;
     if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess ||
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&a, bn_small_fwd_kernel, BN_SMALL_THREADS, 0) != cudaSuccess ||
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, bn_small_bwd_kernel, BN_SMALL_THREADS, 0) != cudaSuccess)
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&a, bn_small_fwd_kernel<256>, 256, 0) != cudaSuccess ||
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, bn_small_bwd_kernel<256>, 256, 0) != cudaSuccess)
       return 0;
     // half of what fits: other kernels (NCCL on the bucket stream) may hold SM slots
     cap = std::min(std::min(a, b) * sms / 2, kPeerLLSlots);
@@ -525,43 +549,34 @@ extern "C" int ganb200_bn_small_fwd_sync(const float* x, const float* gamma, con
                                          int64_t* num_batches_tracked, int N, int C, int HW, float eps, float momentum,
                                          const float* prelu_slope, const void* peer_bufs_dev, int rank, int world,
                                          void* stream) {
-  GB_REQUIRE(ganb200_bn_small_eligible(N, C, HW), GANB200_BAD_SHAPE, "bn_small_fwd_sync: N*HW must be in [1, 4096]");
+  GB_REQUIRE(ganb200_bn_small_eligible(N, C, HW), GANB200_BAD_SHAPE, "bn_small_fwd_sync: N*HW must be in [1, 8192]");
   GB_REQUIRE(peer_bufs_dev && world >= 1 && world <= kPeerMaxWorld && rank >= 0 && rank < world, GANB200_BAD_ARG,
              "bn_small_fwd_sync: bad peer table / rank / world");
   GB_REQUIRE(C <= ganb200_bn_small_sync_max_channels(), GANB200_BAD_SHAPE, "bn_small_fwd_sync: too many channels to be co-resident");
-  bn_small_fwd_kernel<<<C, BN_SMALL_THREADS, 0, (cudaStream_t)stream>>>(
-      x, gamma, beta, y, mean, invstd, running_mean, running_var, num_batches_tracked, N, C, HW, eps, momentum, prelu_slope,
-      PeerRef{(char* const*)peer_bufs_dev, rank, world});
-  GB_CHECK_LAUNCH();
-  return 0;
+  return bn_small_fwd_launch(x, gamma, beta, y, mean, invstd, running_mean, running_var, num_batches_tracked, N, C, HW, eps,
+                             momentum, prelu_slope, PeerRef{(char* const*)peer_bufs_dev, rank, world}, (cudaStream_t)stream);
 }
 
 extern "C" int ganb200_bn_small_bwd(const float* gy, const float* x, const float* mean, const float* invstd,
                                     const float* gamma, float* gx, float* ggamma, float* gbeta, int N, int C, int HW,
                                     const float* beta, const float* prelu_slope, float* gslope, void* stream) {
-  GB_REQUIRE(ganb200_bn_small_eligible(N, C, HW), GANB200_BAD_SHAPE, "bn_small_bwd: N*HW must be in [1, 4096]");
+  GB_REQUIRE(ganb200_bn_small_eligible(N, C, HW), GANB200_BAD_SHAPE, "bn_small_bwd: N*HW must be in [1, 8192]");
   GB_REQUIRE(!prelu_slope || gslope, GANB200_BAD_ARG, "bn_small_bwd: prelu_slope without gslope");
-  bn_small_bwd_kernel<<<C, BN_SMALL_THREADS, 0, (cudaStream_t)stream>>>(gy, x, mean, invstd, gamma, gx, ggamma, gbeta, N,
-                                                                        C, HW, beta, prelu_slope, gslope,
-                                                                        PeerRef{nullptr, 0, 1});
-  GB_CHECK_LAUNCH();
-  return 0;
+  return bn_small_bwd_launch(gy, x, mean, invstd, gamma, gx, ggamma, gbeta, N, C, HW, beta, prelu_slope, gslope,
+                             PeerRef{nullptr, 0, 1}, (cudaStream_t)stream);
 }
 
 extern "C" int ganb200_bn_small_bwd_sync(const float* gy, const float* x, const float* mean, const float* invstd,
                                          const float* gamma, float* gx, float* ggamma, float* gbeta, int N, int C, int HW,
                                          const float* beta, const float* prelu_slope, float* gslope,
                                          const void* peer_bufs_dev, int rank, int world, void* stream) {
-  GB_REQUIRE(ganb200_bn_small_eligible(N, C, HW), GANB200_BAD_SHAPE, "bn_small_bwd_sync: N*HW must be in [1, 4096]");
+  GB_REQUIRE(ganb200_bn_small_eligible(N, C, HW), GANB200_BAD_SHAPE, "bn_small_bwd_sync: N*HW must be in [1, 8192]");
   GB_REQUIRE(!prelu_slope || gslope, GANB200_BAD_ARG, "bn_small_bwd_sync: prelu_slope without gslope");
   GB_REQUIRE(peer_bufs_dev && world >= 1 && world <= kPeerMaxWorld && rank >= 0 && rank < world, GANB200_BAD_ARG,
              "bn_small_bwd_sync: bad peer table / rank / world");
   GB_REQUIRE(C <= ganb200_bn_small_sync_max_channels(), GANB200_BAD_SHAPE, "bn_small_bwd_sync: too many channels to be co-resident");
-  bn_small_bwd_kernel<<<C, BN_SMALL_THREADS, 0, (cudaStream_t)stream>>>(
-      gy, x, mean, invstd, gamma, gx, ggamma, gbeta, N, C, HW, beta, prelu_slope, gslope,
-      PeerRef{(char* const*)peer_bufs_dev, rank, world});
-  GB_CHECK_LAUNCH();
-  return 0;
+  return bn_small_bwd_launch(gy, x, mean, invstd, gamma, gx, ggamma, gbeta, N, C, HW, beta, prelu_slope, gslope,
+                             PeerRef{(char* const*)peer_bufs_dev, rank, world}, (cudaStream_t)stream);
 }
 
 static dim3 bn_reduce_grid(int N, int C, int HW) {

@@ -440,7 +440,8 @@ class CudaBackend:
                                              count_total, st))
         return y, invstd
 
-    BN_SMALL_MAX = 4096
+    # N*HW up to which the one-launch kernels are used (the kernels take up to 8192; GANB200_BN_SMALL_MAX lowers it)
+    BN_SMALL_MAX = min(8192, int(os.environ.get("GANB200_BN_SMALL_MAX", "8192")))
 
     def bn_small_ok(self, x):
         N, C, HW = _nchw(x)

@@ -851,7 +851,7 @@ class BatchNormTrainFn(Function):
 
 class BnPReluTrainFn(Function):
     """nn.BatchNorm1d/2d (training mode) followed by nn.PReLU(C) as ONE launch each way — the `_fc_bn_act` /
-    `_conv_bn_act` triples of generators/generator_13_5.py:60-66 on small per-channel populations (N*HW <= 4096).
+    `_conv_bn_act` triples of generators/generator_13_5.py:60-66 on small per-channel populations (N*HW <= 8192).
     The batch-norm output is not stored: the backward recomputes it from x, mean, invstd, gamma, beta."""
 
     @staticmethod

@@ -80,6 +80,20 @@ int ganb200_conv2d_route(const ganb200_conv_desc* d, int op);
  * (identical operands and accumulation order per output element).  Returns the previous mode; any other value
  * only queries.  Process-wide; also GANB200_CONV_HALO=0 in the environment. */
 int ganb200_conv_halo_mode(int mode);
+/* tcgen05 engine, forward problems with stride 1 whose taps stay inside the materialised (replicate) padding can run on
+ * the flat kernel — the padded NHWC input read as a [flat pixel][channel] matrix, one contiguous row range per tile and
+ * 64-channel chunk, every tap a 128-byte-row shift of the A descriptor.  1 (default) = where it measured faster than the
+ * halo / per-tap kernels (3x3 layers of up to 96 channels on 64 x 64 planes), 2 = wherever a problem qualifies, 0 =
+ * never.  Same operands and accumulation order per output element as the halo kernel.  Returns the previous mode; any
+ * other value only queries.  Process-wide; also GANB200_CONV_FLAT in the environment. */
+int ganb200_conv_flat_mode(int mode);
+/* Hardware self-test behind the tcgen05 engine's tap addressing (csrc/probe.cu; no reference counterpart): loads a
+ * [rows][64] bf16 box (SWIZZLE_128B) with TMA and returns out[128][n] = a[shift : shift + 128] * b^T with the A
+ * descriptor's start address shifted by `shift` 128-byte rows — any shift, not only multiples of the 8-row swizzle atom.
+ * base_offset_mode 0 leaves the descriptor's base_offset field 0, 1 sets it to (start >> 7) & 7.  rows <= 256,
+ * n in {32, 64}. */
+int ganb200_tc_shift_probe(const void* a, const void* b, float* out, int rows, int n, int shift, int base_offset_mode,
+                           void* stream);
 /* tcgen05 engine, dgrad of replicate-padded convolutions: 0 (default) = padded fp32 domain in the workspace, then a fold
  * pass — every sum in a fixed order, the result is reproducible bit for bit; 1 = the MMA epilogue scatters each
  * padded-domain value straight into the clamped pixel of the unpadded plane (plain stores inside, red.global.add on the
@@ -188,7 +202,7 @@ int ganb200_bn_bwd_apply(const float* gy, const float* x, const float* mean, con
                          const float* sum_gy, const float* sum_gy_xhat, float* gx, float* ggamma, float* gbeta,
                          int N, int C, int HW, int64_t count_total, void* stream);
 
-/* Fused training-mode batch norm for small per-channel populations (N*HW <= 4096: every BatchNorm1d and the
+/* Fused training-mode batch norm for small per-channel populations (N*HW <= 8192: every BatchNorm1d and the
  * BatchNorm2d of the 5x5 / 3x3 / 1x1 attention maps, generator_13_5.py:60-66,100-118,212-214): ONE launch computes the
  * batch mean and biased variance (two-pass), y, save_mean / save_invstd, the running statistics (unbiased variance,
  * momentum) and num_batches_tracked += 1; the backward ONE launch computes dx, dgamma, dbeta.  Same results as

@@ -180,7 +180,7 @@ class RefBackend:
 
     def bn_small_ok(self, x):
         n = x.numel() // x.shape[1] if x.dim() > 1 else 1
-        return n <= 4096
+        return n <= 8192
 
     def bn_small_fwd(self, x, gamma, beta, running_mean, running_var, eps, momentum, nbt=None, slope=None):
         mean, var = self.bn_stats(x)

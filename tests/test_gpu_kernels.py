@@ -69,6 +69,10 @@ CONV_CASES = [
     (4, 192, 16, 16, 96, 3, 1, 1, 1),    # k3 @ 16x16
     (3, 72, 20, 36, 200, 3, 1, 1, 0),    # halo kernel: ragged plane, two output-channel tiles, zero pad
     (2, 130, 33, 17, 70, 5, 1, 2, 1),    # halo kernel: odd plane, three channel chunks, k5
+    (2, 64, 64, 64, 64, 3, 1, 1, 1),     # flat kernel: the critic's full-resolution 3x3
+    (2, 130, 33, 40, 70, 5, 1, 2, 1),    # flat kernel: ragged plane, three channel chunks, K = 70 in a 128-wide tile
+    (1, 48, 40, 36, 200, 3, 1, 1, 1),    # flat kernel: two output-channel tiles
+    (2, 390, 64, 64, 96, 1, 1, 0, 1),    # flat kernel: 1x1 on the wide concat at full resolution
     (2, 24, 40, 24, 16, 7, 1, 3, 1),     # halo kernel: k7
     (2, 64, 32, 32, 32, 4, 2, 1, 0),     # ConvTranspose2d(k4, s2, p1) as dgrad: 2x2 tap phases at 32x32 (halo eligible)
     (3, 40, 21, 64, 72, 5, 1, 2, 1),     # row-ring wgrad: 63 rows over 3 images (ranges cross image boundaries), K > 64
@@ -148,11 +152,33 @@ def bf16r(t):
     return t.to(torch.bfloat16).to(torch.float32)
 
 
-@pytest.fixture(params=[1, 0], ids=["halo", "per-tap"])
+@pytest.fixture(params=[(1, 2), (1, 0), (0, 0)], ids=["flat", "halo", "per-tap"])
 def halo_mode(cu, request):
-    prev = cu.lib.ganb200_conv_halo_mode(request.param)
+    """which tcgen05 forward kernel serves the problems that qualify for more than one: (halo mode, flat mode)"""
+    prev = cu.lib.ganb200_conv_halo_mode(request.param[0])
+    prev_flat = cu.lib.ganb200_conv_flat_mode(request.param[1])
     yield request.param
     cu.lib.ganb200_conv_halo_mode(prev)
+    cu.lib.ganb200_conv_flat_mode(prev_flat)
+
+
+def test_tcgen05_operand_start_may_be_shifted_by_single_rows(cu):
+    """the flat convolution kernel reads every filter tap from one shared-memory box through an A descriptor whose start is
+    shifted by whole 128-byte rows — not multiples of the 8-row SWIZZLE_128B atom.  Hardware check (csrc/probe.cu)."""
+    torch.manual_seed(0)
+    rows, n = 256, 64
+    a = torch.randn(rows, 64).to(torch.bfloat16)
+    b = torch.randn(n, 64).to(torch.bfloat16)
+    ag, bg = a.cuda(), b.cuda()
+    out = torch.empty(128, n, device="cuda")
+    st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    for shift in (0, 8, 1, 3, 7, 9, 66, 69, 127, 128):
+        out.zero_()
+        rc = cu.lib.ganb200_tc_shift_probe(ctypes.c_void_p(ag.data_ptr()), ctypes.c_void_p(bg.data_ptr()),
+                                           ctypes.c_void_p(out.data_ptr()), rows, n, shift, 0, st)
+        assert rc == 0
+        want = a[shift:shift + 128].float() @ b.float().t()
+        assert rel(out, want) < 1e-5, shift
 
 
 @pytest.mark.parametrize("case", CONV_CASES)
@@ -271,10 +297,11 @@ def test_batchnorm(cu, ref, shape):
         assert rel(a, b) < 1e-4
 
 
-@pytest.mark.parametrize("shape", [(256, 256), (4, 48), (256, 12, 4, 4), (7, 33, 5, 5), (1024, 3, 2, 2), (6, 5, 1, 1)])
+@pytest.mark.parametrize("shape", [(256, 256), (4, 48), (256, 12, 4, 4), (7, 33, 5, 5), (1024, 3, 2, 2), (6, 5, 1, 1),
+                                   (256, 12, 5, 5), (8192, 2)])
 @pytest.mark.parametrize("affine", [True, False])
 def test_batchnorm_fused_small(cu, ref, shape, affine):
-    """one-launch training-mode batch norm (N*HW <= 4096) against the oracle's stats + apply / reduce + apply"""
+    """one-launch training-mode batch norm (N*HW <= 8192; 256-thread variant above 4096) against the oracle's stats + apply / reduce + apply"""
     torch.manual_seed(16)
     x, gy = rnd(*shape) * 2 + 0.5, rnd(*shape)
     C = shape[1]
