@@ -995,7 +995,16 @@ int make_tmap_bf16(CUtensorMap* m, const void* base, int rank, const uint64_t* d
 
 static inline int pow2ceil(int v) { int p = 1; while (p < v) p <<= 1; return p; }
 static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
-static inline int cpad(int c) { return (c + 7) / 8 * 8; }
+// Channel pitch of the packed (bf16, channels-last) operands.  Tensors of more than 32 channels get whole 128-byte rows
+// (64 channels): TMA fills shared memory from rows whose global pitch is a multiple of 128 bytes at about twice the
+// rate of the 96-byte rows a 48-channel tensor would have (tools/flat_bench.py, profiles/r02_flat_kernel_experiments.txt:
+// the activation stage of a 64-channel layer arrives at 7.2 TB/s chip-wide, that of a 48-channel layer at 3.7 TB/s).
+// GANB200_CPAD64=0: multiples of 8 as in round 1.
+static inline int cpad(int c) {
+  static int wide = -1;
+  if (wide < 0) { const char* e = getenv("GANB200_CPAD64"); wide = (e && e[0] == '0') ? 0 : 1; }
+  return (wide && c > 32) ? (c + 63) / 64 * 64 : (c + 7) / 8 * 8;
+}
 static inline void* align_ws(void* ws) { return (void*)(((uintptr_t)ws + 1023) & ~uintptr_t(1023)); }
 
 // the generic problem fprop and dgrad map to: out[n,ko,(p,q)] = alpha*oscale*sum_{tap,ci} W[tap][ko][ci] *
