@@ -770,8 +770,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_halo_kernel(const __gri
 // Warps: 0 = activation producer, 1 = MMA issuer, 2-5 = epilogue, 6 = weight producer (its own ring, so that the next
 // tile's activations are requested while the current tile's weight boxes still stream).
 constexpr int FLAT_THREADS = 224;
-constexpr int FLAT_BOX_ROWS = 64;                           // rows per TMA box (8 KB)
+constexpr int FLAT_BOX_ROWS = 32;                           // rows per small TMA box (4 KB): the tail of a stage
 constexpr int FLAT_BOX_BYTES = FLAT_BOX_ROWS * 128;
+constexpr int FLAT_BIG_ROWS = 256;                          // rows per large TMA box (32 KB, the largest box there is):
+constexpr int FLAT_BIG_BYTES = FLAT_BIG_ROWS * 128;         // every TMA issue costs the producer ~0.1 us (measured)
 constexpr int FLAT_MAX_B_STAGES = 16;                       // weight ring (barrier slots)
 constexpr int FLAT_FIXED_BYTES = 1024 /*align*/ + 512 /*barriers*/;
 
@@ -779,8 +781,8 @@ struct TcFlatParams {
   int N, K, P, Q, C;
   int R, S, dh0, dw0;
   int Hp, Wp;            // padded input plane
-  int mt;                // sub-tiles (accumulators) of 128 flat pixels per CTA tile
-  int nbox;              // 64-row boxes per activation stage
+  int mt;                // sub-tiles (accumulators) of 128 flat pixels per CTA tile: 1, 2 or (64-wide tiles) 4
+  int nbig, nbox;        // 256-row and 32-row boxes per activation stage
   int a_stages;
   int b_stages;          // weight ring: boxes of n_umma * 128 bytes; the fill is latency-bound, so as deep as fits
   int tiles_img;         // tiles per image = ceil(P * Wp / (mt * 128))
@@ -796,13 +798,14 @@ struct TcFlatParams {
 
 template <int BN>
 __global__ void __launch_bounds__(FLAT_THREADS, 1) tc_conv_flat_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                                       const __grid_constant__ CUtensorMap tmA32,
                                                                        const __grid_constant__ CUtensorMap tmB,
                                                                        const TcFlatParams p) {
-  constexpr int MT_MAX = 2;
+  constexpr int MT_MAX = 256 / BN;             // accumulators per tile: 2 x MT_MAX x BN = 512 TMEM columns
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int SA = p.a_stages, SB = p.b_stages;
-  const int a_bytes = p.nbox * FLAT_BOX_BYTES;
+  const int a_bytes = p.nbig * FLAT_BIG_BYTES + p.nbox * FLAT_BOX_BYTES;
   const int b_bytes = p.n_umma * 128;            // a multiple of 1024 (n_umma is a multiple of 8)
   uint8_t* smA = smem;
   uint8_t* smB = smem + SA * a_bytes;
@@ -829,6 +832,7 @@ __global__ void __launch_bounds__(FLAT_THREADS, 1) tc_conv_flat_kernel(const __g
 
   if (threadIdx.x == 0) {
     prefetch_tmap(&tmA);
+    prefetch_tmap(&tmA32);
     prefetch_tmap(&tmB);
     for (int i = 0; i < SA; ++i) { mbar_init(&fullA[i], 1); mbar_init(&emptyA[i], 1); }
     for (int i = 0; i < SB; ++i) { mbar_init(&fullB[i], 1); mbar_init(&emptyB[i], 1); }
@@ -854,8 +858,12 @@ __global__ void __launch_bounds__(FLAT_THREADS, 1) tc_conv_flat_kernel(const __g
         mbar_wait(&emptyA[sa], pa ^ 1);
         if (leader) {
           mbar_expect_tx(&fullA[sa], (uint32_t)a_bytes);
-          for (int b = 0; b < p.nbox; ++b)
-            tma_load_3d(smA + sa * a_bytes + b * FLAT_BOX_BYTES, &tmA, &fullA[sa], kc * BK, row0 + b * FLAT_BOX_ROWS, 0);
+          uint8_t* dst = smA + sa * a_bytes;
+          int row = row0;
+          for (int b = 0; b < p.nbig; ++b, dst += FLAT_BIG_BYTES, row += FLAT_BIG_ROWS)
+            tma_load_3d(dst, &tmA, &fullA[sa], kc * BK, row, 0);
+          for (int b = 0; b < p.nbox; ++b, dst += FLAT_BOX_BYTES, row += FLAT_BOX_ROWS)
+            tma_load_3d(dst, &tmA32, &fullA[sa], kc * BK, row, 0);
         }
         if (++sa == SA) { sa = 0; pa ^= 1; }
       }
@@ -904,9 +912,11 @@ __global__ void __launch_bounds__(FLAT_THREADS, 1) tc_conv_flat_kernel(const __g
             const uint64_t adesc0 = make_smem_desc_sw128(a_base + (uint32_t)(r * p.Wp + s) * 128u, 16, 1024);
             const uint32_t fresh = (kc == 0 && s == 0 && r == 0) ? 0u : 1u;
             if (leader) {
-              mma_chain_n(ksub, tmem_d, adesc0, bdesc, idesc, fresh, 2u);
-              if (p.mt == 2)
-                mma_chain_n(ksub, tmem_d + (uint32_t)BN, adesc0 + (uint64_t)((TILE_M * 128) >> 4), bdesc, idesc, fresh, 2u);
+#pragma unroll
+              for (int j = 0; j < MT_MAX; ++j)
+                if (j < p.mt)
+                  mma_chain_n(ksub, tmem_d + (uint32_t)(j * BN), adesc0 + (uint64_t)((j * TILE_M * 128) >> 4), bdesc, idesc,
+                              fresh, 2u);
               mma_commit(&emptyB[sb]);
             }
             if (++sb == SB) { sb = 0; pb ^= 1; }
@@ -1091,14 +1101,16 @@ static bool halo_plan(const TcProblem& q, int BN, TcHaloParams& h) {
   return true;
 }
 
-// 1 (default) = the flat kernel where it measured faster than the halo / per-tap kernels (tools/flat_bench.py, B = 256:
-// the generator's 3x3 layers of up to 96 channels on 64 x 64 planes, 1.03-1.07x); 2 = wherever a forward problem
-// qualifies (parity tests); 0 = never.  GANB200_CONV_FLAT or ganb200_conv_flat_mode().
-// What the experiment showed (profiles/r02_flat_kernel_experiments.txt): the 48-channel layers are NOT bound by the bytes
-// they move from L2 — with a quarter of the activation fill (this kernel), or with the weight ring 13 deep instead of 4,
-// or with no weight traffic at all, the launch takes the same time to 5 %; with the MMAs removed it still takes 60 % of
-// it.  The floor is the latency of the per-tile activation stage (two 72 KB stages in flight move ~3 TB/s chip-wide), on
-// top of which the shared-memory-bound N = 48 MMAs (4 KB of A per 24-cycle instruction) add instead of overlapping.
+// 1 (default) = the flat kernel where it measured faster than the halo / per-tap kernels (the rule is at the call site in
+// run_problem); 2 = wherever a forward problem qualifies (parity tests); 0 = never.  GANB200_CONV_FLAT or
+// ganb200_conv_flat_mode().
+// What the experiments showed (profiles/r02_flat_kernel_experiments.txt): the 48-channel layers are NOT bound by the bytes
+// they move from L2 — with a quarter of the activation fill (this kernel), with the weight ring 13 deep instead of 4, with
+// no weight traffic at all, with 2, 3 or 4 activation stages in flight, with 32-, 64- or 256-row TMA boxes, the launch
+// takes the same time to 5 %; with the MMAs removed it still takes 60 % of it.  What it does follow is the NUMBER OF CTA
+// TILES: time = (shared-memory-bound MMA time: 4 KB of A per 24-cycle N = 48 instruction) + ~4 us per tile and CTA.  Four
+// accumulators per tile (512 pixels; 64-wide channel tiles leave the TMEM columns for it) instead of two is what made this
+// kernel 10-14 % faster than the halo kernel on those layers.
 static int g_flat_mode = -1;
 static int flat_mode() {
   if (g_flat_mode < 0) {
@@ -1134,10 +1146,11 @@ static bool flat_plan(const TcProblem& q, int BN, TcFlatParams& f) {
   const int room = HALO_SMEM_MAX - FLAT_FIXED_BYTES;
   int best_mt = 0;
   double best_cost = 0;
-  for (int mt = 2; mt >= 1; --mt) {
+  for (int mt = 256 / BN; mt >= 1; mt >>= 1) {
     const int rows = mt * TILE_M + (R - 1) * Wp + (S - 1);
-    const int nbox = ceil_div(rows, FLAT_BOX_ROWS);
-    const int a_bytes = nbox * FLAT_BOX_BYTES;
+    const int nbig = rows / FLAT_BIG_ROWS;
+    const int nbox = ceil_div(rows - nbig * FLAT_BIG_ROWS, FLAT_BOX_ROWS);
+    const int a_bytes = nbig * FLAT_BIG_BYTES + nbox * FLAT_BOX_BYTES;
     // two activation stages; the rest goes to the weight ring (its boxes are small and the ring is latency-bound: 4
     // stages of 6 KB kept the 48-channel 5x5 layers at 23 % tensor pipe whatever the activation traffic was); what is
     // left after 16 weight stages buys a third activation stage
@@ -1146,10 +1159,12 @@ static bool flat_plan(const TcProblem& q, int BN, TcFlatParams& f) {
     if (b_stages < 4) continue;
     if (b_stages == FLAT_MAX_B_STAGES && room - a_stages * a_bytes - b_stages * b_bytes >= a_bytes) a_stages = 3;
     const int tiles_img = ceil_div(q.Po * Wp, mt * TILE_M);
-    // cost per image: bytes filled + MMA work expressed in bytes (one 128-pixel MMA row block ~ 2 KB of fill time)
-    const double cost = (double)tiles_img * (a_bytes + (double)R * S * b_bytes + mt * 2048.0 * R * S / 4.0);
+    // measured (tools/flat_bench.py with 1, 2 and 4 sub-tiles per tile and 2, 3 and 4 activation stages; 48 and 96
+    // channels; profiles/r02_flat_kernel_experiments.txt): a launch costs its MMA time plus ~4 us per CTA tile, whatever
+    // the number of stages in flight, the box size or the number of TMA issues — so the fewest, largest tiles win
+    const double cost = (double)tiles_img * (4.0 + 1.6 * mt);
     if (!best_mt || cost < best_cost) {
-      best_mt = mt; best_cost = cost; f.nbox = nbox; f.a_stages = a_stages; f.b_stages = b_stages; f.tiles_img = tiles_img;
+      best_mt = mt; best_cost = cost; f.nbig = nbig; f.nbox = nbox; f.a_stages = a_stages; f.b_stages = b_stages; f.tiles_img = tiles_img;
     }
   }
   if (!best_mt) return false;
@@ -1163,15 +1178,17 @@ static bool flat_plan(const TcProblem& q, int BN, TcFlatParams& f) {
 }
 
 template <int BN>
-static int launch_flat(const CUtensorMap& ta, const CUtensorMap& tb, const TcFlatParams& p, dim3 grid, cudaStream_t s) {
+static int launch_flat(const CUtensorMap& ta, const CUtensorMap& ta32, const CUtensorMap& tb, const TcFlatParams& p,
+                       dim3 grid, cudaStream_t s) {
   static bool configured = false;
   if (!configured) {
     GB_CHECK_CUDA(cudaFuncSetAttribute(tc_conv_flat_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        HALO_SMEM_MAX));
     configured = true;
   }
-  const int smem = FLAT_FIXED_BYTES + p.b_stages * p.n_umma * 128 + p.a_stages * p.nbox * FLAT_BOX_BYTES;
-  tc_conv_flat_kernel<BN><<<grid, FLAT_THREADS, smem, s>>>(ta, tb, p);
+  const int smem = FLAT_FIXED_BYTES + p.b_stages * p.n_umma * 128 +
+                   p.a_stages * (p.nbig * FLAT_BIG_BYTES + p.nbox * FLAT_BOX_BYTES);
+  tc_conv_flat_kernel<BN><<<grid, FLAT_THREADS, smem, s>>>(ta, ta32, tb, p);
   GB_CHECK_LAUNCH();
   return 0;
 }
@@ -1241,14 +1258,19 @@ static int run_problem(const TcProblem& q, const __nv_bfloat16* act, const float
   const int BN = q.Ko > 64 ? 128 : 64;   // 64 < Ko < 128 (96, 108): one 128-wide tile, the activations are read once
   {
     TcFlatParams f;
-    const bool flat_wins = q.taps.n == 9 && q.Ci <= 96 && q.Ko <= 96 && q.Ci % 64 != 0 && q.Qo >= 64;
+    // where it measured faster (tools/flat_bench.py, B = 256): 64-wide channel tiles on 64 x 64 planes (four sub-tiles per
+    // CTA tile: 48 -> 48 5x5 1.10x, 3x3 1.14x, 48 -> 54 1.10x, ToRGB 108 -> 3 1.14x, the critic's 64 -> 64 1.02x) and
+    // the 3x3 layers of up to 96 channels
+    const bool flat_wins = q.Qo >= 64 && (q.Ko <= 64 || (q.taps.n == 9 && q.Ci <= 96 && q.Ko <= 96));
     if (halo_mode() >= 1 && (flat_mode() == 2 || (flat_mode() == 1 && flat_wins)) && flat_plan(q, BN, f)) {
       f.alpha = q.alpha; f.oscale = out_scale; f.bias = bias; f.y = out;
-      CUtensorMap ta, tb;
+      CUtensorMap ta, ta32, tb;
       uint64_t dims[3] = {(uint64_t)q.Ci, (uint64_t)q.N * Hp * Wp, 1};
       uint64_t str[2] = {(uint64_t)Cp * 2, (uint64_t)q.N * Hp * Wp * Cp * 2};
-      uint32_t box[3] = {BK, FLAT_BOX_ROWS, 1};
+      uint32_t box[3] = {BK, FLAT_BIG_ROWS, 1}, box32[3] = {BK, FLAT_BOX_ROWS, 1};
       int rc = make_tmap_bf16(&ta, act, 3, dims, str, box);
+      if (rc) return rc;
+      rc = make_tmap_bf16(&ta32, act, 3, dims, str, box32);
       if (rc) return rc;
       uint64_t wd[3] = {(uint64_t)q.Ci, (uint64_t)q.Ko, (uint64_t)NT};
       uint64_t wst[2] = {(uint64_t)Cp * 2, (uint64_t)q.Ko * Cp * 2};
@@ -1257,7 +1279,7 @@ static int run_problem(const TcProblem& q, const __nv_bfloat16* act, const float
       if (rc) return rc;
       const int64_t total = (int64_t)f.tiles_m * f.tiles_n;
       dim3 grid((unsigned)std::min<int64_t>(total, kNumSMs));
-      return BN == 128 ? launch_flat<128>(ta, tb, f, grid, s) : launch_flat<64>(ta, tb, f, grid, s);
+      return BN == 128 ? launch_flat<128>(ta, ta32, tb, f, grid, s) : launch_flat<64>(ta, ta32, tb, f, grid, s);
     }
   }
   {

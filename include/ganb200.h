@@ -83,8 +83,8 @@ int ganb200_conv_halo_mode(int mode);
 /* tcgen05 engine, forward problems with stride 1 whose taps stay inside the materialised (replicate) padding can run on
  * the flat kernel — the padded NHWC input read as a [flat pixel][channel] matrix, one contiguous row range per tile and
  * 64-channel chunk, every tap a 128-byte-row shift of the A descriptor.  1 (default) = where it measured faster than the
- * halo / per-tap kernels (3x3 layers of up to 96 channels on 64 x 64 planes), 2 = wherever a problem qualifies, 0 =
- * never.  Same operands and accumulation order per output element as the halo kernel.  Returns the previous mode; any
+ * halo / per-tap kernels (64 x 64 planes: layers of up to 64 output channels, 3x3 layers of up to 96 channels), 2 =
+ * wherever a problem qualifies, 0 = never.  Same operands and accumulation order per output element as the halo kernel.  Returns the previous mode; any
  * other value only queries.  Process-wide; also GANB200_CONV_FLAT in the environment. */
 int ganb200_conv_flat_mode(int mode);
 /* Hardware self-test behind the tcgen05 engine's tap addressing (csrc/probe.cu; no reference counterpart): loads a
