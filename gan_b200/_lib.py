@@ -54,7 +54,9 @@ SIGNATURES = {
     "ganb200_conv_halo_mode": (c_int, [c_int]),
     "ganb200_conv_scatter_mode": (c_int, [c_int]),
     "ganb200_conv_flat_mode": (c_int, [c_int]),
+    "ganb200_conv_flat_trace": (c_int, [P]),
     "ganb200_tc_shift_probe": (c_int, [P, P, P, c_int, c_int, c_int, c_int, P]),
+    "ganb200_tc_shift_probe_m": (c_int, [P, P, P, c_int, c_int, c_int, c_int, c_int, P]),
     "ganb200_conv2d_route": (c_int, [_DESC_P, c_int]),
     "ganb200_conv2d_fprop": (c_int, [_DESC_P, P, P, P, P, P, P, P, c_size_t, P]),
     "ganb200_conv2d_dgrad": (c_int, [_DESC_P, P, P, P, P, P, P, c_size_t, P]),

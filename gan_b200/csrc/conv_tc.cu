@@ -793,8 +793,15 @@ struct TcFlatParams {
   const float* oscale;
   const float* bias;
   float* y;
+  // diagnosis (ganb200_conv_flat_trace): clock64 stamps of CTA 0's pipeline roles, [role][tile < 32][4]; null = off
+  unsigned long long* trace;
   unsigned char tap_idx[MAX_TAPS];  // packed-weight index of grid point r * S + s
 };
+constexpr int FLAT_TRACE_TILES = 32;
+__device__ __forceinline__ void flat_stamp(unsigned long long* trace, int role, int tile_local, int k) {
+  if (trace && blockIdx.x == 0 && tile_local < FLAT_TRACE_TILES)
+    trace[(role * FLAT_TRACE_TILES + tile_local) * 4 + k] = (unsigned long long)clock64();
+}
 
 template <int BN>
 __global__ void __launch_bounds__(FLAT_THREADS, 1) tc_conv_flat_kernel(const __grid_constant__ CUtensorMap tmA,
@@ -848,14 +855,16 @@ __global__ void __launch_bounds__(FLAT_THREADS, 1) tc_conv_flat_kernel(const __g
   if (warp == 0) {
     // activation producer
     const bool leader = elect_one();
-    int sa = 0;
+    int sa = 0, local = 0;
     uint32_t pa = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++local) {
       int k0, ti, n;
       decode(tile, k0, ti, n);
       const int row0 = n * p.Hp * p.Wp + ti * tile_px + p.dh0 * p.Wp + p.dw0;
       for (int kc = 0; kc < k_chunks; ++kc) {
+        if (leader && kc == 0) flat_stamp(p.trace, 0, local, 0);
         mbar_wait(&emptyA[sa], pa ^ 1);
+        if (leader && kc == 0) flat_stamp(p.trace, 0, local, 1);
         if (leader) {
           mbar_expect_tx(&fullA[sa], (uint32_t)a_bytes);
           uint8_t* dst = smA + sa * a_bytes;
@@ -896,13 +905,16 @@ __global__ void __launch_bounds__(FLAT_THREADS, 1) tc_conv_flat_kernel(const __g
     uint32_t pa = 0, pb = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++local) {
       const int acc = local & 1;
+      if (leader) flat_stamp(p.trace, 1, local, 0);
       mbar_wait(&tmem_empty[acc], ((local >> 1) & 1) ^ 1);
       tc_fence_after();
+      if (leader) flat_stamp(p.trace, 1, local, 1);
       const uint32_t tmem_d = tmem_base + (uint32_t)(acc * MT_MAX * BN);
       for (int kc = 0; kc < k_chunks; ++kc) {
         const int ksub = min(BK / 16, (p.C - kc * BK + 15) / 16);
         mbar_wait(&fullA[sa], pa);
         tc_fence_after();
+        if (leader && kc == 0) flat_stamp(p.trace, 1, local, 2);
         const uint32_t a_base = smem_u32(smA + sa * a_bytes);
         for (int s = 0; s < p.S; ++s)
           for (int r = 0; r < p.R; ++r) {
@@ -925,6 +937,7 @@ __global__ void __launch_bounds__(FLAT_THREADS, 1) tc_conv_flat_kernel(const __g
         if (++sa == SA) { sa = 0; pa ^= 1; }
       }
       if (leader) mma_commit(&tmem_full[acc]);
+      if (leader) flat_stamp(p.trace, 1, local, 3);
     }
     __syncwarp();
   } else {
@@ -938,8 +951,10 @@ __global__ void __launch_bounds__(FLAT_THREADS, 1) tc_conv_flat_kernel(const __g
       decode(tile, k0, ti, n);
       const float* osc = p.oscale ? p.oscale + (int64_t)n * p.K : nullptr;
       const int acc = local & 1;
+      if (warp == 2 && lane == 0) flat_stamp(p.trace, 2, local, 0);
       mbar_wait(&tmem_full[acc], (local >> 1) & 1);
       tc_fence_after();
+      if (warp == 2 && lane == 0) flat_stamp(p.trace, 2, local, 1);
       for (int j = 0; j < p.mt; ++j) {
         const int o = ti * tile_px + j * TILE_M + m;      // flat position inside the image's padded plane
         const int yy = o / p.Wp, xx = o - yy * p.Wp;
@@ -960,6 +975,7 @@ __global__ void __launch_bounds__(FLAT_THREADS, 1) tc_conv_flat_kernel(const __g
       }
       tc_fence_before();
       __syncwarp();
+      if (warp == 2 && lane == 0) flat_stamp(p.trace, 2, local, 2);
       if (lane == 0) mbar_arrive(&tmem_empty[acc]);
     }
   }
@@ -1111,6 +1127,7 @@ static bool halo_plan(const TcProblem& q, int BN, TcHaloParams& h) {
 // TILES: time = (shared-memory-bound MMA time: 4 KB of A per 24-cycle N = 48 instruction) + ~4 us per tile and CTA.  Four
 // accumulators per tile (512 pixels; 64-wide channel tiles leave the TMEM columns for it) instead of two is what made this
 // kernel 10-14 % faster than the halo kernel on those layers.
+static unsigned long long* g_flat_trace = nullptr;   // ganb200_conv_flat_trace
 static int g_flat_mode = -1;
 static int flat_mode() {
   if (g_flat_mode < 0) {
@@ -1263,7 +1280,7 @@ static int run_problem(const TcProblem& q, const __nv_bfloat16* act, const float
     // the 3x3 layers of up to 96 channels
     const bool flat_wins = q.Qo >= 64 && (q.Ko <= 64 || (q.taps.n == 9 && q.Ci <= 96 && q.Ko <= 96));
     if (halo_mode() >= 1 && (flat_mode() == 2 || (flat_mode() == 1 && flat_wins)) && flat_plan(q, BN, f)) {
-      f.alpha = q.alpha; f.oscale = out_scale; f.bias = bias; f.y = out;
+      f.alpha = q.alpha; f.oscale = out_scale; f.bias = bias; f.y = out; f.trace = g_flat_trace;
       CUtensorMap ta, ta32, tb;
       uint64_t dims[3] = {(uint64_t)q.Ci, (uint64_t)q.N * Hp * Wp, 1};
       uint64_t str[2] = {(uint64_t)Cp * 2, (uint64_t)q.N * Hp * Wp * Cp * 2};
@@ -2196,6 +2213,11 @@ extern "C" int ganb200_conv_scatter_mode(int mode) {
   const int prev = scatter_mode();
   if (mode == 0 || mode == 1) g_scatter_mode = mode;
   return prev;
+}
+
+extern "C" int ganb200_conv_flat_trace(unsigned long long* device_buf) {
+  g_flat_trace = device_buf;
+  return 0;
 }
 
 extern "C" int ganb200_conv_flat_mode(int mode) {

@@ -19,7 +19,8 @@ int make_tmap_bf16(CUtensorMap* m, const void* base, int rank, const uint64_t* d
 
 __global__ void __launch_bounds__(128, 1) tc_shift_probe_kernel(const __grid_constant__ CUtensorMap tmA,
                                                                 const __grid_constant__ CUtensorMap tmB, float* out,
-                                                                int rows, int n, int shift, int base_offset_mode) {
+                                                                int rows, int n, int shift, int base_offset_mode,
+                                                                int m) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* smA = smem;                        // rows * 128 B
@@ -50,7 +51,7 @@ __global__ void __launch_bounds__(128, 1) tc_shift_probe_kernel(const __grid_con
       uint64_t adesc = make_smem_desc_sw128(a_addr, 16, 1024);
       if (base_offset_mode) adesc |= (uint64_t)((a_addr >> 7) & 7u) << 49;
       const uint64_t bdesc = make_smem_desc_sw128(smem_u32(smB), 16, 1024);
-      mma_chain<4>(tmem_base, adesc, bdesc, make_idesc_bf16(128, n, 0, 0), 0u, 2u);
+      mma_chain<4>(tmem_base, adesc, bdesc, make_idesc_bf16(m, n, 0, 0), 0u, 2u);
       mma_commit(&bars[1]);
     }
     __syncwarp();
@@ -74,8 +75,17 @@ __global__ void __launch_bounds__(128, 1) tc_shift_probe_kernel(const __grid_con
 using namespace ganb200;
 
 // a: bf16 [rows][64] (rows <= 256, rows >= shift + 128), b: bf16 [n][64] (n = 32 or 64), out: fp32 [128][n]
+// ganb200_tc_shift_probe_m: the same with an M = 64 instruction (m = 64): `out` still receives all 128 TMEM lanes, which
+// shows where the tensor core puts the 64 accumulator rows (lanes the MMA does not write keep what they held).
+extern "C" int ganb200_tc_shift_probe_m(const void* a, const void* b, float* out, int rows, int n, int shift,
+                                        int base_offset_mode, int m, void* stream);
 extern "C" int ganb200_tc_shift_probe(const void* a, const void* b, float* out, int rows, int n, int shift,
                                       int base_offset_mode, void* stream) {
+  return ganb200_tc_shift_probe_m(a, b, out, rows, n, shift, base_offset_mode, 128, stream);
+}
+extern "C" int ganb200_tc_shift_probe_m(const void* a, const void* b, float* out, int rows, int n, int shift,
+                                        int base_offset_mode, int m, void* stream) {
+  GB_REQUIRE(m == 64 || m == 128, GANB200_BAD_ARG, "tc_shift_probe: m must be 64 or 128");
   GB_REQUIRE(a && b && out, GANB200_BAD_ARG, "tc_shift_probe: null argument");
   GB_REQUIRE(rows >= shift + 128 && rows <= 256 && shift >= 0 && (n == 32 || n == 64), GANB200_BAD_SHAPE,
              "tc_shift_probe: rows in [shift + 128, 256], n in {32, 64}");
@@ -90,7 +100,7 @@ extern "C" int ganb200_tc_shift_probe(const void* a, const void* b, float* out, 
   if (rc) return rc;
   const int smem = 256 * 128 + 64 * 128 + 64 + 1024;
   GB_CHECK_CUDA(cudaFuncSetAttribute(tc_shift_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-  tc_shift_probe_kernel<<<1, 128, smem, (cudaStream_t)stream>>>(ta, tb, out, rows, n, shift, base_offset_mode);
+  tc_shift_probe_kernel<<<1, 128, smem, (cudaStream_t)stream>>>(ta, tb, out, rows, n, shift, base_offset_mode, m);
   GB_CHECK_LAUNCH();
   return 0;
 }

@@ -87,6 +87,12 @@ int ganb200_conv_halo_mode(int mode);
  * wherever a problem qualifies, 0 = never.  Same operands and accumulation order per output element as the halo kernel.  Returns the previous mode; any
  * other value only queries.  Process-wide; also GANB200_CONV_FLAT in the environment. */
 int ganb200_conv_flat_mode(int mode);
+/* Diagnosis of the flat kernel's pipeline: while `device_buf` (3 * 32 * 4 uint64 on the device, zeroed by the caller) is
+ * set, CTA 0 of every flat launch writes clock64() stamps for its first 32 tiles — role 0 activation producer
+ * {before, after the wait for a free stage}, role 1 MMA issuer {before / after the wait for a free accumulator, after the
+ * wait for the activation stage, after the last MMA of the tile is issued}, role 2 epilogue warp {before / after the wait
+ * for the accumulator, after its last store}.  NULL switches it off (default).  tools/flat_trace.py prints the timeline. */
+int ganb200_conv_flat_trace(unsigned long long* device_buf);
 /* Hardware self-test behind the tcgen05 engine's tap addressing (csrc/probe.cu; no reference counterpart): loads a
  * [rows][64] bf16 box (SWIZZLE_128B) with TMA and returns out[128][n] = a[shift : shift + 128] * b^T with the A
  * descriptor's start address shifted by `shift` 128-byte rows — any shift, not only multiples of the 8-row swizzle atom.
@@ -94,6 +100,9 @@ int ganb200_conv_flat_mode(int mode);
  * n in {32, 64}. */
 int ganb200_tc_shift_probe(const void* a, const void* b, float* out, int rows, int n, int shift, int base_offset_mode,
                            void* stream);
+/* the same with an M = 64 (m = 64) or M = 128 instruction; `out` always receives all 128 TMEM lanes */
+int ganb200_tc_shift_probe_m(const void* a, const void* b, float* out, int rows, int n, int shift, int base_offset_mode,
+                             int m, void* stream);
 /* tcgen05 engine, dgrad of replicate-padded convolutions: 0 (default) = padded fp32 domain in the workspace, then a fold
  * pass — every sum in a fixed order, the result is reproducible bit for bit; 1 = the MMA epilogue scatters each
  * padded-domain value straight into the clamped pixel of the unpadded plane (plain stores inside, red.global.add on the
