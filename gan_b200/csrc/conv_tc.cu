@@ -1619,6 +1619,7 @@ struct TcWgradParams {
   int chunks, chunks_per_split, splits;
   int off_h, off_w, in_step;
   int n_umma;                // multiple of 16 <= BN
+  int m;                     // rows of the MMA: 128, or 64 when K <= 64 (see wgrad_m)
   float* part;               // [splits][taps][K][C]
 };
 
@@ -1679,11 +1680,11 @@ __global__ void __launch_bounds__(TC_THREADS) tc_wgrad_kernel(const __grid_const
       const int tp = t % p.tiles_p; t /= p.tiles_p;
       const int q0 = tq * p.bw, p0 = tp * p.bh, n0 = t * p.bn;
       if (leader) {
-        mbar_expect_tx(&full[stage], A_BYTES + B_BYTES);
+        mbar_expect_tx(&full[stage], (p.m == 64 ? A_BYTES / 2 : A_BYTES) + B_BYTES);
         uint8_t* a = smA + stage * A_BYTES;
         uint8_t* b = smB + stage * B_BYTES;
         tma_load_4d(a, &tmA, &full[stage], k0, q0, p0, n0);
-        tma_load_4d(a + WG_GROUP_BYTES, &tmA, &full[stage], k0 + 64, q0, p0, n0);
+        if (p.m != 64) tma_load_4d(a + WG_GROUP_BYTES, &tmA, &full[stage], k0 + 64, q0, p0, n0);
 #pragma unroll
         for (int g = 0; g < BN / 64; ++g)
           tma_load_4d(b + g * WG_GROUP_BYTES, &tmB, &full[stage], c0 + g * 64, q0 * p.in_step + s + p.off_w,
@@ -1693,7 +1694,7 @@ __global__ void __launch_bounds__(TC_THREADS) tc_wgrad_kernel(const __grid_const
     __syncwarp();
   } else if (warp == 1) {
     const bool leader = elect_one();
-    const uint32_t idesc = make_idesc_bf16(TILE_M, p.n_umma, 1, 1);
+    const uint32_t idesc = make_idesc_bf16(p.m, p.n_umma, 1, 1);
     for (int it = 0; it < iters; ++it) {
       const int stage = it % STAGES;
       const uint32_t phase = (it / STAGES) & 1;
@@ -1712,14 +1713,16 @@ __global__ void __launch_bounds__(TC_THREADS) tc_wgrad_kernel(const __grid_const
     __syncwarp();
   } else {
     const int quarter = warp & 3;
-    const int k = k0 + quarter * 32 + lane;
+    // M = 64: accumulator row r sits in TMEM lane 32 * (r / 16) + r % 16 (csrc/probe.cu, profiles/r02_tc_m64_lane_probe.txt)
+    const int k = k0 + (p.m == 64 ? quarter * 16 + lane : quarter * 32 + lane);
+    const bool k_ok = k < p.K && (p.m != 64 || lane < 16);
     float* row = p.part + (((int64_t)split * p.taps + tap) * p.K + k) * p.C + c0;
     mbar_wait(tmem_full, 0);
     tc_fence_after();
     for (int j0 = 0; j0 < p.n_umma; j0 += 32) {
       float v[32];
       tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)j0, v);
-      if (k < p.K) {
+      if (k_ok) {
 #pragma unroll
         for (int j = 0; j < 32; ++j)
           if (j0 + j < p.n_umma && c0 + j0 + j < p.C) row[j0 + j] = iters > 0 ? v[j] : 0.f;
@@ -1753,6 +1756,7 @@ struct TcWgRingParams {
   int BN, n_umma, acc_pitch;
   int d_stages, x_slots;
   int row_bytes;            // Q * 128: one image row of one 64-channel group
+  int m;                    // rows of the MMA: 128, or 64 when K <= 64 (see wgrad_m)
   uint32_t tmem_cols;
   float* part;              // [splits][R*S][K][C]
 };
@@ -1829,7 +1833,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_wgrad_ring_kernel(const __gr
     __syncwarp();
   } else if (warp == 1) {
     const bool leader = elect_one();
-    const uint32_t idesc = make_idesc_bf16(TILE_M, p.n_umma, 1, 1);
+    const uint32_t idesc = make_idesc_bf16(p.m, p.n_umma, 1, 1);
     int sd = 0, sx = 0;          // sx / px: slot and fill parity of the OLDEST row in the ring window
     uint32_t pd = 0, px = 0;
     bool fresh = true;
@@ -1878,7 +1882,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_wgrad_ring_kernel(const __gr
     __syncwarp();
   } else {
     const int quarter = warp & 3;
-    const int k = k0 + quarter * 32 + lane;
+    const int k = k0 + (p.m == 64 ? quarter * 16 + lane : quarter * 32 + lane);   // M = 64: 16 lanes per quarter
+    const bool k_ok = k < p.K && (p.m != 64 || lane < 16);
     const bool any = g_end > g_beg;
     mbar_wait(tmem_full, 0);
     tc_fence_after();
@@ -1887,7 +1892,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_wgrad_ring_kernel(const __gr
       for (int j0 = 0; j0 < p.n_umma; j0 += 32) {
         float v[32];
         tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(r * p.acc_pitch + j0), v);
-        if (k < p.K) {
+        if (k_ok) {
 #pragma unroll
           for (int j = 0; j < 32; ++j)
             if (j0 + j < p.n_umma && c0 + j0 + j < p.C) row[j0 + j] = any ? v[j] : 0.f;
@@ -1922,6 +1927,16 @@ __global__ void __launch_bounds__(256) wgrad_reduce_kernel(const float* __restri
     for (; sp < splits; ++sp) acc += __ldg(src + (size_t)sp * step);
     dw[(size_t)i * RS + rs] = acc * alpha;
   }
+}
+
+// Rows of the wgrad MMAs.  The tensor core fetches its shared-memory operands at ~70 bytes per clock and SM (flat-kernel
+// trace, profiles/r02_flat_kernel_trace.txt: a 128 x 48 x 16 MMA takes 77 cycles, a 128 x 96 x 16 one 107), so a narrow MMA
+// costs what its operands weigh: with K <= 64 filters an M = 128 instruction reads 4 KB of dy of which half is padding;
+// M = 64 reads 2 KB.  GANB200_WGRAD_M64=0: always 128.
+static int wgrad_m(const ganb200_conv_desc* d) {
+  static int on = -1;
+  if (on < 0) { const char* e = getenv("GANB200_WGRAD_M64"); on = (e && e[0] == '0') ? 0 : 1; }
+  return (on && d->K <= 64) ? 64 : TILE_M;
 }
 
 struct WgradPlan {
@@ -2041,7 +2056,7 @@ static int wgrad_run(const ganb200_conv_desc* d, const float* x, const float* dy
     r.a_groups = w.ring.a_groups; r.b_groups = w.ring.b_groups;
     r.BN = w.ring.BN; r.n_umma = w.ring.n_umma; r.acc_pitch = w.ring.acc_pitch;
     r.d_stages = w.ring.d_stages; r.x_slots = w.ring.x_slots;
-    r.row_bytes = d->Q * 128; r.tmem_cols = w.ring.tmem_cols; r.part = part;
+    r.row_bytes = d->Q * 128; r.tmem_cols = w.ring.tmem_cols; r.part = part; r.m = wgrad_m(d);
     CUtensorMap ta, tb;
     uint64_t dims[4] = {(uint64_t)d->K, (uint64_t)d->Q, (uint64_t)d->P, (uint64_t)d->N};
     uint64_t str[3] = {(uint64_t)Kp * 2, (uint64_t)d->Q * Kp * 2, (uint64_t)d->P * d->Q * Kp * 2};
@@ -2073,7 +2088,7 @@ static int wgrad_run(const ganb200_conv_desc* d, const float* x, const float* dy
   p.off_h = p.off_w = rep ? 0 : -d->pad;
   p.in_step = d->stride;
   p.n_umma = d->C >= w.BN ? w.BN : (d->C + 15) / 16 * 16;
-  p.part = part;
+  p.part = part; p.m = wgrad_m(d);
   CUtensorMap ta, tb;
   {
     uint64_t dims[4] = {(uint64_t)d->K, (uint64_t)d->Q, (uint64_t)d->P, (uint64_t)d->N};
