@@ -74,6 +74,8 @@ SIGNATURES = {
     "ganb200_ew_binary": (c_int, [c_int, P, P, P, c_int64, c_float, P]),
     "ganb200_ew_bcast": (c_int, [c_int, P, P, P, c_int, c_int, c_int, c_int, P]),
     "ganb200_ew_fma_bcast": (c_int, [P, P, P, P, c_int, c_int, c_int, c_int, P]),
+    "ganb200_sk_merge2_fwd": (c_int, [P, P, P, P, c_int, c_int, c_int, P]),
+    "ganb200_sk_merge2_bwd": (c_int, [P, P, P, P, P, P, P, c_int, c_int, c_int, P]),
     "ganb200_reduce": (c_int, [P, P, P, c_int, c_int, c_int, c_int, c_float, P]),
     "ganb200_prelu_fwd": (c_int, [P, P, P, c_int, c_int, c_int, c_int, P]),
     "ganb200_maskscale": (c_int, [P, P, P, P, c_int, c_int, c_int, c_int, P]),

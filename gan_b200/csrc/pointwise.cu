@@ -281,6 +281,109 @@ extern "C" int ganb200_ew_fma_bcast(const float* x, const float* v, const float*
   return 0;
 }
 
+// ------------------------------------------------------------------ selective-kernel merge of two branches, fused
+// out = a0 * t0 + a1 * t1 with per-(sample, channel) attention weights att[n][i][c] (generator_13_5.py:169,201,294 for
+// M = 2).  As mul_bc + fma_bc the forward is 5 passes over a feature map and the backward 8 (g is read four times); here
+// 3 and 5.  One block (planes of >= 1024 values) or one warp per (n, c) plane; the attention gradients are whole-plane sums
+// taken inside the block / warp in a fixed order.
+namespace ganb200 {
+
+template <bool BWD>
+__global__ void __launch_bounds__(256) sk_merge2_kernel(const float* __restrict__ g, const float* __restrict__ t0,
+                                                        const float* __restrict__ t1, const float* __restrict__ att,
+                                                        float* __restrict__ o0, float* __restrict__ o1,
+                                                        float* __restrict__ gatt, int64_t rows, int C, int HW,
+                                                        bool block_rows) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t step = block_rows ? gridDim.x : (int64_t)gridDim.x * 8;
+  const int t_first = block_rows ? threadIdx.x : lane, t_step = block_rows ? 256 : 32;
+  const bool vec = (HW & 3) == 0;
+  for (int64_t row = block_rows ? blockIdx.x : (int64_t)blockIdx.x * 8 + warp; row < rows; row += step) {
+    const int64_t n = row / C;
+    const int c = (int)(row - n * C);
+    const float a0 = __ldg(att + (n * 2 + 0) * C + c), a1 = __ldg(att + (n * 2 + 1) * C + c);
+    const int64_t base = row * HW;
+    float s0 = 0.f, s1 = 0.f;
+    if (vec) {
+      const float4* p0 = reinterpret_cast<const float4*>(t0 + base);
+      const float4* p1 = reinterpret_cast<const float4*>(t1 + base);
+      const float4* pg = BWD ? reinterpret_cast<const float4*>(g + base) : nullptr;
+      float4* q0 = reinterpret_cast<float4*>(o0 + base);
+      float4* q1 = BWD ? reinterpret_cast<float4*>(o1 + base) : nullptr;
+      for (int i = t_first; i < (HW >> 2); i += t_step) {
+        const float4 u = __ldg(p0 + i), v = __ldg(p1 + i);
+        if (BWD) {
+          const float4 w = __ldg(pg + i);
+          s0 += w.x * u.x + w.y * u.y + w.z * u.z + w.w * u.w;
+          s1 += w.x * v.x + w.y * v.y + w.z * v.z + w.w * v.w;
+          q0[i] = make_float4(a0 * w.x, a0 * w.y, a0 * w.z, a0 * w.w);
+          q1[i] = make_float4(a1 * w.x, a1 * w.y, a1 * w.z, a1 * w.w);
+        } else {
+          q0[i] = make_float4(fmaf(a1, v.x, a0 * u.x), fmaf(a1, v.y, a0 * u.y), fmaf(a1, v.z, a0 * u.z),
+                              fmaf(a1, v.w, a0 * u.w));
+        }
+      }
+    } else {
+      for (int i = t_first; i < HW; i += t_step) {
+        const float u = t0[base + i], v = t1[base + i];
+        if (BWD) {
+          const float w = g[base + i];
+          s0 = fmaf(w, u, s0);
+          s1 = fmaf(w, v, s1);
+          o0[base + i] = a0 * w;
+          o1[base + i] = a1 * w;
+        } else {
+          o0[base + i] = fmaf(a1, v, a0 * u);
+        }
+      }
+    }
+    if (BWD) {
+      if (block_rows) {
+        s0 = block_sum<256>(s0);
+        s1 = block_sum<256>(s1);
+        if (threadIdx.x == 0) { gatt[(n * 2 + 0) * C + c] = s0; gatt[(n * 2 + 1) * C + c] = s1; }
+      } else {
+        s0 = warp_sum(s0);
+        s1 = warp_sum(s1);
+        if (lane == 0) { gatt[(n * 2 + 0) * C + c] = s0; gatt[(n * 2 + 1) * C + c] = s1; }
+      }
+    }
+  }
+}
+
+}  // namespace ganb200
+
+static bool sk_aligned(const void* a, const void* b, const void* c, const void* d, const void* e) {
+  return ((((uintptr_t)a) | ((uintptr_t)b) | ((uintptr_t)c) | ((uintptr_t)d) | ((uintptr_t)e)) & 15) == 0;
+}
+
+extern "C" int ganb200_sk_merge2_fwd(const float* t0, const float* t1, const float* att, float* out, int N, int C, int HW,
+                                     void* stream) {
+  const int64_t rows = (int64_t)N * C;
+  if (rows * HW <= 0) return 0;
+  GB_REQUIRE(t0 && t1 && att && out, GANB200_BAD_ARG, "sk_merge2_fwd: null argument");
+  GB_REQUIRE((HW & 3) != 0 || sk_aligned(t0, t1, out, nullptr, nullptr), GANB200_BAD_ARG, "sk_merge2_fwd: unaligned tensor");
+  const bool block_rows = HW >= 1024;
+  const int grid = (int)std::min<int64_t>(block_rows ? rows : (rows + 7) / 8, (int64_t)kNumSMs * 32);
+  sk_merge2_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>(nullptr, t0, t1, att, out, nullptr, nullptr, rows, C, HW,
+                                                                  block_rows);
+  GB_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int ganb200_sk_merge2_bwd(const float* g, const float* t0, const float* t1, const float* att, float* g0,
+                                     float* g1, float* gatt, int N, int C, int HW, void* stream) {
+  const int64_t rows = (int64_t)N * C;
+  if (rows * HW <= 0) return 0;
+  GB_REQUIRE(g && t0 && t1 && att && g0 && g1 && gatt, GANB200_BAD_ARG, "sk_merge2_bwd: null argument");
+  GB_REQUIRE((HW & 3) != 0 || sk_aligned(g, t0, t1, g0, g1), GANB200_BAD_ARG, "sk_merge2_bwd: unaligned tensor");
+  const bool block_rows = HW >= 1024;
+  const int grid = (int)std::min<int64_t>(block_rows ? rows : (rows + 7) / 8, (int64_t)kNumSMs * 32);
+  sk_merge2_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>(g, t0, t1, att, g0, g1, gatt, rows, C, HW, block_rows);
+  GB_CHECK_LAUNCH();
+  return 0;
+}
+
 extern "C" int ganb200_reduce(const float* x, const float* y, float* out, int N, int C, int HW, int rmode, float scale,
                               void* stream) {
   cudaStream_t s = (cudaStream_t)stream;

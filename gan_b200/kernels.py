@@ -379,6 +379,24 @@ class CudaBackend:
         _lib.check(self.lib.ganb200_ew_fma_bcast(self._p(x), self._p(v), self._p(z), self._p(y), N, C, HW, vmode, st))
         return y
 
+    def sk_merge2_fwd(self, t0, t1, att):
+        """att[:, 0] * t0 + att[:, 1] * t1, att: [N, 2, C] contiguous"""
+        N, C, HW = _nchw(t0)
+        st = self._prep(t0, t1, att)
+        out = torch.empty_like(t0)
+        _lib.check(self.lib.ganb200_sk_merge2_fwd(self._p(t0), self._p(t1), self._p(att), self._p(out), N, C, HW, st))
+        return out
+
+    def sk_merge2_bwd(self, g, t0, t1, att):
+        """-> (g_t0, g_t1, g_att[N, 2, C])"""
+        N, C, HW = _nchw(t0)
+        st = self._prep(g, t0, t1, att)
+        g0, g1 = torch.empty_like(t0), torch.empty_like(t1)
+        gatt = torch.empty((N, 2, C), dtype=torch.float32, device=t0.device)
+        _lib.check(self.lib.ganb200_sk_merge2_bwd(self._p(g), self._p(t0), self._p(t1), self._p(att), self._p(g0),
+                                                  self._p(g1), self._p(gatt), N, C, HW, st))
+        return g0, g1, gatt
+
     def reduce(self, x, y, rmode, scale=1.0):
         N, C, HW = _nchw(x)
         st = self._prep(x, y)

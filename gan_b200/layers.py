@@ -11,6 +11,8 @@ Reference semantics cited per class (paths under /root/reference).
 import math
 
 import numpy as np
+import os
+
 import torch
 import torch.nn as nn
 
@@ -284,6 +286,9 @@ def sk_merge(branches, att):
     """(feas * attention).sum(dim=1) — generator_13_5.py:169,201,294.  att: (b,M,c,1,1) or (b,M,c)."""
     b, m = att.shape[:2]
     att = att.reshape(b, m, -1)
+    if (m == 2 and len(branches) == 2 and branches[0].dim() >= 3 and branches[0].shape == branches[1].shape
+            and branches[0].dtype == torch.float32 and os.environ.get("GANB200_SK_MERGE_FUSED", "1") != "0"):
+        return ops.sk_merge2(branches[0], branches[1], att)      # one pass each way instead of mul_bc + fma_bc
     out = None
     for i, fea in enumerate(branches):
         a_i = ops.slice_channels(att, i, i + 1).reshape(b, -1)

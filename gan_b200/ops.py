@@ -238,6 +238,33 @@ class FmaBcFn(Function):
         return g, gv, gz, None
 
 
+class SkMerge2Fn(Function):
+    """att[:, 0] * t0 + att[:, 1] * t1 in one pass each way (generators/generator_13_5.py:169,201,294, M = 2).  Under
+    create_graph the backward is rebuilt from the twice-differentiable broadcast ops."""
+
+    @staticmethod
+    def forward(ctx, t0, t1, att):
+        t0, t1, att = _c(t0), _c(t1), _c(att)
+        ctx.save_for_backward(t0, t1, att)
+        return K().sk_merge2_fwd(t0, t1, att)
+
+    @staticmethod
+    def backward(ctx, g):
+        t0, t1, att = ctx.saved_tensors
+        g = _c(g)
+        if torch.is_grad_enabled():
+            a0, a1 = att[:, 0].contiguous(), att[:, 1].contiguous()
+            g0, g1 = MulBcFn.apply(g, a0, KN.V_NC), MulBcFn.apply(g, a1, KN.V_NC)
+            s0, s1 = ReduceFn.apply(g, t0, KN.R_HW, 1.0), ReduceFn.apply(g, t1, KN.R_HW, 1.0)
+            return g0, g1, torch.stack([s0, s1], 1)
+        g0, g1, gatt = K().sk_merge2_bwd(g, t0, t1, att)
+        return g0, g1, gatt
+
+
+def sk_merge2(t0, t1, att):
+    return SkMerge2Fn.apply(t0, t1, att)
+
+
 # =====================================================================================================
 # elementwise
 # =====================================================================================================

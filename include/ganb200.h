@@ -181,6 +181,13 @@ int ganb200_ew_fma_bcast(const float* x, const float* v, const float* z, float* 
 /* out = sum x*(y or 1) over: rmode 0: HW -> [N,C];  1: N,HW -> [C];  2: C,HW -> [N];  3: all -> [1].
  * Replaces the bias/scale gradient reductions, AdaptiveAvgPool2d(1) (scaled by the caller), compute_grad2's
  * pow(2).view(B,-1).sum(1) (train/ganR2.py:36-38), torch.mean (train/wgangpR2.py:21). */
+/* Selective-kernel merge of two branches in one pass each way: out = att[n][0][c] * t0 + att[n][1][c] * t1
+ * ((feas * attention).sum(dim=1) with M = 2: generators/generator_13_5.py:169,201,294); backward g0 = att0 * g,
+ * g1 = att1 * g, gatt[n][i][c] = sum_hw g * t_i.  t0, t1, out, g* : [N, C, HW]; att, gatt: [N, 2, C]. */
+int ganb200_sk_merge2_fwd(const float* t0, const float* t1, const float* att, float* out, int N, int C, int HW,
+                          void* stream);
+int ganb200_sk_merge2_bwd(const float* g, const float* t0, const float* t1, const float* att, float* g0, float* g1,
+                          float* gatt, int N, int C, int HW, void* stream);
 int ganb200_reduce(const float* x, const float* y, float* out, int N, int C, int HW, int rmode, float scale, void* stream);
 
 /* PReLU (nn.PReLU(C) discriminator_9_4.py:91,136; nn.PReLU() scalar generator_3_progan.py): a_n = C or 1.

@@ -110,6 +110,20 @@ class RefBackend:
     def ew_fma_bcast(self, x, v, z, vmode):
         return (x + _v(x, v, vmode) * z).contiguous()
 
+    def sk_merge2_fwd(self, t0, t1, att):
+        a = att.reshape(att.shape[0], 2, -1)
+        sh = (t0.shape[0], t0.shape[1]) + (1,) * (t0.dim() - 2)
+        return (a[:, 0].reshape(sh) * t0 + a[:, 1].reshape(sh) * t1).contiguous()
+
+    def sk_merge2_bwd(self, g, t0, t1, att):
+        a = att.reshape(att.shape[0], 2, -1)
+        sh = (t0.shape[0], t0.shape[1]) + (1,) * (t0.dim() - 2)
+        dims = tuple(range(2, t0.dim()))
+        s0 = (g * t0).sum(dims) if dims else g * t0
+        s1 = (g * t1).sum(dims) if dims else g * t1
+        return ((a[:, 0].reshape(sh) * g).contiguous(), (a[:, 1].reshape(sh) * g).contiguous(),
+                torch.stack([s0, s1], 1).contiguous())
+
     def reduce(self, x, y, rmode, scale=1.0):
         t = x if y is None else x * y
         if t.dim() == 1:

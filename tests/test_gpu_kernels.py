@@ -4,6 +4,7 @@
 Tolerances (BASELINE.json north_star): rel. L2 <= 1e-5 for fp32 paths, <= 1e-2 for the bf16 tcgen05 engine.
 """
 import ctypes
+import os
 
 import pytest
 import torch
@@ -330,6 +331,32 @@ def test_batchnorm_fused_small(cu, ref, shape, affine):
         assert len(out) == len(out_r) == 4
         for a, b in zip(out, out_r):
             assert rel(a, b) < 1e-4
+
+
+@pytest.mark.parametrize("shape", [(4, 48, 64, 64), (3, 7, 5, 5), (2, 5, 3, 3), (5, 6, 1, 1), (2, 9, 34, 30)])
+def test_sk_merge_two_branches_fused(cu, ref, shape):
+    """att0 * t0 + att1 * t1 and its adjoints in one launch each (ganb200_sk_merge2_fwd / _bwd) against the oracle, and
+    the layer-level path against the mul_bc + fma_bc chain it replaces"""
+    torch.manual_seed(21)
+    t0, t1, gy = rnd(*shape), rnd(*shape), rnd(*shape)
+    att = torch.softmax(rnd(shape[0], 2, shape[1]), dim=1).contiguous()
+    out = cu.sk_merge2_fwd(g(t0), g(t1), g(att))
+    assert rel(out, ref.sk_merge2_fwd(t0, t1, att)) < FP32_TOL
+    got = cu.sk_merge2_bwd(g(gy), g(t0), g(t1), g(att))
+    want = ref.sk_merge2_bwd(gy, t0, t1, att)
+    for a, b in zip(got, want):
+        assert a.shape == b.shape and rel(a, b) < 1e-5
+    from gan_b200 import layers as L
+    grads = {}
+    for fused in ("1", "0"):
+        os.environ["GANB200_SK_MERGE_FUSED"] = fused
+        leaves = [t.clone().cuda().requires_grad_() for t in (t0, t1, att)]
+        y = L.sk_merge([leaves[0], leaves[1]], leaves[2].view(shape[0], 2, shape[1], 1, 1))
+        y.backward(g(gy))
+        grads[fused] = [y.detach()] + [t.grad for t in leaves]
+    os.environ.pop("GANB200_SK_MERGE_FUSED")
+    for a, b in zip(grads["1"], grads["0"]):
+        assert rel(a, b) < 1e-5
 
 
 def test_softmax_mbstd_bce(cu, ref):
