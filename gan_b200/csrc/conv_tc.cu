@@ -2157,23 +2157,29 @@ __global__ void __launch_bounds__(256) fold_scale_reduce_kernel(const float* __r
 // load per thread and iteration cannot cover the HBM latency.  Here a thread owns UNROLL float4 quads per trip: all centre
 // loads of the padded plane (the only ones an interior quad needs) and the float4 loads of x are issued first; quads on
 // the border ring of the plane then add what the replicate padding folds onto them.  One block per (n, c) plane.
-template <int UNROLL>
+// WARP_PLANES: one WARP per plane (no block-wide barrier between planes: the eight warps of a block stream eight planes
+// independently and a warp's loads of its next trip are not held back by the others' reduction) instead of one block.
+template <int UNROLL, bool WARP_PLANES>
 __global__ void __launch_bounds__(256) fold_scale_reduce_vec_kernel(const float* __restrict__ dxp, const float* __restrict__ s,
                                                                      const float* __restrict__ x, float* __restrict__ gx,
                                                                      float* __restrict__ gs1, int H, int W, int pad,
                                                                      int64_t rows) {
   const int Hp = H + 2 * pad, Wp = W + 2 * pad, HW = H * W, Wq = W >> 2, quads = HW >> 2;
-  for (int64_t row = blockIdx.x; row < rows; row += gridDim.x) {
+  constexpr int TS = WARP_PLANES ? 32 : 256;                   // threads that share a plane
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t row_first = WARP_PLANES ? (int64_t)blockIdx.x * 8 + warp : blockIdx.x;
+  const int64_t row_step = WARP_PLANES ? (int64_t)gridDim.x * 8 : gridDim.x;
+  for (int64_t row = row_first; row < rows; row += row_step) {
     const float sv = s[row];
     const float* src = dxp + row * Hp * Wp;
     const float4* xr = reinterpret_cast<const float4*>(x + row * HW);
     float4* gr = reinterpret_cast<float4*>(gx + row * HW);
     float acc = 0.f;
-    for (int q0 = threadIdx.x; q0 < quads; q0 += 256 * UNROLL) {
+    for (int q0 = WARP_PLANES ? lane : (int)threadIdx.x; q0 < quads; q0 += TS * UNROLL) {
       float4 c[UNROLL], xv[UNROLL];
 #pragma unroll
       for (int u = 0; u < UNROLL; ++u) {
-        const int q = q0 + u * 256;
+        const int q = q0 + u * TS;
         c[u] = xv[u] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (q < quads) {
           const int h = q / Wq, w0 = (q - h * Wq) << 2;
@@ -2184,7 +2190,7 @@ __global__ void __launch_bounds__(256) fold_scale_reduce_vec_kernel(const float*
       }
 #pragma unroll
       for (int u = 0; u < UNROLL; ++u) {
-        const int q = q0 + u * 256;
+        const int q = q0 + u * TS;
         if (q >= quads) continue;
         const int h = q / Wq, w0 = (q - h * Wq) << 2;
         if (h == 0 || h == H - 1 || w0 == 0 || w0 + 4 == W) {   // a quad on the ring: the general clamp sums
@@ -2207,8 +2213,13 @@ __global__ void __launch_bounds__(256) fold_scale_reduce_vec_kernel(const float*
       }
     }
     if (gs1) {
-      acc = block_sum<256>(acc);
-      if (threadIdx.x == 0) gs1[row] = acc;
+      if (WARP_PLANES) {
+        acc = warp_sum(acc);
+        if (lane == 0) gs1[row] = acc;
+      } else {
+        acc = block_sum<256>(acc);
+        if (threadIdx.x == 0) gs1[row] = acc;
+      }
     }
   }
 }
@@ -2320,9 +2331,16 @@ static int modconv_bwd_impl(const ganb200_conv_desc* d, const float* x, const fl
     const int pad = (d->pad_mode == 1 && !folded) ? d->pad : 0;
     const bool vec = HW >= 1024 && (d->W & 3) == 0 && ((((uintptr_t)x) | ((uintptr_t)gx)) & 15) == 0;
     if (vec) {
-      int grid = (int)std::min<int64_t>(rows, (int64_t)kNumSMs * 32);
-      if (HW >= 4096) fold_scale_reduce_vec_kernel<4><<<grid, 256, 0, st>>>(dxp, s, x, gx, gs1, d->H, d->W, pad, rows);
-      else fold_scale_reduce_vec_kernel<1><<<grid, 256, 0, st>>>(dxp, s, x, gx, gs1, d->H, d->W, pad, rows);
+      static int warp_planes = -1;
+      if (warp_planes < 0) { const char* e = getenv("GANB200_FOLD_WARP_PLANES"); warp_planes = (e && e[0] == '0') ? 0 : 1; }
+      if (warp_planes) {
+        int grid = (int)std::min<int64_t>((rows + 7) / 8, (int64_t)kNumSMs * 32);
+        fold_scale_reduce_vec_kernel<4, true><<<grid, 256, 0, st>>>(dxp, s, x, gx, gs1, d->H, d->W, pad, rows);
+      } else {
+        int grid = (int)std::min<int64_t>(rows, (int64_t)kNumSMs * 32);
+        if (HW >= 4096) fold_scale_reduce_vec_kernel<4, false><<<grid, 256, 0, st>>>(dxp, s, x, gx, gs1, d->H, d->W, pad, rows);
+        else fold_scale_reduce_vec_kernel<1, false><<<grid, 256, 0, st>>>(dxp, s, x, gx, gs1, d->H, d->W, pad, rows);
+      }
     } else if (HW >= 1024) {
       int grid = (int)std::min<int64_t>(rows, (int64_t)kNumSMs * 32);
       fold_scale_reduce_kernel<false><<<grid, 256, 0, st>>>(dxp, s, x, gx, gs1, d->H, d->W, pad, rows);

@@ -384,6 +384,66 @@ extern "C" int ganb200_sk_merge2_bwd(const float* g, const float* t0, const floa
   return 0;
 }
 
+// ------------------------------------------------------------------ SK attention input: AdaptiveAvgPool2d(OUT) of t0 + t1
+// (generator_13_5.py:77-80: fea_U = sum of the branches, then the 5x5 pooling).  As add + pooling it is 3 passes over a
+// feature map plus a pooling launch that re-reads the sum; here both branches are read once.  One thread per column of a
+// plane (W threads per plane, 256 / W planes per block): per output row bin the column sums of that bin's input rows, then
+// the OUT x OUT outputs from the column sums in shared memory.  Bins as torch: [floor(o n / OUT), ceil((o + 1) n / OUT)).
+namespace ganb200 {
+
+template <int OUT>
+__global__ void __launch_bounds__(256) pool_sum2_kernel(const float* __restrict__ t0, const float* __restrict__ t1,
+                                                        float* __restrict__ out, int64_t planes, int H, int W) {
+  __shared__ float colsum[256 * OUT];          // [plane in block][OUT][W]
+  const int ppb = 256 / W;
+  const int pl = threadIdx.x / W, w = threadIdx.x - pl * W;
+  const int HW = H * W;
+  for (int64_t p0 = (int64_t)blockIdx.x * ppb; p0 < planes; p0 += (int64_t)gridDim.x * ppb) {
+    const int64_t plane = p0 + pl;
+    const bool ok = plane < planes;
+    const float* a = t0 + plane * HW + w;
+    const float* b = t1 + plane * HW + w;
+#pragma unroll
+    for (int o = 0; o < OUT; ++o) {
+      const int hs = (o * H) / OUT, he = ((o + 1) * H + OUT - 1) / OUT;
+      float acc = 0.f;
+      if (ok) {
+#pragma unroll 4
+        for (int h = hs; h < he; ++h) acc += __ldg(a + h * W) + __ldg(b + h * W);
+      }
+      colsum[(pl * OUT + o) * W + w] = acc / (float)(he - hs);
+    }
+    __syncthreads();
+    if (ok && w < OUT * OUT) {
+      const int o = w / OUT, j = w - o * OUT;
+      const int ws = (j * W) / OUT, we = ((j + 1) * W + OUT - 1) / OUT;
+      const float* row = colsum + (pl * OUT + o) * W;
+      float acc = 0.f;
+      for (int c = ws; c < we; ++c) acc += row[c];
+      out[plane * (OUT * OUT) + w] = acc / (float)(we - ws);
+    }
+    __syncthreads();
+  }
+}
+
+}  // namespace ganb200
+
+extern "C" int ganb200_pool_sum2_eligible(int H, int W, int out_size) {
+  return out_size == 5 && H == W && (W == 32 || W == 64);   // W threads per plane must cover the 25 outputs
+}
+
+extern "C" int ganb200_pool_sum2(const float* t0, const float* t1, float* out, int64_t planes, int H, int W, int out_size,
+                                 void* stream) {
+  if (planes <= 0) return 0;
+  GB_REQUIRE(t0 && t1 && out, GANB200_BAD_ARG, "pool_sum2: null argument");
+  GB_REQUIRE(ganb200_pool_sum2_eligible(H, W, out_size), GANB200_BAD_SHAPE, "pool_sum2: 32x32 or 64x64 planes to 5x5");
+  const int ppb = 256 / W;
+  const int grid = (int)std::min<int64_t>((planes + ppb - 1) / ppb, (int64_t)kNumSMs * 32);
+  pool_sum2_kernel<5><<<grid, 256, 0, (cudaStream_t)stream>>>(t0, t1, out, planes, H, W);
+  GB_CHECK_LAUNCH();
+  return 0;
+}
+
 extern "C" int ganb200_reduce(const float* x, const float* y, float* out, int N, int C, int HW, int rmode, float scale,
                               void* stream) {
   cudaStream_t s = (cudaStream_t)stream;

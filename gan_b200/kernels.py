@@ -379,6 +379,18 @@ class CudaBackend:
         _lib.check(self.lib.ganb200_ew_fma_bcast(self._p(x), self._p(v), self._p(z), self._p(y), N, C, HW, vmode, st))
         return y
 
+    def pool_sum2_ok(self, t0, t1, out):
+        return (t0.dim() == 4 and t0.shape == t1.shape and t0.dtype == torch.float32 and
+                bool(self.lib.ganb200_pool_sum2_eligible(t0.shape[-2], t0.shape[-1], out)))
+
+    def pool_sum2(self, t0, t1, out):
+        """AdaptiveAvgPool2d(out)(t0 + t1) reading each branch once"""
+        N, C, H, W = t0.shape
+        st = self._prep(t0, t1)
+        y = torch.empty((N, C, out, out), dtype=torch.float32, device=t0.device)
+        _lib.check(self.lib.ganb200_pool_sum2(self._p(t0), self._p(t1), self._p(y), N * C, H, W, out, st))
+        return y
+
     def sk_merge2_fwd(self, t0, t1, att):
         """att[:, 0] * t0 + att[:, 1] * t1, att: [N, 2, C] contiguous"""
         N, C, HW = _nchw(t0)

@@ -13,6 +13,8 @@ critics under R-penalties): its create_graph backward goes through `_bn_composed
 from collections import namedtuple
 import math
 
+import os
+
 import torch
 from torch.autograd import Function
 from torch.autograd.function import once_differentiable
@@ -236,6 +238,33 @@ class FmaBcFn(Function):
         if ctx.needs_input_grad[2]:
             gz = MulBcFn.apply(_c(g), v, ctx.vmode)
         return g, gv, gz, None
+
+
+class PoolSum2Fn(Function):
+    """AdaptiveAvgPool2d(out)(t0 + t1) in one pass over the two branches (the SK attention's input,
+    generators/generator_13_5.py:77-80); both branches receive the same gradient, the adjoint of the pooling."""
+
+    @staticmethod
+    def forward(ctx, t0, t1, out):
+        ctx.side, ctx.out = t0.shape[-1], out
+        return K().pool_sum2(_c(t0), _c(t1), out)
+
+    @staticmethod
+    def backward(ctx, g):
+        op = RS.adaptive_avg(ctx.side, ctx.out).T
+        gx = Resample2dFn.apply(_c(g), op, op)
+        return gx, gx, None
+
+
+def pooled_branch_sum(branches, out):
+    """AdaptiveAvgPool2d(out)(sum of the branches)"""
+    if (len(branches) == 2 and os.environ.get("GANB200_POOL_SUM_FUSED", "1") != "0"
+            and K().pool_sum2_ok(branches[0], branches[1], out)):
+        return PoolSum2Fn.apply(branches[0], branches[1], out)
+    acc = branches[0]
+    for t in branches[1:]:
+        acc = add(acc, t)
+    return adaptive_avg_pool(acc, out)
 
 
 class SkMerge2Fn(Function):

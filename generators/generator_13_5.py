@@ -99,7 +99,7 @@ class SKAttention_conv(_SKAttention):
         branches = L.as_branches(feas)
         b, c, _, side = branches[0].shape
         assert (side >= 8)
-        fea_s = self.conv_main(self.gap_conv(L.branch_sum(branches)))
+        fea_s = self.conv_main(ops.pooled_branch_sum(branches, 5))   # gap_conv(sum of the branches), one pass
         fea_z = self.fc_main(self.gap_fc(fea_s).view(b, c))
         return self._heads(fea_z, b, len(branches), c)
 
@@ -336,10 +336,12 @@ class StyleBlock(nn.Module):
             self.skconv = SKStyleConv(d_latent, in_planes, in_planes, m, image_size, True)
         self.conv3 = StyleConv(d_latent, in_planes, out_planes + dense_depth, kernel_size=3)
 
-    def forward(self, x: torch.Tensor, w: torch.Tensor):
+    def forward(self, x: torch.Tensor, w: torch.Tensor, act: nn.Module = None):
+        """`act`: the per-channel PReLU the caller applies to the block's output (BasicBlock's activation_unify /
+        activation_shortcut): handed to the last StyleConv, whose fused tail applies it in the same pass."""
         t = self.conv1(x, w, self.activation1)
         t = self.conv2(t, w, self.activation2) if self.m == 1 else self.skconv(t, w)
-        return self.conv3(t, w)
+        return self.conv3(t, w, act)
 
 
 class ResnetInit(nn.Module):
@@ -436,7 +438,7 @@ class BasicBlock(nn.Module):
     def forward(self, x: torch.Tensor, w: torch.Tensor):
         d = self.out_planes
         if self.is_unify:
-            x = self.activation_unify(self.unify(x, w))
+            x = self.unify(x, w, self.activation_unify)
         head = ops.slice_channels(x, 0, d)
         dense = ops.slice_channels(x, 2 * d)
         x_res = ops.cat_channels([head, dense])
@@ -445,7 +447,7 @@ class BasicBlock(nn.Module):
         res3_head = ops.slice_channels(res3, 0, d)
         feas_residual = L.gated_residual(head, res3_head, self.se_attention_residual(res3_head))
         if self.root:
-            mid = self.activation_shortcut(self.shortcut(x, w))
+            mid = self.shortcut(x, w, self.activation_shortcut)
         else:
             mid = dense
         return ops.cat_channels([feas_residual, tra3, mid, ops.slice_channels(res3, d)])

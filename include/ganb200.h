@@ -181,6 +181,12 @@ int ganb200_ew_fma_bcast(const float* x, const float* v, const float* z, float* 
 /* out = sum x*(y or 1) over: rmode 0: HW -> [N,C];  1: N,HW -> [C];  2: C,HW -> [N];  3: all -> [1].
  * Replaces the bias/scale gradient reductions, AdaptiveAvgPool2d(1) (scaled by the caller), compute_grad2's
  * pow(2).view(B,-1).sum(1) (train/ganR2.py:36-38), torch.mean (train/wgangpR2.py:21). */
+/* AdaptiveAvgPool2d(out_size) of t0 + t1 without materialising the sum (the input of the SK attention,
+ * generators/generator_13_5.py:77-80): t0, t1 [planes, H, W] -> out [planes, out_size, out_size].  Eligible shapes
+ * (ganb200_pool_sum2_eligible): 32 x 32 and 64 x 64 planes to 5 x 5; torch's bins. */
+int ganb200_pool_sum2_eligible(int H, int W, int out_size);
+int ganb200_pool_sum2(const float* t0, const float* t1, float* out, int64_t planes, int H, int W, int out_size,
+                      void* stream);
 /* Selective-kernel merge of two branches in one pass each way: out = att[n][0][c] * t0 + att[n][1][c] * t1
  * ((feas * attention).sum(dim=1) with M = 2: generators/generator_13_5.py:169,201,294); backward g0 = att0 * g,
  * g1 = att1 * g, gatt[n][i][c] = sum_hw g * t_i.  t0, t1, out, g* : [N, C, HW]; att, gatt: [N, 2, C]. */

@@ -71,11 +71,18 @@ def _blockwise(net_cpu, types, run_cpu, precision, tol, monkeypatch, stride=1):
     try:
         net_gpu = copy.deepcopy(net_cpu).cuda()
         gpu_mods = dict(net_gpu.named_modules())
+        cpu_name = {id(m): n for n, m in net_cpu.named_modules()}
+
+        def to_gpu(a):   # tensors move; a module argument (the activation a block hands to its last layer) is mapped
+            if torch.is_tensor(a):
+                return a.cuda()
+            return gpu_mods[cpu_name[id(a)]] if isinstance(a, torch.nn.Module) else a
+
         for idx, args, want in recs[::stride]:
             mod = gpu_mods[names[idx]]
             torch.manual_seed(1000 + idx)
             with torch.no_grad():
-                got = mod(*[a.cuda() if torch.is_tensor(a) else a for a in args])
+                got = mod(*[to_gpu(a) for a in args])
             if torch.is_tensor(want):
                 worst[names[idx]] = rel(got, want)
             else:

@@ -359,6 +359,24 @@ def test_sk_merge_two_branches_fused(cu, ref, shape):
         assert rel(a, b) < 1e-5
 
 
+@pytest.mark.parametrize("shape", [(4, 48, 64, 64), (3, 7, 32, 32), (1, 1, 64, 64)])
+def test_pooled_branch_sum(cu, ref, shape):
+    """AdaptiveAvgPool2d(5)(t0 + t1) in one pass (ganb200_pool_sum2) against torch's pooling of the sum, and the op's
+    gradient against the add + pooling chain"""
+    torch.manual_seed(22)
+    t0, t1 = rnd(*shape), rnd(*shape)
+    assert cu.pool_sum2_ok(g(t0), g(t1), 5) and ref.pool_sum2_ok(t0, t1, 5)
+    assert not cu.pool_sum2_ok(g(rnd(2, 3, 16, 16)), g(rnd(2, 3, 16, 16)), 5)
+    assert rel(cu.pool_sum2(g(t0), g(t1), 5), ref.pool_sum2(t0, t1, 5)) < FP32_TOL
+    from gan_b200 import ops
+    a, b = g(t0).requires_grad_(), g(t1).requires_grad_()
+    gy = g(rnd(shape[0], shape[1], 5, 5))
+    ops.pooled_branch_sum([a, b], 5).backward(gy)
+    a2, b2 = g(t0).requires_grad_(), g(t1).requires_grad_()
+    ops.adaptive_avg_pool(ops.add(a2, b2), 5).backward(gy)
+    assert rel(a.grad, a2.grad) < FP32_TOL and rel(b.grad, b2.grad) < FP32_TOL
+
+
 def test_softmax_mbstd_bce(cu, ref):
     torch.manual_seed(7)
     x, gy = rnd(6, 2, 48), rnd(6, 2, 48)
