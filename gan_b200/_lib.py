@@ -76,6 +76,7 @@ SIGNATURES = {
     "ganb200_ew_fma_bcast": (c_int, [P, P, P, P, c_int, c_int, c_int, c_int, P]),
     "ganb200_pool_sum2_eligible": (c_int, [c_int, c_int, c_int]),
     "ganb200_pool_sum2": (c_int, [P, P, P, c_int64, c_int, c_int, c_int, P]),
+    "ganb200_sk_bwd_finish": (c_int, [P, P, P, P, P, c_int, c_int, c_int, c_int, c_int, P]),
     "ganb200_sk_merge2_fwd": (c_int, [P, P, P, P, c_int, c_int, c_int, P]),
     "ganb200_sk_merge2_bwd": (c_int, [P, P, P, P, P, P, P, c_int, c_int, c_int, P]),
     "ganb200_reduce": (c_int, [P, P, P, c_int, c_int, c_int, c_int, c_float, P]),

@@ -316,8 +316,10 @@ __global__ void __launch_bounds__(256) sk_merge2_kernel(const float* __restrict_
           const float4 w = __ldg(pg + i);
           s0 += w.x * u.x + w.y * u.y + w.z * u.z + w.w * u.w;
           s1 += w.x * v.x + w.y * v.y + w.z * v.z + w.w * v.w;
-          q0[i] = make_float4(a0 * w.x, a0 * w.y, a0 * w.z, a0 * w.w);
-          q1[i] = make_float4(a1 * w.x, a1 * w.y, a1 * w.z, a1 * w.w);
+          if (o0) {   // null: attention gradient only (the feature-map gradients are formed by sk_bwd_finish_kernel)
+            q0[i] = make_float4(a0 * w.x, a0 * w.y, a0 * w.z, a0 * w.w);
+            q1[i] = make_float4(a1 * w.x, a1 * w.y, a1 * w.z, a1 * w.w);
+          }
         } else {
           q0[i] = make_float4(fmaf(a1, v.x, a0 * u.x), fmaf(a1, v.y, a0 * u.y), fmaf(a1, v.z, a0 * u.z),
                               fmaf(a1, v.w, a0 * u.w));
@@ -330,8 +332,10 @@ __global__ void __launch_bounds__(256) sk_merge2_kernel(const float* __restrict_
           const float w = g[base + i];
           s0 = fmaf(w, u, s0);
           s1 = fmaf(w, v, s1);
-          o0[base + i] = a0 * w;
-          o1[base + i] = a1 * w;
+          if (o0) {
+            o0[base + i] = a0 * w;
+            o1[base + i] = a1 * w;
+          }
         } else {
           o0[base + i] = fmaf(a1, v, a0 * u);
         }
@@ -375,7 +379,8 @@ extern "C" int ganb200_sk_merge2_bwd(const float* g, const float* t0, const floa
                                      float* g1, float* gatt, int N, int C, int HW, void* stream) {
   const int64_t rows = (int64_t)N * C;
   if (rows * HW <= 0) return 0;
-  GB_REQUIRE(g && t0 && t1 && att && g0 && g1 && gatt, GANB200_BAD_ARG, "sk_merge2_bwd: null argument");
+  GB_REQUIRE(g && t0 && t1 && att && gatt && ((g0 == nullptr) == (g1 == nullptr)), GANB200_BAD_ARG,
+             "sk_merge2_bwd: null argument");
   GB_REQUIRE((HW & 3) != 0 || sk_aligned(g, t0, t1, g0, g1), GANB200_BAD_ARG, "sk_merge2_bwd: unaligned tensor");
   const bool block_rows = HW >= 1024;
   const int grid = (int)std::min<int64_t>(block_rows ? rows : (rows + 7) / 8, (int64_t)kNumSMs * 32);
@@ -427,6 +432,73 @@ __global__ void __launch_bounds__(256) pool_sum2_kernel(const float* __restrict_
 }
 
 }  // namespace ganb200
+
+// g_i = att[n][i][c] * g + P^T(gp) for both branches in one pass: the merge's feature-map gradients and the adjoint of
+// pool_sum2 (the same for both branches) summed where they are produced, instead of two launches plus two accumulations
+// by the autograd engine (12 passes over a feature map -> 6 with the attention-gradient pass of sk_merge2_kernel).
+// One block per plane; the OUT x OUT pooled gradients, pre-divided by their bin areas, sit in shared memory.
+namespace ganb200 {
+template <int OUT>
+__global__ void __launch_bounds__(256) sk_bwd_finish_kernel(const float* __restrict__ g, const float* __restrict__ att,
+                                                            const float* __restrict__ gp, float* __restrict__ g0,
+                                                            float* __restrict__ g1, int64_t planes, int C, int H, int W) {
+  __shared__ float sgp[OUT * OUT];
+  __shared__ int lo[2][64], hi[2][64];       // first / last bin of every row (0) and column (1); H, W <= 64
+  const int HW = H * W, Wq = W >> 2;
+  for (int i = threadIdx.x; i < H + W; i += 256) {
+    const int d = i < H ? 0 : 1, n = d ? W : H, p = d ? i - H : i;
+    int a = OUT, b = -1;
+    for (int o = 0; o < OUT; ++o) {
+      const int s = (o * n) / OUT, e = ((o + 1) * n + OUT - 1) / OUT;
+      if (p >= s && p < e) { a = min(a, o); b = max(b, o); }
+    }
+    lo[d][p] = a; hi[d][p] = b;
+  }
+  for (int64_t plane = blockIdx.x; plane < planes; plane += gridDim.x) {
+    const int64_t n = plane / C;
+    const int c = (int)(plane - n * C);
+    const float a0 = __ldg(att + (n * 2 + 0) * C + c), a1 = __ldg(att + (n * 2 + 1) * C + c);
+    __syncthreads();
+    if (threadIdx.x < OUT * OUT) {
+      const int o = threadIdx.x / OUT, j = threadIdx.x - o * OUT;
+      const int hs = (o * H) / OUT, he = ((o + 1) * H + OUT - 1) / OUT;
+      const int ws = (j * W) / OUT, we = ((j + 1) * W + OUT - 1) / OUT;
+      sgp[threadIdx.x] = __ldg(gp + plane * (OUT * OUT) + threadIdx.x) / (float)((he - hs) * (we - ws));
+    }
+    __syncthreads();
+    const float4* pg = reinterpret_cast<const float4*>(g + plane * HW);
+    float4* q0 = reinterpret_cast<float4*>(g0 + plane * HW);
+    float4* q1 = reinterpret_cast<float4*>(g1 + plane * HW);
+    for (int q = threadIdx.x; q < (HW >> 2); q += 256) {
+      const int h = q / Wq, w0 = (q - h * Wq) << 2;
+      const float4 v = __ldg(pg + q);
+      float up[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        float t = 0.f;
+        for (int o = lo[0][h]; o <= hi[0][h]; ++o)
+          for (int j = lo[1][w0 + k]; j <= hi[1][w0 + k]; ++j) t += sgp[o * OUT + j];
+        up[k] = t;
+      }
+      q0[q] = make_float4(fmaf(a0, v.x, up[0]), fmaf(a0, v.y, up[1]), fmaf(a0, v.z, up[2]), fmaf(a0, v.w, up[3]));
+      q1[q] = make_float4(fmaf(a1, v.x, up[0]), fmaf(a1, v.y, up[1]), fmaf(a1, v.z, up[2]), fmaf(a1, v.w, up[3]));
+    }
+  }
+}
+}  // namespace ganb200
+
+extern "C" int ganb200_sk_bwd_finish(const float* g, const float* att, const float* gp, float* g0, float* g1, int N, int C,
+                                     int H, int W, int out_size, void* stream) {
+  const int64_t planes = (int64_t)N * C;
+  if (planes <= 0) return 0;
+  GB_REQUIRE(g && att && gp && g0 && g1, GANB200_BAD_ARG, "sk_bwd_finish: null argument");
+  GB_REQUIRE(out_size == 5 && H == W && (W == 32 || W == 64), GANB200_BAD_SHAPE, "sk_bwd_finish: 32x32 or 64x64 planes, 5x5 pooling");
+  GB_REQUIRE(((((uintptr_t)g) | ((uintptr_t)g0) | ((uintptr_t)g1)) & 15) == 0, GANB200_BAD_ARG, "sk_bwd_finish: unaligned tensor");
+  const int grid = (int)std::min<int64_t>(planes, (int64_t)kNumSMs * 32);
+  sk_bwd_finish_kernel<5><<<grid, 256, 0, (cudaStream_t)stream>>>(g, att, gp, g0, g1, planes, C, H, W);
+  GB_CHECK_LAUNCH();
+  return 0;
+}
 
 extern "C" int ganb200_pool_sum2_eligible(int H, int W, int out_size) {
   return out_size == 5 && H == W && (W == 32 || W == 64);   // W threads per plane must cover the 25 outputs

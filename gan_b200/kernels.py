@@ -391,6 +391,15 @@ class CudaBackend:
         _lib.check(self.lib.ganb200_pool_sum2(self._p(t0), self._p(t1), self._p(y), N * C, H, W, out, st))
         return y
 
+    def sk_bwd_finish(self, g, att, gp):
+        """g_i = att[:, i] * g + adjoint of AdaptiveAvgPool2d(gp.shape[-1]) applied to gp -> (g0, g1)"""
+        N, C, H, W = g.shape
+        st = self._prep(g, att, gp)
+        g0, g1 = torch.empty_like(g), torch.empty_like(g)
+        _lib.check(self.lib.ganb200_sk_bwd_finish(self._p(g), self._p(att), self._p(gp), self._p(g0), self._p(g1), N, C, H,
+                                                  W, gp.shape[-1], st))
+        return g0, g1
+
     def sk_merge2_fwd(self, t0, t1, att):
         """att[:, 0] * t0 + att[:, 1] * t1, att: [N, 2, C] contiguous"""
         N, C, HW = _nchw(t0)
@@ -399,11 +408,11 @@ class CudaBackend:
         _lib.check(self.lib.ganb200_sk_merge2_fwd(self._p(t0), self._p(t1), self._p(att), self._p(out), N, C, HW, st))
         return out
 
-    def sk_merge2_bwd(self, g, t0, t1, att):
-        """-> (g_t0, g_t1, g_att[N, 2, C])"""
+    def sk_merge2_bwd(self, g, t0, t1, att, att_only=False):
+        """-> (g_t0, g_t1, g_att[N, 2, C]); att_only: (None, None, g_att)"""
         N, C, HW = _nchw(t0)
         st = self._prep(g, t0, t1, att)
-        g0, g1 = torch.empty_like(t0), torch.empty_like(t1)
+        g0, g1 = (None, None) if att_only else (torch.empty_like(t0), torch.empty_like(t1))
         gatt = torch.empty((N, 2, C), dtype=torch.float32, device=t0.device)
         _lib.check(self.lib.ganb200_sk_merge2_bwd(self._p(g), self._p(t0), self._p(t1), self._p(att), self._p(g0),
                                                   self._p(g1), self._p(gatt), N, C, HW, st))

@@ -240,27 +240,52 @@ class FmaBcFn(Function):
         return g, gv, gz, None
 
 
+class _SkLink:
+    """Couples the two autograd nodes that consume the branches of one SK block (PoolSum2Fn: the attention's input;
+    SkMerge2Fn: the merge).  Autograd always runs the merge's backward first (the attention weights depend on the pooled
+    sum), then the attention network's, then the pooling's.  With the link the merge's backward only forms the attention
+    gradient and parks the incoming gradient here; the pooling's backward then writes att_i * g + P^T(g_pooled) for both
+    branches in one pass (ganb200_sk_bwd_finish) — instead of five passes over a feature map in the merge's backward, one
+    in the pooling's and six more in the engine's two accumulations."""
+    __slots__ = ("parked", "merged")
+
+    def __init__(self):
+        self.parked = None      # (g, att) left by SkMerge2Fn.backward for PoolSum2Fn.backward
+        self.merged = False     # a SkMerge2Fn took this link in the forward pass
+
+
 class PoolSum2Fn(Function):
     """AdaptiveAvgPool2d(out)(t0 + t1) in one pass over the two branches (the SK attention's input,
     generators/generator_13_5.py:77-80); both branches receive the same gradient, the adjoint of the pooling."""
 
     @staticmethod
-    def forward(ctx, t0, t1, out):
-        ctx.side, ctx.out = t0.shape[-1], out
+    def forward(ctx, t0, t1, out, link):
+        ctx.side, ctx.out, ctx.link = t0.shape[-1], out, link
         return K().pool_sum2(_c(t0), _c(t1), out)
 
     @staticmethod
-    def backward(ctx, g):
+    def backward(ctx, gp):
+        link = ctx.link
+        if link is not None and link.parked is not None and not torch.is_grad_enabled():
+            g, att = link.parked
+            link.parked = None
+            g0, g1 = K().sk_bwd_finish(g, att, _c(gp))
+            return g0, g1, None, None
         op = RS.adaptive_avg(ctx.side, ctx.out).T
-        gx = Resample2dFn.apply(_c(g), op, op)
-        return gx, gx, None
+        gx = Resample2dFn.apply(_c(gp), op, op)
+        return gx, gx, None, None
 
 
 def pooled_branch_sum(branches, out):
     """AdaptiveAvgPool2d(out)(sum of the branches)"""
     if (len(branches) == 2 and os.environ.get("GANB200_POOL_SUM_FUSED", "1") != "0"
             and K().pool_sum2_ok(branches[0], branches[1], out)):
-        return PoolSum2Fn.apply(branches[0], branches[1], out)
+        link = None
+        if (torch.is_grad_enabled() and branches[0].requires_grad and branches[1].requires_grad
+                and os.environ.get("GANB200_SK_BWD_FUSED", "1") != "0"):
+            link = _SkLink()
+            branches[0]._gb_sk_link = link      # picked up by sk_merge2 on the same branch tensors
+        return PoolSum2Fn.apply(branches[0], branches[1], out, link)
     acc = branches[0]
     for t in branches[1:]:
         acc = add(acc, t)
@@ -272,9 +297,12 @@ class SkMerge2Fn(Function):
     create_graph the backward is rebuilt from the twice-differentiable broadcast ops."""
 
     @staticmethod
-    def forward(ctx, t0, t1, att):
+    def forward(ctx, t0, t1, att, link):
         t0, t1, att = _c(t0), _c(t1), _c(att)
         ctx.save_for_backward(t0, t1, att)
+        ctx.link = link
+        if link is not None:
+            link.merged = True
         return K().sk_merge2_fwd(t0, t1, att)
 
     @staticmethod
@@ -285,13 +313,25 @@ class SkMerge2Fn(Function):
             a0, a1 = att[:, 0].contiguous(), att[:, 1].contiguous()
             g0, g1 = MulBcFn.apply(g, a0, KN.V_NC), MulBcFn.apply(g, a1, KN.V_NC)
             s0, s1 = ReduceFn.apply(g, t0, KN.R_HW, 1.0), ReduceFn.apply(g, t1, KN.R_HW, 1.0)
-            return g0, g1, torch.stack([s0, s1], 1)
+            return g0, g1, torch.stack([s0, s1], 1), None
+        link = ctx.link
+        # deferred form: needs the attention gradient to travel back to the pooled sum (it always does in the SK block:
+        # the attention weights are a function of it), which is what makes PoolSum2Fn.backward run after this one
+        if (link is not None and ctx.needs_input_grad[0] and ctx.needs_input_grad[1] and ctx.needs_input_grad[2]):
+            _, _, gatt = K().sk_merge2_bwd(g, t0, t1, att, att_only=True)
+            link.parked = (g, att)
+            return None, None, gatt, None
         g0, g1, gatt = K().sk_merge2_bwd(g, t0, t1, att)
-        return g0, g1, gatt
+        return g0, g1, gatt, None
 
 
 def sk_merge2(t0, t1, att):
-    return SkMerge2Fn.apply(t0, t1, att)
+    link = getattr(t0, "_gb_sk_link", None)
+    if link is not None:
+        del t0._gb_sk_link
+        if not (att.requires_grad and torch.is_grad_enabled()):
+            link = None
+    return SkMerge2Fn.apply(t0, t1, att, link)
 
 
 # =====================================================================================================

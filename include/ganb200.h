@@ -187,9 +187,16 @@ int ganb200_ew_fma_bcast(const float* x, const float* v, const float* z, float* 
 int ganb200_pool_sum2_eligible(int H, int W, int out_size);
 int ganb200_pool_sum2(const float* t0, const float* t1, float* out, int64_t planes, int H, int W, int out_size,
                       void* stream);
+/* Backward of the SK block's two uses of its branches in one pass: g_i = att[n][i][c] * g + P^T(gp), i = 0, 1, with P the
+ * AdaptiveAvgPool2d(out_size) of ganb200_pool_sum2, g the gradient of the merged map [N, C, H, W] and gp the gradient of
+ * the pooled sum [N, C, out_size, out_size] (ganb200_sk_merge2_bwd with g0 = g1 = NULL supplies the attention gradient
+ * alone).  32 x 32 and 64 x 64 planes, out_size 5. */
+int ganb200_sk_bwd_finish(const float* g, const float* att, const float* gp, float* g0, float* g1, int N, int C, int H,
+                          int W, int out_size, void* stream);
 /* Selective-kernel merge of two branches in one pass each way: out = att[n][0][c] * t0 + att[n][1][c] * t1
  * ((feas * attention).sum(dim=1) with M = 2: generators/generator_13_5.py:169,201,294); backward g0 = att0 * g,
- * g1 = att1 * g, gatt[n][i][c] = sum_hw g * t_i.  t0, t1, out, g* : [N, C, HW]; att, gatt: [N, 2, C]. */
+ * g1 = att1 * g, gatt[n][i][c] = sum_hw g * t_i.  t0, t1, out, g* : [N, C, HW]; att, gatt: [N, 2, C].  g0 = g1 = NULL:
+ * gatt only. */
 int ganb200_sk_merge2_fwd(const float* t0, const float* t1, const float* att, float* out, int N, int C, int HW,
                           void* stream);
 int ganb200_sk_merge2_bwd(const float* g, const float* t0, const float* t1, const float* att, float* g0, float* g1,

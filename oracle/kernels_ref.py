@@ -122,12 +122,23 @@ class RefBackend:
         sh = (t0.shape[0], t0.shape[1]) + (1,) * (t0.dim() - 2)
         return (a[:, 0].reshape(sh) * t0 + a[:, 1].reshape(sh) * t1).contiguous()
 
-    def sk_merge2_bwd(self, g, t0, t1, att):
+    def sk_bwd_finish(self, g, att, gp):
+        x = torch.zeros_like(g).requires_grad_()
+        with torch.enable_grad():
+            y = torch.nn.functional.adaptive_avg_pool2d(x, gp.shape[-1])
+        (up,) = torch.autograd.grad(y, x, gp)
+        a = att.reshape(att.shape[0], 2, -1)
+        sh = (g.shape[0], g.shape[1], 1, 1)
+        return (a[:, 0].reshape(sh) * g + up).contiguous(), (a[:, 1].reshape(sh) * g + up).contiguous()
+
+    def sk_merge2_bwd(self, g, t0, t1, att, att_only=False):
         a = att.reshape(att.shape[0], 2, -1)
         sh = (t0.shape[0], t0.shape[1]) + (1,) * (t0.dim() - 2)
         dims = tuple(range(2, t0.dim()))
         s0 = (g * t0).sum(dims) if dims else g * t0
         s1 = (g * t1).sum(dims) if dims else g * t1
+        if att_only:
+            return None, None, torch.stack([s0, s1], 1).contiguous()
         return ((a[:, 0].reshape(sh) * g).contiguous(), (a[:, 1].reshape(sh) * g).contiguous(),
                 torch.stack([s0, s1], 1).contiguous())
 

@@ -377,6 +377,38 @@ def test_pooled_branch_sum(cu, ref, shape):
     assert rel(a.grad, a2.grad) < FP32_TOL and rel(b.grad, b2.grad) < FP32_TOL
 
 
+@pytest.mark.parametrize("shape", [(4, 48, 64, 64), (3, 7, 32, 32)])
+def test_sk_block_backward_in_one_pass(cu, ref, shape):
+    """ganb200_sk_bwd_finish (att_i * g + adjoint of the 5x5 pooling, both branches) against the oracle, and a whole SK
+    block — pooled sum -> attention weights -> merge — with the linked backward against the unlinked one"""
+    torch.manual_seed(23)
+    N, C = shape[:2]
+    gy, gp = rnd(*shape), rnd(N, C, 5, 5)
+    att = torch.softmax(rnd(N, 2, C), dim=1).contiguous()
+    got = cu.sk_bwd_finish(g(gy), g(att), g(gp))
+    want = ref.sk_bwd_finish(gy, att, gp)
+    for a, b in zip(got, want):
+        assert rel(a, b) < FP32_TOL
+    _, _, gatt = cu.sk_merge2_bwd(g(gy), g(rnd(*shape)), g(rnd(*shape)), g(att), att_only=True)
+    assert gatt.shape == (N, 2, C)
+    from gan_b200 import layers as L
+    from gan_b200 import ops
+    t0, t1, wmix = rnd(*shape), rnd(*shape), rnd(2, 25)
+    grads = {}
+    for linked in ("1", "0"):
+        os.environ["GANB200_SK_BWD_FUSED"] = linked
+        a, b, wm = g(t0).requires_grad_(), g(t1).requires_grad_(), g(wmix).requires_grad_()
+        branches = [a, b]
+        pooled = ops.pooled_branch_sum(branches, 5)                       # [N, C, 5, 5]
+        logits = torch.einsum("ncp,mp->nmc", pooled.reshape(N, C, 25), wm)  # a stand-in for the attention network
+        y = L.sk_merge(branches, torch.softmax(logits, dim=1).reshape(N, 2, C, 1, 1))
+        y.backward(g(gy))
+        grads[linked] = [y.detach(), a.grad, b.grad, wm.grad]
+    os.environ.pop("GANB200_SK_BWD_FUSED")
+    for u, v in zip(grads["1"], grads["0"]):
+        assert rel(u, v) < 1e-5
+
+
 def test_softmax_mbstd_bce(cu, ref):
     torch.manual_seed(7)
     x, gy = rnd(6, 2, 48), rnd(6, 2, 48)
