@@ -81,22 +81,41 @@ __global__ void __launch_bounds__(256) demod_kernel(const float* __restrict__ s,
 }
 
 // gs[b,i] = gs1[b,i] + 2*s[b,i]*alpha^2 * sum_o dd[b,o]*wsq[o,i],  dd[b,o] = -0.5*Ad[b,o]*sinv[b,o]^2
+// One block = DEMOD_BS samples x 128 input channels: every wsq element a thread loads serves DEMOD_BS samples (one block
+// per sample re-read the whole wsq matrix B times through L2: 600 MB for a 768-channel layer at B = 256).
+constexpr int DEMOD_BS = 8;
 __global__ void __launch_bounds__(128) demod_bwd_s_kernel(const float* __restrict__ gs1, const float* __restrict__ s,
                                                           const float* __restrict__ Ad, const float* __restrict__ sinv,
-                                                          const float* __restrict__ wsq, float* __restrict__ gs, int C,
-                                                          int K, float alpha2) {
-  extern __shared__ float dd[];
-  const int b = blockIdx.x;
-  for (int o = threadIdx.x; o < K; o += 128) {
-    float si = sinv[(int64_t)b * K + o];
-    dd[o] = -0.5f * Ad[(int64_t)b * K + o] * si * si;
+                                                          const float* __restrict__ wsq, float* __restrict__ gs, int B,
+                                                          int C, int K, float alpha2) {
+  extern __shared__ float dd[];   // [DEMOD_BS][K]
+  const int b0 = blockIdx.x * DEMOD_BS;
+  for (int e = threadIdx.x; e < DEMOD_BS * K; e += 128) {
+    const int j = e / K, o = e - j * K;
+    float v = 0.f;
+    if (b0 + j < B) {
+      const float si = sinv[(int64_t)(b0 + j) * K + o];
+      v = -0.5f * Ad[(int64_t)(b0 + j) * K + o] * si * si;
+    }
+    dd[e] = v;
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < C; i += 128) {
-    float acc = 0.f;
-    for (int o = 0; o < K; ++o) acc = fmaf(dd[o], wsq[(int64_t)o * C + i], acc);
-    int64_t idx = (int64_t)b * C + i;
-    gs[idx] = (gs1 ? gs1[idx] : 0.f) + 2.f * s[idx] * alpha2 * acc;
+  const int i = blockIdx.y * 128 + threadIdx.x;
+  if (i >= C) return;
+  float acc[DEMOD_BS];
+#pragma unroll
+  for (int j = 0; j < DEMOD_BS; ++j) acc[j] = 0.f;
+  for (int o = 0; o < K; ++o) {
+    const float w = __ldg(wsq + (int64_t)o * C + i);
+#pragma unroll
+    for (int j = 0; j < DEMOD_BS; ++j) acc[j] = fmaf(dd[j * K + o], w, acc[j]);
+  }
+#pragma unroll
+  for (int j = 0; j < DEMOD_BS; ++j) {
+    if (b0 + j < B) {
+      const int64_t idx = (int64_t)(b0 + j) * C + i;
+      gs[idx] = (gs1 ? gs1[idx] : 0.f) + 2.f * s[idx] * alpha2 * acc[j];
+    }
   }
 }
 
@@ -263,7 +282,10 @@ extern "C" int ganb200_demod(const float* s, const float* wsq, float* sinv, int 
 
 extern "C" int ganb200_demod_bwd_s(const float* gs1, const float* s, const float* Ad, const float* sinv,
                                    const float* wsq, float* gs, int B, int C, int K, float alpha, void* stream) {
-  demod_bwd_s_kernel<<<B, 128, sizeof(float) * K, GB_S(stream)>>>(gs1, s, Ad, sinv, wsq, gs, C, K, alpha * alpha);
+  GB_REQUIRE((size_t)DEMOD_BS * K * sizeof(float) <= 48 * 1024, GANB200_BAD_SHAPE, "demod_bwd_s: more than 1536 output channels");
+  dim3 grid((B + DEMOD_BS - 1) / DEMOD_BS, (C + 127) / 128);
+  demod_bwd_s_kernel<<<grid, 128, sizeof(float) * DEMOD_BS * K, GB_S(stream)>>>(gs1, s, Ad, sinv, wsq, gs, B, C, K,
+                                                                                alpha * alpha);
   GB_CHECK_LAUNCH();
   return 0;
 }
