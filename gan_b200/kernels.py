@@ -379,6 +379,39 @@ class CudaBackend:
         _lib.check(self.lib.ganb200_ew_fma_bcast(self._p(x), self._p(v), self._p(z), self._p(y), N, C, HW, vmode, st))
         return y
 
+    def bmm(self, a, b, ta=False, tb=False, alpha=1.0):
+        """batched op(a) @ op(b) for contiguous 3-D fp32 tensors; ta / tb transpose the last two dimensions of a / b
+        (by strides: nothing is copied)"""
+        if a.dim() != 3 or b.dim() != 3 or a.shape[0] != b.shape[0]:
+            raise _lib.GanB200Error(f"bmm: need two 3-D tensors with one batch size, got {tuple(a.shape)} {tuple(b.shape)}")
+        st = self._prep(a, b)
+        Bn = a.shape[0]
+        M, Ka = (a.shape[2], a.shape[1]) if ta else (a.shape[1], a.shape[2])
+        Kb, N = (b.shape[2], b.shape[1]) if tb else (b.shape[1], b.shape[2])
+        if Ka != Kb:
+            raise _lib.GanB200Error(f"bmm: inner dimensions differ ({Ka} vs {Kb})")
+        sam, sak = (1, a.shape[2]) if ta else (a.shape[2], 1)
+        sbk, sbn = (1, b.shape[2]) if tb else (b.shape[2], 1)
+        c = torch.empty((Bn, M, N), dtype=torch.float32, device=a.device)
+        _lib.check(self.lib.ganb200_bmm(self._p(a), self._p(b), self._p(c), Bn, M, N, Ka, a.shape[1] * a.shape[2], sam,
+                                        sak, b.shape[1] * b.shape[2], sbk, sbn, float(alpha), st))
+        return c
+
+    def softmax_rows_fwd(self, x):
+        """softmax over the last dimension"""
+        st = self._prep(x)
+        y = torch.empty_like(x)
+        n = x.shape[-1]
+        _lib.check(self.lib.ganb200_softmax_rows_fwd(self._p(x), self._p(y), x.numel() // max(n, 1), n, st))
+        return y
+
+    def softmax_rows_bwd(self, gy, y):
+        st = self._prep(gy, y)
+        gx = torch.empty_like(y)
+        n = y.shape[-1]
+        _lib.check(self.lib.ganb200_softmax_rows_bwd(self._p(gy), self._p(y), self._p(gx), y.numel() // max(n, 1), n, st))
+        return gx
+
     def pool_sum2_ok(self, t0, t1, out):
         return (t0.dim() == 4 and t0.shape == t1.shape and t0.dtype == torch.float32 and
                 bool(self.lib.ganb200_pool_sum2_eligible(t0.shape[-2], t0.shape[-1], out)))

@@ -296,6 +296,18 @@ def sk_merge(branches, att):
     return out
 
 
+def self_attention(f, g, h):
+    """SAGAN attention of discriminators/discriminator_9_3.py:70-77 on (B, C', H, W) query / key / value maps:
+    s = f^T g (B, N, N), beta = softmax(s, dim=1), v = h beta, returned as (B, C', H, W).
+    softmax over dim 1 of s is the row softmax of s^T = g^T f, and h beta = h (beta^T)^T — so the attention map is only
+    ever held transposed and the two products read their operands through strides."""
+    b, c, hh, ww = h.shape
+    n = hh * ww
+    f3, g3, h3 = f.reshape(b, -1, n), g.reshape(b, -1, n), h.reshape(b, -1, n)
+    beta_t = ops.softmax_rows(ops.bmm(g3, f3, True, False))      # [b, j, i] = softmax_i(s[b, i, j])
+    return ops.bmm(h3, beta_t, False, True).reshape(b, c, hh, ww)
+
+
 def gate(x, g):
     """x * g with g:(b,c,1,1) — the SE product (discriminator_9_4.py:160, generator_13_5.py:457)."""
     b, c = x.shape[:2]

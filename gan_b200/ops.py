@@ -240,6 +240,62 @@ class FmaBcFn(Function):
         return g, gv, gz, None
 
 
+class BmmFn(Function):
+    """torch.bmm(op(a), op(b)) (discriminators/discriminator_9_3.py:74,76).  Every derivative of a matrix product is a
+    matrix product of (transposed) operands, so the backward is written with BmmFn itself: any order of differentiation."""
+
+    @staticmethod
+    def forward(ctx, a, b, ta, tb):
+        a, b = _c(a), _c(b)
+        ctx.save_for_backward(a, b)
+        ctx.ta, ctx.tb = ta, tb
+        return K().bmm(a, b, ta, tb)
+
+    @staticmethod
+    def backward(ctx, g):
+        a, b = ctx.saved_tensors
+        ta, tb = ctx.ta, ctx.tb
+        ga = gb = None
+        if ctx.needs_input_grad[0]:
+            # C = A' B'  ->  dA' = g B'^T ;  stored a is A' or A'^T
+            ga = BmmFn.apply(b, g, tb, True) if ta else BmmFn.apply(g, b, False, not tb)
+        if ctx.needs_input_grad[1]:
+            gb = BmmFn.apply(g, a, True, ta) if tb else BmmFn.apply(a, g, not ta, False)
+        return ga, gb, None, None
+
+
+def bmm(a, b, ta=False, tb=False):
+    return BmmFn.apply(a, b, ta, tb)
+
+
+class SoftmaxRowsFn(Function):
+    """softmax over the last dimension.  nn.Softmax(dim=1) of the reference's attention map s[b, i, j] is this op on the
+    transposed map (see layers.self_attention)."""
+
+    @staticmethod
+    def forward(ctx, x):
+        y = K().softmax_rows_fwd(_c(x))
+        ctx.save_for_backward(y)
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        (y,) = ctx.saved_tensors
+        if not torch.is_grad_enabled():
+            return K().softmax_rows_bwd(_c(gy), y)
+        # create_graph (the critic's penalties): gx = y * (gy - sum_j gy_j y_j) with twice-differentiable ops on the saved
+        # OUTPUT, whose own graph leads back through this Function
+        shape = y.shape
+        rows = y.numel() // shape[-1]
+        y3, g3 = y.reshape(1, rows, shape[-1]), _c(gy).reshape(1, rows, shape[-1])
+        dot = ReduceFn.apply(g3, y3, KN.R_HW, 1.0)                                  # [1, rows]: sum_j gy_j y_j
+        return MulFn.apply(y3, AddBcFn.apply(g3, affine(dot, -1.0, 0.0), KN.V_NC)).reshape(shape)
+
+
+def softmax_rows(x):
+    return SoftmaxRowsFn.apply(x)
+
+
 class _SkLink:
     """Couples the two autograd nodes that consume the branches of one SK block (PoolSum2Fn: the attention's input;
     SkMerge2Fn: the merge).  Autograd always runs the merge's backward first (the attention weights depend on the pooled

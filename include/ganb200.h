@@ -181,6 +181,15 @@ int ganb200_ew_fma_bcast(const float* x, const float* v, const float* z, float* 
 /* out = sum x*(y or 1) over: rmode 0: HW -> [N,C];  1: N,HW -> [C];  2: C,HW -> [N];  3: all -> [1].
  * Replaces the bias/scale gradient reductions, AdaptiveAvgPool2d(1) (scaled by the caller), compute_grad2's
  * pow(2).view(B,-1).sum(1) (train/ganR2.py:36-38), torch.mean (train/wgangpR2.py:21). */
+/* Self-attention of the discriminator_9 family (discriminators/discriminator_9_3.py:58-80: torch.bmm, nn.Softmax).
+ * ganb200_bmm: c[b][m][n] = alpha * sum_k A[b][m][k] * B[b][k][n], fp32, c contiguous [batch][M][N]; the operands are
+ * addressed through element strides (A[b][m][k] = a[b * sab + m * sam + k * sak], B[b][k][n] = b[b * sbb + k * sbk +
+ * n * sbn]), so the transposes of the forward, backward and double-backward products need no copy.
+ * ganb200_softmax_rows_fwd / _bwd: softmax over the last dimension of [rows][n]; gx = y * (gy - sum(gy * y)). */
+int ganb200_bmm(const float* a, const float* b, float* c, int batch, int M, int N, int K, int64_t sab, int64_t sam,
+                int64_t sak, int64_t sbb, int64_t sbk, int64_t sbn, float alpha, void* stream);
+int ganb200_softmax_rows_fwd(const float* x, float* y, int64_t rows, int n, void* stream);
+int ganb200_softmax_rows_bwd(const float* gy, const float* y, float* gx, int64_t rows, int n, void* stream);
 /* AdaptiveAvgPool2d(out_size) of t0 + t1 without materialising the sum (the input of the SK attention,
  * generators/generator_13_5.py:77-80): t0, t1 [planes, H, W] -> out [planes, out_size, out_size].  Eligible shapes
  * (ganb200_pool_sum2_eligible): 32 x 32 and 64 x 64 planes to 5 x 5; torch's bins. */

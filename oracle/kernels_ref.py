@@ -110,6 +110,17 @@ class RefBackend:
     def ew_fma_bcast(self, x, v, z, vmode):
         return (x + _v(x, v, vmode) * z).contiguous()
 
+    def bmm(self, a, b, ta=False, tb=False, alpha=1.0):
+        a = a.transpose(1, 2) if ta else a
+        b = b.transpose(1, 2) if tb else b
+        return (alpha * torch.bmm(a, b)).contiguous()
+
+    def softmax_rows_fwd(self, x):
+        return torch.softmax(x, dim=-1).contiguous()
+
+    def softmax_rows_bwd(self, gy, y):
+        return (y * (gy - (gy * y).sum(-1, keepdim=True))).contiguous()
+
     def pool_sum2_ok(self, t0, t1, out):
         return (t0.dim() == 4 and t0.shape == t1.shape and out == 5 and t0.shape[-1] == t0.shape[-2]
                 and t0.shape[-1] in (32, 64))

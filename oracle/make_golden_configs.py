@@ -77,6 +77,11 @@ CONFIGS = {
     "clip": dict(gen="generators.generator_2", g_args=lambda: (1, 256, 64, 3), g_kw={},
                  dis="discriminators.discriminator_8", d_args=lambda: (6,), d_kw={},
                  train="train.wgan", B=4, names=("G2", "D8")),
+    # the self-attention critic (SAGAN attention after the stem at 64x64 and at 16x16) under R1 + R2 + GP: torch.bmm and
+    # nn.Softmax(dim=1) differentiated twice
+    "attn9_3": dict(gen="generators.generator_2", g_args=lambda: (1, 256, 64, 3), g_kw={},
+                    dis="discriminators.discriminator_9_3", d_args=lambda: (), d_kw={},
+                    train="train.wgangpR2", B=4, names=("G2", "D9_3")),
     # the same BatchNorm critic under R1 + R2: the penalties differentiate 27 BatchNorms twice
     "rir_r1": dict(gen="generators.generator_2", g_args=lambda: (1, 256, 64, 3), g_kw={},
                    dis="discriminators.discriminator_5", d_args=lambda: (), d_kw={},

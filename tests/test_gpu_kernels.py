@@ -409,6 +409,54 @@ def test_sk_block_backward_in_one_pass(cu, ref, shape):
         assert rel(u, v) < 1e-5
 
 
+@pytest.mark.parametrize("shape", [(3, 70, 45, 33), (2, 4096, 32, 130), (1, 5, 7, 1), (4, 64, 64, 64)])
+def test_bmm_all_transposes(cu, ref, shape):
+    """ganb200_bmm (strided batched fp32 product) against torch.bmm for the four transpose combinations"""
+    torch.manual_seed(24)
+    B, M, K, N = shape
+    for ta in (False, True):
+        for tb in (False, True):
+            a = rnd(B, K, M) if ta else rnd(B, M, K)
+            b = rnd(B, N, K) if tb else rnd(B, K, N)
+            got = cu.bmm(g(a), g(b), ta, tb, 0.5)
+            assert got.shape == (B, M, N)
+            assert rel(got, ref.bmm(a, b, ta, tb, 0.5)) < FP32_TOL, (ta, tb)
+
+
+@pytest.mark.parametrize("shape", [(2, 37, 4096), (3, 5, 1), (1, 300, 257)])
+def test_softmax_rows(cu, ref, shape):
+    torch.manual_seed(25)
+    x, gy = rnd(*shape) * 3, rnd(*shape)
+    y = cu.softmax_rows_fwd(g(x))
+    y_r = ref.softmax_rows_fwd(x)
+    assert rel(y, y_r) < FP32_TOL
+    assert rel(cu.softmax_rows_bwd(g(gy), y), ref.softmax_rows_bwd(gy, y_r)) < 1e-5
+
+
+def test_self_attention_double_backward(cu):
+    """layers.self_attention (bmm -> row softmax -> bmm) against the reference's formulation in torch ops, through a
+    gradient penalty (create_graph): discriminators/discriminator_9_3.py:70-77"""
+    from gan_b200 import layers as L
+    torch.manual_seed(26)
+    B, C, H, W = 2, 6, 8, 8
+    f, k, h = (rnd(B, C, H, W) for _ in range(3))
+
+    def ref_attention(f, k, h):
+        n = H * W
+        s = torch.bmm(f.view(B, -1, n).permute(0, 2, 1), k.view(B, -1, n))
+        return torch.bmm(h.view(B, -1, n), torch.softmax(s, dim=1)).view(B, -1, H, W)
+
+    res = {}
+    for tag, fn, dev in (("ours", L.self_attention, "cuda"), ("ref", ref_attention, "cpu")):
+        ff, kk, hh = (t.clone().to(dev).requires_grad_() for t in (f, k, h))
+        out = fn(ff, kk, hh)
+        (gf,) = torch.autograd.grad((out * out).sum(), ff, create_graph=True)
+        pen = (gf * gf).sum()
+        res[tag] = [out.detach()] + list(torch.autograd.grad(pen, [ff, kk, hh]))
+    for a, b in zip(res["ours"], res["ref"]):
+        assert rel(a, b) < 1e-4
+
+
 def test_softmax_mbstd_bce(cu, ref):
     torch.manual_seed(7)
     x, gy = rnd(6, 2, 48), rnd(6, 2, 48)

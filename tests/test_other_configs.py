@@ -26,8 +26,11 @@ NOISE_PARAMS["rir_r1"] = NOISE_PARAMS["rir_bce"]
 # Adam's eps: update norms 0.0013 / 0.0024 here / in the reference against 0.009 for a full sign step.
 NOISE_PARAMS["style_d"] = re.compile(r"^blocks\.3\.(residual\.1|block\.2)\.bias$")
 NOISE_PARAMS["lazy_r2"] = NOISE_PARAMS["clip"] = NOISE_PARAMS["style_d"]  # the same critic
-NOISE_IN_D = ("rir_bce", "rir_r1", "style_d", "lazy_r2", "clip")
-ZOO = ["dcgan", "sn3", "shuffle", "rir_gp", "rir_sn", "rir_bce", "rir_r1", "style_d", "dense4", "lazy", "lazy_r2", "clip"]  # SURVEY §8(f) rank 3 pairs (make_golden_configs.py)
+# attn9_3: the query bias of a self-attention layer adds b^T g_j to every s[i, j] — constant along the softmax dimension, so
+# its gradient is analytically zero (reference: discriminators/discriminator_9_3.py:74-75)
+NOISE_PARAMS["attn9_3"] = re.compile(r"\.query\.bias$")
+NOISE_IN_D = ("rir_bce", "rir_r1", "style_d", "lazy_r2", "clip", "attn9_3")
+ZOO = ["dcgan", "sn3", "shuffle", "rir_gp", "rir_sn", "rir_bce", "rir_r1", "style_d", "dense4", "lazy", "lazy_r2", "clip", "attn9_3"]  # SURVEY §8(f) rank 3 pairs (make_golden_configs.py)
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 

@@ -2,13 +2,15 @@
 discriminator / critic and moves it to `device`, same names and argument lists.  Lazy imports: a family this repo does
 not carry (outside SURVEY §8(a)) raises NotImplementedError when asked for, not at import.
 
-`get_9_4` is an addition (the reference's main.py builds discriminator_9_4 by hand)."""
+`get_9_4` is an addition (the reference's main.py builds discriminator_9_4 by hand).  discriminator_9_2 / _9_3 have no
+factory in the reference either; they are importable modules (`discriminators.discriminator_9_3.Discriminator()`)."""
 import importlib
 import math
 
 _CARRIED = ("discriminator_1", "discriminator_2", "discriminator_3_wgangp", "discriminator_3_wgangp_progan",
             "discriminator_3_wgangpsn", "discriminator_4", "discriminator_5", "discriminator_5_wgangp", "discriminator_5_wgangpsn",
-            "discriminator_7_wgangp", "discriminator_7_wgangpsn", "discriminator_8", "discriminator_9_4")
+            "discriminator_7_wgangp", "discriminator_7_wgangpsn", "discriminator_8", "discriminator_9", "discriminator_9_2",
+            "discriminator_9_3", "discriminator_9_4")
 
 
 def _module(name):
