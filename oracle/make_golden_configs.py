@@ -82,6 +82,11 @@ CONFIGS = {
     "attn9_3": dict(gen="generators.generator_2", g_args=lambda: (1, 256, 64, 3), g_kw={},
                     dis="discriminators.discriminator_9_3", d_args=lambda: (), d_kw={},
                     train="train.wgangpR2", B=4, names=("G2", "D9_3")),
+    # the selective-kernel critic (skip and conv paths merged by SK attention) under R1 + R2 + GP: pooled branch sum,
+    # attention trunk, softmax across the two heads and the merge, all differentiated twice
+    "sk9_small": dict(gen="generators.generator_2", g_args=lambda: (1, 256, 64, 3), g_kw={},
+                      dis="discriminators.discriminator_9_small", d_args=lambda: (), d_kw={},
+                      train="train.wgangpR2", B=4, names=("G2", "D9_SMALL")),
     # the same BatchNorm critic under R1 + R2: the penalties differentiate 27 BatchNorms twice
     "rir_r1": dict(gen="generators.generator_2", g_args=lambda: (1, 256, 64, 3), g_kw={},
                    dis="discriminators.discriminator_5", d_args=lambda: (), d_kw={},

@@ -30,7 +30,7 @@ NOISE_PARAMS["lazy_r2"] = NOISE_PARAMS["clip"] = NOISE_PARAMS["style_d"]  # the 
 # its gradient is analytically zero (reference: discriminators/discriminator_9_3.py:74-75)
 NOISE_PARAMS["attn9_3"] = re.compile(r"\.query\.bias$")
 NOISE_IN_D = ("rir_bce", "rir_r1", "style_d", "lazy_r2", "clip", "attn9_3")
-ZOO = ["dcgan", "sn3", "shuffle", "rir_gp", "rir_sn", "rir_bce", "rir_r1", "style_d", "dense4", "lazy", "lazy_r2", "clip", "attn9_3"]  # SURVEY §8(f) rank 3 pairs (make_golden_configs.py)
+ZOO = ["dcgan", "sn3", "shuffle", "rir_gp", "rir_sn", "rir_bce", "rir_r1", "style_d", "dense4", "lazy", "lazy_r2", "clip", "attn9_3", "sk9_small"]  # SURVEY §8(f) rank 3 pairs (make_golden_configs.py)
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 

@@ -91,7 +91,9 @@ def test_factories_mirror_the_reference_names():
     with pytest.raises(NotImplementedError):
         get_generators.get_4(1, cpu)
     with pytest.raises(NotImplementedError):
-        get_discriminator.get_9(1, cpu)
+        get_discriminator.get_6_wgan(1, cpu)
+    d9 = get_discriminator.get_9(1, cpu)       # the self-attention critic: 64 base features, five attention layers
+    assert type(d9).__name__ == "Discriminator" and sum(type(m).__name__ == "SelfAttention" for m in d9.conv) == 5
     d4 = get_discriminator.get_3_wgan_progan(1, cpu, ndf=8, nc=3)
     assert type(d4).__name__ == "Discriminator" and len(d4.main) == 24
     # get_2 (both factories) applies the DCGAN weights_init: conv weights N(0, 0.02), BatchNorm weights N(1, 0.02)
