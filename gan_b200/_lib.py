@@ -148,6 +148,7 @@ SIGNATURES = {
     "ganb200_dwconv2d_fprop": (c_int, [P, P, P, P] + [c_int] * 8 + [c_float, P]),
     "ganb200_dwconv2d_dgrad": (c_int, [P, P, P] + [c_int] * 8 + [c_float, P]),
     "ganb200_dwconv2d_wgrad_workspace_bytes": (c_int64, [c_int, c_int]),
+    "ganb200_dwconv2d_wgrad_workspace_bytes_rs": (c_int64, [c_int, c_int, c_int, c_int]),
     "ganb200_dwconv2d_wgrad": (c_int, [P, P, P, P, c_int64] + [c_int] * 8 + [c_float, P]),
     "ganb200_dwconv2d_wgrad_static_max_bytes": (c_int64, []),
     "ganb200_dwconv2d_wgrad_static": (c_int, [P, P, P] + [c_int] * 8 + [c_float, P]),

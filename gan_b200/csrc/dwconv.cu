@@ -1,6 +1,7 @@
-// dwconv.cu — depthwise 3x3 convolution family (fprop / dgrad / wgrad) and channel shuffle, fp32 NCHW.
+// dwconv.cu — depthwise R x R (R = 3, 5, 7) convolution family (fprop / dgrad / wgrad) and channel shuffle, fp32 NCHW.
 // Used by discriminators/discriminator_7_wgangpsn.py:55,61,72 (ShuffleNetV2 units: Conv2d(C,C,3,stride,padding=1,
-// groups=C)) and :27-41 (channel_shuffle).  One multiply-add per 4 bytes moved: these are HBM-bound streaming kernels
+// groups=C)), discriminator_6_wgangp.py:12-13 (bottlenecks with depthwise 3x3 / 5x5 / 7x7, reflect-padded by the caller)
+// and :27-41 (channel_shuffle).  One multiply-add per 4 bytes moved: these are HBM-bound streaming kernels
 // (algorithmic bytes = 4 B read per input element + 4 B written per output element; the 3x3 window re-reads hit L1),
 // they stay on CUDA cores.  The three kernels are each other's derivatives (bilinear map), so the autograd
 // Functions in gan_b200/ops.py are closed under double backward exactly as for the dense convs.
@@ -9,7 +10,7 @@
 namespace ganb200 {
 
 // y[n,c,p,q] = alpha * sum_{r,s} w[c,r,s] * x[n,c,p*st-pad+r, q*st-pad+s] + bias[c]
-template <int ST>
+template <int ST, int R>
 __global__ void __launch_bounds__(256) dw3_fprop_kernel(const float* __restrict__ x, const float* __restrict__ w,
                                                         const float* __restrict__ bias, float* __restrict__ y, int NC,
                                                         int C, int H, int W, int P, int Q, int pad, float alpha) {
@@ -20,17 +21,17 @@ __global__ void __launch_bounds__(256) dw3_fprop_kernel(const float* __restrict_
     int nc = (int)(t / P);
     int c = nc % C;
     const float* xp = x + (int64_t)nc * H * W;
-    const float* wp = w + c * 9;
+    const float* wp = w + c * (R * R);
     int h0 = p * ST - pad, w0 = q * ST - pad;
     float acc = 0.f;
 #pragma unroll
-    for (int r = 0; r < 3; ++r) {
+    for (int r = 0; r < R; ++r) {
       int h = h0 + r;
       if ((unsigned)h >= (unsigned)H) continue;
 #pragma unroll
-      for (int s = 0; s < 3; ++s) {
+      for (int s = 0; s < R; ++s) {
         int ww = w0 + s;
-        if ((unsigned)ww < (unsigned)W) acc = fmaf(__ldg(wp + r * 3 + s), __ldg(xp + h * W + ww), acc);
+        if ((unsigned)ww < (unsigned)W) acc = fmaf(__ldg(wp + r * R + s), __ldg(xp + h * W + ww), acc);
       }
     }
     y[i] = alpha * acc + (bias ? __ldg(bias + c) : 0.f);
@@ -38,7 +39,7 @@ __global__ void __launch_bounds__(256) dw3_fprop_kernel(const float* __restrict_
 }
 
 // dx[n,c,h,w] = alpha * sum_{r,s} w[c,r,s] * dy[n,c,(h+pad-r)/st,(w+pad-s)/st]   (where divisible and in range)
-template <int ST>
+template <int ST, int R>
 __global__ void __launch_bounds__(256) dw3_dgrad_kernel(const float* __restrict__ dy, const float* __restrict__ w,
                                                         float* __restrict__ dx, int NC, int C, int H, int W, int P,
                                                         int Q, int pad, float alpha) {
@@ -49,36 +50,36 @@ __global__ void __launch_bounds__(256) dw3_dgrad_kernel(const float* __restrict_
     int nc = (int)(t / H);
     int c = nc % C;
     const float* gp = dy + (int64_t)nc * P * Q;
-    const float* wp = w + c * 9;
+    const float* wp = w + c * (R * R);
     float acc = 0.f;
 #pragma unroll
-    for (int r = 0; r < 3; ++r) {
+    for (int r = 0; r < R; ++r) {
       int ph = h + pad - r;
       if (ph < 0 || (ST == 2 && (ph & 1))) continue;
       int p = ph / ST;
       if (p >= P) continue;
 #pragma unroll
-      for (int s = 0; s < 3; ++s) {
+      for (int s = 0; s < R; ++s) {
         int pw = ww + pad - s;
         if (pw < 0 || (ST == 2 && (pw & 1))) continue;
         int q = pw / ST;
-        if (q < Q) acc = fmaf(__ldg(wp + r * 3 + s), __ldg(gp + p * Q + q), acc);
+        if (q < Q) acc = fmaf(__ldg(wp + r * R + s), __ldg(gp + p * Q + q), acc);
       }
     }
     dx[i] = alpha * acc;
   });
 }
 
-// partial[split][c][9] = sum over the split's samples and all (p,q) of dy[n,c,p,q] * x[n,c,p*st-pad+r,q*st-pad+s]
+// partial[split][c][R*R] = sum over the split's samples and all (p,q) of dy[n,c,p,q] * x[n,c,p*st-pad+r,q*st-pad+s]
 // grid (C, splits); a warp walks output rows so both reads are coalesced.
-template <int ST>
+template <int ST, int R>
 __global__ void __launch_bounds__(256) dw3_wgrad_kernel(const float* __restrict__ x, const float* __restrict__ dy,
                                                         float* __restrict__ partial, int N, int C, int H, int W, int P,
                                                         int Q, int pad) {
   const int c = blockIdx.x, split = blockIdx.y, splits = gridDim.y;
-  float acc[9];
+  float acc[R * R];
 #pragma unroll
-  for (int k = 0; k < 9; ++k) acc[k] = 0.f;
+  for (int k = 0; k < R * R; ++k) acc[k] = 0.f;
   const int PQ = P * Q;
   for (int n = split; n < N; n += splits) {
     const float* xp = x + ((int64_t)n * C + c) * H * W;
@@ -88,21 +89,21 @@ __global__ void __launch_bounds__(256) dw3_wgrad_kernel(const float* __restrict_
       float g = __ldg(gp + i);
       int h0 = p * ST - pad, w0 = q * ST - pad;
 #pragma unroll
-      for (int r = 0; r < 3; ++r) {
+      for (int r = 0; r < R; ++r) {
         int h = h0 + r;
         if ((unsigned)h >= (unsigned)H) continue;
 #pragma unroll
-        for (int s = 0; s < 3; ++s) {
+        for (int s = 0; s < R; ++s) {
           int ww = w0 + s;
-          if ((unsigned)ww < (unsigned)W) acc[r * 3 + s] = fmaf(g, __ldg(xp + h * W + ww), acc[r * 3 + s]);
+          if ((unsigned)ww < (unsigned)W) acc[r * R + s] = fmaf(g, __ldg(xp + h * W + ww), acc[r * R + s]);
         }
       }
     }
   }
 #pragma unroll
-  for (int k = 0; k < 9; ++k) {
+  for (int k = 0; k < R * R; ++k) {
     float t = block_sum<256>(acc[k]);
-    if (threadIdx.x == 0) partial[((int64_t)split * C + c) * 9 + k] = t;
+    if (threadIdx.x == 0) partial[((int64_t)split * C + c) * (R * R) + k] = t;
   }
 }
 
@@ -136,17 +137,38 @@ __global__ void __launch_bounds__(256) chan_shuffle_kernel(const float* __restri
 
 static int dw_check(int N, int C, int H, int W, int R, int S, int stride, int pad, int* P, int* Q) {
   GB_REQUIRE(N > 0 && C > 0 && H > 0 && W > 0, GANB200_BAD_SHAPE, "dwconv: empty tensor");
-  GB_REQUIRE(R == 3 && S == 3, GANB200_BAD_SHAPE, "dwconv: only 3x3 kernels (discriminator_7_wgangpsn.py)");
+  GB_REQUIRE(R == S && (R == 3 || R == 5 || R == 7), GANB200_BAD_SHAPE, "dwconv: square 3x3, 5x5 or 7x7 kernels only");
   GB_REQUIRE(stride == 1 || stride == 2, GANB200_BAD_SHAPE, "dwconv: stride must be 1 or 2");
-  GB_REQUIRE(pad >= 0 && pad <= 2, GANB200_BAD_SHAPE, "dwconv: pad must be 0..2");
-  *P = (H + 2 * pad - 3) / stride + 1;
-  *Q = (W + 2 * pad - 3) / stride + 1;
+  GB_REQUIRE(pad >= 0 && pad <= R / 2 + 1, GANB200_BAD_SHAPE, "dwconv: pad must be 0 .. R/2 + 1");
+  GB_REQUIRE(H + 2 * pad >= R && W + 2 * pad >= S, GANB200_BAD_SHAPE, "dwconv: empty output");
+  *P = (H + 2 * pad - R) / stride + 1;
+  *Q = (W + 2 * pad - S) / stride + 1;
   GB_REQUIRE(*P > 0 && *Q > 0, GANB200_BAD_SHAPE, "dwconv: empty output");
   return 0;
 }
 
 }  // namespace ganb200
 using namespace ganb200;
+
+// kernel<stride, R> for stride in {1, 2}, R in {3, 5, 7} (dw_check has admitted nothing else)
+#define GB_DW_DISPATCH(KERNEL, GRID, STREAM, ...)                                                      \
+  do {                                                                                                 \
+    if (stride == 1) {                                                                                 \
+      if (R == 3) KERNEL<1, 3><<<GRID, 256, 0, STREAM>>>(__VA_ARGS__);                                  \
+      else if (R == 5) KERNEL<1, 5><<<GRID, 256, 0, STREAM>>>(__VA_ARGS__);                             \
+      else KERNEL<1, 7><<<GRID, 256, 0, STREAM>>>(__VA_ARGS__);                                         \
+    } else {                                                                                           \
+      if (R == 3) KERNEL<2, 3><<<GRID, 256, 0, STREAM>>>(__VA_ARGS__);                                  \
+      else if (R == 5) KERNEL<2, 5><<<GRID, 256, 0, STREAM>>>(__VA_ARGS__);                             \
+      else KERNEL<2, 7><<<GRID, 256, 0, STREAM>>>(__VA_ARGS__);                                         \
+    }                                                                                                  \
+  } while (0)
+
+static int dw_splits(int N, int C) {
+  int splits = (4 * kNumSMs + C - 1) / C;
+  if (splits > N) splits = N;
+  return splits < 1 ? 1 : splits;
+}
 
 extern "C" int ganb200_dwconv2d_fprop(const float* x, const float* w, const float* bias, float* y, int N, int C, int H,
                                       int W, int R, int S, int stride, int pad, float alpha, void* stream) {
@@ -155,10 +177,7 @@ extern "C" int ganb200_dwconv2d_fprop(const float* x, const float* w, const floa
   int64_t total = (int64_t)N * C * P * Q;
   int grid = ew_grid(total, 256, 2);
   cudaStream_t s = (cudaStream_t)stream;
-  if (stride == 1)
-    dw3_fprop_kernel<1><<<grid, 256, 0, s>>>(x, w, bias, y, N * C, C, H, W, P, Q, pad, alpha);
-  else
-    dw3_fprop_kernel<2><<<grid, 256, 0, s>>>(x, w, bias, y, N * C, C, H, W, P, Q, pad, alpha);
+  GB_DW_DISPATCH(dw3_fprop_kernel, grid, s, x, w, bias, y, N * C, C, H, W, P, Q, pad, alpha);
   GB_CHECK_LAUNCH();
   return 0;
 }
@@ -170,19 +189,16 @@ extern "C" int ganb200_dwconv2d_dgrad(const float* dy, const float* w, float* dx
   int64_t total = (int64_t)N * C * H * W;
   int grid = ew_grid(total, 256, 2);
   cudaStream_t s = (cudaStream_t)stream;
-  if (stride == 1)
-    dw3_dgrad_kernel<1><<<grid, 256, 0, s>>>(dy, w, dx, N * C, C, H, W, P, Q, pad, alpha);
-  else
-    dw3_dgrad_kernel<2><<<grid, 256, 0, s>>>(dy, w, dx, N * C, C, H, W, P, Q, pad, alpha);
+  GB_DW_DISPATCH(dw3_dgrad_kernel, grid, s, dy, w, dx, N * C, C, H, W, P, Q, pad, alpha);
   GB_CHECK_LAUNCH();
   return 0;
 }
 
-extern "C" int64_t ganb200_dwconv2d_wgrad_workspace_bytes(int N, int C) {
-  int splits = (4 * kNumSMs + C - 1) / C;
-  if (splits > N) splits = N;
-  if (splits < 1) splits = 1;
-  return (int64_t)splits * C * 9 * sizeof(float);
+extern "C" int64_t ganb200_dwconv2d_wgrad_workspace_bytes(int N, int C) {   // 3x3 kernels
+  return (int64_t)dw_splits(N, C) * C * 9 * sizeof(float);
+}
+extern "C" int64_t ganb200_dwconv2d_wgrad_workspace_bytes_rs(int N, int C, int R, int S) {
+  return (int64_t)dw_splits(N, C) * C * R * S * sizeof(float);
 }
 
 extern "C" int ganb200_dwconv2d_wgrad(const float* x, const float* dy, float* dw, void* workspace,
@@ -190,17 +206,14 @@ extern "C" int ganb200_dwconv2d_wgrad(const float* x, const float* dy, float* dw
                                       int pad, float alpha, void* stream) {
   int P, Q;
   if (int rc = dw_check(N, C, H, W, R, S, stride, pad, &P, &Q)) return rc;
-  int64_t need = ganb200_dwconv2d_wgrad_workspace_bytes(N, C);
+  int64_t need = ganb200_dwconv2d_wgrad_workspace_bytes_rs(N, C, R, S);
   GB_REQUIRE(workspace != nullptr && workspace_bytes >= need, GANB200_BAD_SHAPE, "dwconv wgrad: workspace too small");
-  int splits = (int)(need / ((int64_t)C * 9 * sizeof(float)));
+  int splits = dw_splits(N, C);
   cudaStream_t s = (cudaStream_t)stream;
   dim3 grid(C, splits);
   float* partial = (float*)workspace;
-  if (stride == 1)
-    dw3_wgrad_kernel<1><<<grid, 256, 0, s>>>(x, dy, partial, N, C, H, W, P, Q, pad);
-  else
-    dw3_wgrad_kernel<2><<<grid, 256, 0, s>>>(x, dy, partial, N, C, H, W, P, Q, pad);
-  dw3_wgrad_reduce_kernel<<<ceil_div(C * 9, 256), 256, 0, s>>>(partial, dw, C * 9, splits, alpha);
+  GB_DW_DISPATCH(dw3_wgrad_kernel, grid, s, x, dy, partial, N, C, H, W, P, Q, pad);
+  dw3_wgrad_reduce_kernel<<<ceil_div(C * R * S, 256), 256, 0, s>>>(partial, dw, C * R * S, splits, alpha);
   GB_CHECK_LAUNCH();
   return 0;
 }
@@ -240,7 +253,7 @@ extern "C" int ganb200_dwconv2d_wgrad_static(const float* x, const float* dy, fl
                                              int R, int S, int stride, int pad, float alpha, void* stream) {
   int P, Q;
   if (int rc = dw_check(N, C, H, W, R, S, stride, pad, &P, &Q)) return rc;
-  const int64_t need = ganb200_dwconv2d_wgrad_workspace_bytes(N, C);
+  const int64_t need = ganb200_dwconv2d_wgrad_workspace_bytes_rs(N, C, R, S);
   if (need > kDwWgradStaticFloats * (int64_t)sizeof(float))
     return fail(GANB200_WORKSPACE_TOO_SMALL,
                 "dwconv wgrad (static scratch): this shape needs %s%lld bytes of split partials, the built-in scratch "
@@ -248,14 +261,11 @@ extern "C" int ganb200_dwconv2d_wgrad_static(const float* x, const float* dy, fl
                 (long long)(kDwWgradStaticFloats * sizeof(float)));
   float* partial = nullptr;
   if (int rc = dw_static_partials(&partial)) return rc;
-  const int splits = (int)(need / ((int64_t)C * 9 * sizeof(float)));
+  const int splits = dw_splits(N, C);
   cudaStream_t s = (cudaStream_t)stream;
   dim3 grid(C, splits);
-  if (stride == 1)
-    dw3_wgrad_kernel<1><<<grid, 256, 0, s>>>(x, dy, partial, N, C, H, W, P, Q, pad);
-  else
-    dw3_wgrad_kernel<2><<<grid, 256, 0, s>>>(x, dy, partial, N, C, H, W, P, Q, pad);
-  dw3_wgrad_reduce_kernel<<<ceil_div(C * 9, 256), 256, 0, s>>>(partial, dw, C * 9, splits, alpha);
+  GB_DW_DISPATCH(dw3_wgrad_kernel, grid, s, x, dy, partial, N, C, H, W, P, Q, pad);
+  dw3_wgrad_reduce_kernel<<<ceil_div(C * R * S, 256), 256, 0, s>>>(partial, dw, C * R * S, splits, alpha);
   GB_CHECK_LAUNCH();
   return 0;
 }

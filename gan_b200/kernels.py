@@ -290,7 +290,7 @@ class CudaBackend:
         self._t1(tm)
         return dw
 
-    # -- depthwise 3x3 conv (discriminator_7_wgangpsn.py:55,61,72) -----------------------------------
+    # -- depthwise 3x3 / 5x5 / 7x7 conv (discriminator_7_wgangpsn.py:55,61,72; discriminator_6_wgangp.py:12) -----------------------------------
     def dwconv_fprop(self, x, w, bias, stride, pad, alpha):
         N, C, H, W = x.shape
         assert w.shape[0] == C and w.shape[1] == 1, (x.shape, w.shape)
@@ -320,7 +320,7 @@ class CudaBackend:
         st = self._prep(x, dy)
         LAUNCH_COUNT[0] += 1
         dw = torch.empty((C, 1, R, S), dtype=torch.float32, device=x.device)
-        nb = self.lib.ganb200_dwconv2d_wgrad_workspace_bytes(N, C)
+        nb = self.lib.ganb200_dwconv2d_wgrad_workspace_bytes_rs(N, C, R, S)
         ws = self._workspace(nb, x.device)
         _lib.check(self.lib.ganb200_dwconv2d_wgrad(self._p(x), self._p(dy), self._p(dw), self._p(ws), nb, N, C, H, W,
                                                    R, S, stride, pad, alpha, st))

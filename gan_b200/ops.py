@@ -126,7 +126,8 @@ def conv2d(x, w, bias=None, stride=1, pad=0, pad_mode=0, alpha=1.0, engine=None)
 
 
 def depthwise_conv2d(x, w, bias=None, stride=1, pad=1, alpha=1.0):
-    """nn.Conv2d(C, C, 3, stride, pad, groups=C), zero padding — discriminator_7_wgangpsn.py:55,61,72."""
+    """nn.Conv2d(C, C, k, stride, pad, groups=C), k in 3 / 5 / 7, zero padding — discriminator_7_wgangpsn.py:55,61,72,
+    discriminator_6_wgangp.py:12 (reflect padding: layers.Conv2d mirrors the map first)."""
     return Conv2dFn.apply(x, w, bias, ConvCfg(stride, pad, 0, float(alpha), None, True))
 
 

@@ -441,16 +441,20 @@ int ganb200_spectral_scale_bwd(const float* G, const float* W, const float* u, c
                                const float* sigma, float* dot_scratch, float* gW, int rows, int cols,
                                void* stream);
 
-/* Depthwise 3x3 convolution, zero padding, stride 1|2 (discriminators/discriminator_7_wgangpsn.py:55,61,72:
- * nn.Conv2d(C, C, 3, stride, padding=1, groups=C)).  x:[N,C,H,W]  w:[C,1,3,3]  y:[N,C,P,Q].
+/* Depthwise R x R convolution (R = S in {3, 5, 7}), zero padding 0 .. R/2 + 1, stride 1|2
+ * (discriminators/discriminator_7_wgangpsn.py:55,61,72: nn.Conv2d(C, C, 3, stride, padding=1, groups=C);
+ * discriminators/discriminator_6_wgangp.py:12-13: kernel 3 / 5 / 7, reflect padding applied by the caller).
+ * x:[N,C,H,W]  w:[C,1,R,R]  y:[N,C,P,Q].
  *   fprop: y  = alpha * dwconv(x, w) + bias        (bias may be NULL)
  *   dgrad: dx = alpha * dwconv^T(dy, w)
- *   wgrad: dw = alpha * sum_{n,p,q} dy * x_window   (workspace: ganb200_dwconv2d_wgrad_workspace_bytes) */
+ *   wgrad: dw = alpha * sum_{n,p,q} dy * x_window   (workspace: ganb200_dwconv2d_wgrad_workspace_bytes for 3x3,
+ *          ganb200_dwconv2d_wgrad_workspace_bytes_rs for any admitted kernel) */
 int ganb200_dwconv2d_fprop(const float* x, const float* w, const float* bias, float* y, int N, int C, int H,
                            int W, int R, int S, int stride, int pad, float alpha, void* stream);
 int ganb200_dwconv2d_dgrad(const float* dy, const float* w, float* dx, int N, int C, int H, int W, int R,
                            int S, int stride, int pad, float alpha, void* stream);
 int64_t ganb200_dwconv2d_wgrad_workspace_bytes(int N, int C);
+int64_t ganb200_dwconv2d_wgrad_workspace_bytes_rs(int N, int C, int R, int S);
 int ganb200_dwconv2d_wgrad(const float* x, const float* dy, float* dw, void* workspace,
                            int64_t workspace_bytes, int N, int C, int H, int W, int R, int S, int stride,
                            int pad, float alpha, void* stream);
@@ -460,7 +464,7 @@ int ganb200_dwconv2d_wgrad(const float* x, const float* dy, float* dw, void* wor
  * Same result as ganb200_dwconv2d_wgrad, but the split partials live in a 256 KiB file-scope device array inside the
  * library (held by every GPU that loads it, until exit) instead of a caller workspace; the call performs no cudaMalloc /
  * cudaFree / allocating library call.  Shapes whose partials exceed ganb200_dwconv2d_wgrad_static_max_bytes()
- * (splits * C * 36 bytes > 256 KiB, i.e. C above ~6 600) are rejected with GANB200_WORKSPACE_TOO_SMALL.  All calls share
+ * (splits * C * R * S * 4 bytes > 256 KiB; for 3x3 kernels C above ~6 600) are rejected with GANB200_WORKSPACE_TOO_SMALL.  All calls share
  * the array: calls on one stream are ordered; calls that overlap on the GPU (different streams) race. */
 int64_t ganb200_dwconv2d_wgrad_static_max_bytes(void);
 int ganb200_dwconv2d_wgrad_static(const float* x, const float* dy, float* dw, int N, int C, int H, int W, int R, int S,

@@ -87,6 +87,11 @@ CONFIGS = {
     "sk9_small": dict(gen="generators.generator_2", g_args=lambda: (1, 256, 64, 3), g_kw={},
                       dis="discriminators.discriminator_9_small", d_args=lambda: (), d_kw={},
                       train="train.wgangpR2", B=4, names=("G2", "D9_SMALL")),
+    # the deep-layer-aggregation critic of get_6_wgan (depthwise 3x3 / 5x5 / 7x7 bottlenecks with reflect padding, windowed
+    # SE squeeze, 5x5 stride-2 reflect convs) under R1 + R2 + GP: 1 276 convolutions differentiated twice
+    "tree6": dict(gen="generators.generator_2", g_args=lambda: (1, 256, 64, 3), g_kw={},
+                  dis="discriminators.discriminator_6_wgangp", d_args=lambda: (), d_kw={},
+                  train="train.wgangpR2", B=4, names=("G2", "D6_WGAN")),
     # the same BatchNorm critic under R1 + R2: the penalties differentiate 27 BatchNorms twice
     "rir_r1": dict(gen="generators.generator_2", g_args=lambda: (1, 256, 64, 3), g_kw={},
                    dis="discriminators.discriminator_5", d_args=lambda: (), d_kw={},

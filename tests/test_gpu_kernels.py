@@ -615,23 +615,30 @@ def test_fused_style_layer_on_gpu_matches_unfused_ops(cu):
 # kernels of the other configs: depthwise 3x3 family, channel shuffle, spectral norm, batch-wide stddev channel
 # ---------------------------------------------------------------------------------------------------------------------
 @pytest.mark.parametrize("case", [(4, 32, 64, 64, 2), (4, 244, 32, 32, 1), (3, 122, 16, 16, 1), (5, 976, 4, 4, 2),
-                                  (2, 7, 9, 11, 2), (2, 7, 9, 11, 1), (64, 16, 1, 1, 1)])
+                                  (2, 7, 9, 11, 2), (2, 7, 9, 11, 1), (64, 16, 1, 1, 1),
+                                  # discriminator_6_wgangp.py:12 — 5x5 / 7x7 on a map the caller has reflect-padded (pad 0)
+                                  (4, 6, 36, 36, 1, 5, 0), (4, 12, 22, 22, 1, 7, 0), (4, 16, 10, 10, 1, 3, 0),
+                                  (2, 5, 13, 9, 2, 5, 2), (2, 5, 13, 9, 1, 7, 3), (3, 24, 8, 8, 2, 7, 4), (2, 3, 7, 7, 1, 7, 0)])
 def test_depthwise_conv_family(cu, ref, case):
-    N, C, H, W, stride = case
+    N, C, H, W, stride = case[:5]
+    k, pad = case[5:] if len(case) > 5 else (3, 1)
     torch.manual_seed(11)
-    x, w, b = rnd(N, C, H, W), rnd(C, 1, 3, 3), rnd(C)
-    y_r = ref.dwconv_fprop(x, w, b, stride, 1, 0.7)
-    assert rel(cu.dwconv_fprop(g(x), g(w), g(b), stride, 1, 0.7), y_r) < FP32_TOL
-    assert rel(cu.dwconv_fprop(g(x), g(w), None, stride, 1, 1.0), ref.dwconv_fprop(x, w, None, stride, 1, 1.0)) < FP32_TOL
+    x, w, b = rnd(N, C, H, W), rnd(C, 1, k, k), rnd(C)
+    y_r = ref.dwconv_fprop(x, w, b, stride, pad, 0.7)
+    assert rel(cu.dwconv_fprop(g(x), g(w), g(b), stride, pad, 0.7), y_r) < FP32_TOL
+    assert rel(cu.dwconv_fprop(g(x), g(w), None, stride, pad, 1.0), ref.dwconv_fprop(x, w, None, stride, pad, 1.0)) < FP32_TOL
     dy = rnd(*y_r.shape)
-    assert rel(cu.dwconv_dgrad(g(dy), g(w), (H, W), stride, 1, 0.7), ref.dwconv_dgrad(dy, w, (H, W), stride, 1, 0.7)) < FP32_TOL
-    assert rel(cu.dwconv_wgrad(g(x), g(dy), (3, 3), stride, 1, 0.7), ref.dwconv_wgrad(x, dy, (3, 3), stride, 1, 0.7)) < 2e-5
+    assert rel(cu.dwconv_dgrad(g(dy), g(w), (H, W), stride, pad, 0.7), ref.dwconv_dgrad(dy, w, (H, W), stride, pad, 0.7)) < FP32_TOL
+    assert rel(cu.dwconv_wgrad(g(x), g(dy), (k, k), stride, pad, 0.7), ref.dwconv_wgrad(x, dy, (k, k), stride, pad, 0.7)) < 2e-5
 
 
 def test_depthwise_conv_rejects_other_kernels(cu):
     from gan_b200._lib import GanB200Error
-    with pytest.raises(GanB200Error):
-        cu.dwconv_fprop(g(rnd(1, 4, 8, 8)), g(rnd(4, 1, 5, 5)), None, 1, 2, 1.0)
+    for k, pad in ((4, 1), (9, 4), (1, 0)):           # even, larger than 7, 1x1 (that is a pointwise scale, not this family)
+        with pytest.raises(GanB200Error):
+            cu.dwconv_fprop(g(rnd(1, 4, 12, 12)), g(rnd(4, 1, k, k)), None, 1, pad, 1.0)
+    with pytest.raises(GanB200Error):                  # 3x5: square kernels only
+        cu.dwconv_fprop(g(rnd(1, 4, 12, 12)), g(rnd(4, 1, 3, 5)), None, 1, 1, 1.0)
 
 
 @pytest.mark.parametrize("shape,groups", [((4, 244, 32, 32), 2), ((3, 12, 5, 7), 3), ((2, 1952, 4, 4), 2)])

@@ -90,8 +90,8 @@ def test_factories_mirror_the_reference_names():
         assert callable(getattr(get_discriminator, "get_" + n))
     with pytest.raises(NotImplementedError):
         get_generators.get_4(1, cpu)
-    with pytest.raises(NotImplementedError):
-        get_discriminator.get_6_wgan(1, cpu)
+    d6 = get_discriminator.get_6_wgan(1, cpu)  # every discriminator factory of the reference builds here
+    assert type(d6).__module__ == "discriminators.discriminator_6_wgangp" and len(d6.model) == 8
     d9 = get_discriminator.get_9(1, cpu)       # the self-attention critic: 64 base features, five attention layers
     assert type(d9).__name__ == "Discriminator" and sum(type(m).__name__ == "SelfAttention" for m in d9.conv) == 5
     d4 = get_discriminator.get_3_wgan_progan(1, cpu, ndf=8, nc=3)

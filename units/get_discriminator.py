@@ -9,8 +9,8 @@ import math
 
 _CARRIED = ("discriminator_1", "discriminator_2", "discriminator_3_wgangp", "discriminator_3_wgangp_progan",
             "discriminator_3_wgangpsn", "discriminator_4", "discriminator_5", "discriminator_5_wgangp", "discriminator_5_wgangpsn",
-            "discriminator_7_wgangp", "discriminator_7_wgangpsn", "discriminator_8", "discriminator_9", "discriminator_9_2",
-            "discriminator_9_3", "discriminator_9_4", "discriminator_9_small")
+            "discriminator_6_wgangp", "discriminator_7_wgangp", "discriminator_7_wgangpsn", "discriminator_8", "discriminator_9",
+            "discriminator_9_2", "discriminator_9_3", "discriminator_9_4", "discriminator_9_small")
 
 
 def _module(name):
