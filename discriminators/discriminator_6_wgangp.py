@@ -68,11 +68,14 @@ class SqueezeExcitationBottleneck(nn.Module):
 
 
 class ResnetInit(nn.Module):
-    """reference :38-63 — the residual and the transient stream each feed both outputs."""
+    """reference :38-63 — the residual and the transient stream each feed both outputs.
+    (BOTTLENECK / RIR / BLOCK / _pointwise below: the tree generators generator_7 / generator_8 are this tree with
+    BatchNorm + PReLU bottlenecks; they subclass these classes and swap the parts.)"""
+    BOTTLENECK = SqueezeExcitationBottleneck
 
     def __init__(self, last_planes, in_planes, out_planes, dense_depth, kernel_size, feature_size):
         super(ResnetInit, self).__init__()
-        mk = lambda dd: SqueezeExcitationBottleneck(last_planes, in_planes, out_planes, dd, kernel_size, feature_size)
+        mk = lambda dd: self.BOTTLENECK(last_planes, in_planes, out_planes, dd, kernel_size, feature_size)
         self.residual = mk(dense_depth)
         self.transient = mk(0)
         self.residual_across = mk(0)
@@ -88,6 +91,13 @@ class BasicBlock(nn.Module):
     """reference :66-125 — optional 1x1 `unify`, the three ResnetInit pairs on the same two streams, optional 1x1
     `shortcut` (the aggregation root), and the dense concatenation of the three residual tails."""
 
+    RIR = ResnetInit
+
+    @staticmethod
+    def _pointwise(in_planes, out_planes):
+        """the layers of `unify` / `shortcut`"""
+        return [L.Conv2d(in_planes, out_planes, kernel_size=1, stride=1, padding=0)]
+
     def get_out_planes(self):
         if self.is_unify or self.root:
             return 2 * self.out_planes + 4 * self.dense_depth
@@ -102,18 +112,16 @@ class BasicBlock(nn.Module):
         self.is_unify = is_unify
         self.unify = nn.Sequential()
         if is_unify:
-            self.unify = nn.Sequential(
-                L.Conv2d(last_planes, 2 * out_planes + dense_depth, kernel_size=1, stride=1, padding=0))
+            self.unify = nn.Sequential(*self._pointwise(last_planes, 2 * out_planes + dense_depth))
             stream = out_planes + dense_depth
         else:
             stream = last_planes - out_planes
-        self.rir_3 = ResnetInit(stream, in_planes, out_planes, dense_depth, 3, feature_size)
-        self.rir_5 = ResnetInit(stream, in_planes, out_planes, dense_depth, 5, feature_size)
-        self.rir_7 = ResnetInit(stream, in_planes, out_planes, dense_depth, 7, feature_size)
+        self.rir_3 = self.RIR(stream, in_planes, out_planes, dense_depth, 3, feature_size)
+        self.rir_5 = self.RIR(stream, in_planes, out_planes, dense_depth, 5, feature_size)
+        self.rir_7 = self.RIR(stream, in_planes, out_planes, dense_depth, 7, feature_size)
         self.shortcut = nn.Sequential()
         if root:
-            self.shortcut = nn.Sequential(
-                L.Conv2d(last_planes, 2 * out_planes + dense_depth, kernel_size=1, stride=1, padding=0))
+            self.shortcut = nn.Sequential(*self._pointwise(last_planes, 2 * out_planes + dense_depth))
 
     def forward(self, x):
         d = self.out_planes
@@ -131,6 +139,8 @@ class Tree(nn.Module):
     """reference :128-189 — deep layer aggregation: sub-trees and blocks in sequence, the first 2*out_planes channels
     of every stage (and the dense tail of the last) concatenated into the root block."""
 
+    BLOCK = BasicBlock
+
     def get_out_planes(self):
         return self.root.get_out_planes()
 
@@ -141,7 +151,7 @@ class Tree(nn.Module):
         self.block_num = block_num
         self.out_planes = out_planes
         self.dense_depth = dense_depth
-        plain = lambda planes, unify: BasicBlock(planes, in_planes, out_planes, dense_depth, False, feature_size, unify)
+        plain = lambda planes, unify: self.BLOCK(planes, in_planes, out_planes, dense_depth, False, feature_size, unify)
         self.root_last_planes = 2 * out_planes * (block_num - 1)
         first = 0
         if level == 1:
@@ -153,7 +163,7 @@ class Tree(nn.Module):
             self.prev_root = plain(last_planes, last_planes < 2 * out_planes)
             self.root_last_planes += self.prev_root.get_out_planes()
             for i in reversed(range(1, level)):
-                subtree = Tree(last_planes, in_planes, out_planes, dense_depth, i, block_num, feature_size)
+                subtree = type(self)(last_planes, in_planes, out_planes, dense_depth, i, block_num, feature_size)
                 last_planes = subtree.get_out_planes()
                 self.root_last_planes += last_planes
                 self.__setattr__('level_%d' % i, subtree)
@@ -162,7 +172,7 @@ class Tree(nn.Module):
             last_planes = sub_block.get_out_planes()
             self.__setattr__('block_%d' % i, sub_block)
         self.root_last_planes += sub_block.get_out_planes()
-        self.root = BasicBlock(self.root_last_planes, in_planes * block_num, out_planes, dense_depth, True,
+        self.root = self.BLOCK(self.root_last_planes, in_planes * block_num, out_planes, dense_depth, True,
                                feature_size, False)
 
     def forward(self, x):

@@ -92,6 +92,14 @@ CONFIGS = {
     "tree6": dict(gen="generators.generator_2", g_args=lambda: (1, 256, 64, 3), g_kw={},
                   dis="discriminators.discriminator_6_wgangp", d_args=lambda: (), d_kw={},
                   train="train.wgangpR2", B=4, names=("G2", "D6_WGAN")),
+    # the tree generators of get_7 / get_8 (the same aggregation tree with BatchNorm + scalar-PReLU bottlenecks, 25 M and
+    # 64 M parameters) against DCGAN-shaped critics: WGAN-GP for one, BCE for the other
+    "tree7": dict(gen="generators.generator_7", g_args=lambda: (256,), g_kw={},
+                  dis="discriminators.discriminator_3_wgangp", d_args=lambda: (1, 64, 3), d_kw={},
+                  train="train.wgangp", B=4, names=("G7", "D3_WGAN")),
+    "tree8": dict(gen="generators.generator_8", g_args=lambda: (256,), g_kw={},
+                  dis="discriminators.discriminator_2", d_args=lambda: (1, 64, 3), d_kw={},
+                  train="train.gan", B=4, names=("G8", "D2")),
     # the same BatchNorm critic under R1 + R2: the penalties differentiate 27 BatchNorms twice
     "rir_r1": dict(gen="generators.generator_2", g_args=lambda: (1, 256, 64, 3), g_kw={},
                    dis="discriminators.discriminator_5", d_args=lambda: (), d_kw={},

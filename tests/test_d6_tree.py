@@ -48,3 +48,37 @@ def test_tree_critic_equals_reference(ref_backend):
     for a, b in zip(run(D, torch.float32), run(D_ref, torch.float32)):
         assert rel(a, b) < 1e-5
 
+
+@pytest.mark.parametrize("name", ["generator_7", "generator_8"])
+def test_tree_generators_equal_reference(ref_backend, name):
+    """generator_7 / generator_8: the same tree with BatchNorm + scalar-PReLU bottlenecks (they subclass the critic's
+    classes).  Identical state_dict; for generator_7 also G(z) and first-order gradients in float64 (a full iteration of
+    each against a recorded golden: tests/test_other_configs.py, "tree7" / "tree8")."""
+    ref_mod = R.load("generators." + name)
+    our_mod = importlib.import_module("generators." + name)
+    torch.manual_seed(11)
+    G_ref = ref_mod.Generator(64)
+    torch.manual_seed(11)
+    G = our_mod.Generator(64)
+    sd_ref, sd = G_ref.state_dict(), G.state_dict()
+    assert list(sd.keys()) == list(sd_ref.keys())
+    assert [n for n, _ in G.named_parameters()] == [n for n, _ in G_ref.named_parameters()]
+    for k, v in sd_ref.items():
+        assert torch.equal(sd[k], v), k
+    for cls in ("SqueezeExcitationBottleneck", "ResnetInit", "BasicBlock", "Tree", "Generator"):
+        assert hasattr(our_mod, cls), cls
+    if name != "generator_7":
+        return
+    z = torch.randn(2, 64, 1, 1, generator=torch.Generator().manual_seed(12), dtype=torch.float64)
+
+    def run(net):
+        net = net.double()
+        zi = z.clone().requires_grad_()
+        y = net(zi)
+        assert y.shape == (2, 3, 64, 64)
+        first = next(net.parameters())
+        gz, gw = torch.autograd.grad((y * torch.linspace(-1, 1, y.numel(), dtype=y.dtype).reshape(y.shape)).sum(), [zi, first])
+        return y.detach(), gz, gw
+
+    for a, b in zip(run(G), run(G_ref)):
+        assert rel(a, b) < 1e-11

@@ -79,6 +79,8 @@ CONV_CASES = [
     (3, 40, 21, 64, 72, 5, 1, 2, 1),     # row-ring wgrad: 63 rows over 3 images (ranges cross image boundaries), K > 64
     (5, 130, 9, 32, 200, 3, 1, 1, 0),    # row-ring wgrad: 32-pixel rows, zero pad, three channel tiles, two filter tiles
     (2, 16, 70, 32, 16, 7, 1, 3, 1),     # row-ring wgrad: k7 (seven accumulators)
+    (2, 20, 24, 24, 3, 9, 1, 0, 0),      # tree generators' LastConv: 9x9 on the reflect-padded map (CUDA-core engine only)
+    (2, 16, 36, 36, 16, 5, 2, 0, 0),     # tree critic's down-sampling conv: 5x5 stride 2 on the reflect-padded map
 ]
 
 
