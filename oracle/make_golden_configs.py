@@ -100,6 +100,14 @@ CONFIGS = {
     "tree8": dict(gen="generators.generator_8", g_args=lambda: (256,), g_kw={},
                   dis="discriminators.discriminator_2", d_args=lambda: (1, 64, 3), d_kw={},
                   train="train.gan", B=4, names=("G8", "D2")),
+    # the InstanceNorm tree generators of get_4 / get_5 (ShuffleNet-style split blocks / densely connected blocks, BatchNorm
+    # stems at 2x2 .. 8x8) under the spectral-norm loop with R1 + R2 and the BCE loop with R1 + R2
+    "tree4": dict(gen="generators.generator_4", g_args=lambda: (256,), g_kw={},
+                  dis="discriminators.discriminator_3_wgangpsn", d_args=lambda: (1, 64, 3), d_kw={},
+                  train="train.wgansnR2", B=4, names=("G4", "D3_WGANSN")),
+    "tree5": dict(gen="generators.generator_5", g_args=lambda: (256,), g_kw={},
+                  dis="discriminators.discriminator_2", d_args=lambda: (1, 64, 3), d_kw={},
+                  train="train.ganR2", B=4, names=("G5", "D2")),
     # the same BatchNorm critic under R1 + R2: the penalties differentiate 27 BatchNorms twice
     "rir_r1": dict(gen="generators.generator_2", g_args=lambda: (1, 256, 64, 3), g_kw={},
                    dis="discriminators.discriminator_5", d_args=lambda: (), d_kw={},

@@ -49,11 +49,12 @@ def test_tree_critic_equals_reference(ref_backend):
         assert rel(a, b) < 1e-5
 
 
-@pytest.mark.parametrize("name", ["generator_7", "generator_8"])
+@pytest.mark.parametrize("name", ["generator_4", "generator_5", "generator_7", "generator_8"])
 def test_tree_generators_equal_reference(ref_backend, name):
     """generator_7 / generator_8: the same tree with BatchNorm + scalar-PReLU bottlenecks (they subclass the critic's
-    classes).  Identical state_dict; for generator_7 also G(z) and first-order gradients in float64 (a full iteration of
-    each against a recorded golden: tests/test_other_configs.py, "tree7" / "tree8")."""
+    classes); generator_4 / generator_5: InstanceNorm trees on BatchNorm stems.  Identical state_dict; for generator_7
+    also G(z) and first-order gradients in float64 (a full iteration of each against a recorded golden:
+    tests/test_other_configs.py, "tree4" / "tree5" / "tree7" / "tree8")."""
     ref_mod = R.load("generators." + name)
     our_mod = importlib.import_module("generators." + name)
     torch.manual_seed(11)
@@ -65,8 +66,9 @@ def test_tree_generators_equal_reference(ref_backend, name):
     assert [n for n, _ in G.named_parameters()] == [n for n, _ in G_ref.named_parameters()]
     for k, v in sd_ref.items():
         assert torch.equal(sd[k], v), k
-    for cls in ("SqueezeExcitationBottleneck", "ResnetInit", "BasicBlock", "Tree", "Generator"):
-        assert hasattr(our_mod, cls), cls
+    for cls in [n for n in dir(ref_mod) if isinstance(getattr(ref_mod, n), type) and
+                issubclass(getattr(ref_mod, n), torch.nn.Module) and getattr(ref_mod, n).__module__ == ref_mod.__name__]:
+        assert hasattr(our_mod, cls), cls     # whole-module checkpoints of the reference name these classes
     if name != "generator_7":
         return
     z = torch.randn(2, 64, 1, 1, generator=torch.Generator().manual_seed(12), dtype=torch.float64)
