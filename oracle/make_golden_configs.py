@@ -108,6 +108,16 @@ CONFIGS = {
     "tree5": dict(gen="generators.generator_5", g_args=lambda: (256,), g_kw={},
                   dis="discriminators.discriminator_2", d_args=lambda: (1, 64, 3), d_kw={},
                   train="train.ganR2", B=4, names=("G5", "D2")),
+    # the self-attention tree generators of get_9 / get_10 / get_10_2 (SAGAN attention up to 64x64: 4 096 x 4 096 maps)
+    "tree9": dict(gen="generators.generator_9", g_args=lambda: (256,), g_kw={},
+                  dis="discriminators.discriminator_3_wgangp", d_args=lambda: (1, 64, 3), d_kw={},
+                  train="train.wgangpR2", B=4, names=("G9", "D3_WGAN")),
+    "tree10": dict(gen="generators.generator_10", g_args=lambda: (256,), g_kw={},
+                   dis="discriminators.discriminator_3_wgangpsn", d_args=lambda: (1, 64, 3), d_kw={},
+                   train="train.wgansn", B=4, names=("G10", "D3_WGANSN")),
+    "tree10_2": dict(gen="generators.generator_10_2", g_args=lambda: (256,), g_kw={},
+                     dis="discriminators.discriminator_2", d_args=lambda: (1, 64, 3), d_kw={},
+                     train="train.gan", B=4, names=("G10_2", "D2")),
     # the same BatchNorm critic under R1 + R2: the penalties differentiate 27 BatchNorms twice
     "rir_r1": dict(gen="generators.generator_2", g_args=lambda: (1, 256, 64, 3), g_kw={},
                    dis="discriminators.discriminator_5", d_args=lambda: (), d_kw={},

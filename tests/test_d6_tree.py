@@ -49,17 +49,22 @@ def test_tree_critic_equals_reference(ref_backend):
         assert rel(a, b) < 1e-5
 
 
-@pytest.mark.parametrize("name", ["generator_4", "generator_5", "generator_7", "generator_8"])
+# (generator_5 / 8 / 9 / 10: structure, initialisation and a whole iteration are compared in tests/test_other_configs.py)
+@pytest.mark.parametrize("name", ["generator_4", "generator_7", "generator_10_2"])
 def test_tree_generators_equal_reference(ref_backend, name):
     """generator_7 / generator_8: the same tree with BatchNorm + scalar-PReLU bottlenecks (they subclass the critic's
-    classes); generator_4 / generator_5: InstanceNorm trees on BatchNorm stems.  Identical state_dict; for generator_7
+    classes); generator_4 / generator_5: InstanceNorm trees on BatchNorm stems; generator_9 / 10 / 10_2: self-attention
+    trees (10_2 with run-time-scaled equalised convolutions).  Identical state_dict; for generator_7 and generator_10_2
     also G(z) and first-order gradients in float64 (a full iteration of each against a recorded golden:
-    tests/test_other_configs.py, "tree4" / "tree5" / "tree7" / "tree8")."""
+    tests/test_other_configs.py, "tree4" ... "tree10_2"; 10_2 is too ill-conditioned in float32 for that to say much)."""
+    import random
     ref_mod = R.load("generators." + name)
     our_mod = importlib.import_module("generators." + name)
     torch.manual_seed(11)
+    random.seed(11)              # generator_10 / 10_2 draw their attention gates from Python's `random`
     G_ref = ref_mod.Generator(64)
     torch.manual_seed(11)
+    random.seed(11)
     G = our_mod.Generator(64)
     sd_ref, sd = G_ref.state_dict(), G.state_dict()
     assert list(sd.keys()) == list(sd_ref.keys())
@@ -69,7 +74,7 @@ def test_tree_generators_equal_reference(ref_backend, name):
     for cls in [n for n in dir(ref_mod) if isinstance(getattr(ref_mod, n), type) and
                 issubclass(getattr(ref_mod, n), torch.nn.Module) and getattr(ref_mod, n).__module__ == ref_mod.__name__]:
         assert hasattr(our_mod, cls), cls     # whole-module checkpoints of the reference name these classes
-    if name != "generator_7":
+    if name not in ("generator_7", "generator_10_2"):
         return
     z = torch.randn(2, 64, 1, 1, generator=torch.Generator().manual_seed(12), dtype=torch.float64)
 
@@ -83,4 +88,4 @@ def test_tree_generators_equal_reference(ref_backend, name):
         return y.detach(), gz, gw
 
     for a, b in zip(run(G), run(G_ref)):
-        assert rel(a, b) < 1e-11
+        assert rel(a, b) < (1e-11 if name == "generator_7" else 1e-8)

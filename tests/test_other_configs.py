@@ -37,8 +37,12 @@ NOISE_PARAMS["tree7"] = NOISE_PARAMS["tree8"] = re.compile(r"(res\.[036]|unify\.
 # is (delta x rounding noise)
 NOISE_PARAMS["tree4"] = NOISE_PARAMS["tree5"] = re.compile(
     r"((model_\d\.[036]|res_\d\.[036]|unify\.0|shortcut\.0|upsample\.0|model\.(0|6|8|10)(\.0)?)\.bias|(block_\d|root)\.se_[357]\.[01]\.weight)$")
+# tree9 / tree10: as tree7 / tree8, and the key bias of every self-attention layer: it adds b^T g_j to every s[i, j], constant
+# along the softmax dimension (reference: generators/generator_9.py:20-25)
+NOISE_PARAMS["tree9"] = NOISE_PARAMS["tree10"] = re.compile(
+    r"((res\.[036]|unify\.0|shortcut\.0|Upsample_\d\.0\.0)\.bias|\.key\.bias)$")
 NOISE_IN_D = ("rir_bce", "rir_r1", "style_d", "lazy_r2", "clip", "attn9_3")
-ZOO = ["dcgan", "sn3", "shuffle", "rir_gp", "rir_sn", "rir_bce", "rir_r1", "style_d", "dense4", "lazy", "lazy_r2", "clip", "attn9_3", "sk9_small", "tree4", "tree5", "tree6", "tree7", "tree8"]  # SURVEY §8(f) rank 3 pairs (make_golden_configs.py)
+ZOO = ["dcgan", "sn3", "shuffle", "rir_gp", "rir_sn", "rir_bce", "rir_r1", "style_d", "dense4", "lazy", "lazy_r2", "clip", "attn9_3", "sk9_small", "tree4", "tree5", "tree6", "tree7", "tree8", "tree9", "tree10", "tree10_2"]  # SURVEY §8(f) rank 3 pairs (make_golden_configs.py)
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 
@@ -126,6 +130,13 @@ TOL_CPU = {"shuffle": dict(tol_gloss=5e-2, tol_upd=5e-3), "rir_gp": dict(tol_glo
            # against its default-thread golden: G(z) 3.2e-5 / 1.4e-4, generator loss 2e-6 / 2.6e-4, R2 term of tree5 3.6e-5,
            # update norms (zero-gradient tensors excluded) 164 / 368 > 2e-3 with abs 4.5e-5 / 1.2e-4.  The CPU port: G(z)
            # 3.6e-5 / 1.6e-4, generator loss 3e-6 / 1.1e-4, R2 term 1.0e-4, 68 / 148 > 2e-3 with abs 2.9e-5 / 7.2e-5
+           # tree9 / tree10: CPU port G(z) 7e-6 / 3e-6, update norms 242 / 23 tensors > 2e-3 with abs 9.5e-6 / 1.4e-5
+           "tree9": dict(floor=6e-5, tol_gloss=1e-3), "tree10": dict(floor=6e-5, tol_gloss=1e-3),
+           # tree10_2 is ill-conditioned in fp32 by construction (N(0,1) weights in front of 4 096-way softmaxes): the
+           # reference's own fp32 G(z) is 2.7e-2 away from its float64 run and 1.5e-2 from itself at another thread count,
+           # the port 2.5e-2 from float64 (and 7e-11 from the reference in float64, tests/test_d6_tree.py) -> structure,
+           # initialisation, the critic's output and a finite step only
+           "tree10_2": dict(chain=False, floor=6e-5),
            "tree4": dict(floor=6e-5, tol_gloss=1e-3), "tree5": dict(floor=1.5e-4, tol_out=3e-4, tol_loss=5e-4, tol_gloss=1e-3)}
 
 
@@ -180,6 +191,8 @@ def test_zoo_cuda_fp32_matches_reference_golden(monkeypatch, name):
         tol["floor"] = 2 * TOL_CPU[name]["floor"]
     if name == "tree5":
         tol["tol_out"] = 5e-4
+    if name == "tree10_2":
+        tol["chain"] = False
     compare(name, torch.device("cuda"), **tol)
 
 
