@@ -78,6 +78,8 @@ SIGNATURES = {
                             c_float, P]),
     "ganb200_softmax_rows_fwd": (c_int, [P, P, c_int64, c_int, P]),
     "ganb200_softmax_rows_bwd": (c_int, [P, P, P, c_int64, c_int, P]),
+    "ganb200_pixnorm_fwd": (c_int, [P, P, P, c_int, c_int, c_int64, c_float, P]),
+    "ganb200_pixnorm_bwd": (c_int, [P, P, P, P, c_int, c_int, c_int64, P]),
     "ganb200_pool_sum2_eligible": (c_int, [c_int, c_int, c_int]),
     "ganb200_pool_sum2": (c_int, [P, P, P, c_int64, c_int, c_int, c_int, P]),
     "ganb200_sk_bwd_finish": (c_int, [P, P, P, P, P, c_int, c_int, c_int, c_int, c_int, P]),

@@ -21,6 +21,11 @@ __device__ __forceinline__ float u_apply(int op, float x, float p0, float p1) {
     case GANB200_U_LEAKY_MASK: return x > 0.f ? 1.f : p0;
     case GANB200_U_COPY: return x;
     case GANB200_U_POW: return powf(x, p0);
+    // exact GELU x * Phi(x) (nn.GELU(), generators/generator_6.py:12) and its first two derivatives
+    case GANB200_U_GELU: return 0.5f * x * (1.f + erff(x * 0.70710678118654752f));
+    case GANB200_U_GELU_GRAD:
+      return 0.5f * (1.f + erff(x * 0.70710678118654752f)) + x * 0.39894228040143268f * expf(-0.5f * x * x);
+    case GANB200_U_GELU_GRAD2: return (2.f - x * x) * 0.39894228040143268f * expf(-0.5f * x * x);
   }
   return x;
 }
@@ -231,6 +236,7 @@ extern "C" int ganb200_ew_unary(int op, const float* x, float* y, int64_t n, flo
     UNARY_CASE(GANB200_U_AFFINE) UNARY_CASE(GANB200_U_RSQRT_EPS) UNARY_CASE(GANB200_U_SQRT)
     UNARY_CASE(GANB200_U_LEAKY) UNARY_CASE(GANB200_U_RECIP) UNARY_CASE(GANB200_U_LEAKY_MASK)
     UNARY_CASE(GANB200_U_COPY) UNARY_CASE(GANB200_U_POW)
+    UNARY_CASE(GANB200_U_GELU) UNARY_CASE(GANB200_U_GELU_GRAD) UNARY_CASE(GANB200_U_GELU_GRAD2)
     default: return fail(GANB200_BAD_ARG, "ew_unary: unknown op%s %lld", "", op);
   }
   GB_CHECK_LAUNCH();

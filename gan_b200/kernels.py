@@ -15,6 +15,7 @@ from ._lib import ConvDesc
 
 # enums from include/ganb200.h
 U_SIGMOID, U_TANH, U_SQUARE, U_AFFINE, U_RSQRT_EPS, U_SQRT, U_LEAKY, U_RECIP, U_LEAKY_MASK, U_COPY, U_POW = range(11)
+U_GELU, U_GELU_GRAD, U_GELU_GRAD2 = 11, 12, 13
 B_ADD, B_SUB, B_MUL, B_DIV, B_SIGMOID_BWD, B_TANH_BWD, B_LEAKY_BWD = range(7)
 V_NC, V_C, V_N, V_SCALAR = range(4)
 R_HW, R_NHW, R_CHW, R_ALL = range(4)
@@ -410,6 +411,22 @@ class CudaBackend:
         gx = torch.empty_like(y)
         n = y.shape[-1]
         _lib.check(self.lib.ganb200_softmax_rows_bwd(self._p(gy), self._p(y), self._p(gx), y.numel() // max(n, 1), n, st))
+        return gx
+
+    # -- pixelwise feature-vector normalisation (generators/generator_11.py:9-16) ---------------------
+    def pixnorm_fwd(self, x, eps):
+        N, C, HW = _nchw(x)
+        st = self._prep(x)
+        y = torch.empty_like(x)
+        r = torch.empty((N, HW), dtype=torch.float32, device=x.device)
+        _lib.check(self.lib.ganb200_pixnorm_fwd(self._p(x), self._p(y), self._p(r), N, C, HW, eps, st))
+        return y, r
+
+    def pixnorm_bwd(self, gy, y, r):
+        N, C, HW = _nchw(y)
+        st = self._prep(gy, y, r)
+        gx = torch.empty_like(y)
+        _lib.check(self.lib.ganb200_pixnorm_bwd(self._p(gy), self._p(y), self._p(r), self._p(gx), N, C, HW, st))
         return gx
 
     def pool_sum2_ok(self, t0, t1, out):

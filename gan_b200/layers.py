@@ -51,6 +51,14 @@ class LeakyReLU(nn.LeakyReLU):
         return ops.leaky_relu(x, self.negative_slope)
 
 
+class GELU(nn.GELU):
+    """nn.GELU() — generators/generator_6.py:12 (the exact form only)."""
+
+    def forward(self, x):
+        assert self.approximate == 'none'
+        return ops.gelu(x)
+
+
 class _BatchNormMixin:
     def forward(self, x):
         self._check_input_dim(x)

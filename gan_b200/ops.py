@@ -142,12 +142,13 @@ def linear(x, w, bias=None, alpha=1.0, engine=None):
     return y.reshape(B, w.shape[0])
 
 
-def conv_transpose2d(x, wt, bias=None, stride=1, pad=0, engine=None):
-    """nn.ConvTranspose2d semantics, wt:(Cin,Cout,R,S) = the KCRS weight of the conv whose dgrad this is."""
+def conv_transpose2d(x, wt, bias=None, stride=1, pad=0, engine=None, alpha=1.0):
+    """nn.ConvTranspose2d semantics, wt:(Cin,Cout,R,S) = the KCRS weight of the conv whose dgrad this is; `alpha` scales
+    the product (the run-time equalised-learning-rate gain of generators/generator_11.py:92-103)."""
     R, S = wt.shape[2:]
     Ho = (x.shape[2] - 1) * stride - 2 * pad + R
     Wo = (x.shape[3] - 1) * stride - 2 * pad + S
-    y = ConvDgradFn.apply(x, wt, ConvCfg(stride, pad, 0, 1.0, engine), (Ho, Wo))
+    y = ConvDgradFn.apply(x, wt, ConvCfg(stride, pad, 0, float(alpha), engine), (Ho, Wo))
     if bias is not None:
         y = AddBcFn.apply(y, bias, KN.V_C)
     return y
@@ -295,6 +296,26 @@ class SoftmaxRowsFn(Function):
 
 def softmax_rows(x):
     return SoftmaxRowsFn.apply(x)
+
+
+class PixnormFn(Function):
+    """x / sqrt(eps + mean_c x^2) per pixel (generators/generator_11.py:9-16).  Generators are differentiated once."""
+
+    @staticmethod
+    def forward(ctx, x, eps):
+        y, r = K().pixnorm_fwd(_c(x), float(eps))
+        ctx.save_for_backward(y, r)
+        return y
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, gy):
+        y, r = ctx.saved_tensors
+        return K().pixnorm_bwd(_c(gy), y, r), None
+
+
+def pixnorm(x, eps=1e-8):
+    return PixnormFn.apply(x, eps)
 
 
 class _SkLink:
@@ -503,6 +524,10 @@ class UnaryFn(Function):
             gx = affine(MulFn.apply(g, MulFn.apply(y, y)), -1.0, 0.0)
         elif op == KN.U_POW:
             gx = MulFn.apply(g, affine(UnaryFn.apply(x, KN.U_POW, p0 - 1.0, 0.0), p0, 0.0))
+        elif op == KN.U_GELU:
+            gx = MulFn.apply(g, UnaryFn.apply(x, KN.U_GELU_GRAD, 0.0, 0.0))
+        elif op == KN.U_GELU_GRAD:
+            gx = MulFn.apply(g, UnaryFn.apply(x, KN.U_GELU_GRAD2, 0.0, 0.0))
         else:
             raise NotImplementedError(op)
         return gx, None, None, None
@@ -534,6 +559,11 @@ def tanh(x):
 
 def leaky_relu(x, slope):
     return UnaryFn.apply(x, KN.U_LEAKY, float(slope), 0.0)
+
+
+def gelu(x):
+    """nn.GELU() (exact erf form) — generators/generator_6.py:12; twice differentiable."""
+    return UnaryFn.apply(x, KN.U_GELU, 0.0, 0.0)
 
 
 def square(x):

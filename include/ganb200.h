@@ -161,7 +161,9 @@ enum {
   GANB200_U_SIGMOID = 0, GANB200_U_TANH = 1, GANB200_U_SQUARE = 2, GANB200_U_AFFINE = 3, /* p0*x+p1 */
   GANB200_U_RSQRT_EPS = 4 /* rsqrt(x+p0) */, GANB200_U_SQRT = 5, GANB200_U_LEAKY = 6 /* slope p0 */,
   GANB200_U_RECIP = 7, GANB200_U_LEAKY_MASK = 8 /* x>0 ? 1 : p0 */, GANB200_U_COPY = 9,
-  GANB200_U_POW = 10 /* x^p0 */
+  GANB200_U_POW = 10 /* x^p0 */,
+  GANB200_U_GELU = 11 /* x*Phi(x), exact erf form: nn.GELU(), generators/generator_6.py:12 */,
+  GANB200_U_GELU_GRAD = 12 /* Phi(x) + x*phi(x) */, GANB200_U_GELU_GRAD2 = 13 /* (2 - x^2)*phi(x) */
 };
 enum {
   GANB200_B_ADD = 0, GANB200_B_SUB = 1, GANB200_B_MUL = 2, GANB200_B_DIV = 3,
@@ -190,6 +192,13 @@ int ganb200_bmm(const float* a, const float* b, float* c, int batch, int M, int 
                 int64_t sak, int64_t sbb, int64_t sbk, int64_t sbn, float alpha, void* stream);
 int ganb200_softmax_rows_fwd(const float* x, float* y, int64_t rows, int n, void* stream);
 int ganb200_softmax_rows_bwd(const float* gy, const float* y, float* gx, int64_t rows, int n, void* stream);
+
+/* Pixelwise feature-vector normalisation (generators/generator_11.py:9-16, `Pixnorm`): x:[N,C,HW]
+ *   fwd: rnorm[n,p] = 1 / sqrt(eps + mean_c x[n,c,p]^2),  y = x * rnorm
+ *   bwd: gx = rnorm * (gy - y * mean_c(gy * y)) */
+int ganb200_pixnorm_fwd(const float* x, float* y, float* rnorm, int N, int C, int64_t HW, float eps, void* stream);
+int ganb200_pixnorm_bwd(const float* gy, const float* y, const float* rnorm, float* gx, int N, int C, int64_t HW,
+                        void* stream);
 /* AdaptiveAvgPool2d(out_size) of t0 + t1 without materialising the sum (the input of the SK attention,
  * generators/generator_13_5.py:77-80): t0, t1 [planes, H, W] -> out [planes, out_size, out_size].  Eligible shapes
  * (ganb200_pool_sum2_eligible): 32 x 32 and 64 x 64 planes to 5 x 5; torch's bins. */

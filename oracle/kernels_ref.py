@@ -9,6 +9,7 @@ import torch
 import torch.nn.functional as F
 
 U_SIGMOID, U_TANH, U_SQUARE, U_AFFINE, U_RSQRT_EPS, U_SQRT, U_LEAKY, U_RECIP, U_LEAKY_MASK, U_COPY, U_POW = range(11)
+U_GELU, U_GELU_GRAD, U_GELU_GRAD2 = 11, 12, 13
 B_ADD, B_SUB, B_MUL, B_DIV, B_SIGMOID_BWD, B_TANH_BWD, B_LEAKY_BWD = range(7)
 V_NC, V_C, V_N, V_SCALAR = range(4)
 R_HW, R_NHW, R_CHW, R_ALL = range(4)
@@ -91,6 +92,11 @@ class RefBackend:
         if op == U_LEAKY_MASK: return torch.where(x > 0, torch.ones_like(x), torch.full_like(x, p0))
         if op == U_COPY: return x.clone()
         if op == U_POW: return torch.pow(x, p0)
+        if op == U_GELU: return F.gelu(x)                      # exact (erf) form, nn.GELU() — generators/generator_6.py:12
+        if op in (U_GELU_GRAD, U_GELU_GRAD2):
+            phi = torch.exp(-0.5 * x * x) * 0.3989422804014327
+            if op == U_GELU_GRAD2: return (2.0 - x * x) * phi
+            return 0.5 * (1.0 + torch.erf(x * 0.7071067811865476)) + x * phi
         raise ValueError(op)
 
     def ew_binary(self, op, a, b, p0=0.0):
@@ -120,6 +126,17 @@ class RefBackend:
 
     def softmax_rows_bwd(self, gy, y):
         return (y * (gy - (gy * y).sum(-1, keepdim=True))).contiguous()
+
+    def pixnorm_fwd(self, x, eps):
+        """generators/generator_11.py:9-16 — x / sqrt(eps + mean over channels of x^2); also returns 1 / norm per pixel"""
+        n, c = x.shape[:2]
+        r = torch.rsqrt(eps + (x * x).sum(1, keepdim=True) / c)
+        return (x * r).contiguous(), r.reshape(n, -1).contiguous()
+
+    def pixnorm_bwd(self, gy, y, r):
+        c = y.shape[1]
+        d = (gy * y).sum(1, keepdim=True) / c
+        return (r.reshape(y.shape[0], 1, *y.shape[2:]) * (gy - y * d)).contiguous()
 
     def pool_sum2_ok(self, t0, t1, out):
         return (t0.dim() == 4 and t0.shape == t1.shape and out == 5 and t0.shape[-1] == t0.shape[-2]

@@ -118,6 +118,13 @@ CONFIGS = {
     "tree10_2": dict(gen="generators.generator_10_2", g_args=lambda: (256,), g_kw={},
                      dis="discriminators.discriminator_2", d_args=lambda: (1, 64, 3), d_kw={},
                      train="train.gan", B=4, names=("G10_2", "D2")),
+    # the GELU tree generator of get_6 and the Pixnorm / equalised self-attention generator of get_11
+    "tree6g": dict(gen="generators.generator_6", g_args=lambda: (256,), g_kw={},
+                   dis="discriminators.discriminator_3_wgangp", d_args=lambda: (1, 64, 3), d_kw={},
+                   train="train.wgangp", B=4, names=("G6", "D3_WGAN")),
+    "tree11": dict(gen="generators.generator_11", g_args=lambda: (256,), g_kw={},
+                   dis="discriminators.discriminator_3_wgangp", d_args=lambda: (1, 64, 3), d_kw={},
+                   train="train.wganlazygp", B=4, names=("G11", "D3_WGAN"), d_idx=(0, 1)),
     # the same BatchNorm critic under R1 + R2: the penalties differentiate 27 BatchNorms twice
     "rir_r1": dict(gen="generators.generator_2", g_args=lambda: (1, 256, 64, 3), g_kw={},
                    dis="discriminators.discriminator_5", d_args=lambda: (), d_kw={},

@@ -243,7 +243,8 @@ def test_pointwise(cu, ref):
     for op, inp, p0, p1 in [(KN.U_SIGMOID, x, 0, 0), (KN.U_TANH, x, 0, 0), (KN.U_SQUARE, x, 0, 0),
                             (KN.U_AFFINE, x, 1.7, -0.3), (KN.U_RSQRT_EPS, xp, 1e-8, 0), (KN.U_SQRT, xp, 0, 0),
                             (KN.U_LEAKY, x, 0.2, 0), (KN.U_RECIP, xp, 0, 0), (KN.U_LEAKY_MASK, x, 0.1, 0),
-                            (KN.U_COPY, x, 0, 0), (KN.U_POW, xp, 1.5, 0)]:
+                            (KN.U_COPY, x, 0, 0), (KN.U_POW, xp, 1.5, 0),
+                            (KN.U_GELU, x * 3, 0, 0), (KN.U_GELU_GRAD, x * 3, 0, 0), (KN.U_GELU_GRAD2, x * 3, 0, 0)]:
         assert rel(cu.ew_unary(op, g(inp), p0, p1), ref.ew_unary(op, inp, p0, p1)) < FP32_TOL, op
     a, b = rnd(6, 10, 7, 9), torch.rand(6, 10, 7, 9) * 0.8 + 0.1
     for op, p0 in [(KN.B_ADD, 0), (KN.B_SUB, 0), (KN.B_MUL, 0), (KN.B_DIV, 0), (KN.B_SIGMOID_BWD, 0),
@@ -632,6 +633,19 @@ def test_depthwise_conv_family(cu, ref, case):
     dy = rnd(*y_r.shape)
     assert rel(cu.dwconv_dgrad(g(dy), g(w), (H, W), stride, pad, 0.7), ref.dwconv_dgrad(dy, w, (H, W), stride, pad, 0.7)) < FP32_TOL
     assert rel(cu.dwconv_wgrad(g(x), g(dy), (k, k), stride, pad, 0.7), ref.dwconv_wgrad(x, dy, (k, k), stride, pad, 0.7)) < 2e-5
+
+
+@pytest.mark.parametrize("shape", [(4, 7, 5, 3), (2, 1024, 4, 4), (3, 20, 64, 64), (5, 130, 1, 1)])
+def test_pixnorm(cu, ref, shape):
+    """Pixnorm of generators/generator_11.py:9-16 and its backward"""
+    torch.manual_seed(14)
+    x, gy = rnd(*shape) * 2, rnd(*shape)
+    y_r, r_r = ref.pixnorm_fwd(x, 1e-8)
+    y, r = cu.pixnorm_fwd(g(x), 1e-8)
+    assert rel(y, y_r) < FP32_TOL and rel(r, r_r) < FP32_TOL
+    assert rel(cu.pixnorm_bwd(g(gy), y, r), ref.pixnorm_bwd(gy, y_r, r_r)) < FP32_TOL
+    zero = torch.zeros(2, 6, 3, 3)                      # eps keeps an all-zero pixel finite
+    assert torch.isfinite(cu.pixnorm_fwd(g(zero), 1e-8)[0]).all()
 
 
 def test_depthwise_conv_rejects_other_kernels(cu):

@@ -84,6 +84,8 @@ def test_pointwise_and_broadcast(ref_backend):
     assert gradcheck(ops.sigmoid, (x,)) and gradgradcheck(ops.sigmoid, (x,))
     assert gradcheck(ops.tanh, (x,)) and gradgradcheck(ops.tanh, (x,))
     assert gradcheck(lambda t: ops.leaky_relu(t, 0.2), (x,)) and gradgradcheck(lambda t: ops.leaky_relu(t, 0.2), (x,))
+    assert torch.allclose(ops.gelu(x), torch.nn.functional.gelu(x), atol=1e-12)    # exact erf form (generator_6)
+    assert gradcheck(ops.gelu, (x,)) and gradgradcheck(ops.gelu, (x,))
     xp = (torch.rand(2, 3, dtype=D) + 0.5).requires_grad_()
     assert gradcheck(ops.sqrt, (xp,)) and gradgradcheck(ops.sqrt, (xp,))
     assert gradcheck(lambda t: ops.rsqrt_eps(t, 1e-8), (xp,))
@@ -201,13 +203,13 @@ def test_modulated_conv_equals_per_sample_weight_form(ref_backend, k):
 # ---------------------------------------------------------------------------------------------------------------------
 # ops of the other configs (cfg4 / cfg5)
 # ---------------------------------------------------------------------------------------------------------------------
-@pytest.mark.parametrize("stride", [1, 2])
-def test_depthwise_conv_is_twice_differentiable(ref_backend, stride):
+@pytest.mark.parametrize("stride,k", [(1, 3), (2, 3), (1, 5), (2, 5), (1, 7)])
+def test_depthwise_conv_is_twice_differentiable(ref_backend, stride, k):
     import torch.nn.functional as F
     from gan_b200 import ops
     torch.manual_seed(0)
     x = torch.randn(2, 6, 9, 8, dtype=torch.float64, requires_grad=True)
-    w = torch.randn(6, 1, 3, 3, dtype=torch.float64, requires_grad=True)
+    w = torch.randn(6, 1, k, k, dtype=torch.float64, requires_grad=True)
     b = torch.randn(6, dtype=torch.float64, requires_grad=True)
 
     def penalty(conv):
@@ -215,8 +217,8 @@ def test_depthwise_conv_is_twice_differentiable(ref_backend, stride):
         (gx,) = torch.autograd.grad(y.tanh().sum(), x, create_graph=True)
         return y.square().sum() + gx.square().sum()
 
-    want = torch.autograd.grad(penalty(lambda x, w, b: F.conv2d(x, w, b, stride, 1, groups=6)), (x, w, b))
-    got = torch.autograd.grad(penalty(lambda x, w, b: ops.depthwise_conv2d(x, w, b, stride, 1)), (x, w, b))
+    want = torch.autograd.grad(penalty(lambda x, w, b: F.conv2d(x, w, b, stride, k // 2, groups=6)), (x, w, b))
+    got = torch.autograd.grad(penalty(lambda x, w, b: ops.depthwise_conv2d(x, w, b, stride, k // 2)), (x, w, b))
     for a, e in zip(got, want):
         assert torch.allclose(a, e, rtol=1e-9, atol=1e-9)
 
