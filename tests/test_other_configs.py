@@ -46,7 +46,7 @@ NOISE_PARAMS["tree6g"] = re.compile(
     r"(res\.[036]|unify\.0|shortcut\.0|Stem_1\.0|upsample\.0|Upsample_\d\.0|(residual|transient)_pre_conv\.0)\.bias$")
 NOISE_PARAMS["tree11"] = re.compile(r"\.key\.bias$")
 NOISE_IN_D = ("rir_bce", "rir_r1", "style_d", "lazy_r2", "clip", "attn9_3")
-ZOO = ["dcgan", "sn3", "shuffle", "rir_gp", "rir_sn", "rir_bce", "rir_r1", "style_d", "dense4", "lazy", "lazy_r2", "clip", "attn9_3", "sk9_small", "tree4", "tree5", "tree6", "tree7", "tree8", "tree9", "tree10", "tree10_2", "tree6g", "tree11"]  # SURVEY §8(f) rank 3 pairs (make_golden_configs.py)
+ZOO = ["dcgan", "sn3", "shuffle", "rir_gp", "rir_sn", "rir_bce", "rir_r1", "style_d", "dense4", "lazy", "lazy_r2", "clip", "attn9_3", "sk9_small", "tree4", "tree5", "tree6", "tree7", "tree8", "tree9", "tree10", "tree10_2", "tree6g", "tree11", "tree13_3", "tree13_4"]  # SURVEY §8(f) rank 3 pairs (make_golden_configs.py)
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 
@@ -144,10 +144,16 @@ TOL_CPU = {"shuffle": dict(tol_gloss=5e-2, tol_upd=5e-3), "rir_gp": dict(tol_glo
            # the port 2.5e-2 from float64 (and 7e-11 from the reference in float64, tests/test_d6_tree.py) -> structure,
            # initialisation, the critic's output and a finite step only
            "tree10_2": dict(chain=False, floor=6e-5),
+           # tree13_3 / tree13_4 (planes 16, batch 8): chaotic at initialisation — BatchNorm1d over 8 samples inside hundreds of
+           # attention heads; the port's float32 G(z) is 3e-2 / 1.1 from the reference's, whose own float64 run amplifies a
+           # 1e-14 difference to 2e-4 over the five levels (tests/test_d6_tree.py compares them level by level in float64)
+           "tree13_3": dict(chain=False, floor=6e-5), "tree13_4": dict(chain=False, floor=6e-5),
            "tree4": dict(floor=6e-5, tol_gloss=1e-3), "tree5": dict(floor=1.5e-4, tol_out=3e-4, tol_loss=5e-4, tol_gloss=1e-3)}
 
 
-@pytest.mark.parametrize("name", ["cfg1", "cfg4", "cfg5", "main"] + ZOO)
+# (tree10_2 / tree13_4 — structure-only comparisons of chaotic generators — run on the GPU only; on the CPU the float64 tests
+# of tests/test_d6_tree.py say more about them in less time)
+@pytest.mark.parametrize("name", ["cfg1", "cfg4", "cfg5", "main"] + [n for n in ZOO if n not in ("tree10_2", "tree13_4")])
 def test_config_cpu_port_matches_reference_golden(ref_backend, name):
     compare(name, torch.device("cpu"), **{**dict(tol_out=1e-4, tol_loss=1e-4, tol_upd=2e-3), **TOL_CPU.get(name, {})})
 
@@ -198,7 +204,7 @@ def test_zoo_cuda_fp32_matches_reference_golden(monkeypatch, name):
         tol["floor"] = max(2 * TOL_CPU[name]["floor"], 1e-5)
     if name == "tree5":
         tol["tol_out"] = 5e-4
-    if name == "tree10_2":
+    if TOL_CPU.get(name, {}).get("chain") is False:
         tol["chain"] = False
     compare(name, torch.device("cuda"), **tol)
 
