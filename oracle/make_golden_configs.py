@@ -133,6 +133,10 @@ CONFIGS = {
     "tree13_4": dict(gen="generators.generator_13_4", g_args=lambda: (256,), g_kw={"planes": 16},
                      dis="discriminators.discriminator_3_wgangp", d_args=lambda: (1, 64, 3), d_kw={},
                      train="train.wgangp", B=8, names=("G13_4", "D3_WGAN"), slim=True),
+    # the first style-based ancestor (a mapping network per modulated convolution, no BatchNorm), at planes 16
+    "tree13": dict(gen="generators.generator_13", g_args=lambda: (256,), g_kw={"planes": 16},
+                   dis="discriminators.discriminator_3_wgangpsn", d_args=lambda: (1, 64, 3), d_kw={},
+                   train="train.wgansnR2", B=4, names=("G13", "D3_WGANSN")),
     # the same BatchNorm critic under R1 + R2: the penalties differentiate 27 BatchNorms twice
     "rir_r1": dict(gen="generators.generator_2", g_args=lambda: (1, 256, 64, 3), g_kw={},
                    dis="discriminators.discriminator_5", d_args=lambda: (), d_kw={},

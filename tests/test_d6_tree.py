@@ -135,3 +135,14 @@ def test_final_generator_predecessors_equal_reference(ref_backend, name):
         for a, b in zip(lv[i], lv_ref[i]):
             assert rel(a, b) < bound, (i, rel(a, b))
     assert rel(y, y_ref) < 5e-2
+
+
+def test_generator_13_2_is_generator_13():
+    """the reference's generator_13_2.py is byte for byte its generator_13.py; here it re-exports generator_13's classes"""
+    import filecmp
+    import os
+    ref_dir = os.path.dirname(R.load("generators.generator_13").__file__)
+    assert filecmp.cmp(os.path.join(ref_dir, "generator_13.py"), os.path.join(ref_dir, "generator_13_2.py"), shallow=False)
+    a, b = importlib.import_module("generators.generator_13"), importlib.import_module("generators.generator_13_2")
+    for cls in ("Generator", "Tree", "BasicBlock", "StyleConv", "Conv2dWeightModulate", "SelfAttention"):
+        assert getattr(a, cls) is getattr(b, cls)
