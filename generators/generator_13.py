@@ -173,9 +173,9 @@ class StyleConv(nn.Module):
         y = self.conv(x, w)
         if self.use_noise:
             if rng.philox_noise():
-                z = KN.backend().noise_fill(tuple(y.shape), rng.current(), self.noise_layer, y.device)
+                z = KN.backend().noise_fill(tuple(y.shape), rng.current(), self.noise_layer, y.device).to(y.dtype)
             else:   # the reference's own draw: torch.randn of this shape on the same generator
-                z = rng.randn(*y.shape, device=y.device)
+                z = rng.randn(*y.shape, device=y.device).to(y.dtype)
             y = ops.noise_add(y, self.scale_noise, z)
         return ops.add_bc(y, self.bias, KN.V_C)
 

@@ -137,6 +137,10 @@ CONFIGS = {
     "tree13": dict(gen="generators.generator_13", g_args=lambda: (256,), g_kw={"planes": 16},
                    dis="discriminators.discriminator_3_wgangpsn", d_args=lambda: (1, 64, 3), d_kw={},
                    train="train.wgansnR2", B=4, names=("G13", "D3_WGANSN")),
+    # the StyleGAN2-shaped generator of get_12 (noise drawn inside every StyleConv: the replay draws the same stream), planes 16
+    "tree12": dict(gen="generators.generator_12", g_args=lambda: (256,), g_kw={"planes": 16},
+                   dis="discriminators.discriminator_2", d_args=lambda: (1, 64, 3), d_kw={},
+                   train="train.ganR2", B=4, names=("G12", "D2")),
     # the same BatchNorm critic under R1 + R2: the penalties differentiate 27 BatchNorms twice
     "rir_r1": dict(gen="generators.generator_2", g_args=lambda: (1, 256, 64, 3), g_kw={},
                    dis="discriminators.discriminator_5", d_args=lambda: (), d_kw={},
