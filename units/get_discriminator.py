@@ -1,6 +1,6 @@
 """units.get_discriminator — drop-in for the reference's units/get_discriminator.py:15-90: `get_<name>(...)` builds a
-discriminator / critic and moves it to `device`, same names and argument lists.  Lazy imports: a family this repo does
-not carry (outside SURVEY §8(a)) raises NotImplementedError when asked for, not at import.
+discriminator / critic and moves it to `device`, same names and argument lists.  Lazy imports; every discriminator file
+of the reference has a drop-in here.
 
 `get_9_4` is an addition (the reference's main.py builds discriminator_9_4 by hand).  discriminator_9_2 / _9_3 have no
 factory in the reference either; they are importable modules (`discriminators.discriminator_9_3.Discriminator()`)."""

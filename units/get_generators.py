@@ -1,7 +1,7 @@
 """units.get_generators — drop-in for the reference's units/get_generators.py:12-111: `get_<name>(...)` builds a
-generator and moves it to `device`, same names and argument lists.  Generators are imported lazily, so the factory of
-a family this repo does not carry (everything outside SURVEY §8(a) and §8(f): generator_4-13) raises a clear
-NotImplementedError instead of failing the whole module at import as a missing file would.
+generator and moves it to `device`, same names and argument lists.  Generators are imported lazily (the reference
+imports fourteen model files at module import); every factory of the reference builds — the one model file without a
+drop-in is generators/generator_13_1.py, which no factory names (`_module` raises NotImplementedError for it).
 
 `get_13_5` and `get_14` are additions: the reference has no factory for its two newest generators (its main.py builds
 them by hand)."""
