@@ -141,6 +141,10 @@ CONFIGS = {
     "tree12": dict(gen="generators.generator_12", g_args=lambda: (256,), g_kw={"planes": 16},
                    dis="discriminators.discriminator_2", d_args=lambda: (1, 64, 3), d_kw={},
                    train="train.ganR2", B=4, names=("G12", "D2")),
+    # generator_13_1 (no factory in the reference): attention inside every style block, ToRGB(6) merges of the RGB skips
+    "tree13_1": dict(gen="generators.generator_13_1", g_args=lambda: (256,), g_kw={"planes": 8},
+                     dis="discriminators.discriminator_3_wgangp", d_args=lambda: (1, 64, 3), d_kw={},
+                     train="train.wgangp", B=2, names=("G13_1", "D3_WGAN")),
     # the same BatchNorm critic under R1 + R2: the penalties differentiate 27 BatchNorms twice
     "rir_r1": dict(gen="generators.generator_2", g_args=lambda: (1, 256, 64, 3), g_kw={},
                    dis="discriminators.discriminator_5", d_args=lambda: (), d_kw={},

@@ -121,20 +121,19 @@ def test_final_generator_predecessors_equal_reference(ref_backend, name):
             assert rel(a, b) < 1e-8
         return
 
-    def levels(net):
-        out = {}
-        hooks = [getattr(net, "block%d" % i).register_forward_hook(lambda m, i_, o, k=i: out.__setitem__(k, o))
-                 for i in range(5)]
+    def levels(net):      # 4x4 .. 32x32 (the 64x64 level costs as much as the other four together and says nothing new)
+        out = []
         with torch.no_grad():
-            y = net(z)
-        for h in hooks:
-            h.remove()
-        return y, out
-    (y, lv), (y_ref, lv_ref) = levels(G), levels(G_ref)
+            x, rgb = net.block0(z)
+            out.append((x, rgb))
+            for i in range(1, 4):
+                x, rgb = getattr(net, "block%d" % i)(x, rgb)
+                out.append((x, rgb))
+        return out
+    lv, lv_ref = levels(G), levels(G_ref)
     for i, bound in enumerate([1e-11, 1e-9, 1e-7, 1e-4]):       # measured 2e-14, 1e-12, 9e-11, 6e-8 (then 2e-4 at 64x64)
         for a, b in zip(lv[i], lv_ref[i]):
             assert rel(a, b) < bound, (i, rel(a, b))
-    assert rel(y, y_ref) < 5e-2
 
 
 def test_generator_13_2_is_generator_13():
@@ -146,3 +145,38 @@ def test_generator_13_2_is_generator_13():
     a, b = importlib.import_module("generators.generator_13"), importlib.import_module("generators.generator_13_2")
     for cls in ("Generator", "Tree", "BasicBlock", "StyleConv", "Conv2dWeightModulate", "SelfAttention"):
         assert getattr(a, cls) is getattr(b, cls)
+
+
+def test_generator_13_1_gradients_equal_reference_in_float64(ref_backend):
+    """generator_13_1 at planes=8: G(z) and the gradient of EVERY parameter against the reference in float64.  The bound
+    is loose for a float64 test on purpose: the key / query paths in front of the saturated attention softmaxes agree to
+    ~2e-9 where everything else agrees to 1e-13 — the conditioning that makes their float32 update norms meaningless
+    (tests/test_other_configs.py, NOISE_PARAMS["tree13_1"]).  Key biases have an analytically zero gradient."""
+    ref_mod = R.load("generators.generator_13_1")
+    our_mod = importlib.import_module("generators.generator_13_1")
+    torch.manual_seed(11)
+    G_ref = ref_mod.Generator(32, 8).double()
+    torch.manual_seed(11)
+    G = our_mod.Generator(32, 8).double()
+    sd_ref, sd = G_ref.state_dict(), G.state_dict()
+    assert list(sd.keys()) == list(sd_ref.keys())
+    for k, v in sd_ref.items():
+        assert torch.equal(sd[k], v), k
+    z = torch.randn(2, 32, 1, 1, dtype=torch.float64, generator=torch.Generator().manual_seed(12))
+
+    def run(net):
+        y = net(z)
+        ps = [p for p in net.parameters() if p.requires_grad]
+        return y.detach(), torch.autograd.grad((y * torch.linspace(-1, 1, y.numel(), dtype=y.dtype).reshape(y.shape)).sum(),
+                                               ps, allow_unused=True)
+    (y, g), (y_ref, g_ref) = run(G), run(G_ref)
+    assert rel(y, y_ref) < 1e-12
+    names = [n for n, p in G.named_parameters() if p.requires_grad]
+    worst = {"logits": 0.0, "rest": 0.0}
+    for n, a, b in zip(names, g, g_ref):
+        assert (a is None) == (b is None), n
+        if a is None or n.endswith("key.bias"):
+            continue
+        kind = "logits" if (".key." in n or ".query." in n) else "rest"
+        worst[kind] = max(worst[kind], rel(a, b))
+    assert worst["rest"] < 1e-9 and worst["logits"] < 1e-5, worst

@@ -48,8 +48,13 @@ NOISE_PARAMS["tree11"] = re.compile(r"\.key\.bias$")
 # tree13: here f = query (generators/generator_13.py:331-335), so the query biases are the softmax-invariant ones
 NOISE_PARAMS["tree13"] = re.compile(r"\.query\.bias$")
 NOISE_PARAMS["tree12"] = re.compile(r"\.key\.bias$")      # f = key here (generators/generator_12.py:139-143)
+# tree13_1: its feature maps reach |x| ~ 1e3 at initialisation, so the 4 096-way attention softmaxes are saturated and the
+# gradient of everything in front of the logits (the key / query StyleConvs with their mapping networks: 2 840 tensors) is
+# a difference of nearly equal numbers — in float64 those gradients agree with the reference's to 2e-9 against 1e-13 for
+# the rest (tests/test_d6_tree.py), a 1e7 amplification that leaves nothing in float32, in either implementation
+NOISE_PARAMS["tree13_1"] = re.compile(r"\.(key|query)\.")
 NOISE_IN_D = ("rir_bce", "rir_r1", "style_d", "lazy_r2", "clip", "attn9_3")
-ZOO = ["dcgan", "sn3", "shuffle", "rir_gp", "rir_sn", "rir_bce", "rir_r1", "style_d", "dense4", "lazy", "lazy_r2", "clip", "attn9_3", "sk9_small", "tree4", "tree5", "tree6", "tree7", "tree8", "tree9", "tree10", "tree10_2", "tree6g", "tree11", "tree13_3", "tree13_4", "tree13", "tree12"]  # SURVEY §8(f) rank 3 pairs (make_golden_configs.py)
+ZOO = ["dcgan", "sn3", "shuffle", "rir_gp", "rir_sn", "rir_bce", "rir_r1", "style_d", "dense4", "lazy", "lazy_r2", "clip", "attn9_3", "sk9_small", "tree4", "tree5", "tree6", "tree7", "tree8", "tree9", "tree10", "tree10_2", "tree6g", "tree11", "tree13_3", "tree13_4", "tree13", "tree12", "tree13_1"]  # SURVEY §8(f) rank 3 pairs (make_golden_configs.py)
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 
@@ -147,6 +152,8 @@ TOL_CPU = {"shuffle": dict(tol_gloss=5e-2, tol_upd=5e-3), "rir_gp": dict(tol_glo
            # tree12 (a noise plane drawn inside each of 579 StyleConvs; the replay draws the same stream): G(z) 6e-7, update
            # norms 64 of 4 396 > 2e-3 with abs 5.2e-5
            "tree12": dict(floor=6e-5),
+           # tree13_1: G(z) 2e-6; of the 9 502 update norms outside the key / query paths one exceeds 2e-3 (abs 6e-6)
+           "tree13_1": dict(floor=1e-5),
            # tree10_2 is ill-conditioned in fp32 by construction (N(0,1) weights in front of 4 096-way softmaxes): the
            # reference's own fp32 G(z) is 2.7e-2 away from its float64 run and 1.5e-2 from itself at another thread count,
            # the port 2.5e-2 from float64 (and 7e-11 from the reference in float64, tests/test_d6_tree.py) -> structure,
@@ -199,8 +206,9 @@ def test_config_cuda_tcgen05_matches_reference_golden(monkeypatch, name):
     compare(name, torch.device("cuda"), **TOL_BF16[name])
 
 
+# (tree13_1 was added after this round's GPU time was spent: CPU port only; its kernels are those of tree12 / tree13)
 @pytest.mark.gpu
-@pytest.mark.parametrize("name", ZOO)
+@pytest.mark.parametrize("name", [n for n in ZOO if n != "tree13_1"])
 def test_zoo_cuda_fp32_matches_reference_golden(monkeypatch, name):
     monkeypatch.setenv("GANB200_PRECISION", "fp32")
     # Adam's first update is lr * g / (|g| + eps): its norm follows the ABSOLUTE rounding error of tiny gradients.  Measured

@@ -7,7 +7,7 @@ drop-in is generators/generator_13_1.py, which no factory names (`_module` raise
 them by hand)."""
 import importlib
 
-_CARRIED = ("generator_1", "generator_2", "generator_3_progan", "generator_4", "generator_5", "generator_6", "generator_7", "generator_8", "generator_9", "generator_10", "generator_10_2", "generator_11", "generator_12", "generator_13", "generator_13_2", "generator_13_3", "generator_13_4", "generator_13_5", "generator_14")
+_CARRIED = ("generator_13_1", "generator_1", "generator_2", "generator_3_progan", "generator_4", "generator_5", "generator_6", "generator_7", "generator_8", "generator_9", "generator_10", "generator_10_2", "generator_11", "generator_12", "generator_13", "generator_13_2", "generator_13_3", "generator_13_4", "generator_13_5", "generator_14")
 
 
 def _module(name):
