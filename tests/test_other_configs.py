@@ -206,9 +206,7 @@ def test_config_cuda_tcgen05_matches_reference_golden(monkeypatch, name):
     compare(name, torch.device("cuda"), **TOL_BF16[name])
 
 
-# (tree13_1 was added after this round's GPU time was spent: CPU port only; its kernels are those of tree12 / tree13)
-@pytest.mark.gpu
-@pytest.mark.parametrize("name", [n for n in ZOO if n != "tree13_1"])
+@pytest.mark.parametrize("name", ZOO)
 def test_zoo_cuda_fp32_matches_reference_golden(monkeypatch, name):
     monkeypatch.setenv("GANB200_PRECISION", "fp32")
     # Adam's first update is lr * g / (|g| + eps): its norm follows the ABSOLUTE rounding error of tiny gradients.  Measured
