@@ -206,6 +206,7 @@ def test_config_cuda_tcgen05_matches_reference_golden(monkeypatch, name):
     compare(name, torch.device("cuda"), **TOL_BF16[name])
 
 
+@pytest.mark.gpu
 @pytest.mark.parametrize("name", ZOO)
 def test_zoo_cuda_fp32_matches_reference_golden(monkeypatch, name):
     monkeypatch.setenv("GANB200_PRECISION", "fp32")
